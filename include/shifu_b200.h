@@ -1,0 +1,284 @@
+/*
+ * shifu_b200.h — C ABI of the B200-native tree-ensemble training hot path.
+ *
+ * This is the drop-in boundary for Shifu's GBT / RF trainer (reference: DevinWu/shifu, package
+ * ml.shifu.shifu.core.dtrain.dt).  The reference has no FFI for this path: the boundary is the Java
+ * class surface DTWorker / DTMaster / Impurity / TreeNode.  Every entry point below cites the Java
+ * method whose body it replaces; INTEGRATION.md shows the JNI stub a Shifu maintainer adds.
+ *
+ * Conventions
+ *   - plain C, plain pointers and sizes; no C++ or torch types cross this boundary;
+ *   - every function returns 0 on success and a negative sb_status on failure; sb_last_error()
+ *     returns the thread-local message (the JNI layer turns it into RuntimeException(msg), which is
+ *     what the reference throws: dt/DTWorker.java:359,878,1229);
+ *   - a handle drives ONE GPU (one Guagua worker == one GPU == one process); it is not thread-safe,
+ *     like a DTWorker instance (dt/DTWorker.java:338-349 is called from one Guagua thread);
+ *   - out-buffers are caller-allocated; the library keeps no caller pointer after a call returns,
+ *     except device pointers registered through sb_load_rows_device;
+ *   - there is no CPU fallback: without a CUDA device sb_create fails with SB_ERR_CUDA.
+ *
+ * Encodings that leak through from the reference (kept identical so BinaryDTSerializer output is
+ * unchanged): Node.ROOT_INDEX = 1, Node.INVALID_INDEX = -1 (dt/Node.java:249,254); heap numbering
+ * left = 2*id, right = 2*id+1 (dt/Node.java:534-558); Split.CONTINUOUS = 1, Split.CATEGORICAL = 2
+ * (dt/Split.java:63-64); SimpleBitSet = byte array, value v is bit (v % 8) of byte (v >> 3)
+ * (dt/SimpleBitSet.java:57-68,89-101).
+ */
+#ifndef SHIFU_B200_H
+#define SHIFU_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SB_API __attribute__((visibility("default")))
+
+typedef enum sb_status {
+    SB_OK = 0,
+    SB_ERR_INVALID = -1,   /* bad argument / inconsistent config (reference: RuntimeException / IllegalStateException) */
+    SB_ERR_CUDA = -2,      /* CUDA runtime error, or no device */
+    SB_ERR_STATE = -3,     /* call order violated (e.g. compute before load) */
+    SB_ERR_RANGE = -4,     /* bin index outside [0, n_bins) (reference: ArrayIndexOutOfBounds in featureUpdate) */
+    SB_ERR_NOMEM = -5,
+    SB_ERR_UNSUPPORTED = -6
+} sb_status;
+
+/* Impurity kinds: dt/Impurity.java (Variance :103, FriedmanMSE :255, Entropy :368, Gini :553). */
+enum { SB_IMPURITY_VARIANCE = 0, SB_IMPURITY_FRIEDMANMSE = 1, SB_IMPURITY_ENTROPY = 2, SB_IMPURITY_GINI = 3 };
+/* Loss kinds: dt/Loss.java (Absolute :36, Squared :55, HalfGradSquared :75, Log :90). */
+enum { SB_LOSS_SQUARED = 0, SB_LOSS_HALFGRADSQUARED = 1, SB_LOSS_ABSOLUTE = 2, SB_LOSS_LOG = 3 };
+/* Split.featureType: dt/Split.java:63-64. */
+enum { SB_SPLIT_CONTINUOUS = 1, SB_SPLIT_CATEGORICAL = 2 };
+
+#define SB_ROOT_INDEX 1
+#define SB_INVALID_INDEX (-1)
+
+/* sb_config.flags */
+#define SB_FLAG_DETERMINISTIC 1u /* reserved: the histogram path is order-independent by construction */
+
+typedef struct sb_handle sb_handle;
+
+/*
+ * What DTWorker.init / DTMaster.init read from ModelConfig.json, ColumnConfig.json and train.params
+ * (dt/DTWorker.java:349-550, dt/DTMaster.java:896-1116), flattened.  A "feature slot" is the position
+ * of a selected column in Data.inputs (DTWorker.inputIndexMap, dt/DTWorker.java:224,1148).
+ */
+typedef struct sb_config {
+    int32_t n_features;            /* DTWorker.inputCount */
+    const int32_t* n_bins;         /* [n_features] stats bins: numeric binBoundary.size(), categorical
+                                      binCategory.size()+1 (dt/DTWorker.java:915-919) */
+    const uint8_t* is_categorical; /* [n_features] */
+    const int32_t* column_num;     /* [n_features] ColumnConfig.columnNum of each slot */
+    const double* bin_boundary;    /* concatenated ColumnConfig.binBoundary of the numeric slots (n_bins[f] doubles
+                                      each, in slot order); may be NULL if the caller builds sb_node.left_mask itself */
+    int32_t impurity;              /* SB_IMPURITY_*  (train.params "Impurity") */
+    int32_t num_classes;           /* Entropy/Gini statsSize (dt/DTWorker.java:462); ignored for variance */
+    int32_t loss;                  /* SB_LOSS_*      (train.params "Loss") */
+    int32_t is_gbdt;               /* 1 = GBT, 0 = RF (dt/DTWorker.java:376-377) */
+    int32_t tree_num;              /* "TreeNum" */
+    int32_t weights_per_row;       /* Data.subsampleWeights.length: 1 or tree_num (dt/DTWorker.java:1521-1547) */
+    int32_t max_depth;             /* "MaxDepth" */
+    int32_t min_instances_per_node;/* "MinInstancesPerNode" */
+    double min_info_gain;          /* "MinInfoGain" */
+    double learning_rate;          /* "LearningRate" */
+    int32_t device;                /* CUDA device ordinal this handle drives */
+    uint32_t flags;
+} sb_config;
+
+/*
+ * One node of a flattened tree == dt/Node.java fields the worker needs.  Children are addressed by
+ * index into the same array (-1 = none).  A node is a leaf for routing when it has no split or no
+ * children, exactly as dt/DTWorker.java:1041.
+ *
+ * Routing (dt/DTWorker.java:1052-1088) is carried as `left_mask`: a SimpleBitSet-encoded byte string
+ * over this feature's stats bins, bit b set <=> a row whose bin index is b goes LEFT.  The host builds
+ * it from the reference's own rule: numeric  bit b = (binBoundary[b] < threshold)   (:1057-1062);
+ * categorical  idx = (0 <= bin < nCats) ? bin : nCats,  bit = (bitset.contains(idx) == isLeft)
+ * (:1064-1087).  Carrying the mask instead of the threshold keeps "compare boundary VALUES, not bin
+ * indices" exact even with duplicate boundaries.
+ */
+typedef struct sb_node {
+    int32_t id;              /* heap id, root = 1 */
+    int32_t left;            /* index of left child in the array, -1 if none */
+    int32_t right;           /* index of right child, -1 if none */
+    int32_t feature;         /* feature slot of the split, -1 if the node has no split */
+    int32_t split_type;      /* SB_SPLIT_* (informational on the device side) */
+    int32_t left_mask_offset;/* byte offset of this node's left_mask in sb_tree.mask_pool */
+    int32_t left_mask_bytes; /* n_bins/8 + 1 */
+    int32_t has_predict;     /* Node.predict != null */
+    double predict;          /* Node.predict.predict */
+    /* The reference's raw Split fields (dt/Split.java:39-58).  The device routes by left_mask only; these are
+       carried so the tree can be handed back unchanged (and so the CPU oracle can route the reference's way). */
+    double threshold;        /* Split.threshold (numeric) */
+    int32_t is_left;         /* Split.isLeft (categorical) */
+    int32_t cat_offset;      /* byte offset of Split.leftOrRightCategories (SimpleBitSet bytes) in mask_pool */
+    int32_t cat_bytes;
+    int32_t reserved;
+} sb_node;
+
+typedef struct sb_tree {
+    int32_t tree_id;         /* TreeNode.treeId */
+    int32_t n_nodes;         /* 0 => placeholder tree with root id INVALID_INDEX (dt/DTMaster.java:500-504) */
+    const sb_node* nodes;    /* nodes[0] is the root */
+    const uint8_t* mask_pool;
+    int32_t mask_pool_bytes;
+} sb_tree;
+
+/* One entry of DTMasterParams.todoNodes (dt/DTMasterParams.java:64, dt/TreeNode.java:41-104). */
+typedef struct sb_todo_node {
+    int32_t key;             /* map key (nodeIndexInGroup, dt/DTMaster.java:467-468) */
+    int32_t tree_id;
+    int32_t node_id;         /* heap id */
+    int32_t n_features;      /* TreeNode.features.size(); 0 => all valid features (dt/DTWorker.java:841-843) */
+    const int32_t* features; /* feature SLOTS, in list order */
+} sb_todo_node;
+
+/* DTMasterParams as the worker consumes it (dt/DTWorker.java:563-571, dt/DTMasterParams.java:44-203). */
+typedef struct sb_iter_in {
+    int32_t n_trees;
+    const sb_tree* trees;    /* GBT: the last one or two trees (dt/DTMaster.java:479-487); RF: all trees */
+    int32_t n_todo;
+    const sb_todo_node* todo;
+    int32_t switch_to_next_tree;
+    int32_t is_first_tree;
+    int32_t continuous_running_start; /* must be 0: continuous training stays on the Java side */
+    /* Injected randomness (the reference draws it from unseeded java.util.Random, dt/DTWorker.java:643-668,
+       634-638).  NULL => keep the current weights / drop nothing. */
+    const float* new_weights;   /* [n_train_rows] replacement for subsampleWeights[currTreeIndex % len] on tree switch */
+    const uint8_t* dropout;     /* [n_train_rows] 1 = drop this tree's contribution for the row */
+} sb_iter_in;
+
+/* DTWorkerParams as the master consumes it (dt/DTWorkerParams.java:44-117). */
+typedef struct sb_iter_out {
+    double train_count;       /* weightedTrainCount */
+    double validation_count;  /* weightedValidationCount */
+    double train_error;
+    double validation_error;
+    double* stats;            /* caller-allocated, sb_stats_len(...) doubles, or NULL to leave stats on the device.
+                                 Layout: todo order; within a node its feature list order; within a feature
+                                 bin-major, stat-minor -- i.e. each feature block is the reference's
+                                 double[bins*statsSize] (dt/DTWorkerParams.java:160-245) */
+    int64_t stats_len;
+} sb_iter_out;
+
+/* GainInfo + Split of the winning candidate of one todo node (dt/GainInfo.java:27-43, dt/Split.java). */
+typedef struct sb_gain {
+    int32_t found;            /* 0 => maxGainInfo == null: node becomes a leaf (dt/DTMaster.java:335-339) */
+    int32_t feature;          /* feature slot */
+    int32_t split_type;       /* SB_SPLIT_* */
+    int32_t split_bin;        /* numeric: i of the winning prefix; threshold = binBoundary[i+1] (dt/Impurity.java:200).
+                                 categorical: number of sorted bins scanned (i+1) */
+    int32_t is_left;          /* categorical: bitset holds the left (1) or right (0) categories (dt/Impurity.java:184-193) */
+    int32_t cat_bytes;        /* bytes used in cat_bits */
+    int32_t left_class;       /* Predict.classValue of the left child (Entropy/Gini), else 0 */
+    int32_t right_class;
+    int32_t node_class;
+    int32_t reserved;
+    double gain, impurity, predict;
+    double left_impurity, right_impurity, left_predict, right_predict;
+    double wgt_cnt;
+} sb_gain;
+
+#define SB_MAX_CAT_BYTES 4096 /* Short.MAX_VALUE categories / 8 + 1 (dt/DTWorker.java:100-101) */
+
+/* ------------------------------------------------------------------ lifecycle */
+
+/* Replaces DTWorker.init (dt/DTWorker.java:349-550): fixes the column layout and train params. */
+SB_API int sb_create(const sb_config* cfg, sb_handle** out);
+SB_API void sb_destroy(sb_handle* h);
+/* Thread-local message of the last failing call on this thread. */
+SB_API const char* sb_last_error(void);
+SB_API const char* sb_version(void);
+
+/* ------------------------------------------------------------------ data load */
+
+/*
+ * Replaces the per-line DTWorker.load (dt/DTWorker.java:1099-1297) for already-binned rows: appends
+ * n_rows records to the training (is_validation = 0) or validation list.  bins[f] points at n_rows
+ * bin indices of feature slot f, uint8 when n_bins[f] <= 256 else uint16 (the reference stores
+ * short, dt/DTWorker.java:1593).  weights is tree-major [weights_per_row][n_rows]
+ * (Data.subsampleWeights transposed); NULL => all 1f.  significance NULL => all 1f.
+ * output = predict = label initially (dt/DTWorker.java:1264-1273).
+ * Host pointers; the call copies to the device and returns when the copy is complete.
+ * May be called repeatedly before the first sb_compute; rows are concatenated.
+ */
+SB_API int sb_load_rows(sb_handle* h, int32_t is_validation, int64_t n_rows, const void* const* bins,
+                        const float* label, const float* significance, const float* weights);
+/* Same, but every pointer is a device pointer on the handle's GPU and is ADOPTED, not copied (the
+   caller keeps it alive until sb_destroy).  bins[f] must be 16-byte aligned.  Single call only. */
+SB_API int sb_load_rows_device(sb_handle* h, int32_t is_validation, int64_t n_rows, const void* const* bins,
+                               float* label, float* significance, float* weights);
+/* Reads back per-row state (any pointer may be NULL): Data.predict, Data.output, current node id of
+   tree `tree_id`, subsampleWeights[w_index]. */
+SB_API int sb_read_rows(sb_handle* h, int32_t is_validation, int32_t tree_id, int32_t w_index, float* predict,
+                        float* output, int32_t* node_id, float* weight);
+
+/* ------------------------------------------------------------------ iteration */
+
+/* Number of doubles sb_compute writes for this todo list (dt/DTWorker.java:903-929 initTodoNodeStats). */
+SB_API int64_t sb_stats_len(sb_handle* h, const sb_iter_in* in);
+
+/*
+ * Replaces DTWorker.doCompute (dt/DTWorker.java:558-891): phase A / A' (GBT predict + residual update,
+ * train / validation error, :582-751), phase B (node x feature x bin statistics via
+ * Impurity.featureUpdate, :762-863) and the thread merge (:865-883).  Synchronous: on return `out`
+ * holds the four scalars and (if out->stats != NULL) the statistics on the host.
+ */
+SB_API int sb_compute(sb_handle* h, const sb_iter_in* in, sb_iter_out* out);
+
+/*
+ * The same iteration in pieces, so that the DTMaster merge of worker results (dt/DTMaster.java:298-315) can run
+ * as collectives between them when rows are sharded over several GPUs (one handle / process per GPU):
+ *   sb_compute_begin   phase A / A' (routing, GBT update, error sums) + per-statistic maxima of the pass
+ *   sb_scale_buffer    device pointer to 3 x int32 maxima (fp32 bit patterns)      -> all-reduce MAX
+ *   sb_compute_stats   phase B: fixed-point scales from the maxima, then the histogram kernel, which leaves
+ *                      order-independent integer accumulators on the device
+ *   sb_raw_buffer      device pointer + byte size of those accumulators (int64)    -> all-reduce SUM
+ *   sb_acc_buffer      device pointer to the 4 fp64 scalars (counts, errors)       -> all-reduce SUM
+ *   sb_compute_finish  converts accumulators to the reference's double[] statistics (device-resident),
+ *                      fills the scalars of `out`, copies stats to out->stats when non-NULL.
+ * With one GPU the collectives are simply skipped (that is what sb_compute does).
+ * All work is enqueued on the stream given to sb_set_stream (default: the legacy default stream);
+ * sb_compute_begin returns without synchronising.
+ */
+SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in);
+SB_API int sb_scale_buffer(sb_handle* h, void** dev_ptr, int64_t* bytes);
+SB_API int sb_compute_stats(sb_handle* h);
+SB_API int sb_raw_buffer(sb_handle* h, void** dev_ptr, int64_t* bytes);
+SB_API int sb_acc_buffer(sb_handle* h, void** dev_ptr, int64_t* bytes);
+SB_API int sb_compute_finish(sb_handle* h, sb_iter_out* out);
+SB_API int sb_set_stream(sb_handle* h, void* cuda_stream);
+
+/*
+ * Replaces the per-node body of DTMaster.doCompute (dt/DTMaster.java:316-340): for every todo node of the
+ * last sb_compute*, Impurity.computeImpurity per feature (dt/Impurity.java:120-211,269-360,378-477,563-661)
+ * and GainInfo.getGainInfoByMaxGain across features (dt/GainInfo.java:200-214), on the device, from the
+ * (all-reduced) statistics.  visit_order: feature slots in the order the reference's HashMap iterates
+ * them (dt/DTMaster.java:324), or NULL for each node's own feature list order.
+ * gains: [n_todo]; cat_bits: [n_todo * SB_MAX_CAT_BYTES] or NULL when no categorical feature exists.
+ */
+SB_API int sb_best_splits(sb_handle* h, sb_gain* gains, uint8_t* cat_bits);
+
+/* ------------------------------------------------------------------ pieces of the path (bench / tests) */
+
+/* Re-runs only the statistics pass (phase B) of the last sb_compute_begin, n_repeat times, and reports the
+   mean device time of the histogram kernel in milliseconds (CUDA events on the handle's stream). */
+SB_API int sb_time_stats_pass(sb_handle* h, int32_t n_repeat, float* ms_hist_kernel, float* ms_total);
+/* Counters since creation: kernels launched by this library, bytes copied H2D / D2H. */
+SB_API int sb_counters(sb_handle* h, int64_t* launches, int64_t* h2d_bytes, int64_t* d2h_bytes);
+/* Fills device memory with the synthetic data set of SURVEY.md 8(d) (counter-based splitmix64) and loads it:
+   n_rows rows starting at global row `row0`, all features uint8 with n_bins[f] uniform bins.
+   label_kind 0: binary label from a 5-feature logistic with 10% flips (C2); 1: threshold rule (C1). */
+SB_API int sb_load_synthetic(sb_handle* h, int32_t is_validation, int64_t row0, int64_t n_rows, uint64_t seed,
+                             int32_t label_kind, int32_t weighted);
+/* Copies one synthetic column / label range to the host so the oracle can be fed identical rows. */
+SB_API int sb_read_bins(sb_handle* h, int32_t is_validation, int32_t feature, int64_t row0, int64_t n_rows, void* out);
+SB_API int sb_read_labels(sb_handle* h, int32_t is_validation, int64_t row0, int64_t n_rows, float* label,
+                          float* significance);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SHIFU_B200_H */

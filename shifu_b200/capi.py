@@ -1,0 +1,356 @@
+"""ctypes binding of include/shifu_b200.h (the C ABI of the B200 tree-training hot path).
+
+This is the binding a Python host would use; the Java host binds the same symbols over JNI.
+Nothing here computes: every call goes to libshifu_b200.so, and loading fails loudly if the library is missing.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libshifu_b200.so")
+
+SB_IMPURITY_VARIANCE, SB_IMPURITY_FRIEDMANMSE, SB_IMPURITY_ENTROPY, SB_IMPURITY_GINI = 0, 1, 2, 3
+SB_LOSS_SQUARED, SB_LOSS_HALFGRADSQUARED, SB_LOSS_ABSOLUTE, SB_LOSS_LOG = 0, 1, 2, 3
+SB_SPLIT_CONTINUOUS, SB_SPLIT_CATEGORICAL = 1, 2
+SB_ROOT_INDEX, SB_INVALID_INDEX = 1, -1
+SB_MAX_CAT_BYTES = 4096
+
+
+class SbConfig(C.Structure):
+    _fields_ = [
+        ("n_features", C.c_int32),
+        ("n_bins", C.POINTER(C.c_int32)),
+        ("is_categorical", C.POINTER(C.c_uint8)),
+        ("column_num", C.POINTER(C.c_int32)),
+        ("bin_boundary", C.POINTER(C.c_double)),
+        ("impurity", C.c_int32),
+        ("num_classes", C.c_int32),
+        ("loss", C.c_int32),
+        ("is_gbdt", C.c_int32),
+        ("tree_num", C.c_int32),
+        ("weights_per_row", C.c_int32),
+        ("max_depth", C.c_int32),
+        ("min_instances_per_node", C.c_int32),
+        ("min_info_gain", C.c_double),
+        ("learning_rate", C.c_double),
+        ("device", C.c_int32),
+        ("flags", C.c_uint32),
+    ]
+
+
+class SbNode(C.Structure):
+    _fields_ = [
+        ("id", C.c_int32),
+        ("left", C.c_int32),
+        ("right", C.c_int32),
+        ("feature", C.c_int32),
+        ("split_type", C.c_int32),
+        ("left_mask_offset", C.c_int32),
+        ("left_mask_bytes", C.c_int32),
+        ("has_predict", C.c_int32),
+        ("predict", C.c_double),
+        ("threshold", C.c_double),
+        ("is_left", C.c_int32),
+        ("cat_offset", C.c_int32),
+        ("cat_bytes", C.c_int32),
+        ("reserved", C.c_int32),
+    ]
+
+
+class SbTree(C.Structure):
+    _fields_ = [
+        ("tree_id", C.c_int32),
+        ("n_nodes", C.c_int32),
+        ("nodes", C.POINTER(SbNode)),
+        ("mask_pool", C.POINTER(C.c_uint8)),
+        ("mask_pool_bytes", C.c_int32),
+    ]
+
+
+class SbTodoNode(C.Structure):
+    _fields_ = [
+        ("key", C.c_int32),
+        ("tree_id", C.c_int32),
+        ("node_id", C.c_int32),
+        ("n_features", C.c_int32),
+        ("features", C.POINTER(C.c_int32)),
+    ]
+
+
+class SbIterIn(C.Structure):
+    _fields_ = [
+        ("n_trees", C.c_int32),
+        ("trees", C.POINTER(SbTree)),
+        ("n_todo", C.c_int32),
+        ("todo", C.POINTER(SbTodoNode)),
+        ("switch_to_next_tree", C.c_int32),
+        ("is_first_tree", C.c_int32),
+        ("continuous_running_start", C.c_int32),
+        ("new_weights", C.POINTER(C.c_float)),
+        ("dropout", C.POINTER(C.c_uint8)),
+    ]
+
+
+class SbIterOut(C.Structure):
+    _fields_ = [
+        ("train_count", C.c_double),
+        ("validation_count", C.c_double),
+        ("train_error", C.c_double),
+        ("validation_error", C.c_double),
+        ("stats", C.POINTER(C.c_double)),
+        ("stats_len", C.c_int64),
+    ]
+
+
+class SbGain(C.Structure):
+    _fields_ = [
+        ("found", C.c_int32),
+        ("feature", C.c_int32),
+        ("split_type", C.c_int32),
+        ("split_bin", C.c_int32),
+        ("is_left", C.c_int32),
+        ("cat_bytes", C.c_int32),
+        ("left_class", C.c_int32),
+        ("right_class", C.c_int32),
+        ("node_class", C.c_int32),
+        ("reserved", C.c_int32),
+        ("gain", C.c_double),
+        ("impurity", C.c_double),
+        ("predict", C.c_double),
+        ("left_impurity", C.c_double),
+        ("right_impurity", C.c_double),
+        ("left_predict", C.c_double),
+        ("right_predict", C.c_double),
+        ("wgt_cnt", C.c_double),
+    ]
+
+
+# every symbol include/shifu_b200.h declares (tests check that the library exports all of them)
+EXPORTS = [
+    "sb_create", "sb_destroy", "sb_last_error", "sb_version", "sb_load_rows", "sb_load_rows_device", "sb_read_rows",
+    "sb_stats_len", "sb_compute", "sb_compute_begin", "sb_scale_buffer", "sb_compute_stats", "sb_raw_buffer",
+    "sb_acc_buffer", "sb_compute_finish", "sb_set_stream", "sb_best_splits", "sb_time_stats_pass", "sb_counters",
+    "sb_load_synthetic", "sb_read_bins", "sb_read_labels",
+]
+
+_lib = None
+
+
+def load_library(path=None):
+    """dlopen libshifu_b200.so; raises if it is absent (there is no CPU fallback)."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.exists(p):
+        raise RuntimeError(
+            "%s not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` or ./build.sh "
+            "(shifu_b200 has no CPU fallback)" % p)
+    lib = C.CDLL(p)
+    H = C.c_void_p
+    lib.sb_create.argtypes = [C.POINTER(SbConfig), C.POINTER(H)]
+    lib.sb_destroy.argtypes = [H]
+    lib.sb_destroy.restype = None
+    lib.sb_last_error.restype = C.c_char_p
+    lib.sb_version.restype = C.c_char_p
+    lib.sb_load_rows.argtypes = [H, C.c_int32, C.c_int64, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.sb_load_rows_device.argtypes = [H, C.c_int32, C.c_int64, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.sb_read_rows.argtypes = [H, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.sb_stats_len.argtypes = [H, C.POINTER(SbIterIn)]
+    lib.sb_stats_len.restype = C.c_int64
+    lib.sb_compute.argtypes = [H, C.POINTER(SbIterIn), C.POINTER(SbIterOut)]
+    lib.sb_compute_begin.argtypes = [H, C.POINTER(SbIterIn)]
+    lib.sb_scale_buffer.argtypes = [H, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
+    lib.sb_compute_stats.argtypes = [H]
+    lib.sb_raw_buffer.argtypes = [H, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
+    lib.sb_acc_buffer.argtypes = [H, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
+    lib.sb_compute_finish.argtypes = [H, C.POINTER(SbIterOut)]
+    lib.sb_set_stream.argtypes = [H, C.c_void_p]
+    lib.sb_best_splits.argtypes = [H, C.POINTER(SbGain), C.c_void_p]
+    lib.sb_time_stats_pass.argtypes = [H, C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    lib.sb_counters.argtypes = [H, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+    lib.sb_load_synthetic.argtypes = [H, C.c_int32, C.c_int64, C.c_int64, C.c_uint64, C.c_int32, C.c_int32]
+    lib.sb_read_bins.argtypes = [H, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_void_p]
+    lib.sb_read_labels.argtypes = [H, C.c_int32, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
+    if path is None:
+        _lib = lib
+    return lib
+
+
+class SbError(RuntimeError):
+    """Raised for a non-zero sb_status; the reference throws RuntimeException / IllegalStateException here."""
+
+    def __init__(self, code, msg):
+        super().__init__("shifu_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+def check(lib, rc):
+    if rc != 0:
+        raise SbError(rc, lib.sb_last_error().decode())
+
+
+def _ptr(a, ctype):
+    return a.ctypes.data_as(C.POINTER(ctype))
+
+
+class ConfigArrays:
+    """Keeps the numpy arrays an SbConfig points at alive."""
+
+    def __init__(self, n_bins, is_categorical=None, column_num=None, bin_boundary=None, impurity=SB_IMPURITY_VARIANCE,
+                 num_classes=2, loss=SB_LOSS_SQUARED, is_gbdt=True, tree_num=1, weights_per_row=1, max_depth=8,
+                 min_instances_per_node=1, min_info_gain=0.0, learning_rate=0.05, device=0, flags=0):
+        self.n_bins = np.ascontiguousarray(n_bins, dtype=np.int32)
+        F = len(self.n_bins)
+        self.is_categorical = np.ascontiguousarray(
+            is_categorical if is_categorical is not None else np.zeros(F), dtype=np.uint8)
+        self.column_num = np.ascontiguousarray(column_num if column_num is not None else np.arange(F), dtype=np.int32)
+        if bin_boundary is None:
+            # default boundaries [-inf, 1, 2, ...] for numeric slots
+            bb = []
+            for f in range(F):
+                if not self.is_categorical[f]:
+                    bb.extend([-np.inf] + [float(b) for b in range(1, int(self.n_bins[f]))])
+            bin_boundary = bb
+        self.bin_boundary = np.ascontiguousarray(bin_boundary, dtype=np.float64)
+        c = SbConfig()
+        c.n_features = F
+        c.n_bins = _ptr(self.n_bins, C.c_int32)
+        c.is_categorical = _ptr(self.is_categorical, C.c_uint8)
+        c.column_num = _ptr(self.column_num, C.c_int32)
+        c.bin_boundary = _ptr(self.bin_boundary, C.c_double)
+        c.impurity, c.num_classes, c.loss = impurity, num_classes, loss
+        c.is_gbdt, c.tree_num, c.weights_per_row = int(bool(is_gbdt)), tree_num, weights_per_row
+        c.max_depth, c.min_instances_per_node = max_depth, min_instances_per_node
+        c.min_info_gain, c.learning_rate = min_info_gain, learning_rate
+        c.device, c.flags = device, flags
+        self.struct = c
+        self.stats_size = 3 if impurity in (SB_IMPURITY_VARIANCE, SB_IMPURITY_FRIEDMANMSE) else num_classes
+
+    def boundaries_of(self, f):
+        off = 0
+        for g in range(f):
+            if not self.is_categorical[g]:
+                off += int(self.n_bins[g])
+        return self.bin_boundary[off:off + int(self.n_bins[f])]
+
+
+class Worker:
+    """Thin object wrapper over an sb_handle: the DTWorker of one GPU."""
+
+    def __init__(self, cfg: ConfigArrays):
+        self.lib = load_library()
+        self.cfg = cfg
+        self.h = C.c_void_p()
+        check(self.lib, self.lib.sb_create(C.byref(cfg.struct), C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            self.lib.sb_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def load_rows(self, bins_cols, label, significance=None, weights=None, is_validation=False):
+        """bins_cols: list of 1-D uint8 arrays (one per feature slot); weights: [weights_per_row, n] float32."""
+        n = len(label)
+        self._keep = [np.ascontiguousarray(b, dtype=np.uint8) for b in bins_cols]
+        ptrs = (C.c_void_p * len(self._keep))(*[b.ctypes.data for b in self._keep])
+        label = np.ascontiguousarray(label, dtype=np.float32)
+        sig = None if significance is None else np.ascontiguousarray(significance, dtype=np.float32)
+        w = None if weights is None else np.ascontiguousarray(weights, dtype=np.float32)
+        check(self.lib, self.lib.sb_load_rows(self.h, int(is_validation), n, ptrs, label.ctypes.data,
+                                              None if sig is None else sig.ctypes.data,
+                                              None if w is None else w.ctypes.data))
+
+    def load_synthetic(self, n_rows, seed, row0=0, label_kind=0, weighted=False, is_validation=False):
+        check(self.lib, self.lib.sb_load_synthetic(self.h, int(is_validation), row0, n_rows, seed, label_kind,
+                                                   int(weighted)))
+
+    def read_bins(self, feature, row0, n_rows, is_validation=False):
+        out = np.empty(n_rows, dtype=np.uint8)
+        check(self.lib, self.lib.sb_read_bins(self.h, int(is_validation), feature, row0, n_rows, out.ctypes.data))
+        return out
+
+    def read_labels(self, row0, n_rows, is_validation=False):
+        lab = np.empty(n_rows, dtype=np.float32)
+        sig = np.empty(n_rows, dtype=np.float32)
+        check(self.lib, self.lib.sb_read_labels(self.h, int(is_validation), row0, n_rows, lab.ctypes.data,
+                                                sig.ctypes.data))
+        return lab, sig
+
+    def read_rows(self, n, is_validation=False, tree_id=0, w_index=0, want_weight=True):
+        predict = np.empty(n, dtype=np.float32)
+        output = np.empty(n, dtype=np.float32)
+        node = np.empty(n, dtype=np.int32)
+        weight = np.empty(n, dtype=np.float32) if (want_weight and not is_validation) else None
+        check(self.lib, self.lib.sb_read_rows(self.h, int(is_validation), tree_id, w_index, predict.ctypes.data,
+                                              output.ctypes.data, node.ctypes.data,
+                                              None if weight is None else weight.ctypes.data))
+        return predict, output, node, weight
+
+    def stats_len(self, it):
+        n = self.lib.sb_stats_len(self.h, C.byref(it.struct))
+        if n < 0:
+            check(self.lib, int(n))
+        return int(n)
+
+    def compute(self, it, want_stats=True):
+        """DTWorker.doCompute: returns (train_count, validation_count, train_error, validation_error, stats)."""
+        n = self.stats_len(it)
+        out = SbIterOut()
+        stats = np.zeros(max(n, 1), dtype=np.float64)
+        if want_stats:
+            out.stats = _ptr(stats, C.c_double)
+            out.stats_len = n
+        check(self.lib, self.lib.sb_compute(self.h, C.byref(it.struct), C.byref(out)))
+        return out.train_count, out.validation_count, out.train_error, out.validation_error, stats[:n]
+
+    def compute_begin(self, it):
+        check(self.lib, self.lib.sb_compute_begin(self.h, C.byref(it.struct)))
+
+    def compute_stats(self):
+        check(self.lib, self.lib.sb_compute_stats(self.h))
+
+    def compute_finish(self, n_stats=0, want_stats=False):
+        out = SbIterOut()
+        stats = np.zeros(max(n_stats, 1), dtype=np.float64)
+        if want_stats:
+            out.stats = _ptr(stats, C.c_double)
+            out.stats_len = n_stats
+        check(self.lib, self.lib.sb_compute_finish(self.h, C.byref(out)))
+        return out.train_count, out.validation_count, out.train_error, out.validation_error, stats[:n_stats]
+
+    def device_buffers(self):
+        """(scale_ptr, scale_bytes, raw_ptr, raw_bytes, acc_ptr, acc_bytes): what a multi-GPU driver all-reduces."""
+        p, b = C.c_void_p(), C.c_int64()
+        res = []
+        for fn in (self.lib.sb_scale_buffer, self.lib.sb_raw_buffer, self.lib.sb_acc_buffer):
+            check(self.lib, fn(self.h, C.byref(p), C.byref(b)))
+            res += [p.value, b.value]
+        return tuple(res)
+
+    def best_splits(self, n_todo, with_cat=False):
+        gains = (SbGain * max(n_todo, 1))()
+        bits = np.zeros(max(n_todo, 1) * SB_MAX_CAT_BYTES, dtype=np.uint8) if with_cat else None
+        check(self.lib, self.lib.sb_best_splits(self.h, gains, None if bits is None else bits.ctypes.data))
+        return list(gains)[:n_todo], bits
+
+    def time_stats_pass(self, n_repeat=3):
+        a, b = C.c_float(), C.c_float()
+        check(self.lib, self.lib.sb_time_stats_pass(self.h, n_repeat, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def counters(self):
+        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
+        check(self.lib, self.lib.sb_counters(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def set_stream(self, stream_ptr):
+        check(self.lib, self.lib.sb_set_stream(self.h, C.c_void_p(stream_ptr)))

@@ -1,0 +1,953 @@
+// api.cu -- the C ABI of include/shifu_b200.h: handle, data load, the DTWorker.doCompute replacement and the
+// on-device DTMaster best-split step.  Host logic only; kernels live in hist.cu / rows.cu / split.cu.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <memory>
+
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace sb {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string& msg) { g_last_error = msg; }
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+template <typename T>
+struct DevBuf {  // grow-only device buffer
+    T* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = std::max<size_t>(n, 16);
+        cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+struct HistLaunch {
+    int kind;
+    HistArgs args;
+    int grid;
+    size_t smem;
+};
+
+}  // namespace sb
+
+using namespace sb;
+
+struct sb_handle {
+    sb_config cfg{};
+    std::vector<int32_t> n_bins, column_num;
+    std::vector<uint8_t> is_cat;
+    std::vector<double> bin_boundary;
+    std::vector<int> all_features;  // getAllValidFeatures (dt/DTWorker.java:965-990)
+    int stats_size = 3;
+    int stat_kind = STAT_VARIANCE;
+    int max_bins = 0;
+    cudaStream_t stream = nullptr;
+
+    RowSet train, valid;
+    int32_t* d_feat_bins = nullptr;
+    std::map<int, DeviceTree> trees;  // by tree id
+    int tracked_tree = -1;            // GBT: tree id whose node ids train.node_id currently holds
+
+    // iteration state
+    TodoLayout layout;
+    bool begun = false, stats_ready = false;
+    std::vector<HistLaunch> launches;
+    DevBuf<int64_t> raw;      // [2 * total]: lo then hi
+    DevBuf<double> stats;     // [total]
+    DevBuf<int32_t> tile_feats;
+    DevBuf<uint32_t> slot_fmask;
+    DevBuf<int64_t> pair_off;
+    DevBuf<int16_t> slot_of_node;
+    DevBuf<SplitTask> tasks;
+    DevBuf<int32_t> node_task_begin;
+    DevBuf<sb_gain> cand, gain_out;
+    DevBuf<uint8_t> cand_bits, out_bits, new_dropout;
+    DevBuf<float> new_weights;
+    DevBuf<double> sort_keys;
+    DevBuf<int> sort_idx, sort_tmp;
+    DevBuf<uint8_t> sort_flags;
+    int n_tasks = 0;
+    bool has_cat_tasks = false;
+    double* d_acc = nullptr;          // 4 doubles
+    double* d_err_scratch = nullptr;  // ERR_SCRATCH_DOUBLES
+    uint32_t* d_maxbits = nullptr;    // 3 words (+1 pad)
+    float* d_scales = nullptr;        // 3
+    double* d_inv_scales = nullptr;   // 3
+    uint32_t* d_error_flag = nullptr;
+
+    int64_t launches_count = 0, h2d_bytes = 0, d2h_bytes = 0;
+};
+
+namespace {
+
+bool is_variance(int imp) { return imp == SB_IMPURITY_VARIANCE || imp == SB_IMPURITY_FRIEDMANMSE; }
+
+void free_rowset(RowSet& r) {
+    if (r.d_col) cudaFree((void*)r.d_col);
+    if (r.owns_inputs) {
+        if (r.owned_bins) cudaFree(r.owned_bins);
+        if (r.label) cudaFree(r.label);
+        if (r.significance) cudaFree(r.significance);
+        if (r.weights) cudaFree(r.weights);
+    }
+    if (r.output) cudaFree(r.output);
+    if (r.predict) cudaFree(r.predict);
+    if (r.node_id) cudaFree(r.node_id);
+    r = RowSet();
+}
+
+void free_tree(DeviceTree& t) {
+    if (t.feat) cudaFree(t.feat);
+    if (t.mask_off) cudaFree(t.mask_off);
+    if (t.predict) cudaFree(t.predict);
+    if (t.has_predict) cudaFree(t.has_predict);
+    if (t.masks) cudaFree(t.masks);
+    t = DeviceTree();
+}
+
+TreeView view_of(const DeviceTree& t) { return TreeView{t.feat, t.mask_off, t.predict, t.has_predict, t.masks, t.capacity}; }
+
+int n_node_arrays(const sb_handle* h) { return h->cfg.is_gbdt ? 1 : std::max(1, h->cfg.tree_num); }
+
+// Allocates the derived per-row state and finishes a load (shared by the host and device loaders).
+int finish_load(sb_handle* h, RowSet& r) {
+    const int64_t n = r.n;
+    SB_CUDA(cudaMalloc(&r.d_col, sizeof(void*) * std::max(1, r.n_features)));
+    SB_CUDA(cudaMemcpyAsync((void*)r.d_col, r.h_col.data(), sizeof(void*) * r.n_features, cudaMemcpyHostToDevice, h->stream));
+    SB_CUDA(cudaMalloc(&r.output, sizeof(float) * std::max<int64_t>(n, 1)));
+    SB_CUDA(cudaMalloc(&r.predict, sizeof(float) * std::max<int64_t>(n, 1)));
+    r.n_node_arrays = n_node_arrays(h);
+    SB_CUDA(cudaMalloc(&r.node_id, sizeof(int32_t) * std::max<int64_t>(n * r.n_node_arrays, 1)));
+    // output = predict = label (dt/DTWorker.java:1264-1273); every row starts at the root
+    SB_CUDA(launch_copy_f32(r.output, r.label, n, h->stream));
+    SB_CUDA(launch_copy_f32(r.predict, r.label, n, h->stream));
+    SB_CUDA(launch_fill_i32(r.node_id, n * r.n_node_arrays, SB_ROOT_INDEX, h->stream));
+    // bin indices must address the statistics arrays (the reference would throw ArrayIndexOutOfBounds)
+    SB_CUDA(cudaMemsetAsync(h->d_error_flag, 0, 4, h->stream));
+    SB_CUDA(launch_check_bins(r.d_col, h->d_feat_bins, r.n_features, n, h->d_error_flag, h->stream));
+    h->launches_count += 4;
+    uint32_t flag = 0;
+    SB_CUDA(cudaMemcpyAsync(&flag, h->d_error_flag, 4, cudaMemcpyDeviceToHost, h->stream));
+    SB_CUDA(cudaStreamSynchronize(h->stream));
+    if (flag & 2u) return fail(SB_ERR_RANGE, "a bin index is outside [0, n_bins) of its feature");
+    r.loaded = true;
+    return SB_OK;
+}
+
+int upload_tree(sb_handle* h, const sb_tree& t, DeviceTree& d) {
+    int max_id = 1;
+    for (int i = 0; i < t.n_nodes; ++i) {
+        if (t.nodes[i].id <= 0) return fail(SB_ERR_INVALID, "tree node with non-positive id");
+        max_id = std::max(max_id, t.nodes[i].id);
+    }
+    if (max_id >= (1 << 24)) return fail(SB_ERR_UNSUPPORTED, "node id beyond 2^24 (MaxDepth <= 20 in the reference)");
+    const int cap = max_id + 1;
+    if (cap > d.capacity) {
+        const int mask_cap = d.mask_capacity;
+        uint8_t* masks = d.masks;
+        d.masks = nullptr;
+        free_tree(d);
+        d.masks = masks;
+        d.mask_capacity = mask_cap;
+        int newcap = 256;
+        while (newcap < cap) newcap *= 2;
+        SB_CUDA(cudaMalloc(&d.feat, sizeof(int32_t) * newcap));
+        SB_CUDA(cudaMalloc(&d.mask_off, sizeof(int32_t) * newcap));
+        SB_CUDA(cudaMalloc(&d.predict, sizeof(double) * newcap));
+        SB_CUDA(cudaMalloc(&d.has_predict, newcap));
+        d.capacity = newcap;
+    }
+    if (t.mask_pool_bytes > d.mask_capacity) {
+        if (d.masks) cudaFree(d.masks);
+        int newcap = 4096;
+        while (newcap < t.mask_pool_bytes) newcap *= 2;
+        SB_CUDA(cudaMalloc(&d.masks, newcap));
+        d.mask_capacity = newcap;
+    }
+    std::vector<int32_t> feat((size_t)d.capacity, -1), moff((size_t)d.capacity, 0);
+    std::vector<double> pred((size_t)d.capacity, 0.0);
+    std::vector<uint8_t> hasp((size_t)d.capacity, 0);
+    for (int i = 0; i < t.n_nodes; ++i) {
+        const sb_node& nd = t.nodes[i];
+        const bool routes = nd.feature >= 0 && (nd.left >= 0 || nd.right >= 0);  // dt/DTWorker.java:1041
+        if (routes) {
+            if (nd.feature >= h->cfg.n_features) return fail(SB_ERR_INVALID, "split feature slot out of range");
+            const int need = h->n_bins[nd.feature] / 8 + 1;
+            if (nd.left_mask_bytes < need || nd.left_mask_offset < 0 || nd.left_mask_offset + nd.left_mask_bytes > t.mask_pool_bytes)
+                return fail(SB_ERR_INVALID, "left_mask of a split node is missing or too short");
+            if (h->n_bins[nd.feature] > 256) return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins are not supported yet");
+            feat[nd.id] = nd.feature;
+            moff[nd.id] = nd.left_mask_offset;
+        }
+        pred[nd.id] = nd.predict;
+        hasp[nd.id] = nd.has_predict ? 1 : 0;
+    }
+    SB_CUDA(cudaMemcpyAsync(d.feat, feat.data(), sizeof(int32_t) * d.capacity, cudaMemcpyHostToDevice, h->stream));
+    SB_CUDA(cudaMemcpyAsync(d.mask_off, moff.data(), sizeof(int32_t) * d.capacity, cudaMemcpyHostToDevice, h->stream));
+    SB_CUDA(cudaMemcpyAsync(d.predict, pred.data(), sizeof(double) * d.capacity, cudaMemcpyHostToDevice, h->stream));
+    SB_CUDA(cudaMemcpyAsync(d.has_predict, hasp.data(), d.capacity, cudaMemcpyHostToDevice, h->stream));
+    if (t.mask_pool_bytes > 0)
+        SB_CUDA(cudaMemcpyAsync(d.masks, t.mask_pool, t.mask_pool_bytes, cudaMemcpyHostToDevice, h->stream));
+    h->h2d_bytes += (int64_t)d.capacity * 17 + t.mask_pool_bytes;
+    return SB_OK;
+}
+
+// dt/DTWorker.java:903-929 initTodoNodeStats: sizes and order of the statistics buffer.
+int build_layout(const sb_handle* h, const sb_iter_in* in, TodoLayout& lay) {
+    lay.nodes.clear();
+    int64_t off = 0;
+    for (int i = 0; i < in->n_todo; ++i) {
+        const sb_todo_node& t = in->todo[i];
+        TodoLayout::Node nd;
+        nd.key = t.key; nd.tree_id = t.tree_id; nd.node_id = t.node_id; nd.offset = off;
+        if (t.n_features == 0) nd.features.assign(h->all_features.begin(), h->all_features.end());
+        else nd.features.assign(t.features, t.features + t.n_features);
+        int64_t l = 0;
+        for (int f : nd.features) {
+            if (f < 0 || f >= h->cfg.n_features) return fail(SB_ERR_INVALID, "todo node feature slot out of range");
+            nd.feat_off.push_back(l);
+            l += (int64_t)h->n_bins[f] * h->stats_size;
+        }
+        off += l;
+        lay.nodes.push_back(std::move(nd));
+    }
+    lay.total = off;
+    return SB_OK;
+}
+
+// Iteration order of a java.util.HashMap<Integer, double[]> created with (n, 1f) and filled in list order
+// (dt/DTWorker.java:910, dt/DTWorkerParams.java:235), as walked at dt/DTMaster.java:324: buckets ascending,
+// insertion order inside a bucket.  Returns rank[i] = visit position of list entry i.
+std::vector<int> hashmap_visit_rank(const std::vector<int>& column_nums) {
+    const int n = (int)column_nums.size();
+    int cap = 1;
+    while (cap < n) cap <<= 1;
+    std::vector<int> pos((size_t)n);
+    for (int i = 0; i < n; ++i) pos[i] = i;
+    auto bucket = [cap](int k) {
+        uint32_t x = (uint32_t)k;
+        x ^= x >> 16;
+        return (int)(x & (uint32_t)(cap - 1));
+    };
+    std::stable_sort(pos.begin(), pos.end(), [&](int a, int b) { return bucket(column_nums[a]) < bucket(column_nums[b]); });
+    std::vector<int> rank((size_t)n);
+    for (int i = 0; i < n; ++i) rank[pos[i]] = i;
+    return rank;
+}
+
+int plan_histograms(sb_handle* h, const sb_iter_in* in) {
+    h->launches.clear();
+    const TodoLayout& lay = h->layout;
+    const int S = (int)lay.nodes.size();
+    const int F = h->cfg.n_features;
+    if (S == 0 || h->train.n == 0) return SB_OK;
+
+    // slots grouped by tree (one launch per tree: a row has one node id per tree)
+    std::vector<int> order((size_t)S);
+    for (int i = 0; i < S; ++i) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return lay.nodes[a].tree_id < lay.nodes[b].tree_id; });
+
+    // tiles of 32 feature slots over the union of the feature lists
+    std::vector<uint8_t> used((size_t)F, 0);
+    for (const auto& nd : lay.nodes)
+        for (int f : nd.features) used[f] = 1;
+    std::vector<int32_t> tile_feats;
+    int bins_pad = 1;
+    for (int f = 0; f < F; ++f)
+        if (used[f]) {
+            if (h->n_bins[f] > 256) return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins are not supported yet");
+            tile_feats.push_back(f);
+            bins_pad = std::max(bins_pad, h->n_bins[f]);
+        }
+    while (tile_feats.size() % 32) tile_feats.push_back(-1);
+    const int n_tiles = (int)tile_feats.size() / 32;
+    if (n_tiles == 0) return SB_OK;
+    std::vector<int> tile_of((size_t)F, -1), lane_of((size_t)F, -1);
+    for (size_t i = 0; i < tile_feats.size(); ++i)
+        if (tile_feats[i] >= 0) { tile_of[tile_feats[i]] = (int)(i / 32); lane_of[tile_feats[i]] = (int)(i % 32); }
+
+    std::vector<uint32_t> fmask((size_t)S * n_tiles, 0u);
+    std::vector<int64_t> pair_off((size_t)S * F, -1);
+    for (int s = 0; s < S; ++s) {
+        const auto& nd = lay.nodes[order[s]];
+        for (size_t k = 0; k < nd.features.size(); ++k) {
+            const int f = nd.features[k];
+            fmask[(size_t)s * n_tiles + tile_of[f]] |= 1u << lane_of[f];
+            pair_off[(size_t)s * F + f] = nd.offset + nd.feat_off[k];
+        }
+    }
+    SB_CUDA(h->tile_feats.reserve(tile_feats.size()));
+    SB_CUDA(h->slot_fmask.reserve(fmask.size()));
+    SB_CUDA(h->pair_off.reserve(pair_off.size()));
+    SB_CUDA(cudaMemcpyAsync(h->tile_feats.p, tile_feats.data(), tile_feats.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    SB_CUDA(cudaMemcpyAsync(h->slot_fmask.p, fmask.data(), fmask.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    SB_CUDA(cudaMemcpyAsync(h->pair_off.p, pair_off.data(), pair_off.size() * 8, cudaMemcpyHostToDevice, h->stream));
+    h->h2d_bytes += tile_feats.size() * 4 + fmask.size() * 4 + pair_off.size() * 8;
+
+    const int nw = h->stat_kind == STAT_VARIANCE ? 6 : 2 * h->stats_size;
+    const int max_gs = hist_max_slots_per_block(bins_pad, nw);
+    if (max_gs < 1) return fail(SB_ERR_UNSUPPORTED, "one node's histogram tile does not fit in shared memory");
+
+    // per tree: slot table + launch
+    size_t table_total = 0;
+    std::vector<std::pair<int, int>> tree_ranges;  // [begin, end) in `order`
+    for (int s = 0; s < S;) {
+        int e = s;
+        while (e < S && lay.nodes[order[e]].tree_id == lay.nodes[order[s]].tree_id) ++e;
+        tree_ranges.push_back({s, e});
+        s = e;
+    }
+    std::vector<int> table_size(tree_ranges.size());
+    for (size_t t = 0; t < tree_ranges.size(); ++t) {
+        int max_id = 1;
+        for (int s = tree_ranges[t].first; s < tree_ranges[t].second; ++s) max_id = std::max(max_id, lay.nodes[order[s]].node_id);
+        table_size[t] = max_id + 1;
+        table_total += (size_t)table_size[t];
+    }
+    std::vector<int16_t> tables(table_total, (int16_t)-1);
+    SB_CUDA(h->slot_of_node.reserve(table_total));
+    size_t toff = 0;
+    const int64_t n = h->train.n;
+    const int W = h->cfg.weights_per_row;
+    for (size_t t = 0; t < tree_ranges.size(); ++t) {
+        const int s0 = tree_ranges[t].first, s1 = tree_ranges[t].second;
+        const int tree_id = lay.nodes[order[s0]].tree_id;
+        const int ns = s1 - s0;
+        if (ns > 32767) return fail(SB_ERR_UNSUPPORTED, "more than 32767 todo nodes in one tree");
+        for (int s = s0; s < s1; ++s) {
+            const int nid = lay.nodes[order[s]].node_id;
+            if (nid <= 0) return fail(SB_ERR_INVALID, "todo node with non-positive id");
+            tables[toff + nid] = (int16_t)(s - s0);
+        }
+        HistLaunch L;
+        L.kind = h->stat_kind;
+        HistArgs& a = L.args;
+        a.cols = h->train.d_col;
+        a.feat_bins = h->d_feat_bins;
+        a.output = h->train.output;
+        a.significance = h->train.significance;
+        a.weights = h->train.weights ? h->train.weights + (int64_t)(tree_id % W) * n : nullptr;  // [treeId % len], :847
+        const int arr = h->cfg.is_gbdt ? 0 : tree_id;
+        if (arr < 0 || arr >= h->train.n_node_arrays) return fail(SB_ERR_INVALID, "todo node tree id out of range");
+        a.node_id = h->train.node_id + (int64_t)arr * n;
+        a.slot_of_node = h->slot_of_node.p + toff;
+        a.slot_table_size = table_size[t];
+        a.n_rows = n;
+        a.n_features = F;
+        a.tile_feats = h->tile_feats.p;
+        a.slot_fmask = h->slot_fmask.p + (size_t)s0 * n_tiles;
+        a.pair_off = h->pair_off.p + (size_t)s0 * F;
+        a.n_tiles = n_tiles;
+        a.gs = std::min(ns, max_gs);
+        a.n_groups = (ns + a.gs - 1) / a.gs;
+        a.n_slots = ns;
+        a.bins_pad = bins_pad;
+        const int64_t tiles_rows = (n + HIST_T_ROWS - 1) / HIST_T_ROWS;
+        int64_t n_chunks = (148 * 3 + (int64_t)n_tiles * a.n_groups - 1) / ((int64_t)n_tiles * a.n_groups);
+        n_chunks = std::max<int64_t>(1, std::min(n_chunks, tiles_rows));
+        int64_t rpc = ((tiles_rows + n_chunks - 1) / n_chunks) * HIST_T_ROWS;
+        rpc = std::min<int64_t>(rpc, MAX_ROWS_PER_FLUSH);
+        n_chunks = (n + rpc - 1) / rpc;
+        a.rows_per_chunk = rpc;
+        a.stats_size = h->stats_size;
+        a.scales = h->d_scales;
+        a.raw_lo = h->raw.p;
+        a.raw_hi = h->raw.p + lay.total;
+        a.error_flag = h->d_error_flag;
+        const int64_t grid = n_chunks * n_tiles * a.n_groups;
+        if (grid > 0x7fffffff) return fail(SB_ERR_UNSUPPORTED, "histogram grid too large");
+        L.grid = (int)grid;
+        L.smem = hist_smem_bytes(a.gs, bins_pad, nw);
+        h->launches.push_back(L);
+        toff += (size_t)table_size[t];
+    }
+    SB_CUDA(cudaMemcpyAsync(h->slot_of_node.p, tables.data(), tables.size() * 2, cudaMemcpyHostToDevice, h->stream));
+    h->h2d_bytes += tables.size() * 2;
+    (void)in;
+    return SB_OK;
+}
+
+int plan_split_tasks(sb_handle* h) {
+    const TodoLayout& lay = h->layout;
+    std::vector<SplitTask> tasks;
+    std::vector<int32_t> begin;
+    h->has_cat_tasks = false;
+    int max_cat_bins = 0;
+    for (size_t n = 0; n < lay.nodes.size(); ++n) {
+        const auto& nd = lay.nodes[n];
+        begin.push_back((int32_t)tasks.size());
+        std::vector<int> cols;
+        for (int f : nd.features) cols.push_back(h->column_num[f]);
+        std::vector<int> rank = hashmap_visit_rank(cols);
+        for (size_t k = 0; k < nd.features.size(); ++k) {
+            const int f = nd.features[k];
+            SplitTask t;
+            t.node = (int32_t)n;
+            t.feature = f;
+            t.offset = nd.offset + nd.feat_off[k];
+            t.n_bins = h->n_bins[f];
+            t.categorical = h->is_cat[f];
+            t.visit_rank = rank[k];
+            t.pad = 0;
+            if (t.categorical) { h->has_cat_tasks = true; max_cat_bins = std::max(max_cat_bins, t.n_bins); }
+            tasks.push_back(t);
+        }
+    }
+    begin.push_back((int32_t)tasks.size());
+    h->n_tasks = (int)tasks.size();
+    SB_CUDA(h->tasks.reserve(tasks.size()));
+    SB_CUDA(h->node_task_begin.reserve(begin.size()));
+    SB_CUDA(h->cand.reserve(tasks.size()));
+    SB_CUDA(h->gain_out.reserve(lay.nodes.size()));
+    if (!tasks.empty())
+        SB_CUDA(cudaMemcpyAsync(h->tasks.p, tasks.data(), tasks.size() * sizeof(SplitTask), cudaMemcpyHostToDevice, h->stream));
+    SB_CUDA(cudaMemcpyAsync(h->node_task_begin.p, begin.data(), begin.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    h->h2d_bytes += tasks.size() * sizeof(SplitTask) + begin.size() * 4;
+    if (h->has_cat_tasks) {
+        SB_CUDA(h->cand_bits.reserve(tasks.size() * SB_MAX_CAT_BYTES));
+        SB_CUDA(h->out_bits.reserve(lay.nodes.size() * SB_MAX_CAT_BYTES));
+        SB_CUDA(h->sort_keys.reserve(tasks.size() * max_cat_bins));
+        SB_CUDA(h->sort_idx.reserve(tasks.size() * max_cat_bins));
+        SB_CUDA(h->sort_tmp.reserve(tasks.size() * max_cat_bins));
+        SB_CUDA(h->sort_flags.reserve(tasks.size() * max_cat_bins));
+    }
+    h->max_bins = max_cat_bins;
+    return SB_OK;
+}
+
+int run_histograms(sb_handle* h) {
+    for (const HistLaunch& L : h->launches) {
+        SB_CUDA(hist_launch(L.kind, L.args, L.grid, L.smem, h->stream));
+        h->launches_count += 1;
+    }
+    return SB_OK;
+}
+
+const sb_tree* find_tree(const sb_iter_in* in, int tree_id) {
+    for (int i = 0; i < in->n_trees; ++i)
+        if (in->trees[i].tree_id == tree_id && in->trees[i].n_nodes > 0) return &in->trees[i];
+    return nullptr;
+}
+
+}  // namespace
+
+extern "C" {
+
+SB_API const char* sb_last_error(void) { return g_last_error.c_str(); }
+SB_API const char* sb_version(void) { return "shifu_b200 0.1 (sm_100a)"; }
+
+SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
+    if (!cfg || !out) return fail(SB_ERR_INVALID, "null argument");
+    *out = nullptr;
+    if (cfg->n_features <= 0 || !cfg->n_bins) return fail(SB_ERR_INVALID, "n_features / n_bins missing");
+    if (cfg->weights_per_row < 1) return fail(SB_ERR_INVALID, "weights_per_row must be >= 1");
+    if (cfg->impurity < SB_IMPURITY_VARIANCE || cfg->impurity > SB_IMPURITY_GINI) return fail(SB_ERR_INVALID, "unknown impurity");
+    if (cfg->loss < SB_LOSS_SQUARED || cfg->loss > SB_LOSS_LOG) return fail(SB_ERR_INVALID, "unknown loss");
+    if (!is_variance(cfg->impurity) && (cfg->num_classes < 2 || cfg->num_classes > 16))
+        return fail(SB_ERR_INVALID, "num_classes must be in [2, 16] for entropy / gini");
+    if (cfg->is_gbdt && !is_variance(cfg->impurity))  // core/validator/ModelInspector.java:898-904
+        return fail(SB_ERR_INVALID, "GBT supports only variance / friedmanmse impurity");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(SB_ERR_CUDA, "no CUDA device: shifu_b200 has no CPU fallback");
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(SB_ERR_INVALID, "device ordinal out of range");
+    SB_CUDA(cudaSetDevice(cfg->device));
+    std::unique_ptr<sb_handle> h(new sb_handle());
+    h->cfg = *cfg;
+    h->n_bins.assign(cfg->n_bins, cfg->n_bins + cfg->n_features);
+    h->is_cat.assign((size_t)cfg->n_features, 0);
+    if (cfg->is_categorical) h->is_cat.assign(cfg->is_categorical, cfg->is_categorical + cfg->n_features);
+    h->column_num.resize((size_t)cfg->n_features);
+    for (int f = 0; f < cfg->n_features; ++f) h->column_num[f] = cfg->column_num ? cfg->column_num[f] : f;
+    size_t nb = 0;
+    for (int f = 0; f < cfg->n_features; ++f) {
+        if (h->n_bins[f] < 1 || h->n_bins[f] > 32768) return fail(SB_ERR_INVALID, "n_bins out of range");
+        if (!h->is_cat[f]) nb += (size_t)h->n_bins[f];
+        // getAllValidFeatures: numeric with > 1 boundary, categorical with > 0 categories
+        if ((!h->is_cat[f] && h->n_bins[f] > 1) || (h->is_cat[f] && h->n_bins[f] - 1 > 0)) h->all_features.push_back(f);
+    }
+    if (cfg->bin_boundary) h->bin_boundary.assign(cfg->bin_boundary, cfg->bin_boundary + nb);
+    h->cfg.n_bins = nullptr; h->cfg.is_categorical = nullptr; h->cfg.column_num = nullptr; h->cfg.bin_boundary = nullptr;
+    h->stats_size = is_variance(cfg->impurity) ? 3 : cfg->num_classes;
+    h->stat_kind = is_variance(cfg->impurity) ? STAT_VARIANCE : STAT_CLASS;
+    SB_CUDA(cudaMalloc(&h->d_feat_bins, sizeof(int32_t) * cfg->n_features));
+    SB_CUDA(cudaMemcpy(h->d_feat_bins, h->n_bins.data(), sizeof(int32_t) * cfg->n_features, cudaMemcpyHostToDevice));
+    SB_CUDA(cudaMalloc(&h->d_acc, sizeof(double) * 4));
+    SB_CUDA(cudaMalloc(&h->d_err_scratch, sizeof(double) * ERR_SCRATCH_DOUBLES));
+    SB_CUDA(cudaMemset(h->d_err_scratch, 0, sizeof(double) * ERR_SCRATCH_DOUBLES));
+    SB_CUDA(cudaMalloc(&h->d_maxbits, 16));
+    SB_CUDA(cudaMalloc(&h->d_scales, 16));
+    SB_CUDA(cudaMalloc(&h->d_inv_scales, 32));
+    SB_CUDA(cudaMalloc(&h->d_error_flag, 4));
+    SB_CUDA(cudaMemset(h->d_error_flag, 0, 4));
+    *out = h.release();
+    return SB_OK;
+}
+
+SB_API void sb_destroy(sb_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->cfg.device);
+    cudaDeviceSynchronize();
+    free_rowset(h->train);
+    free_rowset(h->valid);
+    for (auto& kv : h->trees) free_tree(kv.second);
+    h->raw.release(); h->stats.release(); h->tile_feats.release(); h->slot_fmask.release(); h->pair_off.release();
+    h->slot_of_node.release(); h->tasks.release(); h->node_task_begin.release(); h->cand.release(); h->gain_out.release();
+    h->cand_bits.release(); h->out_bits.release(); h->new_dropout.release(); h->new_weights.release();
+    h->sort_keys.release(); h->sort_idx.release(); h->sort_tmp.release(); h->sort_flags.release();
+    if (h->d_feat_bins) cudaFree(h->d_feat_bins);
+    if (h->d_acc) cudaFree(h->d_acc);
+    if (h->d_err_scratch) cudaFree(h->d_err_scratch);
+    if (h->d_maxbits) cudaFree(h->d_maxbits);
+    if (h->d_scales) cudaFree(h->d_scales);
+    if (h->d_inv_scales) cudaFree(h->d_inv_scales);
+    if (h->d_error_flag) cudaFree(h->d_error_flag);
+    delete h;
+}
+
+SB_API int sb_set_stream(sb_handle* h, void* cuda_stream) {
+    if (!h) return fail(SB_ERR_INVALID, "null handle");
+    h->stream = (cudaStream_t)cuda_stream;
+    return SB_OK;
+}
+
+SB_API int sb_load_rows(sb_handle* h, int32_t is_validation, int64_t n_rows, const void* const* bins, const float* label,
+                        const float* significance, const float* weights) {
+    if (!h || !bins || !label || n_rows < 0) return fail(SB_ERR_INVALID, "null argument");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    RowSet& r = is_validation ? h->valid : h->train;
+    if (r.loaded) return fail(SB_ERR_UNSUPPORTED, "rows of this set were already loaded (one load call per set)");
+    const int F = h->cfg.n_features, W = h->cfg.weights_per_row;
+    for (int f = 0; f < F; ++f)
+        if (h->n_bins[f] > 256) return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins are not supported yet");
+    r.n = n_rows;
+    r.n_features = F;
+    r.owns_inputs = true;
+    const int64_t pitch = ((n_rows + 255) / 256) * 256 + 256;  // tail tile reads stay inside the allocation
+    SB_CUDA(cudaMalloc(&r.owned_bins, (size_t)pitch * F));
+    SB_CUDA(cudaMemsetAsync(r.owned_bins, 0, (size_t)pitch * F, h->stream));
+    r.h_col.resize((size_t)F);
+    for (int f = 0; f < F; ++f) {
+        uint8_t* dst = static_cast<uint8_t*>(r.owned_bins) + (size_t)f * pitch;
+        r.h_col[f] = dst;
+        if (!bins[f]) return fail(SB_ERR_INVALID, "null feature column");
+        if (n_rows > 0) SB_CUDA(cudaMemcpyAsync(dst, bins[f], (size_t)n_rows, cudaMemcpyHostToDevice, h->stream));
+    }
+    const size_t nf = (size_t)std::max<int64_t>(n_rows, 1);
+    SB_CUDA(cudaMalloc(&r.label, nf * 4));
+    SB_CUDA(cudaMalloc(&r.significance, nf * 4));
+    SB_CUDA(cudaMemcpyAsync(r.label, label, (size_t)n_rows * 4, cudaMemcpyHostToDevice, h->stream));
+    if (significance) SB_CUDA(cudaMemcpyAsync(r.significance, significance, (size_t)n_rows * 4, cudaMemcpyHostToDevice, h->stream));
+    else SB_CUDA(launch_fill_f32(r.significance, n_rows, 1.0f, h->stream));
+    if (!is_validation) {
+        SB_CUDA(cudaMalloc(&r.weights, nf * 4 * W));
+        if (weights) SB_CUDA(cudaMemcpyAsync(r.weights, weights, (size_t)n_rows * 4 * W, cudaMemcpyHostToDevice, h->stream));
+        else SB_CUDA(launch_fill_f32(r.weights, n_rows * W, 1.0f, h->stream));
+    }
+    h->h2d_bytes += n_rows * (F + 8 + (weights ? 4 * W : 0));
+    return finish_load(h, r);
+}
+
+SB_API int sb_load_rows_device(sb_handle* h, int32_t is_validation, int64_t n_rows, const void* const* bins, float* label,
+                               float* significance, float* weights) {
+    if (!h || !bins || !label || !significance || n_rows < 0) return fail(SB_ERR_INVALID, "null argument");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    RowSet& r = is_validation ? h->valid : h->train;
+    if (r.loaded) return fail(SB_ERR_UNSUPPORTED, "rows of this set were already loaded (one load call per set)");
+    const int F = h->cfg.n_features;
+    r.n = n_rows;
+    r.n_features = F;
+    r.owns_inputs = false;
+    r.h_col.resize((size_t)F);
+    for (int f = 0; f < F; ++f) {
+        if (h->n_bins[f] > 256) return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins are not supported yet");
+        if (!bins[f] || ((uintptr_t)bins[f] & 15)) return fail(SB_ERR_INVALID, "device feature column must be non-null and 16-byte aligned");
+        r.h_col[f] = bins[f];
+    }
+    r.label = label;
+    r.significance = significance;
+    r.weights = is_validation ? nullptr : weights;
+    return finish_load(h, r);
+}
+
+SB_API int sb_load_synthetic(sb_handle* h, int32_t is_validation, int64_t row0, int64_t n_rows, uint64_t seed,
+                             int32_t label_kind, int32_t weighted) {
+    if (!h || n_rows < 0) return fail(SB_ERR_INVALID, "null argument");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    RowSet& r = is_validation ? h->valid : h->train;
+    if (r.loaded) return fail(SB_ERR_UNSUPPORTED, "rows of this set were already loaded (one load call per set)");
+    const int F = h->cfg.n_features, W = h->cfg.weights_per_row;
+    for (int f = 0; f < F; ++f)
+        if (h->n_bins[f] > 256) return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins are not supported yet");
+    r.n = n_rows;
+    r.n_features = F;
+    r.owns_inputs = true;
+    const int64_t pitch = ((n_rows + 255) / 256) * 256 + 256;
+    SB_CUDA(cudaMalloc(&r.owned_bins, (size_t)pitch * F));
+    r.h_col.resize((size_t)F);
+    for (int f = 0; f < F; ++f) r.h_col[f] = static_cast<uint8_t*>(r.owned_bins) + (size_t)f * pitch;
+    const size_t nf = (size_t)std::max<int64_t>(n_rows, 1);
+    SB_CUDA(cudaMalloc(&r.label, nf * 4));
+    SB_CUDA(cudaMalloc(&r.significance, nf * 4));
+    if (!is_validation) {
+        SB_CUDA(cudaMalloc(&r.weights, nf * 4 * W));
+        SB_CUDA(launch_fill_f32(r.weights, n_rows * W, 1.0f, h->stream));
+    }
+    SB_CUDA(launch_synthetic(static_cast<uint8_t*>(r.owned_bins), pitch, F, h->d_feat_bins, r.label, r.significance, row0,
+                             n_rows, seed, label_kind, weighted, h->stream));
+    h->launches_count += 3;
+    return finish_load(h, r);
+}
+
+SB_API int sb_read_bins(sb_handle* h, int32_t is_validation, int32_t feature, int64_t row0, int64_t n_rows, void* out) {
+    if (!h || !out) return fail(SB_ERR_INVALID, "null argument");
+    RowSet& r = is_validation ? h->valid : h->train;
+    if (!r.loaded || feature < 0 || feature >= r.n_features || row0 < 0 || row0 + n_rows > r.n)
+        return fail(SB_ERR_INVALID, "range outside the loaded rows");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    SB_CUDA(cudaMemcpyAsync(out, static_cast<const uint8_t*>(r.h_col[feature]) + row0, (size_t)n_rows, cudaMemcpyDeviceToHost, h->stream));
+    SB_CUDA(cudaStreamSynchronize(h->stream));
+    h->d2h_bytes += n_rows;
+    return SB_OK;
+}
+
+SB_API int sb_read_labels(sb_handle* h, int32_t is_validation, int64_t row0, int64_t n_rows, float* label, float* significance) {
+    if (!h) return fail(SB_ERR_INVALID, "null argument");
+    RowSet& r = is_validation ? h->valid : h->train;
+    if (!r.loaded || row0 < 0 || row0 + n_rows > r.n) return fail(SB_ERR_INVALID, "range outside the loaded rows");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    if (label) SB_CUDA(cudaMemcpyAsync(label, r.label + row0, (size_t)n_rows * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (significance) SB_CUDA(cudaMemcpyAsync(significance, r.significance + row0, (size_t)n_rows * 4, cudaMemcpyDeviceToHost, h->stream));
+    SB_CUDA(cudaStreamSynchronize(h->stream));
+    return SB_OK;
+}
+
+SB_API int sb_read_rows(sb_handle* h, int32_t is_validation, int32_t tree_id, int32_t w_index, float* predict, float* output,
+                        int32_t* node_id, float* weight) {
+    if (!h) return fail(SB_ERR_INVALID, "null argument");
+    RowSet& r = is_validation ? h->valid : h->train;
+    if (!r.loaded) return fail(SB_ERR_STATE, "rows not loaded");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    const size_t nb = (size_t)r.n * 4;
+    if (predict) SB_CUDA(cudaMemcpyAsync(predict, r.predict, nb, cudaMemcpyDeviceToHost, h->stream));
+    if (output) SB_CUDA(cudaMemcpyAsync(output, r.output, nb, cudaMemcpyDeviceToHost, h->stream));
+    if (node_id) {
+        const int arr = h->cfg.is_gbdt ? 0 : tree_id;
+        if (arr < 0 || arr >= r.n_node_arrays) return fail(SB_ERR_INVALID, "tree id out of range");
+        SB_CUDA(cudaMemcpyAsync(node_id, r.node_id + (int64_t)arr * r.n, nb, cudaMemcpyDeviceToHost, h->stream));
+    }
+    if (weight) {
+        if (!r.weights || w_index < 0 || w_index >= h->cfg.weights_per_row) return fail(SB_ERR_INVALID, "weight index out of range");
+        SB_CUDA(cudaMemcpyAsync(weight, r.weights + (int64_t)w_index * r.n, nb, cudaMemcpyDeviceToHost, h->stream));
+    }
+    SB_CUDA(cudaStreamSynchronize(h->stream));
+    return SB_OK;
+}
+
+SB_API int64_t sb_stats_len(sb_handle* h, const sb_iter_in* in) {
+    if (!h || !in) return fail(SB_ERR_INVALID, "null argument");
+    TodoLayout lay;
+    int rc = build_layout(h, in, lay);
+    if (rc != SB_OK) return rc;
+    return lay.total;
+}
+
+SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
+    if (!h || !in) return fail(SB_ERR_INVALID, "null argument");
+    if (!h->train.loaded) return fail(SB_ERR_STATE, "sb_compute before sb_load_rows");
+    if (in->continuous_running_start) return fail(SB_ERR_UNSUPPORTED, "continuous training is handled on the Java side");
+    if (in->n_trees < 1 || !in->trees) return fail(SB_ERR_INVALID, "no trees");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    h->begun = false;
+    h->stats_ready = false;
+    int rc = build_layout(h, in, h->layout);
+    if (rc != SB_OK) return rc;
+    const int64_t total = h->layout.total;
+    SB_CUDA(h->raw.reserve((size_t)std::max<int64_t>(2 * total, 1)));
+    SB_CUDA(h->stats.reserve((size_t)std::max<int64_t>(total, 1)));
+    SB_CUDA(cudaMemsetAsync(h->raw.p, 0, (size_t)(2 * total) * 8, h->stream));
+    SB_CUDA(cudaMemsetAsync(h->d_acc, 0, 32, h->stream));
+    SB_CUDA(cudaMemsetAsync(h->d_maxbits, 0, 16, h->stream));
+    SB_CUDA(cudaMemsetAsync(h->d_error_flag, 0, 4, h->stream));
+    RowSet& tr = h->train;
+    RowSet& va = h->valid;
+    const int loss = h->cfg.loss;
+
+    if (h->cfg.is_gbdt) {
+        const int curr = in->n_trees - 1;  // currTreeIndex (dt/DTWorker.java:620)
+        const sb_tree& cur_tree = in->trees[curr];
+        if (cur_tree.n_nodes < 1) return fail(SB_ERR_INVALID, "current tree has no nodes");
+        if (in->switch_to_next_tree) {
+            if (curr >= 1) {
+                const sb_tree& prev = in->trees[curr - 1];
+                DeviceTree& dprev = h->trees[prev.tree_id];
+                rc = upload_tree(h, prev, dprev);
+                if (rc != SB_OK) return rc;
+                if (h->tracked_tree != prev.tree_id) {  // first time we see it: walk from the root
+                    SB_CUDA(launch_fill_i32(tr.node_id, tr.n, SB_ROOT_INDEX, h->stream));
+                    if (va.loaded) SB_CUDA(launch_fill_i32(va.node_id, va.n, SB_ROOT_INDEX, h->stream));
+                }
+                const TreeView pv = view_of(dprev);
+                SB_CUDA(launch_route(tr.d_col, tr.n, tr.node_id, pv, h->d_error_flag, h->stream));
+                const uint8_t* d_drop = nullptr;
+                if (in->dropout && !in->is_first_tree) {
+                    SB_CUDA(h->new_dropout.reserve((size_t)tr.n));
+                    SB_CUDA(cudaMemcpyAsync(h->new_dropout.p, in->dropout, (size_t)tr.n, cudaMemcpyHostToDevice, h->stream));
+                    h->h2d_bytes += tr.n;
+                    d_drop = h->new_dropout.p;
+                }
+                SB_CUDA(launch_gbt_update(tr.n, tr.node_id, pv, in->is_first_tree, h->cfg.learning_rate, loss, tr.label,
+                                          tr.predict, tr.output, d_drop, h->stream));
+                h->launches_count += 2;
+                if (va.loaded) {
+                    SB_CUDA(launch_route(va.d_col, va.n, va.node_id, pv, h->d_error_flag, h->stream));
+                    SB_CUDA(launch_gbt_update(va.n, va.node_id, pv, in->is_first_tree, h->cfg.learning_rate, loss, va.label,
+                                              va.predict, va.output, nullptr, h->stream));
+                    h->launches_count += 2;
+                }
+                if (in->new_weights) {  // redraw of subsampleWeights[currTreeIndex % len] (dt/DTWorker.java:643-668), injected
+                    const int W = h->cfg.weights_per_row;
+                    SB_CUDA(cudaMemcpyAsync(tr.weights + (int64_t)(curr % W) * tr.n, in->new_weights, (size_t)tr.n * 4,
+                                            cudaMemcpyHostToDevice, h->stream));
+                    h->h2d_bytes += tr.n * 4;
+                }
+            }
+            SB_CUDA(launch_fill_i32(tr.node_id, tr.n, SB_ROOT_INDEX, h->stream));
+            if (va.loaded) SB_CUDA(launch_fill_i32(va.node_id, va.n, SB_ROOT_INDEX, h->stream));
+            h->launches_count += 1 + (va.loaded ? 1 : 0);
+        } else if (h->tracked_tree != cur_tree.tree_id) {
+            SB_CUDA(launch_fill_i32(tr.node_id, tr.n, SB_ROOT_INDEX, h->stream));
+            if (va.loaded) SB_CUDA(launch_fill_i32(va.node_id, va.n, SB_ROOT_INDEX, h->stream));
+            h->launches_count += 1 + (va.loaded ? 1 : 0);
+        }
+        DeviceTree& dcur = h->trees[cur_tree.tree_id];
+        rc = upload_tree(h, cur_tree, dcur);
+        if (rc != SB_OK) return rc;
+        h->tracked_tree = cur_tree.tree_id;
+        // keep the device copies of the current and the previous tree only
+        const int keep_prev = curr >= 1 ? in->trees[curr - 1].tree_id : cur_tree.tree_id;
+        for (auto it = h->trees.begin(); it != h->trees.end();) {
+            if (it->first != cur_tree.tree_id && it->first != keep_prev) { free_tree(it->second); it = h->trees.erase(it); }
+            else ++it;
+        }
+        const TreeView cv = view_of(dcur);
+        SB_CUDA(launch_route(tr.d_col, tr.n, tr.node_id, cv, h->d_error_flag, h->stream));
+        h->launches_count += 1;
+        const bool from_tree = in->is_first_tree && !in->switch_to_next_tree;  // dt/DTWorker.java:672-683
+        if (va.loaded && from_tree) {
+            SB_CUDA(launch_route(va.d_col, va.n, va.node_id, cv, h->d_error_flag, h->stream));
+            h->launches_count += 1;
+        }
+        ErrArgs e{};
+        e.n = tr.n; e.label = tr.label; e.predict = tr.predict; e.significance = tr.significance; e.weights = nullptr;
+        e.node_id = tr.node_id; e.tree = cv; e.from_tree = from_tree ? 1 : 0; e.loss = loss; e.is_validation = 0; e.rf_oob = 0;
+        SB_CUDA(launch_errors(e, h->d_err_scratch, h->d_acc, h->stream));
+        h->launches_count += 1;
+        if (va.loaded) {
+            e.n = va.n; e.label = va.label; e.predict = va.predict; e.significance = va.significance; e.node_id = va.node_id;
+            e.is_validation = 1;
+            SB_CUDA(launch_errors(e, h->d_err_scratch, h->d_acc, h->stream));
+            h->launches_count += 1;
+        }
+    } else {
+        // RF (dt/DTWorker.java:583-605, 691-705): every real tree is walked for the error sums
+        for (int t = 0; t < in->n_trees; ++t) {
+            const sb_tree& tree = in->trees[t];
+            if (tree.n_nodes < 1) continue;  // INVALID_INDEX placeholder
+            if (tree.tree_id < 0 || tree.tree_id >= tr.n_node_arrays) return fail(SB_ERR_INVALID, "tree id out of range");
+            if (tree.tree_id >= h->cfg.weights_per_row) return fail(SB_ERR_INVALID, "RF needs one weight per tree");
+            DeviceTree& d = h->trees[tree.tree_id];
+            rc = upload_tree(h, tree, d);
+            if (rc != SB_OK) return rc;
+            const TreeView v = view_of(d);
+            int32_t* nid = tr.node_id + (int64_t)tree.tree_id * tr.n;
+            SB_CUDA(launch_route(tr.d_col, tr.n, nid, v, h->d_error_flag, h->stream));
+            ErrArgs e{};
+            e.n = tr.n; e.label = tr.label; e.predict = tr.predict; e.significance = tr.significance;
+            e.weights = tr.weights + (int64_t)tree.tree_id * tr.n;  // [treeId], no modulo (:592)
+            e.node_id = nid; e.tree = v; e.from_tree = 1; e.loss = loss; e.is_validation = 0; e.rf_oob = 1;
+            SB_CUDA(launch_errors(e, h->d_err_scratch, h->d_acc, h->stream));
+            h->launches_count += 2;
+            if (va.loaded) {
+                int32_t* vnid = va.node_id + (int64_t)tree.tree_id * va.n;
+                SB_CUDA(launch_route(va.d_col, va.n, vnid, v, h->d_error_flag, h->stream));
+                e.n = va.n; e.label = va.label; e.predict = va.predict; e.significance = va.significance; e.weights = nullptr;
+                e.node_id = vnid; e.is_validation = 1; e.rf_oob = 0;
+                SB_CUDA(launch_errors(e, h->d_err_scratch, h->d_acc, h->stream));
+                h->launches_count += 2;
+            }
+        }
+    }
+
+    // fixed-point scales from the rows that can contribute this pass
+    {
+        const int W = h->cfg.weights_per_row;
+        std::vector<int> wcols;
+        for (const auto& nd : h->layout.nodes) {
+            const int c = nd.tree_id % W;
+            if (std::find(wcols.begin(), wcols.end(), c) == wcols.end()) wcols.push_back(c);
+        }
+        for (int c : wcols) {
+            SB_CUDA(launch_absmax(tr.n, tr.output, tr.significance, tr.weights ? tr.weights + (int64_t)c * tr.n : nullptr,
+                                  h->d_maxbits, h->stream));
+            h->launches_count += 1;
+        }
+    }
+    rc = plan_histograms(h, in);
+    if (rc != SB_OK) return rc;
+    rc = plan_split_tasks(h);
+    if (rc != SB_OK) return rc;
+    h->begun = true;
+    return SB_OK;
+}
+
+SB_API int sb_scale_buffer(sb_handle* h, void** dev_ptr, int64_t* bytes) {
+    if (!h || !dev_ptr) return fail(SB_ERR_INVALID, "null argument");
+    *dev_ptr = h->d_maxbits;
+    if (bytes) *bytes = 12;
+    return SB_OK;
+}
+
+SB_API int sb_compute_stats(sb_handle* h) {
+    if (!h) return fail(SB_ERR_INVALID, "null argument");
+    if (!h->begun) return fail(SB_ERR_STATE, "sb_compute_stats before sb_compute_begin");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    SB_CUDA(launch_make_scales(h->d_maxbits, h->stat_kind, h->d_scales, h->d_inv_scales, h->stream));
+    h->launches_count += 1;
+    return run_histograms(h);
+}
+
+SB_API int sb_raw_buffer(sb_handle* h, void** dev_ptr, int64_t* bytes) {
+    if (!h || !dev_ptr) return fail(SB_ERR_INVALID, "null argument");
+    *dev_ptr = h->raw.p;
+    if (bytes) *bytes = 2 * h->layout.total * 8;
+    return SB_OK;
+}
+
+SB_API int sb_acc_buffer(sb_handle* h, void** dev_ptr, int64_t* bytes) {
+    if (!h || !dev_ptr) return fail(SB_ERR_INVALID, "null argument");
+    *dev_ptr = h->d_acc;
+    if (bytes) *bytes = 32;
+    return SB_OK;
+}
+
+SB_API int sb_compute_finish(sb_handle* h, sb_iter_out* out) {
+    if (!h || !out) return fail(SB_ERR_INVALID, "null argument");
+    if (!h->begun) return fail(SB_ERR_STATE, "sb_compute_finish before sb_compute_begin");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    const int64_t total = h->layout.total;
+    if (out->stats && out->stats_len < total) return fail(SB_ERR_INVALID, "stats buffer too small");
+    SB_CUDA(launch_finalize(h->raw.p, h->raw.p + total, total, h->stats_size, h->stat_kind, h->d_inv_scales, h->stats.p, h->stream));
+    h->launches_count += 1;
+    double acc[4];
+    uint32_t flags[2] = {0, 0};
+    uint32_t maxbits[4];
+    SB_CUDA(cudaMemcpyAsync(acc, h->d_acc, 32, cudaMemcpyDeviceToHost, h->stream));
+    SB_CUDA(cudaMemcpyAsync(flags, h->d_error_flag, 4, cudaMemcpyDeviceToHost, h->stream));
+    SB_CUDA(cudaMemcpyAsync(maxbits, h->d_maxbits, 12, cudaMemcpyDeviceToHost, h->stream));
+    if (out->stats && total > 0) {
+        SB_CUDA(cudaMemcpyAsync(out->stats, h->stats.p, (size_t)total * 8, cudaMemcpyDeviceToHost, h->stream));
+        h->d2h_bytes += total * 8;
+    }
+    SB_CUDA(cudaStreamSynchronize(h->stream));
+    h->d2h_bytes += 48;
+    if (flags[0] & 1u) return fail(SB_ERR_RANGE, "class index (int)(label + 1e-6f) outside [0, num_classes)");
+    if (flags[0] & 2u) return fail(SB_ERR_RANGE, "a bin index is outside [0, n_bins) of its feature");
+    if (flags[0] & 4u) return fail(SB_ERR_STATE, "NextNode is null: a split node is missing a child (dt/DTWorker.java:1089-1094)");
+    for (int k = 0; k < 3; ++k)
+        if ((maxbits[k] & 0x7f800000u) == 0x7f800000u) return fail(SB_ERR_RANGE, "non-finite per-row contribution (label, significance or weight)");
+    out->train_count = acc[0];
+    out->validation_count = acc[1];
+    out->train_error = acc[2];
+    out->validation_error = acc[3];
+    h->stats_ready = true;
+    return SB_OK;
+}
+
+SB_API int sb_compute(sb_handle* h, const sb_iter_in* in, sb_iter_out* out) {
+    int rc = sb_compute_begin(h, in);
+    if (rc != SB_OK) return rc;
+    rc = sb_compute_stats(h);
+    if (rc != SB_OK) return rc;
+    return sb_compute_finish(h, out);
+}
+
+SB_API int sb_best_splits(sb_handle* h, sb_gain* gains, uint8_t* cat_bits) {
+    if (!h || !gains) return fail(SB_ERR_INVALID, "null argument");
+    if (!h->stats_ready) return fail(SB_ERR_STATE, "sb_best_splits before sb_compute_finish");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    const int n_nodes = (int)h->layout.nodes.size();
+    if (n_nodes == 0) return SB_OK;
+    SplitScratch sc;
+    sc.keys = h->sort_keys.p; sc.idx = h->sort_idx.p; sc.tmp = h->sort_tmp.p; sc.flags = h->sort_flags.p; sc.max_bins = h->max_bins;
+    SB_CUDA(launch_best_splits(h->stats.p, h->tasks.p, h->n_tasks, n_nodes, h->cfg.impurity, h->stats_size,
+                               h->cfg.min_instances_per_node, h->cfg.min_info_gain, h->cand.p,
+                               h->has_cat_tasks ? h->cand_bits.p : nullptr, h->gain_out.p,
+                               h->has_cat_tasks ? h->out_bits.p : nullptr, h->node_task_begin.p, sc, h->stream));
+    h->launches_count += 2;
+    SB_CUDA(cudaMemcpyAsync(gains, h->gain_out.p, sizeof(sb_gain) * n_nodes, cudaMemcpyDeviceToHost, h->stream));
+    h->d2h_bytes += sizeof(sb_gain) * n_nodes;
+    if (cat_bits && h->has_cat_tasks) {
+        SB_CUDA(cudaMemcpyAsync(cat_bits, h->out_bits.p, (size_t)n_nodes * SB_MAX_CAT_BYTES, cudaMemcpyDeviceToHost, h->stream));
+        h->d2h_bytes += (int64_t)n_nodes * SB_MAX_CAT_BYTES;
+    }
+    SB_CUDA(cudaStreamSynchronize(h->stream));
+    return SB_OK;
+}
+
+SB_API int sb_time_stats_pass(sb_handle* h, int32_t n_repeat, float* ms_hist_kernel, float* ms_total) {
+    if (!h || n_repeat < 1) return fail(SB_ERR_INVALID, "bad argument");
+    if (!h->begun) return fail(SB_ERR_STATE, "sb_time_stats_pass before sb_compute_begin");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    cudaEvent_t e0, e1;
+    SB_CUDA(cudaEventCreate(&e0));
+    SB_CUDA(cudaEventCreate(&e1));
+    const int64_t total = h->layout.total;
+    double sum_ms = 0;
+    for (int r = 0; r < n_repeat; ++r) {
+        SB_CUDA(cudaMemsetAsync(h->raw.p, 0, (size_t)(2 * total) * 8, h->stream));
+        SB_CUDA(cudaEventRecord(e0, h->stream));
+        int rc = run_histograms(h);
+        if (rc != SB_OK) return rc;
+        SB_CUDA(cudaEventRecord(e1, h->stream));
+        SB_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        SB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        sum_ms += ms;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (ms_hist_kernel) *ms_hist_kernel = (float)(sum_ms / n_repeat);
+    if (ms_total) *ms_total = (float)(sum_ms / n_repeat);
+    return SB_OK;
+}
+
+SB_API int sb_counters(sb_handle* h, int64_t* launches, int64_t* h2d_bytes, int64_t* d2h_bytes) {
+    if (!h) return fail(SB_ERR_INVALID, "null handle");
+    if (launches) *launches = h->launches_count;
+    if (h2d_bytes) *h2d_bytes = h->h2d_bytes;
+    if (d2h_bytes) *d2h_bytes = h->d2h_bytes;
+    return SB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,74 @@
+// common.cuh -- shared declarations of the shifu_b200 device library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/shifu_b200.h"
+
+namespace sb {
+
+void set_error(const std::string& msg);
+int fail(int code, const std::string& msg);
+
+#define SB_CUDA(expr)                                                                                   \
+    do {                                                                                                \
+        cudaError_t _e = (expr);                                                                        \
+        if (_e != cudaSuccess)                                                                          \
+            return ::sb::fail(SB_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e) + " (" +  \
+                                               __FILE__ + ":" + std::to_string(__LINE__) + ")");        \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// Fixed-point accumulation (DESIGN.md "Why integer accumulators").
+// A per-record fp32 contribution v is turned into q = rint(v * 2^e) with |q| < 2^QBITS and summed in
+// 64-bit two's complement (shared memory, per block), then in a (lo, hi) pair of int64 words (global,
+// across blocks and GPUs).  e is chosen per statistic from max|v| over the rows of the pass.
+constexpr int QBITS = 39;                   // |q| < 2^39
+constexpr int64_t MAX_ROWS_PER_FLUSH = 1 << 22;  // 2^22 * 2^39 < 2^63
+
+enum StatKind { STAT_VARIANCE = 0, STAT_CLASS = 1 };
+
+// One set of rows (training or validation) resident in HBM, column-major.
+struct RowSet {
+    int64_t n = 0;
+    int n_features = 0;
+    std::vector<const void*> h_col;  // per feature slot device pointer to n bin indices (uint8 or uint16)
+    const void** d_col = nullptr;    // the same table on the device
+    float* label = nullptr;
+    float* significance = nullptr;
+    float* output = nullptr;   // Data.output
+    float* predict = nullptr;  // Data.predict
+    float* weights = nullptr;  // [weights_per_row][n]
+    int32_t* node_id = nullptr;  // [n_node_arrays][n] current heap id per tracked tree
+    int n_node_arrays = 0;
+    bool owns_inputs = false;
+    void* owned_bins = nullptr;
+    bool loaded = false;
+};
+
+// A flattened tree on the device, indexed by heap id.
+struct DeviceTree {
+    int capacity = 0;        // ids [0, capacity)
+    int32_t* feat = nullptr; // split feature slot if the node routes further (has split AND children), else -1
+    int32_t* mask_off = nullptr;
+    double* predict = nullptr;
+    uint8_t* has_predict = nullptr;
+    uint8_t* masks = nullptr;
+    int mask_capacity = 0;
+};
+
+struct TodoLayout {  // host description of the statistics buffer of one iteration
+    struct Node {
+        int key, tree_id, node_id;
+        std::vector<int> features;
+        std::vector<int64_t> feat_off;  // offset (doubles) of each feature block inside the node block
+        int64_t offset;                 // offset (doubles) of the node block
+    };
+    std::vector<Node> nodes;
+    int64_t total = 0;  // doubles
+};
+
+}  // namespace sb

@@ -1,0 +1,113 @@
+// kernels.cuh -- launch wrappers of the device kernels (definitions in hist.cu, rows.cu, split.cu).
+#pragma once
+#include "common.cuh"
+
+namespace sb {
+
+constexpr int HIST_T_ROWS = 128;
+constexpr int HIST_STAGES = 3;
+constexpr int HIST_THREADS = 512;
+
+struct HistArgs {
+    const void* const* cols;     // [F] device column pointers (uint8 bins)
+    const int32_t* feat_bins;    // [F] stats bins per feature slot
+    const float* output;         // Data.output (the `label` argument of featureUpdate, dt/DTWorker.java:851)
+    const float* significance;
+    const float* weights;        // subsampleWeights[treeId % len] as one column, or nullptr (all 1f)
+    const int32_t* node_id;      // current heap id per row in the tree being accumulated
+    const int16_t* slot_of_node; // heap id -> todo slot (or -1)
+    int slot_table_size;
+    int64_t n_rows;
+    int n_features;
+    const int32_t* tile_feats;   // [n_tiles][32] feature slots, -1 padded
+    const uint32_t* slot_fmask;  // [n_slots][n_tiles] bit l: tile feature l is in the slot's feature list
+    const int64_t* pair_off;     // [n_slots][F] offset (in statistics) of the (slot, feature) block, -1 if absent
+    int n_tiles, n_groups, gs, n_slots, bins_pad;
+    int64_t rows_per_chunk;
+    int stats_size;              // 3 (variance) or numClasses
+    const float* scales;         // [3] 2^e per statistic (count, sum, sum of squares)
+    int64_t* raw_lo;             // global accumulators, one (lo, hi) pair per statistic
+    int64_t* raw_hi;
+    uint32_t* error_flag;        // bit0: class index out of range, bit1: bin index out of range
+};
+
+size_t hist_smem_bytes(int gs, int bins_pad, int nw);
+int hist_max_slots_per_block(int bins_pad, int nw);
+cudaError_t hist_launch(int kind, const HistArgs& a, int grid, size_t smem, cudaStream_t stream);
+
+// ---- rows.cu
+struct TreeView {  // DeviceTree as kernels see it
+    const int32_t* feat;
+    const int32_t* mask_off;
+    const double* predict;
+    const uint8_t* has_predict;
+    const uint8_t* masks;
+    int capacity;
+};
+
+cudaError_t launch_fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t s);
+cudaError_t launch_fill_f32(float* p, int64_t n, float v, cudaStream_t s);
+cudaError_t launch_copy_f32(float* dst, const float* src, int64_t n, cudaStream_t s);
+// predictNodeIndex (dt/DTWorker.java:1036-1096) continued from each row's current node id.
+cudaError_t launch_route(const void* const* cols, int64_t n, int32_t* node_id, TreeView t, uint32_t* error_flag,
+                         cudaStream_t s);
+// GBT tree switch (dt/DTWorker.java:620-669, 721-735): predict / output update from the finished tree's leaves.
+cudaError_t launch_gbt_update(int64_t n, const int32_t* node_id, TreeView prev, int is_first_tree, double learning_rate,
+                              int loss, const float* label, float* predict, float* output, const uint8_t* dropout,
+                              cudaStream_t s);
+// Error sums (dt/DTWorker.java:672-683, 737-748 GBT; 583-605, 691-705 RF).  acc: 4 doubles
+// (train_count, validation_count, train_error, validation_error), accumulated via per-block partials in `scratch`.
+struct ErrArgs {
+    int64_t n;
+    const float* label;
+    const float* predict;      // Data.predict (used when from_tree == 0)
+    const float* significance;
+    const float* weights;      // RF training rows: subsampleWeights[treeId] column; nullptr otherwise
+    const int32_t* node_id;    // used when from_tree == 1
+    TreeView tree;
+    int from_tree;             // 1: error of the current node's predict (skipped when the node has none)
+    int loss;
+    int is_validation;         // validation rows: everything goes to (validation_count, validation_error)
+    int rf_oob;                // RF training rows: weight == 0 -> out-of-bag "validation" sums
+};
+constexpr int ERR_BLOCKS = 592;  // 4 per SM
+constexpr int ERR_SCRATCH_DOUBLES = ERR_BLOCKS * 4 + 1;  // per-block partials + the finish ticket (zeroed once at allocation)
+cudaError_t launch_errors(const ErrArgs& a, double* scratch /*[ERR_SCRATCH_DOUBLES]*/, double* acc /*[4], += */, cudaStream_t s);
+// max |sig*w|, |y*sig*w|, |y*y*sig*w| over rows (as fp32 bit patterns, atomicMax) -> out[3]
+cudaError_t launch_absmax(int64_t n, const float* output, const float* significance, const float* weights,
+                          uint32_t* out, cudaStream_t s);
+// out[3] (bit patterns of maxima) -> scales[3] = 2^e, inv_scales[3] = 2^-e (doubles)
+cudaError_t launch_make_scales(const uint32_t* maxbits, int kind, float* scales, double* inv_scales, cudaStream_t s);
+cudaError_t launch_synthetic(uint8_t* bins, int64_t pitch, int n_features, const int32_t* feat_bins, float* label,
+                             float* significance, int64_t row0, int64_t n, uint64_t seed, int label_kind, int weighted,
+                             cudaStream_t s);
+cudaError_t launch_check_bins(const void* const* cols, const int32_t* feat_bins, int n_features, int64_t n,
+                              uint32_t* error_flag, cudaStream_t s);
+
+// ---- split.cu
+// raw (lo, hi) integer accumulators -> the reference's double statistics (one rounding each).
+cudaError_t launch_finalize(const int64_t* raw_lo, const int64_t* raw_hi, int64_t total, int stats_size, int kind,
+                            const double* inv_scales, double* stats, cudaStream_t s);
+struct SplitTask {       // one (todo node, feature) pair
+    int32_t node;        // todo index
+    int32_t feature;     // feature slot
+    int64_t offset;      // offset of the feature block in stats
+    int32_t n_bins;
+    int32_t categorical;
+    int32_t visit_rank;  // position in the reference's HashMap iteration order (dt/DTMaster.java:324)
+    int32_t pad;
+};
+struct SplitScratch {    // categorical features only: per task, max_bins entries each
+    double* keys = nullptr;
+    int* idx = nullptr;
+    int* tmp = nullptr;
+    uint8_t* flags = nullptr;
+    int max_bins = 0;
+};
+cudaError_t launch_best_splits(const double* stats, const SplitTask* tasks, int n_tasks, int n_nodes, int impurity,
+                               int stats_size, int min_instances, double min_info_gain, sb_gain* cand /*[n_tasks]*/,
+                               uint8_t* cand_bits /*[n_tasks*SB_MAX_CAT_BYTES] or null*/, sb_gain* out /*[n_nodes]*/,
+                               uint8_t* out_bits, const int32_t* node_task_begin /*[n_nodes+1]*/,
+                               const SplitScratch& sc, cudaStream_t s);
+
+}  // namespace sb

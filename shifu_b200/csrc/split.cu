@@ -1,0 +1,319 @@
+// split.cu -- (1) integer accumulators -> the reference's fp64 statistics; (2) on-device best split.
+//
+// (2) replaces the per-node body of DTMaster.doCompute (dt/DTMaster.java:316-340): Impurity.computeImpurity per
+// feature (dt/Impurity.java:120-211 Variance, :269-360 FriedmanMSE, :378-477 Entropy, :563-661 Gini) and
+// GainInfo.getGainInfoByMaxGain (dt/GainInfo.java:200-214).  One thread scans one (node, feature) block in the
+// reference's own order (prefix sums bin by bin, strict '>' from Double.MIN_VALUE, first maximum wins), so given
+// the same statistics it produces the same doubles as the Java code.  Built with -fmad=false.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace sb {
+
+namespace {
+
+// value = hi * 2^32 + lo as a 128-bit integer, converted to double with ONE rounding (nearest-even).
+__device__ __forceinline__ double int96_to_double(long long lo, long long hi) {
+    __int128 v = ((__int128)hi << 32) + (__int128)lo;
+    if (v == 0) return 0.0;
+    const bool neg = v < 0;
+    unsigned __int128 m = neg ? (unsigned __int128)(-v) : (unsigned __int128)v;
+    const unsigned long long top = (unsigned long long)(m >> 64);
+    int shift = 0;
+    unsigned long long w;
+    if (top != 0) {
+        shift = 64 - __clzll((long long)top);  // bits above 64
+        const unsigned long long lost = (unsigned long long)(m & (((unsigned __int128)1 << shift) - 1));
+        w = (unsigned long long)(m >> shift) | (lost != 0 ? 1ULL : 0ULL);  // sticky bit keeps the rounding exact
+    } else {
+        w = (unsigned long long)m;
+    }
+    double d = __ull2double_rn(w);
+    if (shift) d = ldexp(d, shift);
+    return neg ? -d : d;
+}
+
+__global__ void finalize_stats_kernel(const int64_t* __restrict__ raw_lo, const int64_t* __restrict__ raw_hi,
+                                      int64_t total, int stats_size, int kind, const double* __restrict__ inv_scales,
+                                      double* __restrict__ stats) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int st = (kind == STAT_VARIANCE) ? (int)(i % 3) : 0;
+        stats[i] = int96_to_double(raw_lo[i], raw_hi[i]) * inv_scales[st];
+    }
+    (void)stats_size;
+}
+
+constexpr double JAVA_DOUBLE_MIN_VALUE = 4.9406564584124654e-324;
+
+// Double.compareTo ordering: numeric, -0.0 < +0.0, NaN greatest.
+__device__ __forceinline__ bool java_double_less(double a, double b) {
+    if (a < b) return true;
+    if (a > b) return false;
+    if (a == b) {
+        if (a == 0.0) return signbit(a) && !signbit(b);
+        return false;
+    }
+    return !isnan(a) && isnan(b);
+}
+
+__device__ __forceinline__ double var_impurity(double count, double sum, double sum_square) {  // dt/Impurity.java:233-235
+    return (count != 0.0) ? ((sum_square - (sum * sum) / count) / count) : 0.0;
+}
+
+struct ClsInfo { double sum_all; int largest; double impurity; };
+constexpr int MAX_CLASSES = 16;
+
+// Entropy.getEntropyInterInfo (dt/Impurity.java:499-522) / Gini.getGiniInfo (:683-704)
+__device__ ClsInfo cls_info(const double* s, int c, bool entropy) {
+    double sum_all = 0;
+    for (int i = 0; i < c; ++i) sum_all += s[i];
+    double impurity = 0.0;
+    int idx = -1;
+    if (sum_all != 0.0) {
+        double max_element = JAVA_DOUBLE_MIN_VALUE;
+        for (int i = 0; i < c; ++i) {
+            const double rate = s[i] / sum_all;
+            if (entropy) {
+                if (rate != 0.0) {
+                    impurity -= rate * (log(rate) / log(2.0));
+                    if (s[i] > max_element) { max_element = s[i]; idx = i; }
+                }
+            } else {
+                impurity -= rate * rate;
+                if (s[i] > max_element) { max_element = s[i]; idx = i; }
+            }
+        }
+    }
+    return ClsInfo{sum_all, idx, impurity};
+}
+
+// Stable bottom-up merge sort of bin indices by key (Collections.sort is a stable merge sort; any stable sort
+// gives the same permutation under Double.compareTo's total order).
+__device__ void stable_sort_by_key(const double* key, int* idx, int* tmp, int n) {
+    for (int i = 0; i < n; ++i) idx[i] = i;
+    for (int width = 1; width < n; width *= 2) {
+        for (int lo = 0; lo < n; lo += 2 * width) {
+            const int mid = min(lo + width, n), hi = min(lo + 2 * width, n);
+            int a = lo, b = mid, o = lo;
+            while (a < mid && b < hi) {
+                if (java_double_less(key[idx[b]], key[idx[a]])) tmp[o++] = idx[b++];
+                else tmp[o++] = idx[a++];
+            }
+            while (a < mid) tmp[o++] = idx[a++];
+            while (b < hi) tmp[o++] = idx[b++];
+        }
+        for (int i = 0; i < n; ++i) idx[i] = tmp[i];
+    }
+}
+
+struct Cand {
+    bool found;
+    int split_i;       // loop index i of the winner
+    double gain, impurity, predict, li, ri, lp, rp, wgt;
+    int node_class, left_class, right_class;
+};
+
+// One (node, feature) block.  order == nullptr for numeric features.  pass_flags (categorical only) records which
+// loop iterations produced a candidate: only those add their category to leftCategories (the `continue`s at
+// dt/Impurity.java:157,166 skip the add), which is needed to rebuild the winner's bitset.
+__device__ Cand scan_feature(const double* __restrict__ s, int bins, int impurity_kind, int c, int min_inst,
+                             double min_gain, const int* order, uint8_t* pass_flags) {
+    Cand best;
+    best.found = false;
+    double max_gain = JAVA_DOUBLE_MIN_VALUE;
+    if (impurity_kind == SB_IMPURITY_VARIANCE || impurity_kind == SB_IMPURITY_FRIEDMANMSE) {
+        double count = 0, sum = 0, sum_sq = 0;
+        for (int i = 0; i < bins; ++i) { count += s[i * 3]; sum += s[i * 3 + 1]; sum_sq += s[i * 3 + 2]; }
+        const double impurity = var_impurity(count, sum, sum_sq);
+        const double predict = count == 0.0 ? 0.0 : sum / count;
+        double lc = 0, ls = 0, lq = 0;
+        for (int i = 0; i < bins - 1; ++i) {
+            const int index = order ? order[i] : i;
+            lc += s[index * 3]; ls += s[index * 3 + 1]; lq += s[index * 3 + 2];
+            const double rc = count - lc, rs = sum - ls, rq = sum_sq - lq;
+            if (pass_flags) pass_flags[i] = 0;
+            if (lc <= min_inst || rc <= min_inst) continue;
+            const double lw = lc / count, rw = rc / count;
+            const double li = var_impurity(lc, ls, lq), ri = var_impurity(rc, rs, rq);
+            // "friedmanmse" is Variance on the master (dt/DTMaster.java:1026-1032)
+            const double gain = impurity - lw * li - rw * ri;
+            if (gain <= min_gain) continue;
+            if (pass_flags) pass_flags[i] = 1;
+            if (gain > max_gain) {
+                max_gain = gain;
+                best.found = true; best.split_i = i; best.gain = gain; best.impurity = impurity; best.predict = predict;
+                best.li = li; best.ri = ri;
+                best.lp = lc == 0.0 ? 0.0 : ls / lc;
+                best.rp = rc == 0.0 ? 0.0 : rs / rc;
+                best.wgt = count;
+                best.node_class = best.left_class = best.right_class = 0;
+            }
+        }
+    } else {
+        const bool entropy = impurity_kind == SB_IMPURITY_ENTROPY;
+        double tot[MAX_CLASSES], l[MAX_CLASSES], r[MAX_CLASSES];
+        for (int j = 0; j < c; ++j) { tot[j] = 0; l[j] = 0; r[j] = 0; }
+        for (int i = 0; i < bins; ++i)
+            for (int j = 0; j < c; ++j) tot[j] += s[i * c + j];
+        const ClsInfo info = cls_info(tot, c, entropy);
+        const double predict = info.sum_all == 0.0 ? 0.0 : (tot[1] / info.sum_all);
+        for (int i = 0; i < bins - 1; ++i) {
+            const int index = order ? order[i] : i;
+            for (int j = 0; j < c; ++j) l[j] += s[index * c + j];
+            const ClsInfo li = cls_info(l, c, entropy);
+            const double lp = li.sum_all == 0.0 ? 0.0 : (l[1] / li.sum_all);
+            for (int j = 0; j < c; ++j) r[j] = tot[j] - l[j];
+            const ClsInfo ri = cls_info(r, c, entropy);
+            if (pass_flags) pass_flags[i] = 0;
+            if (li.sum_all <= min_inst || ri.sum_all <= min_inst) continue;
+            const double rp = ri.sum_all == 0.0 ? 0.0 : (r[1] / ri.sum_all);
+            const double lw = info.sum_all == 0.0 ? 0.0 : (li.sum_all / info.sum_all);
+            const double rw = info.sum_all == 0.0 ? 0.0 : (ri.sum_all / info.sum_all);
+            const double gain = info.impurity - lw * li.impurity - rw * ri.impurity;
+            if (gain <= min_gain) continue;
+            if (pass_flags) pass_flags[i] = 1;
+            if (gain > max_gain) {
+                max_gain = gain;
+                best.found = true; best.split_i = i; best.gain = gain; best.impurity = info.impurity;
+                best.predict = predict; best.li = li.impurity; best.ri = ri.impurity; best.lp = lp; best.rp = rp;
+                best.wgt = info.sum_all;
+                best.node_class = (int)(int8_t)info.largest;
+                best.left_class = (int)(int8_t)li.largest;
+                best.right_class = (int)(int8_t)ri.largest;
+            }
+        }
+    }
+    return best;
+}
+
+__global__ void feature_split_kernel(const double* __restrict__ stats, const SplitTask* __restrict__ tasks, int n_tasks,
+                                     int impurity_kind, int c, int min_inst, double min_gain, sb_gain* cand,
+                                     uint8_t* cand_bits, double* sort_keys, int* sort_idx, int* sort_tmp,
+                                     uint8_t* pass_flags, int max_bins) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tasks) return;
+    const SplitTask tk = tasks[t];
+    const double* s = stats + tk.offset;
+    const bool variance = impurity_kind == SB_IMPURITY_VARIANCE || impurity_kind == SB_IMPURITY_FRIEDMANMSE;
+    const int ss = variance ? 3 : c;
+    int* order = nullptr;
+    uint8_t* flags = nullptr;
+    if (tk.categorical) {
+        double* key = sort_keys + (size_t)t * max_bins;
+        order = sort_idx + (size_t)t * max_bins;
+        int* tmp = sort_tmp + (size_t)t * max_bins;
+        flags = pass_flags + (size_t)t * max_bins;
+        for (int i = 0; i < tk.n_bins; ++i) {
+            double k;
+            if (variance) {  // dt/Impurity.java:213-231: empty bins sort first with key Double.MIN_VALUE
+                k = JAVA_DOUBLE_MIN_VALUE;
+                if (s[i * 3] != 0.0) k = s[i * 3 + 1] / s[i * 3];
+            } else {         // :479-497, :663-681: positive rate over classes 0 and 1 only
+                const double sum = s[i * ss] + s[i * ss + 1];
+                k = 0.0;
+                if (sum != 0.0) k = s[i * ss + 1] / sum;
+            }
+            key[i] = k;
+        }
+        stable_sort_by_key(key, order, tmp, tk.n_bins);
+    }
+    const Cand b = scan_feature(s, tk.n_bins, impurity_kind, c, min_inst, min_gain, order, flags);
+    sb_gain g;
+    memset(&g, 0, sizeof(g));
+    if (b.found) {
+        g.found = 1;
+        g.feature = tk.feature;
+        g.split_type = tk.categorical ? SB_SPLIT_CATEGORICAL : SB_SPLIT_CONTINUOUS;
+        g.split_bin = b.split_i;
+        g.gain = b.gain; g.impurity = b.impurity; g.predict = b.predict;
+        g.left_impurity = b.li; g.right_impurity = b.ri; g.left_predict = b.lp; g.right_predict = b.rp;
+        g.wgt_cnt = b.wgt;
+        g.node_class = b.node_class; g.left_class = b.left_class; g.right_class = b.right_class;
+        if (tk.categorical) {
+            // rebuild leftCategories as of the winning iteration (dt/Impurity.java:169-198)
+            const int n_cats = tk.n_bins - 1;
+            const int bytes = (n_cats + 1) / 8 + 1;
+            uint8_t* bits = cand_bits + (size_t)t * SB_MAX_CAT_BYTES;
+            for (int i = 0; i < bytes; ++i) bits[i] = 0;
+            int left_size = 0;
+            for (int i = 0; i <= b.split_i; ++i) {
+                if (!flags[i]) continue;
+                const int index = order[i];
+                const int v = index >= n_cats ? n_cats : index;
+                bits[v >> 3] |= (uint8_t)(1 << (v % 8));
+                left_size += 1;
+            }
+            int is_left = 1;
+            if (n_cats + 1 <= left_size * 2) {  // too many on the left: store the right side instead
+                is_left = 0;
+                // complement within [0, n_cats]
+                for (int i = 0; i < bytes; ++i) bits[i] = (uint8_t)~bits[i];
+                for (int v = n_cats + 1; v < bytes * 8; ++v) bits[v >> 3] &= (uint8_t)~(1 << (v % 8));
+            }
+            g.is_left = is_left;
+            g.cat_bytes = bytes;
+        }
+    }
+    cand[t] = g;
+}
+
+// GainInfo.getGainInfoByMaxGain over the features of one node, in the reference's visit order.
+__global__ void node_best_kernel(const sb_gain* __restrict__ cand, const uint8_t* __restrict__ cand_bits,
+                                 const SplitTask* __restrict__ tasks, const int32_t* __restrict__ node_task_begin,
+                                 int n_nodes, sb_gain* out, uint8_t* out_bits) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= n_nodes) return;
+    const int t0 = node_task_begin[n], t1 = node_task_begin[n + 1];
+    double max_gain = JAVA_DOUBLE_MIN_VALUE;
+    int best = -1, best_rank = 0x7fffffff;
+    // tasks of a node are stored in feature-list order; visit_rank gives the HashMap order.  "First strictly
+    // greater wins" == among equal maxima the one with the smallest rank.
+    for (int t = t0; t < t1; ++t) {
+        if (!cand[t].found) continue;
+        const double g = cand[t].gain;
+        if (g > max_gain || (g == max_gain && best >= 0 && tasks[t].visit_rank < best_rank)) {
+            max_gain = g;
+            best = t;
+            best_rank = tasks[t].visit_rank;
+        }
+    }
+    if (best < 0) {
+        sb_gain z;
+        memset(&z, 0, sizeof(z));
+        out[n] = z;
+        return;
+    }
+    out[n] = cand[best];
+    if (out_bits && cand[best].cat_bytes > 0) {
+        const uint8_t* src = cand_bits + (size_t)best * SB_MAX_CAT_BYTES;
+        uint8_t* dst = out_bits + (size_t)n * SB_MAX_CAT_BYTES;
+        for (int i = 0; i < cand[best].cat_bytes; ++i) dst[i] = src[i];
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_finalize(const int64_t* raw_lo, const int64_t* raw_hi, int64_t total, int stats_size, int kind,
+                            const double* inv_scales, double* stats, cudaStream_t s) {
+    if (total <= 0) return cudaSuccess;
+    int64_t g = (total + 255) / 256;
+    if (g > 148 * 8) g = 148 * 8;
+    finalize_stats_kernel<<<(int)g, 256, 0, s>>>(raw_lo, raw_hi, total, stats_size, kind, inv_scales, stats);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_best_splits(const double* stats, const SplitTask* tasks, int n_tasks, int n_nodes, int impurity,
+                               int stats_size, int min_instances, double min_info_gain, sb_gain* cand,
+                               uint8_t* cand_bits, sb_gain* out, uint8_t* out_bits, const int32_t* node_task_begin,
+                               const SplitScratch& sc, cudaStream_t s) {
+    if (n_tasks <= 0 || n_nodes <= 0) return cudaSuccess;
+    feature_split_kernel<<<(n_tasks + 63) / 64, 64, 0, s>>>(stats, tasks, n_tasks, impurity, stats_size, min_instances,
+                                                            min_info_gain, cand, cand_bits, sc.keys, sc.idx, sc.tmp,
+                                                            sc.flags, sc.max_bins);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    node_best_kernel<<<(n_nodes + 63) / 64, 64, 0, s>>>(cand, cand_bits, tasks, node_task_begin, n_nodes, out, out_bits);
+    return cudaGetLastError();
+}
+
+}  // namespace sb

@@ -1,0 +1,189 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on identical seeded inputs.
+
+Bar (BASELINE.json north_star): per-bin counts bit-exact; weighted sums, gains and error sums within 1e-9
+relative; identical chosen split feature / bin; per-row predict / output identical floats.
+"""
+import numpy as np
+import pytest
+
+from shifu_b200 import capi
+from shifu_b200.capi import ConfigArrays, Worker
+from shifu_b200.messages import IterIn, Node
+
+from helpers import apply_gain, gain_fields, make_data, rel_close
+
+pytestmark = pytest.mark.gpu
+
+
+def index_to_level(i):
+    return int(i).bit_length()
+
+
+def is_pos_zero(x):
+    return x == 0.0 and not np.signbit(x)
+
+
+def assert_stats_close(cfg, it, dev, orc, contributions_scale, exact_counts):
+    assert dev.shape == orc.shape
+    ss = cfg.stats_size
+    if ss == 3 and cfg.struct.impurity in (capi.SB_IMPURITY_VARIANCE, capi.SB_IMPURITY_FRIEDMANMSE):
+        d, o = dev.reshape(-1, 3), orc.reshape(-1, 3)
+        if exact_counts:
+            assert np.array_equal(d[:, 0], o[:, 0]), "per-bin counts must be bit-exact"
+        else:
+            assert rel_close(d[:, 0], o[:, 0], scale=contributions_scale[0]).all()
+        assert rel_close(d[:, 1], o[:, 1], scale=contributions_scale[1]).all()
+        assert rel_close(d[:, 2], o[:, 2], scale=contributions_scale[2]).all()
+    else:
+        if exact_counts:
+            assert np.array_equal(dev, orc), "per-bin class counts must be bit-exact"
+        else:
+            assert rel_close(dev, orc, scale=contributions_scale[0]).all()
+
+
+def assert_gain_equal(gd, go, bits_d=None, bits_o=None, idx=0):
+    d, o = gain_fields(gd), gain_fields(go)
+    for k in ("found", "feature", "split_type", "split_bin", "is_left", "cat_bytes", "left_class", "right_class",
+              "node_class"):
+        assert d[k] == o[k], (k, d, o)
+    if not d["found"]:
+        return
+    for k in ("gain", "impurity", "predict", "left_impurity", "right_impurity", "left_predict", "right_predict",
+              "wgt_cnt"):
+        assert abs(d[k] - o[k]) <= 1e-9 * abs(o[k]) + 1e-13, (k, d[k], o[k])
+    if d["cat_bytes"]:
+        a = bits_d[idx * capi.SB_MAX_CAT_BYTES: idx * capi.SB_MAX_CAT_BYTES + d["cat_bytes"]]
+        b = bits_o[idx * capi.SB_MAX_CAT_BYTES: idx * capi.SB_MAX_CAT_BYTES + d["cat_bytes"]]
+        assert np.array_equal(a, b)
+
+
+def run_gbt(n, n_bins, seed, n_trees=2, max_depth=4, weighted=False, loss=capi.SB_LOSS_SQUARED, label="binary",
+            is_categorical=None, feature_subsets=False, with_validation=True, bagging=False, min_inst=1,
+            oracle_threads=3):
+    from oracle.pyoracle import OracleWorker
+    cfg = ConfigArrays(n_bins, is_categorical=is_categorical, loss=loss, is_gbdt=True, tree_num=n_trees,
+                       max_depth=max_depth, min_instances_per_node=min_inst, learning_rate=0.1,
+                       column_num=np.arange(len(n_bins)) + 3)
+    cols, y, sig, _ = make_data(n, n_bins, seed, label=label, weighted=weighted)
+    rng = np.random.default_rng(seed + 1)
+    w0 = (rng.random(n) < 0.7).astype(np.float32)[None, :] if bagging else None
+    dev, orc = Worker(cfg), OracleWorker(cfg)
+    dev.load_rows(cols, y, sig, w0)
+    orc.load_rows(cols, y, sig, w0)
+    if with_validation:
+        vcols, vy, vsig, _ = make_data(max(n // 5, 1), n_bins, seed + 7, label=label, weighted=weighted)
+        dev.load_rows(vcols, vy, vsig, None, is_validation=True)
+        orc.load_rows(vcols, vy, vsig, None, is_validation=True)
+    has_cat = is_categorical is not None and any(is_categorical)
+    F = len(n_bins)
+    trees = []
+    n_iter = 0
+    for t in range(n_trees):
+        root = Node(1)
+        trees.append(root)
+        todo_nodes = [root]
+        switch = True
+        while todo_nodes:
+            todo = []
+            for k, nd in enumerate(todo_nodes):
+                feats = []
+                if feature_subsets:
+                    feats = sorted(rng.choice(F, size=max(1, F // 2), replace=False).tolist())
+                    rng.shuffle(feats)
+                todo.append((k, t, nd.id, feats))
+            sent = [(t - 1, trees[t - 1]), (t, root)] if (switch and t >= 1) else [(t, root)]
+            new_w = (rng.random(n) < 0.7).astype(np.float32) if (bagging and switch and t >= 1) else None
+            # isFirstTree as the master sets it: trees.size() == 1, evaluated before a new root is added
+            # (dt/DTMaster.java:418,475)
+            it = IterIn(cfg, sent, todo, switch_to_next_tree=switch, is_first_tree=(t == 0) or (switch and t == 1),
+                        new_weights=new_w)
+            d = dev.compute(it)
+            o = orc.compute(it, n_threads=oracle_threads)
+            n_iter += 1
+            # scalars
+            for a, b in zip(d[:4], o[:4]):
+                assert abs(a - b) <= 1e-9 * abs(b) + 1e-12, (d[:4], o[:4])
+            # per-row state after phase A
+            dp, dout, dnode, dw = dev.read_rows(n)
+            op, oout = orc.read_rows(n)
+            if loss == capi.SB_LOSS_LOG:
+                assert np.allclose(dp, op, rtol=3e-7, atol=0) and np.allclose(dout, oout, rtol=3e-7, atol=1e-37)
+            else:
+                assert np.array_equal(dp, op) and np.array_equal(dout, oout)
+            wv = np.ones(n, np.float32) if dw is None else dw
+            sv = np.ones(n, np.float32) if sig is None else sig
+            scale = (np.sum(np.abs(sv * wv)), np.sum(np.abs(dout * sv * wv)), np.sum(np.abs(dout * dout * sv * wv)))
+            exact_counts = not weighted
+            assert_stats_close(cfg, it, d[4], o[4], scale, exact_counts)
+            gd, bits_d = dev.best_splits(len(todo), with_cat=has_cat)
+            go, bits_o = orc.best_splits(it, o[4], with_cat=has_cat)
+            next_nodes = []
+            for k, nd in enumerate(todo_nodes):
+                assert_gain_equal(gd[k], go[k], bits_d, bits_o, k)
+                g = gd[k]
+                if not g.found:
+                    continue
+                level = index_to_level(nd.id)
+                is_leaf = g.gain <= 0 or level == max_depth
+                nd.predict = g.predict
+                if is_leaf:
+                    continue
+                left, right = apply_gain(cfg, nd, g, bits_d, k)
+                # Double.compare(x, 0d) == 0 is true for +0.0 only (dt/DTMaster.java:570-571,586-587)
+                if not (level + 1 == max_depth or is_pos_zero(g.left_impurity)):
+                    next_nodes.append(left)
+                if not (level + 1 == max_depth or is_pos_zero(g.right_impurity)):
+                    next_nodes.append(right)
+            todo_nodes = next_nodes
+            switch = False
+    dev.close()
+    orc.close()
+    return n_iter
+
+
+def test_gbt_variance_unweighted_counts_bit_exact():
+    assert run_gbt(20000, [64] * 40, seed=11, n_trees=2, max_depth=5) >= 8
+
+
+def test_gbt_weighted_mixed_bins():
+    run_gbt(15000, [64] * 20 + [32] * 10 + [10] * 7 + [2, 1, 255], seed=12, n_trees=2, max_depth=4, weighted=True)
+
+
+def test_gbt_feature_subsets_and_bagging():
+    run_gbt(12000, [32] * 50, seed=13, n_trees=3, max_depth=4, feature_subsets=True, bagging=True)
+
+
+def test_gbt_log_loss_real_labels_absolute():
+    run_gbt(8000, [16] * 12, seed=14, n_trees=3, max_depth=3, loss=capi.SB_LOSS_LOG)
+    run_gbt(8000, [16] * 12, seed=15, n_trees=2, max_depth=3, loss=capi.SB_LOSS_ABSOLUTE, label="real")
+    run_gbt(8000, [16] * 12, seed=16, n_trees=2, max_depth=3, loss=capi.SB_LOSS_HALFGRADSQUARED, label="real")
+
+
+def test_gbt_categorical_features():
+    n_bins = [64] * 6 + [11, 51, 201, 31]
+    is_cat = [0] * 6 + [1, 1, 1, 1]
+    run_gbt(10000, n_bins, seed=17, n_trees=2, max_depth=4, is_categorical=is_cat)
+
+
+def test_gbt_ragged_sizes():
+    for n in (1, 2, 127, 128, 129, 1000):
+        run_gbt(n, [8] * 5, seed=100 + n, n_trees=2, max_depth=3, with_validation=(n > 4))
+
+
+def test_empty_training_set():
+    cfg = ConfigArrays([8] * 3)
+    w = Worker(cfg)
+    w.load_rows([np.zeros(0, np.uint8)] * 3, np.zeros(0, np.float32))
+    it = IterIn(cfg, [(0, Node(1))], [(0, 0, 1, [])], switch_to_next_tree=True, is_first_tree=True)
+    tc, vc, te, ve, stats = w.compute(it)
+    assert tc == 0 and te == 0 and np.all(stats == 0) and len(stats) == 3 * 8 * 3
+    w.close()
+
+
+def test_bin_out_of_range_is_rejected():
+    cfg = ConfigArrays([8] * 2)
+    w = Worker(cfg)
+    with pytest.raises(capi.SbError) as e:
+        w.load_rows([np.array([1, 9], np.uint8), np.array([0, 0], np.uint8)], np.zeros(2, np.float32))
+    assert e.value.code == -4
+    w.close()
