@@ -202,13 +202,14 @@ SB_API const char* sb_version(void);
  * (Data.subsampleWeights transposed); NULL => all 1f.  significance NULL => all 1f.
  * output = predict = label initially (dt/DTWorker.java:1264-1273).
  * Host pointers; the call copies to the device and returns when the copy is complete.
- * May be called repeatedly before the first sb_compute; rows are concatenated.
+ * One call per set (the Java side batches DTWorker.load lines into direct buffers and loads in postLoad).
  */
 SB_API int sb_load_rows(sb_handle* h, int32_t is_validation, int64_t n_rows, const void* const* bins,
                         const float* label, const float* significance, const float* weights);
 /* Same, but every pointer is a device pointer on the handle's GPU and is ADOPTED, not copied (the
-   caller keeps it alive until sb_destroy).  bins[f] must be 16-byte aligned.  Single call only. */
-SB_API int sb_load_rows_device(sb_handle* h, int32_t is_validation, int64_t n_rows, const void* const* bins,
+   caller keeps it alive until sb_destroy).  bins is the column-major uint8 bin matrix: feature slot f
+   starts at bins + f*pitch; bins 16-byte aligned, pitch a multiple of 16 and >= n_rows. */
+SB_API int sb_load_rows_device(sb_handle* h, int32_t is_validation, int64_t n_rows, const void* bins, int64_t pitch,
                                float* label, float* significance, float* weights);
 /* Reads back per-row state (any pointer may be NULL): Data.predict, Data.output, current node id of
    tree `tree_id`, subsampleWeights[w_index]. */
@@ -266,6 +267,11 @@ SB_API int sb_best_splits(sb_handle* h, sb_gain* gains, uint8_t* cat_bits);
 /* Re-runs only the statistics pass (phase B) of the last sb_compute_begin, n_repeat times, and reports the
    mean device time of the histogram kernel in milliseconds (CUDA events on the handle's stream). */
 SB_API int sb_time_stats_pass(sb_handle* h, int32_t n_repeat, float* ms_hist_kernel, float* ms_total);
+/* Per-pass timing of the histogram kernel: with profiling on, sb_compute_stats brackets the kernel with CUDA
+   events on the handle's stream; sb_hist_time returns (and clears) the accumulated device time, the number of
+   passes and of histogram launches since the last call. */
+SB_API int sb_set_profiling(sb_handle* h, int32_t on);
+SB_API int sb_hist_time(sb_handle* h, float* ms_total, int32_t* n_passes, int32_t* n_launches);
 /* Counters since creation: kernels launched by this library, bytes copied H2D / D2H. */
 SB_API int sb_counters(sb_handle* h, int64_t* launches, int64_t* h2d_bytes, int64_t* d2h_bytes);
 /* Fills device memory with the synthetic data set of SURVEY.md 8(d) (counter-based splitmix64) and loads it:

@@ -132,7 +132,7 @@ EXPORTS = [
     "sb_create", "sb_destroy", "sb_last_error", "sb_version", "sb_load_rows", "sb_load_rows_device", "sb_read_rows",
     "sb_stats_len", "sb_compute", "sb_compute_begin", "sb_scale_buffer", "sb_compute_stats", "sb_raw_buffer",
     "sb_acc_buffer", "sb_compute_finish", "sb_set_stream", "sb_best_splits", "sb_time_stats_pass", "sb_counters",
-    "sb_load_synthetic", "sb_read_bins", "sb_read_labels",
+    "sb_load_synthetic", "sb_read_bins", "sb_read_labels", "sb_set_profiling", "sb_hist_time",
 ]
 
 _lib = None
@@ -156,7 +156,7 @@ def load_library(path=None):
     lib.sb_last_error.restype = C.c_char_p
     lib.sb_version.restype = C.c_char_p
     lib.sb_load_rows.argtypes = [H, C.c_int32, C.c_int64, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p, C.c_void_p]
-    lib.sb_load_rows_device.argtypes = [H, C.c_int32, C.c_int64, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.sb_load_rows_device.argtypes = [H, C.c_int32, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.sb_read_rows.argtypes = [H, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.sb_stats_len.argtypes = [H, C.POINTER(SbIterIn)]
     lib.sb_stats_len.restype = C.c_int64
@@ -174,6 +174,8 @@ def load_library(path=None):
     lib.sb_load_synthetic.argtypes = [H, C.c_int32, C.c_int64, C.c_int64, C.c_uint64, C.c_int32, C.c_int32]
     lib.sb_read_bins.argtypes = [H, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_void_p]
     lib.sb_read_labels.argtypes = [H, C.c_int32, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
+    lib.sb_set_profiling.argtypes = [H, C.c_int32]
+    lib.sb_hist_time.argtypes = [H, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     if path is None:
         _lib = lib
     return lib
@@ -351,6 +353,15 @@ class Worker:
         a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
         check(self.lib, self.lib.sb_counters(self.h, C.byref(a), C.byref(b), C.byref(c)))
         return a.value, b.value, c.value
+
+    def set_profiling(self, on=True):
+        check(self.lib, self.lib.sb_set_profiling(self.h, int(on)))
+
+    def hist_time(self):
+        """(ms_total, n_passes, n_launches) of the histogram kernel since the last call."""
+        ms, a, b = C.c_float(), C.c_int32(), C.c_int32()
+        check(self.lib, self.lib.sb_hist_time(self.h, C.byref(ms), C.byref(a), C.byref(b)))
+        return ms.value, a.value, b.value
 
     def set_stream(self, stream_ptr):
         check(self.lib, self.lib.sb_set_stream(self.h, C.c_void_p(stream_ptr)))

@@ -1,5 +1,7 @@
 // api.cu -- the C ABI of include/shifu_b200.h: handle, data load, the DTWorker.doCompute replacement and the
 // on-device DTMaster best-split step.  Host logic only; kernels live in hist.cu / rows.cu / split.cu.
+#include <cuda.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -41,6 +43,7 @@ struct DevBuf {  // grow-only device buffer
 
 struct HistLaunch {
     int kind;
+    int cnt_int;
     HistArgs args;
     int grid;
     size_t smem;
@@ -92,8 +95,15 @@ struct sb_handle {
     float* d_scales = nullptr;        // 3
     double* d_inv_scales = nullptr;   // 3
     uint32_t* d_error_flag = nullptr;
+    int* d_cnt_shift = nullptr;
+    bool cnt_int = false;  // every sig*weight product of the training rows is an integer in [0, 1024]
 
     int64_t launches_count = 0, h2d_bytes = 0, d2h_bytes = 0;
+
+    // optional per-pass timing of the histogram kernel (CUDA events on the launching stream)
+    bool profiling = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
+    std::vector<int> prof_launches;
 };
 
 namespace {
@@ -127,9 +137,58 @@ TreeView view_of(const DeviceTree& t) { return TreeView{t.feat, t.mask_off, t.pr
 
 int n_node_arrays(const sb_handle* h) { return h->cfg.is_gbdt ? 1 : std::max(1, h->cfg.tree_num); }
 
+// Decides whether the count statistic can be accumulated as plain 32-bit integers (see hist.cu).  Synchronises;
+// called at load time and whenever the caller injects new sample weights.
+int refresh_cnt_int(sb_handle* h) {
+    RowSet& r = h->train;
+    uint32_t* flag_dev = reinterpret_cast<uint32_t*>(h->d_cnt_shift) + 1;  // second word of the same allocation
+    SB_CUDA(cudaMemsetAsync(flag_dev, 0, 4, h->stream));
+    const int W = r.weights ? h->cfg.weights_per_row : 1;
+    for (int c = 0; c < W; ++c) {
+        SB_CUDA(launch_check_int_weights(r.n, r.significance, r.weights ? r.weights + (int64_t)c * r.n : nullptr, flag_dev,
+                                         h->stream));
+        h->launches_count += 1;
+    }
+    uint32_t flag = 0;
+    SB_CUDA(cudaMemcpyAsync(&flag, flag_dev, 4, cudaMemcpyDeviceToHost, h->stream));
+    SB_CUDA(cudaStreamSynchronize(h->stream));
+    h->cnt_int = (flag & 1u) == 0;
+    return SB_OK;
+}
+
+// CUtensorMap over the uint8 bin matrix [F][pitch]: box = {128 rows, 32 feature slots}, 128-byte swizzle, zero fill
+// outside [0, n) x [0, F).  cuTensorMapEncodeTiled is resolved through the runtime, so libcuda is not linked.
+int make_tensor_map(sb_handle* h, RowSet& r) {
+    typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        SB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+        if (qres != cudaDriverEntryPointSuccess || !fn) return fail(SB_ERR_CUDA, "cuTensorMapEncodeTiled not available in this driver");
+        encode = (encode_fn)fn;
+    }
+    (void)h;
+    const cuuint64_t gdim[2] = {(cuuint64_t)std::max<int64_t>(r.n, 1), (cuuint64_t)r.n_features};
+    const cuuint64_t gstride[1] = {(cuuint64_t)r.pitch};
+    const cuuint32_t box[2] = {(cuuint32_t)HIST_T_ROWS, 32u};
+    const cuuint32_t estride[2] = {1u, 1u};
+    CUresult res = encode(reinterpret_cast<CUtensorMap*>(r.tensor_map), CU_TENSOR_MAP_DATA_TYPE_UINT8, 2,
+                          const_cast<void*>(r.bins_base), gdim, gstride, box, estride, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (res != CUDA_SUCCESS) return fail(SB_ERR_CUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)res));
+    return SB_OK;
+}
+
 // Allocates the derived per-row state and finishes a load (shared by the host and device loaders).
 int finish_load(sb_handle* h, RowSet& r) {
     const int64_t n = r.n;
+    r.h_col.resize((size_t)r.n_features);
+    for (int f = 0; f < r.n_features; ++f) r.h_col[f] = static_cast<const uint8_t*>(r.bins_base) + (size_t)f * r.pitch;
+    int trc = make_tensor_map(h, r);
+    if (trc != SB_OK) return trc;
     SB_CUDA(cudaMalloc(&r.d_col, sizeof(void*) * std::max(1, r.n_features)));
     SB_CUDA(cudaMemcpyAsync((void*)r.d_col, r.h_col.data(), sizeof(void*) * r.n_features, cudaMemcpyHostToDevice, h->stream));
     SB_CUDA(cudaMalloc(&r.output, sizeof(float) * std::max<int64_t>(n, 1)));
@@ -149,6 +208,7 @@ int finish_load(sb_handle* h, RowSet& r) {
     SB_CUDA(cudaStreamSynchronize(h->stream));
     if (flag & 2u) return fail(SB_ERR_RANGE, "a bin index is outside [0, n_bins) of its feature");
     r.loaded = true;
+    if (&r == &h->train) return refresh_cnt_int(h);
     return SB_OK;
 }
 
@@ -265,24 +325,34 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     for (int i = 0; i < S; ++i) order[i] = i;
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return lay.nodes[a].tree_id < lay.nodes[b].tree_id; });
 
-    // tiles of 32 feature slots over the union of the feature lists
+    // tiles of 32 CONSECUTIVE feature slots (one TMA box each); only tiles with a used feature are launched
     std::vector<uint8_t> used((size_t)F, 0);
     for (const auto& nd : lay.nodes)
         for (int f : nd.features) used[f] = 1;
-    std::vector<int32_t> tile_feats;
-    int bins_pad = 1;
-    for (int f = 0; f < F; ++f)
-        if (used[f]) {
-            if (h->n_bins[f] > 256) return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins are not supported yet");
-            tile_feats.push_back(f);
-            bins_pad = std::max(bins_pad, h->n_bins[f]);
-        }
-    while (tile_feats.size() % 32) tile_feats.push_back(-1);
-    const int n_tiles = (int)tile_feats.size() / 32;
-    if (n_tiles == 0) return SB_OK;
+    std::vector<int32_t> tile_feats, tile_slot0;
     std::vector<int> tile_of((size_t)F, -1), lane_of((size_t)F, -1);
-    for (size_t i = 0; i < tile_feats.size(); ++i)
-        if (tile_feats[i] >= 0) { tile_of[tile_feats[i]] = (int)(i / 32); lane_of[tile_feats[i]] = (int)(i % 32); }
+    int bins_pad = 1;
+    for (int f0 = 0; f0 < F; f0 += 32) {
+        bool any = false;
+        for (int f = f0; f < std::min(F, f0 + 32); ++f) any |= used[f] != 0;
+        if (!any) continue;
+        const int t = (int)tile_slot0.size();
+        tile_slot0.push_back(f0);
+        for (int l = 0; l < 32; ++l) {
+            const int f = f0 + l;
+            if (f < F && used[f]) {
+                if (h->n_bins[f] > 256) return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins are not supported yet");
+                tile_feats.push_back(f);
+                tile_of[f] = t;
+                lane_of[f] = l;
+                bins_pad = std::max(bins_pad, h->n_bins[f]);
+            } else {
+                tile_feats.push_back(-1);
+            }
+        }
+    }
+    const int n_tiles = (int)tile_slot0.size();
+    if (n_tiles == 0) return SB_OK;
 
     std::vector<uint32_t> fmask((size_t)S * n_tiles, 0u);
     std::vector<int64_t> pair_off((size_t)S * F, -1);
@@ -294,15 +364,17 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
             pair_off[(size_t)s * F + f] = nd.offset + nd.feat_off[k];
         }
     }
-    SB_CUDA(h->tile_feats.reserve(tile_feats.size()));
+    SB_CUDA(h->tile_feats.reserve(tile_feats.size() + tile_slot0.size()));
     SB_CUDA(h->slot_fmask.reserve(fmask.size()));
     SB_CUDA(h->pair_off.reserve(pair_off.size()));
     SB_CUDA(cudaMemcpyAsync(h->tile_feats.p, tile_feats.data(), tile_feats.size() * 4, cudaMemcpyHostToDevice, h->stream));
+    SB_CUDA(cudaMemcpyAsync(h->tile_feats.p + tile_feats.size(), tile_slot0.data(), tile_slot0.size() * 4, cudaMemcpyHostToDevice, h->stream));
     SB_CUDA(cudaMemcpyAsync(h->slot_fmask.p, fmask.data(), fmask.size() * 4, cudaMemcpyHostToDevice, h->stream));
     SB_CUDA(cudaMemcpyAsync(h->pair_off.p, pair_off.data(), pair_off.size() * 8, cudaMemcpyHostToDevice, h->stream));
     h->h2d_bytes += tile_feats.size() * 4 + fmask.size() * 4 + pair_off.size() * 8;
 
-    const int nw = h->stat_kind == STAT_VARIANCE ? 6 : 2 * h->stats_size;
+    const int cnt_int = h->cnt_int ? 1 : 0;
+    const int nw = hist_words_per_bin(h->stat_kind, cnt_int, h->stats_size);
     const int max_gs = hist_max_slots_per_block(bins_pad, nw);
     if (max_gs < 1) return fail(SB_ERR_UNSUPPORTED, "one node's histogram tile does not fit in shared memory");
 
@@ -339,8 +411,8 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         }
         HistLaunch L;
         L.kind = h->stat_kind;
+        L.cnt_int = cnt_int;
         HistArgs& a = L.args;
-        a.cols = h->train.d_col;
         a.feat_bins = h->d_feat_bins;
         a.output = h->train.output;
         a.significance = h->train.significance;
@@ -353,6 +425,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         a.n_rows = n;
         a.n_features = F;
         a.tile_feats = h->tile_feats.p;
+        a.tile_slot0 = h->tile_feats.p + (size_t)n_tiles * 32;
         a.slot_fmask = h->slot_fmask.p + (size_t)s0 * n_tiles;
         a.pair_off = h->pair_off.p + (size_t)s0 * F;
         a.n_tiles = n_tiles;
@@ -364,11 +437,12 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         int64_t n_chunks = (148 * 3 + (int64_t)n_tiles * a.n_groups - 1) / ((int64_t)n_tiles * a.n_groups);
         n_chunks = std::max<int64_t>(1, std::min(n_chunks, tiles_rows));
         int64_t rpc = ((tiles_rows + n_chunks - 1) / n_chunks) * HIST_T_ROWS;
-        rpc = std::min<int64_t>(rpc, MAX_ROWS_PER_FLUSH);
+        rpc = std::min<int64_t>(rpc, cnt_int ? MAX_ROWS_PER_FLUSH / 2 : MAX_ROWS_PER_FLUSH);  // 2^21 rows * 1024 < 2^32
         n_chunks = (n + rpc - 1) / rpc;
         a.rows_per_chunk = rpc;
         a.stats_size = h->stats_size;
         a.scales = h->d_scales;
+        a.cnt_shift = h->d_cnt_shift;
         a.raw_lo = h->raw.p;
         a.raw_hi = h->raw.p + lay.total;
         a.error_flag = h->d_error_flag;
@@ -435,7 +509,7 @@ int plan_split_tasks(sb_handle* h) {
 
 int run_histograms(sb_handle* h) {
     for (const HistLaunch& L : h->launches) {
-        SB_CUDA(hist_launch(L.kind, L.args, L.grid, L.smem, h->stream));
+        SB_CUDA(hist_launch(L.kind, L.cnt_int, L.args, h->train.tensor_map, L.grid, L.smem, h->stream));
         h->launches_count += 1;
     }
     return SB_OK;
@@ -500,6 +574,8 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
     SB_CUDA(cudaMalloc(&h->d_inv_scales, 32));
     SB_CUDA(cudaMalloc(&h->d_error_flag, 4));
     SB_CUDA(cudaMemset(h->d_error_flag, 0, 4));
+    SB_CUDA(cudaMalloc(&h->d_cnt_shift, 8));
+    SB_CUDA(cudaMemset(h->d_cnt_shift, 0, 8));
     *out = h.release();
     return SB_OK;
 }
@@ -522,6 +598,7 @@ SB_API void sb_destroy(sb_handle* h) {
     if (h->d_scales) cudaFree(h->d_scales);
     if (h->d_inv_scales) cudaFree(h->d_inv_scales);
     if (h->d_error_flag) cudaFree(h->d_error_flag);
+    if (h->d_cnt_shift) cudaFree(h->d_cnt_shift);
     delete h;
 }
 
@@ -546,10 +623,10 @@ SB_API int sb_load_rows(sb_handle* h, int32_t is_validation, int64_t n_rows, con
     const int64_t pitch = ((n_rows + 255) / 256) * 256 + 256;  // tail tile reads stay inside the allocation
     SB_CUDA(cudaMalloc(&r.owned_bins, (size_t)pitch * F));
     SB_CUDA(cudaMemsetAsync(r.owned_bins, 0, (size_t)pitch * F, h->stream));
-    r.h_col.resize((size_t)F);
+    r.bins_base = r.owned_bins;
+    r.pitch = pitch;
     for (int f = 0; f < F; ++f) {
         uint8_t* dst = static_cast<uint8_t*>(r.owned_bins) + (size_t)f * pitch;
-        r.h_col[f] = dst;
         if (!bins[f]) return fail(SB_ERR_INVALID, "null feature column");
         if (n_rows > 0) SB_CUDA(cudaMemcpyAsync(dst, bins[f], (size_t)n_rows, cudaMemcpyHostToDevice, h->stream));
     }
@@ -568,9 +645,10 @@ SB_API int sb_load_rows(sb_handle* h, int32_t is_validation, int64_t n_rows, con
     return finish_load(h, r);
 }
 
-SB_API int sb_load_rows_device(sb_handle* h, int32_t is_validation, int64_t n_rows, const void* const* bins, float* label,
-                               float* significance, float* weights) {
+SB_API int sb_load_rows_device(sb_handle* h, int32_t is_validation, int64_t n_rows, const void* bins, int64_t pitch,
+                               float* label, float* significance, float* weights) {
     if (!h || !bins || !label || !significance || n_rows < 0) return fail(SB_ERR_INVALID, "null argument");
+    if (((uintptr_t)bins & 15) || (pitch & 15) || pitch < n_rows) return fail(SB_ERR_INVALID, "bin matrix must be 16-byte aligned with a pitch that is a multiple of 16 and >= n_rows");
     SB_CUDA(cudaSetDevice(h->cfg.device));
     RowSet& r = is_validation ? h->valid : h->train;
     if (r.loaded) return fail(SB_ERR_UNSUPPORTED, "rows of this set were already loaded (one load call per set)");
@@ -578,12 +656,10 @@ SB_API int sb_load_rows_device(sb_handle* h, int32_t is_validation, int64_t n_ro
     r.n = n_rows;
     r.n_features = F;
     r.owns_inputs = false;
-    r.h_col.resize((size_t)F);
-    for (int f = 0; f < F; ++f) {
+    for (int f = 0; f < F; ++f)
         if (h->n_bins[f] > 256) return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins are not supported yet");
-        if (!bins[f] || ((uintptr_t)bins[f] & 15)) return fail(SB_ERR_INVALID, "device feature column must be non-null and 16-byte aligned");
-        r.h_col[f] = bins[f];
-    }
+    r.bins_base = bins;
+    r.pitch = pitch;
     r.label = label;
     r.significance = significance;
     r.weights = is_validation ? nullptr : weights;
@@ -604,8 +680,8 @@ SB_API int sb_load_synthetic(sb_handle* h, int32_t is_validation, int64_t row0, 
     r.owns_inputs = true;
     const int64_t pitch = ((n_rows + 255) / 256) * 256 + 256;
     SB_CUDA(cudaMalloc(&r.owned_bins, (size_t)pitch * F));
-    r.h_col.resize((size_t)F);
-    for (int f = 0; f < F; ++f) r.h_col[f] = static_cast<uint8_t*>(r.owned_bins) + (size_t)f * pitch;
+    r.bins_base = r.owned_bins;
+    r.pitch = pitch;
     const size_t nf = (size_t)std::max<int64_t>(n_rows, 1);
     SB_CUDA(cudaMalloc(&r.label, nf * 4));
     SB_CUDA(cudaMalloc(&r.significance, nf * 4));
@@ -730,6 +806,8 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
                     SB_CUDA(cudaMemcpyAsync(tr.weights + (int64_t)(curr % W) * tr.n, in->new_weights, (size_t)tr.n * 4,
                                             cudaMemcpyHostToDevice, h->stream));
                     h->h2d_bytes += tr.n * 4;
+                    rc = refresh_cnt_int(h);
+                    if (rc != SB_OK) return rc;
                 }
             }
             SB_CUDA(launch_fill_i32(tr.node_id, tr.n, SB_ROOT_INDEX, h->stream));
@@ -832,9 +910,46 @@ SB_API int sb_compute_stats(sb_handle* h) {
     if (!h) return fail(SB_ERR_INVALID, "null argument");
     if (!h->begun) return fail(SB_ERR_STATE, "sb_compute_stats before sb_compute_begin");
     SB_CUDA(cudaSetDevice(h->cfg.device));
-    SB_CUDA(launch_make_scales(h->d_maxbits, h->stat_kind, h->d_scales, h->d_inv_scales, h->stream));
+    SB_CUDA(launch_make_scales(h->d_maxbits, h->stat_kind, h->d_scales, h->d_inv_scales, h->d_cnt_shift, h->stream));
     h->launches_count += 1;
-    return run_histograms(h);
+    if (!h->profiling) return run_histograms(h);
+    cudaEvent_t e0, e1;
+    SB_CUDA(cudaEventCreate(&e0));
+    SB_CUDA(cudaEventCreate(&e1));
+    SB_CUDA(cudaEventRecord(e0, h->stream));
+    int rc = run_histograms(h);
+    SB_CUDA(cudaEventRecord(e1, h->stream));
+    h->prof_events.push_back({e0, e1});
+    h->prof_launches.push_back((int)h->launches.size());
+    return rc;
+}
+
+SB_API int sb_set_profiling(sb_handle* h, int32_t on) {
+    if (!h) return fail(SB_ERR_INVALID, "null handle");
+    h->profiling = on != 0;
+    return SB_OK;
+}
+
+SB_API int sb_hist_time(sb_handle* h, float* ms_total, int32_t* n_passes, int32_t* n_launches) {
+    if (!h) return fail(SB_ERR_INVALID, "null handle");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    double ms = 0;
+    int launches = 0;
+    for (size_t i = 0; i < h->prof_events.size(); ++i) {
+        SB_CUDA(cudaEventSynchronize(h->prof_events[i].second));
+        float t = 0;
+        SB_CUDA(cudaEventElapsedTime(&t, h->prof_events[i].first, h->prof_events[i].second));
+        ms += t;
+        launches += h->prof_launches[i];
+        cudaEventDestroy(h->prof_events[i].first);
+        cudaEventDestroy(h->prof_events[i].second);
+    }
+    if (ms_total) *ms_total = (float)ms;
+    if (n_passes) *n_passes = (int32_t)h->prof_events.size();
+    if (n_launches) *n_launches = launches;
+    h->prof_events.clear();
+    h->prof_launches.clear();
+    return SB_OK;
 }
 
 SB_API int sb_raw_buffer(sb_handle* h, void** dev_ptr, int64_t* bytes) {
@@ -876,6 +991,7 @@ SB_API int sb_compute_finish(sb_handle* h, sb_iter_out* out) {
     if (flags[0] & 4u) return fail(SB_ERR_STATE, "NextNode is null: a split node is missing a child (dt/DTWorker.java:1089-1094)");
     for (int k = 0; k < 3; ++k)
         if ((maxbits[k] & 0x7f800000u) == 0x7f800000u) return fail(SB_ERR_RANGE, "non-finite per-row contribution (label, significance or weight)");
+    if ((maxbits[0] >> 23) >= 127 + 38) return fail(SB_ERR_RANGE, "significance * weight beyond 2^38");
     out->train_count = acc[0];
     out->validation_count = acc[1];
     out->train_error = acc[2];

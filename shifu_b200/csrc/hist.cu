@@ -5,20 +5,26 @@
 //
 // Shape of the kernel (DESIGN.md section 4 has the measurements behind each choice):
 //   * one block = (row chunk) x (tile of 32 feature slots) x (group of GS todo-node slots);
-//   * column tiles  [32 features][T_ROWS bins]  are staged into shared memory by the TMA engine
-//     (cp.async.bulk, one 1-D bulk copy per feature column, completion on an mbarrier), NST stages deep;
-//   * LANE == FEATURE: the 32 lanes of a warp work on the same row and on 32 different features, and the
-//     privatised histogram is laid out [slot][bin][word][lane], so every shared-memory atomic of a warp
-//     instruction hits 32 different banks and 32 different addresses -- no bank conflict and no
-//     same-address serialisation can happen inside a warp (this is what warp-aggregation would buy,
-//     without its __match_any cost);
+//   * warp-specialised: 4 PRODUCER warps turn per-row scalars into fixed-point operands and drive the TMA engine
+//     (cp.async.bulk.tensor.2d: ONE box of [32 features][128 rows] bytes per stage from the column-major bin
+//     matrix, 128-byte swizzled, completion on an mbarrier -- 32 separate 128-byte bulk copies per tile measured
+//     ~3.5x slower end to end); 16 CONSUMER warps do the shared-memory atomics.  NST stages, full/empty
+//     mbarriers, no block-wide barrier inside the row loop;
+//   * LANE == FEATURE: the 32 lanes of a consumer warp work on the same row and on 32 different features, and
+//     the privatised histogram is laid out [slot][bin][word][lane], so every shared-memory atomic of a warp
+//     instruction hits 32 different banks and 32 different addresses -- no bank conflict and no same-address
+//     serialisation can happen inside a warp (what warp-aggregation would buy, without its __match_any cost);
 //   * per-record contributions are the reference's fp32 products, converted to 64-bit fixed point
 //     (q = rint(v * 2^e), |q| < 2^39) and added with native 32-bit ATOMS.ADD + carry: shared-memory
-//     fp32/fp64/u64 atomicAdd compile to CAS loops on sm_100a and measured 6-10x slower (tools/ubench_smem.cu);
+//     fp32/fp64/u64 atomicAdd compile to CAS loops on sm_100a and measured 6-10x slower (tools/ubench_smem.cu).
+//     When every sig*weight product of the pass is a small integer (the default: no weight column, 0/1 bagging
+//     mask, Poisson bag counts) the count statistic is a single 32-bit add;
 //   * at the end of its row chunk a block merges its privatised histogram into the global accumulators
 //     (int64 lo/hi pairs, RED.ADD.64): integer addition is associative, so the merged result does not depend
 //     on block order, launch geometry or the number of GPUs; the conversion to the reference's fp64
 //     statistics happens once, in finalize_stats_kernel, with a single rounding per statistic.
+#include <cuda.h>  // CUtensorMap (type only; the encoder is fetched through cudaGetDriverEntryPoint in api.cu)
+
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -26,21 +32,48 @@ namespace sb {
 
 namespace {
 
-constexpr int T_ROWS = HIST_T_ROWS;      // rows per tile
-constexpr int NST = HIST_STAGES;         // TMA stages
-constexpr int NTHREADS = HIST_THREADS;   // 16 warps
-constexpr int NWARPS = NTHREADS / 32;
-constexpr int ROWS_PER_WARP = T_ROWS / NWARPS;  // 8
-constexpr int TILE_PITCH = T_ROWS + 16;  // bytes; pitch % 128 == 16 makes the per-lane 8/16-byte reads conflict-free
+constexpr int T_ROWS = HIST_T_ROWS;             // rows per tile
+constexpr int NST = HIST_STAGES;                // pipeline stages
+constexpr int N_PROD_WARPS = T_ROWS / 32;       // one producer thread per tile row
+constexpr int N_CONS_WARPS = 16;
+constexpr int NTHREADS = (N_PROD_WARPS + N_CONS_WARPS) * 32;
+constexpr int ROWS_PER_WARP = T_ROWS / N_CONS_WARPS;  // 8
+constexpr int TILE_BYTES = 32 * T_ROWS;         // one TMA box: 32 feature rows of 128 bytes, SWIZZLE_128B
+static_assert(T_ROWS == 128, "the TMA box is 128 bytes wide (the 128-byte swizzle span)");
+constexpr int SLOT_TABLE_SMEM = 512;            // heap ids below this are mapped to slots from shared memory
+static_assert(N_PROD_WARPS == 4 && N_CONS_WARPS == 16, "match[] packs 4 consumer warps per producer warp");
 static_assert(ROWS_PER_WARP == 8, "the consumer loop reads 8 bins per lane (one LDS.64)");
+static_assert(HIST_THREADS == NTHREADS, "kernels.cuh and hist.cu disagree on the block size");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// 32-bit shared-window addressing for the hot loop: ATOMS with an immediate offset, no 64-bit pointer math.
+template <int OFF>
+__device__ __forceinline__ void sred_add(uint32_t addr, uint32_t v) {
+    asm volatile("red.shared.add.u32 [%0+%1], %2;" ::"r"(addr), "n"(OFF), "r"(v) : "memory");
+}
+// hi + carry(old_lo + lo): kept as an opaque carry chain so the compiler cannot pull part of it next to the atomic
+// that produced old_lo (that would stall the warp on the ATOMS return once per row).
+__device__ __forceinline__ uint32_t hi_plus_carry(uint32_t old_lo, uint32_t lo, uint32_t hi) {
+    uint32_t r;
+    asm volatile("{\n.reg .u32 t;\nadd.cc.u32 t, %1, %2;\naddc.u32 %0, %3, 0;\n}" : "=r"(r) : "r"(old_lo), "r"(lo), "r"(hi));
+    return r;
+}
+template <int OFF>
+__device__ __forceinline__ uint32_t satom_add(uint32_t addr, uint32_t v) {
+    uint32_t old;
+    asm volatile("atom.shared.add.u32 %0, [%1+%2], %3;" : "=r"(old) : "r"(addr), "n"(OFF), "r"(v) : "memory");
+    return old;
+}
 
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     asm volatile(
@@ -55,40 +88,56 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "r"(parity)
         : "memory");
 }
-// TMA 1-D bulk copy global -> shared, completion signalled on the mbarrier (SASS: UBLKCP).
-__device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     smem_u32(smem_dst)),
-                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
+// TMA 2-D tiled copy global -> shared, completion signalled on the mbarrier (SASS: UTMALDG).
+// c0 = first row of the box (inner, contiguous dimension), c1 = first feature slot.  Out-of-range parts of
+// the box (tail rows, feature slots >= F) are zero-filled by the hardware.
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, int32_t c0, int32_t c1, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+        : "memory");
 }
 
-// 64-bit two's complement add into a (lo, hi) pair of shared words, lane-strided by 32 words.
-__device__ __forceinline__ void smem_add64(uint32_t* lo_word, uint32_t lo, uint32_t hi) {
-    uint32_t old = atomicAdd(lo_word, lo);
-    uint32_t carry = (uint32_t)((old + lo) < old);
-    atomicAdd(lo_word + 32, hi + carry);
-}
-
-struct __align__(16) RowVals {  // what every lane needs to know about one row (read as two broadcast LDS.128)
-    int32_t slot;        // local slot in this block's group, or -1: skip the row
-    uint32_t fmask;      // bit l set: feature l of the tile is in this node's feature list
-    uint32_t q[6];       // VARIANCE: (cnt_lo, cnt_hi, sum_lo, sum_hi, sq_lo, sq_hi); CLASS: (lo, hi, class, -, -, -)
+struct __align__(16) RowVals {  // what every consumer lane needs to know about one row (two broadcast LDS.128)
+    uint32_t slot_off;   // byte offset of the row's slot inside the block's histogram (CLASS: + the class words)
+    uint32_t fmask;      // bit l set: feature l of the tile takes this row; 0 = skip the row
+    uint32_t q[6];       // VARIANCE: (cnt_lo, cnt_hi, sum_lo, sum_hi, sq_lo, sq_hi); CLASS: (lo, hi, -, -, -, -)
 };
+
+struct Stage {
+    uint64_t tile_full;   // TMA bytes of the stage have landed
+    uint64_t vals_full;   // the producers wrote every RowVals of the stage
+    uint64_t empty;       // every consumer warp is done with the stage
+    uint8_t match[N_PROD_WARPS];  // match[p] bit k: consumer warp 4p+k has at least one row to process
+    uint8_t pad[8 - N_PROD_WARPS];
+};
+
+constexpr size_t CTRL_BYTES = 128 * ((sizeof(Stage) * NST + 127) / 128);
+constexpr size_t SMEM_FIXED = (size_t)NST * TILE_BYTES                   // bin tiles (first: 1024-byte aligned)
+                              + CTRL_BYTES                              // stage control
+                              + SLOT_TABLE_SMEM * sizeof(int16_t)       // slot table
+                              + (size_t)NST * T_ROWS * sizeof(RowVals); // row operands
 
 }  // namespace
 
-template <int KIND>
-__global__ void __launch_bounds__(NTHREADS, 1) hist_kernel(const HistArgs a) {
-    extern __shared__ __align__(128) unsigned char smem[];
-    constexpr int NW = (KIND == STAT_VARIANCE) ? 6 : 0;  // words per bin for VARIANCE; CLASS uses 2*C at run time
-    const int nw = (KIND == STAT_VARIANCE) ? NW : 2 * a.stats_size;
+// words per bin of the privatised histogram
+__host__ __device__ inline int hist_words(int kind, int cnt_int, int stats_size) {
+    if (kind == STAT_VARIANCE) return cnt_int ? 5 : 6;
+    return cnt_int ? stats_size : 2 * stats_size;
+}
+
+template <int KIND, int CNT_INT>
+__global__ void __launch_bounds__(NTHREADS, 1) hist_kernel(const HistArgs a, const __grid_constant__ CUtensorMap tmap) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int nw = hist_words(KIND, CNT_INT, a.stats_size);
 
     // ---- carve shared memory
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem);                         // NST barriers
-    unsigned char* tiles = smem + 128;                                           // NST * 32 * TILE_PITCH
-    RowVals* vals = reinterpret_cast<RowVals*>(tiles + NST * 32 * TILE_PITCH);   // 2 * T_ROWS
-    uint32_t* hist = reinterpret_cast<uint32_t*>(vals + 2 * T_ROWS);             // gs * bins_pad * nw * 32 words
+    unsigned char* tiles = smem;  // the 128-byte swizzle pattern repeats every 1024 bytes: keep tiles 1024-aligned
+    Stage* stages = reinterpret_cast<Stage*>(smem + (size_t)NST * TILE_BYTES);
+    int16_t* slot_tab = reinterpret_cast<int16_t*>(smem + (size_t)NST * TILE_BYTES + CTRL_BYTES);
+    RowVals* vals = reinterpret_cast<RowVals*>(slot_tab + SLOT_TABLE_SMEM);
+    uint32_t* hist = reinterpret_cast<uint32_t*>(vals + NST * T_ROWS);
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
@@ -103,162 +152,246 @@ __global__ void __launch_bounds__(NTHREADS, 1) hist_kernel(const HistArgs a) {
     const int64_t row_begin = (int64_t)chunk * a.rows_per_chunk;
     const int64_t row_end = min(a.n_rows, row_begin + a.rows_per_chunk);
     const int n_tile_iters = (int)((row_end - row_begin + T_ROWS - 1) / T_ROWS);
-
-    const int my_feat = a.tile_feats[tile_id * 32 + lane];  // -1: padding lane
-    const int my_bins = my_feat >= 0 ? a.feat_bins[my_feat] : 0;
-    const unsigned char* my_col = my_feat >= 0 ? static_cast<const unsigned char*>(a.cols[my_feat]) : nullptr;
     const int bins_pad = a.bins_pad;
-    const int hist_words = gcount * bins_pad * nw * 32;
+    const int hist_words_total = gcount * bins_pad * nw * 32;
 
-    for (int i = threadIdx.x; i < hist_words; i += NTHREADS) hist[i] = 0u;
+    for (int i = threadIdx.x; i < hist_words_total; i += NTHREADS) hist[i] = 0u;
+    const int tab_n = min(a.slot_table_size, SLOT_TABLE_SMEM);
+    for (int i = threadIdx.x; i < SLOT_TABLE_SMEM; i += NTHREADS) slot_tab[i] = i < tab_n ? a.slot_of_node[i] : (int16_t)-1;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < NST; ++s) mbar_init(&bars[s], 1);
+        for (int s = 0; s < NST; ++s) {
+            mbar_init(&stages[s].tile_full, 1);
+            mbar_init(&stages[s].vals_full, N_PROD_WARPS * 32);
+            mbar_init(&stages[s].empty, N_CONS_WARPS);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
 
-    const float sc0 = a.scales[0], sc1 = a.scales[1], sc2 = a.scales[2];
+    if (warp < N_PROD_WARPS) {
+        // =========================================================== producers
+        const int tid = threadIdx.x;  // row of the tile
+        const float sc0 = a.scales[0], sc1 = a.scales[1], sc2 = a.scales[2];
 
-    auto issue_tile = [&](int it) {  // called by warp 0 only
-        const int stage = it % NST;
-        const int64_t r0 = row_begin + (int64_t)it * T_ROWS;
-        const int rows = (int)min((int64_t)T_ROWS, row_end - r0);
-        const uint32_t bytes = (uint32_t)((rows + 15) & ~15);
-        const unsigned valid = __ballot_sync(0xffffffffu, my_feat >= 0);
-        if (lane == 0) mbar_expect_tx(&bars[stage], bytes * __popc(valid));
-        __syncwarp();
-        if (my_feat >= 0) tma_load_1d(tiles + (stage * 32 + lane) * TILE_PITCH, my_col + r0, bytes, &bars[stage]);
-    };
-
-    if (warp == 0)
-        for (int it = 0; it < NST - 1 && it < n_tile_iters; ++it) issue_tile(it);
-
-    for (int it = 0; it < n_tile_iters; ++it) {
-        const int stage = it % NST;
-        const int64_t r0 = row_begin + (int64_t)it * T_ROWS;
-        const int rows = (int)min((int64_t)T_ROWS, row_end - r0);
-        RowVals* v = vals + (it & 1) * T_ROWS;
-
-        // ---- per-row values: one thread per row of the tile (dt/Impurity.java:239-241: fp32 products, left to right)
-        if (threadIdx.x < T_ROWS) {
+        // software prefetch of the next tile's per-row scalars
+        int nid = 0;
+        float w = 0.f, sig = 0.f, y = 0.f;
+        auto prefetch = [&](int it) {
+            const int64_t r = row_begin + (int64_t)it * T_ROWS + tid;
+            if (it < n_tile_iters && r < row_end) {
+                nid = a.node_id[r];
+                w = a.weights ? a.weights[r] : 1.0f;
+                sig = a.significance[r];
+                y = a.output[r];
+            } else {
+                nid = -1;
+                w = 0.f;
+            }
+        };
+        prefetch(0);
+        for (int it = 0; it < n_tile_iters; ++it) {
+            const int s = it % NST;
+            Stage& st = stages[s];
+            if (it >= NST) mbar_wait(&st.empty, (uint32_t)(((it / NST) - 1) & 1));
+            const int64_t r0 = row_begin + (int64_t)it * T_ROWS;
+            if (threadIdx.x == 0) {  // one TMA box per stage: 32 consecutive feature slots x rows [r0, r0+128)
+                mbar_expect_tx(&st.tile_full, TILE_BYTES);
+                tma_load_2d(tiles + s * TILE_BYTES, &tmap, (int32_t)r0, a.tile_slot0[tile_id], &st.tile_full);
+            }
+            // ---- this thread's row: the reference's fp32 products (dt/Impurity.java:239-241), then fixed point
+            const int cur_nid = nid;
+            const float cw_ = w, csig = sig, cy = y;
+            prefetch(it + 1);
             RowVals rv;
-            rv.slot = -1;
+            rv.slot_off = 0;
             rv.fmask = 0;
 #pragma unroll
             for (int k = 0; k < 6; ++k) rv.q[k] = 0;
-            if (threadIdx.x < rows) {
-                const int64_t r = r0 + threadIdx.x;
-                const int nid = a.node_id[r];
-                int s = (nid >= 0 && nid < a.slot_table_size) ? (int)a.slot_of_node[nid] : -1;
-                const float w = a.weights ? a.weights[r] : 1.0f;
-                if (s >= g0 && s < g0 + gcount && w != 0.0f) {
-                    const float sig = a.significance[r];
-                    const float y = a.output[r];
-                    rv.slot = s - g0;
-                    rv.fmask = a.slot_fmask[(size_t)s * a.n_tiles + tile_id];
-                    const float cw = __fmul_rn(sig, w);
-                    const long long qc = __float2ll_rn(__fmul_rn(cw, sc0));
+            int sl = -1;
+            if (cur_nid >= 0) {
+                if (cur_nid < SLOT_TABLE_SMEM) sl = slot_tab[cur_nid];
+                else if (cur_nid < a.slot_table_size) sl = a.slot_of_node[cur_nid];
+            }
+            if (sl >= g0 && sl < g0 + gcount && cw_ != 0.0f) {
+                rv.slot_off = (uint32_t)((sl - g0) * bins_pad * nw * 128);
+                rv.fmask = a.slot_fmask[(size_t)sl * a.n_tiles + tile_id];
+                const float cw = __fmul_rn(csig, cw_);
+                long long qc;
+                if (CNT_INT) qc = (long long)__float2int_rn(cw);  // exact: the host verified sig*w is a small integer
+                else qc = __float2ll_rn(__fmul_rn(cw, sc0));
+                if (KIND == STAT_VARIANCE) {
+                    const float sw = __fmul_rn(__fmul_rn(cy, csig), cw_);
+                    const float qw = __fmul_rn(__fmul_rn(__fmul_rn(cy, cy), csig), cw_);
+                    const long long qs = __float2ll_rn(__fmul_rn(sw, sc1));
+                    const long long qq = __float2ll_rn(__fmul_rn(qw, sc2));
+                    rv.q[0] = (uint32_t)qc; rv.q[1] = (uint32_t)(qc >> 32);
+                    rv.q[2] = (uint32_t)qs; rv.q[3] = (uint32_t)(qs >> 32);
+                    rv.q[4] = (uint32_t)qq; rv.q[5] = (uint32_t)(qq >> 32);
+                } else {
+                    const int cls = (int)(__fadd_rn(cy, 0.000001f));  // dt/Impurity.java:539,721
+                    rv.q[0] = (uint32_t)qc; rv.q[1] = (uint32_t)(qc >> 32);
+                    if (cls < 0 || cls >= a.stats_size) { rv.fmask = 0; atomicOr(a.error_flag, 1u); }
+                    else rv.slot_off += (uint32_t)(cls * (CNT_INT ? 128 : 256));
+                }
+            }
+            vals[s * T_ROWS + tid] = rv;
+            // which consumer warps have work: consumer warp c owns rows [8c, 8c+8)
+            const unsigned hit = __ballot_sync(0xffffffffu, rv.fmask != 0u);
+            if (lane == 0) {
+                uint32_t m = 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if ((hit >> (8 * k)) & 0xffu) m |= 1u << k;
+                st.match[warp] = (uint8_t)m;
+            }
+            mbar_arrive(&st.vals_full);
+        }
+    } else {
+        // =========================================================== consumers
+        const int cw = warp - N_PROD_WARPS;
+        const int wr0 = cw * ROWS_PER_WARP;
+        const uint32_t lane_bit = 1u << lane;
+        const uint32_t lane_base = smem_u32(hist) + (uint32_t)lane * 4u;
+        const uint32_t bin_stride = (uint32_t)nw * 128u;
+        for (int it = 0; it < n_tile_iters; ++it) {
+            const int s = it % NST;
+            Stage& st = stages[s];
+            const uint32_t parity = (uint32_t)((it / NST) & 1);
+            mbar_wait(&st.vals_full, parity);
+            if ((st.match[cw >> 2] >> (cw & 3)) & 1u) {
+                mbar_wait(&st.tile_full, parity);
+                const RowVals* v = vals + s * T_ROWS + wr0;
+                // row `lane` of the box; its 16-byte chunk c is stored at chunk (c ^ (lane & 7))  [SWIZZLE_128B]
+                const uint2 packed = *reinterpret_cast<const uint2*>(
+                    tiles + s * TILE_BYTES + lane * T_ROWS + ((((cw >> 1) ^ (lane & 7)) << 4) | ((cw & 1) << 3)));
+                // Two phases so that the 8 rows' returning atomics are all in flight before any carry is needed
+                // (one row at a time the loop is bound by the ATOMS return latency, not by its throughput).
+                // Bin indices were validated against n_bins when the rows were loaded (check_bins_kernel).
+                uint32_t ad[ROWS_PER_WARP];
+                uint32_t lo0[ROWS_PER_WARP], lo1[ROWS_PER_WARP], lo2[ROWS_PER_WARP];  // low words added
+                uint32_t hi0[ROWS_PER_WARP], hi1[ROWS_PER_WARP], hi2[ROWS_PER_WARP];  // high words to add
+                uint32_t o0[ROWS_PER_WARP], o1[ROWS_PER_WARP], o2[ROWS_PER_WARP];     // returned old low words
+                bool ok[ROWS_PER_WARP];
+#pragma unroll
+                for (int j = 0; j < ROWS_PER_WARP; ++j) {
+                    const uint4 v0 = *reinterpret_cast<const uint4*>(&v[j]);  // slot_off, fmask, q0, q1
+                    const uint32_t word = (j < 4) ? packed.x : packed.y;
+                    const uint32_t bin = (word >> ((j & 3) * 8)) & 0xffu;
+                    ok[j] = (v0.y & lane_bit) != 0u;
+                    ad[j] = lane_base + v0.x + bin * bin_stride;
+                    lo0[j] = v0.z; hi0[j] = v0.w;
+                    lo1[j] = hi1[j] = lo2[j] = hi2[j] = 0;
+                    o0[j] = o1[j] = o2[j] = 0;
                     if (KIND == STAT_VARIANCE) {
-                        const float sw = __fmul_rn(__fmul_rn(y, sig), w);
-                        const float qw = __fmul_rn(__fmul_rn(__fmul_rn(y, y), sig), w);
-                        const long long qs = __float2ll_rn(__fmul_rn(sw, sc1));
-                        const long long qq = __float2ll_rn(__fmul_rn(qw, sc2));
-                        rv.q[0] = (uint32_t)qc; rv.q[1] = (uint32_t)(qc >> 32);
-                        rv.q[2] = (uint32_t)qs; rv.q[3] = (uint32_t)(qs >> 32);
-                        rv.q[4] = (uint32_t)qq; rv.q[5] = (uint32_t)(qq >> 32);
-                    } else {
-                        const int cls = (int)(__fadd_rn(y, 0.000001f));  // dt/Impurity.java:539,721
-                        rv.q[0] = (uint32_t)qc; rv.q[1] = (uint32_t)(qc >> 32);
-                        rv.q[2] = (uint32_t)cls;
-                        if (cls < 0 || cls >= a.stats_size) { rv.slot = -1; atomicOr(a.error_flag, 1u); }
+                        const uint4 v1 = *reinterpret_cast<const uint4*>(&v[j].q[2]);  // q2..q5
+                        lo1[j] = v1.x; hi1[j] = v1.y; lo2[j] = v1.z; hi2[j] = v1.w;
+                    }
+                    if (ok[j]) {
+                        if (KIND == STAT_VARIANCE) {
+                            if (CNT_INT) {
+                                sred_add<0>(ad[j], lo0[j]);
+                                o1[j] = satom_add<128>(ad[j], lo1[j]);
+                                o2[j] = satom_add<384>(ad[j], lo2[j]);
+                            } else {
+                                o0[j] = satom_add<0>(ad[j], lo0[j]);
+                                o1[j] = satom_add<256>(ad[j], lo1[j]);
+                                o2[j] = satom_add<512>(ad[j], lo2[j]);
+                            }
+                        } else {
+                            if (CNT_INT) sred_add<0>(ad[j], lo0[j]);
+                            else o0[j] = satom_add<0>(ad[j], lo0[j]);
+                        }
                     }
                 }
-            }
-            v[threadIdx.x] = rv;
-        }
-        __syncthreads();  // vals visible; every warp is done with tile it-1, so its stage may be refilled
-
-        if (warp == 0 && it + NST - 1 < n_tile_iters) issue_tile(it + NST - 1);
-
-        mbar_wait(&bars[stage], (uint32_t)((it / NST) & 1));
-
-        // ---- consume: warp w owns rows [w*8, w*8+8) of the tile; lane == feature
-        const int wr0 = warp * ROWS_PER_WARP;
-        if (wr0 < rows) {
-            const uint2 packed = *reinterpret_cast<const uint2*>(tiles + (stage * 32 + lane) * TILE_PITCH + wr0);
 #pragma unroll
-            for (int j = 0; j < ROWS_PER_WARP; ++j) {
-                const uint4 v0 = *reinterpret_cast<const uint4*>(&v[wr0 + j]);           // slot, fmask, q0, q1
-                if ((int)v0.x < 0) continue;                                              // warp-uniform
-                const uint4 v1 = *reinterpret_cast<const uint4*>(&v[wr0 + j].q[2]);       // q2..q5
-                const uint32_t word = (j < 4) ? packed.x : packed.y;
-                const int bin = (int)((word >> ((j & 3) * 8)) & 0xffu);
-                if (!((v0.y >> lane) & 1u)) continue;
-                if (bin >= my_bins) { atomicOr(a.error_flag, 2u); continue; }
-                if (KIND == STAT_VARIANCE) {
-                    uint32_t* p = hist + (((int)v0.x * bins_pad + bin) * NW) * 32 + lane;
-                    smem_add64(p, v0.z, v0.w);
-                    smem_add64(p + 64, v1.x, v1.y);
-                    smem_add64(p + 128, v1.z, v1.w);
-                } else {
-                    uint32_t* p = hist + (((int)v0.x * bins_pad + bin) * nw + 2 * (int)v1.x) * 32 + lane;
-                    smem_add64(p, v0.z, v0.w);
+                for (int j = 0; j < ROWS_PER_WARP; ++j) {
+                    if (!ok[j]) continue;
+                    if (KIND == STAT_VARIANCE) {
+                        if (CNT_INT) {
+                            sred_add<256>(ad[j], hi_plus_carry(o1[j], lo1[j], hi1[j]));
+                            sred_add<512>(ad[j], hi_plus_carry(o2[j], lo2[j], hi2[j]));
+                        } else {
+                            sred_add<128>(ad[j], hi_plus_carry(o0[j], lo0[j], hi0[j]));
+                            sred_add<384>(ad[j], hi_plus_carry(o1[j], lo1[j], hi1[j]));
+                            sred_add<640>(ad[j], hi_plus_carry(o2[j], lo2[j], hi2[j]));
+                        }
+                    } else if (!CNT_INT) {
+                        sred_add<128>(ad[j], hi_plus_carry(o0[j], lo0[j], hi0[j]));
+                    }
                 }
+            } else {
+                // nothing to do for this warp, but the TMA of the stage must have landed before the stage is reused
+                mbar_wait(&st.tile_full, parity);
             }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&st.empty);
         }
     }
     __syncthreads();
 
     // ---- merge the privatised histogram into the global integer accumulators
-    const int per_slot = bins_pad * (nw / 2) * 32;  // 64-bit statistics per slot
+    const int n_stats = a.stats_size;           // 64-bit statistics per bin
+    const int cnt_shift = CNT_INT ? *a.cnt_shift : 0;
+    const int per_slot = bins_pad * n_stats * 32;
     for (int i = threadIdx.x; i < gcount * per_slot; i += NTHREADS) {
         const int l = i & 31;
         int t = i >> 5;
-        const int st = t % (nw / 2);
-        t /= (nw / 2);
+        const int stt = t % n_stats;
+        t /= n_stats;
         const int bin = t % bins_pad;
         const int sl = t / bins_pad;
-        const uint32_t* p = hist + ((sl * bins_pad + bin) * nw + 2 * st) * 32 + l;
-        const uint32_t lo = p[0], hi = p[32];
-        if ((lo | hi) == 0u) continue;
+        const uint32_t* pb = hist + ((sl * bins_pad + bin) * nw) * 32 + l;
+        long long v;
+        if (KIND == STAT_VARIANCE) {
+            if (CNT_INT) {
+                if (stt == 0) v = (long long)(unsigned long long)pb[0] << cnt_shift;
+                else v = (long long)(((unsigned long long)pb[(2 * stt) * 32] << 32) | pb[(2 * stt - 1) * 32]);
+            } else {
+                v = (long long)(((unsigned long long)pb[(2 * stt + 1) * 32] << 32) | pb[(2 * stt) * 32]);
+            }
+        } else {
+            if (CNT_INT) v = (long long)(unsigned long long)pb[stt * 32] << cnt_shift;
+            else v = (long long)(((unsigned long long)pb[(2 * stt + 1) * 32] << 32) | pb[(2 * stt) * 32]);
+        }
+        if (v == 0) continue;
         const int f = a.tile_feats[tile_id * 32 + l];
         if (f < 0) continue;
         const int64_t off = a.pair_off[(size_t)(g0 + sl) * a.n_features + f];
         if (off < 0) continue;
-        const int64_t idx = off + (int64_t)bin * a.stats_size + st;
-        atomicAdd(reinterpret_cast<unsigned long long*>(a.raw_lo + idx), (unsigned long long)lo);
-        atomicAdd(reinterpret_cast<unsigned long long*>(a.raw_hi + idx), (unsigned long long)(long long)(int32_t)hi);
+        const int64_t idx = off + (int64_t)bin * a.stats_size + stt;
+        // (lo, hi) split: the global sum over all blocks and GPUs may exceed 63 bits, each half cannot
+        atomicAdd(reinterpret_cast<unsigned long long*>(a.raw_lo + idx), (unsigned long long)(v & 0xffffffffLL));
+        atomicAdd(reinterpret_cast<unsigned long long*>(a.raw_hi + idx), (unsigned long long)(v >> 32));
     }
 }
 
-size_t hist_smem_bytes(int gs, int bins_pad, int nw) {
-    return 128 + (size_t)NST * 32 * TILE_PITCH + 2 * T_ROWS * sizeof(RowVals) + (size_t)gs * bins_pad * nw * 32 * 4;
-}
+size_t hist_smem_bytes(int gs, int bins_pad, int nw) { return SMEM_FIXED + (size_t)gs * bins_pad * nw * 32 * 4; }
 
 int hist_max_slots_per_block(int bins_pad, int nw) {
-    const size_t fixed = 128 + (size_t)NST * 32 * TILE_PITCH + 2 * T_ROWS * sizeof(RowVals);
-    const size_t budget = 227 * 1024 - fixed;
+    const size_t budget = 227 * 1024 - SMEM_FIXED;
     return (int)(budget / ((size_t)bins_pad * nw * 32 * 4));
 }
 
-cudaError_t hist_launch(int kind, const HistArgs& a, int grid, size_t smem, cudaStream_t stream) {
-    static bool attr_set[2] = {false, false};
-    if (kind == STAT_VARIANCE) {
-        if (!attr_set[0]) {
-            cudaError_t e = cudaFuncSetAttribute(hist_kernel<STAT_VARIANCE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-            if (e != cudaSuccess) return e;
-            attr_set[0] = true;
-        }
-        hist_kernel<STAT_VARIANCE><<<grid, NTHREADS, smem, stream>>>(a);
-    } else {
-        if (!attr_set[1]) {
-            cudaError_t e = cudaFuncSetAttribute(hist_kernel<STAT_CLASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-            if (e != cudaSuccess) return e;
-            attr_set[1] = true;
-        }
-        hist_kernel<STAT_CLASS><<<grid, NTHREADS, smem, stream>>>(a);
+int hist_words_per_bin(int kind, int cnt_int, int stats_size) { return hist_words(kind, cnt_int, stats_size); }
+
+template <int KIND, int CNT_INT>
+static cudaError_t launch_one(const HistArgs& a, const CUtensorMap& tmap, int grid, size_t smem, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(hist_kernel<KIND, CNT_INT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
     }
+    hist_kernel<KIND, CNT_INT><<<grid, NTHREADS, smem, stream>>>(a, tmap);
     return cudaGetLastError();
+}
+
+cudaError_t hist_launch(int kind, int cnt_int, const HistArgs& a, const void* tensor_map, int grid, size_t smem,
+                        cudaStream_t stream) {
+    const CUtensorMap& tmap = *static_cast<const CUtensorMap*>(tensor_map);
+    if (kind == STAT_VARIANCE)
+        return cnt_int ? launch_one<STAT_VARIANCE, 1>(a, tmap, grid, smem, stream) : launch_one<STAT_VARIANCE, 0>(a, tmap, grid, smem, stream);
+    return cnt_int ? launch_one<STAT_CLASS, 1>(a, tmap, grid, smem, stream) : launch_one<STAT_CLASS, 0>(a, tmap, grid, smem, stream);
 }
 
 }  // namespace sb

@@ -6,10 +6,9 @@ namespace sb {
 
 constexpr int HIST_T_ROWS = 128;
 constexpr int HIST_STAGES = 3;
-constexpr int HIST_THREADS = 512;
+constexpr int HIST_THREADS = 640;  // 4 producer + 16 consumer warps
 
 struct HistArgs {
-    const void* const* cols;     // [F] device column pointers (uint8 bins)
     const int32_t* feat_bins;    // [F] stats bins per feature slot
     const float* output;         // Data.output (the `label` argument of featureUpdate, dt/DTWorker.java:851)
     const float* significance;
@@ -19,13 +18,15 @@ struct HistArgs {
     int slot_table_size;
     int64_t n_rows;
     int n_features;
-    const int32_t* tile_feats;   // [n_tiles][32] feature slots, -1 padded
+    const int32_t* tile_feats;   // [n_tiles][32] feature slot of each lane (tile_slot0 + lane), or -1 if unused
+    const int32_t* tile_slot0;   // [n_tiles] first feature slot of the tile (multiple of 32)
     const uint32_t* slot_fmask;  // [n_slots][n_tiles] bit l: tile feature l is in the slot's feature list
     const int64_t* pair_off;     // [n_slots][F] offset (in statistics) of the (slot, feature) block, -1 if absent
     int n_tiles, n_groups, gs, n_slots, bins_pad;
     int64_t rows_per_chunk;
     int stats_size;              // 3 (variance) or numClasses
     const float* scales;         // [3] 2^e per statistic (count, sum, sum of squares)
+    const int* cnt_shift;        // device: e of the count statistic (integer-count mode shifts by it when merging)
     int64_t* raw_lo;             // global accumulators, one (lo, hi) pair per statistic
     int64_t* raw_hi;
     uint32_t* error_flag;        // bit0: class index out of range, bit1: bin index out of range
@@ -33,7 +34,10 @@ struct HistArgs {
 
 size_t hist_smem_bytes(int gs, int bins_pad, int nw);
 int hist_max_slots_per_block(int bins_pad, int nw);
-cudaError_t hist_launch(int kind, const HistArgs& a, int grid, size_t smem, cudaStream_t stream);
+int hist_words_per_bin(int kind, int cnt_int, int stats_size);
+// tensor_map: a CUtensorMap (128 bytes) over the column-major uint8 bin matrix [F][pitch], box {128 rows, 32 features}
+cudaError_t hist_launch(int kind, int cnt_int, const HistArgs& a, const void* tensor_map, int grid, size_t smem,
+                        cudaStream_t stream);
 
 // ---- rows.cu
 struct TreeView {  // DeviceTree as kernels see it
@@ -76,8 +80,12 @@ cudaError_t launch_errors(const ErrArgs& a, double* scratch /*[ERR_SCRATCH_DOUBL
 // max |sig*w|, |y*sig*w|, |y*y*sig*w| over rows (as fp32 bit patterns, atomicMax) -> out[3]
 cudaError_t launch_absmax(int64_t n, const float* output, const float* significance, const float* weights,
                           uint32_t* out, cudaStream_t s);
-// out[3] (bit patterns of maxima) -> scales[3] = 2^e, inv_scales[3] = 2^-e (doubles)
-cudaError_t launch_make_scales(const uint32_t* maxbits, int kind, float* scales, double* inv_scales, cudaStream_t s);
+// out[3] (bit patterns of maxima) -> scales[3] = 2^e, inv_scales[3] = 2^-e (doubles), cnt_shift = max(e[0], 0)
+cudaError_t launch_make_scales(const uint32_t* maxbits, int kind, float* scales, double* inv_scales, int* cnt_shift,
+                               cudaStream_t s);
+// flag |= 1 unless every sig*w product is an integer in [0, 1024]
+cudaError_t launch_check_int_weights(int64_t n, const float* significance, const float* weights, uint32_t* flag,
+                                     cudaStream_t s);
 cudaError_t launch_synthetic(uint8_t* bins, int64_t pitch, int n_features, const int32_t* feat_bins, float* label,
                              float* significance, int64_t row0, int64_t n, uint64_t seed, int label_kind, int weighted,
                              cudaStream_t s);

@@ -195,7 +195,17 @@ __global__ void __launch_bounds__(TPB) absmax_kernel(int64_t n, const float* __r
     }
 }
 
-__global__ void make_scales_kernel(const uint32_t* maxbits, int kind, float* scales, double* inv_scales) {
+__global__ void check_int_weights_kernel(int64_t n, const float* __restrict__ significance,
+                                         const float* __restrict__ weights, uint32_t* flag) {
+    bool bad = false;
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        const float c = significance[r] * (weights ? weights[r] : 1.0f);
+        bad |= !(c >= 0.0f && c <= 1024.0f && c == truncf(c));
+    }
+    if (bad) atomicOr(flag, 1u);
+}
+
+__global__ void make_scales_kernel(const uint32_t* maxbits, int kind, float* scales, double* inv_scales, int* cnt_shift) {
     const int k = threadIdx.x;
     if (k >= 3) return;
     const float m = __uint_as_float(maxbits[k]);
@@ -208,6 +218,7 @@ __global__ void make_scales_kernel(const uint32_t* maxbits, int kind, float* sca
     if (kind == STAT_CLASS && k > 0) e = 0;
     scales[k] = ldexpf(1.0f, e);
     inv_scales[k] = ldexp(1.0, -e);
+    if (k == 0) *cnt_shift = e > 0 ? e : 0;
 }
 
 // Counter-based generator of SURVEY.md 8(d): every (row, feature) value is a pure function of (seed, row, feature).
@@ -324,8 +335,15 @@ cudaError_t launch_absmax(int64_t n, const float* output, const float* significa
     absmax_kernel<<<grid_for(n, TPB, 148 * 8), TPB, 0, s>>>(n, output, significance, weights, out);
     return cudaGetLastError();
 }
-cudaError_t launch_make_scales(const uint32_t* maxbits, int kind, float* scales, double* inv_scales, cudaStream_t s) {
-    make_scales_kernel<<<1, 32, 0, s>>>(maxbits, kind, scales, inv_scales);
+cudaError_t launch_make_scales(const uint32_t* maxbits, int kind, float* scales, double* inv_scales, int* cnt_shift,
+                               cudaStream_t s) {
+    make_scales_kernel<<<1, 32, 0, s>>>(maxbits, kind, scales, inv_scales, cnt_shift);
+    return cudaGetLastError();
+}
+cudaError_t launch_check_int_weights(int64_t n, const float* significance, const float* weights, uint32_t* flag,
+                                     cudaStream_t s) {
+    if (n <= 0) return cudaSuccess;
+    check_int_weights_kernel<<<grid_for(n, TPB, 148 * 8), TPB, 0, s>>>(n, significance, weights, flag);
     return cudaGetLastError();
 }
 cudaError_t launch_synthetic(uint8_t* bins, int64_t pitch, int n_features, const int32_t* feat_bins, float* label,

@@ -1,0 +1,42 @@
+"""Per-level timing of the histogram kernel on a synthetic GBT workload (developer tool, not the bench)."""
+import argparse
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from shifu_b200.capi import ConfigArrays, Worker  # noqa: E402
+from shifu_b200.dt_master import DTMaster  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--rows", type=int, default=10_000_000)
+ap.add_argument("--features", type=int, default=200)
+ap.add_argument("--bins", type=int, default=64)
+ap.add_argument("--depth", type=int, default=8)
+ap.add_argument("--trees", type=int, default=2)
+ap.add_argument("--weighted", type=int, default=0)
+a = ap.parse_args()
+
+cfg = ConfigArrays([a.bins] * a.features, max_depth=a.depth, tree_num=a.trees, learning_rate=0.05, min_instances_per_node=5)
+w = Worker(cfg)
+t0 = time.time()
+w.load_synthetic(a.rows, seed=1002, weighted=bool(a.weighted))
+print("load_synthetic %.2fs" % (time.time() - t0))
+w.set_profiling(True)
+m = DTMaster(cfg, tree_num=a.trees, max_depth=a.depth, learning_rate=0.05)
+it = m.build_initial_master_params()
+algo_bytes = a.rows * (a.features + 16)
+while it is not None:
+    t0 = time.time()
+    w.compute_begin(it)
+    w.compute_stats()
+    sc = w.compute_finish()
+    gains, bits = w.best_splits(it.n_todo)
+    wall = (time.time() - t0) * 1e3
+    ms, npass, nl = w.hist_time()
+    lvl = max(t[2] for t in [(0, 0, it.todo[i].node_id) for i in range(it.n_todo)]).bit_length()
+    print("tree %d level %d todo %3d  hist %.3f ms  wall %.3f ms  %.1f GB/s (algorithmic)  %.3e cells/s  err=%.6g" % (
+        len(m.trees) - 1, lvl, it.n_todo, ms, wall, algo_bytes / ms / 1e6, a.rows * a.features / ms * 1e3,
+        sc[2] / max(sc[0], 1)))
+    it = m.do_compute(gains, bits)
+w.close()
