@@ -1,0 +1,404 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the GBT statistics-build hot path on B200 (BASELINE.json metric).
+
+Workload (BASELINE.json configs[2], the one the north-star target is quoted on): synthetic 100M rows x 200
+numeric features x 64 bins, GBT, squared loss, depth-8 level-wise trees.  One "step" = one GBT tree =
+the D-1 statistics passes of its levels + routing + residual update + error sums + all-reduce + on-device best
+split, driven by the host DTMaster mirror.  `value` = rows x features x passes / time over all GPUs, with the data
+resident in HBM; `e2e` = the same through sb_compute with HOST in/out buffers (message in, statistics out).
+Rows are sharded contiguously over the GPUs (strong scaling: the 100M rows are fixed); the DTMaster merge is an
+NCCL all-reduce of the integer accumulators.
+
+`--impl reference` times the CPU restatement of the reference path (oracle/, all host threads) on a bounded
+sample of the same workload; the Java original cannot run here (no JVM).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SEED = 1002
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--rows", type=int, default=100_000_000)
+    ap.add_argument("--features", type=int, default=200)
+    ap.add_argument("--bins", type=int, default=64)
+    ap.add_argument("--depth", type=int, default=8)
+    ap.add_argument("--cpu-sample-rows", type=int, default=1_000_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"  # /opt/skills/guides/B200_PROFILING.md
+
+
+class ClockSampler:
+    """nvidia-smi samples of one GPU during the timed region (clocks line of the profiling recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.samples = []
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            parts = [p.strip() for p in s.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+class DevView:
+    """A raw device allocation exposed through __cuda_array_interface__ so torch can wrap it without a copy."""
+
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+def grow_tree(worker, master, it, dist_ctx, e2e_buffers=None):
+    """One GBT tree through the device path; returns (next message, passes, last scalars)."""
+    from shifu_b200 import capi
+    passes = 0
+    tree_index = len(master.trees)
+    scalars = None
+    while it is not None:
+        if e2e_buffers is None and dist_ctx is None:
+            worker.compute_begin(it)
+            worker.compute_stats()
+            scalars = worker.compute_finish()
+        elif dist_ctx is None:
+            # the call a user makes: DTWorker.doCompute with host buffers (message in, statistics out)
+            n = worker.stats_len(it)
+            out = capi.SbIterOut()
+            out.stats = C.cast(e2e_buffers["stats_ptr"], C.POINTER(C.c_double))
+            out.stats_len = e2e_buffers["stats_cap"]
+            assert n <= e2e_buffers["stats_cap"]
+            capi.check(worker.lib, worker.lib.sb_compute(worker.h, C.byref(it.struct), C.byref(out)))
+            e2e_buffers["d2h"] += n * 8 + 32
+            scalars = (out.train_count, out.validation_count, out.train_error, out.validation_error)
+        else:
+            import torch
+            import torch.distributed as dist
+            worker.compute_begin(it)
+            sp, sb, rp, rb, ap_, ab = worker.device_buffers()
+            dist.all_reduce(torch.as_tensor(DevView(sp, 3, "<i4"), device="cuda"), op=dist.ReduceOp.MAX)
+            worker.compute_stats()
+            sp, sb, rp, rb, ap_, ab = worker.device_buffers()
+            if rb > 0:
+                dist.all_reduce(torch.as_tensor(DevView(rp, rb // 8, "<i8"), device="cuda"), op=dist.ReduceOp.SUM)
+            dist.all_reduce(torch.as_tensor(DevView(ap_, 4, "<f8"), device="cuda"), op=dist.ReduceOp.SUM)
+            if e2e_buffers is None:
+                scalars = worker.compute_finish()
+            else:
+                n = worker.stats_len(it)
+                out = capi.SbIterOut()
+                out.stats = C.cast(e2e_buffers["stats_ptr"], C.POINTER(C.c_double))
+                out.stats_len = e2e_buffers["stats_cap"]
+                capi.check(worker.lib, worker.lib.sb_compute_finish(worker.h, C.byref(out)))
+                e2e_buffers["d2h"] += n * 8 + 32
+                scalars = (out.train_count, out.validation_count, out.train_error, out.validation_error)
+        gains, bits = worker.best_splits(it.n_todo)
+        passes += 1
+        it = master.do_compute(gains, bits)
+        if it is None or len(master.trees) != tree_index:
+            break
+    return it, passes, scalars
+
+
+def run_b200(a):
+    import torch
+    from shifu_b200.capi import ConfigArrays, Worker
+    from shifu_b200.dt_master import DTMaster
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dist_ctx = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist_ctx = dist
+    n_gpus = world
+    rows_local = a.rows // world + (1 if rank < a.rows % world else 0)
+    row0 = rank * (a.rows // world) + min(rank, a.rows % world)
+
+    n_trees_total = a.warmup + a.steps + a.steps + 2
+    cfg = ConfigArrays([a.bins] * a.features, max_depth=a.depth, tree_num=n_trees_total, learning_rate=0.05,
+                       min_instances_per_node=5, device=local_rank)
+    worker = Worker(cfg)
+    worker.load_synthetic(rows_local, seed=SEED, row0=row0, label_kind=0)
+    master = DTMaster(cfg, tree_num=n_trees_total, max_depth=a.depth, learning_rate=0.05, worker_number=world)
+    it = master.build_initial_master_params()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist_ctx is not None:
+            dist_ctx.barrier()
+            torch.cuda.synchronize()
+
+    # ---- warm-up trees
+    for _ in range(a.warmup):
+        it, _, _ = grow_tree(worker, master, it, dist_ctx)
+    worker.hist_time()
+    worker.set_profiling(True)
+    l0, h2d0, d2h0 = worker.counters()
+
+    # ---- timed region 1: device-resident
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    passes = 0
+    for _ in range(a.steps):
+        it, p, scalars = grow_tree(worker, master, it, dist_ctx)
+        passes += p
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    l1, h2d1, d2h1 = worker.counters()
+    hist_ms, hist_passes, hist_launches = worker.hist_time()
+    worker.set_profiling(False)
+
+    # ---- timed region 2: end to end through sb_compute with pinned host buffers
+    stats_cap = (1 << (a.depth - 2)) * a.features * a.bins * 3 + 16
+    pinned = torch.empty(stats_cap, dtype=torch.float64, pin_memory=True)
+    e2e_buf = {"stats_ptr": pinned.data_ptr(), "stats_cap": stats_cap, "d2h": 0}
+    _, h2d_a, d2h_a = worker.counters()
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    e2e_passes = 0
+    for _ in range(a.steps):
+        it, p, _ = grow_tree(worker, master, it, dist_ctx, e2e_buffers=e2e_buf)
+        e2e_passes += p
+    f1.record()
+    barrier()
+    ms_e2e = f0.elapsed_time(f1)
+    _, h2d_b, d2h_b = worker.counters()
+
+    if dist_ctx is not None:
+        t = torch.tensor([ms, ms_e2e, hist_ms], dtype=torch.float64, device="cuda")
+        dist_ctx.all_reduce(t, op=dist_ctx.ReduceOp.MAX)
+        ms, ms_e2e, hist_ms = [float(x) for x in t.tolist()]
+
+    if rank != 0:
+        worker.close()
+        if dist_ctx is not None:
+            dist_ctx.destroy_process_group()
+        return
+
+    cells = float(a.rows) * a.features
+    value = cells * passes / (ms * 1e-3)
+    e2e_value = cells * e2e_passes / (ms_e2e * 1e-3)
+    peak, peak_kind = measured_peak_gbs()
+    # algorithmic bytes of one pass on one GPU: every bin index once + per-row output,
+    # significance, sample weight (4 B each) and node id (4 B here: heap ids are kept as int32)
+    algo_bytes = float(rows_local) * (a.features * 1 + 16)
+    avg_hist_ms = hist_ms / max(hist_passes, 1)
+    achieved = algo_bytes / (avg_hist_ms * 1e-3) / 1e9
+    line = {
+        "metric": "binned rows*features/sec histogram build (GBT tree levels, incl. routing, residual update, best split)",
+        "value": value,
+        "unit": "rows*features/s",
+        "n_gpus": n_gpus,
+        "steps": a.steps,
+        "warmup": a.warmup,
+        "ms_per_step": ms / a.steps,
+        "sec_per_tree": ms / a.steps / 1e3,
+        "higher_is_better": True,
+        "scaling": "strong",
+        "vs_baseline": None,
+        "dtype": "u8 bins -> i64 fixed-point accumulators -> f64 statistics",
+        "data": "synthetic",
+        "config": {"workload": "C2: synthetic %d rows x %d features x %d bins, GBT squared loss depth %d (level-wise, %d stats passes/tree)"
+                               % (a.rows, a.features, a.bins, a.depth, passes // max(a.steps, 1)),
+                   "parallelism": "rows sharded over %d GPU(s); integer all-reduce of node stats" % n_gpus,
+                   "cache": "inputs (%.1f GB/GPU) far larger than L2; no flush needed" % (rows_local * (a.features + 24) / 1e9),
+                   "seed": SEED},
+        "passes_per_step": passes / max(a.steps, 1),
+        "hist_ms_per_pass": avg_hist_ms,
+        "hist_share_of_step": hist_ms / ms,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "peak_source": peak_kind,
+                     "algorithmic_bytes_per_launch": algo_bytes,
+                     "note": "average over the passes of the timed trees (levels 1..%d); see DESIGN.md for the shared-memory atomic ceiling" % (a.depth - 1)},
+        "e2e": {"value": e2e_value, "unit": "rows*features/s",
+                "h2d_bytes_per_step": (h2d_b - h2d_a) / max(a.steps, 1),
+                "d2h_bytes_per_step": (d2h_b - d2h_a) / max(a.steps, 1),
+                "ms_per_step": ms_e2e / a.steps},
+        "gpu_launches": int(l1 - l0),
+        "clocks": clocks,
+        "train_error_last": (scalars[2] / scalars[0]) if scalars and scalars[0] else None,
+    }
+    if n_gpus == 1 and not a.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(a, a.cpu_sample_rows, steps=1)
+    worker.close()
+    if dist_ctx is not None:
+        dist_ctx.destroy_process_group()
+    print(json.dumps(line))
+
+
+def oracle_tree(orc, cfg, max_depth, tree_index, prev_root, threads):
+    """One level-wise GBT tree grown with oracle calls only (DTWorker.doCompute + DTMaster best split restated)."""
+    from shifu_b200.messages import IterIn, Node
+    root = Node(1)
+    todo_nodes = [root]
+    switch = True
+    passes = 0
+    while todo_nodes:
+        todo = [(k, tree_index, nd.id, []) for k, nd in enumerate(todo_nodes)]
+        sent = [(tree_index - 1, prev_root), (tree_index, root)] if (switch and prev_root is not None) else [(tree_index, root)]
+        it = IterIn(cfg, sent, todo, switch_to_next_tree=switch,
+                    is_first_tree=(tree_index == 0) or (switch and tree_index == 1))
+        res = orc.compute(it, n_threads=threads)
+        gains, _ = orc.best_splits(it, res[4])
+        passes += 1
+        nxt = []
+        for k, nd in enumerate(todo_nodes):
+            g = gains[k]
+            if not g.found:
+                continue
+            level = int(nd.id).bit_length()
+            nd.predict = g.predict
+            if g.gain <= 0 or level == max_depth:
+                continue
+            nd.feature, nd.split_type = g.feature, g.split_type
+            nd.threshold = float(cfg.boundaries_of(g.feature)[g.split_bin + 1])
+            nd.left, nd.right = Node(2 * nd.id, g.left_predict), Node(2 * nd.id + 1, g.right_predict)
+            if level + 1 != max_depth:
+                if not (g.left_impurity == 0.0 and not np.signbit(g.left_impurity)):
+                    nxt.append(nd.left)
+                if not (g.right_impurity == 0.0 and not np.signbit(g.right_impurity)):
+                    nxt.append(nd.right)
+        todo_nodes = nxt
+        switch = False
+    return root, passes
+
+
+def cpu_baseline(a, sample_rows, steps=1, warmup=0):
+    """The reference path restated on the CPU (oracle/), all host threads, on a bounded sample of the workload."""
+    from oracle.pyoracle import OracleWorker
+    from shifu_b200 import synthetic
+    from shifu_b200.capi import ConfigArrays
+    cores = os.cpu_count() or 1
+    cfg = ConfigArrays([a.bins] * a.features, max_depth=a.depth, tree_num=steps + warmup + 1, learning_rate=0.05,
+                       min_instances_per_node=5)
+    cols, y, sig = synthetic.make(SEED, [a.bins] * a.features, 0, sample_rows)
+    orc = OracleWorker(cfg)
+    orc.load_rows(cols, y, sig, None)
+    prev = None
+    t_idx = 0
+    for _ in range(warmup):
+        prev, _ = oracle_tree(orc, cfg, a.depth, t_idx, prev, cores)
+        t_idx += 1
+    t0 = time.perf_counter()
+    passes = 0
+    for _ in range(steps):
+        prev, p = oracle_tree(orc, cfg, a.depth, t_idx, prev, cores)
+        passes += p
+        t_idx += 1
+    dt = time.perf_counter() - t0
+    orc.close()
+    return {"value": float(sample_rows) * a.features * passes / dt, "unit": "rows*features/s", "cores": cores,
+            "kind": "port",
+            "sample": "%d rows x %d features x %d bins of the same generator, %d GBT tree(s) of depth %d (%d passes), "
+                      "C++ restatement of DTWorker.doCompute with workerThreadCount=%d (phase A single-threaded as in the reference); "
+                      "the Java original cannot run here (no JVM)" % (sample_rows, a.features, a.bins, steps, a.depth, passes, cores),
+            "seconds": dt, "ms_per_step": dt * 1e3 / max(steps, 1)}
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    base = cpu_baseline(a, a.cpu_sample_rows, steps=a.steps, warmup=min(a.warmup, 1))
+    line = {
+        "impl": "reference",
+        "metric": "binned rows*features/sec histogram build (GBT tree levels, incl. routing, residual update, best split)",
+        "value": base["value"],
+        "unit": "rows*features/s",
+        "n_gpus": a.gpus,
+        "steps": a.steps,
+        "warmup": min(a.warmup, 1),
+        "ms_per_step": base["ms_per_step"],
+        "higher_is_better": True,
+        "scaling": "strong",
+        "vs_baseline": None,
+        "dtype": "i16 bins -> f64 statistics (CPU)",
+        "data": "synthetic",
+        "config": {"workload": "C2 sample: %d of %d rows x %d features x %d bins, GBT squared loss depth %d"
+                               % (a.cpu_sample_rows, a.rows, a.features, a.bins, a.depth), "seed": SEED},
+        "cpu_baseline": base,
+        "e2e": {"value": base["value"], "unit": "rows*features/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
