@@ -262,6 +262,23 @@ SB_API int sb_set_stream(sb_handle* h, void* cuda_stream);
  */
 SB_API int sb_best_splits(sb_handle* h, sb_gain* gains, uint8_t* cat_bits);
 
+/*
+ * No counterpart in the reference.  Weighted error sums of a row set -- out[0] = sum(significance),
+ * out[1] = sum(significance * Loss.computeError(predict, label)), the two numbers a GBT iteration reports as
+ * trainCount / trainError -- for callers that must not allocate device memory: a monitoring thread next to a
+ * running trainer (cudaMalloc / cudaFree would stall the training stream), or a process whose HBM is already
+ * fully committed.  The reduction scratch is a static 64 KB device array inside the library, so no handle is
+ * needed and nothing is allocated or freed, ever.
+ *   - at most SB_STATIC_MAX_ROWS rows per call (more => SB_ERR_RANGE);
+ *   - label / predict / significance (NULL = all 1f) / out are device pointers on the CURRENT device; out holds
+ *     2 doubles and is valid once `cuda_stream` (NULL = default stream) has reached this call;
+ *   - the first call on a device looks up the scratch address; make it before any stream capture on that device;
+ *   - all calls on a device share the scratch and must not overlap on the GPU (they would race).
+ */
+#define SB_STATIC_MAX_ROWS 67108864LL
+SB_API int sb_error_sums_static(const float* label, const float* predict, const float* significance, int64_t n_rows,
+                                int32_t loss, double* out, void* cuda_stream);
+
 /* ------------------------------------------------------------------ pieces of the path (bench / tests) */
 
 /* Re-runs only the statistics pass (phase B) of the last sb_compute_begin, n_repeat times, and reports the

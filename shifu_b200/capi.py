@@ -16,6 +16,7 @@ SB_LOSS_SQUARED, SB_LOSS_HALFGRADSQUARED, SB_LOSS_ABSOLUTE, SB_LOSS_LOG = 0, 1, 
 SB_SPLIT_CONTINUOUS, SB_SPLIT_CATEGORICAL = 1, 2
 SB_ROOT_INDEX, SB_INVALID_INDEX = 1, -1
 SB_MAX_CAT_BYTES = 4096
+SB_STATIC_MAX_ROWS = 67108864
 
 
 class SbConfig(C.Structure):
@@ -133,6 +134,7 @@ EXPORTS = [
     "sb_stats_len", "sb_compute", "sb_compute_begin", "sb_scale_buffer", "sb_compute_stats", "sb_raw_buffer",
     "sb_acc_buffer", "sb_compute_finish", "sb_set_stream", "sb_best_splits", "sb_time_stats_pass", "sb_counters",
     "sb_load_synthetic", "sb_read_bins", "sb_read_labels", "sb_set_profiling", "sb_hist_time",
+    "sb_error_sums_static",
 ]
 
 _lib = None
@@ -176,6 +178,7 @@ def load_library(path=None):
     lib.sb_read_labels.argtypes = [H, C.c_int32, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
     lib.sb_set_profiling.argtypes = [H, C.c_int32]
     lib.sb_hist_time.argtypes = [H, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    lib.sb_error_sums_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]
     if path is None:
         _lib = lib
     return lib
