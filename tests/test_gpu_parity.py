@@ -187,3 +187,92 @@ def test_bin_out_of_range_is_rejected():
         w.load_rows([np.array([1, 9], np.uint8), np.array([0, 0], np.uint8)], np.zeros(2, np.float32))
     assert e.value.code == -4
     w.close()
+
+
+def run_rf(n, n_bins, seed, n_trees=4, max_depth=4, impurity=capi.SB_IMPURITY_GINI, num_classes=2, weighted=False,
+           is_categorical=None, feature_subsets=True, oracle_threads=3):
+    """RF: all trees advance together, Poisson bag counts per (row, tree), per-node feature subsets, OOB error."""
+    from oracle.pyoracle import OracleWorker
+    cfg = ConfigArrays(n_bins, is_categorical=is_categorical, impurity=impurity, num_classes=num_classes,
+                       loss=capi.SB_LOSS_SQUARED, is_gbdt=False, tree_num=n_trees, weights_per_row=n_trees,
+                       max_depth=max_depth, min_instances_per_node=1)
+    cols, y, sig, w = make_data(n, n_bins, seed, weighted=weighted, wpr=n_trees, poisson=True)
+    if num_classes > 2:
+        rng0 = np.random.default_rng(seed + 3)
+        y = ((y + rng0.integers(0, num_classes, n)) % num_classes).astype(np.float32)
+    dev, orc = Worker(cfg), OracleWorker(cfg)
+    dev.load_rows(cols, y, sig, w)
+    orc.load_rows(cols, y, sig, w)
+    vcols, vy, vsig, _ = make_data(max(n // 4, 1), n_bins, seed + 9, weighted=weighted)
+    dev.load_rows(vcols, vy, vsig, None, is_validation=True)
+    orc.load_rows(vcols, vy, vsig, None, is_validation=True)
+    has_cat = is_categorical is not None and any(is_categorical)
+    rng = np.random.default_rng(seed + 1)
+    F = len(n_bins)
+    roots = [Node(1) for _ in range(n_trees)]
+    todo_nodes = [(t, roots[t]) for t in range(n_trees)]
+    n_iter = 0
+    while todo_nodes:
+        todo = []
+        for k, (t, nd) in enumerate(todo_nodes):
+            feats = []
+            if feature_subsets:
+                feats = rng.choice(F, size=max(1, (2 * F) // 3), replace=False).tolist()
+            todo.append((k, t, nd.id, feats))
+        it = IterIn(cfg, [(t, roots[t]) for t in range(n_trees)], todo)
+        d = dev.compute(it)
+        o = orc.compute(it, n_threads=oracle_threads)
+        n_iter += 1
+        for a, b in zip(d[:4], o[:4]):
+            assert abs(a - b) <= 1e-9 * abs(b) + 1e-12, (d[:4], o[:4])
+        scale = (float(np.sum(np.abs((1.0 if sig is None else sig) * w.max(axis=0)))),) * 3
+        assert_stats_close(cfg, it, d[4], o[4], scale, exact_counts=not weighted)
+        gd, bits_d = dev.best_splits(len(todo), with_cat=has_cat)
+        go, bits_o = orc.best_splits(it, o[4], with_cat=has_cat)
+        nxt = []
+        for k, (t, nd) in enumerate(todo_nodes):
+            assert_gain_equal(gd[k], go[k], bits_d, bits_o, k)
+            g = gd[k]
+            if not g.found:
+                continue
+            level = index_to_level(nd.id)
+            nd.predict = g.predict
+            if g.gain <= 0 or level == max_depth:
+                continue
+            left, right = apply_gain(cfg, nd, g, bits_d, k)
+            if not (level + 1 == max_depth or is_pos_zero(g.left_impurity)):
+                nxt.append((t, left))
+            if not (level + 1 == max_depth or is_pos_zero(g.right_impurity)):
+                nxt.append((t, right))
+        todo_nodes = nxt
+    dev.close()
+    orc.close()
+    return n_iter
+
+
+def test_rf_gini_poisson_bags():
+    assert run_rf(12000, [32] * 40, seed=21, n_trees=4, max_depth=5) >= 4
+
+
+def test_rf_entropy_weighted_multiclass():
+    run_rf(9000, [16] * 20 + [8] * 5, seed=22, n_trees=3, max_depth=4, impurity=capi.SB_IMPURITY_ENTROPY,
+           num_classes=3, weighted=True)
+
+
+def test_rf_gini_categorical():
+    run_rf(8000, [32] * 5 + [13, 41, 7], seed=23, n_trees=3, max_depth=4,
+           is_categorical=[0] * 5 + [1, 1, 1], feature_subsets=False)
+
+
+def test_synthetic_generator_matches_host_twin():
+    from shifu_b200 import synthetic
+    n_bins = [64, 32, 7, 200]
+    cfg = ConfigArrays(n_bins)
+    w = Worker(cfg)
+    w.load_synthetic(10000, seed=77, row0=12345)
+    cols, y, sig = synthetic.make(77, n_bins, 12345, 10000)
+    for f in range(4):
+        assert np.array_equal(w.read_bins(f, 0, 10000), cols[f])
+    lab, s = w.read_labels(0, 10000)
+    assert np.mean(lab != y) < 1e-3 and np.array_equal(s, sig)
+    w.close()
