@@ -47,6 +47,10 @@ struct HistLaunch {
     HistArgs args;
     int grid;
     size_t smem;
+    // row-list path (more todo nodes than one slot group): lists are rebuilt before the kernel, every pass
+    bool use_rows = false;
+    RowListArgs list{};
+    HistRowsArgs rows{};
 };
 
 }  // namespace sb
@@ -96,6 +100,14 @@ struct sb_handle {
     double* d_inv_scales = nullptr;   // 3
     uint32_t* d_error_flag = nullptr;
     int* d_cnt_shift = nullptr;
+    // row-list path buffers
+    DevBuf<uint8_t> rl_keys;      // [2n]
+    DevBuf<uint32_t> rl_vals;     // [2n]
+    DevBuf<uint8_t> rl_temp;
+    DevBuf<int64_t> rl_tables;    // offsets[257] + chunk_begin[max] + chunk_end[max]
+    DevBuf<int32_t> rl_chunk_group;  // [max] + n_chunks scalar at the end
+    DevBuf<RowOps> rl_ops;        // [n]
+    bool enable_row_lists = true;
     bool cnt_int = false;  // every sig*weight product of the training rows is an integer in [0, 1024]
 
     int64_t launches_count = 0, h2d_bytes = 0, d2h_bytes = 0;
@@ -121,6 +133,7 @@ void free_rowset(RowSet& r) {
     if (r.output) cudaFree(r.output);
     if (r.predict) cudaFree(r.predict);
     if (r.node_id) cudaFree(r.node_id);
+    if (r.bins_rm) cudaFree(r.bins_rm);
     r = RowSet();
 }
 
@@ -431,6 +444,51 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         a.n_tiles = n_tiles;
         a.gs = std::min(ns, max_gs);
         a.n_groups = (ns + a.gs - 1) / a.gs;
+        if (a.n_groups > 1 && h->enable_row_lists && n < (int64_t)0xffffffff) {
+            // more todo nodes than one block can hold: group the rows by slot group and walk the lists instead
+            const int rgs = std::min(ns, hist_rows_max_slots_per_block(bins_pad, nw));
+            const int rgroups = (ns + rgs - 1) / rgs;
+            if (rgs >= 1 && rgroups <= 254) {
+                RowSet& tr = h->train;
+                if (!tr.bins_rm) {  // row-major twin of the bin matrix, built once
+                    tr.fpad = ((F + 31) / 32) * 32;
+                    SB_CUDA(cudaMalloc(&tr.bins_rm, (size_t)std::max<int64_t>(n, 1) * tr.fpad));
+                    SB_CUDA(launch_transpose_bins(static_cast<const uint8_t*>(tr.bins_base), tr.pitch, F, n, tr.bins_rm, tr.fpad, h->stream));
+                    h->launches_count += 1;
+                }
+                const int64_t want_chunks = std::max<int64_t>(1, (148 * 3 + n_tiles - 1) / n_tiles);
+                int64_t chunk_rows = ((n + want_chunks - 1) / want_chunks + 127) / 128 * 128;
+                chunk_rows = std::max<int64_t>(chunk_rows, 1024);
+                chunk_rows = std::min<int64_t>(chunk_rows, cnt_int ? MAX_ROWS_PER_FLUSH / 2 : MAX_ROWS_PER_FLUSH);
+                const int max_chunks = (int)(n / chunk_rows + rgroups + 1);
+                SB_CUDA(h->rl_keys.reserve((size_t)2 * n));
+                SB_CUDA(h->rl_vals.reserve((size_t)2 * n));
+                const size_t temp_bytes = rowlist_sort_temp_bytes(n);
+                SB_CUDA(h->rl_temp.reserve(temp_bytes + 16));
+                SB_CUDA(h->rl_tables.reserve((size_t)257 + 2 * (size_t)max_chunks));
+                SB_CUDA(h->rl_chunk_group.reserve((size_t)max_chunks + 1));
+                SB_CUDA(h->rl_ops.reserve((size_t)n));
+                L.use_rows = true;
+                RowListArgs& la = L.list;
+                la.n = n; la.node_id = a.node_id; la.output = a.output; la.significance = a.significance; la.weights = a.weights;
+                la.slot_of_node = a.slot_of_node; la.slot_table_size = a.slot_table_size; la.gs = rgs; la.n_groups = rgroups;
+                la.stats_size = h->stats_size; la.kind = h->stat_kind; la.cnt_int = cnt_int; la.scales = h->d_scales;
+                la.keys_in = h->rl_keys.p; la.keys_out = h->rl_keys.p + n; la.vals_in = h->rl_vals.p; la.vals_out = h->rl_vals.p + n;
+                la.temp = h->rl_temp.p; la.temp_bytes = temp_bytes; la.chunk_rows = chunk_rows;
+                la.offsets = h->rl_tables.p; la.chunk_begin = h->rl_tables.p + 257; la.chunk_end = h->rl_tables.p + 257 + max_chunks;
+                la.chunk_group = h->rl_chunk_group.p; la.n_chunks = h->rl_chunk_group.p + max_chunks; la.max_chunks = max_chunks;
+                la.ops = h->rl_ops.p; la.error_flag = h->d_error_flag;
+                HistRowsArgs& ra = L.rows;
+                ra.rm_bins = tr.bins_rm; ra.fpad = tr.fpad; ra.ops = la.ops; ra.chunk_group = la.chunk_group;
+                ra.chunk_begin = la.chunk_begin; ra.chunk_end = la.chunk_end; ra.n_chunks = la.n_chunks;
+                ra.tile_feats = h->tile_feats.p; ra.tile_slot0 = h->tile_feats.p + (size_t)n_tiles * 32;
+                ra.slot_fmask = a.slot_fmask; ra.pair_off = a.pair_off; ra.n_tiles = n_tiles; ra.gs = rgs; ra.n_slots = ns;
+                ra.bins_pad = bins_pad; ra.n_features = F; ra.stats_size = h->stats_size; ra.cnt_shift = h->d_cnt_shift;
+                ra.raw_lo = h->raw.p; ra.raw_hi = h->raw.p + lay.total;
+                L.grid = max_chunks * n_tiles;
+                L.smem = hist_rows_smem_bytes(rgs, bins_pad, nw);
+            }
+        }
         a.n_slots = ns;
         a.bins_pad = bins_pad;
         const int64_t tiles_rows = (n + HIST_T_ROWS - 1) / HIST_T_ROWS;
@@ -446,10 +504,12 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         a.raw_lo = h->raw.p;
         a.raw_hi = h->raw.p + lay.total;
         a.error_flag = h->d_error_flag;
-        const int64_t grid = n_chunks * n_tiles * a.n_groups;
-        if (grid > 0x7fffffff) return fail(SB_ERR_UNSUPPORTED, "histogram grid too large");
-        L.grid = (int)grid;
-        L.smem = hist_smem_bytes(a.gs, bins_pad, nw);
+        if (!L.use_rows) {
+            const int64_t grid = n_chunks * n_tiles * a.n_groups;
+            if (grid > 0x7fffffff) return fail(SB_ERR_UNSUPPORTED, "histogram grid too large");
+            L.grid = (int)grid;
+            L.smem = hist_smem_bytes(a.gs, bins_pad, nw);
+        }
         h->launches.push_back(L);
         toff += (size_t)table_size[t];
     }
@@ -509,8 +569,14 @@ int plan_split_tasks(sb_handle* h) {
 
 int run_histograms(sb_handle* h) {
     for (const HistLaunch& L : h->launches) {
-        SB_CUDA(hist_launch(L.kind, L.cnt_int, L.args, h->train.tensor_map, L.grid, L.smem, h->stream));
-        h->launches_count += 1;
+        if (L.use_rows) {
+            SB_CUDA(launch_rowlist_build(L.list, h->stream));
+            SB_CUDA(hist_rows_launch(L.kind, L.cnt_int, L.rows, L.grid, L.smem, h->stream));
+            h->launches_count += 6;  // keys, radix sort (2 kernels), chunk table, operands, histogram
+        } else {
+            SB_CUDA(hist_launch(L.kind, L.cnt_int, L.args, h->train.tensor_map, L.grid, L.smem, h->stream));
+            h->launches_count += 1;
+        }
     }
     return SB_OK;
 }
@@ -562,6 +628,7 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
     }
     if (cfg->bin_boundary) h->bin_boundary.assign(cfg->bin_boundary, cfg->bin_boundary + nb);
     h->cfg.n_bins = nullptr; h->cfg.is_categorical = nullptr; h->cfg.column_num = nullptr; h->cfg.bin_boundary = nullptr;
+    h->enable_row_lists = (cfg->flags & SB_FLAG_NO_ROW_LISTS) == 0;
     h->stats_size = is_variance(cfg->impurity) ? 3 : cfg->num_classes;
     h->stat_kind = is_variance(cfg->impurity) ? STAT_VARIANCE : STAT_CLASS;
     SB_CUDA(cudaMalloc(&h->d_feat_bins, sizeof(int32_t) * cfg->n_features));
@@ -591,6 +658,7 @@ SB_API void sb_destroy(sb_handle* h) {
     h->slot_of_node.release(); h->tasks.release(); h->node_task_begin.release(); h->cand.release(); h->gain_out.release();
     h->cand_bits.release(); h->out_bits.release(); h->new_dropout.release(); h->new_weights.release();
     h->sort_keys.release(); h->sort_idx.release(); h->sort_tmp.release(); h->sort_flags.release();
+    h->rl_keys.release(); h->rl_vals.release(); h->rl_temp.release(); h->rl_tables.release(); h->rl_chunk_group.release(); h->rl_ops.release();
     if (h->d_feat_bins) cudaFree(h->d_feat_bins);
     if (h->d_acc) cudaFree(h->d_acc);
     if (h->d_err_scratch) cudaFree(h->d_err_scratch);

@@ -46,6 +46,8 @@ struct RowSet {
     int n_node_arrays = 0;
     bool owns_inputs = false;
     void* owned_bins = nullptr;
+    uint8_t* bins_rm = nullptr;       // row-major twin [n][fpad] for the row-list path (built on first use)
+    int fpad = 0;
     const void* bins_base = nullptr;  // column-major uint8 bin matrix: feature f starts at bins_base + f * pitch
     int64_t pitch = 0;
     alignas(64) unsigned char tensor_map[128];  // CUtensorMap over the bin matrix (see hist.cu)

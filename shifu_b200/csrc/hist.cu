@@ -88,6 +88,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "r"(parity)
         : "memory");
 }
+// TMA 1-D bulk copy global -> shared, completion signalled on the mbarrier (SASS: UBLKCP).
+__device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 // TMA 2-D tiled copy global -> shared, completion signalled on the mbarrier (SASS: UTMALDG).
 // c0 = first row of the box (inner, contiguous dimension), c1 = first feature slot.  Out-of-range parts of
 // the box (tail rows, feature slots >= F) are zero-filled by the hardware.
@@ -125,6 +132,44 @@ constexpr size_t SMEM_FIXED = (size_t)NST * TILE_BYTES                   // bin 
 __host__ __device__ inline int hist_words(int kind, int cnt_int, int stats_size) {
     if (kind == STAT_VARIANCE) return cnt_int ? 5 : 6;
     return cnt_int ? stats_size : 2 * stats_size;
+}
+
+// Merge a block's privatised histogram into the global integer accumulators.  (lo, hi) split: the global sum over
+// all blocks and GPUs may exceed 63 bits, each half cannot.
+template <int KIND, int CNT_INT>
+__device__ __forceinline__ void flush_hist(const uint32_t* hist, int gcount, int g0, int bins_pad, int nw, int n_stats,
+                                           int cnt_shift, const int32_t* tile_feats, const int64_t* pair_off,
+                                           int n_features, int64_t* raw_lo, int64_t* raw_hi, int nthreads) {
+    const int per_slot = bins_pad * n_stats * 32;  // 64-bit statistics per slot
+    for (int i = threadIdx.x; i < gcount * per_slot; i += nthreads) {
+        const int l = i & 31;
+        int t = i >> 5;
+        const int stt = t % n_stats;
+        t /= n_stats;
+        const int bin = t % bins_pad;
+        const int sl = t / bins_pad;
+        const uint32_t* pb = hist + ((sl * bins_pad + bin) * nw) * 32 + l;
+        long long v;
+        if (KIND == STAT_VARIANCE) {
+            if (CNT_INT) {
+                if (stt == 0) v = (long long)((unsigned long long)pb[0] << cnt_shift);
+                else v = (long long)(((unsigned long long)pb[(2 * stt) * 32] << 32) | pb[(2 * stt - 1) * 32]);
+            } else {
+                v = (long long)(((unsigned long long)pb[(2 * stt + 1) * 32] << 32) | pb[(2 * stt) * 32]);
+            }
+        } else {
+            if (CNT_INT) v = (long long)((unsigned long long)pb[stt * 32] << cnt_shift);
+            else v = (long long)(((unsigned long long)pb[(2 * stt + 1) * 32] << 32) | pb[(2 * stt) * 32]);
+        }
+        if (v == 0) continue;
+        const int f = tile_feats[l];
+        if (f < 0) continue;
+        const int64_t off = pair_off[(size_t)(g0 + sl) * n_features + f];
+        if (off < 0) continue;
+        const int64_t idx = off + (int64_t)bin * n_stats + stt;
+        atomicAdd(reinterpret_cast<unsigned long long*>(raw_lo + idx), (unsigned long long)(v & 0xffffffffLL));
+        atomicAdd(reinterpret_cast<unsigned long long*>(raw_hi + idx), (unsigned long long)(v >> 32));
+    }
 }
 
 template <int KIND, int CNT_INT>
@@ -329,40 +374,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) hist_kernel(const HistArgs a, con
     }
     __syncthreads();
 
-    // ---- merge the privatised histogram into the global integer accumulators
-    const int n_stats = a.stats_size;           // 64-bit statistics per bin
-    const int cnt_shift = CNT_INT ? *a.cnt_shift : 0;
-    const int per_slot = bins_pad * n_stats * 32;
-    for (int i = threadIdx.x; i < gcount * per_slot; i += NTHREADS) {
-        const int l = i & 31;
-        int t = i >> 5;
-        const int stt = t % n_stats;
-        t /= n_stats;
-        const int bin = t % bins_pad;
-        const int sl = t / bins_pad;
-        const uint32_t* pb = hist + ((sl * bins_pad + bin) * nw) * 32 + l;
-        long long v;
-        if (KIND == STAT_VARIANCE) {
-            if (CNT_INT) {
-                if (stt == 0) v = (long long)(unsigned long long)pb[0] << cnt_shift;
-                else v = (long long)(((unsigned long long)pb[(2 * stt) * 32] << 32) | pb[(2 * stt - 1) * 32]);
-            } else {
-                v = (long long)(((unsigned long long)pb[(2 * stt + 1) * 32] << 32) | pb[(2 * stt) * 32]);
-            }
-        } else {
-            if (CNT_INT) v = (long long)(unsigned long long)pb[stt * 32] << cnt_shift;
-            else v = (long long)(((unsigned long long)pb[(2 * stt + 1) * 32] << 32) | pb[(2 * stt) * 32]);
-        }
-        if (v == 0) continue;
-        const int f = a.tile_feats[tile_id * 32 + l];
-        if (f < 0) continue;
-        const int64_t off = a.pair_off[(size_t)(g0 + sl) * a.n_features + f];
-        if (off < 0) continue;
-        const int64_t idx = off + (int64_t)bin * a.stats_size + stt;
-        // (lo, hi) split: the global sum over all blocks and GPUs may exceed 63 bits, each half cannot
-        atomicAdd(reinterpret_cast<unsigned long long*>(a.raw_lo + idx), (unsigned long long)(v & 0xffffffffLL));
-        atomicAdd(reinterpret_cast<unsigned long long*>(a.raw_hi + idx), (unsigned long long)(v >> 32));
-    }
+    flush_hist<KIND, CNT_INT>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0, a.tile_feats + tile_id * 32,
+                              a.pair_off, a.n_features, a.raw_lo, a.raw_hi, NTHREADS);
 }
 
 size_t hist_smem_bytes(int gs, int bins_pad, int nw) { return SMEM_FIXED + (size_t)gs * bins_pad * nw * 32 * 4; }
@@ -392,6 +405,173 @@ cudaError_t hist_launch(int kind, int cnt_int, const HistArgs& a, const void* te
     if (kind == STAT_VARIANCE)
         return cnt_int ? launch_one<STAT_VARIANCE, 1>(a, tmap, grid, smem, stream) : launch_one<STAT_VARIANCE, 0>(a, tmap, grid, smem, stream);
     return cnt_int ? launch_one<STAT_CLASS, 1>(a, tmap, grid, smem, stream) : launch_one<STAT_CLASS, 0>(a, tmap, grid, smem, stream);
+}
+
+
+// =====================================================================================================================
+// hist_rows_kernel: the same accumulation driven by a per-group row list (rowlist.cu).  A block takes one chunk of one
+// slot group's list and one tile of 32 feature slots.  One producer warp streams the RowOps of the chunk into shared
+// memory with TMA 1-D bulk copies (4 KB per stage); 16 consumer warps read, per row, the 32 bins of the tile from the
+// row-major bin copy with ONE coalesced 32-byte load (lane == feature), then issue the same two-phase atomics.
+namespace {
+constexpr int R_NST = 4;
+constexpr int R_CONS_WARPS = 16;
+constexpr int R_NTHREADS = (1 + R_CONS_WARPS) * 32;
+constexpr int R_TILE = 128;                       // rows per stage
+constexpr int R_ROWS_PER_WARP = R_TILE / R_CONS_WARPS;
+constexpr size_t R_SMEM_FIXED = (size_t)R_NST * R_TILE * sizeof(RowOps) + 128 /* barriers */ + 64 /* fmask table */;
+struct RStage { uint64_t full, empty; };
+}  // namespace
+
+template <int KIND, int CNT_INT>
+__global__ void __launch_bounds__(R_NTHREADS, 1) hist_rows_kernel(const HistRowsArgs a) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int ci = blockIdx.x / a.n_tiles;
+    const int tile_id = blockIdx.x - ci * a.n_tiles;
+    if (ci >= *a.n_chunks) return;  // the grid is an upper bound; uniform for the block
+    const int nw = hist_words(KIND, CNT_INT, a.stats_size);
+    RowOps* ops_s = reinterpret_cast<RowOps*>(smem);
+    RStage* st = reinterpret_cast<RStage*>(smem + (size_t)R_NST * R_TILE * sizeof(RowOps));
+    uint32_t* fm_tab = reinterpret_cast<uint32_t*>(smem + (size_t)R_NST * R_TILE * sizeof(RowOps) + 128);
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem + R_SMEM_FIXED);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int group = a.chunk_group[ci];
+    const int64_t begin = a.chunk_begin[ci], end = a.chunk_end[ci];
+    const int g0 = group * a.gs;
+    const int gcount = min(a.gs, a.n_slots - g0);
+    const int bins_pad = a.bins_pad;
+    const int n_iters = (int)((end - begin + R_TILE - 1) / R_TILE);
+
+    for (int i = threadIdx.x; i < gcount * bins_pad * nw * 32; i += R_NTHREADS) hist[i] = 0u;
+    if (threadIdx.x < 16) fm_tab[threadIdx.x] = threadIdx.x < gcount ? a.slot_fmask[(size_t)(g0 + threadIdx.x) * a.n_tiles + tile_id] : 0u;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < R_NST; ++s) {
+            mbar_init(&st[s].full, 1);
+            mbar_init(&st[s].empty, R_CONS_WARPS);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int it = 0; it < n_iters; ++it) {
+                const int s = it % R_NST;
+                if (it >= R_NST) mbar_wait(&st[s].empty, (uint32_t)(((it / R_NST) - 1) & 1));
+                const int64_t r0 = begin + (int64_t)it * R_TILE;
+                const uint32_t bytes = (uint32_t)(min((int64_t)R_TILE, end - r0) * (int64_t)sizeof(RowOps));
+                mbar_expect_tx(&st[s].full, bytes);
+                tma_load_1d(ops_s + s * R_TILE, a.ops + r0, bytes, &st[s].full);
+            }
+        }
+    } else {
+        const int cw = warp - 1;
+        const int wr0 = cw * R_ROWS_PER_WARP;
+        const uint32_t lane_bit = 1u << lane;
+        const uint32_t lane_base = smem_u32(hist) + (uint32_t)lane * 4u;
+        const uint32_t bin_stride = (uint32_t)nw * 128u;
+        const uint32_t slot_stride = (uint32_t)bins_pad * bin_stride;
+        const uint8_t* my_bins = a.rm_bins + a.tile_slot0[tile_id] + lane;
+        for (int it = 0; it < n_iters; ++it) {
+            const int s = it % R_NST;
+            mbar_wait(&st[s].full, (uint32_t)((it / R_NST) & 1));
+            const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
+            if (wr0 < rows) {
+                const RowOps* v = ops_s + s * R_TILE + wr0;
+                uint4 v0[R_ROWS_PER_WARP];
+                uint32_t bin[R_ROWS_PER_WARP];
+                bool ok[R_ROWS_PER_WARP];
+#pragma unroll
+                for (int j = 0; j < R_ROWS_PER_WARP; ++j) {  // phase 0: operands + the row's 32 bins (one 32-byte load per warp)
+                    ok[j] = wr0 + j < rows;
+                    v0[j] = make_uint4(0u, 0xffffffffu, 0u, 0u);
+                    bin[j] = 0;
+                    if (ok[j]) {
+                        v0[j] = *reinterpret_cast<const uint4*>(&v[j]);  // row, slot, q0, q1
+                        bin[j] = __ldg(my_bins + (size_t)v0[j].x * a.fpad);
+                    }
+                }
+                uint32_t ad[R_ROWS_PER_WARP];
+                uint32_t lo0[R_ROWS_PER_WARP], lo1[R_ROWS_PER_WARP], lo2[R_ROWS_PER_WARP];
+                uint32_t hi0[R_ROWS_PER_WARP], hi1[R_ROWS_PER_WARP], hi2[R_ROWS_PER_WARP];
+                uint32_t o0[R_ROWS_PER_WARP], o1[R_ROWS_PER_WARP], o2[R_ROWS_PER_WARP];
+#pragma unroll
+                for (int j = 0; j < R_ROWS_PER_WARP; ++j) {  // phase 1
+                    const uint32_t slot = v0[j].y;
+                    ok[j] = ok[j] && slot < (uint32_t)gcount && (fm_tab[slot & 15u] & lane_bit) != 0u;
+                    ad[j] = lane_base + slot * slot_stride + bin[j] * bin_stride;
+                    lo0[j] = v0[j].z; hi0[j] = v0[j].w;
+                    lo1[j] = hi1[j] = lo2[j] = hi2[j] = 0;
+                    o0[j] = o1[j] = o2[j] = 0;
+                    const uint4 v1 = *reinterpret_cast<const uint4*>(&v[j].q[2]);
+                    if (KIND == STAT_VARIANCE) { lo1[j] = v1.x; hi1[j] = v1.y; lo2[j] = v1.z; hi2[j] = v1.w; }
+                    else ad[j] += v1.x;  // class words
+                    if (ok[j]) {
+                        if (KIND == STAT_VARIANCE) {
+                            if (CNT_INT) {
+                                sred_add<0>(ad[j], lo0[j]);
+                                o1[j] = satom_add<128>(ad[j], lo1[j]);
+                                o2[j] = satom_add<384>(ad[j], lo2[j]);
+                            } else {
+                                o0[j] = satom_add<0>(ad[j], lo0[j]);
+                                o1[j] = satom_add<256>(ad[j], lo1[j]);
+                                o2[j] = satom_add<512>(ad[j], lo2[j]);
+                            }
+                        } else {
+                            if (CNT_INT) sred_add<0>(ad[j], lo0[j]);
+                            else o0[j] = satom_add<0>(ad[j], lo0[j]);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < R_ROWS_PER_WARP; ++j) {  // phase 2: carries
+                    if (!ok[j]) continue;
+                    if (KIND == STAT_VARIANCE) {
+                        if (CNT_INT) {
+                            sred_add<256>(ad[j], hi_plus_carry(o1[j], lo1[j], hi1[j]));
+                            sred_add<512>(ad[j], hi_plus_carry(o2[j], lo2[j], hi2[j]));
+                        } else {
+                            sred_add<128>(ad[j], hi_plus_carry(o0[j], lo0[j], hi0[j]));
+                            sred_add<384>(ad[j], hi_plus_carry(o1[j], lo1[j], hi1[j]));
+                            sred_add<640>(ad[j], hi_plus_carry(o2[j], lo2[j], hi2[j]));
+                        }
+                    } else if (!CNT_INT) {
+                        sred_add<128>(ad[j], hi_plus_carry(o0[j], lo0[j], hi0[j]));
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&st[s].empty);
+        }
+    }
+    __syncthreads();
+    flush_hist<KIND, CNT_INT>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0, a.tile_feats + tile_id * 32,
+                              a.pair_off, a.n_features, a.raw_lo, a.raw_hi, R_NTHREADS);
+}
+
+size_t hist_rows_smem_bytes(int gs, int bins_pad, int nw) { return R_SMEM_FIXED + (size_t)gs * bins_pad * nw * 32 * 4; }
+int hist_rows_max_slots_per_block(int bins_pad, int nw) {
+    const size_t budget = 227 * 1024 - R_SMEM_FIXED;
+    int gs = (int)(budget / ((size_t)bins_pad * nw * 32 * 4));
+    return gs > 16 ? 16 : gs;  // fm_tab holds 16 masks
+}
+
+template <int KIND, int CNT_INT>
+static cudaError_t launch_rows_one(const HistRowsArgs& a, int grid, size_t smem, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(hist_rows_kernel<KIND, CNT_INT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    hist_rows_kernel<KIND, CNT_INT><<<grid, R_NTHREADS, smem, stream>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t hist_rows_launch(int kind, int cnt_int, const HistRowsArgs& a, int grid, size_t smem, cudaStream_t stream) {
+    if (kind == STAT_VARIANCE) return cnt_int ? launch_rows_one<STAT_VARIANCE, 1>(a, grid, smem, stream) : launch_rows_one<STAT_VARIANCE, 0>(a, grid, smem, stream);
+    return cnt_int ? launch_rows_one<STAT_CLASS, 1>(a, grid, smem, stream) : launch_rows_one<STAT_CLASS, 0>(a, grid, smem, stream);
 }
 
 }  // namespace sb

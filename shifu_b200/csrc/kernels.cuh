@@ -32,6 +32,60 @@ struct HistArgs {
     uint32_t* error_flag;        // bit0: class index out of range, bit1: bin index out of range
 };
 
+// ---- row-list path (rowlist.cu + hist_rows_kernel in hist.cu): passes with more todo nodes than one slot group
+struct __align__(16) RowOps {   // one active row of the pass, in slot-group order
+    uint32_t row;               // row index (ascending inside a group)
+    uint32_t slot;              // slot inside its group, 0..gs-1
+    uint32_t q[6];              // VARIANCE: (cnt_lo, cnt_hi, sum_lo, sum_hi, sq_lo, sq_hi); CLASS: (lo, hi, class byte offset, -, -, -)
+};
+struct RowListArgs {
+    int64_t n;
+    const int32_t* node_id;
+    const float* output;
+    const float* significance;
+    const float* weights;
+    const int16_t* slot_of_node;
+    int slot_table_size, gs, n_groups, stats_size, kind, cnt_int;
+    const float* scales;
+    uint8_t *keys_in, *keys_out;
+    uint32_t *vals_in, *vals_out;
+    void* temp;
+    size_t temp_bytes;
+    int64_t chunk_rows;
+    int64_t* offsets;          // [n_groups + 1]
+    int32_t* chunk_group;      // [max_chunks]
+    int64_t* chunk_begin;
+    int64_t* chunk_end;
+    int32_t* n_chunks;         // device scalar
+    int max_chunks;
+    RowOps* ops;               // [n]
+    uint32_t* error_flag;
+};
+cudaError_t launch_transpose_bins(const uint8_t* cm, int64_t pitch, int n_features, int64_t n, uint8_t* rm, int fpad,
+                                  cudaStream_t s);
+size_t rowlist_sort_temp_bytes(int64_t n);
+cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s);
+struct HistRowsArgs {
+    const uint8_t* rm_bins;      // row-major bins [n][fpad]
+    int fpad;
+    const RowOps* ops;
+    const int32_t* chunk_group;
+    const int64_t* chunk_begin;
+    const int64_t* chunk_end;
+    const int32_t* n_chunks;
+    const int32_t* tile_feats;   // as HistArgs
+    const int32_t* tile_slot0;
+    const uint32_t* slot_fmask;  // [n_slots][n_tiles]
+    const int64_t* pair_off;     // [n_slots][F]
+    int n_tiles, gs, n_slots, bins_pad, n_features, stats_size;
+    const int* cnt_shift;
+    int64_t* raw_lo;
+    int64_t* raw_hi;
+};
+cudaError_t hist_rows_launch(int kind, int cnt_int, const HistRowsArgs& a, int grid, size_t smem, cudaStream_t stream);
+size_t hist_rows_smem_bytes(int gs, int bins_pad, int nw);
+int hist_rows_max_slots_per_block(int bins_pad, int nw);
+
 size_t hist_smem_bytes(int gs, int bins_pad, int nw);
 int hist_max_slots_per_block(int bins_pad, int nw);
 int hist_words_per_bin(int kind, int cnt_int, int stats_size);

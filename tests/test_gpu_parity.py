@@ -59,11 +59,11 @@ def assert_gain_equal(gd, go, bits_d=None, bits_o=None, idx=0):
 
 def run_gbt(n, n_bins, seed, n_trees=2, max_depth=4, weighted=False, loss=capi.SB_LOSS_SQUARED, label="binary",
             is_categorical=None, feature_subsets=False, with_validation=True, bagging=False, min_inst=1,
-            oracle_threads=3):
+            oracle_threads=3, flags=0):
     from oracle.pyoracle import OracleWorker
     cfg = ConfigArrays(n_bins, is_categorical=is_categorical, loss=loss, is_gbdt=True, tree_num=n_trees,
                        max_depth=max_depth, min_instances_per_node=min_inst, learning_rate=0.1,
-                       column_num=np.arange(len(n_bins)) + 3)
+                       column_num=np.arange(len(n_bins)) + 3, flags=flags)
     cols, y, sig, _ = make_data(n, n_bins, seed, label=label, weighted=weighted)
     rng = np.random.default_rng(seed + 1)
     w0 = (rng.random(n) < 0.7).astype(np.float32)[None, :] if bagging else None
@@ -143,6 +143,14 @@ def run_gbt(n, n_bins, seed, n_trees=2, max_depth=4, weighted=False, loss=capi.S
 
 def test_gbt_variance_unweighted_counts_bit_exact():
     assert run_gbt(20000, [64] * 40, seed=11, n_trees=2, max_depth=5) >= 8
+
+
+def test_gbt_deep_levels_row_lists_and_tile_groups():
+    # depth 7: up to 32 todo nodes per pass -> several shared-memory slot groups.  Default: per-pass row lists over the
+    # row-major bin copy; SB_FLAG_NO_ROW_LISTS: the column-tile kernel visits every tile once per group.
+    run_gbt(30000, [64] * 40, seed=18, n_trees=1, max_depth=7, weighted=True)
+    run_gbt(30000, [64] * 40, seed=18, n_trees=1, max_depth=7, weighted=True, flags=2)
+    run_gbt(30000, [64] * 40, seed=19, n_trees=2, max_depth=6, bagging=True, feature_subsets=True)
 
 
 def test_gbt_weighted_mixed_bins():
