@@ -49,6 +49,7 @@ struct HistLaunch {
     size_t smem;
     // row-list path (more todo nodes than one slot group): lists are rebuilt before the kernel, every pass
     bool use_rows = false;
+    int fpl = 1, allf = 0;
     RowListArgs list{};
     HistRowsArgs rows{};
 };
@@ -107,6 +108,8 @@ struct sb_handle {
     DevBuf<int64_t> rl_tables;    // offsets[257] + chunk_begin[max] + chunk_end[max]
     DevBuf<int32_t> rl_chunk_group;  // [max] + n_chunks scalar at the end
     DevBuf<RowOps> rl_ops;        // [n]
+    DevBuf<int32_t> rt_tiles;     // row-list path: tile_feats [n_rt][32*fpl] then tile_slot0 [n_rt]
+    DevBuf<uint32_t> rt_fmask;    // [n_slots][n_rt][fpl]
     bool enable_row_lists = true;
     bool cnt_int = false;  // every sig*weight product of the training rows is an integer in [0, 1024]
 
@@ -391,6 +394,58 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     const int max_gs = hist_max_slots_per_block(bins_pad, nw);
     if (max_gs < 1) return fail(SB_ERR_UNSUPPORTED, "one node's histogram tile does not fit in shared memory");
 
+    // ---- row-list path tables: tiles of 32*fpl consecutive feature slots, fpl = features per lane
+    int fpl = 0, rows_max_gs = 0, n_rt = 0, allf = 1;
+    const bool rows_enabled = h->enable_row_lists && h->train.n < (int64_t)0xffffffff;
+    if (rows_enabled) {
+        for (int f : {4, 2, 1}) {
+            rows_max_gs = hist_rows_max_slots_per_block(bins_pad, nw, f);
+            if (rows_max_gs >= 1) { fpl = f; break; }
+        }
+    }
+    if (fpl > 0) {
+        const int tw = 32 * fpl;
+        std::vector<int32_t> rt_feats, rt_slot0;
+        std::vector<int> rt_of((size_t)F, -1);
+        for (int f0 = 0; f0 < F; f0 += tw) {
+            bool any = false;
+            for (int f = f0; f < std::min(F, f0 + tw); ++f) any |= used[f] != 0;
+            if (!any) continue;
+            const int t = (int)rt_slot0.size();
+            rt_slot0.push_back(f0);
+            for (int k = 0; k < fpl; ++k)
+                for (int l = 0; l < 32; ++l) {
+                    const int f = f0 + fpl * l + k;
+                    if (f < F && used[f]) { rt_feats.push_back(f); rt_of[f] = t; }
+                    else rt_feats.push_back(-1);
+                }
+        }
+        n_rt = (int)rt_slot0.size();
+        std::vector<uint32_t> rfm((size_t)S * n_rt * fpl, 0u);
+        for (int s = 0; s < S; ++s) {
+            const auto& nd = lay.nodes[order[s]];
+            for (int f : nd.features) {
+                const int t = rt_of[f];
+                const int rel = f - rt_slot0[t];
+                rfm[((size_t)s * n_rt + t) * fpl + rel % fpl] |= 1u << (rel / fpl);
+            }
+        }
+        for (int s = 0; s < S && allf; ++s)
+            for (int t = 0; t < n_rt && allf; ++t)
+                for (int k = 0; k < fpl && allf; ++k) {
+                    uint32_t full = 0;
+                    for (int l = 0; l < 32; ++l)
+                        if (rt_slot0[t] + fpl * l + k < F) full |= 1u << l;
+                    if (rfm[((size_t)s * n_rt + t) * fpl + k] != full) allf = 0;
+                }
+        SB_CUDA(h->rt_tiles.reserve(rt_feats.size() + rt_slot0.size()));
+        SB_CUDA(h->rt_fmask.reserve(rfm.size()));
+        SB_CUDA(cudaMemcpyAsync(h->rt_tiles.p, rt_feats.data(), rt_feats.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        SB_CUDA(cudaMemcpyAsync(h->rt_tiles.p + rt_feats.size(), rt_slot0.data(), rt_slot0.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        SB_CUDA(cudaMemcpyAsync(h->rt_fmask.p, rfm.data(), rfm.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        h->h2d_bytes += (rt_feats.size() + rt_slot0.size() + rfm.size()) * 4;
+    }
+
     // per tree: slot table + launch
     size_t table_total = 0;
     std::vector<std::pair<int, int>> tree_ranges;  // [begin, end) in `order`
@@ -422,7 +477,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
             if (nid <= 0) return fail(SB_ERR_INVALID, "todo node with non-positive id");
             tables[toff + nid] = (int16_t)(s - s0);
         }
-        HistLaunch L;
+        HistLaunch L{};
         L.kind = h->stat_kind;
         L.cnt_int = cnt_int;
         HistArgs& a = L.args;
@@ -444,19 +499,23 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         a.n_tiles = n_tiles;
         a.gs = std::min(ns, max_gs);
         a.n_groups = (ns + a.gs - 1) / a.gs;
-        if (a.n_groups > 1 && h->enable_row_lists && n < (int64_t)0xffffffff) {
-            // more todo nodes than one block can hold: group the rows by slot group and walk the lists instead
-            const int rgs = std::min(ns, hist_rows_max_slots_per_block(bins_pad, nw));
+        a.n_slots = ns;
+        a.bins_pad = bins_pad;
+        if (fpl > 0) {
+            // group the rows by slot group once per pass and walk the lists (rowlist.cu, hist_rows_kernel)
+            const int rgs = std::min(ns, rows_max_gs);
             const int rgroups = (ns + rgs - 1) / rgs;
-            if (rgs >= 1 && rgroups <= 254) {
+            if (rgroups <= 254) {
                 RowSet& tr = h->train;
                 if (!tr.bins_rm) {  // row-major twin of the bin matrix, built once
+                    // 32-byte row pitch: a lane group that reaches past F reads into the next row (masked out in
+                    // the kernel); the allocation is padded so the last row's over-read stays inside it
                     tr.fpad = ((F + 31) / 32) * 32;
-                    SB_CUDA(cudaMalloc(&tr.bins_rm, (size_t)std::max<int64_t>(n, 1) * tr.fpad));
+                    SB_CUDA(cudaMalloc(&tr.bins_rm, (size_t)std::max<int64_t>(n, 1) * tr.fpad + 256));
                     SB_CUDA(launch_transpose_bins(static_cast<const uint8_t*>(tr.bins_base), tr.pitch, F, n, tr.bins_rm, tr.fpad, h->stream));
                     h->launches_count += 1;
                 }
-                const int64_t want_chunks = std::max<int64_t>(1, (148 * 3 + n_tiles - 1) / n_tiles);
+                const int64_t want_chunks = std::max<int64_t>(1, (148 * 3 + n_rt - 1) / n_rt);
                 int64_t chunk_rows = ((n + want_chunks - 1) / want_chunks + 127) / 128 * 128;
                 chunk_rows = std::max<int64_t>(chunk_rows, 1024);
                 chunk_rows = std::min<int64_t>(chunk_rows, cnt_int ? MAX_ROWS_PER_FLUSH / 2 : MAX_ROWS_PER_FLUSH);
@@ -469,6 +528,8 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 SB_CUDA(h->rl_chunk_group.reserve((size_t)max_chunks + 1));
                 SB_CUDA(h->rl_ops.reserve((size_t)n));
                 L.use_rows = true;
+                L.fpl = fpl;
+                L.allf = allf;
                 RowListArgs& la = L.list;
                 la.n = n; la.node_id = a.node_id; la.output = a.output; la.significance = a.significance; la.weights = a.weights;
                 la.slot_of_node = a.slot_of_node; la.slot_table_size = a.slot_table_size; la.gs = rgs; la.n_groups = rgroups;
@@ -481,16 +542,14 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 HistRowsArgs& ra = L.rows;
                 ra.rm_bins = tr.bins_rm; ra.fpad = tr.fpad; ra.ops = la.ops; ra.chunk_group = la.chunk_group;
                 ra.chunk_begin = la.chunk_begin; ra.chunk_end = la.chunk_end; ra.n_chunks = la.n_chunks;
-                ra.tile_feats = h->tile_feats.p; ra.tile_slot0 = h->tile_feats.p + (size_t)n_tiles * 32;
-                ra.slot_fmask = a.slot_fmask; ra.pair_off = a.pair_off; ra.n_tiles = n_tiles; ra.gs = rgs; ra.n_slots = ns;
-                ra.bins_pad = bins_pad; ra.n_features = F; ra.stats_size = h->stats_size; ra.cnt_shift = h->d_cnt_shift;
-                ra.raw_lo = h->raw.p; ra.raw_hi = h->raw.p + lay.total;
-                L.grid = max_chunks * n_tiles;
-                L.smem = hist_rows_smem_bytes(rgs, bins_pad, nw);
+                ra.tile_feats = h->rt_tiles.p; ra.tile_slot0 = h->rt_tiles.p + (size_t)n_rt * 32 * fpl;
+                ra.slot_fmask = h->rt_fmask.p + (size_t)s0 * n_rt * fpl; ra.pair_off = a.pair_off; ra.n_tiles = n_rt; ra.gs = rgs;
+                ra.n_slots = ns; ra.bins_pad = bins_pad; ra.n_features = F; ra.stats_size = h->stats_size;
+                ra.cnt_shift = h->d_cnt_shift; ra.raw_lo = h->raw.p; ra.raw_hi = h->raw.p + lay.total;
+                L.grid = max_chunks * n_rt;
+                L.smem = hist_rows_smem_bytes(rgs, bins_pad, nw, fpl);
             }
         }
-        a.n_slots = ns;
-        a.bins_pad = bins_pad;
         const int64_t tiles_rows = (n + HIST_T_ROWS - 1) / HIST_T_ROWS;
         int64_t n_chunks = (148 * 3 + (int64_t)n_tiles * a.n_groups - 1) / ((int64_t)n_tiles * a.n_groups);
         n_chunks = std::max<int64_t>(1, std::min(n_chunks, tiles_rows));
@@ -571,7 +630,7 @@ int run_histograms(sb_handle* h) {
     for (const HistLaunch& L : h->launches) {
         if (L.use_rows) {
             SB_CUDA(launch_rowlist_build(L.list, h->stream));
-            SB_CUDA(hist_rows_launch(L.kind, L.cnt_int, L.rows, L.grid, L.smem, h->stream));
+            SB_CUDA(hist_rows_launch(L.kind, L.cnt_int, L.fpl, L.allf, L.rows, L.grid, L.smem, h->stream));
             h->launches_count += 6;  // keys, radix sort (2 kernels), chunk table, operands, histogram
         } else {
             SB_CUDA(hist_launch(L.kind, L.cnt_int, L.args, h->train.tensor_map, L.grid, L.smem, h->stream));
@@ -658,7 +717,7 @@ SB_API void sb_destroy(sb_handle* h) {
     h->slot_of_node.release(); h->tasks.release(); h->node_task_begin.release(); h->cand.release(); h->gain_out.release();
     h->cand_bits.release(); h->out_bits.release(); h->new_dropout.release(); h->new_weights.release();
     h->sort_keys.release(); h->sort_idx.release(); h->sort_tmp.release(); h->sort_flags.release();
-    h->rl_keys.release(); h->rl_vals.release(); h->rl_temp.release(); h->rl_tables.release(); h->rl_chunk_group.release(); h->rl_ops.release();
+    h->rl_keys.release(); h->rl_vals.release(); h->rl_temp.release(); h->rl_tables.release(); h->rl_chunk_group.release(); h->rl_ops.release(); h->rt_tiles.release(); h->rt_fmask.release();
     if (h->d_feat_bins) cudaFree(h->d_feat_bins);
     if (h->d_acc) cudaFree(h->d_acc);
     if (h->d_err_scratch) cudaFree(h->d_err_scratch);

@@ -136,30 +136,31 @@ __host__ __device__ inline int hist_words(int kind, int cnt_int, int stats_size)
 
 // Merge a block's privatised histogram into the global integer accumulators.  (lo, hi) split: the global sum over
 // all blocks and GPUs may exceed 63 bits, each half cannot.
-template <int KIND, int CNT_INT>
+template <int KIND, int CNT_INT, int FPL>
 __device__ __forceinline__ void flush_hist(const uint32_t* hist, int gcount, int g0, int bins_pad, int nw, int n_stats,
                                            int cnt_shift, const int32_t* tile_feats, const int64_t* pair_off,
                                            int n_features, int64_t* raw_lo, int64_t* raw_hi, int nthreads) {
-    const int per_slot = bins_pad * n_stats * 32;  // 64-bit statistics per slot
+    constexpr int LW = 32 * FPL;                      // features (words) per histogram word row: [k][lane]
+    const int per_slot = bins_pad * n_stats * LW;    // 64-bit statistics per slot
     for (int i = threadIdx.x; i < gcount * per_slot; i += nthreads) {
-        const int l = i & 31;
-        int t = i >> 5;
+        const int l = i % LW;                        // k * 32 + lane
+        int t = i / LW;
         const int stt = t % n_stats;
         t /= n_stats;
         const int bin = t % bins_pad;
         const int sl = t / bins_pad;
-        const uint32_t* pb = hist + ((sl * bins_pad + bin) * nw) * 32 + l;
+        const uint32_t* pb = hist + ((sl * bins_pad + bin) * nw) * LW + l;
         long long v;
         if (KIND == STAT_VARIANCE) {
             if (CNT_INT) {
                 if (stt == 0) v = (long long)((unsigned long long)pb[0] << cnt_shift);
-                else v = (long long)(((unsigned long long)pb[(2 * stt) * 32] << 32) | pb[(2 * stt - 1) * 32]);
+                else v = (long long)(((unsigned long long)pb[(2 * stt) * LW] << 32) | pb[(2 * stt - 1) * LW]);
             } else {
-                v = (long long)(((unsigned long long)pb[(2 * stt + 1) * 32] << 32) | pb[(2 * stt) * 32]);
+                v = (long long)(((unsigned long long)pb[(2 * stt + 1) * LW] << 32) | pb[(2 * stt) * LW]);
             }
         } else {
-            if (CNT_INT) v = (long long)((unsigned long long)pb[stt * 32] << cnt_shift);
-            else v = (long long)(((unsigned long long)pb[(2 * stt + 1) * 32] << 32) | pb[(2 * stt) * 32]);
+            if (CNT_INT) v = (long long)((unsigned long long)pb[stt * LW] << cnt_shift);
+            else v = (long long)(((unsigned long long)pb[(2 * stt + 1) * LW] << 32) | pb[(2 * stt) * LW]);
         }
         if (v == 0) continue;
         const int f = tile_feats[l];
@@ -374,8 +375,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) hist_kernel(const HistArgs a, con
     }
     __syncthreads();
 
-    flush_hist<KIND, CNT_INT>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0, a.tile_feats + tile_id * 32,
-                              a.pair_off, a.n_features, a.raw_lo, a.raw_hi, NTHREADS);
+    flush_hist<KIND, CNT_INT, 1>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0, a.tile_feats + tile_id * 32,
+                                 a.pair_off, a.n_features, a.raw_lo, a.raw_hi, NTHREADS);
 }
 
 size_t hist_smem_bytes(int gs, int bins_pad, int nw) { return SMEM_FIXED + (size_t)gs * bins_pad * nw * 32 * 4; }
@@ -410,21 +411,31 @@ cudaError_t hist_launch(int kind, int cnt_int, const HistArgs& a, const void* te
 
 // =====================================================================================================================
 // hist_rows_kernel: the same accumulation driven by a per-group row list (rowlist.cu).  A block takes one chunk of one
-// slot group's list and one tile of 32 feature slots.  One producer warp streams the RowOps of the chunk into shared
-// memory with TMA 1-D bulk copies (4 KB per stage); 16 consumer warps read, per row, the 32 bins of the tile from the
-// row-major bin copy with ONE coalesced 32-byte load (lane == feature), then issue the same two-phase atomics.
+// slot group's list and one tile of 32*FPL consecutive feature slots.  One producer warp streams the RowOps of the
+// chunk into shared memory with TMA 1-D bulk copies (4 KB per stage); the consumer warps read, per row, the 32*FPL
+// bins of the tile from the row-major bin copy with ONE coalesced load (lane l holds features FPL*l .. FPL*l+FPL-1),
+// then issue the two-phase atomics.  The per-row operands are warp-uniform and cost as many LSU cycles to broadcast
+// (8 words) as the atomics of 32 cells do; with FPL = 4 that cost is shared by 128 cells.  The histogram is laid out
+// [slot][bin][word][k][lane] (feature = FPL*lane + k), so for every k a warp's atomics still hit 32 distinct banks.
 namespace {
 constexpr int R_NST = 4;
-constexpr int R_CONS_WARPS = 16;
-constexpr int R_NTHREADS = (1 + R_CONS_WARPS) * 32;
-constexpr int R_TILE = 128;                       // rows per stage
-constexpr int R_ROWS_PER_WARP = R_TILE / R_CONS_WARPS;
-constexpr size_t R_SMEM_FIXED = (size_t)R_NST * R_TILE * sizeof(RowOps) + 128 /* barriers */ + 64 /* fmask table */;
+constexpr int R_TILE = 128;  // rows per stage
+constexpr size_t R_SMEM_FIXED = (size_t)R_NST * R_TILE * sizeof(RowOps) + 128 /* barriers */ + 256 /* fmask table */;
 struct RStage { uint64_t full, empty; };
+constexpr int R_MAX_GS = 16;  // fm_tab: 16 slots x FPL words <= 64 words
+template <int FPL> struct RCfg {
+    static constexpr int CONS_WARPS = 16;
+    static constexpr int NTHREADS = (1 + CONS_WARPS) * 32;
+    static constexpr int RPW = R_TILE / CONS_WARPS;                   // rows of a tile per consumer warp (8)
+    static constexpr int BATCH = FPL == 4 ? 2 : (FPL == 2 ? 4 : 8);  // rows whose atomics are in flight together
+};
 }  // namespace
 
-template <int KIND, int CNT_INT>
-__global__ void __launch_bounds__(R_NTHREADS, 1) hist_rows_kernel(const HistRowsArgs a) {
+template <int KIND, int CNT_INT, int FPL, int ALLF>
+__global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const HistRowsArgs a) {
+    constexpr int CONS_WARPS = RCfg<FPL>::CONS_WARPS;
+    constexpr int NTHR = RCfg<FPL>::NTHREADS;
+    constexpr int BATCH = RCfg<FPL>::BATCH;
     extern __shared__ __align__(1024) unsigned char smem[];
     const int ci = blockIdx.x / a.n_tiles;
     const int tile_id = blockIdx.x - ci * a.n_tiles;
@@ -443,12 +454,15 @@ __global__ void __launch_bounds__(R_NTHREADS, 1) hist_rows_kernel(const HistRows
     const int bins_pad = a.bins_pad;
     const int n_iters = (int)((end - begin + R_TILE - 1) / R_TILE);
 
-    for (int i = threadIdx.x; i < gcount * bins_pad * nw * 32; i += R_NTHREADS) hist[i] = 0u;
-    if (threadIdx.x < 16) fm_tab[threadIdx.x] = threadIdx.x < gcount ? a.slot_fmask[(size_t)(g0 + threadIdx.x) * a.n_tiles + tile_id] : 0u;
+    for (int i = threadIdx.x; i < gcount * bins_pad * nw * 32 * FPL; i += NTHR) hist[i] = 0u;
+    if (threadIdx.x < R_MAX_GS * FPL) {
+        const int sl = threadIdx.x / FPL, k = threadIdx.x % FPL;
+        fm_tab[threadIdx.x] = sl < gcount ? a.slot_fmask[((size_t)(g0 + sl) * a.n_tiles + tile_id) * FPL + k] : 0u;
+    }
     if (threadIdx.x == 0) {
         for (int s = 0; s < R_NST; ++s) {
             mbar_init(&st[s].full, 1);
-            mbar_init(&st[s].empty, R_CONS_WARPS);
+            mbar_init(&st[s].empty, CONS_WARPS);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -467,111 +481,154 @@ __global__ void __launch_bounds__(R_NTHREADS, 1) hist_rows_kernel(const HistRows
         }
     } else {
         const int cw = warp - 1;
-        const int wr0 = cw * R_ROWS_PER_WARP;
+        constexpr int RPW = RCfg<FPL>::RPW;
         const uint32_t lane_bit = 1u << lane;
         const uint32_t lane_base = smem_u32(hist) + (uint32_t)lane * 4u;
-        const uint32_t bin_stride = (uint32_t)nw * 128u;
-        const uint32_t slot_stride = (uint32_t)bins_pad * bin_stride;
-        const uint8_t* my_bins = a.rm_bins + a.tile_slot0[tile_id] + lane;
-        for (int it = 0; it < n_iters; ++it) {
+        const uint32_t bin_stride = (uint32_t)nw * 128u * FPL;         // bytes between bins
+        const uint32_t slot_stride = (uint32_t)bins_pad * bin_stride;   // bytes between slots
+        constexpr uint32_t WORD = 128u * FPL;                           // bytes between the words of one bin
+        const uint8_t* my_bins = a.rm_bins + a.tile_slot0[tile_id] + lane * FPL;
+        // lanes whose feature slot does not exist (tile reaches past F) never touch the histogram
+        uint32_t lane_feat_ok = 0;
+#pragma unroll
+        for (int k = 0; k < FPL; ++k)
+            if (a.tile_feats[tile_id * 32 * FPL + k * 32 + lane] >= 0 || !ALLF) lane_feat_ok |= 1u << k;
+        const int wr0 = cw * RPW;
+        // per-lane dummy bin right behind the block's histogram (one bin's worth of words)
+        const uint32_t dummy_addr = lane_base + (uint32_t)gcount * slot_stride;
+
+        // The bins of tile it+1 are requested before the atomics of tile it are issued, so the global-load latency
+        // of one tile hides behind the shared-memory work of the previous one.
+        uint32_t bw_cur[RPW], bw_next[RPW];
+        auto fetch_bins = [&](int it, uint32_t (&bw)[RPW]) {
             const int s = it % R_NST;
             mbar_wait(&st[s].full, (uint32_t)((it / R_NST) & 1));
             const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
-            if (wr0 < rows) {
-                const RowOps* v = ops_s + s * R_TILE + wr0;
-                uint4 v0[R_ROWS_PER_WARP];
-                uint32_t bin[R_ROWS_PER_WARP];
-                bool ok[R_ROWS_PER_WARP];
+            const RowOps* v = ops_s + s * R_TILE + wr0;
 #pragma unroll
-                for (int j = 0; j < R_ROWS_PER_WARP; ++j) {  // phase 0: operands + the row's 32 bins (one 32-byte load per warp)
-                    ok[j] = wr0 + j < rows;
-                    v0[j] = make_uint4(0u, 0xffffffffu, 0u, 0u);
-                    bin[j] = 0;
-                    if (ok[j]) {
-                        v0[j] = *reinterpret_cast<const uint4*>(&v[j]);  // row, slot, q0, q1
-                        bin[j] = __ldg(my_bins + (size_t)v0[j].x * a.fpad);
-                    }
+            for (int j = 0; j < RPW; ++j) {
+                bw[j] = 0;
+                if (wr0 + j < rows) {
+                    const uint8_t* src = my_bins + (size_t)v[j].row * a.fpad;
+                    if (FPL == 4) bw[j] = __ldg(reinterpret_cast<const uint32_t*>(src));
+                    else if (FPL == 2) bw[j] = __ldg(reinterpret_cast<const unsigned short*>(src));
+                    else bw[j] = __ldg(src);
                 }
-                uint32_t ad[R_ROWS_PER_WARP];
-                uint32_t lo0[R_ROWS_PER_WARP], lo1[R_ROWS_PER_WARP], lo2[R_ROWS_PER_WARP];
-                uint32_t hi0[R_ROWS_PER_WARP], hi1[R_ROWS_PER_WARP], hi2[R_ROWS_PER_WARP];
-                uint32_t o0[R_ROWS_PER_WARP], o1[R_ROWS_PER_WARP], o2[R_ROWS_PER_WARP];
+            }
+        };
+        if (n_iters > 0) fetch_bins(0, bw_cur);
+        for (int it = 0; it < n_iters; ++it) {
+            const int s = it % R_NST;
+            if (it + 1 < n_iters) fetch_bins(it + 1, bw_next);
+            const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
+            const RowOps* v = ops_s + s * R_TILE + wr0;
 #pragma unroll
-                for (int j = 0; j < R_ROWS_PER_WARP; ++j) {  // phase 1
-                    const uint32_t slot = v0[j].y;
-                    ok[j] = ok[j] && slot < (uint32_t)gcount && (fm_tab[slot & 15u] & lane_bit) != 0u;
-                    ad[j] = lane_base + slot * slot_stride + bin[j] * bin_stride;
-                    lo0[j] = v0[j].z; hi0[j] = v0[j].w;
+            for (int jb = 0; jb < RPW; jb += BATCH) {
+                if (wr0 + jb >= rows) break;  // warp-uniform
+                // Every atomic below is unconditional: a cell that must not count (row past the end of the list, lane
+                // whose feature is not in the node's list or does not exist) is redirected to a per-lane dummy bin
+                // behind the histogram.  No predicates, no divergence, no reconvergence bookkeeping in the hot loop.
+                uint32_t ad[BATCH][FPL];
+                uint32_t o0[BATCH][FPL], o1[BATCH][FPL], o2[BATCH][FPL];
+                uint32_t lo0[BATCH], lo1[BATCH], lo2[BATCH], hi0[BATCH], hi1[BATCH], hi2[BATCH];
+#pragma unroll
+                for (int j = 0; j < BATCH; ++j) {  // phase 1: operands, addresses, low-word atomics
+                    const uint4 v0 = *reinterpret_cast<const uint4*>(&v[jb + j]);       // row, slot, q0, q1
+                    const uint4 v1 = *reinterpret_cast<const uint4*>(&v[jb + j].q[2]);  // q2..q5
+                    const uint32_t slot = v0.y;
+                    const bool rowok = (wr0 + jb + j < rows) && slot < (uint32_t)gcount;
+                    uint32_t base = lane_base + slot * slot_stride;
+                    lo0[j] = v0.z; hi0[j] = v0.w;
                     lo1[j] = hi1[j] = lo2[j] = hi2[j] = 0;
-                    o0[j] = o1[j] = o2[j] = 0;
-                    const uint4 v1 = *reinterpret_cast<const uint4*>(&v[j].q[2]);
                     if (KIND == STAT_VARIANCE) { lo1[j] = v1.x; hi1[j] = v1.y; lo2[j] = v1.z; hi2[j] = v1.w; }
-                    else ad[j] += v1.x;  // class words
-                    if (ok[j]) {
+                    else base += v1.x * FPL;  // class words
+                    uint32_t fmw[FPL];
+#pragma unroll
+                    for (int k = 0; k < FPL; ++k) fmw[k] = ALLF ? 0xffffffffu : fm_tab[(slot & (R_MAX_GS - 1)) * FPL + k];
+#pragma unroll
+                    for (int k = 0; k < FPL; ++k) {
+                        const uint32_t bin = (bw_cur[jb + j] >> (8 * k)) & 0xffu;
+                        const bool ok = rowok && ((lane_feat_ok >> k) & 1u) && (ALLF || (fmw[k] & lane_bit) != 0u);
+                        ad[j][k] = ok ? base + bin * bin_stride + k * 128u : dummy_addr;
                         if (KIND == STAT_VARIANCE) {
                             if (CNT_INT) {
-                                sred_add<0>(ad[j], lo0[j]);
-                                o1[j] = satom_add<128>(ad[j], lo1[j]);
-                                o2[j] = satom_add<384>(ad[j], lo2[j]);
+                                sred_add<0>(ad[j][k], lo0[j]);
+                                o1[j][k] = satom_add<WORD>(ad[j][k], lo1[j]);
+                                o2[j][k] = satom_add<3 * WORD>(ad[j][k], lo2[j]);
                             } else {
-                                o0[j] = satom_add<0>(ad[j], lo0[j]);
-                                o1[j] = satom_add<256>(ad[j], lo1[j]);
-                                o2[j] = satom_add<512>(ad[j], lo2[j]);
+                                o0[j][k] = satom_add<0>(ad[j][k], lo0[j]);
+                                o1[j][k] = satom_add<2 * WORD>(ad[j][k], lo1[j]);
+                                o2[j][k] = satom_add<4 * WORD>(ad[j][k], lo2[j]);
                             }
                         } else {
-                            if (CNT_INT) sred_add<0>(ad[j], lo0[j]);
-                            else o0[j] = satom_add<0>(ad[j], lo0[j]);
+                            if (CNT_INT) sred_add<0>(ad[j][k], lo0[j]);
+                            else o0[j][k] = satom_add<0>(ad[j][k], lo0[j]);
                         }
                     }
                 }
 #pragma unroll
-                for (int j = 0; j < R_ROWS_PER_WARP; ++j) {  // phase 2: carries
-                    if (!ok[j]) continue;
-                    if (KIND == STAT_VARIANCE) {
-                        if (CNT_INT) {
-                            sred_add<256>(ad[j], hi_plus_carry(o1[j], lo1[j], hi1[j]));
-                            sred_add<512>(ad[j], hi_plus_carry(o2[j], lo2[j], hi2[j]));
-                        } else {
-                            sred_add<128>(ad[j], hi_plus_carry(o0[j], lo0[j], hi0[j]));
-                            sred_add<384>(ad[j], hi_plus_carry(o1[j], lo1[j], hi1[j]));
-                            sred_add<640>(ad[j], hi_plus_carry(o2[j], lo2[j], hi2[j]));
+                for (int j = 0; j < BATCH; ++j) {  // phase 2: carries
+#pragma unroll
+                    for (int k = 0; k < FPL; ++k) {
+                        if (KIND == STAT_VARIANCE) {
+                            if (CNT_INT) {
+                                sred_add<2 * WORD>(ad[j][k], hi_plus_carry(o1[j][k], lo1[j], hi1[j]));
+                                sred_add<4 * WORD>(ad[j][k], hi_plus_carry(o2[j][k], lo2[j], hi2[j]));
+                            } else {
+                                sred_add<WORD>(ad[j][k], hi_plus_carry(o0[j][k], lo0[j], hi0[j]));
+                                sred_add<3 * WORD>(ad[j][k], hi_plus_carry(o1[j][k], lo1[j], hi1[j]));
+                                sred_add<5 * WORD>(ad[j][k], hi_plus_carry(o2[j][k], lo2[j], hi2[j]));
+                            }
+                        } else if (!CNT_INT) {
+                            sred_add<WORD>(ad[j][k], hi_plus_carry(o0[j][k], lo0[j], hi0[j]));
                         }
-                    } else if (!CNT_INT) {
-                        sred_add<128>(ad[j], hi_plus_carry(o0[j], lo0[j], hi0[j]));
                     }
                 }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&st[s].empty);
+#pragma unroll
+            for (int j = 0; j < RPW; ++j) bw_cur[j] = bw_next[j];
         }
     }
     __syncthreads();
-    flush_hist<KIND, CNT_INT>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0, a.tile_feats + tile_id * 32,
-                              a.pair_off, a.n_features, a.raw_lo, a.raw_hi, R_NTHREADS);
+    flush_hist<KIND, CNT_INT, FPL>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0,
+                                   a.tile_feats + tile_id * 32 * FPL, a.pair_off, a.n_features, a.raw_lo, a.raw_hi, NTHR);
 }
 
-size_t hist_rows_smem_bytes(int gs, int bins_pad, int nw) { return R_SMEM_FIXED + (size_t)gs * bins_pad * nw * 32 * 4; }
-int hist_rows_max_slots_per_block(int bins_pad, int nw) {
-    const size_t budget = 227 * 1024 - R_SMEM_FIXED;
-    int gs = (int)(budget / ((size_t)bins_pad * nw * 32 * 4));
-    return gs > 16 ? 16 : gs;  // fm_tab holds 16 masks
+size_t hist_rows_smem_bytes(int gs, int bins_pad, int nw, int fpl) {
+    return R_SMEM_FIXED + (size_t)gs * bins_pad * nw * 32 * fpl * 4 + (size_t)nw * 32 * fpl * 4 /* dummy bin */;
+}
+int hist_rows_max_slots_per_block(int bins_pad, int nw, int fpl) {
+    const size_t budget = 227 * 1024 - R_SMEM_FIXED - (size_t)nw * 32 * fpl * 4;
+    int gs = (int)(budget / ((size_t)bins_pad * nw * 32 * fpl * 4));
+    return gs > R_MAX_GS ? R_MAX_GS : gs;
 }
 
-template <int KIND, int CNT_INT>
+template <int KIND, int CNT_INT, int FPL, int ALLF>
 static cudaError_t launch_rows_one(const HistRowsArgs& a, int grid, size_t smem, cudaStream_t stream) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(hist_rows_kernel<KIND, CNT_INT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(hist_rows_kernel<KIND, CNT_INT, FPL, ALLF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    hist_rows_kernel<KIND, CNT_INT><<<grid, R_NTHREADS, smem, stream>>>(a);
+    hist_rows_kernel<KIND, CNT_INT, FPL, ALLF><<<grid, RCfg<FPL>::NTHREADS, smem, stream>>>(a);
     return cudaGetLastError();
 }
 
-cudaError_t hist_rows_launch(int kind, int cnt_int, const HistRowsArgs& a, int grid, size_t smem, cudaStream_t stream) {
-    if (kind == STAT_VARIANCE) return cnt_int ? launch_rows_one<STAT_VARIANCE, 1>(a, grid, smem, stream) : launch_rows_one<STAT_VARIANCE, 0>(a, grid, smem, stream);
-    return cnt_int ? launch_rows_one<STAT_CLASS, 1>(a, grid, smem, stream) : launch_rows_one<STAT_CLASS, 0>(a, grid, smem, stream);
+template <int KIND, int CNT_INT>
+static cudaError_t launch_rows_kc(int fpl, int allf, const HistRowsArgs& a, int grid, size_t smem, cudaStream_t stream) {
+    if (fpl == 4) return allf ? launch_rows_one<KIND, CNT_INT, 4, 1>(a, grid, smem, stream) : launch_rows_one<KIND, CNT_INT, 4, 0>(a, grid, smem, stream);
+    if (fpl == 2) return allf ? launch_rows_one<KIND, CNT_INT, 2, 1>(a, grid, smem, stream) : launch_rows_one<KIND, CNT_INT, 2, 0>(a, grid, smem, stream);
+    return allf ? launch_rows_one<KIND, CNT_INT, 1, 1>(a, grid, smem, stream) : launch_rows_one<KIND, CNT_INT, 1, 0>(a, grid, smem, stream);
+}
+
+cudaError_t hist_rows_launch(int kind, int cnt_int, int fpl, int allf, const HistRowsArgs& a, int grid, size_t smem,
+                             cudaStream_t stream) {
+    if (kind == STAT_VARIANCE)
+        return cnt_int ? launch_rows_kc<STAT_VARIANCE, 1>(fpl, allf, a, grid, smem, stream) : launch_rows_kc<STAT_VARIANCE, 0>(fpl, allf, a, grid, smem, stream);
+    return cnt_int ? launch_rows_kc<STAT_CLASS, 1>(fpl, allf, a, grid, smem, stream) : launch_rows_kc<STAT_CLASS, 0>(fpl, allf, a, grid, smem, stream);
 }
 
 }  // namespace sb

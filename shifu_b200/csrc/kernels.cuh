@@ -73,18 +73,20 @@ struct HistRowsArgs {
     const int64_t* chunk_begin;
     const int64_t* chunk_end;
     const int32_t* n_chunks;
-    const int32_t* tile_feats;   // as HistArgs
-    const int32_t* tile_slot0;
-    const uint32_t* slot_fmask;  // [n_slots][n_tiles]
+    const int32_t* tile_feats;   // [n_tiles][32*fpl]: entry k*32+lane = feature slot tile_slot0 + fpl*lane + k, or -1
+    const int32_t* tile_slot0;   // [n_tiles] first feature slot of the tile (multiple of 32*fpl)
+    const uint32_t* slot_fmask;  // [n_slots][n_tiles][fpl]: word k, bit lane: that feature is in the slot's list
     const int64_t* pair_off;     // [n_slots][F]
     int n_tiles, gs, n_slots, bins_pad, n_features, stats_size;
     const int* cnt_shift;
     int64_t* raw_lo;
     int64_t* raw_hi;
 };
-cudaError_t hist_rows_launch(int kind, int cnt_int, const HistRowsArgs& a, int grid, size_t smem, cudaStream_t stream);
-size_t hist_rows_smem_bytes(int gs, int bins_pad, int nw);
-int hist_rows_max_slots_per_block(int bins_pad, int nw);
+// fpl = features per lane (1, 2 or 4); allf = every slot takes every feature of the tile (skips the mask lookups)
+cudaError_t hist_rows_launch(int kind, int cnt_int, int fpl, int allf, const HistRowsArgs& a, int grid, size_t smem,
+                             cudaStream_t stream);
+size_t hist_rows_smem_bytes(int gs, int bins_pad, int nw, int fpl);
+int hist_rows_max_slots_per_block(int bins_pad, int nw, int fpl);
 
 size_t hist_smem_bytes(int gs, int bins_pad, int nw);
 int hist_max_slots_per_block(int bins_pad, int nw);
