@@ -235,10 +235,10 @@ class ConfigArrays:
         self.stats_size = 3 if impurity in (SB_IMPURITY_VARIANCE, SB_IMPURITY_FRIEDMANMSE) else num_classes
 
     def boundaries_of(self, f):
-        off = 0
-        for g in range(f):
-            if not self.is_categorical[g]:
-                off += int(self.n_bins[g])
+        if not hasattr(self, "_bb_off"):
+            sizes = np.where(self.is_categorical != 0, 0, self.n_bins).astype(np.int64)
+            self._bb_off = np.concatenate([[0], np.cumsum(sizes)])
+        off = int(self._bb_off[f])
         return self.bin_boundary[off:off + int(self.n_bins[f])]
 
 

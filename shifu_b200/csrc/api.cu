@@ -79,6 +79,15 @@ struct sb_handle {
     bool begun = false, stats_ready = false;
     std::vector<HistLaunch> launches;
     DevBuf<int64_t> raw;      // [2 * total]: lo then hi
+    // histogram subtraction: the previous pass's merged accumulators and layout stay around for one pass
+    DevBuf<int64_t> raw_prev;
+    TodoLayout prev_layout;
+    bool prev_valid = false;
+    bool enable_subtraction = true;
+    std::vector<PairDesc> pairs;
+    DevBuf<PairDesc> d_pairs;
+    DevBuf<int32_t> d_small_is_b;
+    int64_t pair_max_len = 0;
     DevBuf<double> stats;     // [total]
     DevBuf<int32_t> tile_feats;
     DevBuf<uint32_t> slot_fmask;
@@ -111,6 +120,7 @@ struct sb_handle {
     DevBuf<int32_t> rt_tiles;     // row-list path: tile_feats [n_rt][32*fpl] then tile_slot0 [n_rt]
     DevBuf<uint32_t> rt_fmask;    // [n_slots][n_rt][fpl]
     bool enable_row_lists = true;
+    bool scales_valid = false;  // d_maxbits holds the maxima of the current tree's contributions
     bool cnt_int = false;  // every sig*weight product of the training rows is an integer in [0, 1024]
 
     int64_t launches_count = 0, h2d_bytes = 0, d2h_bytes = 0;
@@ -329,17 +339,52 @@ std::vector<int> hashmap_visit_rank(const std::vector<int>& column_nums) {
     return rank;
 }
 
+const sb_tree* find_tree(const sb_iter_in* in, int tree_id) {
+    for (int i = 0; i < in->n_trees; ++i)
+        if (in->trees[i].tree_id == tree_id && in->trees[i].n_nodes > 0) return &in->trees[i];
+    return nullptr;
+}
+
 int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     h->launches.clear();
     const TodoLayout& lay = h->layout;
-    const int S = (int)lay.nodes.size();
     const int F = h->cfg.n_features;
-    if (S == 0 || h->train.n == 0) return SB_OK;
+    if (lay.nodes.empty() || h->train.n == 0) return SB_OK;
 
-    // slots grouped by tree (one launch per tree: a row has one node id per tree)
-    std::vector<int> order((size_t)S);
-    for (int i = 0; i < S; ++i) order[i] = i;
+    // Slots: one per todo node -- or one per SIBLING PAIR whose parent's merged accumulators are still on the device
+    // (the previous pass): then only the smaller child is accumulated and the other is parent - child, which is
+    // exact in the integer accumulators (same scales within a tree).  `order[s]` is the todo index a slot stands for
+    // (child A of a pair); slots are grouped by tree (one launch per tree: a row has one node id per tree).
+    const int S_all = (int)lay.nodes.size();
+    std::vector<int> partner((size_t)S_all, -1);  // todo index of child B for child A of a pair; -2 for child B
+    h->pairs.clear();
+    h->pair_max_len = 0;
+    std::vector<int> pair_parent_prev;            // per pair: index into prev_layout
+    if (h->enable_subtraction && h->prev_valid) {
+        std::map<std::pair<int, int>, int> cur_idx, prev_idx;
+        for (int i = 0; i < S_all; ++i) cur_idx[{lay.nodes[i].tree_id, lay.nodes[i].node_id}] = i;
+        for (size_t i = 0; i < h->prev_layout.nodes.size(); ++i)
+            prev_idx[{h->prev_layout.nodes[i].tree_id, h->prev_layout.nodes[i].node_id}] = (int)i;
+        for (int i = 0; i < S_all; ++i) {
+            const auto& a = lay.nodes[i];
+            if (a.node_id < 2 || (a.node_id & 1)) continue;
+            auto ib = cur_idx.find({a.tree_id, a.node_id + 1});
+            auto ip = prev_idx.find({a.tree_id, a.node_id / 2});
+            if (ib == cur_idx.end() || ip == prev_idx.end()) continue;
+            const auto& b = lay.nodes[ib->second];
+            const auto& par = h->prev_layout.nodes[ip->second];
+            if (a.features != b.features || a.features != par.features) continue;
+            if (find_tree(in, a.tree_id) == nullptr) continue;
+            partner[i] = ib->second;
+            partner[ib->second] = -2;
+            pair_parent_prev.push_back(ip->second);
+        }
+    }
+    std::vector<int> order;
+    for (int i = 0; i < S_all; ++i)
+        if (partner[i] != -2) order.push_back(i);
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return lay.nodes[a].tree_id < lay.nodes[b].tree_id; });
+    const int S = (int)order.size();  // shadows the node count from here on: number of slots
 
     // tiles of 32 CONSECUTIVE feature slots (one TMA box each); only tiles with a used feature are launched
     std::vector<uint8_t> used((size_t)F, 0);
@@ -458,7 +503,8 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     std::vector<int> table_size(tree_ranges.size());
     for (size_t t = 0; t < tree_ranges.size(); ++t) {
         int max_id = 1;
-        for (int s = tree_ranges[t].first; s < tree_ranges[t].second; ++s) max_id = std::max(max_id, lay.nodes[order[s]].node_id);
+        for (int s = tree_ranges[t].first; s < tree_ranges[t].second; ++s)
+            max_id = std::max(max_id, lay.nodes[order[s]].node_id + (partner[order[s]] >= 0 ? 1 : 0));
         table_size[t] = max_id + 1;
         table_total += (size_t)table_size[t];
     }
@@ -473,10 +519,46 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         const int ns = s1 - s0;
         if (ns > 32767) return fail(SB_ERR_UNSUPPORTED, "more than 32767 todo nodes in one tree");
         for (int s = s0; s < s1; ++s) {
-            const int nid = lay.nodes[order[s]].node_id;
+            const auto& na = lay.nodes[order[s]];
+            const int nid = na.node_id;
             if (nid <= 0) return fail(SB_ERR_INVALID, "todo node with non-positive id");
             tables[toff + nid] = (int16_t)(s - s0);
+            if (partner[order[s]] >= 0) {
+                // both children map to the pair's slot for now; pair_decide_kernel removes the larger one
+                const auto& nb = lay.nodes[partner[order[s]]];
+                tables[toff + nb.node_id] = (int16_t)(s - s0);
+                // the parent: its split feature, left mask and node block in the previous pass
+                const sb_tree* tr_msg = find_tree(in, na.tree_id);
+                const sb_node* pn = nullptr;
+                for (int q = 0; q < tr_msg->n_nodes; ++q)
+                    if (tr_msg->nodes[q].id == nid / 2) pn = &tr_msg->nodes[q];
+                const TodoLayout::Node* par = nullptr;
+                for (const auto& pv : h->prev_layout.nodes)
+                    if (pv.tree_id == na.tree_id && pv.node_id == nid / 2) par = &pv;
+                int kf = -1;
+                if (pn && par)
+                    for (size_t k = 0; k < par->features.size(); ++k)
+                        if (par->features[k] == pn->feature) kf = (int)k;
+                if (!pn || !par || kf < 0 || pn->feature < 0) return fail(SB_ERR_STATE, "histogram subtraction: parent split not found");
+                PairDesc d{};
+                d.parent_split_block = par->offset + par->feat_off[(size_t)kf];
+                d.parent_off = par->offset;
+                d.off_a = na.offset;
+                d.off_b = nb.offset;
+                int64_t len = 0;
+                for (int f : na.features) len += (int64_t)h->n_bins[f] * h->stats_size;
+                d.len = len;
+                d.left_mask = h->trees[na.tree_id].masks + pn->left_mask_offset;
+                d.n_bins = h->n_bins[pn->feature];
+                d.node_a = nid;
+                d.node_b = nb.node_id;
+                d.slot = s;
+                d.table_off = (int32_t)toff;
+                h->pairs.push_back(d);
+                h->pair_max_len = std::max(h->pair_max_len, len);
+            }
         }
+        if (table_size[t] < 0) return fail(SB_ERR_STATE, "slot table");
         HistLaunch L{};
         L.kind = h->stat_kind;
         L.cnt_int = cnt_int;
@@ -574,7 +656,15 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     }
     SB_CUDA(cudaMemcpyAsync(h->slot_of_node.p, tables.data(), tables.size() * 2, cudaMemcpyHostToDevice, h->stream));
     h->h2d_bytes += tables.size() * 2;
-    (void)in;
+    if (!h->pairs.empty()) {
+        SB_CUDA(h->d_pairs.reserve(h->pairs.size()));
+        SB_CUDA(h->d_small_is_b.reserve(h->pairs.size()));
+        SB_CUDA(cudaMemcpyAsync(h->d_pairs.p, h->pairs.data(), h->pairs.size() * sizeof(PairDesc), cudaMemcpyHostToDevice, h->stream));
+        h->h2d_bytes += h->pairs.size() * sizeof(PairDesc);
+        SB_CUDA(launch_pair_decide(h->d_pairs.p, (int)h->pairs.size(), h->raw_prev.p, h->raw_prev.p + h->prev_layout.total,
+                                   h->stats_size, h->stat_kind, F, h->slot_of_node.p, h->pair_off.p, h->d_small_is_b.p, h->stream));
+        h->launches_count += 1;
+    }
     return SB_OK;
 }
 
@@ -640,12 +730,6 @@ int run_histograms(sb_handle* h) {
     return SB_OK;
 }
 
-const sb_tree* find_tree(const sb_iter_in* in, int tree_id) {
-    for (int i = 0; i < in->n_trees; ++i)
-        if (in->trees[i].tree_id == tree_id && in->trees[i].n_nodes > 0) return &in->trees[i];
-    return nullptr;
-}
-
 }  // namespace
 
 extern "C" {
@@ -688,6 +772,7 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
     if (cfg->bin_boundary) h->bin_boundary.assign(cfg->bin_boundary, cfg->bin_boundary + nb);
     h->cfg.n_bins = nullptr; h->cfg.is_categorical = nullptr; h->cfg.column_num = nullptr; h->cfg.bin_boundary = nullptr;
     h->enable_row_lists = (cfg->flags & SB_FLAG_NO_ROW_LISTS) == 0;
+    h->enable_subtraction = (cfg->flags & SB_FLAG_NO_SUBTRACTION) == 0;
     h->stats_size = is_variance(cfg->impurity) ? 3 : cfg->num_classes;
     h->stat_kind = is_variance(cfg->impurity) ? STAT_VARIANCE : STAT_CLASS;
     SB_CUDA(cudaMalloc(&h->d_feat_bins, sizeof(int32_t) * cfg->n_features));
@@ -713,7 +798,7 @@ SB_API void sb_destroy(sb_handle* h) {
     free_rowset(h->train);
     free_rowset(h->valid);
     for (auto& kv : h->trees) free_tree(kv.second);
-    h->raw.release(); h->stats.release(); h->tile_feats.release(); h->slot_fmask.release(); h->pair_off.release();
+    h->raw.release(); h->raw_prev.release(); h->d_pairs.release(); h->d_small_is_b.release(); h->stats.release(); h->tile_feats.release(); h->slot_fmask.release(); h->pair_off.release();
     h->slot_of_node.release(); h->tasks.release(); h->node_task_begin.release(); h->cand.release(); h->gain_out.release();
     h->cand_bits.release(); h->out_bits.release(); h->new_dropout.release(); h->new_weights.release();
     h->sort_keys.release(); h->sort_idx.release(); h->sort_tmp.release(); h->sort_flags.release();
@@ -890,7 +975,6 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     SB_CUDA(h->stats.reserve((size_t)std::max<int64_t>(total, 1)));
     SB_CUDA(cudaMemsetAsync(h->raw.p, 0, (size_t)(2 * total) * 8, h->stream));
     SB_CUDA(cudaMemsetAsync(h->d_acc, 0, 32, h->stream));
-    SB_CUDA(cudaMemsetAsync(h->d_maxbits, 0, 16, h->stream));
     SB_CUDA(cudaMemsetAsync(h->d_error_flag, 0, 4, h->stream));
     RowSet& tr = h->train;
     RowSet& va = h->valid;
@@ -1004,19 +1088,28 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
         }
     }
 
-    // fixed-point scales from the rows that can contribute this pass
-    {
-        const int W = h->cfg.weights_per_row;
+    // Fixed-point scales: maxima of the per-row contributions.  They change only when Data.output or the sample
+    // weights change, i.e. at a GBT tree switch (RF: never after load), so they are computed once per tree and
+    // the accumulators of all levels of a tree share one scale.
+    if (!h->scales_valid || (h->cfg.is_gbdt && in->switch_to_next_tree)) {
+        SB_CUDA(cudaMemsetAsync(h->d_maxbits, 0, 16, h->stream));
+        const int W = tr.weights ? h->cfg.weights_per_row : 1;
         std::vector<int> wcols;
-        for (const auto& nd : h->layout.nodes) {
-            const int c = nd.tree_id % W;
-            if (std::find(wcols.begin(), wcols.end(), c) == wcols.end()) wcols.push_back(c);
+        if (h->cfg.is_gbdt) {
+            for (const auto& nd : h->layout.nodes) {
+                const int c = nd.tree_id % W;
+                if (std::find(wcols.begin(), wcols.end(), c) == wcols.end()) wcols.push_back(c);
+            }
+            if (wcols.empty()) wcols.push_back((in->n_trees - 1) % W);
+        } else {
+            for (int c = 0; c < W; ++c) wcols.push_back(c);
         }
         for (int c : wcols) {
             SB_CUDA(launch_absmax(tr.n, tr.output, tr.significance, tr.weights ? tr.weights + (int64_t)c * tr.n : nullptr,
                                   h->d_maxbits, h->stream));
             h->launches_count += 1;
         }
+        h->scales_valid = true;
     }
     rc = plan_histograms(h, in);
     if (rc != SB_OK) return rc;
@@ -1099,6 +1192,12 @@ SB_API int sb_compute_finish(sb_handle* h, sb_iter_out* out) {
     SB_CUDA(cudaSetDevice(h->cfg.device));
     const int64_t total = h->layout.total;
     if (out->stats && out->stats_len < total) return fail(SB_ERR_INVALID, "stats buffer too small");
+    if (!h->pairs.empty()) {  // the larger child of every sibling pair = parent - smaller child (after the merge)
+        SB_CUDA(launch_pair_fixup(h->d_pairs.p, (int)h->pairs.size(), h->pair_max_len, h->d_small_is_b.p, h->raw_prev.p,
+                                  h->raw_prev.p + h->prev_layout.total, h->raw.p, h->raw.p + total, h->stream));
+        h->launches_count += 1;
+        h->pairs.clear();
+    }
     SB_CUDA(launch_finalize(h->raw.p, h->raw.p + total, total, h->stats_size, h->stat_kind, h->d_inv_scales, h->stats.p, h->stream));
     h->launches_count += 1;
     double acc[4];
@@ -1124,6 +1223,12 @@ SB_API int sb_compute_finish(sb_handle* h, sb_iter_out* out) {
     out->train_error = acc[2];
     out->validation_error = acc[3];
     h->stats_ready = true;
+    if (h->enable_subtraction) {  // keep this pass's merged accumulators for the children of its nodes
+        std::swap(h->raw, h->raw_prev);
+        h->prev_layout = h->layout;
+        h->prev_valid = true;
+    }
+    h->begun = false;
     return SB_OK;
 }
 

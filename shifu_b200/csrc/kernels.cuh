@@ -152,6 +152,24 @@ cudaError_t launch_check_bins(const void* const* cols, const int32_t* feat_bins,
 // raw (lo, hi) integer accumulators -> the reference's double statistics (one rounding each).
 cudaError_t launch_finalize(const int64_t* raw_lo, const int64_t* raw_hi, int64_t total, int stats_size, int kind,
                             const double* inv_scales, double* stats, cudaStream_t s);
+// Sibling pair whose parent's merged accumulators are still on the device (histogram subtraction).
+struct PairDesc {
+    int64_t parent_split_block;  // offset (in statistics) of the parent's block of its own split feature, in the previous pass
+    int64_t parent_off;          // offset of the parent's node block in the previous pass
+    int64_t off_a, off_b;        // offsets of the two children's node blocks in this pass (same feature lists => same layout)
+    int64_t len;                 // statistics per node block
+    const uint8_t* left_mask;    // device: the parent's left_mask (bit b: bin b goes to child A = 2*id)
+    int32_t n_bins;              // bins of the parent's split feature
+    int32_t node_a, node_b;      // heap ids 2p, 2p+1
+    int32_t slot;                // global slot index of the pair (row of pair_off)
+    int32_t table_off;           // offset of the tree's slot table inside the slot-table buffer
+    int32_t pad;
+};
+cudaError_t launch_pair_decide(const PairDesc* pairs, int n_pairs, const int64_t* prev_lo, const int64_t* prev_hi,
+                               int stats_size, int kind, int n_features, int16_t* slot_tables, int64_t* pair_off,
+                               int32_t* small_is_b, cudaStream_t s);
+cudaError_t launch_pair_fixup(const PairDesc* pairs, int n_pairs, int64_t max_len, const int32_t* small_is_b,
+                              const int64_t* prev_lo, const int64_t* prev_hi, int64_t* lo, int64_t* hi, cudaStream_t s);
 struct SplitTask {       // one (todo node, feature) pair
     int32_t node;        // todo index
     int32_t feature;     // feature slot

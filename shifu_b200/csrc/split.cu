@@ -257,41 +257,119 @@ __global__ void feature_split_kernel(const double* __restrict__ stats, const Spl
     cand[t] = g;
 }
 
-// GainInfo.getGainInfoByMaxGain over the features of one node, in the reference's visit order.
+// GainInfo.getGainInfoByMaxGain over the features of one node, in the reference's visit order: one warp per node.
+// "First strictly greater wins" == the maximum gain; among equal maxima the smallest visit rank.
 __global__ void node_best_kernel(const sb_gain* __restrict__ cand, const uint8_t* __restrict__ cand_bits,
                                  const SplitTask* __restrict__ tasks, const int32_t* __restrict__ node_task_begin,
                                  int n_nodes, sb_gain* out, uint8_t* out_bits) {
-    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
     if (n >= n_nodes) return;
     const int t0 = node_task_begin[n], t1 = node_task_begin[n + 1];
     double max_gain = JAVA_DOUBLE_MIN_VALUE;
     int best = -1, best_rank = 0x7fffffff;
-    // tasks of a node are stored in feature-list order; visit_rank gives the HashMap order.  "First strictly
-    // greater wins" == among equal maxima the one with the smallest rank.
-    for (int t = t0; t < t1; ++t) {
+    for (int t = t0 + lane; t < t1; t += 32) {
         if (!cand[t].found) continue;
         const double g = cand[t].gain;
-        if (g > max_gain || (g == max_gain && best >= 0 && tasks[t].visit_rank < best_rank)) {
+        const int rk = tasks[t].visit_rank;
+        if (g > max_gain || (g == max_gain && best >= 0 && rk < best_rank)) {
             max_gain = g;
             best = t;
-            best_rank = tasks[t].visit_rank;
+            best_rank = rk;
         }
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double og = __shfl_down_sync(0xffffffffu, max_gain, o);
+        const int ob = __shfl_down_sync(0xffffffffu, best, o);
+        const int ork = __shfl_down_sync(0xffffffffu, best_rank, o);
+        if (ob >= 0 && (best < 0 || og > max_gain || (og == max_gain && ork < best_rank))) {
+            max_gain = og;
+            best = ob;
+            best_rank = ork;
+        }
+    }
+    best = __shfl_sync(0xffffffffu, best, 0);
     if (best < 0) {
-        sb_gain z;
-        memset(&z, 0, sizeof(z));
-        out[n] = z;
+        if (lane == 0) {
+            sb_gain z;
+            memset(&z, 0, sizeof(z));
+            out[n] = z;
+        }
         return;
     }
-    out[n] = cand[best];
+    if (lane == 0) out[n] = cand[best];
     if (out_bits && cand[best].cat_bytes > 0) {
         const uint8_t* src = cand_bits + (size_t)best * SB_MAX_CAT_BYTES;
         uint8_t* dst = out_bits + (size_t)n * SB_MAX_CAT_BYTES;
-        for (int i = 0; i < cand[best].cat_bytes; ++i) dst[i] = src[i];
+        for (int i = lane; i < cand[best].cat_bytes; i += 32) dst[i] = src[i];
+    }
+}
+
+// ---- histogram subtraction (sibling = parent - child), exact in the integer accumulators
+// One thread per sibling pair: which child holds less (weighted) count under the parent's split?  Only that child is
+// accumulated directly; the other one is derived after the merge.  The decision is made from the parent's merged
+// (all-reduced) accumulators, so every GPU takes the same one.
+__global__ void pair_decide_kernel(const PairDesc* __restrict__ pairs, int n_pairs, const int64_t* __restrict__ prev_lo,
+                                   const int64_t* __restrict__ prev_hi, int stats_size, int kind, int n_features,
+                                   int16_t* __restrict__ slot_tables, int64_t* __restrict__ pair_off, int32_t* __restrict__ small_is_b) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pairs) return;
+    const PairDesc d = pairs[p];
+    const int per_bin = kind == STAT_VARIANCE ? 1 : stats_size;  // the count is stat 0 (variance) or the sum over classes
+    __int128 left = 0, total = 0;
+    for (int b = 0; b < d.n_bins; ++b) {
+        __int128 c = 0;
+        for (int k = 0; k < per_bin; ++k) {
+            const int64_t i = d.parent_split_block + (int64_t)b * stats_size + k;
+            c += ((__int128)prev_hi[i] << 32) + (__int128)prev_lo[i];
+        }
+        total += c;
+        if ((d.left_mask[b >> 3] >> (b & 7)) & 1) left += c;
+    }
+    const int b_small = (2 * left > total) ? 1 : 0;  // left = child A (even id); ties -> A
+    small_is_b[p] = b_small;
+    int16_t* table = slot_tables + d.table_off;
+    table[b_small ? d.node_a : d.node_b] = (int16_t)-1;  // the larger child is not accumulated
+    if (b_small) {
+        int64_t* row = pair_off + (size_t)d.slot * n_features;
+        for (int f = 0; f < n_features; ++f)
+            if (row[f] >= 0) row[f] += d.off_b - d.off_a;
+    }
+}
+
+__global__ void pair_fixup_kernel(const PairDesc* __restrict__ pairs, const int32_t* __restrict__ small_is_b,
+                                  const int64_t* __restrict__ prev_lo, const int64_t* __restrict__ prev_hi,
+                                  int64_t* __restrict__ lo, int64_t* __restrict__ hi) {
+    const PairDesc d = pairs[blockIdx.y];
+    const int64_t small_off = small_is_b[blockIdx.y] ? d.off_b : d.off_a;
+    const int64_t large_off = small_is_b[blockIdx.y] ? d.off_a : d.off_b;
+    for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < d.len; e += (int64_t)gridDim.x * blockDim.x) {
+        lo[large_off + e] = prev_lo[d.parent_off + e] - lo[small_off + e];
+        hi[large_off + e] = prev_hi[d.parent_off + e] - hi[small_off + e];
     }
 }
 
 }  // namespace
+
+cudaError_t launch_pair_decide(const PairDesc* pairs, int n_pairs, const int64_t* prev_lo, const int64_t* prev_hi,
+                               int stats_size, int kind, int n_features, int16_t* slot_tables, int64_t* pair_off,
+                               int32_t* small_is_b, cudaStream_t s) {
+    if (n_pairs <= 0) return cudaSuccess;
+    pair_decide_kernel<<<(n_pairs + 63) / 64, 64, 0, s>>>(pairs, n_pairs, prev_lo, prev_hi, stats_size, kind, n_features,
+                                                          slot_tables, pair_off, small_is_b);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pair_fixup(const PairDesc* pairs, int n_pairs, int64_t max_len, const int32_t* small_is_b,
+                              const int64_t* prev_lo, const int64_t* prev_hi, int64_t* lo, int64_t* hi, cudaStream_t s) {
+    if (n_pairs <= 0 || max_len <= 0) return cudaSuccess;
+    int64_t gx = (max_len + 255) / 256;
+    if (gx > 64) gx = 64;
+    dim3 grid((unsigned)gx, (unsigned)n_pairs);
+    pair_fixup_kernel<<<grid, 256, 0, s>>>(pairs, small_is_b, prev_lo, prev_hi, lo, hi);
+    return cudaGetLastError();
+}
 
 cudaError_t launch_finalize(const int64_t* raw_lo, const int64_t* raw_hi, int64_t total, int stats_size, int kind,
                             const double* inv_scales, double* stats, cudaStream_t s) {
@@ -312,7 +390,7 @@ cudaError_t launch_best_splits(const double* stats, const SplitTask* tasks, int 
                                                             sc.flags, sc.max_bins);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    node_best_kernel<<<(n_nodes + 63) / 64, 64, 0, s>>>(cand, cand_bits, tasks, node_task_begin, n_nodes, out, out_bits);
+    node_best_kernel<<<(n_nodes * 32 + 127) / 128, 128, 0, s>>>(cand, cand_bits, tasks, node_task_begin, n_nodes, out, out_bits);
     return cudaGetLastError();
 }
 

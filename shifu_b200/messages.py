@@ -33,6 +33,7 @@ class Node:
         self.right_predict = 0.0
         self.wgt_cnt = 0.0
         self.is_leaf = True
+        self._mask = None  # left_mask bytes, computed once the split is final (a split never changes afterwards)
 
     def walk(self):
         yield self
@@ -49,9 +50,9 @@ def left_mask(cfg, node):
     mask = bytearray(nb // 8 + 1)
     if not cfg.is_categorical[f]:
         bb = cfg.boundaries_of(f)
-        for b in range(nb):
-            if bb[b] < node.threshold:  # dt/DTWorker.java:1057-1062
-                mask[b >> 3] |= 1 << (b % 8)
+        bits = np.zeros((nb // 8 + 1) * 8, dtype=np.uint8)
+        bits[:nb] = bb < node.threshold  # dt/DTWorker.java:1057-1062
+        return np.packbits(bits, bitorder="little").tobytes()
     else:
         n_cats = nb - 1
         for b in range(nb):
@@ -64,45 +65,52 @@ def left_mask(cfg, node):
     return bytes(mask)
 
 
+NODE_DTYPE = np.dtype([("id", "<i4"), ("left", "<i4"), ("right", "<i4"), ("feature", "<i4"), ("split_type", "<i4"),
+                       ("left_mask_offset", "<i4"), ("left_mask_bytes", "<i4"), ("has_predict", "<i4"),
+                       ("predict", "<f8"), ("threshold", "<f8"), ("is_left", "<i4"), ("cat_offset", "<i4"),
+                       ("cat_bytes", "<i4"), ("reserved", "<i4")], align=True)
+assert NODE_DTYPE.itemsize == C.sizeof(SbNode)
+
+
+TODO_DTYPE = np.dtype([("key", "<i4"), ("tree_id", "<i4"), ("node_id", "<i4"), ("n_features", "<i4"),
+                       ("features", "<u8")], align=True)
+assert TODO_DTYPE.itemsize == C.sizeof(SbTodoNode)
+
+
 class FlatTree:
-    """An sb_tree plus the arrays it points at."""
+    """An sb_tree plus the arrays it points at (sb_node records are filled through a numpy structured array)."""
 
     def __init__(self, cfg, tree_id, root):
         self.tree_id = tree_id
         if root is None:  # placeholder tree (root id INVALID_INDEX, dt/DTMaster.java:500-504)
-            self.nodes = (SbNode * 1)()
+            self.nodes = np.zeros(1, dtype=NODE_DTYPE)
             self.pool = np.zeros(1, dtype=np.uint8)
             n_nodes = 0
         else:
             lst = list(root.walk())
             index = {id(n): i for i, n in enumerate(lst)}
-            self.nodes = (SbNode * len(lst))()
             pool = bytearray()
-            for i, n in enumerate(lst):
-                s = self.nodes[i]
-                s.id = n.id
-                s.left = index[id(n.left)] if n.left is not None else -1
-                s.right = index[id(n.right)] if n.right is not None else -1
-                s.feature = n.feature
-                s.split_type = n.split_type
-                s.has_predict = 0 if n.predict is None else 1
-                s.predict = 0.0 if n.predict is None else float(n.predict)
-                s.threshold = float(n.threshold)
-                s.is_left = int(bool(n.is_left))
+            recs = []
+            for n in lst:
+                mo = mb = co = cb = 0
                 if n.feature >= 0:
-                    m = left_mask(cfg, n)
-                    s.left_mask_offset = len(pool)
-                    s.left_mask_bytes = len(m)
-                    pool += m
-                    s.cat_offset = len(pool)
-                    s.cat_bytes = len(n.cat_bits)
+                    if n._mask is None:
+                        n._mask = left_mask(cfg, n)
+                    mo, mb = len(pool), len(n._mask)
+                    pool += n._mask
+                    co, cb = len(pool), len(n.cat_bits)
                     pool += n.cat_bits
+                recs.append((n.id, index[id(n.left)] if n.left is not None else -1,
+                             index[id(n.right)] if n.right is not None else -1, n.feature, n.split_type, mo, mb,
+                             0 if n.predict is None else 1, 0.0 if n.predict is None else n.predict, n.threshold,
+                             1 if n.is_left else 0, co, cb, 0))
+            self.nodes = np.array(recs, dtype=NODE_DTYPE)
             self.pool = np.frombuffer(bytes(pool) + b"\0", dtype=np.uint8).copy()
             n_nodes = len(lst)
         t = SbTree()
         t.tree_id = tree_id
         t.n_nodes = n_nodes
-        t.nodes = C.cast(self.nodes, C.POINTER(SbNode))
+        t.nodes = C.cast(self.nodes.ctypes.data, C.POINTER(SbNode))
         t.mask_pool = self.pool.ctypes.data_as(C.POINTER(C.c_uint8))
         t.mask_pool_bytes = len(self.pool) - 1
         self.struct = t
@@ -116,17 +124,21 @@ class IterIn:
                  dropout=None):
         self.flat = [FlatTree(cfg, tid, root) for tid, root in trees]
         self.trees = (SbTree * max(len(self.flat), 1))(*[f.struct for f in self.flat])
-        self.todo_feats = [np.ascontiguousarray(t[3], dtype=np.int32) for t in todo]
-        self.todo = (SbTodoNode * max(len(todo), 1))()
-        for i, t in enumerate(todo):
-            self.todo[i].key, self.todo[i].tree_id, self.todo[i].node_id = t[0], t[1], t[2]
-            self.todo[i].n_features = len(self.todo_feats[i])
-            self.todo[i].features = self.todo_feats[i].ctypes.data_as(C.POINTER(C.c_int32))
+        # sb_todo_node records through a structured array; all feature lists share one int32 pool
+        flat_feats = [f for t in todo for f in t[3]]
+        self.todo_feats = np.array(flat_feats if flat_feats else [0], dtype=np.int32)
+        base = self.todo_feats.ctypes.data
+        recs, off = [], 0
+        for t in todo:
+            nf = len(t[3])
+            recs.append((t[0], t[1], t[2], nf, base + 4 * off))
+            off += nf
+        self.todo = np.array(recs if recs else [(0, 0, 0, 0, 0)], dtype=TODO_DTYPE)
         s = SbIterIn()
         s.n_trees = len(self.flat)
         s.trees = C.cast(self.trees, C.POINTER(SbTree))
         s.n_todo = len(todo)
-        s.todo = C.cast(self.todo, C.POINTER(SbTodoNode))
+        s.todo = C.cast(self.todo.ctypes.data, C.POINTER(SbTodoNode))
         s.switch_to_next_tree = int(bool(switch_to_next_tree))
         s.is_first_tree = int(bool(is_first_tree))
         s.continuous_running_start = 0

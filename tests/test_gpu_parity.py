@@ -153,6 +153,40 @@ def test_gbt_deep_levels_row_lists_and_tile_groups():
     run_gbt(30000, [64] * 40, seed=19, n_trees=2, max_depth=6, bagging=True, feature_subsets=True)
 
 
+def test_histogram_subtraction_is_exact():
+    """sibling = parent - child on the integer accumulators must give the very same statistics as accumulating every
+    node directly (SB_FLAG_NO_SUBTRACTION), bit for bit, weighted or not."""
+    n, n_bins = 25000, [64] * 30 + [16] * 6
+    cols, y, sig, _ = make_data(n, n_bins, seed=41, weighted=True)
+    runs = []
+    for flags in (0, 4):
+        cfg = ConfigArrays(n_bins, max_depth=6, min_instances_per_node=1, flags=flags)
+        w = Worker(cfg)
+        w.load_rows(cols, y, sig, None)
+        root = Node(1)
+        todo_nodes, switch, stats_all = [root], True, []
+        while todo_nodes:
+            todo = [(k, 0, nd.id, []) for k, nd in enumerate(todo_nodes)]
+            it = IterIn(cfg, [(0, root)], todo, switch_to_next_tree=switch, is_first_tree=True)
+            res = w.compute(it)
+            stats_all.append(res[4].copy())
+            gains, bits = w.best_splits(len(todo))
+            nxt = []
+            for k, nd in enumerate(todo_nodes):
+                g = gains[k]
+                if not g.found or g.gain <= 0 or index_to_level(nd.id) == 6:
+                    continue
+                left, right = apply_gain(cfg, nd, g, bits, k)
+                if index_to_level(nd.id) + 1 < 6:
+                    nxt += [left, right]
+            todo_nodes, switch = nxt, False
+        runs.append(stats_all)
+        w.close()
+    assert len(runs[0]) == len(runs[1]) >= 5
+    for a, b in zip(runs[0], runs[1]):
+        assert np.array_equal(a, b)
+
+
 def test_gbt_weighted_mixed_bins():
     run_gbt(15000, [64] * 20 + [32] * 10 + [10] * 7 + [2, 1, 255], seed=12, n_trees=2, max_depth=4, weighted=True)
 

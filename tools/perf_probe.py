@@ -34,7 +34,7 @@ while it is not None:
     gains, bits = w.best_splits(it.n_todo)
     wall = (time.time() - t0) * 1e3
     ms, npass, nl = w.hist_time()
-    lvl = max(t[2] for t in [(0, 0, it.todo[i].node_id) for i in range(it.n_todo)]).bit_length()
+    lvl = int(max(it.todo["node_id"][:it.n_todo])).bit_length()
     print("tree %d level %d todo %3d  hist %.3f ms  wall %.3f ms  %.1f GB/s (algorithmic)  %.3e cells/s  err=%.6g" % (
         len(m.trees) - 1, lvl, it.n_todo, ms, wall, algo_bytes / ms / 1e6, a.rows * a.features / ms * 1e3,
         sc[2] / max(sc[0], 1)))
