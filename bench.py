@@ -116,7 +116,7 @@ def grow_tree(worker, master, it, dist_ctx, e2e_buffers=None):
     """One GBT tree through the device path; returns (next message, passes, last scalars)."""
     from shifu_b200 import capi
     passes = 0
-    tree_index = len(master.trees)
+    tree_index = master.n_trees
     scalars = None
     while it is not None:
         if e2e_buffers is None and dist_ctx is None:
@@ -137,13 +137,16 @@ def grow_tree(worker, master, it, dist_ctx, e2e_buffers=None):
             import torch
             import torch.distributed as dist
             worker.compute_begin(it)
+            scales_fresh, acc_fresh = worker.pass_info()
             sp, sb, rp, rb, ap_, ab = worker.device_buffers()
-            dist.all_reduce(torch.as_tensor(DevView(sp, 3, "<i4"), device="cuda"), op=dist.ReduceOp.MAX)
+            if scales_fresh:
+                dist.all_reduce(torch.as_tensor(DevView(sp, 3, "<i4"), device="cuda"), op=dist.ReduceOp.MAX)
             worker.compute_stats()
             sp, sb, rp, rb, ap_, ab = worker.device_buffers()
-            if rb > 0:
+            if rb > 0:  # the DTMaster merge: one integer all-reduce per pass
                 dist.all_reduce(torch.as_tensor(DevView(rp, rb // 8, "<i8"), device="cuda"), op=dist.ReduceOp.SUM)
-            dist.all_reduce(torch.as_tensor(DevView(ap_, 4, "<f8"), device="cuda"), op=dist.ReduceOp.SUM)
+            if acc_fresh:
+                dist.all_reduce(torch.as_tensor(DevView(ap_, 4, "<f8"), device="cuda"), op=dist.ReduceOp.SUM)
             if e2e_buffers is None:
                 scalars = worker.compute_finish()
             else:
@@ -157,15 +160,14 @@ def grow_tree(worker, master, it, dist_ctx, e2e_buffers=None):
         gains, bits = worker.best_splits(it.n_todo)
         passes += 1
         it = master.do_compute(gains, bits)
-        if it is None or len(master.trees) != tree_index:
+        if it is None or master.n_trees != tree_index:
             break
     return it, passes, scalars
 
 
 def run_b200(a):
     import torch
-    from shifu_b200.capi import ConfigArrays, Worker
-    from shifu_b200.dt_master import DTMaster
+    from shifu_b200.capi import ConfigArrays, NativeMaster, Worker
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -185,7 +187,7 @@ def run_b200(a):
                        min_instances_per_node=5, device=local_rank)
     worker = Worker(cfg)
     worker.load_synthetic(rows_local, seed=SEED, row0=row0, label_kind=0)
-    master = DTMaster(cfg, tree_num=n_trees_total, max_depth=a.depth, learning_rate=0.05, worker_number=world)
+    master = NativeMaster(cfg, tree_num=n_trees_total, max_depth=a.depth, learning_rate=0.05, worker_number=world)
     it = master.build_initial_master_params()
 
     def barrier():

@@ -250,6 +250,10 @@ SB_API int sb_compute(sb_handle* h, const sb_iter_in* in, sb_iter_out* out);
  * sb_compute_begin returns without synchronising.
  */
 SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in);
+/* After sb_compute_begin: were the scale maxima / the 4 scalars recomputed by this pass?  Inside a GBT tree neither
+   changes (output, weights and predict move only at a tree switch), so a multi-GPU driver all-reduces them only when
+   the flag is set; a buffer that was not recomputed still holds the already-reduced values. */
+SB_API int sb_pass_info(sb_handle* h, int32_t* scales_fresh, int32_t* acc_fresh);
 SB_API int sb_scale_buffer(sb_handle* h, void** dev_ptr, int64_t* bytes);
 SB_API int sb_compute_stats(sb_handle* h);
 SB_API int sb_raw_buffer(sb_handle* h, void** dev_ptr, int64_t* bytes);
@@ -266,6 +270,46 @@ SB_API int sb_set_stream(sb_handle* h, void* cuda_stream);
  * gains: [n_todo]; cat_bits: [n_todo * SB_MAX_CAT_BYTES] or NULL when no categorical feature exists.
  */
 SB_API int sb_best_splits(sb_handle* h, sb_gain* gains, uint8_t* cat_bits);
+
+/* ------------------------------------------------------------------ host mirror of DTMaster (no CUDA) */
+
+/* core/dtrain/FeatureSubsetStrategy.java:23-31; SBH_FSS_RATE = "featureSubsetStrategy is a number" (dt/DTMaster.java:823-825) */
+enum { SBH_FSS_ALL = 0, SBH_FSS_HALF = 1, SBH_FSS_ONETHIRD = 2, SBH_FSS_TWOTHIRDS = 3, SBH_FSS_AUTO = 4, SBH_FSS_SQRT = 5,
+       SBH_FSS_LOG2 = 6, SBH_FSS_RATE = 7 };
+
+/* The train.params DTMaster.init reads (dt/DTMaster.java:932-1051). */
+typedef struct sbh_params {
+    int32_t tree_num;                /* "TreeNum" */
+    int32_t max_depth;               /* "MaxDepth" */
+    int32_t is_gbdt;
+    int32_t feature_subset_strategy; /* SBH_FSS_* */
+    double feature_subset_rate;      /* used with SBH_FSS_RATE */
+    double learning_rate;            /* "LearningRate": TreeNode.learningRate of every tree but the first (:421, :1108) */
+    int64_t feature_sampling_seed;   /* the reference's featureSamplingRandom is unseeded (:246); injected here */
+    int32_t max_leaves;              /* "MaxLeaves": > 0 switches to leaf-wise growth (:980-982) */
+    int32_t max_batch_split_size;    /* "MaxBatchSplitSize" (unused by the reference's loop, :359-363) */
+    int64_t max_stats_memory;        /* "MaxStatsMemoryMB" in bytes (:1001-1013) */
+    int32_t worker_number;           /* workers the statistics memory estimate is scaled by (:745) */
+    int32_t reserved;
+} sbh_params;
+
+typedef struct sbh_master sbh_master;
+
+/* DTMaster.init (dt/DTMaster.java:896-1116): cfg needs bin_boundary (split thresholds are boundary values). */
+SB_API int sbh_master_create(const sb_config* cfg, const sbh_params* params, sbh_master** out);
+SB_API void sbh_master_destroy(sbh_master* m);
+/* buildInitialMasterParams (dt/DTMaster.java:759-820): the first DTMasterParams, flattened.  The returned message and
+   everything it points at stay valid until the next sbh_master_* call on this object. */
+SB_API const sb_iter_in* sbh_master_initial(sbh_master* m);
+/* DTMaster.doCompute (dt/DTMaster.java:316-537) fed with the sb_gain records of sb_best_splits for the todo nodes of
+   the previous message (same order).  Returns the next message, or NULL when training halts (:396-407, :431-435). */
+SB_API const sb_iter_in* sbh_master_do_compute(sbh_master* m, const sb_gain* gains, const uint8_t* cat_bits);
+SB_API int sbh_master_tree_count(sbh_master* m);
+SB_API int sbh_master_halted(sbh_master* m);
+/* Copies tree `index` out: sb_node records in pre-order + mask pool, and per node 7 doubles
+   (gain, impurity, leftImpurity, rightImpurity, leftPredict, rightPredict, wgtCnt).  Call with nodes == NULL to size. */
+SB_API int sbh_master_export_tree(sbh_master* m, int index, sb_node* nodes, int node_cap, uint8_t* pool, int pool_cap,
+                                  double* extras, int* n_nodes, int* pool_bytes);
 
 /*
  * No counterpart in the reference.  Weighted error sums of a row set -- out[0] = sum(significance),

@@ -128,13 +128,35 @@ class SbGain(C.Structure):
     ]
 
 
+class SbhParams(C.Structure):
+    _fields_ = [
+        ("tree_num", C.c_int32),
+        ("max_depth", C.c_int32),
+        ("is_gbdt", C.c_int32),
+        ("feature_subset_strategy", C.c_int32),
+        ("feature_subset_rate", C.c_double),
+        ("learning_rate", C.c_double),
+        ("feature_sampling_seed", C.c_int64),
+        ("max_leaves", C.c_int32),
+        ("max_batch_split_size", C.c_int32),
+        ("max_stats_memory", C.c_int64),
+        ("worker_number", C.c_int32),
+        ("reserved", C.c_int32),
+    ]
+
+
+SBH_FSS = {"ALL": 0, "HALF": 1, "ONETHIRD": 2, "TWOTHIRDS": 3, "AUTO": 4, "SQRT": 5, "LOG2": 6, None: 7}
+
+
 # every symbol include/shifu_b200.h declares (tests check that the library exports all of them)
 EXPORTS = [
     "sb_create", "sb_destroy", "sb_last_error", "sb_version", "sb_load_rows", "sb_load_rows_device", "sb_read_rows",
     "sb_stats_len", "sb_compute", "sb_compute_begin", "sb_scale_buffer", "sb_compute_stats", "sb_raw_buffer",
     "sb_acc_buffer", "sb_compute_finish", "sb_set_stream", "sb_best_splits", "sb_time_stats_pass", "sb_counters",
     "sb_load_synthetic", "sb_read_bins", "sb_read_labels", "sb_set_profiling", "sb_hist_time",
-    "sb_error_sums_static",
+    "sb_error_sums_static", "sb_pass_info",
+    "sbh_master_create", "sbh_master_destroy", "sbh_master_initial", "sbh_master_do_compute", "sbh_master_tree_count",
+    "sbh_master_halted", "sbh_master_export_tree",
 ]
 
 _lib = None
@@ -178,6 +200,17 @@ def load_library(path=None):
     lib.sb_read_labels.argtypes = [H, C.c_int32, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]
     lib.sb_set_profiling.argtypes = [H, C.c_int32]
     lib.sb_hist_time.argtypes = [H, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    lib.sb_pass_info.argtypes = [H, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    lib.sbh_master_create.argtypes = [C.POINTER(SbConfig), C.POINTER(SbhParams), C.POINTER(H)]
+    lib.sbh_master_destroy.argtypes = [H]
+    lib.sbh_master_destroy.restype = None
+    lib.sbh_master_initial.argtypes = [H]
+    lib.sbh_master_initial.restype = C.POINTER(SbIterIn)
+    lib.sbh_master_do_compute.argtypes = [H, C.POINTER(SbGain), C.c_void_p]
+    lib.sbh_master_do_compute.restype = C.POINTER(SbIterIn)
+    lib.sbh_master_tree_count.argtypes = [H]
+    lib.sbh_master_halted.argtypes = [H]
+    lib.sbh_master_export_tree.argtypes = [H, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.sb_error_sums_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]
     if path is None:
         _lib = lib
@@ -320,6 +353,12 @@ class Worker:
     def compute_begin(self, it):
         check(self.lib, self.lib.sb_compute_begin(self.h, C.byref(it.struct)))
 
+    def pass_info(self):
+        """(scales_fresh, acc_fresh) of the last compute_begin: which small buffers need an all-reduce this pass."""
+        a, b = C.c_int32(), C.c_int32()
+        check(self.lib, self.lib.sb_pass_info(self.h, C.byref(a), C.byref(b)))
+        return bool(a.value), bool(b.value)
+
     def compute_stats(self):
         check(self.lib, self.lib.sb_compute_stats(self.h))
 
@@ -345,7 +384,7 @@ class Worker:
         gains = (SbGain * max(n_todo, 1))()
         bits = np.zeros(max(n_todo, 1) * SB_MAX_CAT_BYTES, dtype=np.uint8) if with_cat else None
         check(self.lib, self.lib.sb_best_splits(self.h, gains, None if bits is None else bits.ctypes.data))
-        return list(gains)[:n_todo], bits
+        return gains, bits  # gains: ctypes array, entries [0, n_todo) are valid
 
     def time_stats_pass(self, n_repeat=3):
         a, b = C.c_float(), C.c_float()
@@ -368,3 +407,70 @@ class Worker:
 
     def set_stream(self, stream_ptr):
         check(self.lib, self.lib.sb_set_stream(self.h, C.c_void_p(stream_ptr)))
+
+
+class NativeMessage:
+    """A DTMasterParams message owned by a NativeMaster (valid until its next call); duck-types messages.IterIn."""
+
+    def __init__(self, ptr):
+        self.struct = ptr.contents
+        self.n_todo = self.struct.n_todo
+
+    @property
+    def todo(self):
+        n = self.n_todo
+        return {"node_id": np.array([self.struct.todo[i].node_id for i in range(n)], dtype=np.int32)}
+
+
+class NativeMaster:
+    """The C++ DTMaster mirror (csrc/host_master.cpp) behind the sbh_* entry points."""
+
+    def __init__(self, cfg: ConfigArrays, tree_num, max_depth, is_gbdt=True, learning_rate=0.05,
+                 feature_subset_strategy="ALL", feature_subset_rate=1.0, feature_sampling_seed=0, max_leaves=-1,
+                 max_batch_split_size=32, max_stats_memory=256 << 20, worker_number=1):
+        self.lib = load_library()
+        self.cfg = cfg
+        p = SbhParams()
+        p.tree_num, p.max_depth, p.is_gbdt = tree_num, max_depth, int(bool(is_gbdt))
+        p.feature_subset_strategy = SBH_FSS[feature_subset_strategy]
+        p.feature_subset_rate, p.learning_rate = feature_subset_rate, learning_rate
+        p.feature_sampling_seed, p.max_leaves = feature_sampling_seed, max_leaves
+        p.max_batch_split_size, p.max_stats_memory, p.worker_number = max_batch_split_size, max_stats_memory, worker_number
+        self.h = C.c_void_p()
+        check(self.lib, self.lib.sbh_master_create(C.byref(cfg.struct), C.byref(p), C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            self.lib.sbh_master_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def build_initial_master_params(self):
+        return NativeMessage(self.lib.sbh_master_initial(self.h))
+
+    def do_compute(self, gains, cat_bits=None):
+        """gains: the (SbGain * n) array or list returned by Worker.best_splits."""
+        if isinstance(gains, list):
+            gains = (SbGain * max(len(gains), 1))(*gains)
+        ptr = self.lib.sbh_master_do_compute(self.h, gains, None if cat_bits is None else cat_bits.ctypes.data)
+        return NativeMessage(ptr) if ptr else None
+
+    @property
+    def n_trees(self):
+        return self.lib.sbh_master_tree_count(self.h)
+
+    def export_tree(self, index):
+        """(nodes structured array in pre-order, mask pool bytes, extras [n, 7])."""
+        nn, pb = C.c_int(), C.c_int()
+        check(self.lib, self.lib.sbh_master_export_tree(self.h, index, None, 0, None, 0, None, C.byref(nn), C.byref(pb)))
+        nodes = (SbNode * max(nn.value, 1))()
+        pool = np.zeros(max(pb.value, 1), dtype=np.uint8)
+        extras = np.zeros((max(nn.value, 1), 7), dtype=np.float64)
+        check(self.lib, self.lib.sbh_master_export_tree(self.h, index, nodes, nn.value, pool.ctypes.data, pb.value,
+                                                        extras.ctypes.data, C.byref(nn), C.byref(pb)))
+        return list(nodes)[:nn.value], pool[:pb.value], extras[:nn.value]

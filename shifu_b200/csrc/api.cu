@@ -120,6 +120,8 @@ struct sb_handle {
     DevBuf<int32_t> rt_tiles;     // row-list path: tile_feats [n_rt][32*fpl] then tile_slot0 [n_rt]
     DevBuf<uint32_t> rt_fmask;    // [n_slots][n_rt][fpl]
     bool enable_row_lists = true;
+    bool acc_valid = false;     // d_acc holds the error sums of the current Data.predict (GBT, inside a tree)
+    bool acc_fresh = false, scales_fresh = false;  // recomputed by the last sb_compute_begin (=> need an all-reduce)
     bool scales_valid = false;  // d_maxbits holds the maxima of the current tree's contributions
     bool cnt_int = false;  // every sig*weight product of the training rows is an integer in [0, 1024]
 
@@ -974,7 +976,12 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     SB_CUDA(h->raw.reserve((size_t)std::max<int64_t>(2 * total, 1)));
     SB_CUDA(h->stats.reserve((size_t)std::max<int64_t>(total, 1)));
     SB_CUDA(cudaMemsetAsync(h->raw.p, 0, (size_t)(2 * total) * 8, h->stream));
-    SB_CUDA(cudaMemsetAsync(h->d_acc, 0, 32, h->stream));
+    // GBT error sums are sums over Data.predict, which only changes at a tree switch (dt/DTWorker.java:627-640, 681):
+    // inside a tree (after the first one) the four scalars of the previous pass are still the answer.
+    const bool errors_from_tree = h->cfg.is_gbdt && in->is_first_tree && !in->switch_to_next_tree;
+    const bool need_errors = !h->cfg.is_gbdt || in->switch_to_next_tree || errors_from_tree || !h->acc_valid;
+    h->acc_fresh = need_errors;
+    if (need_errors) SB_CUDA(cudaMemsetAsync(h->d_acc, 0, 32, h->stream));
     SB_CUDA(cudaMemsetAsync(h->d_error_flag, 0, 4, h->stream));
     RowSet& tr = h->train;
     RowSet& va = h->valid;
@@ -1042,7 +1049,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
         const TreeView cv = view_of(dcur);
         SB_CUDA(launch_route(tr.d_col, tr.n, tr.node_id, cv, h->d_error_flag, h->stream));
         h->launches_count += 1;
-        const bool from_tree = in->is_first_tree && !in->switch_to_next_tree;  // dt/DTWorker.java:672-683
+        const bool from_tree = errors_from_tree;  // dt/DTWorker.java:672-683
         if (va.loaded && from_tree) {
             SB_CUDA(launch_route(va.d_col, va.n, va.node_id, cv, h->d_error_flag, h->stream));
             h->launches_count += 1;
@@ -1050,13 +1057,16 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
         ErrArgs e{};
         e.n = tr.n; e.label = tr.label; e.predict = tr.predict; e.significance = tr.significance; e.weights = nullptr;
         e.node_id = tr.node_id; e.tree = cv; e.from_tree = from_tree ? 1 : 0; e.loss = loss; e.is_validation = 0; e.rf_oob = 0;
-        SB_CUDA(launch_errors(e, h->d_err_scratch, h->d_acc, h->stream));
-        h->launches_count += 1;
-        if (va.loaded) {
-            e.n = va.n; e.label = va.label; e.predict = va.predict; e.significance = va.significance; e.node_id = va.node_id;
-            e.is_validation = 1;
+        if (need_errors) {
             SB_CUDA(launch_errors(e, h->d_err_scratch, h->d_acc, h->stream));
             h->launches_count += 1;
+            if (va.loaded) {
+                e.n = va.n; e.label = va.label; e.predict = va.predict; e.significance = va.significance; e.node_id = va.node_id;
+                e.is_validation = 1;
+                SB_CUDA(launch_errors(e, h->d_err_scratch, h->d_acc, h->stream));
+                h->launches_count += 1;
+            }
+            h->acc_valid = !from_tree;  // sums over the current tree's leaves change with every level
         }
     } else {
         // RF (dt/DTWorker.java:583-605, 691-705): every real tree is walked for the error sums
@@ -1091,7 +1101,9 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     // Fixed-point scales: maxima of the per-row contributions.  They change only when Data.output or the sample
     // weights change, i.e. at a GBT tree switch (RF: never after load), so they are computed once per tree and
     // the accumulators of all levels of a tree share one scale.
+    h->scales_fresh = false;
     if (!h->scales_valid || (h->cfg.is_gbdt && in->switch_to_next_tree)) {
+        h->scales_fresh = true;
         SB_CUDA(cudaMemsetAsync(h->d_maxbits, 0, 16, h->stream));
         const int W = tr.weights ? h->cfg.weights_per_row : 1;
         std::vector<int> wcols;
@@ -1123,6 +1135,13 @@ SB_API int sb_scale_buffer(sb_handle* h, void** dev_ptr, int64_t* bytes) {
     if (!h || !dev_ptr) return fail(SB_ERR_INVALID, "null argument");
     *dev_ptr = h->d_maxbits;
     if (bytes) *bytes = 12;
+    return SB_OK;
+}
+
+SB_API int sb_pass_info(sb_handle* h, int32_t* scales_fresh, int32_t* acc_fresh) {
+    if (!h) return fail(SB_ERR_INVALID, "null handle");
+    if (scales_fresh) *scales_fresh = h->scales_fresh ? 1 : 0;
+    if (acc_fresh) *acc_fresh = h->acc_fresh ? 1 : 0;
     return SB_OK;
 }
 

@@ -98,6 +98,10 @@ class DTMaster:
         self.iteration = 0
         self.stats_size = cfg.stats_size
 
+    @property
+    def n_trees(self):
+        return len(self.trees)
+
     # ---- feature sub-sampling, dt/DTMaster.java:822-850, 880-893
     def get_subsampling_features(self):
         n = len(self.all_features)

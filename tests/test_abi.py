@@ -22,7 +22,7 @@ def lib():
 
 def declared_symbols():
     src = open(HEADER).read()
-    return sorted(set(re.findall(r"SB_API\s+[A-Za-z_0-9\s\*]+?\b(sb_[a-z_0-9]+)\s*\(", src)))
+    return sorted(set(re.findall(r"SB_API\s+[A-Za-z_0-9\s\*]+?\b(sbh?_[a-z_0-9]+)\s*\(", src)))
 
 
 def test_header_symbols_all_exported(lib):

@@ -28,12 +28,15 @@ it = m.build_initial_master_params()
 n_iter = 0
 while it is not None:
     w.compute_begin(it)
+    scales_fresh, acc_fresh = w.pass_info()
     sp, sb, rp, rb, ap, ab = w.device_buffers()
-    dist.all_reduce(torch.as_tensor(DevView(sp, 3, "<i4"), device="cuda"), op=dist.ReduceOp.MAX)
+    if scales_fresh:
+        dist.all_reduce(torch.as_tensor(DevView(sp, 3, "<i4"), device="cuda"), op=dist.ReduceOp.MAX)
     w.compute_stats()
     sp, sb, rp, rb, ap, ab = w.device_buffers()
     dist.all_reduce(torch.as_tensor(DevView(rp, rb // 8, "<i8"), device="cuda"), op=dist.ReduceOp.SUM)
-    dist.all_reduce(torch.as_tensor(DevView(ap, 4, "<f8"), device="cuda"), op=dist.ReduceOp.SUM)
+    if acc_fresh:
+        dist.all_reduce(torch.as_tensor(DevView(ap, 4, "<f8"), device="cuda"), op=dist.ReduceOp.SUM)
     n = w.stats_len(it)
     sc = w.compute_finish(n, want_stats=True)
     gains, bits = w.best_splits(it.n_todo)

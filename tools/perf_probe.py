@@ -6,7 +6,7 @@ import time
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from shifu_b200.capi import ConfigArrays, Worker  # noqa: E402
-from shifu_b200.dt_master import DTMaster  # noqa: E402
+from shifu_b200.capi import NativeMaster  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--rows", type=int, default=10_000_000)
@@ -23,20 +23,29 @@ t0 = time.time()
 w.load_synthetic(a.rows, seed=1002, weighted=bool(a.weighted))
 print("load_synthetic %.2fs" % (time.time() - t0))
 w.set_profiling(True)
-m = DTMaster(cfg, tree_num=a.trees, max_depth=a.depth, learning_rate=0.05)
+m = NativeMaster(cfg, tree_num=a.trees, max_depth=a.depth, learning_rate=0.05)
 it = m.build_initial_master_params()
 algo_bytes = a.rows * (a.features + 16)
+tm = time.time()
 while it is not None:
     t0 = time.time()
     w.compute_begin(it)
+    t1 = time.time()
     w.compute_stats()
+    t2 = time.time()
     sc = w.compute_finish()
+    t3 = time.time()
     gains, bits = w.best_splits(it.n_todo)
-    wall = (time.time() - t0) * 1e3
+    t4 = time.time()
+    wall = (t4 - t0) * 1e3
+    host_master = (t0 - tm) * 1e3
+    print("   host: master+message %.2f  begin %.2f  stats %.2f  finish(sync) %.2f  best_splits %.2f ms" % (
+        host_master, (t1 - t0) * 1e3, (t2 - t1) * 1e3, (t3 - t2) * 1e3, (t4 - t3) * 1e3))
     ms, npass, nl = w.hist_time()
-    lvl = int(max(it.todo["node_id"][:it.n_todo])).bit_length()
+    lvl = int(max(it.struct.todo[i].node_id for i in range(it.n_todo))).bit_length()
     print("tree %d level %d todo %3d  hist %.3f ms  wall %.3f ms  %.1f GB/s (algorithmic)  %.3e cells/s  err=%.6g" % (
-        len(m.trees) - 1, lvl, it.n_todo, ms, wall, algo_bytes / ms / 1e6, a.rows * a.features / ms * 1e3,
+        m.n_trees - 1, lvl, it.n_todo, ms, wall, algo_bytes / ms / 1e6, a.rows * a.features / ms * 1e3,
         sc[2] / max(sc[0], 1)))
+    tm = time.time()
     it = m.do_compute(gains, bits)
 w.close()
