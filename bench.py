@@ -136,17 +136,17 @@ def grow_tree(worker, master, it, dist_ctx, e2e_buffers=None):
         else:
             import torch
             import torch.distributed as dist
+            from shifu_b200.sharding import reduce_pass
             worker.compute_begin(it)
             scales_fresh, acc_fresh = worker.pass_info()
             sp, sb, rp, rb, ap_, ab = worker.device_buffers()
-            if scales_fresh:
-                dist.all_reduce(torch.as_tensor(DevView(sp, 3, "<i4"), device="cuda"), op=dist.ReduceOp.MAX)
+            reduce_pass(dist, torch.as_tensor(DevView(sp, 3, "<i4"), device="cuda") if scales_fresh else None, None, None,
+                        scales_fresh, False)
             worker.compute_stats()
             sp, sb, rp, rb, ap_, ab = worker.device_buffers()
-            if rb > 0:  # the DTMaster merge: one integer all-reduce per pass
-                dist.all_reduce(torch.as_tensor(DevView(rp, rb // 8, "<i8"), device="cuda"), op=dist.ReduceOp.SUM)
-            if acc_fresh:
-                dist.all_reduce(torch.as_tensor(DevView(ap_, 4, "<f8"), device="cuda"), op=dist.ReduceOp.SUM)
+            # the DTMaster merge: one integer all-reduce per pass (+ the 4 scalars when they were recomputed)
+            reduce_pass(dist, None, torch.as_tensor(DevView(rp, rb // 8, "<i8"), device="cuda") if rb > 0 else None,
+                        torch.as_tensor(DevView(ap_, 4, "<f8"), device="cuda") if acc_fresh else None, False, acc_fresh)
             if e2e_buffers is None:
                 scalars = worker.compute_finish()
             else:
@@ -179,8 +179,8 @@ def run_b200(a):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         dist_ctx = dist
     n_gpus = world
-    rows_local = a.rows // world + (1 if rank < a.rows % world else 0)
-    row0 = rank * (a.rows // world) + min(rank, a.rows % world)
+    from shifu_b200.sharding import shard_rows
+    row0, rows_local = shard_rows(a.rows, world, rank)
 
     n_trees_total = a.warmup + a.steps + a.steps + 2
     cfg = ConfigArrays([a.bins] * a.features, max_depth=a.depth, tree_num=n_trees_total, learning_rate=0.05,

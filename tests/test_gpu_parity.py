@@ -318,3 +318,37 @@ def test_synthetic_generator_matches_host_twin():
     lab, s = w.read_labels(0, 10000)
     assert np.mean(lab != y) < 1e-3 and np.array_equal(s, sig)
     w.close()
+
+
+def test_large_shape_size_independent_properties():
+    """At a size the CPU oracle cannot finish quickly (8M rows x 200 features x 64 bins, the C2 column shape): properties
+    that hold at any size.  (1) every feature's per-bin counts of a node add up to the node's row count, and sums /
+    sums of squares add up to the same totals for every feature; (2) the two children of a split add up to the parent,
+    bin by bin, exactly (integer accumulators); (3) a second run gives the same bits (order independence)."""
+    n, F, B = 8_000_000, 200, 64
+    from shifu_b200.capi import NativeMaster
+    runs = []
+    for rep in range(2):
+        cfg = ConfigArrays([B] * F, max_depth=4, min_instances_per_node=5)
+        w = Worker(cfg)
+        w.load_synthetic(n, seed=1002)
+        m = NativeMaster(cfg, tree_num=1, max_depth=4)
+        it = m.build_initial_master_params()
+        levels = []
+        while it is not None:
+            res = w.compute(it)
+            levels.append(res[4].reshape(it.n_todo, F, B, 3).copy())
+            gains, bits = w.best_splits(it.n_todo)
+            it = m.do_compute(gains, bits)
+        runs.append(levels)
+        w.close()
+    root = runs[0][0][0]
+    assert np.all(root[:, :, 0].sum(axis=1) == float(n))                       # (1) counts
+    assert np.all(root[:, :, 1].sum(axis=1) == root[0, :, 1].sum())            # labels are 0/1: sums are exact integers
+    assert np.all(root[:, :, 2].sum(axis=1) == root[0, :, 2].sum())
+    lvl2 = runs[0][1]
+    assert lvl2.shape[0] == 2 and np.array_equal(lvl2[0] + lvl2[1], root)      # (2) children add up to the parent
+    lvl3 = runs[0][2]
+    assert np.array_equal(lvl3[0] + lvl3[1], lvl2[0]) and np.array_equal(lvl3[2] + lvl3[3], lvl2[1])
+    for a, b in zip(runs[0], runs[1]):                                         # (3) reproducible bits
+        assert np.array_equal(a, b)
