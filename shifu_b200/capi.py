@@ -296,9 +296,11 @@ class Worker:
             pass
 
     def load_rows(self, bins_cols, label, significance=None, weights=None, is_validation=False):
-        """bins_cols: list of 1-D uint8 arrays (one per feature slot); weights: [weights_per_row, n] float32."""
+        """bins_cols: list of 1-D arrays, one per feature slot (copied to uint8, or uint16 for features with more than
+        256 bins); weights: [weights_per_row, n] float32."""
         n = len(label)
-        self._keep = [np.ascontiguousarray(b, dtype=np.uint8) for b in bins_cols]
+        self._keep = [np.ascontiguousarray(b, dtype=np.uint16 if self.cfg.n_bins[f] > 256 else np.uint8)
+                      for f, b in enumerate(bins_cols)]
         ptrs = (C.c_void_p * len(self._keep))(*[b.ctypes.data for b in self._keep])
         label = np.ascontiguousarray(label, dtype=np.float32)
         sig = None if significance is None else np.ascontiguousarray(significance, dtype=np.float32)
@@ -312,7 +314,7 @@ class Worker:
                                                    int(weighted)))
 
     def read_bins(self, feature, row0, n_rows, is_validation=False):
-        out = np.empty(n_rows, dtype=np.uint8)
+        out = np.empty(n_rows, dtype=np.uint16 if self.cfg.n_bins[feature] > 256 else np.uint8)
         check(self.lib, self.lib.sb_read_bins(self.h, int(is_validation), feature, row0, n_rows, out.ctypes.data))
         return out
 

@@ -48,8 +48,11 @@ struct HistLaunch {
     int grid;
     size_t smem;
     // row-list path (more todo nodes than one slot group): lists are rebuilt before the kernel, every pass
-    bool use_rows = false;
+    bool use_rows = false, has_narrow = false, has_wide = false;
     int fpl = 1, allf = 0;
+    HistRowsArgs wide{};
+    int wide_grid = 0;
+    size_t wide_smem = 0;
     RowListArgs list{};
     HistRowsArgs rows{};
 };
@@ -64,6 +67,8 @@ struct sb_handle {
     std::vector<uint8_t> is_cat;
     std::vector<double> bin_boundary;
     std::vector<int> all_features;  // getAllValidFeatures (dt/DTWorker.java:965-990)
+    std::vector<int> wide_index;    // per feature slot: index among the wide (> 256 bins, uint16) features, or -1
+    int n_wide = 0;
     int stats_size = 3;
     int stat_kind = STAT_VARIANCE;
     int max_bins = 0;
@@ -119,6 +124,8 @@ struct sb_handle {
     DevBuf<RowOps> rl_ops;        // [n]
     DevBuf<int32_t> rt_tiles;     // row-list path: tile_feats [n_rt][32*fpl] then tile_slot0 [n_rt]
     DevBuf<uint32_t> rt_fmask;    // [n_slots][n_rt][fpl]
+    DevBuf<int32_t> wt_tiles;     // wide tiles: tile_feats [n_wt][8] then first wide index [n_wt]
+    DevBuf<uint32_t> wt_fmask;    // [n_slots][n_wt]
     bool enable_row_lists = true;
     bool acc_valid = false;     // d_acc holds the error sums of the current Data.predict (GBT, inside a tree)
     bool acc_fresh = false, scales_fresh = false;  // recomputed by the last sb_compute_begin (=> need an all-reduce)
@@ -149,6 +156,8 @@ void free_rowset(RowSet& r) {
     if (r.predict) cudaFree(r.predict);
     if (r.node_id) cudaFree(r.node_id);
     if (r.bins_rm) cudaFree(r.bins_rm);
+    if (r.bins16) cudaFree(r.bins16);
+    if (r.bins16_rm) cudaFree(r.bins16_rm);
     r = RowSet();
 }
 
@@ -214,7 +223,10 @@ int make_tensor_map(sb_handle* h, RowSet& r) {
 int finish_load(sb_handle* h, RowSet& r) {
     const int64_t n = r.n;
     r.h_col.resize((size_t)r.n_features);
-    for (int f = 0; f < r.n_features; ++f) r.h_col[f] = static_cast<const uint8_t*>(r.bins_base) + (size_t)f * r.pitch;
+    for (int f = 0; f < r.n_features; ++f) {
+        if (h->wide_index[f] >= 0) r.h_col[f] = r.bins16 + (size_t)h->wide_index[f] * r.pitch16;
+        else r.h_col[f] = static_cast<const uint8_t*>(r.bins_base) + (size_t)f * r.pitch;
+    }
     int trc = make_tensor_map(h, r);
     if (trc != SB_OK) return trc;
     SB_CUDA(cudaMalloc(&r.d_col, sizeof(void*) * std::max(1, r.n_features)));
@@ -281,7 +293,6 @@ int upload_tree(sb_handle* h, const sb_tree& t, DeviceTree& d) {
             const int need = h->n_bins[nd.feature] / 8 + 1;
             if (nd.left_mask_bytes < need || nd.left_mask_offset < 0 || nd.left_mask_offset + nd.left_mask_bytes > t.mask_pool_bytes)
                 return fail(SB_ERR_INVALID, "left_mask of a split node is missing or too short");
-            if (h->n_bins[nd.feature] > 256) return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins are not supported yet");
             feat[nd.id] = nd.feature;
             moff[nd.id] = nd.left_mask_offset;
         }
@@ -389,9 +400,14 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     const int S = (int)order.size();  // shadows the node count from here on: number of slots
 
     // tiles of 32 CONSECUTIVE feature slots (one TMA box each); only tiles with a used feature are launched
-    std::vector<uint8_t> used((size_t)F, 0);
+    // `used`: narrow (uint8) features some todo node asks for; wide (uint16) ones go to their own 8-feature tiles
+    std::vector<uint8_t> used((size_t)F, 0), used_wide((size_t)F, 0);
+    bool any_wide = false;
     for (const auto& nd : lay.nodes)
-        for (int f : nd.features) used[f] = 1;
+        for (int f : nd.features) {
+            if (h->wide_index[f] >= 0) { used_wide[f] = 1; any_wide = true; }
+            else used[f] = 1;
+        }
     std::vector<int32_t> tile_feats, tile_slot0;
     std::vector<int> tile_of((size_t)F, -1), lane_of((size_t)F, -1);
     int bins_pad = 1;
@@ -404,7 +420,6 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         for (int l = 0; l < 32; ++l) {
             const int f = f0 + l;
             if (f < F && used[f]) {
-                if (h->n_bins[f] > 256) return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins are not supported yet");
                 tile_feats.push_back(f);
                 tile_of[f] = t;
                 lane_of[f] = l;
@@ -415,7 +430,9 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         }
     }
     const int n_tiles = (int)tile_slot0.size();
-    if (n_tiles == 0) return SB_OK;
+    if (n_tiles == 0 && !any_wide) return SB_OK;
+    if (any_wide && !(h->enable_row_lists && h->train.n < (int64_t)0xffffffff))
+        return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins need the row-list path (SB_FLAG_NO_ROW_LISTS is set)");
 
     std::vector<uint32_t> fmask((size_t)S * n_tiles, 0u);
     std::vector<int64_t> pair_off((size_t)S * F, -1);
@@ -423,7 +440,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         const auto& nd = lay.nodes[order[s]];
         for (size_t k = 0; k < nd.features.size(); ++k) {
             const int f = nd.features[k];
-            fmask[(size_t)s * n_tiles + tile_of[f]] |= 1u << lane_of[f];
+            if (tile_of[f] >= 0) fmask[(size_t)s * n_tiles + tile_of[f]] |= 1u << lane_of[f];
             pair_off[(size_t)s * F + f] = nd.offset + nd.feat_off[k];
         }
     }
@@ -441,10 +458,52 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     const int max_gs = hist_max_slots_per_block(bins_pad, nw);
     if (max_gs < 1) return fail(SB_ERR_UNSUPPORTED, "one node's histogram tile does not fit in shared memory");
 
+    // ---- wide features (uint16 bins): tiles of 8, histogram [slot][bin][word][8] (hist_rows_wide_kernel)
+    int n_wt = 0, bins_pad_w = 1, wide_max_gs = 0;
+    if (any_wide) {
+        std::vector<int> feat_of_wide((size_t)h->n_wide, -1);
+        for (int f = 0; f < F; ++f)
+            if (h->wide_index[f] >= 0) feat_of_wide[(size_t)h->wide_index[f]] = f;
+        std::vector<int32_t> wt_feats, wt_slot0;
+        std::vector<int> wt_of((size_t)F, -1), wj_of((size_t)F, -1);
+        for (int w0 = 0; w0 < h->n_wide; w0 += 8) {
+            bool any = false;
+            for (int w = w0; w < std::min(h->n_wide, w0 + 8); ++w) any |= used_wide[feat_of_wide[(size_t)w]] != 0;
+            if (!any) continue;
+            const int t = (int)wt_slot0.size();
+            wt_slot0.push_back(w0);
+            for (int j = 0; j < 8; ++j) {
+                const int w = w0 + j;
+                const int f = w < h->n_wide ? feat_of_wide[(size_t)w] : -1;
+                if (f >= 0 && used_wide[f]) {
+                    wt_feats.push_back(f);
+                    wt_of[f] = t;
+                    wj_of[f] = j;
+                    bins_pad_w = std::max(bins_pad_w, h->n_bins[f]);
+                } else {
+                    wt_feats.push_back(-1);
+                }
+            }
+        }
+        n_wt = (int)wt_slot0.size();
+        std::vector<uint32_t> wfm((size_t)S * n_wt, 0u);
+        for (int s = 0; s < S; ++s)
+            for (int f : lay.nodes[order[s]].features)
+                if (wt_of[f] >= 0) wfm[(size_t)s * n_wt + wt_of[f]] |= 1u << wj_of[f];
+        wide_max_gs = hist_rows_wide_max_slots_per_block(bins_pad_w, nw);
+        if (wide_max_gs < 1) return fail(SB_ERR_UNSUPPORTED, "a tile of 8 wide features does not fit in shared memory");
+        SB_CUDA(h->wt_tiles.reserve(wt_feats.size() + wt_slot0.size()));
+        SB_CUDA(h->wt_fmask.reserve(wfm.size()));
+        SB_CUDA(cudaMemcpyAsync(h->wt_tiles.p, wt_feats.data(), wt_feats.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        SB_CUDA(cudaMemcpyAsync(h->wt_tiles.p + wt_feats.size(), wt_slot0.data(), wt_slot0.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        SB_CUDA(cudaMemcpyAsync(h->wt_fmask.p, wfm.data(), wfm.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        h->h2d_bytes += (wt_feats.size() + wt_slot0.size() + wfm.size()) * 4;
+    }
+
     // ---- row-list path tables: tiles of 32*fpl consecutive feature slots, fpl = features per lane
     int fpl = 0, rows_max_gs = 0, n_rt = 0, allf = 1;
     const bool rows_enabled = h->enable_row_lists && h->train.n < (int64_t)0xffffffff;
-    if (rows_enabled) {
+    if (rows_enabled && n_tiles > 0) {
         for (int f : {4, 2, 1}) {
             rows_max_gs = hist_rows_max_slots_per_block(bins_pad, nw, f);
             if (rows_max_gs >= 1) { fpl = f; break; }
@@ -473,6 +532,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
             const auto& nd = lay.nodes[order[s]];
             for (int f : nd.features) {
                 const int t = rt_of[f];
+                if (t < 0) continue;  // wide feature
                 const int rel = f - rt_slot0[t];
                 rfm[((size_t)s * n_rt + t) * fpl + rel % fpl] |= 1u << (rel / fpl);
             }
@@ -585,13 +645,23 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         a.n_groups = (ns + a.gs - 1) / a.gs;
         a.n_slots = ns;
         a.bins_pad = bins_pad;
-        if (fpl > 0) {
-            // group the rows by slot group once per pass and walk the lists (rowlist.cu, hist_rows_kernel)
-            const int rgs = std::min(ns, rows_max_gs);
+        if (fpl > 0 || any_wide) {
+            // group the rows by slot group once per pass and walk the lists (rowlist.cu, hist_rows_kernel);
+            // narrow and wide tiles share the lists, so they share the group size
+            int rgs = ns;
+            if (fpl > 0) rgs = std::min(rgs, rows_max_gs);
+            if (any_wide) rgs = std::min(rgs, wide_max_gs);
             const int rgroups = (ns + rgs - 1) / rgs;
+            if (rgroups > 254 && any_wide) return fail(SB_ERR_UNSUPPORTED, "more than 254 slot groups with wide features");
             if (rgroups <= 254) {
                 RowSet& tr = h->train;
-                if (!tr.bins_rm) {  // row-major twin of the bin matrix, built once
+                if (any_wide && !tr.bins16_rm) {
+                    tr.wpad = ((h->n_wide + 7) / 8) * 8;
+                    SB_CUDA(cudaMalloc(&tr.bins16_rm, ((size_t)std::max<int64_t>(n, 1) * tr.wpad + 64) * 2));
+                    SB_CUDA(launch_transpose_bins16(tr.bins16, tr.pitch16, h->n_wide, n, tr.bins16_rm, tr.wpad, h->stream));
+                    h->launches_count += 1;
+                }
+                if (fpl > 0 && !tr.bins_rm) {  // row-major twin of the bin matrix, built once
                     // 32-byte row pitch: a lane group that reaches past F reads into the next row (masked out in
                     // the kernel); the allocation is padded so the last row's over-read stays inside it
                     tr.fpad = ((F + 31) / 32) * 32;
@@ -599,7 +669,8 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                     SB_CUDA(launch_transpose_bins(static_cast<const uint8_t*>(tr.bins_base), tr.pitch, F, n, tr.bins_rm, tr.fpad, h->stream));
                     h->launches_count += 1;
                 }
-                const int64_t want_chunks = std::max<int64_t>(1, (148 * 3 + n_rt - 1) / n_rt);
+                const int tiles_total = n_rt + n_wt;
+                const int64_t want_chunks = std::max<int64_t>(1, (148 * 3 + tiles_total - 1) / tiles_total);
                 int64_t chunk_rows = ((n + want_chunks - 1) / want_chunks + 127) / 128 * 128;
                 chunk_rows = std::max<int64_t>(chunk_rows, 1024);
                 chunk_rows = std::min<int64_t>(chunk_rows, cnt_int ? MAX_ROWS_PER_FLUSH / 2 : MAX_ROWS_PER_FLUSH);
@@ -630,12 +701,27 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 ra.slot_fmask = h->rt_fmask.p + (size_t)s0 * n_rt * fpl; ra.pair_off = a.pair_off; ra.n_tiles = n_rt; ra.gs = rgs;
                 ra.n_slots = ns; ra.bins_pad = bins_pad; ra.n_features = F; ra.stats_size = h->stats_size;
                 ra.cnt_shift = h->d_cnt_shift; ra.raw_lo = h->raw.p; ra.raw_hi = h->raw.p + lay.total;
-                L.grid = max_chunks * n_rt;
-                L.smem = hist_rows_smem_bytes(rgs, bins_pad, nw, fpl);
+                L.has_narrow = fpl > 0 && n_rt > 0;
+                L.grid = max_chunks * std::max(n_rt, 1);
+                L.smem = L.has_narrow ? hist_rows_smem_bytes(rgs, bins_pad, nw, fpl) : 0;
+                if (any_wide) {
+                    L.has_wide = true;
+                    L.wide = ra;
+                    L.wide.rm_bins = reinterpret_cast<const uint8_t*>(tr.bins16_rm);
+                    L.wide.fpad = tr.wpad;
+                    L.wide.tile_feats = h->wt_tiles.p;
+                    L.wide.tile_slot0 = h->wt_tiles.p + (size_t)n_wt * 8;
+                    L.wide.slot_fmask = h->wt_fmask.p + (size_t)s0 * n_wt;
+                    L.wide.n_tiles = n_wt;
+                    L.wide.bins_pad = bins_pad_w;
+                    L.wide_grid = max_chunks * n_wt;
+                    L.wide_smem = hist_rows_wide_smem_bytes(rgs, bins_pad_w, nw);
+                }
             }
         }
         const int64_t tiles_rows = (n + HIST_T_ROWS - 1) / HIST_T_ROWS;
-        int64_t n_chunks = (148 * 3 + (int64_t)n_tiles * a.n_groups - 1) / ((int64_t)n_tiles * a.n_groups);
+        const int64_t tile_items = std::max<int64_t>(1, (int64_t)n_tiles * a.n_groups);  // n_tiles == 0: wide features only
+        int64_t n_chunks = (148 * 3 + tile_items - 1) / tile_items;
         n_chunks = std::max<int64_t>(1, std::min(n_chunks, tiles_rows));
         int64_t rpc = ((tiles_rows + n_chunks - 1) / n_chunks) * HIST_T_ROWS;
         rpc = std::min<int64_t>(rpc, cnt_int ? MAX_ROWS_PER_FLUSH / 2 : MAX_ROWS_PER_FLUSH);  // 2^21 rows * 1024 < 2^32
@@ -722,8 +808,15 @@ int run_histograms(sb_handle* h) {
     for (const HistLaunch& L : h->launches) {
         if (L.use_rows) {
             SB_CUDA(launch_rowlist_build(L.list, h->stream));
-            SB_CUDA(hist_rows_launch(L.kind, L.cnt_int, L.fpl, L.allf, L.rows, L.grid, L.smem, h->stream));
-            h->launches_count += 6;  // keys, radix sort (2 kernels), chunk table, operands, histogram
+            h->launches_count += 5;  // keys, radix sort (2 kernels), chunk table, operands
+            if (L.has_narrow) {
+                SB_CUDA(hist_rows_launch(L.kind, L.cnt_int, L.fpl, L.allf, L.rows, L.grid, L.smem, h->stream));
+                h->launches_count += 1;
+            }
+            if (L.has_wide) {
+                SB_CUDA(hist_rows_wide_launch(L.kind, L.cnt_int, L.wide, L.wide_grid, L.wide_smem, h->stream));
+                h->launches_count += 1;
+            }
         } else {
             SB_CUDA(hist_launch(L.kind, L.cnt_int, L.args, h->train.tensor_map, L.grid, L.smem, h->stream));
             h->launches_count += 1;
@@ -771,6 +864,9 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
         // getAllValidFeatures: numeric with > 1 boundary, categorical with > 0 categories
         if ((!h->is_cat[f] && h->n_bins[f] > 1) || (h->is_cat[f] && h->n_bins[f] - 1 > 0)) h->all_features.push_back(f);
     }
+    h->wide_index.assign((size_t)cfg->n_features, -1);
+    for (int f = 0; f < cfg->n_features; ++f)
+        if (h->n_bins[f] > 256) h->wide_index[f] = h->n_wide++;
     if (cfg->bin_boundary) h->bin_boundary.assign(cfg->bin_boundary, cfg->bin_boundary + nb);
     h->cfg.n_bins = nullptr; h->cfg.is_categorical = nullptr; h->cfg.column_num = nullptr; h->cfg.bin_boundary = nullptr;
     h->enable_row_lists = (cfg->flags & SB_FLAG_NO_ROW_LISTS) == 0;
@@ -804,7 +900,7 @@ SB_API void sb_destroy(sb_handle* h) {
     h->slot_of_node.release(); h->tasks.release(); h->node_task_begin.release(); h->cand.release(); h->gain_out.release();
     h->cand_bits.release(); h->out_bits.release(); h->new_dropout.release(); h->new_weights.release();
     h->sort_keys.release(); h->sort_idx.release(); h->sort_tmp.release(); h->sort_flags.release();
-    h->rl_keys.release(); h->rl_vals.release(); h->rl_temp.release(); h->rl_tables.release(); h->rl_chunk_group.release(); h->rl_ops.release(); h->rt_tiles.release(); h->rt_fmask.release();
+    h->rl_keys.release(); h->rl_vals.release(); h->rl_temp.release(); h->rl_tables.release(); h->rl_chunk_group.release(); h->rl_ops.release(); h->rt_tiles.release(); h->rt_fmask.release(); h->wt_tiles.release(); h->wt_fmask.release();
     if (h->d_feat_bins) cudaFree(h->d_feat_bins);
     if (h->d_acc) cudaFree(h->d_acc);
     if (h->d_err_scratch) cudaFree(h->d_err_scratch);
@@ -829,8 +925,6 @@ SB_API int sb_load_rows(sb_handle* h, int32_t is_validation, int64_t n_rows, con
     RowSet& r = is_validation ? h->valid : h->train;
     if (r.loaded) return fail(SB_ERR_UNSUPPORTED, "rows of this set were already loaded (one load call per set)");
     const int F = h->cfg.n_features, W = h->cfg.weights_per_row;
-    for (int f = 0; f < F; ++f)
-        if (h->n_bins[f] > 256) return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins are not supported yet");
     r.n = n_rows;
     r.n_features = F;
     r.owns_inputs = true;
@@ -839,10 +933,16 @@ SB_API int sb_load_rows(sb_handle* h, int32_t is_validation, int64_t n_rows, con
     SB_CUDA(cudaMemsetAsync(r.owned_bins, 0, (size_t)pitch * F, h->stream));
     r.bins_base = r.owned_bins;
     r.pitch = pitch;
+    r.n_wide = h->n_wide;
+    r.pitch16 = pitch;
+    if (h->n_wide > 0) SB_CUDA(cudaMalloc(&r.bins16, (size_t)pitch * h->n_wide * 2));
     for (int f = 0; f < F; ++f) {
-        uint8_t* dst = static_cast<uint8_t*>(r.owned_bins) + (size_t)f * pitch;
         if (!bins[f]) return fail(SB_ERR_INVALID, "null feature column");
-        if (n_rows > 0) SB_CUDA(cudaMemcpyAsync(dst, bins[f], (size_t)n_rows, cudaMemcpyHostToDevice, h->stream));
+        if (n_rows <= 0) continue;
+        if (h->wide_index[f] >= 0)  // uint16 column (the reference stores short, dt/DTWorker.java:1593)
+            SB_CUDA(cudaMemcpyAsync(r.bins16 + (size_t)h->wide_index[f] * pitch, bins[f], (size_t)n_rows * 2, cudaMemcpyHostToDevice, h->stream));
+        else
+            SB_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(r.owned_bins) + (size_t)f * pitch, bins[f], (size_t)n_rows, cudaMemcpyHostToDevice, h->stream));
     }
     const size_t nf = (size_t)std::max<int64_t>(n_rows, 1);
     SB_CUDA(cudaMalloc(&r.label, nf * 4));
@@ -870,8 +970,7 @@ SB_API int sb_load_rows_device(sb_handle* h, int32_t is_validation, int64_t n_ro
     r.n = n_rows;
     r.n_features = F;
     r.owns_inputs = false;
-    for (int f = 0; f < F; ++f)
-        if (h->n_bins[f] > 256) return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins are not supported yet");
+    if (h->n_wide > 0) return fail(SB_ERR_UNSUPPORTED, "sb_load_rows_device takes the uint8 matrix only: features wider than 256 bins need sb_load_rows");
     r.bins_base = bins;
     r.pitch = pitch;
     r.label = label;
@@ -887,8 +986,6 @@ SB_API int sb_load_synthetic(sb_handle* h, int32_t is_validation, int64_t row0, 
     RowSet& r = is_validation ? h->valid : h->train;
     if (r.loaded) return fail(SB_ERR_UNSUPPORTED, "rows of this set were already loaded (one load call per set)");
     const int F = h->cfg.n_features, W = h->cfg.weights_per_row;
-    for (int f = 0; f < F; ++f)
-        if (h->n_bins[f] > 256) return fail(SB_ERR_UNSUPPORTED, "features wider than 256 bins are not supported yet");
     r.n = n_rows;
     r.n_features = F;
     r.owns_inputs = true;
@@ -896,6 +993,16 @@ SB_API int sb_load_synthetic(sb_handle* h, int32_t is_validation, int64_t row0, 
     SB_CUDA(cudaMalloc(&r.owned_bins, (size_t)pitch * F));
     r.bins_base = r.owned_bins;
     r.pitch = pitch;
+    r.n_wide = h->n_wide;
+    r.pitch16 = pitch;
+    if (h->n_wide > 0) {
+        SB_CUDA(cudaMalloc(&r.bins16, (size_t)pitch * h->n_wide * 2));
+        for (int f = 0; f < F; ++f)
+            if (h->wide_index[f] >= 0) {
+                SB_CUDA(launch_synthetic16(r.bins16 + (size_t)h->wide_index[f] * pitch, n_rows, f, F, h->n_bins[f], row0, seed, h->stream));
+                h->launches_count += 1;
+            }
+    }
     const size_t nf = (size_t)std::max<int64_t>(n_rows, 1);
     SB_CUDA(cudaMalloc(&r.label, nf * 4));
     SB_CUDA(cudaMalloc(&r.significance, nf * 4));
@@ -915,7 +1022,8 @@ SB_API int sb_read_bins(sb_handle* h, int32_t is_validation, int32_t feature, in
     if (!r.loaded || feature < 0 || feature >= r.n_features || row0 < 0 || row0 + n_rows > r.n)
         return fail(SB_ERR_INVALID, "range outside the loaded rows");
     SB_CUDA(cudaSetDevice(h->cfg.device));
-    SB_CUDA(cudaMemcpyAsync(out, static_cast<const uint8_t*>(r.h_col[feature]) + row0, (size_t)n_rows, cudaMemcpyDeviceToHost, h->stream));
+    const size_t width = h->wide_index[feature] >= 0 ? 2 : 1;  // `out` receives uint16 for features wider than 256 bins
+    SB_CUDA(cudaMemcpyAsync(out, static_cast<const uint8_t*>(r.h_col[feature]) + row0 * width, (size_t)n_rows * width, cudaMemcpyDeviceToHost, h->stream));
     SB_CUDA(cudaStreamSynchronize(h->stream));
     h->d2h_bytes += n_rows;
     return SB_OK;
@@ -1002,7 +1110,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
                     if (va.loaded) SB_CUDA(launch_fill_i32(va.node_id, va.n, SB_ROOT_INDEX, h->stream));
                 }
                 const TreeView pv = view_of(dprev);
-                SB_CUDA(launch_route(tr.d_col, tr.n, tr.node_id, pv, h->d_error_flag, h->stream));
+                SB_CUDA(launch_route(tr.d_col, h->d_feat_bins, tr.n, tr.node_id, pv, h->d_error_flag, h->stream));
                 const uint8_t* d_drop = nullptr;
                 if (in->dropout && !in->is_first_tree) {
                     SB_CUDA(h->new_dropout.reserve((size_t)tr.n));
@@ -1014,7 +1122,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
                                           tr.predict, tr.output, d_drop, h->stream));
                 h->launches_count += 2;
                 if (va.loaded) {
-                    SB_CUDA(launch_route(va.d_col, va.n, va.node_id, pv, h->d_error_flag, h->stream));
+                    SB_CUDA(launch_route(va.d_col, h->d_feat_bins, va.n, va.node_id, pv, h->d_error_flag, h->stream));
                     SB_CUDA(launch_gbt_update(va.n, va.node_id, pv, in->is_first_tree, h->cfg.learning_rate, loss, va.label,
                                               va.predict, va.output, nullptr, h->stream));
                     h->launches_count += 2;
@@ -1047,11 +1155,11 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
             else ++it;
         }
         const TreeView cv = view_of(dcur);
-        SB_CUDA(launch_route(tr.d_col, tr.n, tr.node_id, cv, h->d_error_flag, h->stream));
+        SB_CUDA(launch_route(tr.d_col, h->d_feat_bins, tr.n, tr.node_id, cv, h->d_error_flag, h->stream));
         h->launches_count += 1;
         const bool from_tree = errors_from_tree;  // dt/DTWorker.java:672-683
         if (va.loaded && from_tree) {
-            SB_CUDA(launch_route(va.d_col, va.n, va.node_id, cv, h->d_error_flag, h->stream));
+            SB_CUDA(launch_route(va.d_col, h->d_feat_bins, va.n, va.node_id, cv, h->d_error_flag, h->stream));
             h->launches_count += 1;
         }
         ErrArgs e{};
@@ -1080,7 +1188,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
             if (rc != SB_OK) return rc;
             const TreeView v = view_of(d);
             int32_t* nid = tr.node_id + (int64_t)tree.tree_id * tr.n;
-            SB_CUDA(launch_route(tr.d_col, tr.n, nid, v, h->d_error_flag, h->stream));
+            SB_CUDA(launch_route(tr.d_col, h->d_feat_bins, tr.n, nid, v, h->d_error_flag, h->stream));
             ErrArgs e{};
             e.n = tr.n; e.label = tr.label; e.predict = tr.predict; e.significance = tr.significance;
             e.weights = tr.weights + (int64_t)tree.tree_id * tr.n;  // [treeId], no modulo (:592)
@@ -1089,7 +1197,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
             h->launches_count += 2;
             if (va.loaded) {
                 int32_t* vnid = va.node_id + (int64_t)tree.tree_id * va.n;
-                SB_CUDA(launch_route(va.d_col, va.n, vnid, v, h->d_error_flag, h->stream));
+                SB_CUDA(launch_route(va.d_col, h->d_feat_bins, va.n, vnid, v, h->d_error_flag, h->stream));
                 e.n = va.n; e.label = va.label; e.predict = va.predict; e.significance = va.significance; e.weights = nullptr;
                 e.node_id = vnid; e.is_validation = 1; e.rf_oob = 0;
                 SB_CUDA(launch_errors(e, h->d_err_scratch, h->d_acc, h->stream));

@@ -48,6 +48,12 @@ struct RowSet {
     void* owned_bins = nullptr;
     uint8_t* bins_rm = nullptr;       // row-major twin [n][fpad] for the row-list path (built on first use)
     int fpad = 0;
+    // features with more than 256 bins: uint16 columns [n_wide][pitch16] (+ row-major twin [n][wpad])
+    uint16_t* bins16 = nullptr;
+    int64_t pitch16 = 0;  // elements
+    int n_wide = 0;
+    uint16_t* bins16_rm = nullptr;
+    int wpad = 0;
     const void* bins_base = nullptr;  // column-major uint8 bin matrix: feature f starts at bins_base + f * pitch
     int64_t pitch = 0;
     alignas(64) unsigned char tensor_map[128];  // CUtensorMap over the bin matrix (see hist.cu)

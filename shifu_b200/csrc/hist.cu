@@ -136,11 +136,11 @@ __host__ __device__ inline int hist_words(int kind, int cnt_int, int stats_size)
 
 // Merge a block's privatised histogram into the global integer accumulators.  (lo, hi) split: the global sum over
 // all blocks and GPUs may exceed 63 bits, each half cannot.
-template <int KIND, int CNT_INT, int FPL>
+template <int KIND, int CNT_INT, int LW>
 __device__ __forceinline__ void flush_hist(const uint32_t* hist, int gcount, int g0, int bins_pad, int nw, int n_stats,
                                            int cnt_shift, const int32_t* tile_feats, const int64_t* pair_off,
                                            int n_features, int64_t* raw_lo, int64_t* raw_hi, int nthreads) {
-    constexpr int LW = 32 * FPL;                      // features (words) per histogram word row: [k][lane]
+    // LW = features (words) per histogram word row: 32*FPL laid out [k][lane], or 8 for the wide-feature kernel
     const int per_slot = bins_pad * n_stats * LW;    // 64-bit statistics per slot
     for (int i = threadIdx.x; i < gcount * per_slot; i += nthreads) {
         const int l = i % LW;                        // k * 32 + lane
@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) hist_kernel(const HistArgs a, con
     }
     __syncthreads();
 
-    flush_hist<KIND, CNT_INT, 1>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0, a.tile_feats + tile_id * 32,
+    flush_hist<KIND, CNT_INT, 32>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0, a.tile_feats + tile_id * 32,
                                  a.pair_off, a.n_features, a.raw_lo, a.raw_hi, NTHREADS);
 }
 
@@ -592,7 +592,7 @@ __global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const
         }
     }
     __syncthreads();
-    flush_hist<KIND, CNT_INT, FPL>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0,
+    flush_hist<KIND, CNT_INT, 32 * FPL>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0,
                                    a.tile_feats + tile_id * 32 * FPL, a.pair_off, a.n_features, a.raw_lo, a.raw_hi, NTHR);
 }
 
@@ -629,6 +629,179 @@ cudaError_t hist_rows_launch(int kind, int cnt_int, int fpl, int allf, const His
     if (kind == STAT_VARIANCE)
         return cnt_int ? launch_rows_kc<STAT_VARIANCE, 1>(fpl, allf, a, grid, smem, stream) : launch_rows_kc<STAT_VARIANCE, 0>(fpl, allf, a, grid, smem, stream);
     return cnt_int ? launch_rows_kc<STAT_CLASS, 1>(fpl, allf, a, grid, smem, stream) : launch_rows_kc<STAT_CLASS, 0>(fpl, allf, a, grid, smem, stream);
+}
+
+
+// =====================================================================================================================
+// hist_rows_wide_kernel: features with more than 256 bins (categorical columns, uint16 bin indices).  32 such
+// features cannot have private histograms in one SM (1001 bins x 5 words x 32 lanes = 640 KB), so a tile is 8 wide
+// features and a warp instruction covers 4 rows x 8 features: lane = (row slot q = lane >> 3, feature j = lane & 7),
+// histogram [slot][bin][word][8].  Two lanes can now meet on one address (two of the 4 rows in the same bin of the
+// same feature); the shared-memory atomic unit serialises exactly those.  Same row lists, same RowOps, same
+// two-phase carry as hist_rows_kernel.
+namespace {
+constexpr size_t W_SMEM_FIXED = R_SMEM_FIXED;
+constexpr int W_NTHREADS = (1 + 16) * 32;
+}  // namespace
+
+template <int KIND, int CNT_INT>
+__global__ void __launch_bounds__(W_NTHREADS, 1) hist_rows_wide_kernel(const HistRowsArgs a) {
+    constexpr int CONS_WARPS = 16;
+    constexpr int RPW = R_TILE / CONS_WARPS;  // 8 rows of a stage per warp = 2 steps of 4 rows
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int ci = blockIdx.x / a.n_tiles;
+    const int tile_id = blockIdx.x - ci * a.n_tiles;
+    if (ci >= *a.n_chunks) return;
+    const int nw = hist_words(KIND, CNT_INT, a.stats_size);
+    RowOps* ops_s = reinterpret_cast<RowOps*>(smem);
+    RStage* st = reinterpret_cast<RStage*>(smem + (size_t)R_NST * R_TILE * sizeof(RowOps));
+    uint32_t* fm_tab = reinterpret_cast<uint32_t*>(smem + (size_t)R_NST * R_TILE * sizeof(RowOps) + 128);
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem + W_SMEM_FIXED);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int group = a.chunk_group[ci];
+    const int64_t begin = a.chunk_begin[ci], end = a.chunk_end[ci];
+    const int g0 = group * a.gs;
+    const int gcount = min(a.gs, a.n_slots - g0);
+    const int bins_pad = a.bins_pad;
+    const int n_iters = (int)((end - begin + R_TILE - 1) / R_TILE);
+
+    for (int i = threadIdx.x; i < (gcount * bins_pad + 1) * nw * 8; i += W_NTHREADS) hist[i] = 0u;
+    if (threadIdx.x < R_MAX_GS)
+        fm_tab[threadIdx.x] = threadIdx.x < gcount ? a.slot_fmask[(size_t)(g0 + threadIdx.x) * a.n_tiles + tile_id] : 0u;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < R_NST; ++s) {
+            mbar_init(&st[s].full, 1);
+            mbar_init(&st[s].empty, CONS_WARPS);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int it = 0; it < n_iters; ++it) {
+                const int s = it % R_NST;
+                if (it >= R_NST) mbar_wait(&st[s].empty, (uint32_t)(((it / R_NST) - 1) & 1));
+                const int64_t r0 = begin + (int64_t)it * R_TILE;
+                const uint32_t bytes = (uint32_t)(min((int64_t)R_TILE, end - r0) * (int64_t)sizeof(RowOps));
+                mbar_expect_tx(&st[s].full, bytes);
+                tma_load_1d(ops_s + s * R_TILE, a.ops + r0, bytes, &st[s].full);
+            }
+        }
+    } else {
+        const int cw = warp - 1;
+        const int q = lane >> 3, j = lane & 7;
+        const uint32_t feat_bit = 1u << j;
+        const bool feat_ok = a.tile_feats[tile_id * 8 + j] >= 0;
+        const uint32_t lane_base = smem_u32(hist) + (uint32_t)j * 4u;
+        constexpr uint32_t WORD = 32u;                                  // bytes between the words of one bin
+        const uint32_t bin_stride = (uint32_t)nw * WORD;
+        const uint32_t slot_stride = (uint32_t)bins_pad * bin_stride;
+        const uint32_t dummy_addr = lane_base + (uint32_t)gcount * slot_stride;
+        const uint16_t* my_bins = reinterpret_cast<const uint16_t*>(a.rm_bins) + a.tile_slot0[tile_id] + j;
+        const int wr0 = cw * RPW;
+        uint32_t bw_cur[2], bw_next[2];
+        auto fetch_bins = [&](int it, uint32_t (&bw)[2]) {
+            const int s = it % R_NST;
+            mbar_wait(&st[s].full, (uint32_t)((it / R_NST) & 1));
+            const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
+#pragma unroll
+            for (int hs = 0; hs < 2; ++hs) {
+                const int r = wr0 + hs * 4 + q;
+                bw[hs] = 0;
+                if (r < rows) bw[hs] = __ldg(my_bins + (size_t)ops_s[s * R_TILE + r].row * a.fpad);
+            }
+        };
+        if (n_iters > 0) fetch_bins(0, bw_cur);
+        for (int it = 0; it < n_iters; ++it) {
+            const int s = it % R_NST;
+            if (it + 1 < n_iters) fetch_bins(it + 1, bw_next);
+            const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
+            if (wr0 < rows) {
+                uint32_t ad[2], o0[2], o1[2], o2[2], lo0[2], lo1[2], lo2[2], hi0[2], hi1[2], hi2[2];
+#pragma unroll
+                for (int hs = 0; hs < 2; ++hs) {
+                    const int r = min(wr0 + hs * 4 + q, R_TILE - 1);
+                    const RowOps* v = ops_s + s * R_TILE + r;
+                    const uint4 v0 = *reinterpret_cast<const uint4*>(v);          // row, slot, q0, q1
+                    const uint4 v1 = *reinterpret_cast<const uint4*>(&v->q[2]);   // q2..q5
+                    const uint32_t slot = v0.y;
+                    const bool ok = (wr0 + hs * 4 + q < rows) && slot < (uint32_t)gcount && feat_ok &&
+                                    (fm_tab[slot & (R_MAX_GS - 1)] & feat_bit) != 0u && bw_cur[hs] < (uint32_t)bins_pad;
+                    uint32_t base = lane_base + slot * slot_stride + bw_cur[hs] * bin_stride;
+                    lo0[hs] = v0.z; hi0[hs] = v0.w;
+                    lo1[hs] = hi1[hs] = lo2[hs] = hi2[hs] = 0;
+                    if (KIND == STAT_VARIANCE) { lo1[hs] = v1.x; hi1[hs] = v1.y; lo2[hs] = v1.z; hi2[hs] = v1.w; }
+                    else base += v1.x / 4u;  // class byte offset was computed for 128-byte words; here words are 32 bytes
+                    ad[hs] = ok ? base : dummy_addr;
+                    o0[hs] = o1[hs] = o2[hs] = 0;
+                    if (KIND == STAT_VARIANCE) {
+                        if (CNT_INT) {
+                            sred_add<0>(ad[hs], lo0[hs]);
+                            o1[hs] = satom_add<WORD>(ad[hs], lo1[hs]);
+                            o2[hs] = satom_add<3 * WORD>(ad[hs], lo2[hs]);
+                        } else {
+                            o0[hs] = satom_add<0>(ad[hs], lo0[hs]);
+                            o1[hs] = satom_add<2 * WORD>(ad[hs], lo1[hs]);
+                            o2[hs] = satom_add<4 * WORD>(ad[hs], lo2[hs]);
+                        }
+                    } else {
+                        if (CNT_INT) sred_add<0>(ad[hs], lo0[hs]);
+                        else o0[hs] = satom_add<0>(ad[hs], lo0[hs]);
+                    }
+                }
+#pragma unroll
+                for (int hs = 0; hs < 2; ++hs) {
+                    if (KIND == STAT_VARIANCE) {
+                        if (CNT_INT) {
+                            sred_add<2 * WORD>(ad[hs], hi_plus_carry(o1[hs], lo1[hs], hi1[hs]));
+                            sred_add<4 * WORD>(ad[hs], hi_plus_carry(o2[hs], lo2[hs], hi2[hs]));
+                        } else {
+                            sred_add<WORD>(ad[hs], hi_plus_carry(o0[hs], lo0[hs], hi0[hs]));
+                            sred_add<3 * WORD>(ad[hs], hi_plus_carry(o1[hs], lo1[hs], hi1[hs]));
+                            sred_add<5 * WORD>(ad[hs], hi_plus_carry(o2[hs], lo2[hs], hi2[hs]));
+                        }
+                    } else if (!CNT_INT) {
+                        sred_add<WORD>(ad[hs], hi_plus_carry(o0[hs], lo0[hs], hi0[hs]));
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&st[s].empty);
+            bw_cur[0] = bw_next[0];
+            bw_cur[1] = bw_next[1];
+        }
+    }
+    __syncthreads();
+    flush_hist<KIND, CNT_INT, 8>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0,
+                                 a.tile_feats + tile_id * 8, a.pair_off, a.n_features, a.raw_lo, a.raw_hi, W_NTHREADS);
+}
+
+size_t hist_rows_wide_smem_bytes(int gs, int bins_pad, int nw) {
+    return W_SMEM_FIXED + ((size_t)gs * bins_pad + 1) * nw * 8 * 4;
+}
+int hist_rows_wide_max_slots_per_block(int bins_pad, int nw) {
+    const size_t budget = 227 * 1024 - W_SMEM_FIXED - (size_t)nw * 8 * 4;
+    int gs = (int)(budget / ((size_t)bins_pad * nw * 8 * 4));
+    return gs > R_MAX_GS ? R_MAX_GS : gs;
+}
+
+template <int KIND, int CNT_INT>
+static cudaError_t launch_wide_one(const HistRowsArgs& a, int grid, size_t smem, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(hist_rows_wide_kernel<KIND, CNT_INT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    hist_rows_wide_kernel<KIND, CNT_INT><<<grid, W_NTHREADS, smem, stream>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t hist_rows_wide_launch(int kind, int cnt_int, const HistRowsArgs& a, int grid, size_t smem, cudaStream_t stream) {
+    if (kind == STAT_VARIANCE) return cnt_int ? launch_wide_one<STAT_VARIANCE, 1>(a, grid, smem, stream) : launch_wide_one<STAT_VARIANCE, 0>(a, grid, smem, stream);
+    return cnt_int ? launch_wide_one<STAT_CLASS, 1>(a, grid, smem, stream) : launch_wide_one<STAT_CLASS, 0>(a, grid, smem, stream);
 }
 
 }  // namespace sb

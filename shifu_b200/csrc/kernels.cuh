@@ -63,6 +63,10 @@ struct RowListArgs {
 };
 cudaError_t launch_transpose_bins(const uint8_t* cm, int64_t pitch, int n_features, int64_t n, uint8_t* rm, int fpad,
                                   cudaStream_t s);
+// wide (uint16) columns [n_wide][pitch16] -> row-major [n][wpad]
+cudaError_t launch_transpose_bins16(const uint16_t* cm, int64_t pitch16, int n_wide, int64_t n, uint16_t* rm, int wpad,
+                                    cudaStream_t s);
+
 size_t rowlist_sort_temp_bytes(int64_t n);
 cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s);
 struct HistRowsArgs {
@@ -85,6 +89,11 @@ struct HistRowsArgs {
 // fpl = features per lane (1, 2 or 4); allf = every slot takes every feature of the tile (skips the mask lookups)
 cudaError_t hist_rows_launch(int kind, int cnt_int, int fpl, int allf, const HistRowsArgs& a, int grid, size_t smem,
                              cudaStream_t stream);
+// hist_rows_wide_kernel: tiles of 8 wide features, lane = (row slot, feature); args as hist_rows (rm_bins = uint16 twin,
+// fpad = wpad in elements, tile tables with 8 entries per tile)
+cudaError_t hist_rows_wide_launch(int kind, int cnt_int, const HistRowsArgs& a, int grid, size_t smem, cudaStream_t stream);
+size_t hist_rows_wide_smem_bytes(int gs, int bins_pad, int nw);
+int hist_rows_wide_max_slots_per_block(int bins_pad, int nw);
 size_t hist_rows_smem_bytes(int gs, int bins_pad, int nw, int fpl);
 int hist_rows_max_slots_per_block(int bins_pad, int nw, int fpl);
 
@@ -109,8 +118,10 @@ cudaError_t launch_fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t s);
 cudaError_t launch_fill_f32(float* p, int64_t n, float v, cudaStream_t s);
 cudaError_t launch_copy_f32(float* dst, const float* src, int64_t n, cudaStream_t s);
 // predictNodeIndex (dt/DTWorker.java:1036-1096) continued from each row's current node id.
-cudaError_t launch_route(const void* const* cols, int64_t n, int32_t* node_id, TreeView t, uint32_t* error_flag,
-                         cudaStream_t s);
+cudaError_t launch_route(const void* const* cols, const int32_t* feat_bins, int64_t n, int32_t* node_id, TreeView t,
+                         uint32_t* error_flag, cudaStream_t s);
+cudaError_t launch_synthetic16(uint16_t* col, int64_t n, int feature, int n_features, int n_bins, int64_t row0,
+                               uint64_t seed, cudaStream_t s);
 // GBT tree switch (dt/DTWorker.java:620-669, 721-735): predict / output update from the finished tree's leaves.
 cudaError_t launch_gbt_update(int64_t n, const int32_t* node_id, TreeView prev, int is_first_tree, double learning_rate,
                               int loss, const float* label, float* predict, float* output, const uint8_t* dropout,

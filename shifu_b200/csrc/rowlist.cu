@@ -131,6 +131,23 @@ __global__ void rowlist_ops_kernel(const uint32_t* __restrict__ sorted_rows, con
 
 }  // namespace
 
+__global__ void transpose_bins16_kernel(const uint16_t* __restrict__ cm, int64_t pitch16, int n_wide, int64_t n,
+                                        uint16_t* __restrict__ rm, int wpad) {
+    // one-time layout change of the (few) wide columns: coalesced reads along rows, strided writes
+    const int j = blockIdx.y;
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x)
+        rm[r * wpad + j] = j < n_wide ? cm[(int64_t)j * pitch16 + r] : (uint16_t)0;
+}
+cudaError_t launch_transpose_bins16(const uint16_t* cm, int64_t pitch16, int n_wide, int64_t n, uint16_t* rm, int wpad,
+                                    cudaStream_t s) {
+    if (n <= 0 || wpad <= 0) return cudaSuccess;
+    int64_t gx = (n + 255) / 256;
+    if (gx > 148 * 8) gx = 148 * 8;
+    dim3 grid((unsigned)gx, (unsigned)wpad);
+    transpose_bins16_kernel<<<grid, 256, 0, s>>>(cm, pitch16, n_wide, n, rm, wpad);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_transpose_bins(const uint8_t* cm, int64_t pitch, int n_features, int64_t n, uint8_t* rm, int fpad,
                                   cudaStream_t s) {
     if (n <= 0) return cudaSuccess;

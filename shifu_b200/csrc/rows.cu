@@ -29,15 +29,20 @@ __global__ void copy_f32_kernel(float* d, const float* s, int64_t n) {
 
 // dt/DTWorker.java:1036-1096.  A node routes further iff it has a split and children (feat[id] >= 0);
 // the left/right decision is the host-built left_mask bit of the row's bin (see sb_node in shifu_b200.h).
-__global__ void route_kernel(const void* const* __restrict__ cols, int64_t n, int32_t* __restrict__ node_id, TreeView t,
-                             uint32_t* error_flag) {
+// A column holds uint8 bin indices when its feature has <= 256 bins, uint16 otherwise (the reference stores short).
+__device__ __forceinline__ int load_bin(const void* const* cols, const int32_t* feat_bins, int f, int64_t r) {
+    return feat_bins[f] > 256 ? (int)static_cast<const uint16_t*>(cols[f])[r] : (int)static_cast<const uint8_t*>(cols[f])[r];
+}
+
+__global__ void route_kernel(const void* const* __restrict__ cols, const int32_t* __restrict__ feat_bins, int64_t n,
+                             int32_t* __restrict__ node_id, TreeView t, uint32_t* error_flag) {
     for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
         int id = node_id[r];
         const int id0 = id;
         while (id > 0 && id < t.capacity) {
             const int f = t.feat[id];
             if (f < 0) break;
-            const int bin = static_cast<const uint8_t*>(cols[f])[r];
+            const int bin = load_bin(cols, feat_bins, f, r);
             const uint8_t m = t.masks[t.mask_off[id] + (bin >> 3)];
             id = 2 * id + (((m >> (bin & 7)) & 1) ? 0 : 1);
         }
@@ -243,7 +248,7 @@ __global__ void synthetic_bins_kernel(uint8_t* bins, int64_t pitch, int n_featur
         for (int k = 0; k < 8; ++k) {
             const int64_t r = rg * 8 + k;
             const uint64_t h = splitmix64(seed ^ (uint64_t)((row0 + r) * (int64_t)n_features + f));
-            const uint64_t b = (r < n) ? (uint64_t)((uint32_t)(h >> 33) % nb) : 0;
+            const uint64_t b = (r < n && nb <= 256u) ? (uint64_t)((uint32_t)(h >> 33) % nb) : 0;
             packed |= b << (8 * k);
         }
         *reinterpret_cast<uint64_t*>(bins + (int64_t)f * pitch + rg * 8) = packed;
@@ -284,11 +289,10 @@ __global__ void synthetic_labels_kernel(const uint8_t* bins, int64_t pitch, int 
 __global__ void check_bins_kernel(const void* const* cols, const int32_t* feat_bins, int n_features, int64_t n,
                                   uint32_t* error_flag) {
     const int f = blockIdx.y;
-    const uint8_t* c = static_cast<const uint8_t*>(cols[f]);
     const int nb = feat_bins[f];
     bool bad = false;
     for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x)
-        bad |= ((int)c[r] >= nb);
+        bad |= (load_bin(cols, feat_bins, f, r) >= nb);
     if (bad) atomicOr(error_flag, 2u);
     (void)n_features;
 }
@@ -310,10 +314,24 @@ cudaError_t launch_copy_f32(float* dst, const float* src, int64_t n, cudaStream_
     copy_f32_kernel<<<grid_for(n, TPB, 148 * 8), TPB, 0, s>>>(dst, src, n);
     return cudaGetLastError();
 }
-cudaError_t launch_route(const void* const* cols, int64_t n, int32_t* node_id, TreeView t, uint32_t* error_flag,
-                         cudaStream_t s) {
+cudaError_t launch_route(const void* const* cols, const int32_t* feat_bins, int64_t n, int32_t* node_id, TreeView t,
+                         uint32_t* error_flag, cudaStream_t s) {
     if (n <= 0) return cudaSuccess;
-    route_kernel<<<grid_for(n, TPB, 148 * 16), TPB, 0, s>>>(cols, n, node_id, t, error_flag);
+    route_kernel<<<grid_for(n, TPB, 148 * 16), TPB, 0, s>>>(cols, feat_bins, n, node_id, t, error_flag);
+    return cudaGetLastError();
+}
+
+__global__ void synthetic_bins16_kernel(uint16_t* col, int64_t n, int feature, int n_features, int n_bins, int64_t row0,
+                                        uint64_t seed) {
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        const uint64_t h = splitmix64(seed ^ (uint64_t)((row0 + r) * (int64_t)n_features + feature));
+        col[r] = (uint16_t)((uint32_t)(h >> 33) % (uint32_t)n_bins);
+    }
+}
+cudaError_t launch_synthetic16(uint16_t* col, int64_t n, int feature, int n_features, int n_bins, int64_t row0,
+                               uint64_t seed, cudaStream_t s) {
+    if (n <= 0) return cudaSuccess;
+    synthetic_bins16_kernel<<<grid_for(n, TPB, 148 * 8), TPB, 0, s>>>(col, n, feature, n_features, n_bins, row0, seed);
     return cudaGetLastError();
 }
 cudaError_t launch_gbt_update(int64_t n, const int32_t* node_id, TreeView prev, int is_first_tree, double learning_rate,

@@ -21,7 +21,7 @@ def bins_column(seed, feature, n_features, n_bins, row0, n_rows):
     with np.errstate(over="ignore"):
         r = np.arange(row0, row0 + n_rows, dtype=np.uint64)
         h = splitmix64(np.uint64(seed) ^ (r * np.uint64(n_features) + np.uint64(feature)))
-    return ((h >> np.uint64(33)).astype(np.uint32) % np.uint32(n_bins)).astype(np.uint8)
+    return ((h >> np.uint64(33)).astype(np.uint32) % np.uint32(n_bins)).astype(np.uint16 if n_bins > 256 else np.uint8)
 
 
 def labels(seed, cols, n_bins, row0, n_rows, label_kind=0, weighted=False):
@@ -34,7 +34,9 @@ def labels(seed, cols, n_bins, row0, n_rows, label_kind=0, weighted=False):
     if label_kind == 0:
         z = np.zeros(n_rows, dtype=np.float32)
         for f in range(min(F, 5)):
-            x = cols[f].astype(np.float32) / np.float32(n_bins[f]) - np.float32(0.5)
+            # the device label kernel reads the uint8 matrix, where a wide (> 256 bins) feature is stored as 0
+            c = cols[f] if n_bins[f] <= 256 else np.zeros(n_rows, dtype=np.uint8)
+            x = c.astype(np.float32) / np.float32(n_bins[f]) - np.float32(0.5)
             z += np.float32(-2.0 if f & 1 else 3.0) * x
         p = np.float32(1.0) / (np.float32(1.0) + np.exp(-z, dtype=np.float32))
         y = (u < p).astype(np.float32)

@@ -8,7 +8,8 @@ from shifu_b200.messages import Node
 def make_data(n, n_bins, seed, is_categorical=None, label="binary", weighted=False, wpr=1, poisson=False):
     rng = np.random.default_rng(seed)
     F = len(n_bins)
-    cols = [rng.integers(0, n_bins[f], size=n, dtype=np.int64).astype(np.uint8) for f in range(F)]
+    cols = [rng.integers(0, n_bins[f], size=n, dtype=np.int64).astype(np.uint16 if n_bins[f] > 256 else np.uint8)
+            for f in range(F)]
     z = sum((cols[f].astype(np.float64) / n_bins[f] - 0.5) * (3.0 if f % 2 == 0 else -2.0) for f in range(min(F, 5)))
     if label == "binary":
         y = (rng.random(n) < 1.0 / (1.0 + np.exp(-z))).astype(np.float32)

@@ -207,6 +207,22 @@ def test_gbt_categorical_features():
     run_gbt(10000, n_bins, seed=17, n_trees=2, max_depth=4, is_categorical=is_cat)
 
 
+def test_gbt_wide_categorical_uint16_columns():
+    """Config C3's column mix in small: numeric 64-bin features plus categorical features with up to 1000 categories
+    (1001 statistics bins -> uint16 bin indices, 8-feature tiles in hist_rows_wide_kernel), GBT with log loss."""
+    n_bins = [64] * 10 + [301, 1001, 11, 257] + [64] * 3
+    is_cat = [0] * 10 + [1, 1, 1, 1] + [0] * 3
+    run_gbt(20000, n_bins, seed=51, n_trees=2, max_depth=5, is_categorical=is_cat, loss=capi.SB_LOSS_LOG)
+    run_gbt(9000, n_bins, seed=52, n_trees=2, max_depth=4, is_categorical=is_cat, weighted=True, feature_subsets=True)
+    # only wide features, and a numeric feature with more than 256 bins
+    run_gbt(6000, [400, 1001, 300], seed=53, n_trees=1, max_depth=4, is_categorical=[0, 1, 1])
+
+
+def test_rf_entropy_wide_categorical():
+    run_rf(8000, [32] * 6 + [501, 300], seed=54, n_trees=3, max_depth=4, impurity=capi.SB_IMPURITY_ENTROPY,
+           is_categorical=[0] * 6 + [1, 1], feature_subsets=False)
+
+
 def test_gbt_ragged_sizes():
     for n in (1, 2, 127, 128, 129, 1000):
         run_gbt(n, [8] * 5, seed=100 + n, n_trees=2, max_depth=3, with_validation=(n > 4))
@@ -308,12 +324,12 @@ def test_rf_gini_categorical():
 
 def test_synthetic_generator_matches_host_twin():
     from shifu_b200 import synthetic
-    n_bins = [64, 32, 7, 200]
+    n_bins = [64, 32, 7, 200, 1001]
     cfg = ConfigArrays(n_bins)
     w = Worker(cfg)
     w.load_synthetic(10000, seed=77, row0=12345)
     cols, y, sig = synthetic.make(77, n_bins, 12345, 10000)
-    for f in range(4):
+    for f in range(5):
         assert np.array_equal(w.read_bins(f, 0, 10000), cols[f])
     lab, s = w.read_labels(0, 10000)
     assert np.mean(lab != y) < 1e-3 and np.array_equal(s, sig)
