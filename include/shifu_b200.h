@@ -216,6 +216,9 @@ SB_API int sb_load_rows(sb_handle* h, int32_t is_validation, int64_t n_rows, con
    starts at bins + f*pitch; bins 16-byte aligned, pitch a multiple of 16 and >= n_rows. */
 SB_API int sb_load_rows_device(sb_handle* h, int32_t is_validation, int64_t n_rows, const void* bins, int64_t pitch,
                                float* label, float* significance, float* weights);
+/* Replaces Data.subsampleWeights[w_index] of every training row (host array of n floats): the bag counts / bagging
+   mask DTWorker.sampleWeights draws at load time (dt/DTWorker.java:1515-1575), injected by the caller. */
+SB_API int sb_set_weights(sb_handle* h, int32_t w_index, const float* weights);
 /* Reads back per-row state (any pointer may be NULL): Data.predict, Data.output, current node id of
    tree `tree_id`, subsampleWeights[w_index]. */
 SB_API int sb_read_rows(sb_handle* h, int32_t is_validation, int32_t tree_id, int32_t w_index, float* predict,

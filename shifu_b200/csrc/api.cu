@@ -1062,6 +1062,18 @@ SB_API int sb_read_rows(sb_handle* h, int32_t is_validation, int32_t tree_id, in
     return SB_OK;
 }
 
+SB_API int sb_set_weights(sb_handle* h, int32_t w_index, const float* weights) {
+    if (!h || !weights) return fail(SB_ERR_INVALID, "null argument");
+    RowSet& r = h->train;
+    if (!r.loaded || !r.weights) return fail(SB_ERR_STATE, "training rows not loaded (or adopted without a weight array)");
+    if (w_index < 0 || w_index >= h->cfg.weights_per_row) return fail(SB_ERR_INVALID, "weight index out of range");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    SB_CUDA(cudaMemcpyAsync(r.weights + (int64_t)w_index * r.n, weights, (size_t)r.n * 4, cudaMemcpyHostToDevice, h->stream));
+    h->h2d_bytes += r.n * 4;
+    h->scales_valid = false;
+    return refresh_cnt_int(h);
+}
+
 SB_API int64_t sb_stats_len(sb_handle* h, const sb_iter_in* in) {
     if (!h || !in) return fail(SB_ERR_INVALID, "null argument");
     TodoLayout lay;
