@@ -219,6 +219,17 @@ SB_API int sb_load_rows_device(sb_handle* h, int32_t is_validation, int64_t n_ro
 /* Replaces Data.subsampleWeights[w_index] of every training row (host array of n floats): the bag counts / bagging
    mask DTWorker.sampleWeights draws at load time (dt/DTWorker.java:1515-1575), injected by the caller. */
 SB_API int sb_set_weights(sb_handle* h, int32_t w_index, const float* weights);
+/* The GBT bagging mask of DTWorker.sampleWeights / the per-tree redraw (dt/DTWorker.java:1521-1544, 643-668), drawn
+   on the device: subsampleWeights[w_index] of training row j becomes 1f iff the (first_draw + j)-th nextDouble() of
+   `new java.util.Random(seed)` is <= rate, else 0f -- the same numbers a seeded (baggingSampleSeed) reference worker
+   draws for its rows in load order.  Not stratified (the reference keeps one Random per class for that). */
+SB_API int sb_sample_weights(sb_handle* h, int32_t w_index, int64_t seed, double rate, int64_t first_draw);
+/* DTWorker.getBinIndex (dt/DTWorker.java:1001-1034) for a whole numeric column: values (device, n floats; NaN counts as
+   0f like DTWorker.getFloatValue :1299-1305) -> bin indices (device, uint8 if out_width == 1 else uint16).
+   bin_boundary is a HOST array of n_bins (<= 4096) doubles.  A value below the first boundary gets the all-ones
+   index (the reference returns -1), which sb_load_rows rejects.  Handle-free; runs on cuda_stream (NULL = default). */
+SB_API int sb_bin_values(const float* values, int64_t n, const double* bin_boundary, int32_t n_bins, void* bins_out,
+                         int32_t out_width, void* cuda_stream);
 /* Reads back per-row state (any pointer may be NULL): Data.predict, Data.output, current node id of
    tree `tree_id`, subsampleWeights[w_index]. */
 SB_API int sb_read_rows(sb_handle* h, int32_t is_validation, int32_t tree_id, int32_t w_index, float* predict,

@@ -154,7 +154,7 @@ EXPORTS = [
     "sb_stats_len", "sb_compute", "sb_compute_begin", "sb_scale_buffer", "sb_compute_stats", "sb_raw_buffer",
     "sb_acc_buffer", "sb_compute_finish", "sb_set_stream", "sb_best_splits", "sb_time_stats_pass", "sb_counters",
     "sb_load_synthetic", "sb_read_bins", "sb_read_labels", "sb_set_profiling", "sb_hist_time",
-    "sb_error_sums_static", "sb_pass_info", "sb_set_weights",
+    "sb_error_sums_static", "sb_pass_info", "sb_set_weights", "sb_sample_weights", "sb_bin_values",
     "sbh_master_create", "sbh_master_destroy", "sbh_master_initial", "sbh_master_do_compute", "sbh_master_tree_count",
     "sbh_master_halted", "sbh_master_export_tree",
 ]
@@ -201,6 +201,8 @@ def load_library(path=None):
     lib.sb_set_profiling.argtypes = [H, C.c_int32]
     lib.sb_hist_time.argtypes = [H, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     lib.sb_set_weights.argtypes = [H, C.c_int32, C.c_void_p]
+    lib.sb_sample_weights.argtypes = [H, C.c_int32, C.c_int64, C.c_double, C.c_int64]
+    lib.sb_bin_values.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]
     lib.sb_pass_info.argtypes = [H, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     lib.sbh_master_create.argtypes = [C.POINTER(SbConfig), C.POINTER(SbhParams), C.POINTER(H)]
     lib.sbh_master_destroy.argtypes = [H]
@@ -313,6 +315,9 @@ class Worker:
     def set_weights(self, w_index, weights):
         w = np.ascontiguousarray(weights, dtype=np.float32)
         check(self.lib, self.lib.sb_set_weights(self.h, w_index, w.ctypes.data))
+
+    def sample_weights(self, w_index, seed, rate, first_draw=0):
+        check(self.lib, self.lib.sb_sample_weights(self.h, w_index, seed, rate, first_draw))
 
     def load_synthetic(self, n_rows, seed, row0=0, label_kind=0, weighted=False, is_validation=False):
         check(self.lib, self.lib.sb_load_synthetic(self.h, int(is_validation), row0, n_rows, seed, label_kind,

@@ -1074,6 +1074,19 @@ SB_API int sb_set_weights(sb_handle* h, int32_t w_index, const float* weights) {
     return refresh_cnt_int(h);
 }
 
+SB_API int sb_sample_weights(sb_handle* h, int32_t w_index, int64_t seed, double rate, int64_t first_draw) {
+    if (!h) return fail(SB_ERR_INVALID, "null handle");
+    RowSet& r = h->train;
+    if (!r.loaded || !r.weights) return fail(SB_ERR_STATE, "training rows not loaded (or adopted without a weight array)");
+    if (w_index < 0 || w_index >= h->cfg.weights_per_row) return fail(SB_ERR_INVALID, "weight index out of range");
+    if (first_draw < 0) return fail(SB_ERR_INVALID, "first_draw must be >= 0");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    SB_CUDA(launch_java_bagging_mask(r.weights + (int64_t)w_index * r.n, r.n, seed, rate, first_draw, h->stream));
+    h->launches_count += 1;
+    h->scales_valid = false;
+    return refresh_cnt_int(h);
+}
+
 SB_API int64_t sb_stats_len(sb_handle* h, const sb_iter_in* in) {
     if (!h || !in) return fail(SB_ERR_INVALID, "null argument");
     TodoLayout lay;

@@ -159,6 +159,9 @@ cudaError_t launch_synthetic(uint8_t* bins, int64_t pitch, int n_features, const
 cudaError_t launch_check_bins(const void* const* cols, const int32_t* feat_bins, int n_features, int64_t n,
                               uint32_t* error_flag, cudaStream_t s);
 
+// ---- prep.cu
+cudaError_t launch_java_bagging_mask(float* weights, int64_t n, long long seed, double rate, long long first_draw, cudaStream_t s);
+
 // ---- split.cu
 // raw (lo, hi) integer accumulators -> the reference's double statistics (one rounding each).
 cudaError_t launch_finalize(const int64_t* raw_lo, const int64_t* raw_hi, int64_t total, int stats_size, int kind,

@@ -1,0 +1,106 @@
+// prep.cu -- the two steps on either side of the statistics build that SURVEY.md 8(f) ranks next:
+//   f1  binning at load: DTWorker.getBinIndex (dt/DTWorker.java:1001-1034) for a whole column on the device;
+//   f4  bagging masks from java.util.Random on the device (dt/DTWorker.java:1521-1544 at load, :643-668 per tree),
+//       with jump-ahead so that row j gets exactly the j-th nextDouble() of `new Random(seed)`.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace {
+
+constexpr int MAX_BOUNDARIES = 4096;
+__constant__ double c_boundaries[MAX_BOUNDARIES];
+
+// getBinIndex: NaN is mapped to 0f first, as DTWorker.getFloatValue does for unparsable input (:1299-1305).
+__global__ void bin_values_kernel(const float* __restrict__ values, int64_t n, int n_bins, void* out, int out_width) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        float v = values[i];
+        if (isnan(v)) v = 0.0f;
+        int bin = -1;
+        if (n_bins <= 1) bin = 0;
+        else if (v == __int_as_float(0x7f800000)) bin = n_bins - 1;
+        else if (v == __int_as_float(0xff800000)) bin = 0;
+        else {
+            int low = 0, high = n_bins - 1;
+            const double dv = (double)v;
+            while (low <= high) {
+                const int mid = (int)(((unsigned)low + (unsigned)high) >> 1);
+                const double lo_t = c_boundaries[mid];
+                const double hi_t = mid == n_bins - 1 ? 1.7976931348623157e308 : c_boundaries[mid + 1];
+                if (dv >= lo_t && dv < hi_t) { bin = mid; break; }
+                if (dv >= hi_t) low = mid + 1;
+                else high = mid - 1;
+            }
+        }
+        // -1 (value below the first boundary) is stored as the all-ones index, which sb_load_rows rejects
+        if (out_width == 2) static_cast<uint16_t*>(out)[i] = (uint16_t)bin;
+        else static_cast<uint8_t*>(out)[i] = (uint8_t)bin;
+    }
+}
+
+constexpr unsigned long long LCG_A = 0x5DEECE66DULL, LCG_C = 0xBULL, LCG_MASK = (1ULL << 48) - 1;
+
+// state after k steps from s: s * A^k + C * (A^(k-1) + ... + 1)  (mod 2^48), by binary decomposition of k
+__device__ __forceinline__ unsigned long long lcg_jump(unsigned long long s, unsigned long long k) {
+    unsigned long long a_acc = 1, c_acc = 0;        // identity map
+    unsigned long long a_pow = LCG_A, c_pow = LCG_C;  // the map "one step", squared as we go
+    while (k) {
+        if (k & 1) {
+            a_acc = (a_acc * a_pow) & LCG_MASK;
+            c_acc = (c_acc * a_pow + c_pow) & LCG_MASK;
+        }
+        c_pow = (c_pow * (a_pow + 1)) & LCG_MASK;
+        a_pow = (a_pow * a_pow) & LCG_MASK;
+        k >>= 1;
+    }
+    return (s * a_acc + c_acc) & LCG_MASK;
+}
+
+constexpr int ROWS_PER_THREAD = 32;
+
+// weights[j] = (j-th nextDouble() of new Random(seed), counted from first_draw) <= rate ? 1f : 0f
+__global__ void java_bagging_mask_kernel(float* __restrict__ weights, int64_t n, long long seed, double rate, long long first_draw) {
+    const int64_t chunks = (n + ROWS_PER_THREAD - 1) / ROWS_PER_THREAD;
+    for (int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; c < chunks; c += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t j0 = c * ROWS_PER_THREAD;
+        unsigned long long s = ((unsigned long long)seed ^ LCG_A) & LCG_MASK;  // Random(seed) scrambles the seed
+        s = lcg_jump(s, 2ULL * (unsigned long long)(first_draw + j0));           // two next() calls per nextDouble()
+        const int64_t j1 = min(n, j0 + ROWS_PER_THREAD);
+        for (int64_t j = j0; j < j1; ++j) {
+            s = (s * LCG_A + LCG_C) & LCG_MASK;
+            const long long hi = (long long)(s >> (48 - 26));
+            s = (s * LCG_A + LCG_C) & LCG_MASK;
+            const long long lo = (long long)(s >> (48 - 27));
+            const double d = (double)((hi << 27) + lo) * (1.0 / 9007199254740992.0);
+            weights[j] = d <= rate ? 1.0f : 0.0f;
+        }
+    }
+}
+
+}  // namespace
+
+namespace sb {
+cudaError_t launch_java_bagging_mask(float* weights, int64_t n, long long seed, double rate, long long first_draw, cudaStream_t s) {
+    if (n <= 0) return cudaSuccess;
+    int64_t g = ((n + ROWS_PER_THREAD - 1) / ROWS_PER_THREAD + 255) / 256;
+    if (g > 148 * 8) g = 148 * 8;
+    if (g < 1) g = 1;
+    java_bagging_mask_kernel<<<(int)g, 256, 0, s>>>(weights, n, seed, rate, first_draw);
+    return cudaGetLastError();
+}
+}  // namespace sb
+
+extern "C" SB_API int sb_bin_values(const float* values, int64_t n, const double* bin_boundary, int32_t n_bins, void* bins_out,
+                                    int32_t out_width, void* cuda_stream) {
+    if (!values || !bin_boundary || !bins_out || n < 0) return sb::fail(SB_ERR_INVALID, "sb_bin_values: null argument");
+    if (n_bins < 1 || n_bins > MAX_BOUNDARIES) return sb::fail(SB_ERR_RANGE, "sb_bin_values: between 1 and 4096 boundaries are supported");
+    if (out_width != 1 && out_width != 2) return sb::fail(SB_ERR_INVALID, "sb_bin_values: out_width must be 1 (uint8) or 2 (uint16)");
+    if (out_width == 1 && n_bins > 256) return sb::fail(SB_ERR_INVALID, "sb_bin_values: more than 256 bins need uint16 output");
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    SB_CUDA(cudaMemcpyToSymbolAsync(c_boundaries, bin_boundary, sizeof(double) * n_bins, 0, cudaMemcpyHostToDevice, stream));
+    if (n == 0) return SB_OK;
+    int64_t g = (n + 255) / 256;
+    if (g > 148 * 8) g = 148 * 8;
+    bin_values_kernel<<<(int)g, 256, 0, stream>>>(values, n, n_bins, bins_out, out_width);
+    SB_CUDA(cudaGetLastError());
+    return SB_OK;
+}

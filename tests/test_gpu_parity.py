@@ -368,3 +368,49 @@ def test_large_shape_size_independent_properties():
     assert np.array_equal(lvl3[0] + lvl3[1], lvl2[0]) and np.array_equal(lvl3[2] + lvl3[3], lvl2[1])
     for a, b in zip(runs[0], runs[1]):                                         # (3) reproducible bits
         assert np.array_equal(a, b)
+
+
+def test_device_binning_matches_get_bin_index(oracle_lib):
+    """f1: sb_bin_values against DTWorker.getBinIndex restated in the oracle, incl. +-inf, NaN, duplicate boundaries,
+    values on a boundary, a single-boundary column, and the reference's own cancer-judgement boundaries."""
+    import ctypes as C
+    import os
+    import torch
+    lib = capi.load_library()
+    rng = np.random.default_rng(61)
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cancer_judgement.npz"))
+    cases = [np.array([-np.inf, 1.0, 1.0, 2.0, 5.5]), np.array([-np.inf]), np.array([0.0, 0.25, 0.5]),
+             z["boundaries"][0], np.concatenate([[-np.inf], np.sort(rng.normal(size=300))])]
+    for bb in cases:
+        bb = np.ascontiguousarray(bb, dtype=np.float64)
+        v = rng.normal(size=5000).astype(np.float32) * 3
+        v[:8] = [np.inf, -np.inf, np.nan, 1.0, 2.0, 0.25, -1e30, 1e30]
+        v[8:8 + min(len(bb), 100)] = bb[:100].astype(np.float32)
+        width = 2 if len(bb) > 256 else 1
+        d_v = torch.from_numpy(v).cuda()
+        d_out = torch.zeros(len(v), dtype=torch.int16 if width == 2 else torch.uint8, device="cuda")
+        capi.check(lib, lib.sb_bin_values(d_v.data_ptr(), len(v), bb.ctypes.data, len(bb), d_out.data_ptr(), width, None))
+        torch.cuda.synchronize()
+        got = d_out.cpu().numpy().astype(np.int64)
+        vv = np.where(np.isnan(v), np.float32(0), v)
+        want = np.array([oracle_lib.orc_get_bin_index(C.c_float(float(x)), bb.ctypes.data, len(bb)) for x in vv])
+        want = np.where(want < 0, -1 if width == 2 else 255, want)
+        assert np.array_equal(got, want)
+
+
+def test_device_bagging_mask_is_java_random():
+    """f4: subsampleWeights drawn on the device are `new java.util.Random(seed).nextDouble() <= rate`, row by row."""
+    from shifu_b200.dt_master import JavaRandom
+    n = 70001
+    cfg = ConfigArrays([8] * 3)
+    w = Worker(cfg)
+    w.load_synthetic(n, seed=5)
+    for seed, rate, first in ((42, 0.7, 0), (-123456789012, 0.25, 1000003)):
+        w.sample_weights(0, seed, rate, first)
+        _, _, _, got = w.read_rows(n)
+        r = JavaRandom(seed)
+        for _ in range(first):
+            r.next_double()
+        want = np.array([1.0 if r.next_double() <= rate else 0.0 for _ in range(n)], dtype=np.float32)
+        assert np.array_equal(got, want)
+    w.close()
