@@ -673,7 +673,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 const int64_t want_chunks = std::max<int64_t>(1, (148 * 3 + tiles_total - 1) / tiles_total);
                 int64_t chunk_rows = ((n + want_chunks - 1) / want_chunks + 127) / 128 * 128;
                 chunk_rows = std::max<int64_t>(chunk_rows, 1024);
-                chunk_rows = std::min<int64_t>(chunk_rows, cnt_int ? MAX_ROWS_PER_FLUSH / 2 : MAX_ROWS_PER_FLUSH);
+                chunk_rows = std::min<int64_t>(chunk_rows, MAX_ROWS_PER_FLUSH);  // integer counts: 2^18 rows * 1024 < 2^32 as well
                 const int max_chunks = (int)(n / chunk_rows + rgroups + 1);
                 SB_CUDA(h->rl_keys.reserve((size_t)2 * n));
                 SB_CUDA(h->rl_vals.reserve((size_t)2 * n));
@@ -724,7 +724,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         int64_t n_chunks = (148 * 3 + tile_items - 1) / tile_items;
         n_chunks = std::max<int64_t>(1, std::min(n_chunks, tiles_rows));
         int64_t rpc = ((tiles_rows + n_chunks - 1) / n_chunks) * HIST_T_ROWS;
-        rpc = std::min<int64_t>(rpc, cnt_int ? MAX_ROWS_PER_FLUSH / 2 : MAX_ROWS_PER_FLUSH);  // 2^21 rows * 1024 < 2^32
+        rpc = std::min<int64_t>(rpc, MAX_ROWS_PER_FLUSH);  // integer counts: 2^18 rows * 1024 < 2^32 as well
         n_chunks = (n + rpc - 1) / rpc;
         a.rows_per_chunk = rpc;
         a.stats_size = h->stats_size;

@@ -26,8 +26,8 @@ int fail(int code, const std::string& msg);
 // A per-record fp32 contribution v is turned into q = rint(v * 2^e) with |q| < 2^QBITS and summed in
 // 64-bit two's complement (shared memory, per block), then in a (lo, hi) pair of int64 words (global,
 // across blocks and GPUs).  e is chosen per statistic from max|v| over the rows of the pass.
-constexpr int QBITS = 39;                   // |q| < 2^39
-constexpr int64_t MAX_ROWS_PER_FLUSH = 1 << 22;  // 2^22 * 2^39 < 2^63
+constexpr int QBITS = 44;                   // |q| < 2^44: fp32 values down to max * 2^-20 are represented exactly
+constexpr int64_t MAX_ROWS_PER_FLUSH = 1 << 18;  // rows per block between merges: 2^18 * 2^44 < 2^63
 
 enum StatKind { STAT_VARIANCE = 0, STAT_CLASS = 1 };
 

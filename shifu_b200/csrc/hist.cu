@@ -15,7 +15,7 @@
 //     instruction hits 32 different banks and 32 different addresses -- no bank conflict and no same-address
 //     serialisation can happen inside a warp (what warp-aggregation would buy, without its __match_any cost);
 //   * per-record contributions are the reference's fp32 products, converted to 64-bit fixed point
-//     (q = rint(v * 2^e), |q| < 2^39) and added with native 32-bit ATOMS.ADD + carry: shared-memory
+//     (q = rint(v * 2^e), |q| < 2^44) and added with native 32-bit ATOMS.ADD + carry: shared-memory
 //     fp32/fp64/u64 atomicAdd compile to CAS loops on sm_100a and measured 6-10x slower (tools/ubench_smem.cu).
 //     When every sig*weight product of the pass is a small integer (the default: no weight column, 0/1 bagging
 //     mask, Poisson bag counts) the count statistic is a single 32-bit add;

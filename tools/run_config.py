@@ -82,8 +82,8 @@ while it is not None:
     todo_trees = len({it.struct.todo[i].tree_id for i in range(n_todo)})
     feats = sum((it.struct.todo[i].n_features or F) for i in range(n_todo)) / max(n_todo, 1)
     if C["gbdt"] and C["rate"] < 1.0 and it.struct.switch_to_next_tree and m.n_trees >= 2:
-        nw = (rng.random(n_local) <= 0.5).astype(np.float32)  # bagging mask redrawn per tree (dt/DTWorker.java:643-668)
-        it.struct.new_weights = nw.ctypes.data_as(capi.C.POINTER(capi.C.c_float))
+        # bagging mask redrawn per tree (dt/DTWorker.java:643-668) on the device, java.util.Random semantics
+        w.sample_weights(0, 1000 + m.n_trees, 0.5, 0)
     nxt, p, sc = None, 0, None
     # one pass (bench.grow_tree grows a whole GBT tree; here passes are timed one by one)
     w.compute_begin(it)
