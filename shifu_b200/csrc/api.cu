@@ -670,11 +670,9 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                     h->launches_count += 1;
                 }
                 const int tiles_total = n_rt + n_wt;
-                const int64_t want_chunks = std::max<int64_t>(1, (148 * 3 + tiles_total - 1) / tiles_total);
-                int64_t chunk_rows = ((n + want_chunks - 1) / want_chunks + 127) / 128 * 128;
-                chunk_rows = std::max<int64_t>(chunk_rows, 1024);
-                chunk_rows = std::min<int64_t>(chunk_rows, MAX_ROWS_PER_FLUSH);  // integer counts: 2^18 rows * 1024 < 2^32 as well
-                const int max_chunks = (int)(n / chunk_rows + rgroups + 1);
+                const int target_chunks = (int)std::max<int64_t>(1, (148 * 4 + tiles_total - 1) / tiles_total);
+                const int64_t chunk_rows = MAX_ROWS_PER_FLUSH;  // upper bound; integer counts: 2^18 rows * 1024 < 2^32 as well
+                const int max_chunks = (int)(n / chunk_rows + target_chunks + rgroups + 2);
                 SB_CUDA(h->rl_keys.reserve((size_t)2 * n));
                 SB_CUDA(h->rl_vals.reserve((size_t)2 * n));
                 const size_t temp_bytes = rowlist_sort_temp_bytes(n);
@@ -690,7 +688,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 la.slot_of_node = a.slot_of_node; la.slot_table_size = a.slot_table_size; la.gs = rgs; la.n_groups = rgroups;
                 la.stats_size = h->stats_size; la.kind = h->stat_kind; la.cnt_int = cnt_int; la.scales = h->d_scales;
                 la.keys_in = h->rl_keys.p; la.keys_out = h->rl_keys.p + n; la.vals_in = h->rl_vals.p; la.vals_out = h->rl_vals.p + n;
-                la.temp = h->rl_temp.p; la.temp_bytes = temp_bytes; la.chunk_rows = chunk_rows;
+                la.temp = h->rl_temp.p; la.temp_bytes = temp_bytes; la.chunk_rows = chunk_rows; la.target_chunks = target_chunks;
                 la.offsets = h->rl_tables.p; la.chunk_begin = h->rl_tables.p + 257; la.chunk_end = h->rl_tables.p + 257 + max_chunks;
                 la.chunk_group = h->rl_chunk_group.p; la.n_chunks = h->rl_chunk_group.p + max_chunks; la.max_chunks = max_chunks;
                 la.ops = h->rl_ops.p; la.error_flag = h->d_error_flag;

@@ -51,7 +51,8 @@ struct RowListArgs {
     uint32_t *vals_in, *vals_out;
     void* temp;
     size_t temp_bytes;
-    int64_t chunk_rows;
+    int64_t chunk_rows;        // upper bound of rows per chunk (accumulator headroom)
+    int target_chunks;         // the chunk size is chosen on the device so that about this many chunks result
     int64_t* offsets;          // [n_groups + 1]
     int32_t* chunk_group;      // [max_chunks]
     int64_t* chunk_begin;

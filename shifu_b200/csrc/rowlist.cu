@@ -60,8 +60,8 @@ __global__ void rowlist_keys_kernel(int64_t n, const int32_t* __restrict__ node_
 
 // offsets[g] = first position of key >= g in the sorted keys, g = 0..n_groups (offsets[n_groups] = number of active
 // rows); then the chunk table: chunk c covers ops [begin, end) of one group.
-__global__ void rowlist_chunks_kernel(const uint8_t* __restrict__ sorted_keys, int64_t n, int n_groups, int64_t chunk_rows,
-                                      int64_t* __restrict__ offsets, int32_t* __restrict__ chunk_group,
+__global__ void rowlist_chunks_kernel(const uint8_t* __restrict__ sorted_keys, int64_t n, int n_groups, int64_t max_chunk_rows,
+                                      int target_chunks, int64_t* __restrict__ offsets, int32_t* __restrict__ chunk_group,
                                       int64_t* __restrict__ chunk_begin, int64_t* __restrict__ chunk_end,
                                       int32_t* __restrict__ n_chunks, int max_chunks) {
     __shared__ int64_t off[257];
@@ -77,6 +77,12 @@ __global__ void rowlist_chunks_kernel(const uint8_t* __restrict__ sorted_keys, i
     }
     __syncthreads();
     if (threadIdx.x == 0) {
+        // chunk size from the number of ACTIVE rows of this pass (with subtraction most passes touch a fraction of the
+        // rows): about target_chunks chunks, so the grid fills the GPU several times over whatever the list length
+        const int64_t total = off[n_groups];
+        int64_t chunk_rows = ((total + target_chunks - 1) / target_chunks + 127) / 128 * 128;
+        if (chunk_rows < 1024) chunk_rows = 1024;
+        if (chunk_rows > max_chunk_rows) chunk_rows = max_chunk_rows;
         int c = 0;
         for (int g = 0; g < n_groups; ++g)
             for (int64_t b = off[g]; b < off[g + 1] && c < max_chunks; b += chunk_rows) {
@@ -174,8 +180,8 @@ cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s) {
     size_t temp = a.temp_bytes;
     e = cub::DeviceRadixSort::SortPairs(a.temp, temp, (const uint8_t*)a.keys_in, a.keys_out, (const uint32_t*)a.vals_in, a.vals_out, n, 0, 8, s);
     if (e != cudaSuccess) return e;
-    rowlist_chunks_kernel<<<1, 256, 0, s>>>(a.keys_out, n, a.n_groups, a.chunk_rows, a.offsets, a.chunk_group, a.chunk_begin,
-                                            a.chunk_end, a.n_chunks, a.max_chunks);
+    rowlist_chunks_kernel<<<1, 256, 0, s>>>(a.keys_out, n, a.n_groups, a.chunk_rows, a.target_chunks, a.offsets, a.chunk_group,
+                                            a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
 #define OPS(K, C)                                                                                                          \
