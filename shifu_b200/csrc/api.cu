@@ -670,7 +670,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                     h->launches_count += 1;
                 }
                 const int tiles_total = n_rt + n_wt;
-                const int target_chunks = (int)std::max<int64_t>(1, (148 * 4 + tiles_total - 1) / tiles_total);
+                const int target_chunks = (int)std::max<int64_t>(1, (148 * 2 + tiles_total - 1) / tiles_total);
                 const int64_t chunk_rows = MAX_ROWS_PER_FLUSH;  // upper bound; integer counts: 2^18 rows * 1024 < 2^32 as well
                 const int max_chunks = (int)(n / chunk_rows + target_chunks + rgroups + 2);
                 SB_CUDA(h->rl_keys.reserve((size_t)2 * n));
@@ -689,6 +689,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 la.stats_size = h->stats_size; la.kind = h->stat_kind; la.cnt_int = cnt_int; la.scales = h->d_scales;
                 la.keys_in = h->rl_keys.p; la.keys_out = h->rl_keys.p + n; la.vals_in = h->rl_vals.p; la.vals_out = h->rl_vals.p + n;
                 la.temp = h->rl_temp.p; la.temp_bytes = temp_bytes; la.chunk_rows = chunk_rows; la.target_chunks = target_chunks;
+                la.identity = (ns == 1 && lay.nodes[order[s0]].node_id == SB_ROOT_INDEX && partner[order[s0]] < 0) ? 1 : 0;
                 la.offsets = h->rl_tables.p; la.chunk_begin = h->rl_tables.p + 257; la.chunk_end = h->rl_tables.p + 257 + max_chunks;
                 la.chunk_group = h->rl_chunk_group.p; la.n_chunks = h->rl_chunk_group.p + max_chunks; la.max_chunks = max_chunks;
                 la.ops = h->rl_ops.p; la.error_flag = h->d_error_flag;
@@ -760,12 +761,17 @@ int plan_split_tasks(sb_handle* h) {
     std::vector<int32_t> begin;
     h->has_cat_tasks = false;
     int max_cat_bins = 0;
+    std::vector<int> rank;
+    tasks.reserve(lay.nodes.size() * (size_t)h->cfg.n_features);
     for (size_t n = 0; n < lay.nodes.size(); ++n) {
         const auto& nd = lay.nodes[n];
         begin.push_back((int32_t)tasks.size());
-        std::vector<int> cols;
-        for (int f : nd.features) cols.push_back(h->column_num[f]);
-        std::vector<int> rank = hashmap_visit_rank(cols);
+        // the visit order depends on the feature list only; consecutive todo nodes usually share it (ALL features)
+        if (n == 0 || nd.features != lay.nodes[n - 1].features) {
+            std::vector<int> cols;
+            for (int f : nd.features) cols.push_back(h->column_num[f]);
+            rank = hashmap_visit_rank(cols);
+        }
         for (size_t k = 0; k < nd.features.size(); ++k) {
             const int f = nd.features[k];
             SplitTask t;

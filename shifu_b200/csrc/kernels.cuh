@@ -52,6 +52,7 @@ struct RowListArgs {
     void* temp;
     size_t temp_bytes;
     int64_t chunk_rows;        // upper bound of rows per chunk (accumulator headroom)
+    int identity;              // 1: no sort -- the list is all rows in storage order (single todo node that is a tree root)
     int target_chunks;         // the chunk size is chosen on the device so that about this many chunks result
     int64_t* offsets;          // [n_groups + 1]
     int32_t* chunk_group;      // [max_chunks]

@@ -67,6 +67,7 @@ __global__ void rowlist_chunks_kernel(const uint8_t* __restrict__ sorted_keys, i
     __shared__ int64_t off[257];
     for (int g = threadIdx.x; g <= n_groups; g += blockDim.x) {
         int64_t lo = 0, hi = n;
+        if (!sorted_keys) lo = hi = (g == 0 ? 0 : n);  // identity list: a single group holding every row
         while (lo < hi) {
             const int64_t mid = (lo + hi) >> 1;
             if ((int)sorted_keys[mid] < g) lo = mid + 1;
@@ -100,14 +101,30 @@ template <int KIND, int CNT_INT>
 __global__ void rowlist_ops_kernel(const uint32_t* __restrict__ sorted_rows, const int64_t* __restrict__ offsets, int n_groups,
                                    const int32_t* __restrict__ node_id, const float* __restrict__ output,
                                    const float* __restrict__ significance, const float* __restrict__ weights,
-                                   const int16_t* __restrict__ slot_of_node, int gs, int stats_size,
+                                   const int16_t* __restrict__ slot_of_node, int slot_table_size, int gs, int stats_size,
                                    const float* __restrict__ scales, RowOps* __restrict__ ops, uint32_t* error_flag) {
     const int64_t total = offsets[n_groups];
     const float sc0 = scales[0], sc1 = scales[1], sc2 = scales[2];
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const uint32_t r = sorted_rows[i];
-        const int s = slot_of_node[node_id[r]];
+        // sorted_rows == nullptr: identity list (a pass whose single todo node is a tree root takes the rows in
+        // storage order; rows that do not belong to it are marked instead of being sorted out)
+        const uint32_t r = sorted_rows ? sorted_rows[i] : (uint32_t)i;
+        int s;
+        if (sorted_rows) s = slot_of_node[node_id[r]];
+        else {
+            const int nid = node_id[r];
+            s = (nid >= 0 && nid < slot_table_size) ? (int)slot_of_node[nid] : -1;
+        }
         const float w = weights ? weights[r] : 1.0f;
+        if (s < 0 || w == 0.0f) {
+            RowOps skip;
+            skip.row = r;
+            skip.slot = 0xffffffffu;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) skip.q[k] = 0;
+            ops[i] = skip;
+            continue;
+        }
         const float sig = significance[r];
         const float y = output[r];
         RowOps o;
@@ -174,19 +191,29 @@ cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s) {
     if (n <= 0) return cudaSuccess;
     int64_t g = (n + TPB - 1) / TPB;
     if (g > 148 * 16) g = 148 * 16;
-    rowlist_keys_kernel<<<(int)g, TPB, 0, s>>>(n, a.node_id, a.weights, a.slot_of_node, a.slot_table_size, a.gs, a.keys_in, a.vals_in);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    size_t temp = a.temp_bytes;
-    e = cub::DeviceRadixSort::SortPairs(a.temp, temp, (const uint8_t*)a.keys_in, a.keys_out, (const uint32_t*)a.vals_in, a.vals_out, n, 0, 8, s);
-    if (e != cudaSuccess) return e;
-    rowlist_chunks_kernel<<<1, 256, 0, s>>>(a.keys_out, n, a.n_groups, a.chunk_rows, a.target_chunks, a.offsets, a.chunk_group,
-                                            a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks);
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
+    cudaError_t e;
+    if (a.identity) {
+        // no keys, no sort: one group = all rows in storage order
+        rowlist_chunks_kernel<<<1, 256, 0, s>>>(nullptr, n, 1, a.chunk_rows, a.target_chunks, a.offsets, a.chunk_group,
+                                                a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    } else {
+        rowlist_keys_kernel<<<(int)g, TPB, 0, s>>>(n, a.node_id, a.weights, a.slot_of_node, a.slot_table_size, a.gs, a.keys_in, a.vals_in);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        size_t temp = a.temp_bytes;
+        e = cub::DeviceRadixSort::SortPairs(a.temp, temp, (const uint8_t*)a.keys_in, a.keys_out, (const uint32_t*)a.vals_in, a.vals_out, n, 0, 8, s);
+        if (e != cudaSuccess) return e;
+        rowlist_chunks_kernel<<<1, 256, 0, s>>>(a.keys_out, n, a.n_groups, a.chunk_rows, a.target_chunks, a.offsets, a.chunk_group,
+                                                a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
 #define OPS(K, C)                                                                                                          \
-    rowlist_ops_kernel<K, C><<<(int)g, TPB, 0, s>>>(a.vals_out, a.offsets, a.n_groups, a.node_id, a.output, a.significance, \
-                                                    a.weights, a.slot_of_node, a.gs, a.stats_size, a.scales, a.ops, a.error_flag)
+    rowlist_ops_kernel<K, C><<<(int)g, TPB, 0, s>>>(a.identity ? nullptr : a.vals_out, a.offsets, a.identity ? 1 : a.n_groups,  \
+                                                    a.node_id, a.output, a.significance, a.weights, a.slot_of_node,            \
+                                                    a.slot_table_size, a.gs, a.stats_size, a.scales, a.ops, a.error_flag)
     if (a.kind == STAT_VARIANCE) { if (a.cnt_int) OPS(STAT_VARIANCE, 1); else OPS(STAT_VARIANCE, 0); }
     else { if (a.cnt_int) OPS(STAT_CLASS, 1); else OPS(STAT_CLASS, 0); }
 #undef OPS
