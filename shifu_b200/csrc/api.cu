@@ -99,6 +99,7 @@ struct sb_handle {
     DevBuf<int64_t> pair_off;
     DevBuf<int16_t> slot_of_node;
     DevBuf<SplitTask> tasks;
+    DevBuf<int64_t> task_node_off;
     DevBuf<int32_t> node_task_begin;
     DevBuf<sb_gain> cand, gain_out;
     DevBuf<uint8_t> cand_bits, out_bits, new_dropout;
@@ -757,52 +758,73 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
 
 int plan_split_tasks(sb_handle* h) {
     const TodoLayout& lay = h->layout;
-    std::vector<SplitTask> tasks;
-    std::vector<int32_t> begin;
+    const size_t N = lay.nodes.size();
     h->has_cat_tasks = false;
     int max_cat_bins = 0;
-    std::vector<int> rank;
-    tasks.reserve(lay.nodes.size() * (size_t)h->cfg.n_features);
-    for (size_t n = 0; n < lay.nodes.size(); ++n) {
+    bool same_lists = N > 0;
+    for (size_t n = 1; n < N && same_lists; ++n) same_lists = lay.nodes[n].features == lay.nodes[0].features;
+    // tasks of one node: (feature, block offset relative to the node, bins, kind, HashMap visit rank)
+    auto node_tasks = [&](size_t n, int64_t base, std::vector<SplitTask>& out) {
         const auto& nd = lay.nodes[n];
-        begin.push_back((int32_t)tasks.size());
-        // the visit order depends on the feature list only; consecutive todo nodes usually share it (ALL features)
-        if (n == 0 || nd.features != lay.nodes[n - 1].features) {
-            std::vector<int> cols;
-            for (int f : nd.features) cols.push_back(h->column_num[f]);
-            rank = hashmap_visit_rank(cols);
-        }
+        std::vector<int> cols;
+        for (int f : nd.features) cols.push_back(h->column_num[f]);
+        const std::vector<int> rank = hashmap_visit_rank(cols);
         for (size_t k = 0; k < nd.features.size(); ++k) {
             const int f = nd.features[k];
             SplitTask t;
             t.node = (int32_t)n;
             t.feature = f;
-            t.offset = nd.offset + nd.feat_off[k];
+            t.offset = base + nd.feat_off[k];
             t.n_bins = h->n_bins[f];
             t.categorical = h->is_cat[f];
             t.visit_rank = rank[k];
             t.pad = 0;
             if (t.categorical) { h->has_cat_tasks = true; max_cat_bins = std::max(max_cat_bins, t.n_bins); }
-            tasks.push_back(t);
+            out.push_back(t);
         }
+    };
+    size_t n_tasks = 0;
+    for (const auto& nd : lay.nodes) n_tasks += nd.features.size();
+    h->n_tasks = (int)n_tasks;
+    SB_CUDA(h->tasks.reserve(n_tasks + (N ? lay.nodes[0].features.size() : 0) + 1));
+    SB_CUDA(h->node_task_begin.reserve(N + 1));
+    SB_CUDA(h->cand.reserve(n_tasks));
+    SB_CUDA(h->gain_out.reserve(N));
+    if (same_lists && N > 1) {
+        // one template row + the node offsets; expanded on the device
+        std::vector<SplitTask> tmpl;
+        node_tasks(0, 0, tmpl);
+        const int fk = (int)tmpl.size();
+        std::vector<int64_t> node_off(N);
+        for (size_t n = 0; n < N; ++n) node_off[n] = lay.nodes[n].offset;
+        SB_CUDA(h->task_node_off.reserve(N));
+        SplitTask* d_tmpl = h->tasks.p + n_tasks;  // parked behind the expanded table
+        if (fk > 0) SB_CUDA(cudaMemcpyAsync(d_tmpl, tmpl.data(), tmpl.size() * sizeof(SplitTask), cudaMemcpyHostToDevice, h->stream));
+        SB_CUDA(cudaMemcpyAsync(h->task_node_off.p, node_off.data(), N * 8, cudaMemcpyHostToDevice, h->stream));
+        SB_CUDA(launch_expand_tasks(d_tmpl, fk, h->task_node_off.p, (int)N, h->tasks.p, h->node_task_begin.p, h->stream));
+        h->launches_count += 1;
+        h->h2d_bytes += tmpl.size() * sizeof(SplitTask) + N * 8;
+    } else {
+        std::vector<SplitTask> tasks;
+        std::vector<int32_t> begin;
+        tasks.reserve(n_tasks);
+        for (size_t n = 0; n < N; ++n) {
+            begin.push_back((int32_t)tasks.size());
+            node_tasks(n, lay.nodes[n].offset, tasks);
+        }
+        begin.push_back((int32_t)tasks.size());
+        if (!tasks.empty())
+            SB_CUDA(cudaMemcpyAsync(h->tasks.p, tasks.data(), tasks.size() * sizeof(SplitTask), cudaMemcpyHostToDevice, h->stream));
+        SB_CUDA(cudaMemcpyAsync(h->node_task_begin.p, begin.data(), begin.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        h->h2d_bytes += tasks.size() * sizeof(SplitTask) + begin.size() * 4;
     }
-    begin.push_back((int32_t)tasks.size());
-    h->n_tasks = (int)tasks.size();
-    SB_CUDA(h->tasks.reserve(tasks.size()));
-    SB_CUDA(h->node_task_begin.reserve(begin.size()));
-    SB_CUDA(h->cand.reserve(tasks.size()));
-    SB_CUDA(h->gain_out.reserve(lay.nodes.size()));
-    if (!tasks.empty())
-        SB_CUDA(cudaMemcpyAsync(h->tasks.p, tasks.data(), tasks.size() * sizeof(SplitTask), cudaMemcpyHostToDevice, h->stream));
-    SB_CUDA(cudaMemcpyAsync(h->node_task_begin.p, begin.data(), begin.size() * 4, cudaMemcpyHostToDevice, h->stream));
-    h->h2d_bytes += tasks.size() * sizeof(SplitTask) + begin.size() * 4;
     if (h->has_cat_tasks) {
-        SB_CUDA(h->cand_bits.reserve(tasks.size() * SB_MAX_CAT_BYTES));
-        SB_CUDA(h->out_bits.reserve(lay.nodes.size() * SB_MAX_CAT_BYTES));
-        SB_CUDA(h->sort_keys.reserve(tasks.size() * max_cat_bins));
-        SB_CUDA(h->sort_idx.reserve(tasks.size() * max_cat_bins));
-        SB_CUDA(h->sort_tmp.reserve(tasks.size() * max_cat_bins));
-        SB_CUDA(h->sort_flags.reserve(tasks.size() * max_cat_bins));
+        SB_CUDA(h->cand_bits.reserve(n_tasks * SB_MAX_CAT_BYTES));
+        SB_CUDA(h->out_bits.reserve(N * SB_MAX_CAT_BYTES));
+        SB_CUDA(h->sort_keys.reserve(n_tasks * max_cat_bins));
+        SB_CUDA(h->sort_idx.reserve(n_tasks * max_cat_bins));
+        SB_CUDA(h->sort_tmp.reserve(n_tasks * max_cat_bins));
+        SB_CUDA(h->sort_flags.reserve(n_tasks * max_cat_bins));
     }
     h->max_bins = max_cat_bins;
     return SB_OK;
@@ -901,7 +923,7 @@ SB_API void sb_destroy(sb_handle* h) {
     free_rowset(h->valid);
     for (auto& kv : h->trees) free_tree(kv.second);
     h->raw.release(); h->raw_prev.release(); h->d_pairs.release(); h->d_small_is_b.release(); h->stats.release(); h->tile_feats.release(); h->slot_fmask.release(); h->pair_off.release();
-    h->slot_of_node.release(); h->tasks.release(); h->node_task_begin.release(); h->cand.release(); h->gain_out.release();
+    h->slot_of_node.release(); h->tasks.release(); h->task_node_off.release(); h->node_task_begin.release(); h->cand.release(); h->gain_out.release();
     h->cand_bits.release(); h->out_bits.release(); h->new_dropout.release(); h->new_weights.release();
     h->sort_keys.release(); h->sort_idx.release(); h->sort_tmp.release(); h->sort_flags.release();
     h->rl_keys.release(); h->rl_vals.release(); h->rl_temp.release(); h->rl_tables.release(); h->rl_chunk_group.release(); h->rl_ops.release(); h->rt_tiles.release(); h->rt_fmask.release(); h->wt_tiles.release(); h->wt_fmask.release();

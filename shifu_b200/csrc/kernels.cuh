@@ -195,6 +195,8 @@ struct SplitTask {       // one (todo node, feature) pair
     int32_t visit_rank;  // position in the reference's HashMap iteration order (dt/DTMaster.java:324)
     int32_t pad;
 };
+cudaError_t launch_expand_tasks(const SplitTask* tmpl, int fk, const int64_t* node_off, int n_nodes, SplitTask* tasks,
+                                int32_t* begin, cudaStream_t s);
 struct SplitScratch {    // categorical features only: per task, max_bins entries each
     double* keys = nullptr;
     int* idx = nullptr;

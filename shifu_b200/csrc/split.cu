@@ -5,6 +5,8 @@
 // GainInfo.getGainInfoByMaxGain (dt/GainInfo.java:200-214).  One thread scans one (node, feature) block in the
 // reference's own order (prefix sums bin by bin, strict '>' from Double.MIN_VALUE, first maximum wins), so given
 // the same statistics it produces the same doubles as the Java code.  Built with -fmad=false.
+#include <algorithm>
+
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -351,6 +353,26 @@ __global__ void pair_fixup_kernel(const PairDesc* __restrict__ pairs, const int3
 }
 
 }  // namespace
+
+// All todo nodes share one feature list (the usual case): the (node, feature) task table is the first node's row
+// repeated with the node's block offset added, so only one row and the node offsets cross PCIe.
+__global__ void expand_tasks_kernel(const SplitTask* __restrict__ tmpl, int fk, const int64_t* __restrict__ node_off,
+                                    int n_nodes, SplitTask* __restrict__ tasks, int32_t* __restrict__ begin) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i <= n_nodes) begin[i] = i * fk;
+    if (i >= n_nodes * fk) return;
+    const int n = i / fk, k = i - n * fk;
+    SplitTask t = tmpl[k];
+    t.node = n;
+    t.offset += node_off[n];
+    tasks[i] = t;
+}
+cudaError_t launch_expand_tasks(const SplitTask* tmpl, int fk, const int64_t* node_off, int n_nodes, SplitTask* tasks,
+                                int32_t* begin, cudaStream_t s) {
+    const int total = std::max(n_nodes * fk, n_nodes + 1);
+    expand_tasks_kernel<<<(total + 255) / 256, 256, 0, s>>>(tmpl, fk, node_off, n_nodes, tasks, begin);
+    return cudaGetLastError();
+}
 
 cudaError_t launch_pair_decide(const PairDesc* pairs, int n_pairs, const int64_t* prev_lo, const int64_t* prev_hi,
                                int stats_size, int kind, int n_features, int16_t* slot_tables, int64_t* pair_off,
