@@ -112,6 +112,21 @@ class DevView:
         self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
 
 
+_WRAPPED = {}
+
+
+def _wrap(ptr, n, typestr):
+    """torch view of a library-owned device buffer (cached: the buffers only move when they grow)."""
+    import torch
+    key = (ptr, n, typestr)
+    t = _WRAPPED.get(key)
+    if t is None:
+        if len(_WRAPPED) > 64:
+            _WRAPPED.clear()
+        t = _WRAPPED[key] = torch.as_tensor(DevView(ptr, n, typestr), device="cuda")
+    return t
+
+
 def grow_tree(worker, master, it, dist_ctx, e2e_buffers=None):
     """One GBT tree through the device path; returns (next message, passes, last scalars)."""
     from shifu_b200 import capi
@@ -119,10 +134,11 @@ def grow_tree(worker, master, it, dist_ctx, e2e_buffers=None):
     tree_index = master.n_trees
     scalars = None
     while it is not None:
+        gains = None
         if e2e_buffers is None and dist_ctx is None:
             worker.compute_begin(it)
             worker.compute_stats()
-            scalars = worker.compute_finish()
+            scalars, gains, bits = worker.compute_finish_split(it.n_todo)
         elif dist_ctx is None:
             # the call a user makes: DTWorker.doCompute with host buffers (message in, statistics out)
             n = worker.stats_len(it)
@@ -134,30 +150,31 @@ def grow_tree(worker, master, it, dist_ctx, e2e_buffers=None):
             e2e_buffers["d2h"] += n * 8 + 32
             scalars = (out.train_count, out.validation_count, out.train_error, out.validation_error)
         else:
-            import torch
             import torch.distributed as dist
             from shifu_b200.sharding import reduce_pass
             worker.compute_begin(it)
             scales_fresh, acc_fresh = worker.pass_info()
-            sp, sb, rp, rb, ap_, ab = worker.device_buffers()
-            reduce_pass(dist, torch.as_tensor(DevView(sp, 3, "<i4"), device="cuda") if scales_fresh else None, None, None,
-                        scales_fresh, False)
+            if scales_fresh:
+                sp, sb = worker.device_buffer("scale")
+                reduce_pass(dist, _wrap(sp, 3, "<i4"), None, None, True, False)
             worker.compute_stats()
-            sp, sb, rp, rb, ap_, ab = worker.device_buffers()
+            rp, rb = worker.device_buffer("raw")
             # the DTMaster merge: one integer all-reduce per pass (+ the 4 scalars when they were recomputed)
-            reduce_pass(dist, None, torch.as_tensor(DevView(rp, rb // 8, "<i8"), device="cuda") if rb > 0 else None,
-                        torch.as_tensor(DevView(ap_, 4, "<f8"), device="cuda") if acc_fresh else None, False, acc_fresh)
-            if e2e_buffers is None:
-                scalars = worker.compute_finish()
-            else:
+            acc = None
+            if acc_fresh:
+                ap_, ab = worker.device_buffer("acc")
+                acc = _wrap(ap_, 4, "<f8")
+            reduce_pass(dist, None, _wrap(rp, rb // 8, "<i8") if rb > 0 else None, acc, False, acc_fresh)
+            out = None
+            if e2e_buffers is not None:
                 n = worker.stats_len(it)
                 out = capi.SbIterOut()
                 out.stats = C.cast(e2e_buffers["stats_ptr"], C.POINTER(C.c_double))
                 out.stats_len = e2e_buffers["stats_cap"]
-                capi.check(worker.lib, worker.lib.sb_compute_finish(worker.h, C.byref(out)))
                 e2e_buffers["d2h"] += n * 8 + 32
-                scalars = (out.train_count, out.validation_count, out.train_error, out.validation_error)
-        gains, bits = worker.best_splits(it.n_todo)
+            scalars, gains, bits = worker.compute_finish_split(it.n_todo, out=out)
+        if gains is None:
+            gains, bits = worker.best_splits(it.n_todo)
         passes += 1
         it = master.do_compute(gains, bits)
         if it is None or master.n_trees != tree_index:

@@ -284,6 +284,9 @@ SB_API int sb_set_stream(sb_handle* h, void* cuda_stream);
  * gains: [n_todo]; cat_bits: [n_todo * SB_MAX_CAT_BYTES] or NULL when no categorical feature exists.
  */
 SB_API int sb_best_splits(sb_handle* h, sb_gain* gains, uint8_t* cat_bits);
+/* sb_compute_finish followed by sb_best_splits with one stream synchronisation between them (the per-pass
+   latency matters once a level's statistics take under a millisecond). */
+SB_API int sb_compute_finish_split(sb_handle* h, sb_iter_out* out, sb_gain* gains, uint8_t* cat_bits);
 
 /* ------------------------------------------------------------------ host mirror of DTMaster (no CUDA) */
 

@@ -152,7 +152,7 @@ SBH_FSS = {"ALL": 0, "HALF": 1, "ONETHIRD": 2, "TWOTHIRDS": 3, "AUTO": 4, "SQRT"
 EXPORTS = [
     "sb_create", "sb_destroy", "sb_last_error", "sb_version", "sb_load_rows", "sb_load_rows_device", "sb_read_rows",
     "sb_stats_len", "sb_compute", "sb_compute_begin", "sb_scale_buffer", "sb_compute_stats", "sb_raw_buffer",
-    "sb_acc_buffer", "sb_compute_finish", "sb_set_stream", "sb_best_splits", "sb_time_stats_pass", "sb_counters",
+    "sb_acc_buffer", "sb_compute_finish", "sb_compute_finish_split", "sb_set_stream", "sb_best_splits", "sb_time_stats_pass", "sb_counters",
     "sb_load_synthetic", "sb_read_bins", "sb_read_labels", "sb_set_profiling", "sb_hist_time",
     "sb_error_sums_static", "sb_pass_info", "sb_set_weights", "sb_sample_weights", "sb_bin_values",
     "sbh_master_create", "sbh_master_destroy", "sbh_master_initial", "sbh_master_do_compute", "sbh_master_tree_count",
@@ -193,6 +193,7 @@ def load_library(path=None):
     lib.sb_compute_finish.argtypes = [H, C.POINTER(SbIterOut)]
     lib.sb_set_stream.argtypes = [H, C.c_void_p]
     lib.sb_best_splits.argtypes = [H, C.POINTER(SbGain), C.c_void_p]
+    lib.sb_compute_finish_split.argtypes = [H, C.POINTER(SbIterOut), C.POINTER(SbGain), C.c_void_p]
     lib.sb_time_stats_pass.argtypes = [H, C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.sb_counters.argtypes = [H, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     lib.sb_load_synthetic.argtypes = [H, C.c_int32, C.c_int64, C.c_int64, C.c_uint64, C.c_int32, C.c_int32]
@@ -382,6 +383,21 @@ class Worker:
             out.stats_len = n_stats
         check(self.lib, self.lib.sb_compute_finish(self.h, C.byref(out)))
         return out.train_count, out.validation_count, out.train_error, out.validation_error, stats[:n_stats]
+
+    def compute_finish_split(self, n_todo, with_cat=False, out=None):
+        """compute_finish + best_splits behind one synchronisation: ((scalars), gains, bits)."""
+        out = out or SbIterOut()
+        gains = (SbGain * max(n_todo, 1))()
+        bits = np.zeros(max(n_todo, 1) * SB_MAX_CAT_BYTES, dtype=np.uint8) if with_cat else None
+        check(self.lib, self.lib.sb_compute_finish_split(self.h, C.byref(out), gains, None if bits is None else bits.ctypes.data))
+        return (out.train_count, out.validation_count, out.train_error, out.validation_error), gains, bits
+
+    def device_buffer(self, which):
+        """(ptr, bytes) of one of the "scale" / "raw" / "acc" buffers."""
+        p, b = C.c_void_p(), C.c_int64()
+        fn = {"scale": self.lib.sb_scale_buffer, "raw": self.lib.sb_raw_buffer, "acc": self.lib.sb_acc_buffer}[which]
+        check(self.lib, fn(self.h, C.byref(p), C.byref(b)))
+        return p.value, b.value
 
     def device_buffers(self):
         """(scale_ptr, scale_bytes, raw_ptr, raw_bytes, acc_ptr, acc_bytes): what a multi-GPU driver all-reduces."""

@@ -110,6 +110,8 @@ struct sb_handle {
     int n_tasks = 0;
     bool has_cat_tasks = false;
     double* d_acc = nullptr;          // 4 doubles
+    void* pin = nullptr;              // pinned host block: PinnedOut, then the sb_gain records (+ category bits)
+    size_t pin_bytes = 0;
     double* d_err_scratch = nullptr;  // ERR_SCRATCH_DOUBLES
     uint32_t* d_maxbits = nullptr;    // 3 words (+1 pad)
     float* d_scales = nullptr;        // 3
@@ -123,6 +125,7 @@ struct sb_handle {
     DevBuf<int64_t> rl_tables;    // offsets[257] + chunk_begin[max] + chunk_end[max]
     DevBuf<int32_t> rl_chunk_group;  // [max] + n_chunks scalar at the end
     DevBuf<RowOps> rl_ops;        // [n]
+    DevBuf<int32_t> twin_map;     // feature held at each byte position of a twin row
     DevBuf<int32_t> rt_tiles;     // row-list path: tile_feats [n_rt][32*fpl] then tile_slot0 [n_rt]
     DevBuf<uint32_t> rt_fmask;    // [n_slots][n_rt][fpl]
     DevBuf<int32_t> wt_tiles;     // wide tiles: tile_feats [n_wt][8] then first wide index [n_wt]
@@ -510,9 +513,24 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
             if (rows_max_gs >= 1) { fpl = f; break; }
         }
     }
+    // Byte layout of a row of the row-major twin: full tiles hold features fpl*lane + k in natural order; the last,
+    // partly filled tile spreads its r features over the lanes first (kact = ceil(r / 32) features per lane), so the
+    // kernel issues kact instead of fpl rounds of atomics per row for it.
+    std::vector<int32_t> pos_of((size_t)F, -1);
+    int twin_pad = 32;
     if (fpl > 0) {
         const int tw = 32 * fpl;
-        std::vector<int32_t> rt_feats, rt_slot0;
+        for (int f0 = 0; f0 < F; f0 += tw) {
+            const int r = std::min(tw, F - f0), kact = (r + 31) / 32;
+            for (int j = 0; j < r; ++j) pos_of[f0 + j] = f0 + fpl * (j / kact) + (j % kact);
+        }
+        int max_pos = 0;
+        for (int f = 0; f < F; ++f) max_pos = std::max(max_pos, pos_of[f]);
+        twin_pad = (max_pos / 32 + 1) * 32;
+    }
+    if (fpl > 0) {
+        const int tw = 32 * fpl;
+        std::vector<int32_t> rt_feats, rt_slot0, rt_kact;
         std::vector<int> rt_of((size_t)F, -1);
         for (int f0 = 0; f0 < F; f0 += tw) {
             bool any = false;
@@ -520,12 +538,17 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
             if (!any) continue;
             const int t = (int)rt_slot0.size();
             rt_slot0.push_back(f0);
-            for (int k = 0; k < fpl; ++k)
-                for (int l = 0; l < 32; ++l) {
-                    const int f = f0 + fpl * l + k;
-                    if (f < F && used[f]) { rt_feats.push_back(f); rt_of[f] = t; }
-                    else rt_feats.push_back(-1);
-                }
+            const size_t base = rt_feats.size();
+            rt_feats.resize(base + tw, -1);
+            int kact = 1;
+            for (int f = f0; f < std::min(F, f0 + tw); ++f) {
+                if (!used[f]) continue;
+                const int rel = pos_of[f] - f0;
+                rt_feats[base + (size_t)(rel % fpl) * 32 + rel / fpl] = f;
+                rt_of[f] = t;
+                kact = std::max(kact, rel % fpl + 1);
+            }
+            rt_kact.push_back(kact);
         }
         n_rt = (int)rt_slot0.size();
         std::vector<uint32_t> rfm((size_t)S * n_rt * fpl, 0u);
@@ -534,24 +557,27 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
             for (int f : nd.features) {
                 const int t = rt_of[f];
                 if (t < 0) continue;  // wide feature
-                const int rel = f - rt_slot0[t];
+                const int rel = pos_of[f] - rt_slot0[t];
                 rfm[((size_t)s * n_rt + t) * fpl + rel % fpl] |= 1u << (rel / fpl);
             }
         }
         for (int s = 0; s < S && allf; ++s)
             for (int t = 0; t < n_rt && allf; ++t)
                 for (int k = 0; k < fpl && allf; ++k) {
-                    uint32_t full = 0;
-                    for (int l = 0; l < 32; ++l)
-                        if (rt_slot0[t] + fpl * l + k < F) full |= 1u << l;
+                    uint32_t full = 0;  // every feature that lives in this (tile, k)
+                    for (int f = rt_slot0[t]; f < std::min(F, rt_slot0[t] + tw); ++f) {
+                        const int rel = pos_of[f] - rt_slot0[t];
+                        if (rel % fpl == k) full |= 1u << (rel / fpl);
+                    }
                     if (rfm[((size_t)s * n_rt + t) * fpl + k] != full) allf = 0;
                 }
-        SB_CUDA(h->rt_tiles.reserve(rt_feats.size() + rt_slot0.size()));
+        SB_CUDA(h->rt_tiles.reserve(rt_feats.size() + 2 * rt_slot0.size()));
         SB_CUDA(h->rt_fmask.reserve(rfm.size()));
         SB_CUDA(cudaMemcpyAsync(h->rt_tiles.p, rt_feats.data(), rt_feats.size() * 4, cudaMemcpyHostToDevice, h->stream));
         SB_CUDA(cudaMemcpyAsync(h->rt_tiles.p + rt_feats.size(), rt_slot0.data(), rt_slot0.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        SB_CUDA(cudaMemcpyAsync(h->rt_tiles.p + rt_feats.size() + rt_slot0.size(), rt_kact.data(), rt_kact.size() * 4, cudaMemcpyHostToDevice, h->stream));
         SB_CUDA(cudaMemcpyAsync(h->rt_fmask.p, rfm.data(), rfm.size() * 4, cudaMemcpyHostToDevice, h->stream));
-        h->h2d_bytes += (rt_feats.size() + rt_slot0.size() + rfm.size()) * 4;
+        h->h2d_bytes += (rt_feats.size() + 2 * rt_slot0.size() + rfm.size()) * 4;
     }
 
     // per tree: slot table + launch
@@ -662,12 +688,23 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                     SB_CUDA(launch_transpose_bins16(tr.bins16, tr.pitch16, h->n_wide, n, tr.bins16_rm, tr.wpad, h->stream));
                     h->launches_count += 1;
                 }
+                if (fpl > 0 && tr.bins_rm && tr.rm_fpl != fpl) {  // the statistics layout changed (integer <-> real counts)
+                    SB_CUDA(cudaStreamSynchronize(h->stream));
+                    cudaFree(tr.bins_rm);
+                    tr.bins_rm = nullptr;
+                }
                 if (fpl > 0 && !tr.bins_rm) {  // row-major twin of the bin matrix, built once
                     // 32-byte row pitch: a lane group that reaches past F reads into the next row (masked out in
                     // the kernel); the allocation is padded so the last row's over-read stays inside it
-                    tr.fpad = ((F + 31) / 32) * 32;
+                    tr.fpad = twin_pad;
+                    tr.rm_fpl = fpl;
+                    std::vector<int32_t> feat_of_pos((size_t)twin_pad, -1);
+                    for (int f = 0; f < F; ++f) feat_of_pos[pos_of[f]] = f;
+                    SB_CUDA(h->twin_map.reserve((size_t)twin_pad));
+                    SB_CUDA(cudaMemcpyAsync(h->twin_map.p, feat_of_pos.data(), (size_t)twin_pad * 4, cudaMemcpyHostToDevice, h->stream));
+                    SB_CUDA(cudaStreamSynchronize(h->stream));  // feat_of_pos is a local
                     SB_CUDA(cudaMalloc(&tr.bins_rm, (size_t)std::max<int64_t>(n, 1) * tr.fpad + 256));
-                    SB_CUDA(launch_transpose_bins(static_cast<const uint8_t*>(tr.bins_base), tr.pitch, F, n, tr.bins_rm, tr.fpad, h->stream));
+                    SB_CUDA(launch_transpose_bins(static_cast<const uint8_t*>(tr.bins_base), tr.pitch, F, h->twin_map.p, n, tr.bins_rm, tr.fpad, h->stream));
                     h->launches_count += 1;
                 }
                 const int tiles_total = n_rt + n_wt;
@@ -698,6 +735,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 ra.rm_bins = tr.bins_rm; ra.fpad = tr.fpad; ra.ops = la.ops; ra.chunk_group = la.chunk_group;
                 ra.chunk_begin = la.chunk_begin; ra.chunk_end = la.chunk_end; ra.n_chunks = la.n_chunks;
                 ra.tile_feats = h->rt_tiles.p; ra.tile_slot0 = h->rt_tiles.p + (size_t)n_rt * 32 * fpl;
+                ra.tile_kact = ra.tile_slot0 + n_rt;
                 ra.slot_fmask = h->rt_fmask.p + (size_t)s0 * n_rt * fpl; ra.pair_off = a.pair_off; ra.n_tiles = n_rt; ra.gs = rgs;
                 ra.n_slots = ns; ra.bins_pad = bins_pad; ra.n_features = F; ra.stats_size = h->stats_size;
                 ra.cnt_shift = h->d_cnt_shift; ra.raw_lo = h->raw.p; ra.raw_hi = h->raw.p + lay.total;
@@ -922,13 +960,14 @@ SB_API void sb_destroy(sb_handle* h) {
     free_rowset(h->train);
     free_rowset(h->valid);
     for (auto& kv : h->trees) free_tree(kv.second);
-    h->raw.release(); h->raw_prev.release(); h->d_pairs.release(); h->d_small_is_b.release(); h->stats.release(); h->tile_feats.release(); h->slot_fmask.release(); h->pair_off.release();
+    h->raw.release(); h->raw_prev.release(); h->d_pairs.release(); h->d_small_is_b.release(); h->stats.release(); h->tile_feats.release(); h->twin_map.release(); h->slot_fmask.release(); h->pair_off.release();
     h->slot_of_node.release(); h->tasks.release(); h->task_node_off.release(); h->node_task_begin.release(); h->cand.release(); h->gain_out.release();
     h->cand_bits.release(); h->out_bits.release(); h->new_dropout.release(); h->new_weights.release();
     h->sort_keys.release(); h->sort_idx.release(); h->sort_tmp.release(); h->sort_flags.release();
     h->rl_keys.release(); h->rl_vals.release(); h->rl_temp.release(); h->rl_tables.release(); h->rl_chunk_group.release(); h->rl_ops.release(); h->rt_tiles.release(); h->rt_fmask.release(); h->wt_tiles.release(); h->wt_fmask.release();
     if (h->d_feat_bins) cudaFree(h->d_feat_bins);
     if (h->d_acc) cudaFree(h->d_acc);
+    if (h->pin) cudaFreeHost(h->pin);
     if (h->d_err_scratch) cudaFree(h->d_err_scratch);
     if (h->d_maxbits) cudaFree(h->d_maxbits);
     if (h->d_scales) cudaFree(h->d_scales);
@@ -1364,10 +1403,25 @@ SB_API int sb_acc_buffer(sb_handle* h, void** dev_ptr, int64_t* bytes) {
     return SB_OK;
 }
 
-SB_API int sb_compute_finish(sb_handle* h, sb_iter_out* out) {
-    if (!h || !out) return fail(SB_ERR_INVALID, "null argument");
-    if (!h->begun) return fail(SB_ERR_STATE, "sb_compute_finish before sb_compute_begin");
-    SB_CUDA(cudaSetDevice(h->cfg.device));
+// Small results travel through one pinned block so that a pass ends with a single stream synchronisation.
+struct PinnedOut {
+    double acc[4];
+    uint32_t flags[2];
+    uint32_t maxbits[4];
+};
+
+static int pinned_reserve(sb_handle* h, size_t bytes) {
+    if (bytes <= h->pin_bytes) return SB_OK;
+    if (h->pin) cudaFreeHost(h->pin);
+    h->pin = nullptr;
+    h->pin_bytes = 0;
+    const size_t cap = std::max<size_t>(bytes * 2, 1 << 16);
+    SB_CUDA(cudaMallocHost(&h->pin, cap));
+    h->pin_bytes = cap;
+    return SB_OK;
+}
+
+static int finish_enqueue(sb_handle* h, sb_iter_out* out) {
     const int64_t total = h->layout.total;
     if (out->stats && out->stats_len < total) return fail(SB_ERR_INVALID, "stats buffer too small");
     if (!h->pairs.empty()) {  // the larger child of every sibling pair = parent - smaller child (after the merge)
@@ -1378,35 +1432,99 @@ SB_API int sb_compute_finish(sb_handle* h, sb_iter_out* out) {
     }
     SB_CUDA(launch_finalize(h->raw.p, h->raw.p + total, total, h->stats_size, h->stat_kind, h->d_inv_scales, h->stats.p, h->stream));
     h->launches_count += 1;
-    double acc[4];
-    uint32_t flags[2] = {0, 0};
-    uint32_t maxbits[4];
-    SB_CUDA(cudaMemcpyAsync(acc, h->d_acc, 32, cudaMemcpyDeviceToHost, h->stream));
-    SB_CUDA(cudaMemcpyAsync(flags, h->d_error_flag, 4, cudaMemcpyDeviceToHost, h->stream));
-    SB_CUDA(cudaMemcpyAsync(maxbits, h->d_maxbits, 12, cudaMemcpyDeviceToHost, h->stream));
+    PinnedOut* po = static_cast<PinnedOut*>(h->pin);
+    SB_CUDA(cudaMemcpyAsync(po->acc, h->d_acc, 32, cudaMemcpyDeviceToHost, h->stream));
+    SB_CUDA(cudaMemcpyAsync(po->flags, h->d_error_flag, 4, cudaMemcpyDeviceToHost, h->stream));
+    SB_CUDA(cudaMemcpyAsync(po->maxbits, h->d_maxbits, 12, cudaMemcpyDeviceToHost, h->stream));
     if (out->stats && total > 0) {
         SB_CUDA(cudaMemcpyAsync(out->stats, h->stats.p, (size_t)total * 8, cudaMemcpyDeviceToHost, h->stream));
         h->d2h_bytes += total * 8;
     }
-    SB_CUDA(cudaStreamSynchronize(h->stream));
     h->d2h_bytes += 48;
-    if (flags[0] & 1u) return fail(SB_ERR_RANGE, "class index (int)(label + 1e-6f) outside [0, num_classes)");
-    if (flags[0] & 2u) return fail(SB_ERR_RANGE, "a bin index is outside [0, n_bins) of its feature");
-    if (flags[0] & 4u) return fail(SB_ERR_STATE, "NextNode is null: a split node is missing a child (dt/DTWorker.java:1089-1094)");
+    return SB_OK;
+}
+
+static int finish_check(sb_handle* h, sb_iter_out* out) {
+    const PinnedOut* po = static_cast<const PinnedOut*>(h->pin);
+    const uint32_t flags = po->flags[0];
+    h->begun = false;
+    if (flags & 1u) return fail(SB_ERR_RANGE, "class index (int)(label + 1e-6f) outside [0, num_classes)");
+    if (flags & 2u) return fail(SB_ERR_RANGE, "a bin index is outside [0, n_bins) of its feature");
+    if (flags & 4u) return fail(SB_ERR_STATE, "NextNode is null: a split node is missing a child (dt/DTWorker.java:1089-1094)");
     for (int k = 0; k < 3; ++k)
-        if ((maxbits[k] & 0x7f800000u) == 0x7f800000u) return fail(SB_ERR_RANGE, "non-finite per-row contribution (label, significance or weight)");
-    if ((maxbits[0] >> 23) >= 127 + 38) return fail(SB_ERR_RANGE, "significance * weight beyond 2^38");
-    out->train_count = acc[0];
-    out->validation_count = acc[1];
-    out->train_error = acc[2];
-    out->validation_error = acc[3];
+        if ((po->maxbits[k] & 0x7f800000u) == 0x7f800000u) return fail(SB_ERR_RANGE, "non-finite per-row contribution (label, significance or weight)");
+    if ((po->maxbits[0] >> 23) >= 127 + 38) return fail(SB_ERR_RANGE, "significance * weight beyond 2^38");
+    out->train_count = po->acc[0];
+    out->validation_count = po->acc[1];
+    out->train_error = po->acc[2];
+    out->validation_error = po->acc[3];
     h->stats_ready = true;
     if (h->enable_subtraction) {  // keep this pass's merged accumulators for the children of its nodes
         std::swap(h->raw, h->raw_prev);
         h->prev_layout = h->layout;
         h->prev_valid = true;
     }
-    h->begun = false;
+    return SB_OK;
+}
+
+// device side of sb_best_splits; the records land in the pinned block behind PinnedOut
+static int best_enqueue(sb_handle* h, bool want_bits) {
+    const int n_nodes = (int)h->layout.nodes.size();
+    if (n_nodes == 0) return SB_OK;
+    SplitScratch sc;
+    sc.keys = h->sort_keys.p; sc.idx = h->sort_idx.p; sc.tmp = h->sort_tmp.p; sc.flags = h->sort_flags.p; sc.max_bins = h->max_bins;
+    SB_CUDA(launch_best_splits(h->stats.p, h->tasks.p, h->n_tasks, n_nodes, h->cfg.impurity, h->stats_size,
+                               h->cfg.min_instances_per_node, h->cfg.min_info_gain, h->cand.p,
+                               h->has_cat_tasks ? h->cand_bits.p : nullptr, h->gain_out.p,
+                               h->has_cat_tasks ? h->out_bits.p : nullptr, h->node_task_begin.p, sc, h->stream));
+    h->launches_count += 2;
+    uint8_t* dst = static_cast<uint8_t*>(h->pin) + 256;
+    SB_CUDA(cudaMemcpyAsync(dst, h->gain_out.p, sizeof(sb_gain) * n_nodes, cudaMemcpyDeviceToHost, h->stream));
+    h->d2h_bytes += sizeof(sb_gain) * n_nodes;
+    if (want_bits && h->has_cat_tasks) {
+        SB_CUDA(cudaMemcpyAsync(dst + sizeof(sb_gain) * n_nodes, h->out_bits.p, (size_t)n_nodes * SB_MAX_CAT_BYTES, cudaMemcpyDeviceToHost, h->stream));
+        h->d2h_bytes += (int64_t)n_nodes * SB_MAX_CAT_BYTES;
+    }
+    return SB_OK;
+}
+
+static void best_deliver(sb_handle* h, sb_gain* gains, uint8_t* cat_bits) {
+    const size_t n_nodes = h->layout.nodes.size();
+    const uint8_t* src = static_cast<const uint8_t*>(h->pin) + 256;
+    memcpy(gains, src, sizeof(sb_gain) * n_nodes);
+    if (cat_bits && h->has_cat_tasks) memcpy(cat_bits, src + sizeof(sb_gain) * n_nodes, n_nodes * SB_MAX_CAT_BYTES);
+}
+
+static size_t pinned_need(const sb_handle* h) {
+    return 256 + h->layout.nodes.size() * (sizeof(sb_gain) + SB_MAX_CAT_BYTES);
+}
+
+SB_API int sb_compute_finish(sb_handle* h, sb_iter_out* out) {
+    if (!h || !out) return fail(SB_ERR_INVALID, "null argument");
+    if (!h->begun) return fail(SB_ERR_STATE, "sb_compute_finish before sb_compute_begin");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    int rc = pinned_reserve(h, pinned_need(h));
+    if (rc != SB_OK) return rc;
+    rc = finish_enqueue(h, out);
+    if (rc != SB_OK) return rc;
+    SB_CUDA(cudaStreamSynchronize(h->stream));
+    return finish_check(h, out);
+}
+
+SB_API int sb_compute_finish_split(sb_handle* h, sb_iter_out* out, sb_gain* gains, uint8_t* cat_bits) {
+    if (!h || !out || !gains) return fail(SB_ERR_INVALID, "null argument");
+    if (!h->begun) return fail(SB_ERR_STATE, "sb_compute_finish_split before sb_compute_begin");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    int rc = pinned_reserve(h, pinned_need(h));
+    if (rc != SB_OK) return rc;
+    rc = finish_enqueue(h, out);
+    if (rc != SB_OK) return rc;
+    rc = best_enqueue(h, cat_bits != nullptr);
+    if (rc != SB_OK) return rc;
+    SB_CUDA(cudaStreamSynchronize(h->stream));
+    rc = finish_check(h, out);
+    if (rc != SB_OK) return rc;
+    best_deliver(h, gains, cat_bits);
     return SB_OK;
 }
 
@@ -1422,22 +1540,13 @@ SB_API int sb_best_splits(sb_handle* h, sb_gain* gains, uint8_t* cat_bits) {
     if (!h || !gains) return fail(SB_ERR_INVALID, "null argument");
     if (!h->stats_ready) return fail(SB_ERR_STATE, "sb_best_splits before sb_compute_finish");
     SB_CUDA(cudaSetDevice(h->cfg.device));
-    const int n_nodes = (int)h->layout.nodes.size();
-    if (n_nodes == 0) return SB_OK;
-    SplitScratch sc;
-    sc.keys = h->sort_keys.p; sc.idx = h->sort_idx.p; sc.tmp = h->sort_tmp.p; sc.flags = h->sort_flags.p; sc.max_bins = h->max_bins;
-    SB_CUDA(launch_best_splits(h->stats.p, h->tasks.p, h->n_tasks, n_nodes, h->cfg.impurity, h->stats_size,
-                               h->cfg.min_instances_per_node, h->cfg.min_info_gain, h->cand.p,
-                               h->has_cat_tasks ? h->cand_bits.p : nullptr, h->gain_out.p,
-                               h->has_cat_tasks ? h->out_bits.p : nullptr, h->node_task_begin.p, sc, h->stream));
-    h->launches_count += 2;
-    SB_CUDA(cudaMemcpyAsync(gains, h->gain_out.p, sizeof(sb_gain) * n_nodes, cudaMemcpyDeviceToHost, h->stream));
-    h->d2h_bytes += sizeof(sb_gain) * n_nodes;
-    if (cat_bits && h->has_cat_tasks) {
-        SB_CUDA(cudaMemcpyAsync(cat_bits, h->out_bits.p, (size_t)n_nodes * SB_MAX_CAT_BYTES, cudaMemcpyDeviceToHost, h->stream));
-        h->d2h_bytes += (int64_t)n_nodes * SB_MAX_CAT_BYTES;
-    }
+    if (h->layout.nodes.empty()) return SB_OK;
+    int rc = pinned_reserve(h, pinned_need(h));
+    if (rc != SB_OK) return rc;
+    rc = best_enqueue(h, cat_bits != nullptr);
+    if (rc != SB_OK) return rc;
     SB_CUDA(cudaStreamSynchronize(h->stream));
+    best_deliver(h, gains, cat_bits);
     return SB_OK;
 }
 

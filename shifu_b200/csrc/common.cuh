@@ -48,6 +48,7 @@ struct RowSet {
     void* owned_bins = nullptr;
     uint8_t* bins_rm = nullptr;       // row-major twin [n][fpad] for the row-list path (built on first use)
     int fpad = 0;
+    int rm_fpl = 0;                   // features per lane the twin's byte layout was built for
     // features with more than 256 bins: uint16 columns [n_wide][pitch16] (+ row-major twin [n][wpad])
     uint16_t* bins16 = nullptr;
     int64_t pitch16 = 0;  // elements

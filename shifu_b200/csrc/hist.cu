@@ -437,9 +437,12 @@ __global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const
     constexpr int NTHR = RCfg<FPL>::NTHREADS;
     constexpr int BATCH = RCfg<FPL>::BATCH;
     extern __shared__ __align__(1024) unsigned char smem[];
-    const int ci = blockIdx.x / a.n_tiles;
-    const int tile_id = blockIdx.x - ci * a.n_tiles;
-    if (ci >= *a.n_chunks) return;  // the grid is an upper bound; uniform for the block
+    // Tile-major block order: the blocks of a full tile (fpl rounds of atomics per row) are dispatched before those of
+    // the partly filled last tile (kact rounds), so the shorter blocks fill the tail of the launch.
+    const int n_chunks = *a.n_chunks;
+    const int tile_id = blockIdx.x / n_chunks;
+    const int ci = blockIdx.x - tile_id * n_chunks;
+    if (tile_id >= a.n_tiles) return;  // the grid is an upper bound; uniform for the block
     const int nw = hist_words(KIND, CNT_INT, a.stats_size);
     RowOps* ops_s = reinterpret_cast<RowOps*>(smem);
     RStage* st = reinterpret_cast<RStage*>(smem + (size_t)R_NST * R_TILE * sizeof(RowOps));
@@ -494,6 +497,7 @@ __global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const
         for (int k = 0; k < FPL; ++k)
             if (a.tile_feats[tile_id * 32 * FPL + k * 32 + lane] >= 0 || !ALLF) lane_feat_ok |= 1u << k;
         const int wr0 = cw * RPW;
+        const int kact = a.tile_kact[tile_id];  // a partly filled tile spreads its features over the lanes first
         // per-lane dummy bin right behind the block's histogram (one bin's worth of words)
         const uint32_t dummy_addr = lane_base + (uint32_t)gcount * slot_stride;
 
@@ -547,6 +551,7 @@ __global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const
                     for (int k = 0; k < FPL; ++k) fmw[k] = ALLF ? 0xffffffffu : fm_tab[(slot & (R_MAX_GS - 1)) * FPL + k];
 #pragma unroll
                     for (int k = 0; k < FPL; ++k) {
+                        if (k >= kact) break;  // block-uniform
                         const uint32_t bin = (bw_cur[jb + j] >> (8 * k)) & 0xffu;
                         const bool ok = rowok && ((lane_feat_ok >> k) & 1u) && (ALLF || (fmw[k] & lane_bit) != 0u);
                         ad[j][k] = ok ? base + bin * bin_stride + k * 128u : dummy_addr;
@@ -570,6 +575,7 @@ __global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const
                 for (int j = 0; j < BATCH; ++j) {  // phase 2: carries
 #pragma unroll
                     for (int k = 0; k < FPL; ++k) {
+                        if (k >= kact) break;
                         if (KIND == STAT_VARIANCE) {
                             if (CNT_INT) {
                                 sred_add<2 * WORD>(ad[j][k], hi_plus_carry(o1[j][k], lo1[j], hi1[j]));

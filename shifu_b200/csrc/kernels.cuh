@@ -63,7 +63,7 @@ struct RowListArgs {
     RowOps* ops;               // [n]
     uint32_t* error_flag;
 };
-cudaError_t launch_transpose_bins(const uint8_t* cm, int64_t pitch, int n_features, int64_t n, uint8_t* rm, int fpad,
+cudaError_t launch_transpose_bins(const uint8_t* cm, int64_t pitch, int n_features, const int32_t* feat_of_pos, int64_t n, uint8_t* rm, int fpad,
                                   cudaStream_t s);
 // wide (uint16) columns [n_wide][pitch16] -> row-major [n][wpad]
 cudaError_t launch_transpose_bins16(const uint16_t* cm, int64_t pitch16, int n_wide, int64_t n, uint16_t* rm, int wpad,
@@ -79,8 +79,9 @@ struct HistRowsArgs {
     const int64_t* chunk_begin;
     const int64_t* chunk_end;
     const int32_t* n_chunks;
-    const int32_t* tile_feats;   // [n_tiles][32*fpl]: entry k*32+lane = feature slot tile_slot0 + fpl*lane + k, or -1
-    const int32_t* tile_slot0;   // [n_tiles] first feature slot of the tile (multiple of 32*fpl)
+    const int32_t* tile_feats;   // [n_tiles][32*fpl]: entry k*32+lane = feature held at byte tile_slot0 + fpl*lane + k of a twin row, or -1
+    const int32_t* tile_slot0;   // [n_tiles] byte position of the tile in a row of the twin (multiple of 32*fpl)
+    const int32_t* tile_kact;    // [n_tiles] features per lane actually populated (<= fpl): the k loop stops there
     const uint32_t* slot_fmask;  // [n_slots][n_tiles][fpl]: word k, bit lane: that feature is in the slot's list
     const int64_t* pair_off;     // [n_slots][F]
     int n_tiles, gs, n_slots, bins_pad, n_features, stats_size;

@@ -18,17 +18,17 @@ namespace {
 constexpr int TPB = 256;
 
 // column-major [F][pitch] -> row-major [n][fpad]; block = 32 features x 128 rows through shared memory
-__global__ void transpose_bins_kernel(const uint8_t* __restrict__ cm, int64_t pitch, int n_features, int64_t n,
-                                      uint8_t* __restrict__ rm, int fpad) {
+__global__ void transpose_bins_kernel(const uint8_t* __restrict__ cm, int64_t pitch, int n_features,
+                                      const int32_t* __restrict__ feat_of_pos, int64_t n, uint8_t* __restrict__ rm, int fpad) {
     __shared__ uint8_t tile[32][128 + 4];
     const int64_t r0 = (int64_t)blockIdx.x * 128;
     const int f0 = blockIdx.y * 32;
     // load: each warp takes 4 feature rows, a lane reads 4 consecutive bytes
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;  // 8 warps
     for (int k = warp; k < 32; k += 8) {
-        const int f = f0 + k;
+        const int f = feat_of_pos[f0 + k];  // byte f0 + k of a twin row holds this feature (-1: padding)
         uint32_t v = 0;
-        if (f < n_features) {
+        if (f >= 0 && f < n_features) {
             const int64_t rb = r0 + lane * 4;
             const uint8_t* src = cm + (int64_t)f * pitch + rb;
             if (rb + 3 < pitch) v = *reinterpret_cast<const uint32_t*>(src);
@@ -171,11 +171,11 @@ cudaError_t launch_transpose_bins16(const uint16_t* cm, int64_t pitch16, int n_w
     return cudaGetLastError();
 }
 
-cudaError_t launch_transpose_bins(const uint8_t* cm, int64_t pitch, int n_features, int64_t n, uint8_t* rm, int fpad,
-                                  cudaStream_t s) {
+cudaError_t launch_transpose_bins(const uint8_t* cm, int64_t pitch, int n_features, const int32_t* feat_of_pos, int64_t n,
+                                  uint8_t* rm, int fpad, cudaStream_t s) {
     if (n <= 0) return cudaSuccess;
     dim3 grid((unsigned)((n + 127) / 128), (unsigned)(fpad / 32));
-    transpose_bins_kernel<<<grid, 256, 0, s>>>(cm, pitch, n_features, n, rm, fpad);
+    transpose_bins_kernel<<<grid, 256, 0, s>>>(cm, pitch, n_features, feat_of_pos, n, rm, fpad);
     return cudaGetLastError();
 }
 

@@ -115,13 +115,21 @@ struct Cand {
     int node_class, left_class, right_class;
 };
 
-// One (node, feature) block.  order == nullptr for numeric features.  pass_flags (categorical only) records which
-// loop iterations produced a candidate: only those add their category to leftCategories (the `continue`s at
-// dt/Impurity.java:157,166 skip the add), which is needed to rebuild the winner's bitset.
-__device__ Cand scan_feature(const double* __restrict__ s, int bins, int impurity_kind, int c, int min_inst,
-                             double min_gain, const int* order, uint8_t* pass_flags) {
+// One (node, feature) block, scanned by one warp.  The running left-hand sums are a chain of double additions whose
+// order fixes the result bits, so every lane walks the whole chain (the same additions in the same order -> the same
+// bits); what is spread over the lanes is the expensive part, the divisions of the candidate evaluation: lane l keeps
+// the prefix of candidates l, l + 32, ... and evaluates those.  Each lane keeps its first strictly-greater maximum; the
+// warp then takes the largest gain, smallest candidate index among equals -- the candidate the sequential loop's
+// "gain > maxGain" test selects (dt/Impurity.java:182-196).
+// order == nullptr for numeric features.  pass_flags (categorical only) records which loop iterations produced a
+// candidate: only those add their category to leftCategories (the `continue`s at dt/Impurity.java:157,166 skip the
+// add), which is needed to rebuild the winner's bitset.
+__device__ Cand warp_scan_feature(const double* __restrict__ s, int bins, int impurity_kind, int c, int min_inst,
+                                  double min_gain, const int* order, uint8_t* pass_flags, int lane) {
     Cand best;
     best.found = false;
+    best.split_i = 0x7fffffff;
+    best.gain = 0.0;
     double max_gain = JAVA_DOUBLE_MIN_VALUE;
     if (impurity_kind == SB_IMPURITY_VARIANCE || impurity_kind == SB_IMPURITY_FRIEDMANMSE) {
         double count = 0, sum = 0, sum_sq = 0;
@@ -129,14 +137,21 @@ __device__ Cand scan_feature(const double* __restrict__ s, int bins, int impurit
         const double impurity = var_impurity(count, sum, sum_sq);
         const double predict = count == 0.0 ? 0.0 : sum / count;
         double lc = 0, ls = 0, lq = 0;
-        for (int i = 0; i < bins - 1; ++i) {
-            const int index = order ? order[i] : i;
-            lc += s[index * 3]; ls += s[index * 3 + 1]; lq += s[index * 3 + 2];
-            const double rc = count - lc, rs = sum - ls, rq = sum_sq - lq;
+        for (int base = 0; base < bins - 1; base += 32) {
+            const int end = min(base + 32, bins - 1);
+            double mc = 0, ms = 0, mq = 0;
+            for (int i = base; i < end; ++i) {
+                const int index = order ? order[i] : i;
+                lc += s[index * 3]; ls += s[index * 3 + 1]; lq += s[index * 3 + 2];
+                if (i - base == lane) { mc = lc; ms = ls; mq = lq; }
+            }
+            const int i = base + lane;
+            if (i >= end) continue;
+            const double rc = count - mc, rs = sum - ms, rq = sum_sq - mq;
             if (pass_flags) pass_flags[i] = 0;
-            if (lc <= min_inst || rc <= min_inst) continue;
-            const double lw = lc / count, rw = rc / count;
-            const double li = var_impurity(lc, ls, lq), ri = var_impurity(rc, rs, rq);
+            if (mc <= min_inst || rc <= min_inst) continue;
+            const double lw = mc / count, rw = rc / count;
+            const double li = var_impurity(mc, ms, mq), ri = var_impurity(rc, rs, rq);
             // "friedmanmse" is Variance on the master (dt/DTMaster.java:1026-1032)
             const double gain = impurity - lw * li - rw * ri;
             if (gain <= min_gain) continue;
@@ -145,7 +160,7 @@ __device__ Cand scan_feature(const double* __restrict__ s, int bins, int impurit
                 max_gain = gain;
                 best.found = true; best.split_i = i; best.gain = gain; best.impurity = impurity; best.predict = predict;
                 best.li = li; best.ri = ri;
-                best.lp = lc == 0.0 ? 0.0 : ls / lc;
+                best.lp = mc == 0.0 ? 0.0 : ms / mc;
                 best.rp = rc == 0.0 ? 0.0 : rs / rc;
                 best.wgt = count;
                 best.node_class = best.left_class = best.right_class = 0;
@@ -153,18 +168,25 @@ __device__ Cand scan_feature(const double* __restrict__ s, int bins, int impurit
         }
     } else {
         const bool entropy = impurity_kind == SB_IMPURITY_ENTROPY;
-        double tot[MAX_CLASSES], l[MAX_CLASSES], r[MAX_CLASSES];
-        for (int j = 0; j < c; ++j) { tot[j] = 0; l[j] = 0; r[j] = 0; }
+        double tot[MAX_CLASSES], l[MAX_CLASSES], m[MAX_CLASSES], r[MAX_CLASSES];
+        for (int j = 0; j < c; ++j) { tot[j] = 0; l[j] = 0; m[j] = 0; r[j] = 0; }
         for (int i = 0; i < bins; ++i)
             for (int j = 0; j < c; ++j) tot[j] += s[i * c + j];
         const ClsInfo info = cls_info(tot, c, entropy);
         const double predict = info.sum_all == 0.0 ? 0.0 : (tot[1] / info.sum_all);
-        for (int i = 0; i < bins - 1; ++i) {
-            const int index = order ? order[i] : i;
-            for (int j = 0; j < c; ++j) l[j] += s[index * c + j];
-            const ClsInfo li = cls_info(l, c, entropy);
-            const double lp = li.sum_all == 0.0 ? 0.0 : (l[1] / li.sum_all);
-            for (int j = 0; j < c; ++j) r[j] = tot[j] - l[j];
+        for (int base = 0; base < bins - 1; base += 32) {
+            const int end = min(base + 32, bins - 1);
+            for (int i = base; i < end; ++i) {
+                const int index = order ? order[i] : i;
+                for (int j = 0; j < c; ++j) l[j] += s[index * c + j];
+                if (i - base == lane)
+                    for (int j = 0; j < c; ++j) m[j] = l[j];
+            }
+            const int i = base + lane;
+            if (i >= end) continue;
+            const ClsInfo li = cls_info(m, c, entropy);
+            const double lp = li.sum_all == 0.0 ? 0.0 : (m[1] / li.sum_all);
+            for (int j = 0; j < c; ++j) r[j] = tot[j] - m[j];
             const ClsInfo ri = cls_info(r, c, entropy);
             if (pass_flags) pass_flags[i] = 0;
             if (li.sum_all <= min_inst || ri.sum_all <= min_inst) continue;
@@ -188,16 +210,27 @@ __device__ Cand scan_feature(const double* __restrict__ s, int bins, int impurit
     return best;
 }
 
-__global__ void feature_split_kernel(const double* __restrict__ stats, const SplitTask* __restrict__ tasks, int n_tasks,
-                                     int impurity_kind, int c, int min_inst, double min_gain, sb_gain* cand,
-                                     uint8_t* cand_bits, double* sort_keys, int* sort_idx, int* sort_tmp,
-                                     uint8_t* pass_flags, int max_bins) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n_tasks) return;
+constexpr int SPLIT_WARPS = 4;       // tasks per block
+constexpr int SPLIT_STAGE = 1024;    // doubles of one task's statistics staged in shared memory (64 bins x 16 classes)
+constexpr int RANK_SORT_MAX = 128;   // categories up to which the warp sorts by counting ranks
+
+__global__ void __launch_bounds__(SPLIT_WARPS * 32)
+feature_split_kernel(const double* __restrict__ stats, const SplitTask* __restrict__ tasks, int n_tasks,
+                     int impurity_kind, int c, int min_inst, double min_gain, sb_gain* cand, uint8_t* cand_bits,
+                     double* sort_keys, int* sort_idx, int* sort_tmp, uint8_t* pass_flags, int max_bins) {
+    __shared__ double stage[SPLIT_WARPS][SPLIT_STAGE];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int t = blockIdx.x * SPLIT_WARPS + warp;
+    if (t >= n_tasks) return;  // warps are independent: no block-wide barrier below
     const SplitTask tk = tasks[t];
     const double* s = stats + tk.offset;
     const bool variance = impurity_kind == SB_IMPURITY_VARIANCE || impurity_kind == SB_IMPURITY_FRIEDMANMSE;
     const int ss = variance ? 3 : c;
+    if (tk.n_bins * ss <= SPLIT_STAGE) {
+        for (int i = lane; i < tk.n_bins * ss; i += 32) stage[warp][i] = s[i];
+        __syncwarp();
+        s = stage[warp];
+    }
     int* order = nullptr;
     uint8_t* flags = nullptr;
     if (tk.categorical) {
@@ -205,7 +238,7 @@ __global__ void feature_split_kernel(const double* __restrict__ stats, const Spl
         order = sort_idx + (size_t)t * max_bins;
         int* tmp = sort_tmp + (size_t)t * max_bins;
         flags = pass_flags + (size_t)t * max_bins;
-        for (int i = 0; i < tk.n_bins; ++i) {
+        for (int i = lane; i < tk.n_bins; i += 32) {
             double k;
             if (variance) {  // dt/Impurity.java:213-231: empty bins sort first with key Double.MIN_VALUE
                 k = JAVA_DOUBLE_MIN_VALUE;
@@ -217,44 +250,78 @@ __global__ void feature_split_kernel(const double* __restrict__ stats, const Spl
             }
             key[i] = k;
         }
-        stable_sort_by_key(key, order, tmp, tk.n_bins);
+        __syncwarp();
+        if (tk.n_bins <= RANK_SORT_MAX) {
+            // stable sort by counting: position of i = #{j : key[j] < key[i], or equal and j < i}
+            for (int i = lane; i < tk.n_bins; i += 32) {
+                const double ki = key[i];
+                int rank = 0;
+                for (int j = 0; j < tk.n_bins; ++j) {
+                    const double kj = key[j];
+                    if (java_double_less(kj, ki) || (j < i && !java_double_less(ki, kj))) ++rank;
+                }
+                order[rank] = i;
+            }
+        } else if (lane == 0) {
+            stable_sort_by_key(key, order, tmp, tk.n_bins);
+        }
+        __syncwarp();
     }
-    const Cand b = scan_feature(s, tk.n_bins, impurity_kind, c, min_inst, min_gain, order, flags);
+    const Cand b = warp_scan_feature(s, tk.n_bins, impurity_kind, c, min_inst, min_gain, order, flags, lane);
+    // winner over the lanes: largest gain, smallest loop index among equal gains
+    int win = b.found ? lane : -1;
+    double wg = b.gain;
+    int wi = b.split_i;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const int ow = __shfl_xor_sync(0xffffffffu, win, o);
+        const double og = __shfl_xor_sync(0xffffffffu, wg, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, wi, o);
+        if (ow >= 0 && (win < 0 || og > wg || (og == wg && oi < wi))) { win = ow; wg = og; wi = oi; }
+    }
+    __syncwarp();  // pass_flags of every lane are visible to the winner
+    if (win < 0) {
+        if (lane == 0) {
+            sb_gain g;
+            memset(&g, 0, sizeof(g));
+            cand[t] = g;
+        }
+        return;
+    }
+    if (lane != win) return;
     sb_gain g;
     memset(&g, 0, sizeof(g));
-    if (b.found) {
-        g.found = 1;
-        g.feature = tk.feature;
-        g.split_type = tk.categorical ? SB_SPLIT_CATEGORICAL : SB_SPLIT_CONTINUOUS;
-        g.split_bin = b.split_i;
-        g.gain = b.gain; g.impurity = b.impurity; g.predict = b.predict;
-        g.left_impurity = b.li; g.right_impurity = b.ri; g.left_predict = b.lp; g.right_predict = b.rp;
-        g.wgt_cnt = b.wgt;
-        g.node_class = b.node_class; g.left_class = b.left_class; g.right_class = b.right_class;
-        if (tk.categorical) {
-            // rebuild leftCategories as of the winning iteration (dt/Impurity.java:169-198)
-            const int n_cats = tk.n_bins - 1;
-            const int bytes = (n_cats + 1) / 8 + 1;
-            uint8_t* bits = cand_bits + (size_t)t * SB_MAX_CAT_BYTES;
-            for (int i = 0; i < bytes; ++i) bits[i] = 0;
-            int left_size = 0;
-            for (int i = 0; i <= b.split_i; ++i) {
-                if (!flags[i]) continue;
-                const int index = order[i];
-                const int v = index >= n_cats ? n_cats : index;
-                bits[v >> 3] |= (uint8_t)(1 << (v % 8));
-                left_size += 1;
-            }
-            int is_left = 1;
-            if (n_cats + 1 <= left_size * 2) {  // too many on the left: store the right side instead
-                is_left = 0;
-                // complement within [0, n_cats]
-                for (int i = 0; i < bytes; ++i) bits[i] = (uint8_t)~bits[i];
-                for (int v = n_cats + 1; v < bytes * 8; ++v) bits[v >> 3] &= (uint8_t)~(1 << (v % 8));
-            }
-            g.is_left = is_left;
-            g.cat_bytes = bytes;
+    g.found = 1;
+    g.feature = tk.feature;
+    g.split_type = tk.categorical ? SB_SPLIT_CATEGORICAL : SB_SPLIT_CONTINUOUS;
+    g.split_bin = b.split_i;
+    g.gain = b.gain; g.impurity = b.impurity; g.predict = b.predict;
+    g.left_impurity = b.li; g.right_impurity = b.ri; g.left_predict = b.lp; g.right_predict = b.rp;
+    g.wgt_cnt = b.wgt;
+    g.node_class = b.node_class; g.left_class = b.left_class; g.right_class = b.right_class;
+    if (tk.categorical) {
+        // rebuild leftCategories as of the winning iteration (dt/Impurity.java:169-198)
+        const int n_cats = tk.n_bins - 1;
+        const int bytes = (n_cats + 1) / 8 + 1;
+        uint8_t* bits = cand_bits + (size_t)t * SB_MAX_CAT_BYTES;
+        for (int i = 0; i < bytes; ++i) bits[i] = 0;
+        int left_size = 0;
+        for (int i = 0; i <= b.split_i; ++i) {
+            if (!flags[i]) continue;
+            const int index = order[i];
+            const int v = index >= n_cats ? n_cats : index;
+            bits[v >> 3] |= (uint8_t)(1 << (v % 8));
+            left_size += 1;
         }
+        int is_left = 1;
+        if (n_cats + 1 <= left_size * 2) {  // too many on the left: store the right side instead
+            is_left = 0;
+            // complement within [0, n_cats]
+            for (int i = 0; i < bytes; ++i) bits[i] = (uint8_t)~bits[i];
+            for (int v = n_cats + 1; v < bytes * 8; ++v) bits[v >> 3] &= (uint8_t)~(1 << (v % 8));
+        }
+        g.is_left = is_left;
+        g.cat_bytes = bytes;
     }
     cand[t] = g;
 }
@@ -309,18 +376,19 @@ __global__ void node_best_kernel(const sb_gain* __restrict__ cand, const uint8_t
 }
 
 // ---- histogram subtraction (sibling = parent - child), exact in the integer accumulators
-// One thread per sibling pair: which child holds less (weighted) count under the parent's split?  Only that child is
+// One warp per sibling pair: which child holds less (weighted) count under the parent's split?  Only that child is
 // accumulated directly; the other one is derived after the merge.  The decision is made from the parent's merged
-// (all-reduced) accumulators, so every GPU takes the same one.
+// (all-reduced) accumulators, so every GPU takes the same one.  Integer sums: the lane order does not matter.
 __global__ void pair_decide_kernel(const PairDesc* __restrict__ pairs, int n_pairs, const int64_t* __restrict__ prev_lo,
                                    const int64_t* __restrict__ prev_hi, int stats_size, int kind, int n_features,
                                    int16_t* __restrict__ slot_tables, int64_t* __restrict__ pair_off, int32_t* __restrict__ small_is_b) {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
     if (p >= n_pairs) return;
-    const PairDesc d = pairs[p];
+    const PairDesc& d = pairs[p];
     const int per_bin = kind == STAT_VARIANCE ? 1 : stats_size;  // the count is stat 0 (variance) or the sum over classes
     __int128 left = 0, total = 0;
-    for (int b = 0; b < d.n_bins; ++b) {
+    for (int b = lane; b < d.n_bins; b += 32) {
         __int128 c = 0;
         for (int k = 0; k < per_bin; ++k) {
             const int64_t i = d.parent_split_block + (int64_t)b * stats_size + k;
@@ -329,14 +397,26 @@ __global__ void pair_decide_kernel(const PairDesc* __restrict__ pairs, int n_pai
         total += c;
         if ((d.left_mask[b >> 3] >> (b & 7)) & 1) left += c;
     }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long l0 = __shfl_xor_sync(0xffffffffu, (unsigned long long)left, o);
+        const long long l1 = __shfl_xor_sync(0xffffffffu, (long long)(left >> 64), o);
+        const unsigned long long t0 = __shfl_xor_sync(0xffffffffu, (unsigned long long)total, o);
+        const long long t1 = __shfl_xor_sync(0xffffffffu, (long long)(total >> 64), o);
+        left += ((__int128)l1 << 64) + (__int128)l0;
+        total += ((__int128)t1 << 64) + (__int128)t0;
+    }
     const int b_small = (2 * left > total) ? 1 : 0;  // left = child A (even id); ties -> A
-    small_is_b[p] = b_small;
-    int16_t* table = slot_tables + d.table_off;
-    table[b_small ? d.node_a : d.node_b] = (int16_t)-1;  // the larger child is not accumulated
+    if (lane == 0) {
+        small_is_b[p] = b_small;
+        int16_t* table = slot_tables + d.table_off;
+        table[b_small ? d.node_a : d.node_b] = (int16_t)-1;  // the larger child is not accumulated
+    }
     if (b_small) {
         int64_t* row = pair_off + (size_t)d.slot * n_features;
-        for (int f = 0; f < n_features; ++f)
-            if (row[f] >= 0) row[f] += d.off_b - d.off_a;
+        const int64_t delta = d.off_b - d.off_a;
+        for (int f = lane; f < n_features; f += 32)
+            if (row[f] >= 0) row[f] += delta;
     }
 }
 
@@ -378,7 +458,7 @@ cudaError_t launch_pair_decide(const PairDesc* pairs, int n_pairs, const int64_t
                                int stats_size, int kind, int n_features, int16_t* slot_tables, int64_t* pair_off,
                                int32_t* small_is_b, cudaStream_t s) {
     if (n_pairs <= 0) return cudaSuccess;
-    pair_decide_kernel<<<(n_pairs + 63) / 64, 64, 0, s>>>(pairs, n_pairs, prev_lo, prev_hi, stats_size, kind, n_features,
+    pair_decide_kernel<<<(n_pairs * 32 + 127) / 128, 128, 0, s>>>(pairs, n_pairs, prev_lo, prev_hi, stats_size, kind, n_features,
                                                           slot_tables, pair_off, small_is_b);
     return cudaGetLastError();
 }
@@ -407,7 +487,7 @@ cudaError_t launch_best_splits(const double* stats, const SplitTask* tasks, int 
                                uint8_t* cand_bits, sb_gain* out, uint8_t* out_bits, const int32_t* node_task_begin,
                                const SplitScratch& sc, cudaStream_t s) {
     if (n_tasks <= 0 || n_nodes <= 0) return cudaSuccess;
-    feature_split_kernel<<<(n_tasks + 63) / 64, 64, 0, s>>>(stats, tasks, n_tasks, impurity, stats_size, min_instances,
+    feature_split_kernel<<<(n_tasks + SPLIT_WARPS - 1) / SPLIT_WARPS, SPLIT_WARPS * 32, 0, s>>>(stats, tasks, n_tasks, impurity, stats_size, min_instances,
                                                             min_info_gain, cand, cand_bits, sc.keys, sc.idx, sc.tmp,
                                                             sc.flags, sc.max_bins);
     cudaError_t e = cudaGetLastError();

@@ -202,6 +202,46 @@ def test_histogram_subtraction_is_exact():
         assert np.array_equal(a, b)
 
 
+def test_finish_split_equals_finish_then_best_splits():
+    """sb_compute_finish_split is sb_compute_finish + sb_best_splits behind one synchronisation: same bytes out."""
+    import ctypes as C
+    n, n_bins = 20000, [64] * 12 + [9] * 4
+    is_cat = [False] * 12 + [True] * 4
+    cols, y, sig, _ = make_data(n, n_bins, seed=77, weighted=True)
+    outs = []
+    for fused in (False, True):
+        cfg = ConfigArrays(n_bins, is_categorical=is_cat, max_depth=4, min_instances_per_node=1)
+        w = Worker(cfg)
+        w.load_rows(cols, y, sig, None)
+        root = Node(1)
+        todo_nodes, switch, rec = [root], True, []
+        while todo_nodes:
+            todo = [(k, 0, nd.id, []) for k, nd in enumerate(todo_nodes)]
+            it = IterIn(cfg, [(0, root)], todo, switch_to_next_tree=switch, is_first_tree=True)
+            w.compute_begin(it)
+            w.compute_stats()
+            if fused:
+                scal, gains, bits = w.compute_finish_split(len(todo), with_cat=True)
+            else:
+                scal = w.compute_finish()[:4]
+                gains, bits = w.best_splits(len(todo), with_cat=True)
+            rec.append((tuple(scal), C.string_at(gains, C.sizeof(capi.SbGain) * len(todo)), bits.tobytes()))
+            nxt = []
+            for k, nd in enumerate(todo_nodes):
+                g = gains[k]
+                if not g.found or g.gain <= 0 or index_to_level(nd.id) == 4:
+                    continue
+                left, right = apply_gain(cfg, nd, g, bits, k)
+                if index_to_level(nd.id) + 1 < 4:
+                    nxt += [left, right]
+            todo_nodes, switch = nxt, False
+        outs.append(rec)
+        w.close()
+    assert len(outs[0]) == len(outs[1]) >= 3
+    for a, b in zip(outs[0], outs[1]):
+        assert a == b
+
+
 def test_gbt_weighted_mixed_bins():
     run_gbt(15000, [64] * 20 + [32] * 10 + [10] * 7 + [2, 1, 255], seed=12, n_trees=2, max_depth=4, weighted=True)
 
