@@ -25,6 +25,8 @@
 //     statistics happens once, in finalize_stats_kernel, with a single rounding per statistic.
 #include <cuda.h>  // CUtensorMap (type only; the encoder is fetched through cudaGetDriverEntryPoint in api.cu)
 
+#include <utility>
+
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -431,11 +433,146 @@ template <int FPL> struct RCfg {
 };
 }  // namespace
 
+namespace {
+template <int... Ks, class F>
+__device__ __forceinline__ void static_for(std::integer_sequence<int, Ks...>, F&& f) {
+    (f(std::integral_constant<int, Ks>{}), ...);
+}
+}  // namespace
+
+// The consumer loop of hist_rows_kernel for a tile whose lanes hold KACT features each (KACT == FPL for a full tile).
+// KACT is a template parameter so that the k loop has no branches and the k * 128 byte offsets fold into the
+// immediates of the atomics.
+template <int KIND, int CNT_INT, int FPL, int ALLF, int KACT>
+__device__ __forceinline__ void rows_consume(const HistRowsArgs& a, const RowOps* ops_s, RStage* st, const uint32_t* fm_tab,
+                                             uint32_t hist_base, int cw, int lane, int tile_id, int gcount, int64_t begin,
+                                             int64_t end, int n_iters, int nw) {
+    constexpr int RPW = RCfg<FPL>::RPW;
+    constexpr int BATCH = RCfg<FPL>::BATCH;
+    constexpr uint32_t WORD = 128u * FPL;                           // bytes between the words of one bin
+    constexpr auto KS = std::make_integer_sequence<int, KACT>{};
+    const uint32_t lane_bit = 1u << lane;
+    const uint32_t lane_base = hist_base + (uint32_t)lane * 4u;
+    const uint32_t bin_stride = (uint32_t)nw * 128u * FPL;         // bytes between bins
+    const uint32_t slot_stride = (uint32_t)a.bins_pad * bin_stride;  // bytes between slots
+    const uint8_t* my_bins = a.rm_bins + a.tile_slot0[tile_id] + lane * FPL;
+    // ALLF (every todo node takes every feature): a (lane, k) without a feature reads a zero padding byte of the twin
+    // and accumulates into its own, never flushed column, so the hot loop carries no per-cell feature test; a lane
+    // without any feature does not load at all.  Otherwise the per-slot feature masks decide cell by cell.
+    bool lane_loads = !ALLF;
+#pragma unroll
+    for (int k = 0; k < FPL; ++k)
+        if (a.tile_feats[tile_id * 32 * FPL + k * 32 + lane] >= 0) lane_loads = true;
+    const int wr0 = cw * RPW;
+    // per-lane dummy bin right behind the block's histogram (one bin's worth of words)
+    const uint32_t dummy_addr = lane_base + (uint32_t)gcount * slot_stride;
+
+    // The bins of tile it+1 are requested before the atomics of tile it are issued, so the global-load latency
+    // of one tile hides behind the shared-memory work of the previous one.
+    uint32_t bw_cur[RPW], bw_next[RPW];
+    auto fetch_bins = [&](int it, uint32_t (&bw)[RPW]) {
+        const int s = it % R_NST;
+        mbar_wait(&st[s].full, (uint32_t)((it / R_NST) & 1));
+        const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
+        const RowOps* v = ops_s + s * R_TILE + wr0;
+#pragma unroll
+        for (int j = 0; j < RPW; ++j) {
+            bw[j] = 0;
+            if (wr0 + j < rows && lane_loads) {
+                const uint8_t* src = my_bins + (size_t)v[j].row * a.fpad;
+                if (FPL == 4) bw[j] = __ldg(reinterpret_cast<const uint32_t*>(src));
+                else if (FPL == 2) bw[j] = __ldg(reinterpret_cast<const unsigned short*>(src));
+                else bw[j] = __ldg(src);
+            }
+        }
+    };
+    if (n_iters > 0) fetch_bins(0, bw_cur);
+    for (int it = 0; it < n_iters; ++it) {
+        const int s = it % R_NST;
+        if (it + 1 < n_iters) fetch_bins(it + 1, bw_next);
+        const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
+        const RowOps* v = ops_s + s * R_TILE + wr0;
+#pragma unroll
+        for (int jb = 0; jb < RPW; jb += BATCH) {
+            if (wr0 + jb >= rows) break;  // warp-uniform
+            // Every atomic below is unconditional: a cell that must not count (row past the end of the list, skipped
+            // row, feature not in the node's list) is redirected to the per-lane dummy bin behind the histogram.
+            // No predicates, no divergence, no reconvergence bookkeeping in the hot loop.
+            uint32_t ad[BATCH][KACT];
+            uint32_t o0[BATCH][KACT], o1[BATCH][KACT], o2[BATCH][KACT];
+            uint32_t lo0[BATCH], lo1[BATCH], lo2[BATCH], hi0[BATCH], hi1[BATCH], hi2[BATCH];
+#pragma unroll
+            for (int j = 0; j < BATCH; ++j) {  // phase 1: operands, addresses, low-word atomics
+                const uint4 v0 = *reinterpret_cast<const uint4*>(&v[jb + j]);       // row, slot, q0, q1
+                const uint4 v1 = *reinterpret_cast<const uint4*>(&v[jb + j].q[2]);  // q2..q5
+                const uint32_t slot = v0.y;
+                const bool rowok = (wr0 + jb + j < rows) && slot < (uint32_t)gcount;
+                uint32_t base = lane_base + slot * slot_stride;
+                lo0[j] = v0.z; hi0[j] = v0.w;
+                lo1[j] = hi1[j] = lo2[j] = hi2[j] = 0;
+                if (KIND == STAT_VARIANCE) { lo1[j] = v1.x; hi1[j] = v1.y; lo2[j] = v1.z; hi2[j] = v1.w; }
+                else base += v1.x * FPL;  // class words
+                // ALLF: one select per row; a bad row lands in the dummy bin whatever its bins are
+                const uint32_t rbase = rowok ? base : dummy_addr;
+                const uint32_t bmul = rowok ? bin_stride : 0u;
+                const uint32_t bwj = bw_cur[jb + j];
+                const uint32_t fm_row = (slot & (R_MAX_GS - 1)) * FPL;
+                static_for(KS, [&](auto kc) {
+                    constexpr int k = decltype(kc)::value;
+                    constexpr uint32_t KO = 128u * k;
+                    const uint32_t bin = (k == 3) ? (bwj >> 24) : ((bwj >> (8 * k)) & 0xffu);
+                    uint32_t adr;
+                    if (ALLF) adr = rbase + bin * bmul;
+                    else adr = (rowok && (fm_tab[fm_row + k] & lane_bit) != 0u) ? base + bin * bin_stride : dummy_addr;
+                    ad[j][k] = adr;
+                    if (KIND == STAT_VARIANCE) {
+                        if (CNT_INT) {
+                            sred_add<KO>(adr, lo0[j]);
+                            o1[j][k] = satom_add<KO + WORD>(adr, lo1[j]);
+                            o2[j][k] = satom_add<KO + 3 * WORD>(adr, lo2[j]);
+                        } else {
+                            o0[j][k] = satom_add<KO>(adr, lo0[j]);
+                            o1[j][k] = satom_add<KO + 2 * WORD>(adr, lo1[j]);
+                            o2[j][k] = satom_add<KO + 4 * WORD>(adr, lo2[j]);
+                        }
+                    } else {
+                        if (CNT_INT) sred_add<KO>(adr, lo0[j]);
+                        else o0[j][k] = satom_add<KO>(adr, lo0[j]);
+                    }
+                });
+            }
+#pragma unroll
+            for (int j = 0; j < BATCH; ++j) {  // phase 2: carries
+                static_for(KS, [&](auto kc) {
+                    constexpr int k = decltype(kc)::value;
+                    constexpr uint32_t KO = 128u * k;
+                    const uint32_t adr = ad[j][k];
+                    if (KIND == STAT_VARIANCE) {
+                        if (CNT_INT) {
+                            sred_add<KO + 2 * WORD>(adr, hi_plus_carry(o1[j][k], lo1[j], hi1[j]));
+                            sred_add<KO + 4 * WORD>(adr, hi_plus_carry(o2[j][k], lo2[j], hi2[j]));
+                        } else {
+                            sred_add<KO + WORD>(adr, hi_plus_carry(o0[j][k], lo0[j], hi0[j]));
+                            sred_add<KO + 3 * WORD>(adr, hi_plus_carry(o1[j][k], lo1[j], hi1[j]));
+                            sred_add<KO + 5 * WORD>(adr, hi_plus_carry(o2[j][k], lo2[j], hi2[j]));
+                        }
+                    } else if (!CNT_INT) {
+                        sred_add<KO + WORD>(adr, hi_plus_carry(o0[j][k], lo0[j], hi0[j]));
+                    }
+                });
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&st[s].empty);
+#pragma unroll
+        for (int j = 0; j < RPW; ++j) bw_cur[j] = bw_next[j];
+    }
+}
+
 template <int KIND, int CNT_INT, int FPL, int ALLF>
 __global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const HistRowsArgs a) {
     constexpr int CONS_WARPS = RCfg<FPL>::CONS_WARPS;
     constexpr int NTHR = RCfg<FPL>::NTHREADS;
-    constexpr int BATCH = RCfg<FPL>::BATCH;
     extern __shared__ __align__(1024) unsigned char smem[];
     // Tile-major block order: the blocks of a full tile (fpl rounds of atomics per row) are dispatched before those of
     // the partly filled last tile (kact rounds), so the shorter blocks fill the tail of the launch.
@@ -457,7 +594,8 @@ __global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const
     const int bins_pad = a.bins_pad;
     const int n_iters = (int)((end - begin + R_TILE - 1) / R_TILE);
 
-    for (int i = threadIdx.x; i < gcount * bins_pad * nw * 32 * FPL; i += NTHR) hist[i] = 0u;
+    // the dummy bin behind the histogram is zeroed too: it only ever absorbs additions
+    for (int i = threadIdx.x; i < (gcount * bins_pad + 1) * nw * 32 * FPL; i += NTHR) hist[i] = 0u;
     if (threadIdx.x < R_MAX_GS * FPL) {
         const int sl = threadIdx.x / FPL, k = threadIdx.x % FPL;
         fm_tab[threadIdx.x] = sl < gcount ? a.slot_fmask[((size_t)(g0 + sl) * a.n_tiles + tile_id) * FPL + k] : 0u;
@@ -484,118 +622,16 @@ __global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const
         }
     } else {
         const int cw = warp - 1;
-        constexpr int RPW = RCfg<FPL>::RPW;
-        const uint32_t lane_bit = 1u << lane;
-        const uint32_t lane_base = smem_u32(hist) + (uint32_t)lane * 4u;
-        const uint32_t bin_stride = (uint32_t)nw * 128u * FPL;         // bytes between bins
-        const uint32_t slot_stride = (uint32_t)bins_pad * bin_stride;   // bytes between slots
-        constexpr uint32_t WORD = 128u * FPL;                           // bytes between the words of one bin
-        const uint8_t* my_bins = a.rm_bins + a.tile_slot0[tile_id] + lane * FPL;
-        // lanes whose feature slot does not exist (tile reaches past F) never touch the histogram
-        uint32_t lane_feat_ok = 0;
-#pragma unroll
-        for (int k = 0; k < FPL; ++k)
-            if (a.tile_feats[tile_id * 32 * FPL + k * 32 + lane] >= 0 || !ALLF) lane_feat_ok |= 1u << k;
-        const int wr0 = cw * RPW;
         const int kact = a.tile_kact[tile_id];  // a partly filled tile spreads its features over the lanes first
-        // per-lane dummy bin right behind the block's histogram (one bin's worth of words)
-        const uint32_t dummy_addr = lane_base + (uint32_t)gcount * slot_stride;
-
-        // The bins of tile it+1 are requested before the atomics of tile it are issued, so the global-load latency
-        // of one tile hides behind the shared-memory work of the previous one.
-        uint32_t bw_cur[RPW], bw_next[RPW];
-        auto fetch_bins = [&](int it, uint32_t (&bw)[RPW]) {
-            const int s = it % R_NST;
-            mbar_wait(&st[s].full, (uint32_t)((it / R_NST) & 1));
-            const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
-            const RowOps* v = ops_s + s * R_TILE + wr0;
-#pragma unroll
-            for (int j = 0; j < RPW; ++j) {
-                bw[j] = 0;
-                if (wr0 + j < rows) {
-                    const uint8_t* src = my_bins + (size_t)v[j].row * a.fpad;
-                    if (FPL == 4) bw[j] = __ldg(reinterpret_cast<const uint32_t*>(src));
-                    else if (FPL == 2) bw[j] = __ldg(reinterpret_cast<const unsigned short*>(src));
-                    else bw[j] = __ldg(src);
-                }
-            }
-        };
-        if (n_iters > 0) fetch_bins(0, bw_cur);
-        for (int it = 0; it < n_iters; ++it) {
-            const int s = it % R_NST;
-            if (it + 1 < n_iters) fetch_bins(it + 1, bw_next);
-            const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
-            const RowOps* v = ops_s + s * R_TILE + wr0;
-#pragma unroll
-            for (int jb = 0; jb < RPW; jb += BATCH) {
-                if (wr0 + jb >= rows) break;  // warp-uniform
-                // Every atomic below is unconditional: a cell that must not count (row past the end of the list, lane
-                // whose feature is not in the node's list or does not exist) is redirected to a per-lane dummy bin
-                // behind the histogram.  No predicates, no divergence, no reconvergence bookkeeping in the hot loop.
-                uint32_t ad[BATCH][FPL];
-                uint32_t o0[BATCH][FPL], o1[BATCH][FPL], o2[BATCH][FPL];
-                uint32_t lo0[BATCH], lo1[BATCH], lo2[BATCH], hi0[BATCH], hi1[BATCH], hi2[BATCH];
-#pragma unroll
-                for (int j = 0; j < BATCH; ++j) {  // phase 1: operands, addresses, low-word atomics
-                    const uint4 v0 = *reinterpret_cast<const uint4*>(&v[jb + j]);       // row, slot, q0, q1
-                    const uint4 v1 = *reinterpret_cast<const uint4*>(&v[jb + j].q[2]);  // q2..q5
-                    const uint32_t slot = v0.y;
-                    const bool rowok = (wr0 + jb + j < rows) && slot < (uint32_t)gcount;
-                    uint32_t base = lane_base + slot * slot_stride;
-                    lo0[j] = v0.z; hi0[j] = v0.w;
-                    lo1[j] = hi1[j] = lo2[j] = hi2[j] = 0;
-                    if (KIND == STAT_VARIANCE) { lo1[j] = v1.x; hi1[j] = v1.y; lo2[j] = v1.z; hi2[j] = v1.w; }
-                    else base += v1.x * FPL;  // class words
-                    uint32_t fmw[FPL];
-#pragma unroll
-                    for (int k = 0; k < FPL; ++k) fmw[k] = ALLF ? 0xffffffffu : fm_tab[(slot & (R_MAX_GS - 1)) * FPL + k];
-#pragma unroll
-                    for (int k = 0; k < FPL; ++k) {
-                        if (k >= kact) break;  // block-uniform
-                        const uint32_t bin = (bw_cur[jb + j] >> (8 * k)) & 0xffu;
-                        const bool ok = rowok && ((lane_feat_ok >> k) & 1u) && (ALLF || (fmw[k] & lane_bit) != 0u);
-                        ad[j][k] = ok ? base + bin * bin_stride + k * 128u : dummy_addr;
-                        if (KIND == STAT_VARIANCE) {
-                            if (CNT_INT) {
-                                sred_add<0>(ad[j][k], lo0[j]);
-                                o1[j][k] = satom_add<WORD>(ad[j][k], lo1[j]);
-                                o2[j][k] = satom_add<3 * WORD>(ad[j][k], lo2[j]);
-                            } else {
-                                o0[j][k] = satom_add<0>(ad[j][k], lo0[j]);
-                                o1[j][k] = satom_add<2 * WORD>(ad[j][k], lo1[j]);
-                                o2[j][k] = satom_add<4 * WORD>(ad[j][k], lo2[j]);
-                            }
-                        } else {
-                            if (CNT_INT) sred_add<0>(ad[j][k], lo0[j]);
-                            else o0[j][k] = satom_add<0>(ad[j][k], lo0[j]);
-                        }
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < BATCH; ++j) {  // phase 2: carries
-#pragma unroll
-                    for (int k = 0; k < FPL; ++k) {
-                        if (k >= kact) break;
-                        if (KIND == STAT_VARIANCE) {
-                            if (CNT_INT) {
-                                sred_add<2 * WORD>(ad[j][k], hi_plus_carry(o1[j][k], lo1[j], hi1[j]));
-                                sred_add<4 * WORD>(ad[j][k], hi_plus_carry(o2[j][k], lo2[j], hi2[j]));
-                            } else {
-                                sred_add<WORD>(ad[j][k], hi_plus_carry(o0[j][k], lo0[j], hi0[j]));
-                                sred_add<3 * WORD>(ad[j][k], hi_plus_carry(o1[j][k], lo1[j], hi1[j]));
-                                sred_add<5 * WORD>(ad[j][k], hi_plus_carry(o2[j][k], lo2[j], hi2[j]));
-                            }
-                        } else if (!CNT_INT) {
-                            sred_add<WORD>(ad[j][k], hi_plus_carry(o0[j][k], lo0[j], hi0[j]));
-                        }
-                    }
-                }
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&st[s].empty);
-#pragma unroll
-            for (int j = 0; j < RPW; ++j) bw_cur[j] = bw_next[j];
-        }
+        const uint32_t hb = smem_u32(hist);
+#define SB_CONSUME(K) rows_consume<KIND, CNT_INT, FPL, ALLF, K>(a, ops_s, st, fm_tab, hb, cw, lane, tile_id, gcount, begin, end, n_iters, nw)
+        if (kact >= FPL) SB_CONSUME(FPL);
+        else if constexpr (FPL == 4) {
+            if (kact == 3) SB_CONSUME(3);
+            else if (kact == 2) SB_CONSUME(2);
+            else SB_CONSUME(1);
+        } else if constexpr (FPL == 2) SB_CONSUME(1);
+#undef SB_CONSUME
     }
     __syncthreads();
     flush_hist<KIND, CNT_INT, 32 * FPL>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0,
