@@ -503,12 +503,12 @@ __device__ __forceinline__ void rows_consume(const HistRowsArgs& a, const RowOps
             uint32_t lo0[BATCH], lo1[BATCH], lo2[BATCH], hi0[BATCH], hi1[BATCH], hi2[BATCH];
 #pragma unroll
             for (int j = 0; j < BATCH; ++j) {  // phase 1: operands, addresses, low-word atomics
-                const uint4 v0 = *reinterpret_cast<const uint4*>(&v[jb + j]);       // row, slot, q0, q1
-                const uint4 v1 = *reinterpret_cast<const uint4*>(&v[jb + j].q[2]);  // q2..q5
-                const uint32_t slot = v0.y;
+                const uint4 v0 = *reinterpret_cast<const uint4*>(&v[jb + j]);       // row, cnt_hi, slot, cnt_lo
+                const uint4 v1 = *reinterpret_cast<const uint4*>(&v[jb + j].q[0]);  // sum / sq words
+                const uint32_t slot = v0.z;
                 const bool rowok = (wr0 + jb + j < rows) && slot < (uint32_t)gcount;
                 uint32_t base = lane_base + slot * slot_stride;
-                lo0[j] = v0.z; hi0[j] = v0.w;
+                lo0[j] = v0.w; hi0[j] = v0.y;
                 lo1[j] = hi1[j] = lo2[j] = hi2[j] = 0;
                 if (KIND == STAT_VARIANCE) { lo1[j] = v1.x; hi1[j] = v1.y; lo2[j] = v1.z; hi2[j] = v1.w; }
                 else base += v1.x * FPL;  // class words
@@ -766,13 +766,13 @@ __global__ void __launch_bounds__(W_NTHREADS, 1) hist_rows_wide_kernel(const His
                 for (int hs = 0; hs < 2; ++hs) {
                     const int r = min(wr0 + hs * 4 + q, R_TILE - 1);
                     const RowOps* v = ops_s + s * R_TILE + r;
-                    const uint4 v0 = *reinterpret_cast<const uint4*>(v);          // row, slot, q0, q1
-                    const uint4 v1 = *reinterpret_cast<const uint4*>(&v->q[2]);   // q2..q5
-                    const uint32_t slot = v0.y;
+                    const uint4 v0 = *reinterpret_cast<const uint4*>(v);          // row, cnt_hi, slot, cnt_lo
+                    const uint4 v1 = *reinterpret_cast<const uint4*>(&v->q[0]);   // sum / sq words
+                    const uint32_t slot = v0.z;
                     const bool ok = (wr0 + hs * 4 + q < rows) && slot < (uint32_t)gcount && feat_ok &&
                                     (fm_tab[slot & (R_MAX_GS - 1)] & feat_bit) != 0u && bw_cur[hs] < (uint32_t)bins_pad;
                     uint32_t base = lane_base + slot * slot_stride + bw_cur[hs] * bin_stride;
-                    lo0[hs] = v0.z; hi0[hs] = v0.w;
+                    lo0[hs] = v0.w; hi0[hs] = v0.y;
                     lo1[hs] = hi1[hs] = lo2[hs] = hi2[hs] = 0;
                     if (KIND == STAT_VARIANCE) { lo1[hs] = v1.x; hi1[hs] = v1.y; lo2[hs] = v1.z; hi2[hs] = v1.w; }
                     else base += v1.x / 4u;  // class byte offset was computed for 128-byte words; here words are 32 bytes

@@ -34,9 +34,13 @@ struct HistArgs {
 
 // ---- row-list path (rowlist.cu + hist_rows_kernel in hist.cu): passes with more todo nodes than one slot group
 struct __align__(16) RowOps {   // one active row of the pass, in slot-group order
+    // (slot, cnt_lo) share an aligned 8-byte word: with integer counts a consumer needs those two and q[0..3],
+    // one 64-bit and one 128-bit broadcast load per row
     uint32_t row;               // row index (ascending inside a group)
+    uint32_t cnt_hi;
     uint32_t slot;              // slot inside its group, 0..gs-1
-    uint32_t q[6];              // VARIANCE: (cnt_lo, cnt_hi, sum_lo, sum_hi, sq_lo, sq_hi); CLASS: (lo, hi, class byte offset, -, -, -)
+    uint32_t cnt_lo;
+    uint32_t q[4];              // VARIANCE: (sum_lo, sum_hi, sq_lo, sq_hi); CLASS: (class byte offset, -, -, -)
 };
 struct RowListArgs {
     int64_t n;

@@ -121,7 +121,9 @@ __global__ void rowlist_ops_kernel(const uint32_t* __restrict__ sorted_rows, con
             skip.row = r;
             skip.slot = 0xffffffffu;
 #pragma unroll
-            for (int k = 0; k < 6; ++k) skip.q[k] = 0;
+            skip.cnt_lo = skip.cnt_hi = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) skip.q[k] = 0;
             ops[i] = skip;
             continue;
         }
@@ -134,19 +136,19 @@ __global__ void rowlist_ops_kernel(const uint32_t* __restrict__ sorted_rows, con
         long long qc;
         if (CNT_INT) qc = (long long)__float2int_rn(cw);
         else qc = __float2ll_rn(__fmul_rn(cw, sc0));
-        o.q[0] = (uint32_t)qc; o.q[1] = (uint32_t)(qc >> 32);
+        o.cnt_lo = (uint32_t)qc; o.cnt_hi = (uint32_t)(qc >> 32);
         if (KIND == STAT_VARIANCE) {
             const float sw = __fmul_rn(__fmul_rn(y, sig), w);
             const float qw = __fmul_rn(__fmul_rn(__fmul_rn(y, y), sig), w);
             const long long qs = __float2ll_rn(__fmul_rn(sw, sc1));
             const long long qq = __float2ll_rn(__fmul_rn(qw, sc2));
-            o.q[2] = (uint32_t)qs; o.q[3] = (uint32_t)(qs >> 32);
-            o.q[4] = (uint32_t)qq; o.q[5] = (uint32_t)(qq >> 32);
+            o.q[0] = (uint32_t)qs; o.q[1] = (uint32_t)(qs >> 32);
+            o.q[2] = (uint32_t)qq; o.q[3] = (uint32_t)(qq >> 32);
         } else {
             const int cls = (int)(__fadd_rn(y, 0.000001f));
-            if (cls < 0 || cls >= stats_size) { atomicOr(error_flag, 1u); o.slot = 0xffffffffu; o.q[2] = 0; }
-            else o.q[2] = (uint32_t)(cls * (CNT_INT ? 128 : 256));  // byte offset of the class words
-            o.q[3] = o.q[4] = o.q[5] = 0;
+            if (cls < 0 || cls >= stats_size) { atomicOr(error_flag, 1u); o.slot = 0xffffffffu; o.q[0] = 0; }
+            else o.q[0] = (uint32_t)(cls * (CNT_INT ? 128 : 256));  // byte offset of the class words
+            o.q[1] = o.q[2] = o.q[3] = 0;
         }
         ops[i] = o;
     }
