@@ -59,6 +59,8 @@ enum { SB_SPLIT_CONTINUOUS = 1, SB_SPLIT_CATEGORICAL = 2 };
 #define SB_FLAG_DETERMINISTIC 1u /* reserved: the histogram path is order-independent by construction */
 #define SB_FLAG_NO_SUBTRACTION 4u /* accumulate every todo node directly instead of deriving the larger child of a
                                      sibling pair as parent - smaller child (same numbers either way) */
+#define SB_FLAG_NO_ROOT_COUNT_CACHE 8u /* accumulate the bin counts of a tree root every time instead of reusing those of the
+                                          previous root pass while the sample weights are unchanged */
 #define SB_FLAG_NO_ROW_LISTS 2u  /* never build per-pass row lists / the row-major bin copy: passes with more todo
                                     nodes than one shared-memory slot group then stream the column tiles once per group
                                     (slower, but needs no extra memory) */

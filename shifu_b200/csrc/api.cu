@@ -55,6 +55,8 @@ struct HistLaunch {
     size_t wide_smem = 0;
     RowListArgs list{};
     HistRowsArgs rows{};
+    int root_counts = 0;   // 1: save the bin counts of this root pass after the kernel; 2: the kernel skips them, restore
+    int64_t root_bins = 0;
 };
 
 }  // namespace sb
@@ -134,6 +136,13 @@ struct sb_handle {
     bool acc_valid = false;     // d_acc holds the error sums of the current Data.predict (GBT, inside a tree)
     bool acc_fresh = false, scales_fresh = false;  // recomputed by the last sb_compute_begin (=> need an all-reduce)
     bool scales_valid = false;  // d_maxbits holds the maxima of the current tree's contributions
+    // Bin counts of a tree root: they depend on the bins and the sample weights only, so consecutive trees share them.
+    DevBuf<int64_t> root_cnt;
+    bool root_cnt_valid = false, enable_root_cache = true;
+    uint64_t weights_version = 0, root_cnt_version = 0;
+    int root_cnt_wcol = -1;
+    int64_t root_cnt_total = 0;
+    std::vector<int> root_cnt_feats;
     bool cnt_int = false;  // every sig*weight product of the training rows is an integer in [0, 1024]
 
     int64_t launches_count = 0, h2d_bytes = 0, d2h_bytes = 0;
@@ -194,6 +203,7 @@ int refresh_cnt_int(sb_handle* h) {
     SB_CUDA(cudaMemcpyAsync(&flag, flag_dev, 4, cudaMemcpyDeviceToHost, h->stream));
     SB_CUDA(cudaStreamSynchronize(h->stream));
     h->cnt_int = (flag & 1u) == 0;
+    h->weights_version += 1;  // every caller changed (or loaded) sample weights
     return SB_OK;
 }
 
@@ -740,6 +750,25 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 ra.n_slots = ns; ra.bins_pad = bins_pad; ra.n_features = F; ra.stats_size = h->stats_size;
                 ra.cnt_shift = h->d_cnt_shift; ra.raw_lo = h->raw.p; ra.raw_hi = h->raw.p + lay.total;
                 L.has_narrow = fpl > 0 && n_rt > 0;
+                // a pass that is one tree root over every feature: its bin counts repeat from tree to tree
+                if (h->enable_root_cache && la.identity && S == 1 && cnt_int == 1 && h->stat_kind == STAT_VARIANCE && allf &&
+                    !any_wide && L.has_narrow) {
+                    const int wcol = tree_id % W;
+                    const auto& feats = lay.nodes[order[s0]].features;
+                    L.root_bins = lay.total / h->stats_size;
+                    if (h->root_cnt_valid && h->root_cnt_version == h->weights_version && h->root_cnt_wcol == wcol &&
+                        h->root_cnt_total == lay.total && h->root_cnt_feats == feats) {
+                        L.root_counts = 2;
+                    } else {
+                        SB_CUDA(h->root_cnt.reserve((size_t)(2 * L.root_bins)));
+                        L.root_counts = 1;
+                        h->root_cnt_valid = true;
+                        h->root_cnt_version = h->weights_version;
+                        h->root_cnt_wcol = wcol;
+                        h->root_cnt_total = lay.total;
+                        h->root_cnt_feats = feats;
+                    }
+                }
                 L.grid = max_chunks * std::max(n_rt, 1);
                 L.smem = L.has_narrow ? hist_rows_smem_bytes(rgs, bins_pad, nw, fpl) : 0;
                 if (any_wide) {
@@ -874,7 +903,12 @@ int run_histograms(sb_handle* h) {
             SB_CUDA(launch_rowlist_build(L.list, h->stream));
             h->launches_count += 5;  // keys, radix sort (2 kernels), chunk table, operands
             if (L.has_narrow) {
-                SB_CUDA(hist_rows_launch(L.kind, L.cnt_int, L.fpl, L.allf, L.rows, L.grid, L.smem, h->stream));
+                SB_CUDA(hist_rows_launch(L.kind, L.root_counts == 2 ? 2 : L.cnt_int, L.fpl, L.allf, L.rows, L.grid, L.smem, h->stream));
+                h->launches_count += 1;
+            }
+            if (L.root_counts) {
+                SB_CUDA(launch_counts_cache(L.rows.raw_lo, L.rows.raw_hi, h->root_cnt.p, L.root_bins, h->stats_size,
+                                            L.root_counts == 1, h->stream));
                 h->launches_count += 1;
             }
             if (L.has_wide) {
@@ -935,6 +969,7 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
     h->cfg.n_bins = nullptr; h->cfg.is_categorical = nullptr; h->cfg.column_num = nullptr; h->cfg.bin_boundary = nullptr;
     h->enable_row_lists = (cfg->flags & SB_FLAG_NO_ROW_LISTS) == 0;
     h->enable_subtraction = (cfg->flags & SB_FLAG_NO_SUBTRACTION) == 0;
+    h->enable_root_cache = (cfg->flags & SB_FLAG_NO_ROOT_COUNT_CACHE) == 0;
     h->stats_size = is_variance(cfg->impurity) ? 3 : cfg->num_classes;
     h->stat_kind = is_variance(cfg->impurity) ? STAT_VARIANCE : STAT_CLASS;
     SB_CUDA(cudaMalloc(&h->d_feat_bins, sizeof(int32_t) * cfg->n_features));
@@ -960,7 +995,7 @@ SB_API void sb_destroy(sb_handle* h) {
     free_rowset(h->train);
     free_rowset(h->valid);
     for (auto& kv : h->trees) free_tree(kv.second);
-    h->raw.release(); h->raw_prev.release(); h->d_pairs.release(); h->d_small_is_b.release(); h->stats.release(); h->tile_feats.release(); h->twin_map.release(); h->slot_fmask.release(); h->pair_off.release();
+    h->raw.release(); h->raw_prev.release(); h->d_pairs.release(); h->d_small_is_b.release(); h->stats.release(); h->tile_feats.release(); h->twin_map.release(); h->root_cnt.release(); h->slot_fmask.release(); h->pair_off.release();
     h->slot_of_node.release(); h->tasks.release(); h->task_node_off.release(); h->node_task_begin.release(); h->cand.release(); h->gain_out.release();
     h->cand_bits.release(); h->out_bits.release(); h->new_dropout.release(); h->new_weights.release();
     h->sort_keys.release(); h->sort_idx.release(); h->sort_tmp.release(); h->sort_flags.release();

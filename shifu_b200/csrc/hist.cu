@@ -527,7 +527,7 @@ __device__ __forceinline__ void rows_consume(const HistRowsArgs& a, const RowOps
                     ad[j][k] = adr;
                     if (KIND == STAT_VARIANCE) {
                         if (CNT_INT) {
-                            sred_add<KO>(adr, lo0[j]);
+                            if (CNT_INT != 2) sred_add<KO>(adr, lo0[j]);  // 2: the counts of this pass are known already
                             o1[j][k] = satom_add<KO + WORD>(adr, lo1[j]);
                             o2[j][k] = satom_add<KO + 3 * WORD>(adr, lo2[j]);
                         } else {
@@ -668,6 +668,12 @@ static cudaError_t launch_rows_kc(int fpl, int allf, const HistRowsArgs& a, int 
 
 cudaError_t hist_rows_launch(int kind, int cnt_int, int fpl, int allf, const HistRowsArgs& a, int grid, size_t smem,
                              cudaStream_t stream) {
+    if (kind == STAT_VARIANCE && cnt_int == 2) {  // integer counts that are not accumulated (cached root counts)
+        if (!allf) return cudaErrorInvalidValue;
+        if (fpl == 4) return launch_rows_one<STAT_VARIANCE, 2, 4, 1>(a, grid, smem, stream);
+        if (fpl == 2) return launch_rows_one<STAT_VARIANCE, 2, 2, 1>(a, grid, smem, stream);
+        return launch_rows_one<STAT_VARIANCE, 2, 1, 1>(a, grid, smem, stream);
+    }
     if (kind == STAT_VARIANCE)
         return cnt_int ? launch_rows_kc<STAT_VARIANCE, 1>(fpl, allf, a, grid, smem, stream) : launch_rows_kc<STAT_VARIANCE, 0>(fpl, allf, a, grid, smem, stream);
     return cnt_int ? launch_rows_kc<STAT_CLASS, 1>(fpl, allf, a, grid, smem, stream) : launch_rows_kc<STAT_CLASS, 0>(fpl, allf, a, grid, smem, stream);

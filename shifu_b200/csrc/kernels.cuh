@@ -202,6 +202,8 @@ struct SplitTask {       // one (todo node, feature) pair
 };
 cudaError_t launch_expand_tasks(const SplitTask* tmpl, int fk, const int64_t* node_off, int n_nodes, SplitTask* tasks,
                                 int32_t* begin, cudaStream_t s);
+cudaError_t launch_counts_cache(int64_t* raw_lo, int64_t* raw_hi, int64_t* cache, int64_t n_bins_total, int stats_size, int save,
+                                cudaStream_t s);
 struct SplitScratch {    // categorical features only: per task, max_bins entries each
     double* keys = nullptr;
     int* idx = nullptr;

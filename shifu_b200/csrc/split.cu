@@ -454,6 +454,22 @@ cudaError_t launch_expand_tasks(const SplitTask* tmpl, int fk, const int64_t* no
     return cudaGetLastError();
 }
 
+// Count statistic (stat 0) of every bin of a raw block, saved to / restored from a cache of (lo, hi) pairs.
+__global__ void counts_cache_kernel(int64_t* __restrict__ raw_lo, int64_t* __restrict__ raw_hi, int64_t* __restrict__ cache,
+                                    int64_t n_bins_total, int stats_size, int save) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n_bins_total) return;
+    const int64_t idx = i * stats_size;
+    if (save) { cache[2 * i] = raw_lo[idx]; cache[2 * i + 1] = raw_hi[idx]; }
+    else { raw_lo[idx] = cache[2 * i]; raw_hi[idx] = cache[2 * i + 1]; }
+}
+cudaError_t launch_counts_cache(int64_t* raw_lo, int64_t* raw_hi, int64_t* cache, int64_t n_bins_total, int stats_size, int save,
+                                cudaStream_t s) {
+    if (n_bins_total <= 0) return cudaSuccess;
+    counts_cache_kernel<<<(unsigned)((n_bins_total + 255) / 256), 256, 0, s>>>(raw_lo, raw_hi, cache, n_bins_total, stats_size, save);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_pair_decide(const PairDesc* pairs, int n_pairs, const int64_t* prev_lo, const int64_t* prev_hi,
                                int stats_size, int kind, int n_features, int16_t* slot_tables, int64_t* pair_off,
                                int32_t* small_is_b, cudaStream_t s) {

@@ -160,6 +160,15 @@ def test_gbt_variance_unweighted_counts_bit_exact():
     assert run_gbt(20000, [64] * 40, seed=11, n_trees=2, max_depth=5) >= 8
 
 
+def test_root_count_cache_matches_direct_accumulation():
+    # trees 2 and 3 take the root's bin counts from the first root pass (weights unchanged); flag 8 accumulates them
+    # every time.  Both are checked against the oracle pass by pass (counts bit-exact).
+    assert run_gbt(20000, [64] * 40, seed=13, n_trees=3, max_depth=3) >= 6
+    assert run_gbt(20000, [64] * 40, seed=13, n_trees=3, max_depth=3, flags=8) >= 6
+    # redrawn bags invalidate the cache
+    run_gbt(20000, [64] * 40, seed=14, n_trees=3, max_depth=3, bagging=True)
+
+
 def test_gbt_deep_levels_row_lists_and_tile_groups():
     # depth 7: up to 32 todo nodes per pass -> several shared-memory slot groups.  Default: per-pass row lists over the
     # row-major bin copy; SB_FLAG_NO_ROW_LISTS: the column-tile kernel visits every tile once per group.
