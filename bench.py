@@ -32,7 +32,7 @@ SEED = 1002
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--rows", type=int, default=100_000_000)
@@ -68,7 +68,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -112,69 +112,28 @@ class DevView:
         self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
 
 
-_WRAPPED = {}
+def grow_tree(worker, master, it, e2e_buffers=None):
+    """One GBT tree through the device path; returns (next message, passes, last scalars).
 
-
-def _wrap(ptr, n, typestr):
-    """torch view of a library-owned device buffer (cached: the buffers only move when they grow)."""
-    import torch
-    key = (ptr, n, typestr)
-    t = _WRAPPED.get(key)
-    if t is None:
-        if len(_WRAPPED) > 64:
-            _WRAPPED.clear()
-        t = _WRAPPED[key] = torch.as_tensor(DevView(ptr, n, typestr), device="cuda")
-    return t
-
-
-def grow_tree(worker, master, it, dist_ctx, e2e_buffers=None):
-    """One GBT tree through the device path; returns (next message, passes, last scalars)."""
+    Device-resident measurement: the native iteration loop (sbh_grow_tree).  End-to-end measurement: the call a
+    user of the reference makes, DTWorker.doCompute with HOST buffers (message in, statistics out: sb_compute), then
+    sb_best_splits and the master step.  With several GPUs the merge is the library's own NCCL all-reduce in both."""
     from shifu_b200 import capi
+    if e2e_buffers is None:
+        return master.grow_tree(worker, it)
     passes = 0
     tree_index = master.n_trees
     scalars = None
     while it is not None:
-        gains = None
-        if e2e_buffers is None and dist_ctx is None:
-            worker.compute_begin(it)
-            worker.compute_stats()
-            scalars, gains, bits = worker.compute_finish_split(it.n_todo)
-        elif dist_ctx is None:
-            # the call a user makes: DTWorker.doCompute with host buffers (message in, statistics out)
-            n = worker.stats_len(it)
-            out = capi.SbIterOut()
-            out.stats = C.cast(e2e_buffers["stats_ptr"], C.POINTER(C.c_double))
-            out.stats_len = e2e_buffers["stats_cap"]
-            assert n <= e2e_buffers["stats_cap"]
-            capi.check(worker.lib, worker.lib.sb_compute(worker.h, C.byref(it.struct), C.byref(out)))
-            e2e_buffers["d2h"] += n * 8 + 32
-            scalars = (out.train_count, out.validation_count, out.train_error, out.validation_error)
-        else:
-            import torch.distributed as dist
-            from shifu_b200.sharding import reduce_pass
-            worker.compute_begin(it)
-            scales_fresh, acc_fresh = worker.pass_info()
-            if scales_fresh:
-                sp, sb = worker.device_buffer("scale")
-                reduce_pass(dist, _wrap(sp, 3, "<i4"), None, None, True, False)
-            worker.compute_stats()
-            rp, rb = worker.device_buffer("raw")
-            # the DTMaster merge: one integer all-reduce per pass (+ the 4 scalars when they were recomputed)
-            acc = None
-            if acc_fresh:
-                ap_, ab = worker.device_buffer("acc")
-                acc = _wrap(ap_, 4, "<f8")
-            reduce_pass(dist, None, _wrap(rp, rb // 8, "<i8") if rb > 0 else None, acc, False, acc_fresh)
-            out = None
-            if e2e_buffers is not None:
-                n = worker.stats_len(it)
-                out = capi.SbIterOut()
-                out.stats = C.cast(e2e_buffers["stats_ptr"], C.POINTER(C.c_double))
-                out.stats_len = e2e_buffers["stats_cap"]
-                e2e_buffers["d2h"] += n * 8 + 32
-            scalars, gains, bits = worker.compute_finish_split(it.n_todo, out=out)
-        if gains is None:
-            gains, bits = worker.best_splits(it.n_todo)
+        n = worker.stats_len(it)
+        out = capi.SbIterOut()
+        out.stats = C.cast(e2e_buffers["stats_ptr"], C.POINTER(C.c_double))
+        out.stats_len = e2e_buffers["stats_cap"]
+        assert n <= e2e_buffers["stats_cap"]
+        capi.check(worker.lib, worker.lib.sb_compute(worker.h, C.byref(it.struct), C.byref(out)))
+        e2e_buffers["d2h"] += n * 8 + 32
+        scalars = (out.train_count, out.validation_count, out.train_error, out.validation_error)
+        gains, bits = worker.best_splits(it.n_todo)
         passes += 1
         it = master.do_compute(gains, bits)
         if it is None or master.n_trees != tree_index:
@@ -204,6 +163,12 @@ def run_b200(a):
                        min_instances_per_node=5, device=local_rank)
     worker = Worker(cfg)
     worker.load_synthetic(rows_local, seed=SEED, row0=row0, label_kind=0)
+    if dist_ctx is not None:
+        # the library's own communicator (sb_dist_init): torch.distributed only carries the 128-byte id and the barriers
+        from shifu_b200.capi import dist_unique_id
+        ids = [dist_unique_id() if rank == 0 else None]
+        dist_ctx.broadcast_object_list(ids, src=0)
+        worker.dist_init(ids[0], rank, world)
     master = NativeMaster(cfg, tree_num=n_trees_total, max_depth=a.depth, learning_rate=0.05, worker_number=world)
     it = master.build_initial_master_params()
 
@@ -215,7 +180,7 @@ def run_b200(a):
 
     # ---- warm-up trees
     for _ in range(a.warmup):
-        it, _, _ = grow_tree(worker, master, it, dist_ctx)
+        it, _, _ = grow_tree(worker, master, it)
     worker.hist_time()
     worker.set_profiling(True)
     l0, h2d0, d2h0 = worker.counters()
@@ -229,7 +194,7 @@ def run_b200(a):
     e0.record()
     passes = 0
     for _ in range(a.steps):
-        it, p, scalars = grow_tree(worker, master, it, dist_ctx)
+        it, p, scalars = grow_tree(worker, master, it)
         passes += p
     e1.record()
     barrier()
@@ -249,7 +214,7 @@ def run_b200(a):
     f0.record()
     e2e_passes = 0
     for _ in range(a.steps):
-        it, p, _ = grow_tree(worker, master, it, dist_ctx, e2e_buffers=e2e_buf)
+        it, p, _ = grow_tree(worker, master, it, e2e_buffers=e2e_buf)
         e2e_passes += p
     f1.record()
     barrier()

@@ -278,6 +278,19 @@ SB_API int sb_compute_finish(sb_handle* h, sb_iter_out* out);
 SB_API int sb_set_stream(sb_handle* h, void* cuda_stream);
 
 /*
+ * One process per GPU, rows sharded over the processes: the merge of the workers' statistics that Guagua hands to
+ * DTMaster.doCompute (dt/DTMaster.java:316-331 sums the NodeStats of every worker; :342-352 the error sums)
+ * becomes an NCCL all-reduce inside sb_compute / sb_compute_stats (integer sum of the accumulators, MAX of the
+ * fixed-point scales at a tree switch, sum of the four error scalars).  Rank 0 calls sb_dist_unique_id and hands
+ * the 128 bytes to every process (any side channel); each process then calls sb_dist_init once on its handle.
+ * Afterwards every rank's sb_compute returns the merged statistics and sb_best_splits the same splits.
+ * NCCL is opened with dlopen("libnccl.so.2") at the first call; single-GPU use needs no NCCL.
+ * No counterpart call in the reference: there the merge is the Guagua master's message loop.
+ */
+SB_API int sb_dist_unique_id(uint8_t* id128);
+SB_API int sb_dist_init(sb_handle* h, const uint8_t* id128, int32_t rank, int32_t world_size);
+
+/*
  * Replaces the per-node body of DTMaster.doCompute (dt/DTMaster.java:316-340): for every todo node of the
  * last sb_compute*, Impurity.computeImpurity per feature (dt/Impurity.java:120-211,269-360,378-477,563-661)
  * and GainInfo.getGainInfoByMaxGain across features (dt/GainInfo.java:200-214), on the device, from the
@@ -323,6 +336,13 @@ SB_API const sb_iter_in* sbh_master_initial(sbh_master* m);
 /* DTMaster.doCompute (dt/DTMaster.java:316-537) fed with the sb_gain records of sb_best_splits for the todo nodes of
    the previous message (same order).  Returns the next message, or NULL when training halts (:396-407, :431-435). */
 SB_API const sb_iter_in* sbh_master_do_compute(sbh_master* m, const sb_gain* gains, const uint8_t* cat_bits);
+/* The iteration loop of one tree in native code: starting from message `first`, run sb_compute_begin /
+   sb_compute_stats / sb_compute_finish_split on `worker` and feed sbh_master_do_compute until the master switches to
+   the next tree (or halts).  *next: the first message of the next tree (NULL when training halted); *n_passes: worker
+   iterations run; *last: the scalars of the last iteration.  What the Guagua iteration loop does between
+   DTWorker.doCompute and DTMaster.doCompute (guagua MasterComputable / WorkerComputable contract). */
+SB_API int sbh_grow_tree(sbh_master* m, sb_handle* worker, const sb_iter_in* first, const sb_iter_in** next,
+                         int32_t* n_passes, sb_iter_out* last);
 SB_API int sbh_master_tree_count(sbh_master* m);
 SB_API int sbh_master_halted(sbh_master* m);
 /* Copies tree `index` out: sb_node records in pre-order + mask pool, and per node 7 doubles

@@ -155,6 +155,7 @@ EXPORTS = [
     "sb_acc_buffer", "sb_compute_finish", "sb_compute_finish_split", "sb_set_stream", "sb_best_splits", "sb_time_stats_pass", "sb_counters",
     "sb_load_synthetic", "sb_read_bins", "sb_read_labels", "sb_set_profiling", "sb_hist_time",
     "sb_error_sums_static", "sb_pass_info", "sb_set_weights", "sb_sample_weights", "sb_bin_values",
+    "sb_dist_unique_id", "sb_dist_init", "sbh_grow_tree",
     "sbh_master_create", "sbh_master_destroy", "sbh_master_initial", "sbh_master_do_compute", "sbh_master_tree_count",
     "sbh_master_halted", "sbh_master_export_tree",
 ]
@@ -211,6 +212,10 @@ def load_library(path=None):
     lib.sbh_master_initial.argtypes = [H]
     lib.sbh_master_initial.restype = C.POINTER(SbIterIn)
     lib.sbh_master_do_compute.argtypes = [H, C.POINTER(SbGain), C.c_void_p]
+    lib.sb_dist_unique_id.argtypes = [C.c_void_p]
+    lib.sb_dist_init.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32]
+    lib.sbh_grow_tree.argtypes = [H, H, C.POINTER(SbIterIn), C.POINTER(C.POINTER(SbIterIn)), C.POINTER(C.c_int32),
+                                  C.POINTER(SbIterOut)]
     lib.sbh_master_do_compute.restype = C.POINTER(SbIterIn)
     lib.sbh_master_tree_count.argtypes = [H]
     lib.sbh_master_halted.argtypes = [H]
@@ -392,6 +397,11 @@ class Worker:
         check(self.lib, self.lib.sb_compute_finish_split(self.h, C.byref(out), gains, None if bits is None else bits.ctypes.data))
         return (out.train_count, out.validation_count, out.train_error, out.validation_error), gains, bits
 
+    def dist_init(self, id128, rank, world_size):
+        """Join the library's own NCCL communicator (id128: the 128 bytes of dist_unique_id() made on rank 0)."""
+        buf = (C.c_uint8 * 128).from_buffer_copy(bytes(id128))
+        check(self.lib, self.lib.sb_dist_init(self.h, buf, rank, world_size))
+
     def device_buffer(self, which):
         """(ptr, bytes) of one of the "scale" / "raw" / "acc" buffers."""
         p, b = C.c_void_p(), C.c_int64()
@@ -435,6 +445,14 @@ class Worker:
 
     def set_stream(self, stream_ptr):
         check(self.lib, self.lib.sb_set_stream(self.h, C.c_void_p(stream_ptr)))
+
+
+def dist_unique_id():
+    """128 bytes for Worker.dist_init, to be made on one rank and handed to all."""
+    lib = load_library()
+    buf = (C.c_uint8 * 128)()
+    check(lib, lib.sb_dist_unique_id(buf))
+    return bytes(buf)
 
 
 class NativeMessage:
@@ -487,6 +505,15 @@ class NativeMaster:
             gains = (SbGain * max(len(gains), 1))(*gains)
         ptr = self.lib.sbh_master_do_compute(self.h, gains, None if cat_bits is None else cat_bits.ctypes.data)
         return NativeMessage(ptr) if ptr else None
+
+    def grow_tree(self, worker, message):
+        """The iteration loop of one tree in native code: (next message or None, passes, (4 scalars))."""
+        nxt = C.POINTER(SbIterIn)()
+        n = C.c_int32()
+        out = SbIterOut()
+        check(self.lib, self.lib.sbh_grow_tree(self.h, worker.h, C.byref(message.struct), C.byref(nxt), C.byref(n), C.byref(out)))
+        return (NativeMessage(nxt) if nxt else None, n.value,
+                (out.train_count, out.validation_count, out.train_error, out.validation_error))
 
     @property
     def n_trees(self):

@@ -1,6 +1,8 @@
 // api.cu -- the C ABI of include/shifu_b200.h: handle, data load, the DTWorker.doCompute replacement and the
 // on-device DTMaster best-split step.  Host logic only; kernels live in hist.cu / rows.cu / split.cu.
 #include <cuda.h>
+#include <dlfcn.h>
+#include <nccl.h>  // types and enums only: the library is opened at run time (sb_dist_init)
 
 #include <algorithm>
 #include <cmath>
@@ -112,6 +114,8 @@ struct sb_handle {
     int n_tasks = 0;
     bool has_cat_tasks = false;
     double* d_acc = nullptr;          // 4 doubles
+    ncclComm_t comm = nullptr;        // set by sb_dist_init: the pass merges itself over NCCL
+    int world = 1, rank = 0;
     void* pin = nullptr;              // pinned host block: PinnedOut, then the sb_gain records (+ category bits)
     size_t pin_bytes = 0;
     double* d_err_scratch = nullptr;  // ERR_SCRATCH_DOUBLES
@@ -897,6 +901,38 @@ int plan_split_tasks(sb_handle* h) {
     return SB_OK;
 }
 
+// ---- NCCL, opened at run time so that single-GPU users need no NCCL at all.  In a process that already holds a
+// libnccl.so.2 (PyTorch's), dlopen returns that copy.
+struct NcclApi {
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    bool ok = false;
+};
+NcclApi& nccl_api() {
+    static NcclApi api;
+    static bool tried = false;
+    if (tried) return api;
+    tried = true;
+    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) return api;
+    api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(dlsym(lib, "ncclGetUniqueId"));
+    api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(dlsym(lib, "ncclCommInitRank"));
+    api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(dlsym(lib, "ncclCommDestroy"));
+    api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(dlsym(lib, "ncclAllReduce"));
+    api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(dlsym(lib, "ncclGetErrorString"));
+    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllReduce && api.GetErrorString;
+    return api;
+}
+#define SB_NCCL(call)                                                                              \
+    do {                                                                                           \
+        ncclResult_t r_ = (call);                                                                  \
+        if (r_ != ncclSuccess) return fail(SB_ERR_CUDA, std::string("NCCL: ") + nccl_api().GetErrorString(r_)); \
+    } while (0)
+
 int run_histograms(sb_handle* h) {
     for (const HistLaunch& L : h->launches) {
         if (L.use_rows) {
@@ -1003,6 +1039,7 @@ SB_API void sb_destroy(sb_handle* h) {
     if (h->d_feat_bins) cudaFree(h->d_feat_bins);
     if (h->d_acc) cudaFree(h->d_acc);
     if (h->pin) cudaFreeHost(h->pin);
+    if (h->comm && nccl_api().ok) nccl_api().CommDestroy(h->comm);
     if (h->d_err_scratch) cudaFree(h->d_err_scratch);
     if (h->d_maxbits) cudaFree(h->d_maxbits);
     if (h->d_scales) cudaFree(h->d_scales);
@@ -1373,8 +1410,9 @@ SB_API int sb_scale_buffer(sb_handle* h, void** dev_ptr, int64_t* bytes) {
 
 SB_API int sb_pass_info(sb_handle* h, int32_t* scales_fresh, int32_t* acc_fresh) {
     if (!h) return fail(SB_ERR_INVALID, "null handle");
-    if (scales_fresh) *scales_fresh = h->scales_fresh ? 1 : 0;
-    if (acc_fresh) *acc_fresh = h->acc_fresh ? 1 : 0;
+    // after sb_dist_init the library merges by itself: nothing is left for the caller to reduce
+    if (scales_fresh) *scales_fresh = (h->scales_fresh && !h->comm) ? 1 : 0;
+    if (acc_fresh) *acc_fresh = (h->acc_fresh && !h->comm) ? 1 : 0;
     return SB_OK;
 }
 
@@ -1382,18 +1420,59 @@ SB_API int sb_compute_stats(sb_handle* h) {
     if (!h) return fail(SB_ERR_INVALID, "null argument");
     if (!h->begun) return fail(SB_ERR_STATE, "sb_compute_stats before sb_compute_begin");
     SB_CUDA(cudaSetDevice(h->cfg.device));
+    // one process per GPU: the maxima behind the fixed-point scales are non-negative floats, so their bit patterns
+    // order like unsigned integers
+    if (h->comm && h->scales_fresh)
+        SB_NCCL(nccl_api().AllReduce(h->d_maxbits, h->d_maxbits, 3, ncclUint32, ncclMax, h->comm, h->stream));
     SB_CUDA(launch_make_scales(h->d_maxbits, h->stat_kind, h->d_scales, h->d_inv_scales, h->d_cnt_shift, h->stream));
     h->launches_count += 1;
-    if (!h->profiling) return run_histograms(h);
-    cudaEvent_t e0, e1;
-    SB_CUDA(cudaEventCreate(&e0));
-    SB_CUDA(cudaEventCreate(&e1));
-    SB_CUDA(cudaEventRecord(e0, h->stream));
-    int rc = run_histograms(h);
-    SB_CUDA(cudaEventRecord(e1, h->stream));
-    h->prof_events.push_back({e0, e1});
-    h->prof_launches.push_back((int)h->launches.size());
-    return rc;
+    int rc;
+    if (!h->profiling) rc = run_histograms(h);
+    else {
+        cudaEvent_t e0, e1;
+        SB_CUDA(cudaEventCreate(&e0));
+        SB_CUDA(cudaEventCreate(&e1));
+        SB_CUDA(cudaEventRecord(e0, h->stream));
+        rc = run_histograms(h);
+        SB_CUDA(cudaEventRecord(e1, h->stream));
+        h->prof_events.push_back({e0, e1});
+        h->prof_launches.push_back((int)h->launches.size());
+    }
+    if (rc != SB_OK) return rc;
+    if (h->comm) {
+        // the DTMaster merge (dt/DTMaster.java:316-331 adds the workers' statistics node by node): one integer sum
+        // over all GPUs, exact and order-independent; plus the four error scalars when this pass recomputed them
+        if (h->layout.total > 0)
+            SB_NCCL(nccl_api().AllReduce(h->raw.p, h->raw.p, (size_t)(2 * h->layout.total), ncclInt64, ncclSum, h->comm, h->stream));
+        if (h->acc_fresh) SB_NCCL(nccl_api().AllReduce(h->d_acc, h->d_acc, 4, ncclFloat64, ncclSum, h->comm, h->stream));
+    }
+    return SB_OK;
+}
+
+SB_API int sb_dist_unique_id(uint8_t* id128) {
+    if (!id128) return fail(SB_ERR_INVALID, "null argument");
+    NcclApi& api = nccl_api();
+    if (!api.ok) return fail(SB_ERR_UNSUPPORTED, "libnccl.so.2 not found");
+    ncclUniqueId id;
+    SB_NCCL(api.GetUniqueId(&id));
+    static_assert(sizeof(id) == 128, "ncclUniqueId is 128 bytes");
+    memcpy(id128, &id, 128);
+    return SB_OK;
+}
+
+SB_API int sb_dist_init(sb_handle* h, const uint8_t* id128, int32_t rank, int32_t world_size) {
+    if (!h || !id128) return fail(SB_ERR_INVALID, "null argument");
+    if (world_size < 1 || rank < 0 || rank >= world_size) return fail(SB_ERR_INVALID, "rank / world_size out of range");
+    if (h->comm) return fail(SB_ERR_STATE, "sb_dist_init was already called on this handle");
+    NcclApi& api = nccl_api();
+    if (!api.ok) return fail(SB_ERR_UNSUPPORTED, "libnccl.so.2 not found");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    ncclUniqueId id;
+    memcpy(&id, id128, 128);
+    SB_NCCL(api.CommInitRank(&h->comm, world_size, id, rank));
+    h->world = world_size;
+    h->rank = rank;
+    return SB_OK;
 }
 
 SB_API int sb_set_profiling(sb_handle* h, int32_t on) {

@@ -394,6 +394,36 @@ SB_API const sb_iter_in* sbh_master_initial(sbh_master* m) { return m ? m->build
 SB_API const sb_iter_in* sbh_master_do_compute(sbh_master* m, const sb_gain* gains, const uint8_t* cat_bits) {
     return (m && gains) ? m->do_compute(gains, cat_bits) : nullptr;
 }
+SB_API int sbh_grow_tree(sbh_master* m, sb_handle* worker, const sb_iter_in* first, const sb_iter_in** next,
+                         int32_t* n_passes, sb_iter_out* last) {
+    if (!m || !worker || !first || !next) return SB_ERR_INVALID;
+    const size_t tree0 = m->trees.size();
+    const sb_iter_in* it = first;
+    std::vector<sb_gain> gains;
+    std::vector<uint8_t> bits;
+    int passes = 0;
+    sb_iter_out out{};
+    while (it) {
+        int rc = sb_compute_begin(worker, it);
+        if (rc != SB_OK) return rc;
+        rc = sb_compute_stats(worker);
+        if (rc != SB_OK) return rc;
+        const size_t n = (size_t)std::max(it->n_todo, 1);
+        gains.resize(n);
+        bits.resize(n * SB_MAX_CAT_BYTES);
+        out = sb_iter_out{};
+        rc = sb_compute_finish_split(worker, &out, gains.data(), bits.data());
+        if (rc != SB_OK) return rc;
+        ++passes;
+        it = m->do_compute(gains.data(), bits.data());
+        if (m->trees.size() != tree0) break;
+    }
+    *next = it;
+    if (n_passes) *n_passes = passes;
+    if (last) *last = out;
+    return SB_OK;
+}
+
 SB_API int sbh_master_tree_count(sbh_master* m) { return m ? (int)m->trees.size() : 0; }
 SB_API int sbh_master_halted(sbh_master* m) { return m && m->halt ? 1 : 0; }
 

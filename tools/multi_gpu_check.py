@@ -53,4 +53,63 @@ while it is not None:
     n_iter += 1
 if rank == 0:
     print("multi-gpu check ok: %d iterations, %d trees, bit-identical to the single-GPU run" % (n_iter, len(m.trees)))
+
+# ---- the same through the library's own NCCL communicator (sb_dist_init) and the native tree loop (sbh_grow_tree)
+from shifu_b200.capi import NativeMaster, dist_unique_id  # noqa: E402
+
+ids = [dist_unique_id() if rank == 0 else None]
+dist.broadcast_object_list(ids, src=0)
+w2 = Worker(cfg)
+w2.load_synthetic(per, seed=5, row0=rank * per, weighted=True)
+w2.dist_init(ids[0], rank, world)
+full2 = None
+if rank == 0:
+    full2 = Worker(cfg)
+    full2.load_synthetic(per * world, seed=5, row0=0, weighted=True)
+m2 = DTMaster(cfg, tree_num=2, max_depth=5, worker_number=world)
+it = m2.build_initial_master_params()
+n_iter = 0
+while it is not None:
+    sc = w2.compute(it)  # begin + stats (+ all-reduce inside) + finish
+    gains, bits = w2.best_splits(it.n_todo)
+    if full2 is not None:
+        ref = full2.compute(it)
+        assert np.array_equal(ref[4], sc[4]), "in-library merge differs from the single-GPU run"
+        assert abs(ref[2] - sc[2]) <= 1e-9 * abs(ref[2]) + 1e-12 and ref[0] == sc[0]
+    it = m2.do_compute(gains, bits)
+    n_iter += 1
+w2.close()
+if full2 is not None:
+    full2.close()
+
+
+def grow_all(worker, n_workers):
+    nm = NativeMaster(cfg, tree_num=3, max_depth=5, worker_number=n_workers)
+    msg, total = nm.build_initial_master_params(), 0
+    while msg is not None:
+        msg, passes, _ = nm.grow_tree(worker, msg)
+        total += passes
+    out = []
+    for t in range(nm.n_trees):
+        nodes, pool, extras = nm.export_tree(t)
+        out.append((bytes(b"".join(bytes(x) for x in nodes)), pool.tobytes(), extras.tobytes()))
+    return out, total
+
+
+ids = [dist_unique_id() if rank == 0 else None]  # a communicator per handle
+dist.broadcast_object_list(ids, src=0)
+w3 = Worker(cfg)
+w3.load_synthetic(per, seed=5, row0=rank * per, weighted=True)
+w3.dist_init(ids[0], rank, world)
+trees_sharded, passes = grow_all(w3, world)
+w3.close()
+if rank == 0:
+    full3 = Worker(cfg)
+    full3.load_synthetic(per * world, seed=5, row0=0, weighted=True)
+    trees_full, passes_full = grow_all(full3, 1)
+    full3.close()
+    assert passes == passes_full and trees_sharded == trees_full, "native tree loop: sharded trees differ from the single-GPU trees"
+    print("in-library NCCL merge ok: %d iterations bit-identical; native tree loop: %d trees, %d passes, identical to single GPU"
+          % (n_iter, len(trees_full), passes))
+dist.barrier()
 dist.destroy_process_group()
