@@ -125,8 +125,7 @@ struct sb_handle {
     uint32_t* d_error_flag = nullptr;
     int* d_cnt_shift = nullptr;
     // row-list path buffers
-    DevBuf<uint8_t> rl_keys;      // [2n]
-    DevBuf<uint32_t> rl_vals;     // [2n]
+    DevBuf<uint32_t> rl_counts;   // [2][n_groups * n_ranges + 1]: counts, then their exclusive scan
     DevBuf<uint8_t> rl_temp;
     DevBuf<int64_t> rl_tables;    // offsets[257] + chunk_begin[max] + chunk_end[max]
     DevBuf<int32_t> rl_chunk_group;  // [max] + n_chunks scalar at the end
@@ -540,7 +539,10 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         }
         int max_pos = 0;
         for (int f = 0; f < F; ++f) max_pos = std::max(max_pos, pos_of[f]);
+        // Row pitch: DRAM is fetched in whole 128-byte lines, so a tile of a row must not straddle lines -- rows
+        // wider than one line are padded to a multiple of 128 bytes (a 224-byte pitch read 450 bytes per row).
         twin_pad = (max_pos / 32 + 1) * 32;
+        if (twin_pad > 128) twin_pad = (twin_pad + 127) / 128 * 128;
     }
     if (fpl > 0) {
         const int tw = 32 * fpl;
@@ -725,9 +727,9 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 const int target_chunks = (int)std::max<int64_t>(1, (148 * 2 + tiles_total - 1) / tiles_total);
                 const int64_t chunk_rows = MAX_ROWS_PER_FLUSH;  // upper bound; integer counts: 2^18 rows * 1024 < 2^32 as well
                 const int max_chunks = (int)(n / chunk_rows + target_chunks + rgroups + 2);
-                SB_CUDA(h->rl_keys.reserve((size_t)2 * n));
-                SB_CUDA(h->rl_vals.reserve((size_t)2 * n));
-                const size_t temp_bytes = rowlist_sort_temp_bytes(n);
+                const size_t scan_items = (size_t)rgroups * (size_t)rowlist_n_ranges(n) + 1;
+                SB_CUDA(h->rl_counts.reserve(2 * scan_items));
+                const size_t temp_bytes = rowlist_scan_temp_bytes((int64_t)scan_items);
                 SB_CUDA(h->rl_temp.reserve(temp_bytes + 16));
                 SB_CUDA(h->rl_tables.reserve((size_t)257 + 2 * (size_t)max_chunks));
                 SB_CUDA(h->rl_chunk_group.reserve((size_t)max_chunks + 1));
@@ -739,7 +741,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 la.n = n; la.node_id = a.node_id; la.output = a.output; la.significance = a.significance; la.weights = a.weights;
                 la.slot_of_node = a.slot_of_node; la.slot_table_size = a.slot_table_size; la.gs = rgs; la.n_groups = rgroups;
                 la.stats_size = h->stats_size; la.kind = h->stat_kind; la.cnt_int = cnt_int; la.scales = h->d_scales;
-                la.keys_in = h->rl_keys.p; la.keys_out = h->rl_keys.p + n; la.vals_in = h->rl_vals.p; la.vals_out = h->rl_vals.p + n;
+                la.counts = h->rl_counts.p; la.scanned = h->rl_counts.p + scan_items;
                 la.temp = h->rl_temp.p; la.temp_bytes = temp_bytes; la.chunk_rows = chunk_rows; la.target_chunks = target_chunks;
                 la.identity = (ns == 1 && lay.nodes[order[s0]].node_id == SB_ROOT_INDEX && partner[order[s0]] < 0) ? 1 : 0;
                 la.offsets = h->rl_tables.p; la.chunk_begin = h->rl_tables.p + 257; la.chunk_end = h->rl_tables.p + 257 + max_chunks;
@@ -937,7 +939,7 @@ int run_histograms(sb_handle* h) {
     for (const HistLaunch& L : h->launches) {
         if (L.use_rows) {
             SB_CUDA(launch_rowlist_build(L.list, h->stream));
-            h->launches_count += 5;  // keys, radix sort (2 kernels), chunk table, operands
+            h->launches_count += L.list.identity ? 2 : 5;  // count, scan (2 kernels), chunk table, scatter | chunk table, operands
             if (L.has_narrow) {
                 SB_CUDA(hist_rows_launch(L.kind, L.root_counts == 2 ? 2 : L.cnt_int, L.fpl, L.allf, L.rows, L.grid, L.smem, h->stream));
                 h->launches_count += 1;
@@ -1035,7 +1037,7 @@ SB_API void sb_destroy(sb_handle* h) {
     h->slot_of_node.release(); h->tasks.release(); h->task_node_off.release(); h->node_task_begin.release(); h->cand.release(); h->gain_out.release();
     h->cand_bits.release(); h->out_bits.release(); h->new_dropout.release(); h->new_weights.release();
     h->sort_keys.release(); h->sort_idx.release(); h->sort_tmp.release(); h->sort_flags.release();
-    h->rl_keys.release(); h->rl_vals.release(); h->rl_temp.release(); h->rl_tables.release(); h->rl_chunk_group.release(); h->rl_ops.release(); h->rt_tiles.release(); h->rt_fmask.release(); h->wt_tiles.release(); h->wt_fmask.release();
+    h->rl_counts.release(); h->rl_temp.release(); h->rl_tables.release(); h->rl_chunk_group.release(); h->rl_ops.release(); h->rt_tiles.release(); h->rt_fmask.release(); h->wt_tiles.release(); h->wt_fmask.release();
     if (h->d_feat_bins) cudaFree(h->d_feat_bins);
     if (h->d_acc) cudaFree(h->d_acc);
     if (h->pin) cudaFreeHost(h->pin);

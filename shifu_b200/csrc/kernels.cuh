@@ -51,8 +51,8 @@ struct RowListArgs {
     const int16_t* slot_of_node;
     int slot_table_size, gs, n_groups, stats_size, kind, cnt_int;
     const float* scales;
-    uint8_t *keys_in, *keys_out;
-    uint32_t *vals_in, *vals_out;
+    uint32_t* counts;          // [n_groups * n_ranges + 1] active rows per (group, range of 1024 rows), group-major
+    uint32_t* scanned;         // exclusive prefix sum of counts: first position of each (group, range)
     void* temp;
     size_t temp_bytes;
     int64_t chunk_rows;        // upper bound of rows per chunk (accumulator headroom)
@@ -73,7 +73,8 @@ cudaError_t launch_transpose_bins(const uint8_t* cm, int64_t pitch, int n_featur
 cudaError_t launch_transpose_bins16(const uint16_t* cm, int64_t pitch16, int n_wide, int64_t n, uint16_t* rm, int wpad,
                                     cudaStream_t s);
 
-size_t rowlist_sort_temp_bytes(int64_t n);
+int64_t rowlist_n_ranges(int64_t n);
+size_t rowlist_scan_temp_bytes(int64_t items);
 cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s);
 struct HistRowsArgs {
     const uint8_t* rm_bins;      // row-major bins [n][fpad]

@@ -1,12 +1,19 @@
 // rowlist.cu -- per-pass row lists for levels whose todo nodes do not fit one shared-memory slot group.
 //
 // When a pass has more todo nodes than one block can hold histograms for (GS slots), the column-major tile kernel
-// would have to stream every row tile once per slot group.  Instead the rows are grouped by slot group once per
-// pass (a one-digit radix sort of (group id, row index) -- row indices stay ascending inside a group), their
-// fixed-point operands are gathered into a compact array in that order, and hist_rows_kernel (hist.cu) walks each
-// group's list, reading the 32 bins of a row and feature tile from a ROW-major copy of the bin matrix with one
-// coalesced 32-byte load.  Every active row is then touched once per feature tile, whatever the number of groups.
-#include <cub/device/device_radix_sort.cuh>
+// would have to stream every row tile once per slot group.  Instead the ACTIVE rows of the pass are grouped by slot
+// group once per pass, their fixed-point operands written as a compact RowOps array in that order, and
+// hist_rows_kernel (hist.cu) walks each group's list, reading the bins of a row and feature tile from a ROW-major copy
+// of the bin matrix with one coalesced load.  Every active row is then touched once per feature tile, whatever the
+// number of groups.
+//
+// The grouping is a stable counting sort with very few keys (the slot groups), done in two streaming passes over the
+// rows and one prefix sum: (1) every warp counts, per group, the active rows of its own range of 1024 consecutive rows;
+// (2) an exclusive scan over the (group, range) counts, group-major, gives every warp the position of its first row
+// of every group; (3) every warp walks its range again and writes the RowOps of each active row to its position.
+// Rows stay in ascending order inside a group, inactive rows (no todo node, zero weight) are neither sorted nor
+// written, and no row index array or key array exists.
+#include <cub/device/device_scan.cuh>
 
 #include "common.cuh"
 #include "kernels.cuh"
@@ -46,35 +53,71 @@ __global__ void transpose_bins_kernel(const uint8_t* __restrict__ cm, int64_t pi
     }
 }
 
-__global__ void rowlist_keys_kernel(int64_t n, const int32_t* __restrict__ node_id, const float* __restrict__ weights,
-                                    const int16_t* __restrict__ slot_of_node, int slot_table_size, int gs,
-                                    uint8_t* __restrict__ keys, uint32_t* __restrict__ vals) {
-    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
-        const int nid = node_id[r];
-        int s = (nid >= 0 && nid < slot_table_size) ? (int)slot_of_node[nid] : -1;
-        const float w = weights ? weights[r] : 1.0f;
-        keys[r] = (s >= 0 && w != 0.0f) ? (uint8_t)(s / gs) : (uint8_t)255;
-        vals[r] = (uint32_t)r;
-    }
+constexpr int RL_RANGE = 1024;  // consecutive rows counted / scattered by one warp
+constexpr int RL_WARPS = 8;
+
+// group id of a row: its slot group, or 255 when the row takes no part in this pass; *slot_out = the slot
+__device__ __forceinline__ int row_group(int64_t r, int64_t n, const int32_t* __restrict__ node_id,
+                                         const float* __restrict__ weights, const int16_t* __restrict__ slot_of_node,
+                                         int slot_table_size, int gs, int* slot_out, float* w_out) {
+    *slot_out = -1;
+    *w_out = 0.0f;
+    if (r >= n) return 255;
+    const int nid = node_id[r];
+    const int s = (nid >= 0 && nid < slot_table_size) ? (int)slot_of_node[nid] : -1;
+    const float w = weights ? weights[r] : 1.0f;
+    *slot_out = s;
+    *w_out = w;
+    return (s >= 0 && w != 0.0f) ? s / gs : 255;
 }
 
-// offsets[g] = first position of key >= g in the sorted keys, g = 0..n_groups (offsets[n_groups] = number of active
-// rows); then the chunk table: chunk c covers ops [begin, end) of one group.
-__global__ void rowlist_chunks_kernel(const uint8_t* __restrict__ sorted_keys, int64_t n, int n_groups, int64_t max_chunk_rows,
-                                      int target_chunks, int64_t* __restrict__ offsets, int32_t* __restrict__ chunk_group,
-                                      int64_t* __restrict__ chunk_begin, int64_t* __restrict__ chunk_end,
-                                      int32_t* __restrict__ n_chunks, int max_chunks) {
+// counts[g * n_ranges + range] = active rows of group g in the range; one trailing zero so that the exclusive scan
+// also yields the total
+__global__ void __launch_bounds__(RL_WARPS * 32)
+rowlist_count_kernel(int64_t n, const int32_t* __restrict__ node_id, const float* __restrict__ weights,
+                     const int16_t* __restrict__ slot_of_node, int slot_table_size, int gs, int n_groups, int64_t n_ranges,
+                     uint32_t* __restrict__ counts) {
+    __shared__ uint32_t cnt[RL_WARPS][256];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t range = (int64_t)blockIdx.x * RL_WARPS + warp;
+    if (blockIdx.x == 0 && threadIdx.x == 0) counts[(int64_t)n_groups * n_ranges] = 0u;
+    if (range >= n_ranges) return;
+    for (int i = lane; i < 256; i += 32) cnt[warp][i] = 0u;
+    __syncwarp();
+    const int64_t r0 = range * RL_RANGE;
+    constexpr int U = 4;
+    for (int step = 0; step < RL_RANGE / 32; step += U) {
+        int key[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            int sl;
+            float w;
+            key[u] = row_group(r0 + (step + u) * 32 + lane, n, node_id, weights, slot_of_node, slot_table_size, gs, &sl, &w);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint32_t mask = __match_any_sync(0xffffffffu, key[u]);
+            if (key[u] != 255 && lane == __ffs(mask) - 1) cnt[warp][key[u]] += __popc(mask);
+            __syncwarp();
+        }
+    }
+    for (int g = lane; g < n_groups; g += 32) counts[(int64_t)g * n_ranges + range] = cnt[warp][g];
+}
+
+// offsets[g] = first position of group g (offsets[n_groups] = number of active rows), from the scanned counts or, for
+// the identity list (scanned == nullptr), a single group holding every row; then the chunk table: chunk c covers ops
+// [begin, end) of one group.
+__global__ void rowlist_chunks_kernel(const uint32_t* __restrict__ scanned, int64_t n_ranges, int64_t n, int n_groups,
+                                      int64_t max_chunk_rows, int target_chunks, int64_t* __restrict__ offsets,
+                                      int32_t* __restrict__ chunk_group, int64_t* __restrict__ chunk_begin,
+                                      int64_t* __restrict__ chunk_end, int32_t* __restrict__ n_chunks, int max_chunks) {
     __shared__ int64_t off[257];
     for (int g = threadIdx.x; g <= n_groups; g += blockDim.x) {
-        int64_t lo = 0, hi = n;
-        if (!sorted_keys) lo = hi = (g == 0 ? 0 : n);  // identity list: a single group holding every row
-        while (lo < hi) {
-            const int64_t mid = (lo + hi) >> 1;
-            if ((int)sorted_keys[mid] < g) lo = mid + 1;
-            else hi = mid;
-        }
-        off[g] = lo;
-        offsets[g] = lo;
+        int64_t v;
+        if (!scanned) v = (g == 0 ? 0 : n);  // identity list
+        else v = (int64_t)scanned[(int64_t)g * n_ranges];
+        off[g] = v;
+        offsets[g] = v;
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -96,61 +139,100 @@ __global__ void rowlist_chunks_kernel(const uint8_t* __restrict__ sorted_keys, i
     }
 }
 
-// ops[i] for the i-th row of the sorted order: {row index, local slot, fixed-point operands} (see RowOps in kernels.cuh)
+// RowOps of one active row (see kernels.cuh): slot inside its group and the fixed-point operands
 template <int KIND, int CNT_INT>
-__global__ void rowlist_ops_kernel(const uint32_t* __restrict__ sorted_rows, const int64_t* __restrict__ offsets, int n_groups,
-                                   const int32_t* __restrict__ node_id, const float* __restrict__ output,
+__device__ __forceinline__ RowOps make_row_ops(uint32_t r, int s, int gs, float w, float sig, float y, float sc0, float sc1,
+                                               float sc2, int stats_size, uint32_t* error_flag) {
+    RowOps o;
+    o.row = r;
+    o.slot = (uint32_t)(s % gs);
+    const float cw = __fmul_rn(sig, w);
+    long long qc;
+    if (CNT_INT) qc = (long long)__float2int_rn(cw);
+    else qc = __float2ll_rn(__fmul_rn(cw, sc0));
+    o.cnt_lo = (uint32_t)qc; o.cnt_hi = (uint32_t)(qc >> 32);
+    if (KIND == STAT_VARIANCE) {
+        const float sw = __fmul_rn(__fmul_rn(y, sig), w);
+        const float qw = __fmul_rn(__fmul_rn(__fmul_rn(y, y), sig), w);
+        const long long qs = __float2ll_rn(__fmul_rn(sw, sc1));
+        const long long qq = __float2ll_rn(__fmul_rn(qw, sc2));
+        o.q[0] = (uint32_t)qs; o.q[1] = (uint32_t)(qs >> 32);
+        o.q[2] = (uint32_t)qq; o.q[3] = (uint32_t)(qq >> 32);
+    } else {
+        const int cls = (int)(__fadd_rn(y, 0.000001f));
+        if (cls < 0 || cls >= stats_size) { atomicOr(error_flag, 1u); o.slot = 0xffffffffu; o.q[0] = 0; }
+        else o.q[0] = (uint32_t)(cls * (CNT_INT ? 128 : 256));  // byte offset of the class words
+        o.q[1] = o.q[2] = o.q[3] = 0;
+    }
+    return o;
+}
+
+// pass (3): every warp writes the RowOps of the active rows of its range at the scanned positions
+template <int KIND, int CNT_INT>
+__global__ void __launch_bounds__(RL_WARPS * 32)
+rowlist_scatter_kernel(int64_t n, const int32_t* __restrict__ node_id, const float* __restrict__ output,
+                       const float* __restrict__ significance, const float* __restrict__ weights,
+                       const int16_t* __restrict__ slot_of_node, int slot_table_size, int gs, int n_groups, int64_t n_ranges,
+                       const uint32_t* __restrict__ scanned, int stats_size, const float* __restrict__ scales,
+                       RowOps* __restrict__ ops, uint32_t* error_flag) {
+    __shared__ uint32_t off[RL_WARPS][256];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t range = (int64_t)blockIdx.x * RL_WARPS + warp;
+    if (range >= n_ranges) return;
+    for (int g = lane; g < n_groups; g += 32) off[warp][g] = scanned[(int64_t)g * n_ranges + range];
+    __syncwarp();
+    const float sc0 = scales[0], sc1 = scales[1], sc2 = scales[2];
+    const int64_t r0 = range * RL_RANGE;
+    const uint32_t lt = (1u << lane) - 1u;
+    constexpr int U = 2;
+    for (int step = 0; step < RL_RANGE / 32; step += U) {
+        int key[U], sl[U];
+        float w[U], sig[U], y[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t r = r0 + (step + u) * 32 + lane;
+            key[u] = row_group(r, n, node_id, weights, slot_of_node, slot_table_size, gs, &sl[u], &w[u]);
+            sig[u] = y[u] = 0.0f;
+            if (key[u] != 255) { sig[u] = significance[r]; y[u] = output[r]; }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint32_t mask = __match_any_sync(0xffffffffu, key[u]);
+            uint32_t pos = 0;
+            if (key[u] != 255) pos = off[warp][key[u]] + __popc(mask & lt);
+            __syncwarp();
+            if (key[u] != 255 && lane == __ffs(mask) - 1) off[warp][key[u]] += __popc(mask);
+            __syncwarp();
+            if (key[u] != 255)
+                ops[pos] = make_row_ops<KIND, CNT_INT>((uint32_t)(r0 + (step + u) * 32 + lane), sl[u], gs, w[u], sig[u], y[u], sc0,
+                                                       sc1, sc2, stats_size, error_flag);
+        }
+    }
+}
+
+// identity list (a pass whose single todo node is a tree root): ops[i] for row i in storage order; rows that do not
+// belong to the node are marked instead of being left out
+template <int KIND, int CNT_INT>
+__global__ void rowlist_ops_kernel(int64_t total, const int32_t* __restrict__ node_id, const float* __restrict__ output,
                                    const float* __restrict__ significance, const float* __restrict__ weights,
                                    const int16_t* __restrict__ slot_of_node, int slot_table_size, int gs, int stats_size,
                                    const float* __restrict__ scales, RowOps* __restrict__ ops, uint32_t* error_flag) {
-    const int64_t total = offsets[n_groups];
     const float sc0 = scales[0], sc1 = scales[1], sc2 = scales[2];
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        // sorted_rows == nullptr: identity list (a pass whose single todo node is a tree root takes the rows in
-        // storage order; rows that do not belong to it are marked instead of being sorted out)
-        const uint32_t r = sorted_rows ? sorted_rows[i] : (uint32_t)i;
-        int s;
-        if (sorted_rows) s = slot_of_node[node_id[r]];
-        else {
-            const int nid = node_id[r];
-            s = (nid >= 0 && nid < slot_table_size) ? (int)slot_of_node[nid] : -1;
-        }
-        const float w = weights ? weights[r] : 1.0f;
+        const int nid = node_id[i];
+        const int s = (nid >= 0 && nid < slot_table_size) ? (int)slot_of_node[nid] : -1;
+        const float w = weights ? weights[i] : 1.0f;
         if (s < 0 || w == 0.0f) {
             RowOps skip;
-            skip.row = r;
+            skip.row = (uint32_t)i;
             skip.slot = 0xffffffffu;
-#pragma unroll
             skip.cnt_lo = skip.cnt_hi = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) skip.q[k] = 0;
             ops[i] = skip;
             continue;
         }
-        const float sig = significance[r];
-        const float y = output[r];
-        RowOps o;
-        o.row = r;
-        o.slot = (uint32_t)(s % gs);
-        const float cw = __fmul_rn(sig, w);
-        long long qc;
-        if (CNT_INT) qc = (long long)__float2int_rn(cw);
-        else qc = __float2ll_rn(__fmul_rn(cw, sc0));
-        o.cnt_lo = (uint32_t)qc; o.cnt_hi = (uint32_t)(qc >> 32);
-        if (KIND == STAT_VARIANCE) {
-            const float sw = __fmul_rn(__fmul_rn(y, sig), w);
-            const float qw = __fmul_rn(__fmul_rn(__fmul_rn(y, y), sig), w);
-            const long long qs = __float2ll_rn(__fmul_rn(sw, sc1));
-            const long long qq = __float2ll_rn(__fmul_rn(qw, sc2));
-            o.q[0] = (uint32_t)qs; o.q[1] = (uint32_t)(qs >> 32);
-            o.q[2] = (uint32_t)qq; o.q[3] = (uint32_t)(qq >> 32);
-        } else {
-            const int cls = (int)(__fadd_rn(y, 0.000001f));
-            if (cls < 0 || cls >= stats_size) { atomicOr(error_flag, 1u); o.slot = 0xffffffffu; o.q[0] = 0; }
-            else o.q[0] = (uint32_t)(cls * (CNT_INT ? 128 : 256));  // byte offset of the class words
-            o.q[1] = o.q[2] = o.q[3] = 0;
-        }
-        ops[i] = o;
+        ops[i] = make_row_ops<KIND, CNT_INT>((uint32_t)i, s, gs, w, significance[i], output[i], sc0, sc1, sc2, stats_size, error_flag);
     }
 }
 
@@ -181,44 +263,56 @@ cudaError_t launch_transpose_bins(const uint8_t* cm, int64_t pitch, int n_featur
     return cudaGetLastError();
 }
 
-size_t rowlist_sort_temp_bytes(int64_t n) {
+int64_t rowlist_n_ranges(int64_t n) { return (n + RL_RANGE - 1) / RL_RANGE; }
+
+size_t rowlist_scan_temp_bytes(int64_t items) {
     size_t bytes = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint8_t*)nullptr, (uint8_t*)nullptr, (const uint32_t*)nullptr,
-                                    (uint32_t*)nullptr, n, 0, 8);
+    cub::DeviceScan::ExclusiveSum(nullptr, bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, items);
     return bytes;
 }
 
 cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s) {
     const int64_t n = a.n;
     if (n <= 0) return cudaSuccess;
-    int64_t g = (n + TPB - 1) / TPB;
-    if (g > 148 * 16) g = 148 * 16;
     cudaError_t e;
     if (a.identity) {
-        // no keys, no sort: one group = all rows in storage order
-        rowlist_chunks_kernel<<<1, 256, 0, s>>>(nullptr, n, 1, a.chunk_rows, a.target_chunks, a.offsets, a.chunk_group,
+        // no grouping: one group = all rows in storage order
+        rowlist_chunks_kernel<<<1, 256, 0, s>>>(nullptr, 0, n, 1, a.chunk_rows, a.target_chunks, a.offsets, a.chunk_group,
                                                 a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
-    } else {
-        rowlist_keys_kernel<<<(int)g, TPB, 0, s>>>(n, a.node_id, a.weights, a.slot_of_node, a.slot_table_size, a.gs, a.keys_in, a.vals_in);
-        e = cudaGetLastError();
-        if (e != cudaSuccess) return e;
-        size_t temp = a.temp_bytes;
-        e = cub::DeviceRadixSort::SortPairs(a.temp, temp, (const uint8_t*)a.keys_in, a.keys_out, (const uint32_t*)a.vals_in, a.vals_out, n, 0, 8, s);
-        if (e != cudaSuccess) return e;
-        rowlist_chunks_kernel<<<1, 256, 0, s>>>(a.keys_out, n, a.n_groups, a.chunk_rows, a.target_chunks, a.offsets, a.chunk_group,
-                                                a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks);
-        e = cudaGetLastError();
-        if (e != cudaSuccess) return e;
-    }
-#define OPS(K, C)                                                                                                          \
-    rowlist_ops_kernel<K, C><<<(int)g, TPB, 0, s>>>(a.identity ? nullptr : a.vals_out, a.offsets, a.identity ? 1 : a.n_groups,  \
-                                                    a.node_id, a.output, a.significance, a.weights, a.slot_of_node,            \
+        int64_t g = (n + TPB - 1) / TPB;
+        if (g > 148 * 16) g = 148 * 16;
+#define OPS(K, C)                                                                                                      \
+    rowlist_ops_kernel<K, C><<<(int)g, TPB, 0, s>>>(n, a.node_id, a.output, a.significance, a.weights, a.slot_of_node, \
                                                     a.slot_table_size, a.gs, a.stats_size, a.scales, a.ops, a.error_flag)
-    if (a.kind == STAT_VARIANCE) { if (a.cnt_int) OPS(STAT_VARIANCE, 1); else OPS(STAT_VARIANCE, 0); }
-    else { if (a.cnt_int) OPS(STAT_CLASS, 1); else OPS(STAT_CLASS, 0); }
+        if (a.kind == STAT_VARIANCE) { if (a.cnt_int) OPS(STAT_VARIANCE, 1); else OPS(STAT_VARIANCE, 0); }
+        else { if (a.cnt_int) OPS(STAT_CLASS, 1); else OPS(STAT_CLASS, 0); }
 #undef OPS
+        return cudaGetLastError();
+    }
+    const int64_t n_ranges = rowlist_n_ranges(n);
+    const int64_t items = (int64_t)a.n_groups * n_ranges + 1;
+    const unsigned grid = (unsigned)((n_ranges + RL_WARPS - 1) / RL_WARPS);
+    rowlist_count_kernel<<<grid, RL_WARPS * 32, 0, s>>>(n, a.node_id, a.weights, a.slot_of_node, a.slot_table_size, a.gs,
+                                                        a.n_groups, n_ranges, a.counts);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    size_t temp = a.temp_bytes;
+    e = cub::DeviceScan::ExclusiveSum(a.temp, temp, (const uint32_t*)a.counts, a.scanned, items, s);
+    if (e != cudaSuccess) return e;
+    rowlist_chunks_kernel<<<1, 256, 0, s>>>(a.scanned, n_ranges, n, a.n_groups, a.chunk_rows, a.target_chunks, a.offsets,
+                                            a.chunk_group, a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+#define SCATTER(K, C)                                                                                                     \
+    rowlist_scatter_kernel<K, C><<<grid, RL_WARPS * 32, 0, s>>>(n, a.node_id, a.output, a.significance, a.weights,        \
+                                                                a.slot_of_node, a.slot_table_size, a.gs, a.n_groups,      \
+                                                                n_ranges, a.scanned, a.stats_size, a.scales, a.ops,       \
+                                                                a.error_flag)
+    if (a.kind == STAT_VARIANCE) { if (a.cnt_int) SCATTER(STAT_VARIANCE, 1); else SCATTER(STAT_VARIANCE, 0); }
+    else { if (a.cnt_int) SCATTER(STAT_CLASS, 1); else SCATTER(STAT_CLASS, 0); }
+#undef SCATTER
     return cudaGetLastError();
 }
 
