@@ -146,6 +146,9 @@ struct sb_handle {
     int root_cnt_wcol = -1;
     int64_t root_cnt_total = 0;
     std::vector<int> root_cnt_feats;
+    bool weights_all_one = false;
+    bool pending_route = false;  // compute_begin left the walk of the training rows to the row-list counting pass
+    TreeView pending_tree{};
     bool cnt_int = false;  // every sig*weight product of the training rows is an integer in [0, 1024]
 
     int64_t launches_count = 0, h2d_bytes = 0, d2h_bytes = 0;
@@ -206,6 +209,7 @@ int refresh_cnt_int(sb_handle* h) {
     SB_CUDA(cudaMemcpyAsync(&flag, flag_dev, 4, cudaMemcpyDeviceToHost, h->stream));
     SB_CUDA(cudaStreamSynchronize(h->stream));
     h->cnt_int = (flag & 1u) == 0;
+    h->weights_all_one = (flag & 2u) == 0;  // then the weight arrays need not be read at all (x * 1.0f == x)
     h->weights_version += 1;  // every caller changed (or loaded) sample weights
     return SB_OK;
 }
@@ -671,7 +675,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         a.feat_bins = h->d_feat_bins;
         a.output = h->train.output;
         a.significance = h->train.significance;
-        a.weights = h->train.weights ? h->train.weights + (int64_t)(tree_id % W) * n : nullptr;  // [treeId % len], :847
+        a.weights = (h->train.weights && !h->weights_all_one) ? h->train.weights + (int64_t)(tree_id % W) * n : nullptr;  // [treeId % len], :847
         const int arr = h->cfg.is_gbdt ? 0 : tree_id;
         if (arr < 0 || arr >= h->train.n_node_arrays) return fail(SB_ERR_INVALID, "todo node tree id out of range");
         a.node_id = h->train.node_id + (int64_t)arr * n;
@@ -744,6 +748,15 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 la.counts = h->rl_counts.p; la.scanned = h->rl_counts.p + scan_items;
                 la.temp = h->rl_temp.p; la.temp_bytes = temp_bytes; la.chunk_rows = chunk_rows; la.target_chunks = target_chunks;
                 la.identity = (ns == 1 && lay.nodes[order[s0]].node_id == SB_ROOT_INDEX && partner[order[s0]] < 0) ? 1 : 0;
+                la.route = 0;
+                if (h->pending_route && !la.identity && tree_ranges.size() == 1 && h->cfg.is_gbdt) {
+                    la.route = 1;
+                    la.tree = h->pending_tree;
+                    la.cols = tr.d_col;
+                    la.feat_bins = h->d_feat_bins;
+                    la.node_id_rw = tr.node_id;
+                    h->pending_route = false;
+                }
                 la.offsets = h->rl_tables.p; la.chunk_begin = h->rl_tables.p + 257; la.chunk_end = h->rl_tables.p + 257 + max_chunks;
                 la.chunk_group = h->rl_chunk_group.p; la.n_chunks = h->rl_chunk_group.p + max_chunks; la.max_chunks = max_chunks;
                 la.ops = h->rl_ops.p; la.error_flag = h->d_error_flag;
@@ -1319,9 +1332,20 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
             else ++it;
         }
         const TreeView cv = view_of(dcur);
-        SB_CUDA(launch_route(tr.d_col, h->d_feat_bins, tr.n, tr.node_id, cv, h->d_error_flag, h->stream));
-        h->launches_count += 1;
         const bool from_tree = errors_from_tree;  // dt/DTWorker.java:672-683
+        // predictNodeIndex for the training rows.  A tree that is only its root has nowhere to send them; otherwise
+        // the walk is folded into the counting pass of the row lists (plan_histograms) unless the error sums of this
+        // pass need the node ids first.
+        h->pending_route = false;
+        if (cur_tree.n_nodes > 1) {
+            if (h->enable_row_lists && !(need_errors && from_tree)) {
+                h->pending_route = true;
+                h->pending_tree = cv;
+            } else {
+                SB_CUDA(launch_route(tr.d_col, h->d_feat_bins, tr.n, tr.node_id, cv, h->d_error_flag, h->stream));
+                h->launches_count += 1;
+            }
+        }
         if (va.loaded && from_tree) {
             SB_CUDA(launch_route(va.d_col, h->d_feat_bins, va.n, va.node_id, cv, h->d_error_flag, h->stream));
             h->launches_count += 1;
@@ -1389,7 +1413,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
             for (int c = 0; c < W; ++c) wcols.push_back(c);
         }
         for (int c : wcols) {
-            SB_CUDA(launch_absmax(tr.n, tr.output, tr.significance, tr.weights ? tr.weights + (int64_t)c * tr.n : nullptr,
+            SB_CUDA(launch_absmax(tr.n, tr.output, tr.significance, (tr.weights && !h->weights_all_one) ? tr.weights + (int64_t)c * tr.n : nullptr,
                                   h->d_maxbits, h->stream));
             h->launches_count += 1;
         }
@@ -1397,6 +1421,11 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     }
     rc = plan_histograms(h, in);
     if (rc != SB_OK) return rc;
+    if (h->pending_route) {  // no row list took the walk along: do it on its own
+        SB_CUDA(launch_route(tr.d_col, h->d_feat_bins, tr.n, tr.node_id, h->pending_tree, h->d_error_flag, h->stream));
+        h->launches_count += 1;
+        h->pending_route = false;
+    }
     rc = plan_split_tasks(h);
     if (rc != SB_OK) return rc;
     h->begun = true;

@@ -42,6 +42,15 @@ struct __align__(16) RowOps {   // one active row of the pass, in slot-group ord
     uint32_t cnt_lo;
     uint32_t q[4];              // VARIANCE: (sum_lo, sum_hi, sq_lo, sq_hi); CLASS: (class byte offset, -, -, -)
 };
+struct TreeView {  // DeviceTree as kernels see it
+    const int32_t* feat;
+    const int32_t* mask_off;
+    const double* predict;
+    const uint8_t* has_predict;
+    const uint8_t* masks;
+    int capacity;
+};
+
 struct RowListArgs {
     int64_t n;
     const int32_t* node_id;
@@ -51,6 +60,13 @@ struct RowListArgs {
     const int16_t* slot_of_node;
     int slot_table_size, gs, n_groups, stats_size, kind, cnt_int;
     const float* scales;
+    // route == 1: the counting pass first walks every row down the current tree from its node (predictNodeIndex,
+    // dt/DTWorker.java:1036-1096) and stores the new node id, instead of a separate routing pass over the rows
+    int route;
+    TreeView tree;
+    const void* const* cols;
+    const int32_t* feat_bins;
+    int32_t* node_id_rw;
     uint32_t* counts;          // [n_groups * n_ranges + 1] active rows per (group, range of 1024 rows), group-major
     uint32_t* scanned;         // exclusive prefix sum of counts: first position of each (group, range)
     void* temp;
@@ -113,14 +129,6 @@ cudaError_t hist_launch(int kind, int cnt_int, const HistArgs& a, const void* te
                         cudaStream_t stream);
 
 // ---- rows.cu
-struct TreeView {  // DeviceTree as kernels see it
-    const int32_t* feat;
-    const int32_t* mask_off;
-    const double* predict;
-    const uint8_t* has_predict;
-    const uint8_t* masks;
-    int capacity;
-};
 
 cudaError_t launch_fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t s);
 cudaError_t launch_fill_f32(float* p, int64_t n, float v, cudaStream_t s);

@@ -71,12 +71,27 @@ __device__ __forceinline__ int row_group(int64_t r, int64_t n, const int32_t* __
     return (s >= 0 && w != 0.0f) ? s / gs : 255;
 }
 
+// predictNodeIndex continued from node `id` (same walk as route_kernel in rows.cu)
+__device__ __forceinline__ int walk_down(int id, int64_t r, const void* const* __restrict__ cols,
+                                         const int32_t* __restrict__ feat_bins, const TreeView& t) {
+    while (id > 0 && id < t.capacity) {
+        const int f = t.feat[id];
+        if (f < 0) break;
+        const int bin = feat_bins[f] > 256 ? (int)static_cast<const uint16_t*>(cols[f])[r] : (int)static_cast<const uint8_t*>(cols[f])[r];
+        const uint8_t m = t.masks[t.mask_off[id] + (bin >> 3)];
+        id = 2 * id + (((m >> (bin & 7)) & 1) ? 0 : 1);
+    }
+    return id;
+}
+
 // counts[g * n_ranges + range] = active rows of group g in the range; one trailing zero so that the exclusive scan
-// also yields the total
+// also yields the total.  ROUTE: rows are first moved from their node to the child the current tree sends them to.
+template <bool ROUTE>
 __global__ void __launch_bounds__(RL_WARPS * 32)
-rowlist_count_kernel(int64_t n, const int32_t* __restrict__ node_id, const float* __restrict__ weights,
+rowlist_count_kernel(int64_t n, int32_t* __restrict__ node_id, const float* __restrict__ weights,
                      const int16_t* __restrict__ slot_of_node, int slot_table_size, int gs, int n_groups, int64_t n_ranges,
-                     uint32_t* __restrict__ counts) {
+                     uint32_t* __restrict__ counts, TreeView t, const void* const* __restrict__ cols,
+                     const int32_t* __restrict__ feat_bins, uint32_t* error_flag) {
     __shared__ uint32_t cnt[RL_WARPS][256];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t range = (int64_t)blockIdx.x * RL_WARPS + warp;
@@ -85,14 +100,52 @@ rowlist_count_kernel(int64_t n, const int32_t* __restrict__ node_id, const float
     for (int i = lane; i < 256; i += 32) cnt[warp][i] = 0u;
     __syncwarp();
     const int64_t r0 = range * RL_RANGE;
-    constexpr int U = 4;
+    constexpr int U = 8;
     for (int step = 0; step < RL_RANGE / 32; step += U) {
         int key[U];
+        if (ROUTE) {
+            // first step of the walk for U rows at once (loads of different rows in flight together); a row that has
+            // further to go (a tree seen for the first time) finishes in walk_down
+            int id[U], f[U], bin[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            int sl;
-            float w;
-            key[u] = row_group(r0 + (step + u) * 32 + lane, n, node_id, weights, slot_of_node, slot_table_size, gs, &sl, &w);
+            for (int u = 0; u < U; ++u) {
+                const int64_t r = r0 + (step + u) * 32 + lane;
+                id[u] = r < n ? node_id[r] : 0;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) f[u] = (id[u] > 0 && id[u] < t.capacity) ? t.feat[id[u]] : -1;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t r = r0 + (step + u) * 32 + lane;
+                bin[u] = 0;
+                if (f[u] >= 0)
+                    bin[u] = feat_bins[f[u]] > 256 ? (int)static_cast<const uint16_t*>(cols[f[u]])[r]
+                                                   : (int)static_cast<const uint8_t*>(cols[f[u]])[r];
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t r = r0 + (step + u) * 32 + lane;
+                int nid = id[u];
+                if (f[u] >= 0) {
+                    const uint8_t m = t.masks[t.mask_off[nid] + (bin[u] >> 3)];
+                    nid = walk_down(2 * nid + (((m >> (bin[u] & 7)) & 1) ? 0 : 1), r, cols, feat_bins, t);
+                    if (nid >= t.capacity) atomicOr(error_flag, 4u);  // child missing (dt/DTWorker.java:1089-1094)
+                    node_id[r] = nid;
+                }
+                key[u] = 255;
+                if (r < n) {
+                    const int s = (nid >= 0 && nid < slot_table_size) ? (int)slot_of_node[nid] : -1;
+                    const float w = weights ? weights[r] : 1.0f;
+                    if (s >= 0 && w != 0.0f) key[u] = s / gs;
+                }
+            }
+        } else {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                int sl;
+                float w;
+                key[u] = row_group(r0 + (step + u) * 32 + lane, n, node_id, weights, slot_of_node, slot_table_size, gs, &sl, &w);
+            }
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -184,7 +237,7 @@ rowlist_scatter_kernel(int64_t n, const int32_t* __restrict__ node_id, const flo
     const float sc0 = scales[0], sc1 = scales[1], sc2 = scales[2];
     const int64_t r0 = range * RL_RANGE;
     const uint32_t lt = (1u << lane) - 1u;
-    constexpr int U = 2;
+    constexpr int U = 4;
     for (int step = 0; step < RL_RANGE / 32; step += U) {
         int key[U], sl[U];
         float w[U], sig[U], y[U];
@@ -294,8 +347,14 @@ cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s) {
     const int64_t n_ranges = rowlist_n_ranges(n);
     const int64_t items = (int64_t)a.n_groups * n_ranges + 1;
     const unsigned grid = (unsigned)((n_ranges + RL_WARPS - 1) / RL_WARPS);
-    rowlist_count_kernel<<<grid, RL_WARPS * 32, 0, s>>>(n, a.node_id, a.weights, a.slot_of_node, a.slot_table_size, a.gs,
-                                                        a.n_groups, n_ranges, a.counts);
+    if (a.route)
+        rowlist_count_kernel<true><<<grid, RL_WARPS * 32, 0, s>>>(n, a.node_id_rw, a.weights, a.slot_of_node, a.slot_table_size,
+                                                                  a.gs, a.n_groups, n_ranges, a.counts, a.tree, a.cols,
+                                                                  a.feat_bins, a.error_flag);
+    else
+        rowlist_count_kernel<false><<<grid, RL_WARPS * 32, 0, s>>>(n, const_cast<int32_t*>(a.node_id), a.weights, a.slot_of_node,
+                                                                   a.slot_table_size, a.gs, a.n_groups, n_ranges, a.counts,
+                                                                   TreeView{}, nullptr, nullptr, a.error_flag);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     size_t temp = a.temp_bytes;

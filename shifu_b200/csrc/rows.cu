@@ -202,12 +202,15 @@ __global__ void __launch_bounds__(TPB) absmax_kernel(int64_t n, const float* __r
 
 __global__ void check_int_weights_kernel(int64_t n, const float* __restrict__ significance,
                                          const float* __restrict__ weights, uint32_t* flag) {
-    bool bad = false;
+    bool bad = false, not_one = false;
     for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
-        const float c = significance[r] * (weights ? weights[r] : 1.0f);
+        const float w = weights ? weights[r] : 1.0f;
+        const float c = significance[r] * w;
         bad |= !(c >= 0.0f && c <= 1024.0f && c == truncf(c));
+        not_one |= w != 1.0f;
     }
     if (bad) atomicOr(flag, 1u);
+    if (not_one) atomicOr(flag, 2u);  // bit 1: some sample weight differs from 1
 }
 
 __global__ void make_scales_kernel(const uint32_t* maxbits, int kind, float* scales, double* inv_scales, int* cnt_shift) {
