@@ -276,7 +276,7 @@ def run_b200(a):
         "train_error_last": (scalars[2] / scalars[0]) if scalars and scalars[0] else None,
     }
     if n_gpus == 1 and not a.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline(a, a.cpu_sample_rows, steps=1)
+        line["cpu_baseline"] = cpu_baseline(a, a.cpu_sample_rows, steps=10)  # about 10 s of CPU work
     worker.close()
     if dist_ctx is not None:
         dist_ctx.destroy_process_group()

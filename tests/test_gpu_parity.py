@@ -542,3 +542,45 @@ def test_c0_cancer_judgement_full_train_and_model_file(tmp_path):
     assert np.allclose(scores, predict, rtol=2e-5, atol=2e-6)
     dev.close()
     orc.close()
+
+
+def _export_all(master):
+    out = []
+    for t in range(master.n_trees):
+        nodes, pool, extras = master.export_tree(t)
+        out.append((b"".join(bytes(x) for x in nodes), pool.tobytes(), extras.tobytes()))
+    return out
+
+
+def test_native_tree_loop_and_single_rank_communicator():
+    """sbh_grow_tree (the iteration loop of a tree in native code) grows the trees of the call-by-call loop, and a
+    one-rank NCCL communicator inside the library (sb_dist_init) changes nothing."""
+    from shifu_b200.capi import NativeMaster, dist_unique_id
+    n_bins = [32] * 24 + [7] * 3
+    is_cat = [False] * 24 + [True] * 3
+    grown = []
+    for mode in ("calls", "native", "native+comm"):
+        cfg = ConfigArrays(n_bins, is_categorical=is_cat, max_depth=5, tree_num=3, min_instances_per_node=2, learning_rate=0.1)
+        w = Worker(cfg)
+        w.load_synthetic(60000, seed=21, row0=0, weighted=True)
+        if mode == "native+comm":
+            w.dist_init(dist_unique_id(), 0, 1)
+        m = NativeMaster(cfg, tree_num=3, max_depth=5, learning_rate=0.1)
+        it = m.build_initial_master_params()
+        passes = 0
+        while it is not None:
+            if mode == "calls":
+                w.compute_begin(it)
+                w.compute_stats()
+                _, gains, bits = w.compute_finish_split(it.n_todo, with_cat=True)
+                it = m.do_compute(gains, bits)
+                passes += 1
+            else:
+                it, p, scal = m.grow_tree(w, it)
+                passes += p
+                assert scal[0] > 0
+        grown.append((passes, _export_all(m)))
+        m.close()
+        w.close()
+    assert grown[0][0] == grown[1][0] == grown[2][0] >= 9
+    assert grown[0][1] == grown[1][1] == grown[2][1]
