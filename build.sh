@@ -3,7 +3,7 @@
 set -e
 cd "$(dirname "$0")"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
-SRC="shifu_b200/csrc/api.cu shifu_b200/csrc/rowlist.cu shifu_b200/csrc/hist.cu shifu_b200/csrc/rows.cu shifu_b200/csrc/split.cu shifu_b200/csrc/noalloc.cu shifu_b200/csrc/prep.cu shifu_b200/csrc/host_master.cpp"
+SRC="shifu_b200/csrc/api.cu shifu_b200/csrc/rowlist.cu shifu_b200/csrc/hist.cu shifu_b200/csrc/rows.cu shifu_b200/csrc/split.cu shifu_b200/csrc/noalloc.cu shifu_b200/csrc/prep.cu shifu_b200/csrc/score.cu shifu_b200/csrc/host_master.cpp"
 $NVCC -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -fmad=false \
     -Xcompiler -fPIC,-fvisibility=hidden -shared -o shifu_b200/libshifu_b200.so $SRC "$@"
 make -s -C oracle

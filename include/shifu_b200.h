@@ -278,6 +278,58 @@ SB_API int sb_compute_finish(sb_handle* h, sb_iter_out* out);
 SB_API int sb_set_stream(sb_handle* h, void* cuda_stream);
 
 /*
+ * Batch scoring: IndependentTreeModel.compute(double[] data) (dt/IndependentTreeModel.java:352-446) over a block of
+ * rows.  The model is the in-memory form of a BinaryDTSerializer file: bags of trees with a weight each (the tree's
+ * learning rate for GBT, :397-403; bag weights for RF, :426-435).  predictNode (:516-560) is followed literally: a
+ * node is walked through while it has a split and at least one child; numeric: left iff value < threshold;
+ * categorical: index = categoricalSize when Double.compare(value, 0) < 0 or Double.compare(value, size) >= 0, else
+ * (short)(value + 0.1); left iff SimpleBitSet.contains(index) == isLeft.
+ * Output: regression -> one double per row (GBT: sum of score*weight per bag, converted, averaged over the bags;
+ * RF: weighted mean per bag, averaged); classification -> n_trees doubles per row (class value of every tree).
+ */
+#define SB_CONVERT_RAW 0
+#define SB_CONVERT_OLD_SIGMOID 1 /* 1 / (1 + min(1e19, exp(-score)))       :505-507 */
+#define SB_CONVERT_SIGMOID 2     /* 1 / (1 + min(1e19, exp(-20 * score)))  :491-493 */
+#define SB_CONVERT_CUTOFF 3      /* clamp to [0, 1]                        :471-479 */
+
+typedef struct {
+    int32_t left, right;      /* index in the model's node array, -1 = null (Node.left / Node.right) */
+    int32_t column;           /* getColumnIndex(split.columnNum): position in a data row; -1 = Node.split == null */
+    int32_t split_type;       /* SB_SPLIT_CONTINUOUS / SB_SPLIT_CATEGORICAL */
+    double threshold;         /* Split.threshold */
+    int32_t is_left;          /* Split.isLeft */
+    int32_t cat_offset;       /* Split.leftOrRightCategories as SimpleBitSet bytes inside cat_pool */
+    int32_t cat_bytes;
+    int32_t class_value;      /* Predict.classValue */
+    double predict;           /* Predict.predict */
+} sb_score_node;
+
+typedef struct {
+    int32_t n_bags;
+    const int32_t* bag_begin;         /* [n_bags + 1] range of trees of each bag */
+    int32_t n_trees;
+    const int32_t* tree_root;         /* [n_trees] node index of each tree's root */
+    const double* weights;            /* [n_trees] */
+    int32_t n_nodes;
+    const sb_score_node* nodes;
+    const uint8_t* cat_pool;
+    int32_t cat_pool_bytes;
+    int32_t is_gbdt, is_classification, convert;
+    int32_t n_columns;                /* doubles per data row */
+    const int32_t* categorical_size;  /* [n_columns] getCategoricalSize of the column at that position, 0 if numeric */
+} sb_score_model;
+
+typedef struct sb_scorer sb_scorer;
+/* copies the model to `device`; the sb_score_model and what it points at may be released afterwards */
+SB_API int sb_scorer_create(const sb_score_model* model, int32_t device, sb_scorer** out);
+SB_API void sb_scorer_destroy(sb_scorer* s);
+/* data: row-major [n_rows][n_columns] doubles, host memory (or device memory when data_on_device != 0);
+   scores: host buffer of n_rows (regression) or n_rows * n_trees (classification) doubles */
+SB_API int sb_scorer_score(sb_scorer* s, int64_t n_rows, const double* data, int32_t data_on_device, double* scores);
+/* kernel time of the last sb_scorer_score call in milliseconds (CUDA events around the kernel) */
+SB_API int sb_scorer_last_kernel_ms(sb_scorer* s, float* ms);
+
+/*
  * One process per GPU, rows sharded over the processes: the merge of the workers' statistics that Guagua hands to
  * DTMaster.doCompute (dt/DTMaster.java:316-331 sums the NodeStats of every worker; :342-352 the error sums)
  * becomes an NCCL all-reduce inside sb_compute / sb_compute_stats (integer sum of the accumulators, MAX of the

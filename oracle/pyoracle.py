@@ -49,6 +49,7 @@ def load():
     lib.orc_feature_update.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float]
     lib.orc_feature_update.restype = None
     lib.orc_java_random_doubles.argtypes = [C.c_int64, C.c_int, C.c_void_p]
+    lib.orc_score_rows.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
     lib.orc_java_random_doubles.restype = None
     lib.orc_index_to_level.argtypes = [C.c_int]
     lib.orc_sample_features.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.c_void_p]
@@ -125,3 +126,15 @@ class OracleWorker:
                                            bits.ctypes.data)
         assert rc == 0
         return g, bits
+
+
+def score_rows(model, data):
+    """IndependentTreeModel.compute restated (orc_score_rows) over the rows of `data`; model: capi.ScoreModel."""
+    import numpy as np
+    lib = load()
+    data = np.ascontiguousarray(data, dtype=np.float64)
+    out = np.zeros((data.shape[0], model.out_per_row()), dtype=np.float64)
+    rc = lib.orc_score_rows(C.byref(model.struct), data.shape[0], data.ctypes.data, out.ctypes.data)
+    if rc != 0:
+        raise RuntimeError("NullPointerException in predictNode: a split node is missing a child")
+    return out if model.is_classification else out[:, 0]

@@ -832,6 +832,92 @@ SB_API void orc_feature_update(int kind, int stats_size, double* stats, int bin,
     Impurity imp{kind, stats_size, 1, 0.0};
     imp.featureUpdate(stats, bin, label, significance, weight);
 }
+/*
+ * IndependentTreeModel.compute(double[] data) over a block of rows (dt/IndependentTreeModel.java:352-446), with
+ * predictNode (:516-560) and the score converts (:471-507), on the flattened model of include/shifu_b200.h.
+ * Returns 0, or -1 when a walk meets a null child (the reference throws a NullPointerException there).
+ */
+static int scoreCompareDouble(double a, double b) {  // Double.compare
+    if (a < b) return -1;
+    if (a > b) return 1;
+    int64_t x, y;
+    memcpy(&x, &a, 8);
+    memcpy(&y, &b, 8);
+    if (std::isnan(a)) x = 0x7ff8000000000000LL;  // doubleToLongBits collapses NaNs
+    if (std::isnan(b)) y = 0x7ff8000000000000LL;
+    return x == y ? 0 : (x < y ? -1 : 1);
+}
+static int scorePredictNode(const sb_score_model* m, int node, const double* data, bool* npe) {
+    while (true) {
+        const sb_score_node& cur = m->nodes[node];
+        if (cur.column < 0 || (cur.left < 0 && cur.right < 0)) return node;  // split == null || isRealLeaf()
+        const double value = data[cur.column];
+        int next;
+        if (cur.split_type == SB_SPLIT_CONTINUOUS) {
+            next = (value < cur.threshold) ? cur.left : cur.right;  // :523-529
+        } else {
+            const int categoricalSize = m->categorical_size[cur.column];
+            int16_t indexValue;
+            if (scoreCompareDouble(value, 0.0) < 0 || scoreCompareDouble(value, (double)categoricalSize) >= 0) {
+                indexValue = (int16_t)categoricalSize;  // :533-534
+            } else {
+                const double v = value + 0.1;            // :537, (short) cast = d2i (saturating, NaN -> 0) then i2s
+                int32_t i;
+                if (std::isnan(v)) i = 0;
+                else if (v >= 2147483647.0) i = 2147483647;
+                else if (v <= -2147483648.0) i = (int32_t)(-2147483647 - 1);
+                else i = (int32_t)v;
+                indexValue = (int16_t)i;
+            }
+            bool contains = false;  // SimpleBitSet.contains (dt/SimpleBitSet.java:89-101)
+            if (indexValue >= 0 && (indexValue >> 3) < cur.cat_bytes)
+                contains = ((m->cat_pool[cur.cat_offset + (indexValue >> 3)] >> (indexValue % 8)) & 1) != 0;
+            if (cur.is_left) next = contains ? cur.left : cur.right;   // :540-546
+            else next = contains ? cur.right : cur.left;               // :547-553
+        }
+        if (next < 0) { *npe = true; return node; }
+        node = next;
+    }
+}
+SB_API int orc_score_rows(const sb_score_model* m, int64_t n_rows, const double* data, double* scores) {
+    bool npe = false;
+    const int out_per_row = m->is_classification ? m->n_trees : 1;
+    for (int64_t r = 0; r < n_rows; ++r) {
+        const double* row = data + r * m->n_columns;
+        double* out = scores + r * out_per_row;
+        if (m->is_classification) {  // computeClassificationScore :365-379
+            for (int t = 0; t < m->n_trees; ++t) out[t] = (double)m->nodes[scorePredictNode(m, m->tree_root[t], row, &npe)].class_value;
+            continue;
+        }
+        const int bags = m->n_bags;
+        double finalPredict = 0.0;
+        for (int i = 0; i < bags; ++i) {
+            if (m->is_gbdt) {  // :390-420
+                double predict = 0.0;
+                for (int j = m->bag_begin[i]; j < m->bag_begin[i + 1]; ++j) {
+                    const double score = m->nodes[scorePredictNode(m, m->tree_root[j], row, &npe)].predict;
+                    predict += score * m->weights[j];
+                }
+                if (m->convert == SB_CONVERT_OLD_SIGMOID) predict = 1 / (1 + std::min(1.0E19, std::exp(-predict)));
+                else if (m->convert == SB_CONVERT_SIGMOID) predict = 1 / (1 + std::min(1.0E19, std::exp(-20 * predict)));
+                else if (m->convert == SB_CONVERT_CUTOFF) predict = predict < 0.0 ? 0.0 : (predict > 1.0 ? 1.0 : predict);
+                finalPredict += predict;
+            } else {           // :423-441
+                double predictSum = 0.0, weightSum = 0.0;
+                for (int j = m->bag_begin[i]; j < m->bag_begin[i + 1]; ++j) {
+                    const double score = m->nodes[scorePredictNode(m, m->tree_root[j], row, &npe)].predict;
+                    const double weight = m->weights[j];
+                    weightSum += weight;
+                    predictSum += score * weight;
+                }
+                finalPredict += (predictSum / weightSum);
+            }
+        }
+        out[0] = finalPredict / bags;
+    }
+    return npe ? -1 : 0;
+}
+
 SB_API void orc_java_random_doubles(int64_t seed, int n, double* out) {
     JavaRandom r(seed);
     for (int i = 0; i < n; ++i) out[i] = r.nextDouble();

@@ -128,6 +128,117 @@ class SbGain(C.Structure):
     ]
 
 
+class SbScoreNode(C.Structure):
+    _fields_ = [("left", C.c_int32), ("right", C.c_int32), ("column", C.c_int32), ("split_type", C.c_int32),
+                ("threshold", C.c_double), ("is_left", C.c_int32), ("cat_offset", C.c_int32), ("cat_bytes", C.c_int32),
+                ("class_value", C.c_int32), ("predict", C.c_double)]
+
+
+class SbScoreModel(C.Structure):
+    _fields_ = [("n_bags", C.c_int32), ("bag_begin", C.POINTER(C.c_int32)), ("n_trees", C.c_int32),
+                ("tree_root", C.POINTER(C.c_int32)), ("weights", C.POINTER(C.c_double)), ("n_nodes", C.c_int32),
+                ("nodes", C.POINTER(SbScoreNode)), ("cat_pool", C.POINTER(C.c_uint8)), ("cat_pool_bytes", C.c_int32),
+                ("is_gbdt", C.c_int32), ("is_classification", C.c_int32), ("convert", C.c_int32),
+                ("n_columns", C.c_int32), ("categorical_size", C.POINTER(C.c_int32))]
+
+
+SCORE_NODE_DTYPE = np.dtype([("left", "<i4"), ("right", "<i4"), ("column", "<i4"), ("split_type", "<i4"),
+                             ("threshold", "<f8"), ("is_left", "<i4"), ("cat_offset", "<i4"), ("cat_bytes", "<i4"),
+                             ("class_value", "<i4"), ("predict", "<f8")], align=True)
+assert SCORE_NODE_DTYPE.itemsize == C.sizeof(SbScoreNode)
+CONVERT = {"RAW": 0, "OLD_SIGMOID": 1, "SIGMOID": 2, "CUTOFF": 3}
+
+
+class ScoreModel:
+    """Flattened IndependentTreeModel (sb_score_model) plus the numpy arrays it points at.
+
+    bags: list of bags, each a list of (root, weight); a node is a dict with "split" (None or {"column", "feature_type",
+    "threshold" | "categories" + "is_left"}), "left", "right" (dicts or None) and "predict" ((value, class) or None);
+    split["column"] is the position in a data row.  categorical_size: per data column, 0 for numeric."""
+
+    def __init__(self, bags, n_columns, categorical_size=None, is_gbdt=True, is_classification=False, convert="RAW"):
+        recs, pool, roots, weights, bag_begin = [], bytearray(), [], [], [0]
+
+        def add(n):
+            i = len(recs)
+            recs.append(None)
+            sp = n.get("split")
+            col, st, thr, isl, co, cb = -1, 0, 0.0, 0, 0, 0
+            if sp is not None:
+                col, st = sp["column"], sp["feature_type"]
+                if st == SB_SPLIT_CATEGORICAL:
+                    isl = 1 if sp["is_left"] else 0
+                    cats = sp.get("categories") or b""
+                    co, cb = len(pool), len(cats)
+                    pool.extend(cats)
+                else:
+                    thr = sp["threshold"]
+            left = add(n["left"]) if n.get("left") is not None else -1
+            right = add(n["right"]) if n.get("right") is not None else -1
+            pr = n.get("predict") or (0.0, 0)
+            recs[i] = (left, right, col, st, thr, isl, co, cb, int(pr[1]), float(pr[0]))
+            return i
+
+        for bag in bags:
+            for root, w in bag:
+                roots.append(add(root))
+                weights.append(w)
+            bag_begin.append(len(roots))
+        self.nodes = np.array(recs, dtype=SCORE_NODE_DTYPE)
+        self.pool = np.frombuffer(bytes(pool) + b"\0", dtype=np.uint8).copy()
+        self.roots = np.array(roots, dtype=np.int32)
+        self.weights = np.array(weights, dtype=np.float64)
+        self.bag_begin = np.array(bag_begin, dtype=np.int32)
+        self.cat_size = np.zeros(n_columns, dtype=np.int32) if categorical_size is None else np.asarray(categorical_size, dtype=np.int32)
+        assert len(self.cat_size) == n_columns
+        m = SbScoreModel()
+        m.n_bags, m.bag_begin = len(bags), self.bag_begin.ctypes.data_as(C.POINTER(C.c_int32))
+        m.n_trees, m.tree_root = len(roots), self.roots.ctypes.data_as(C.POINTER(C.c_int32))
+        m.weights = self.weights.ctypes.data_as(C.POINTER(C.c_double))
+        m.n_nodes, m.nodes = len(recs), C.cast(self.nodes.ctypes.data, C.POINTER(SbScoreNode))
+        m.cat_pool, m.cat_pool_bytes = self.pool.ctypes.data_as(C.POINTER(C.c_uint8)), len(self.pool) - 1
+        m.is_gbdt, m.is_classification, m.convert = int(bool(is_gbdt)), int(bool(is_classification)), CONVERT[convert]
+        m.n_columns, m.categorical_size = n_columns, self.cat_size.ctypes.data_as(C.POINTER(C.c_int32))
+        self.struct = m
+        self.n_trees, self.n_columns, self.is_classification = len(roots), n_columns, bool(is_classification)
+
+    def out_per_row(self):
+        return self.n_trees if self.is_classification else 1
+
+
+class Scorer:
+    """sb_scorer: the model resident on one GPU; score(data) -> IndependentTreeModel.compute for every row."""
+
+    def __init__(self, model: ScoreModel, device=0):
+        self.lib = load_library()
+        self.model = model
+        self.h = C.c_void_p()
+        check(self.lib, self.lib.sb_scorer_create(C.byref(model.struct), device, C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            self.lib.sb_scorer_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def score(self, data):
+        data = np.ascontiguousarray(data, dtype=np.float64)
+        assert data.ndim == 2 and data.shape[1] == self.model.n_columns
+        out = np.zeros((data.shape[0], self.model.out_per_row()), dtype=np.float64)
+        check(self.lib, self.lib.sb_scorer_score(self.h, data.shape[0], data.ctypes.data, 0, out.ctypes.data))
+        return out[:, 0] if not self.model.is_classification else out
+
+    def last_kernel_ms(self):
+        ms = C.c_float()
+        check(self.lib, self.lib.sb_scorer_last_kernel_ms(self.h, C.byref(ms)))
+        return ms.value
+
+
 class SbhParams(C.Structure):
     _fields_ = [
         ("tree_num", C.c_int32),
@@ -156,6 +267,7 @@ EXPORTS = [
     "sb_load_synthetic", "sb_read_bins", "sb_read_labels", "sb_set_profiling", "sb_hist_time",
     "sb_error_sums_static", "sb_pass_info", "sb_set_weights", "sb_sample_weights", "sb_bin_values",
     "sb_dist_unique_id", "sb_dist_init", "sbh_grow_tree",
+    "sb_scorer_create", "sb_scorer_destroy", "sb_scorer_score", "sb_scorer_last_kernel_ms",
     "sbh_master_create", "sbh_master_destroy", "sbh_master_initial", "sbh_master_do_compute", "sbh_master_tree_count",
     "sbh_master_halted", "sbh_master_export_tree",
 ]
@@ -213,6 +325,11 @@ def load_library(path=None):
     lib.sbh_master_initial.restype = C.POINTER(SbIterIn)
     lib.sbh_master_do_compute.argtypes = [H, C.POINTER(SbGain), C.c_void_p]
     lib.sb_dist_unique_id.argtypes = [C.c_void_p]
+    lib.sb_scorer_create.argtypes = [C.POINTER(SbScoreModel), C.c_int32, C.POINTER(H)]
+    lib.sb_scorer_destroy.argtypes = [H]
+    lib.sb_scorer_destroy.restype = None
+    lib.sb_scorer_score.argtypes = [H, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p]
+    lib.sb_scorer_last_kernel_ms.argtypes = [H, C.POINTER(C.c_float)]
     lib.sb_dist_init.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32]
     lib.sbh_grow_tree.argtypes = [H, H, C.POINTER(SbIterIn), C.POINTER(C.POINTER(SbIterIn)), C.POINTER(C.c_int32),
                                   C.POINTER(SbIterOut)]

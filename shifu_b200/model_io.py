@@ -235,3 +235,37 @@ def score_gbt(m, raw_row):
                 n = n["left"] if bool(has) == s["is_left"] else n["right"]
         score += t["learning_rate"] * n["predict"][0]
     return score
+
+
+def to_score_model(m, convert="RAW"):
+    """The in-memory IndependentTreeModel of a parsed model file as a capi.ScoreModel (sb_score_model): split columns
+    become positions in a data row through the file's columnNum -> index mapping (dt/IndependentTreeModel.java:566-568),
+    categorical sizes come from the file's category lists (:570-573), tree weights are the trees' learning rates."""
+    from .capi import ScoreModel
+    mapping = dict(m["column_mapping"])
+    n_columns = max(mapping.values()) + 1 if mapping else 1
+    cat_size = [0] * n_columns
+    for col, vals in m["categories"]:
+        if col in mapping:
+            cat_size[mapping[col]] = len(vals)
+
+    def conv(n):
+        sp = n["split"]
+        out = {"split": None, "left": None, "right": None, "predict": n["predict"]}
+        if sp is not None:
+            o = {"column": mapping[sp["column_num"]], "feature_type": sp["feature_type"]}
+            if sp["feature_type"] == CATEGORICAL:
+                o["is_left"] = sp["is_left"]
+                o["categories"] = sp["categories"] or b""
+            else:
+                o["threshold"] = sp["threshold"]
+            out["split"] = o
+        if n["left"] is not None:
+            out["left"] = conv(n["left"])
+        if n["right"] is not None:
+            out["right"] = conv(n["right"])
+        return out
+
+    bags = [[(conv(t["root"]), t["learning_rate"]) for t in bag] for bag in m["bags"]]
+    return ScoreModel(bags, n_columns, cat_size, is_gbdt=m["algorithm"].upper() == "GBT",
+                      is_classification=m["is_classification"], convert=convert)
