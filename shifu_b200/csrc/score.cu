@@ -2,9 +2,11 @@
 // and predictNode (:516-560) over a block of rows of raw values (the step after training).
 //
 // One thread scores one row.  The rows of a block are staged in shared memory with coalesced loads (a data row is
-// read by one thread, column after column, as the trees ask for them), the flattened model lives in global memory
-// and is read through the read-only path: it is small and shared by every thread, so it stays in L1/L2.  The walk and
-// the accumulation follow the reference's loop order in fp64 without contraction (-fmad=false), so raw and cut-off
+// read by one thread, column after column, as the trees ask for them).  The model is re-laid out at creation: every
+// tree in pre-order (the left child of node i is node i + 1), 16 bytes per node {threshold | leaf value | bitset
+// reference, right child, column, flags}, so a step of the walk is one 16-byte read-only load that hits L1 (100 trees
+// of the reference's fixture = 69 KB; half of the SM's L1/shared array is left to L1 for it).  The walk and the
+// accumulation follow the reference's loop order in fp64 without contraction (-fmad=false), so raw and cut-off
 // scores are bit-identical to the Java loop; the sigmoid converts go through exp().
 #include <algorithm>
 #include <cmath>
@@ -23,11 +25,25 @@ namespace {
 constexpr int SC_ROWS = 128;           // rows (= threads) per block
 constexpr int SC_MAX_SMEM_COLS = 200;  // widest data row staged in shared memory (200 * 128 * 8 B = 200 KB)
 
+// flags of a packed node
+constexpr uint32_t PN_WALK = 1u;    // has a split and at least one child: predictNode goes on
+constexpr uint32_t PN_CAT = 2u;     // categorical split: value = (bitset offset, bitset bytes)
+constexpr uint32_t PN_ISLEFT = 4u;  // Split.isLeft
+constexpr uint32_t PN_LEFT = 8u;    // left child exists (at index + 1)
+constexpr uint32_t PN_RIGHT = 16u;  // right child exists (at .right)
+
+struct __align__(16) PackedNode {
+    double value;    // numeric split: threshold; leaf: Predict.predict (classification: the class value); categorical: bitset ref
+    int32_t right;
+    int16_t column;
+    uint16_t flags;
+};
+
 struct ScoreView {
     const int32_t* bag_begin;
     const int32_t* tree_root;
     const double* weights;
-    const sb_score_node* nodes;
+    const PackedNode* nodes;
     const uint8_t* cat_pool;
     const int32_t* categorical_size;
     int n_bags, n_trees, n_nodes, cat_pool_bytes, is_gbdt, is_classification, convert, n_columns;
@@ -41,32 +57,34 @@ __device__ __forceinline__ bool java_compare_lt(double a, double b) {
     return !isnan(a) && isnan(b);
 }
 
-// predictNode (dt/IndependentTreeModel.java:516-560); returns the node index it stops at
+// predictNode (dt/IndependentTreeModel.java:516-560); returns the value of the node it stops at
 template <class RowReader>
-__device__ __forceinline__ int predict_node(const ScoreView& m, int node, const RowReader& row, uint32_t* error_flag) {
+__device__ __forceinline__ double predict_node(const ScoreView& m, int node, const RowReader& row, uint32_t* error_flag) {
     while (true) {
-        const sb_score_node& nd = m.nodes[node];
-        if (nd.column < 0 || (nd.left < 0 && nd.right < 0)) return node;  // split == null or isRealLeaf()
-        const double value = row(nd.column);
+        const int4 raw = __ldg(reinterpret_cast<const int4*>(m.nodes + node));
+        const double nvalue = __hiloint2double(raw.y, raw.x);
+        const uint32_t flags = (uint32_t)raw.w >> 16;
+        if (!(flags & PN_WALK)) return nvalue;  // split == null or isRealLeaf()
+        const int column = (int)(short)(raw.w & 0xffff);
+        const double value = row(column);
         bool go_left;
-        if (nd.split_type == SB_SPLIT_CONTINUOUS) {
-            go_left = value < nd.threshold;
+        if (!(flags & PN_CAT)) {
+            go_left = value < nvalue;
         } else {
-            const int size = m.categorical_size[nd.column];
+            const int size = m.categorical_size[column];
             int idx;
             // Double.compare(value, 0d) < 0 || Double.compare(value, categoricalSize) >= 0  -> the missing category
             if (java_compare_lt(value, 0.0) || !java_compare_lt(value, (double)size)) idx = (int)(short)size;
             else idx = (int)(short)(int)(value + 0.1);  // (short)(value + 0.1d): d2i then i2s
             bool has = false;
-            if (idx >= 0 && (idx >> 3) < nd.cat_bytes) has = (m.cat_pool[nd.cat_offset + (idx >> 3)] >> (idx & 7)) & 1;
-            go_left = has == (nd.is_left != 0);
+            if (idx >= 0 && (idx >> 3) < raw.y) has = (m.cat_pool[raw.x + (idx >> 3)] >> (idx & 7)) & 1;
+            go_left = has == ((flags & PN_ISLEFT) != 0);
         }
-        const int next = go_left ? nd.left : nd.right;
-        if (next < 0) {  // the reference would throw a NullPointerException here
+        if (!(flags & (go_left ? PN_LEFT : PN_RIGHT))) {  // the reference would throw a NullPointerException here
             atomicOr(error_flag, 1u);
-            return node;
+            return nvalue;
         }
-        node = next;
+        node = go_left ? node + 1 : raw.z;
     }
 }
 
@@ -82,7 +100,7 @@ __device__ __forceinline__ double convert_score(int convert, double predict) {
 template <class RowReader>
 __device__ __forceinline__ void score_row(const ScoreView& m, const RowReader& row, double* out, uint32_t* error_flag) {
     if (m.is_classification) {  // computeClassificationScore (:365-379): every tree's class value
-        for (int t = 0; t < m.n_trees; ++t) out[t] = (double)m.nodes[predict_node(m, m.tree_root[t], row, error_flag)].class_value;
+        for (int t = 0; t < m.n_trees; ++t) out[t] = predict_node(m, m.tree_root[t], row, error_flag);
         return;
     }
     double final_predict = 0.0;
@@ -90,12 +108,12 @@ __device__ __forceinline__ void score_row(const ScoreView& m, const RowReader& r
         if (m.is_gbdt) {  // :390-420
             double predict = 0.0;
             for (int t = m.bag_begin[b]; t < m.bag_begin[b + 1]; ++t)
-                predict += m.nodes[predict_node(m, m.tree_root[t], row, error_flag)].predict * m.weights[t];
+                predict += predict_node(m, m.tree_root[t], row, error_flag) * m.weights[t];
             final_predict += convert_score(m.convert, predict);
         } else {          // :423-441
             double predict_sum = 0.0, weight_sum = 0.0;
             for (int t = m.bag_begin[b]; t < m.bag_begin[b + 1]; ++t) {
-                const double score = m.nodes[predict_node(m, m.tree_root[t], row, error_flag)].predict;
+                const double score = predict_node(m, m.tree_root[t], row, error_flag);
                 const double weight = m.weights[t];
                 weight_sum += weight;
                 predict_sum += score * weight;
@@ -186,20 +204,66 @@ SB_API int sb_scorer_create(const sb_score_model* m, int32_t device, sb_scorer**
     SB_CUDA(cudaSetDevice(device));
     std::unique_ptr<sb_scorer> s(new sb_scorer());
     s->device = device;
+    // pre-order re-layout of every tree: the left child of packed node i is packed node i + 1
+    std::vector<PackedNode> packed;
+    std::vector<int32_t> roots((size_t)m->n_trees);
+    packed.reserve((size_t)m->n_nodes);
+    for (int t = 0; t < m->n_trees; ++t) {
+        roots[t] = (int32_t)packed.size();
+        // explicit stack of (source node, packed index of the parent whose .right must be patched, or -1)
+        std::vector<std::pair<int, int>> stack{{m->tree_root[t], -1}};
+        while (!stack.empty()) {
+            const auto [src, patch] = stack.back();
+            stack.pop_back();
+            if (packed.size() > (size_t)m->n_nodes * 2 + 16 || packed.size() >= (size_t)0x7fffffff)
+                return fail(SB_ERR_INVALID, "the node links of a tree form a cycle (or a node is shared by trees more than once per node)");
+            const sb_score_node& nd = m->nodes[src];
+            const int me = (int)packed.size();
+            if (patch >= 0) packed[patch].right = me;
+            PackedNode pn;
+            pn.right = -1;
+            pn.column = (int16_t)-1;
+            uint32_t flags = 0;
+            const bool walk = nd.column >= 0 && (nd.left >= 0 || nd.right >= 0);
+            if (walk) {
+                if (nd.column > 32767) return fail(SB_ERR_UNSUPPORTED, "more than 32767 data columns");
+                flags |= PN_WALK;
+                pn.column = (int16_t)nd.column;
+                if (nd.split_type == SB_SPLIT_CATEGORICAL) {
+                    flags |= PN_CAT;
+                    if (nd.is_left) flags |= PN_ISLEFT;
+                    const int32_t ref[2] = {nd.cat_offset, nd.cat_bytes};
+                    memcpy(&pn.value, ref, 8);
+                } else {
+                    pn.value = nd.threshold;
+                }
+                if (nd.left >= 0) flags |= PN_LEFT;
+                if (nd.right >= 0) flags |= PN_RIGHT;
+            } else {
+                pn.value = m->is_classification ? (double)nd.class_value : nd.predict;
+            }
+            pn.flags = (uint16_t)flags;
+            packed.push_back(pn);
+            if (walk) {  // right is pushed first so that the left subtree is laid out right behind this node
+                if (nd.right >= 0) stack.push_back({nd.right, me});
+                if (nd.left >= 0) stack.push_back({nd.left, -1});
+            }
+        }
+    }
     // one blob: [nodes][weights][bag_begin][tree_root][categorical_size][cat_pool], each 16-byte aligned
     auto up = [](size_t v) { return (v + 15) / 16 * 16; };
     const size_t o_nodes = 0;
-    const size_t o_w = o_nodes + up(sizeof(sb_score_node) * m->n_nodes);
+    const size_t o_w = o_nodes + up(sizeof(PackedNode) * packed.size());
     const size_t o_bag = o_w + up(8 * (size_t)m->n_trees);
     const size_t o_root = o_bag + up(4 * (size_t)(m->n_bags + 1));
     const size_t o_cat = o_root + up(4 * (size_t)m->n_trees);
     const size_t o_pool = o_cat + up(4 * (size_t)m->n_columns);
     const size_t total = o_pool + up((size_t)std::max(m->cat_pool_bytes, 1));
     std::vector<uint8_t> host(total, 0);
-    memcpy(host.data() + o_nodes, m->nodes, sizeof(sb_score_node) * m->n_nodes);
+    memcpy(host.data() + o_nodes, packed.data(), sizeof(PackedNode) * packed.size());
     memcpy(host.data() + o_w, m->weights, 8 * (size_t)m->n_trees);
     memcpy(host.data() + o_bag, m->bag_begin, 4 * (size_t)(m->n_bags + 1));
-    memcpy(host.data() + o_root, m->tree_root, 4 * (size_t)m->n_trees);
+    memcpy(host.data() + o_root, roots.data(), 4 * (size_t)m->n_trees);
     memcpy(host.data() + o_cat, m->categorical_size, 4 * (size_t)m->n_columns);
     if (m->cat_pool_bytes > 0 && m->cat_pool) memcpy(host.data() + o_pool, m->cat_pool, (size_t)m->cat_pool_bytes);
     SB_CUDA(cudaMalloc(&s->blob, total));
@@ -209,13 +273,13 @@ SB_API int sb_scorer_create(const sb_score_model* m, int32_t device, sb_scorer**
     SB_CUDA(cudaEventCreate(&s->e1));
     uint8_t* b = static_cast<uint8_t*>(s->blob);
     ScoreView& v = s->view;
-    v.nodes = reinterpret_cast<const sb_score_node*>(b + o_nodes);
+    v.nodes = reinterpret_cast<const PackedNode*>(b + o_nodes);
     v.weights = reinterpret_cast<const double*>(b + o_w);
     v.bag_begin = reinterpret_cast<const int32_t*>(b + o_bag);
     v.tree_root = reinterpret_cast<const int32_t*>(b + o_root);
     v.categorical_size = reinterpret_cast<const int32_t*>(b + o_cat);
     v.cat_pool = b + o_pool;
-    v.n_bags = m->n_bags; v.n_trees = m->n_trees; v.n_nodes = m->n_nodes; v.cat_pool_bytes = m->cat_pool_bytes;
+    v.n_bags = m->n_bags; v.n_trees = m->n_trees; v.n_nodes = (int)packed.size(); v.cat_pool_bytes = m->cat_pool_bytes;
     v.is_gbdt = m->is_gbdt; v.is_classification = m->is_classification; v.convert = m->convert; v.n_columns = m->n_columns;
     *out = s.release();
     return SB_OK;
@@ -265,6 +329,8 @@ SB_API int sb_scorer_score(sb_scorer* s, int64_t n_rows, const double* data, int
         static bool attr_set = false;
         if (!attr_set) {
             SB_CUDA(cudaFuncSetAttribute(score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            // leave half of the L1/shared array to L1: the packed model is re-read by every thread
+            SB_CUDA(cudaFuncSetAttribute(score_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 50));
             attr_set = true;
         }
         score_kernel<true><<<grid, SC_ROWS, smem, 0>>>(v, d_in, n_rows, s->d_scores, s->d_error);
