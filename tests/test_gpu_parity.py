@@ -584,3 +584,46 @@ def test_native_tree_loop_and_single_rank_communicator():
         w.close()
     assert grown[0][0] == grown[1][0] == grown[2][0] >= 9
     assert grown[0][1] == grown[1][1] == grown[2][1]
+
+
+def test_feature_counts_cover_every_tile_shape():
+    """The last feature tile holds 1..4 features per lane (template parameter KACT of hist_rows_kernel): 27 -> 1,
+    40 -> 2, 80 -> 3, 128 -> 4 exactly full, 130 -> a full tile plus a 2-feature tile, 200 -> 4 + 3."""
+    for F, seed in ((27, 51), (80, 52), (128, 53), (130, 54), (200, 55)):
+        run_gbt(6000, [16] * F, seed=seed, n_trees=2, max_depth=3, weighted=(F % 2 == 0), with_validation=False)
+    run_gbt(6000, [16] * 80, seed=56, n_trees=1, max_depth=4, feature_subsets=True, with_validation=False)  # per-cell masks
+
+
+def test_worker_that_joins_a_tree_midway_routes_from_the_root():
+    """A handle that first sees a tree at its third level (the message carries the whole tree, as always) must walk its
+    rows from the root: the statistics equal those of the handle that saw every pass."""
+    n, n_bins = 30000, [32] * 24
+    cols, y, sig, _ = make_data(n, n_bins, seed=91, weighted=True)
+    cfg = ConfigArrays(n_bins, max_depth=5, min_instances_per_node=1, tree_num=2)
+    a = Worker(cfg)
+    a.load_rows(cols, y, sig, None)
+    root = Node(1)
+    todo_nodes, switch, level = [root], True, 1
+    while todo_nodes:
+        todo = [(k, 0, nd.id, []) for k, nd in enumerate(todo_nodes)]
+        it = IterIn(cfg, [(0, root)], todo, switch_to_next_tree=switch, is_first_tree=True)
+        ra = a.compute(it)
+        if level >= 3:  # a fresh handle sees only this message
+            b = Worker(cfg)
+            b.load_rows(cols, y, sig, None)
+            rb = b.compute(it)
+            assert np.array_equal(ra[4], rb[4]) and ra[0] == rb[0]
+            b.close()
+        gains, bits = a.best_splits(len(todo))
+        nxt = []
+        for k, nd in enumerate(todo_nodes):
+            g = gains[k]
+            if not g.found or g.gain <= 0 or index_to_level(nd.id) == 5:
+                continue
+            nd.predict = g.predict
+            left, right = apply_gain(cfg, nd, g, bits, k)
+            if index_to_level(nd.id) + 1 < 5:
+                nxt += [left, right]
+        todo_nodes, switch, level = nxt, False, level + 1
+    assert level >= 4
+    a.close()
