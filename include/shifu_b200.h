@@ -226,6 +226,15 @@ SB_API int sb_set_weights(sb_handle* h, int32_t w_index, const float* weights);
    `new java.util.Random(seed)` is <= rate, else 0f -- the same numbers a seeded (baggingSampleSeed) reference worker
    draws for its rows in load order.  Not stratified (the reference keeps one Random per class for that). */
 SB_API int sb_sample_weights(sb_handle* h, int32_t w_index, int64_t seed, double rate, int64_t first_draw);
+/* Stratified variant (isStratifiedSampling, dt/DTWorker.java:1526-1532 and :646-653): the reference keeps one Random
+   per class value (int)(label + 0.01f), every one created from the same seed, so training row j gets the k-th
+   nextDouble() of `new java.util.Random(seed)`, k = number of earlier rows of its class in load order. */
+SB_API int sb_sample_weights_stratified(sb_handle* h, int32_t w_index, int64_t seed, double rate, int32_t n_classes);
+/* RF bag counts (dt/DTWorker.java:1547-1571): subsampleWeights[w_index] of training row j becomes a Poisson(rate) count.
+   The reference samples commons-math3's PoissonDistribution from an unseeded generator, so this matches it in
+   distribution only: the count is the inverse Poisson CDF of a counter-based uniform of (seed, row0 + j, w_index) --
+   row0 = global index of the handle's first row, so any sharding of the rows draws the same bags. */
+SB_API int sb_sample_poisson(sb_handle* h, int32_t w_index, uint64_t seed, double rate, int64_t row0);
 /* DTWorker.getBinIndex (dt/DTWorker.java:1001-1034) for a whole numeric column: values (device, n floats; NaN counts as
    0f like DTWorker.getFloatValue :1299-1305) -> bin indices (device, uint8 if out_width == 1 else uint16).
    bin_boundary is a HOST array of n_bins (<= 4096) doubles.  A value below the first boundary gets the all-ones

@@ -267,7 +267,7 @@ EXPORTS = [
     "sb_load_synthetic", "sb_read_bins", "sb_read_labels", "sb_set_profiling", "sb_hist_time",
     "sb_error_sums_static", "sb_pass_info", "sb_set_weights", "sb_sample_weights", "sb_bin_values",
     "sb_dist_unique_id", "sb_dist_init", "sbh_grow_tree",
-    "sb_scorer_create", "sb_scorer_destroy", "sb_scorer_score", "sb_scorer_last_kernel_ms",
+    "sb_sample_weights_stratified", "sb_sample_poisson", "sb_scorer_create", "sb_scorer_destroy", "sb_scorer_score", "sb_scorer_last_kernel_ms",
     "sbh_master_create", "sbh_master_destroy", "sbh_master_initial", "sbh_master_do_compute", "sbh_master_tree_count",
     "sbh_master_halted", "sbh_master_export_tree",
 ]
@@ -325,6 +325,8 @@ def load_library(path=None):
     lib.sbh_master_initial.restype = C.POINTER(SbIterIn)
     lib.sbh_master_do_compute.argtypes = [H, C.POINTER(SbGain), C.c_void_p]
     lib.sb_dist_unique_id.argtypes = [C.c_void_p]
+    lib.sb_sample_weights_stratified.argtypes = [H, C.c_int32, C.c_int64, C.c_double, C.c_int32]
+    lib.sb_sample_poisson.argtypes = [H, C.c_int32, C.c_uint64, C.c_double, C.c_int64]
     lib.sb_scorer_create.argtypes = [C.POINTER(SbScoreModel), C.c_int32, C.POINTER(H)]
     lib.sb_scorer_destroy.argtypes = [H]
     lib.sb_scorer_destroy.restype = None
@@ -513,6 +515,12 @@ class Worker:
         bits = np.zeros(max(n_todo, 1) * SB_MAX_CAT_BYTES, dtype=np.uint8) if with_cat else None
         check(self.lib, self.lib.sb_compute_finish_split(self.h, C.byref(out), gains, None if bits is None else bits.ctypes.data))
         return (out.train_count, out.validation_count, out.train_error, out.validation_error), gains, bits
+
+    def sample_weights_stratified(self, w_index, seed, rate, n_classes):
+        check(self.lib, self.lib.sb_sample_weights_stratified(self.h, w_index, seed, rate, n_classes))
+
+    def sample_poisson(self, w_index, seed, rate, row0=0):
+        check(self.lib, self.lib.sb_sample_poisson(self.h, w_index, seed, rate, row0))
 
     def dist_init(self, id128, rank, world_size):
         """Join the library's own NCCL communicator (id128: the 128 bytes of dist_unique_id() made on rank 0)."""

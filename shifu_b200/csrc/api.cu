@@ -1239,6 +1239,43 @@ SB_API int sb_sample_weights(sb_handle* h, int32_t w_index, int64_t seed, double
     return refresh_cnt_int(h);
 }
 
+SB_API int sb_sample_weights_stratified(sb_handle* h, int32_t w_index, int64_t seed, double rate, int32_t n_classes) {
+    if (!h) return fail(SB_ERR_INVALID, "null handle");
+    RowSet& r = h->train;
+    if (!r.loaded || !r.weights) return fail(SB_ERR_STATE, "training rows not loaded (or adopted without a weight array)");
+    if (w_index < 0 || w_index >= h->cfg.weights_per_row) return fail(SB_ERR_INVALID, "weight index out of range");
+    if (n_classes < 1 || n_classes > 64) return fail(SB_ERR_INVALID, "n_classes must be in [1, 64]");
+    if (r.n >= (int64_t)0xffffffff) return fail(SB_ERR_UNSUPPORTED, "more than 2^32 - 1 rows per handle");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    const size_t n = (size_t)std::max<int64_t>(r.n, 1);
+    const size_t temp_bytes = stratified_temp_bytes(r.n);
+    SB_CUDA(h->rl_counts.reserve(2 * n));
+    SB_CUDA(h->rl_temp.reserve(temp_bytes + 16));
+    SB_CUDA(cudaMemsetAsync(h->d_error_flag, 0, 4, h->stream));
+    SB_CUDA(launch_stratified_mask(r.weights + (int64_t)w_index * r.n, r.label, r.n, n_classes, seed, rate, h->rl_counts.p,
+                                   h->rl_counts.p + n, h->rl_temp.p, temp_bytes, h->d_error_flag, h->stream));
+    h->launches_count += 4 * n_classes;
+    uint32_t flag = 0;
+    SB_CUDA(cudaMemcpyAsync(&flag, h->d_error_flag, 4, cudaMemcpyDeviceToHost, h->stream));
+    SB_CUDA(cudaStreamSynchronize(h->stream));
+    if (flag & 1u) return fail(SB_ERR_RANGE, "class (int)(label + 0.01f) outside [0, n_classes)");
+    h->scales_valid = false;
+    return refresh_cnt_int(h);
+}
+
+SB_API int sb_sample_poisson(sb_handle* h, int32_t w_index, uint64_t seed, double rate, int64_t row0) {
+    if (!h) return fail(SB_ERR_INVALID, "null handle");
+    RowSet& r = h->train;
+    if (!r.loaded || !r.weights) return fail(SB_ERR_STATE, "training rows not loaded (or adopted without a weight array)");
+    if (w_index < 0 || w_index >= h->cfg.weights_per_row) return fail(SB_ERR_INVALID, "weight index out of range");
+    if (!(rate > 0.0) || rate > 64.0 || row0 < 0) return fail(SB_ERR_INVALID, "rate must be in (0, 64], row0 >= 0");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    SB_CUDA(launch_poisson_bags(r.weights + (int64_t)w_index * r.n, r.n, seed, row0, w_index, rate, std::exp(-rate), h->stream));
+    h->launches_count += 1;
+    h->scales_valid = false;
+    return refresh_cnt_int(h);
+}
+
 SB_API int64_t sb_stats_len(sb_handle* h, const sb_iter_in* in) {
     if (!h || !in) return fail(SB_ERR_INVALID, "null argument");
     TodoLayout lay;

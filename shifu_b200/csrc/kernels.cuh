@@ -177,6 +177,12 @@ cudaError_t launch_check_bins(const void* const* cols, const int32_t* feat_bins,
 
 // ---- prep.cu
 cudaError_t launch_java_bagging_mask(float* weights, int64_t n, long long seed, double rate, long long first_draw, cudaStream_t s);
+size_t stratified_temp_bytes(int64_t n);
+cudaError_t launch_stratified_mask(float* weights, const float* label, int64_t n, int n_classes, long long seed, double rate,
+                                   uint32_t* ind, uint32_t* ordinal, void* temp, size_t temp_bytes, uint32_t* error_flag,
+                                   cudaStream_t s);
+cudaError_t launch_poisson_bags(float* weights, int64_t n, unsigned long long seed, long long row0, int tree, double rate, double p0,
+                                cudaStream_t s);
 
 // ---- split.cu
 // raw (lo, hi) integer accumulators -> the reference's double statistics (one rounding each).

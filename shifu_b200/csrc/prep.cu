@@ -2,6 +2,8 @@
 //   f1  binning at load: DTWorker.getBinIndex (dt/DTWorker.java:1001-1034) for a whole column on the device;
 //   f4  bagging masks from java.util.Random on the device (dt/DTWorker.java:1521-1544 at load, :643-668 per tree),
 //       with jump-ahead so that row j gets exactly the j-th nextDouble() of `new Random(seed)`.
+#include <cub/device/device_scan.cuh>
+
 #include "common.cuh"
 #include "kernels.cuh"
 
@@ -76,9 +78,94 @@ __global__ void java_bagging_mask_kernel(float* __restrict__ weights, int64_t n,
     }
 }
 
+// Stratified variant (dt/DTWorker.java:1526-1532, 646-653): one Random per class, all created from the same seed, so a row
+// gets the k-th nextDouble() of `new Random(seed)` where k counts the earlier rows of ITS class.
+// class of a row = (int)(label + 0.01f) (:1520).
+__global__ void class_indicator_kernel(const float* __restrict__ label, int64_t n, int cls, int n_classes, uint32_t* __restrict__ ind,
+                                       uint32_t* error_flag) {
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(label[r] + 0.01f);
+        if (cls == 0 && (c < 0 || c >= n_classes)) atomicOr(error_flag, 1u);
+        ind[r] = c == cls ? 1u : 0u;
+    }
+}
+__global__ void stratified_mask_kernel(float* __restrict__ weights, const float* __restrict__ label, const uint32_t* __restrict__ ordinal,
+                                       int64_t n, int cls, long long seed, double rate) {
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        if ((int)(label[r] + 0.01f) != cls) continue;
+        unsigned long long s = ((unsigned long long)seed ^ LCG_A) & LCG_MASK;
+        s = lcg_jump(s, 2ULL * (unsigned long long)ordinal[r]);
+        s = (s * LCG_A + LCG_C) & LCG_MASK;
+        const long long hi = (long long)(s >> (48 - 26));
+        s = (s * LCG_A + LCG_C) & LCG_MASK;
+        const long long lo = (long long)(s >> (48 - 27));
+        const double d = (double)((hi << 27) + lo) * (1.0 / 9007199254740992.0);
+        weights[r] = d <= rate ? 1.0f : 0.0f;
+    }
+}
+
+// RF bag counts (dt/DTWorker.java:1547-1571): the reference draws PoissonDistribution(rate).sample() from an unseeded
+// commons-math3 generator, so only the distribution can be matched.  Here the count of (row, tree) is the inverse CDF of
+// a counter-based uniform, splitmix64(seed ^ (global row * M1 + tree * M2)): any shard of the rows can be drawn anywhere
+// (shifu_b200/synthetic.py:poisson_bags is the host twin).  exp(-rate) comes from the host so both sides share it.
+__device__ __forceinline__ unsigned long long splitmix64_dev(unsigned long long x) {
+    x += 0x9E3779B97F4A7C15ULL;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
+}
+__global__ void poisson_bags_kernel(float* __restrict__ weights, int64_t n, unsigned long long seed, long long row0, int tree,
+                                    double rate, double p0) {
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        const unsigned long long key = (unsigned long long)(row0 + r) * 0xD1342543DE82EF95ULL + (unsigned long long)tree * 0x9E3779B97F4A7C15ULL;
+        const double u = (double)(splitmix64_dev(seed ^ key) >> 11) * (1.0 / 9007199254740992.0);
+        int k = 0;
+        double pk = p0, cdf = p0;
+        while (u > cdf && k < 1000) {
+            ++k;
+            pk = pk * rate / (double)k;
+            cdf += pk;
+        }
+        weights[r] = (float)k;
+    }
+}
+
 }  // namespace
 
 namespace sb {
+size_t stratified_temp_bytes(int64_t n) {
+    size_t bytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, n);
+    return bytes;
+}
+// ind / ordinal: n uint32 each; temp: stratified_temp_bytes(n)
+cudaError_t launch_stratified_mask(float* weights, const float* label, int64_t n, int n_classes, long long seed, double rate,
+                                   uint32_t* ind, uint32_t* ordinal, void* temp, size_t temp_bytes, uint32_t* error_flag,
+                                   cudaStream_t s) {
+    if (n <= 0) return cudaSuccess;
+    int64_t g = (n + 255) / 256;
+    if (g > 148 * 16) g = 148 * 16;
+    for (int c = 0; c < n_classes; ++c) {
+        class_indicator_kernel<<<(int)g, 256, 0, s>>>(label, n, c, n_classes, ind, error_flag);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        size_t tb = temp_bytes;
+        e = cub::DeviceScan::ExclusiveSum(temp, tb, (const uint32_t*)ind, ordinal, n, s);
+        if (e != cudaSuccess) return e;
+        stratified_mask_kernel<<<(int)g, 256, 0, s>>>(weights, label, ordinal, n, c, seed, rate);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+cudaError_t launch_poisson_bags(float* weights, int64_t n, unsigned long long seed, long long row0, int tree, double rate, double p0,
+                                cudaStream_t s) {
+    if (n <= 0) return cudaSuccess;
+    int64_t g = (n + 255) / 256;
+    if (g > 148 * 16) g = 148 * 16;
+    poisson_bags_kernel<<<(int)g, 256, 0, s>>>(weights, n, seed, row0, tree, rate, p0);
+    return cudaGetLastError();
+}
 cudaError_t launch_java_bagging_mask(float* weights, int64_t n, long long seed, double rate, long long first_draw, cudaStream_t s) {
     if (n <= 0) return cudaSuccess;
     int64_t g = ((n + ROWS_PER_THREAD - 1) / ROWS_PER_THREAD + 255) / 256;

@@ -57,3 +57,24 @@ def make(seed, n_bins, row0, n_rows, label_kind=0, weighted=False):
     cols = [bins_column(seed, f, F, int(n_bins[f]), row0, n_rows) for f in range(F)]
     y, sig = labels(seed, cols, n_bins, row0, n_rows, label_kind, weighted)
     return cols, y, sig
+
+
+def poisson_bags(seed, tree, rate, row0, n_rows):
+    """Host twin of sb_sample_poisson (prep.cu poisson_bags_kernel): inverse Poisson CDF of a counter-based uniform."""
+    import math
+    with np.errstate(over="ignore"):
+        r = np.arange(row0, row0 + n_rows, dtype=np.uint64)
+        key = (r * np.uint64(0xD1342543DE82EF95) + np.uint64(tree) * np.uint64(0x9E3779B97F4A7C15)) & _M
+        u = (splitmix64(np.uint64(seed) ^ key) >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+    p0 = math.exp(-rate)
+    k = np.zeros(n_rows, dtype=np.int64)
+    pk = np.full(n_rows, p0)
+    cdf = np.full(n_rows, p0)
+    for _ in range(1000):
+        more = u > cdf
+        if not more.any():
+            break
+        k[more] += 1
+        pk[more] = pk[more] * rate / k[more]
+        cdf[more] = cdf[more] + pk[more]
+    return k.astype(np.float32)

@@ -482,6 +482,55 @@ def test_device_bagging_mask_is_java_random():
     w.close()
 
 
+def test_device_stratified_mask_is_one_java_random_per_class():
+    """f4, isStratifiedSampling: one Random(seed) per class value, so a row gets the k-th nextDouble(), k = earlier rows
+    of its class (dt/DTWorker.java:1526-1532)."""
+    from shifu_b200.dt_master import JavaRandom
+    n, n_bins = 50021, [8] * 3
+    rng = np.random.default_rng(17)
+    cols = [rng.integers(0, 8, size=n).astype(np.uint8) for _ in n_bins]
+    y = rng.choice([0.0, 1.0, 2.0], size=n, p=[0.6, 0.3, 0.1]).astype(np.float32)
+    cfg = ConfigArrays(n_bins)
+    w = Worker(cfg)
+    w.load_rows(cols, y, None, None)
+    seed, rate = 20240517, 0.35
+    w.sample_weights_stratified(0, seed, rate, 3)
+    _, _, _, got = w.read_rows(n)
+    r = JavaRandom(seed)
+    draws = np.array([r.next_double() for _ in range(n)])
+    want = np.zeros(n, dtype=np.float32)
+    for c in range(3):
+        idx = np.flatnonzero((y + np.float32(0.01)).astype(np.int32) == c)
+        want[idx] = (draws[:len(idx)] <= rate).astype(np.float32)
+    assert np.array_equal(got, want)
+    with pytest.raises(RuntimeError):
+        w.sample_weights_stratified(0, seed, rate, 2)   # class 2 exists
+    w.close()
+
+
+def test_device_poisson_bags_match_the_host_twin_and_the_distribution():
+    """f4, RF bag counts: counter-based, so two shards draw what one handle draws; Poisson(rate) in distribution."""
+    from shifu_b200 import synthetic
+    n = 400003
+    cfg = ConfigArrays([8] * 3, is_gbdt=False, tree_num=3, weights_per_row=3, impurity=capi.SB_IMPURITY_GINI, num_classes=2)
+    w = Worker(cfg)
+    w.load_synthetic(n, seed=5, label_kind=1)
+    for t, rate in ((0, 1.0), (2, 0.5)):
+        w.sample_poisson(t, 77, rate, row0=1000)
+        _, _, _, got = w.read_rows(n, w_index=t)
+        assert np.array_equal(got, synthetic.poisson_bags(77, t, rate, 1000, n))
+        assert abs(got.mean() - rate) < 0.01 and abs(got.var() - rate) < 0.02
+        assert abs((got == 0).mean() - np.exp(-rate)) < 0.005
+    half = Worker(cfg)
+    half.load_synthetic(n // 2, seed=5, label_kind=1)
+    half.sample_poisson(0, 77, 1.0, row0=1000 + (n - n // 2))
+    _, _, _, tail = half.read_rows(n // 2, w_index=0)
+    _, _, _, full = w.read_rows(n, w_index=0)
+    assert np.array_equal(tail, full[n - n // 2:])
+    half.close()
+    w.close()
+
+
 def test_c0_cancer_judgement_full_train_and_model_file(tmp_path):
     """Config C0: the reference's own example (429 rows x 30 numeric x 10 bins, binned with its ColumnConfig.json), GBT
     10 trees depth 6 squared loss lr 0.05, all features.  Every iteration's statistics, scalars and chosen splits are

@@ -62,8 +62,8 @@ t0 = time.time()
 w.load_synthetic(n_local, seed=C["seed"], row0=row0, label_kind=C["label_kind"])
 rng = np.random.default_rng(C["seed"] + rank)
 if not C["gbdt"]:
-    for t in range(T):  # Poisson(1) bag counts per (row, tree) (dt/DTWorker.java:1547-1571), injected
-        w.set_weights(t, rng.poisson(1.0, n_local).astype(np.float32))
+    for t in range(T):  # Poisson(1) bag counts per (row, tree) (dt/DTWorker.java:1547-1571), drawn on the device
+        w.sample_poisson(t, C["seed"], 1.0, row0=row0)
 load_s = time.time() - t0
 m = NativeMaster(cfg, tree_num=T + (1 if C["gbdt"] else 0), max_depth=C["depth"], is_gbdt=C["gbdt"], learning_rate=0.05,
                  feature_subset_strategy=C["fss"], feature_subset_rate=C["rate"], feature_sampling_seed=7,
