@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -728,7 +729,10 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                     h->launches_count += 1;
                 }
                 const int tiles_total = n_rt + n_wt;
-                const int target_chunks = (int)std::max<int64_t>(1, (148 * 2 + tiles_total - 1) / tiles_total);
+                static const int waves = [] { const char* e = getenv("SB_CHUNK_WAVES"); return e ? std::max(1, atoi(e)) : 2; }();
+                // every group ends with a partial chunk: leave room for those, or the launch spills into one more wave
+                const int64_t blocks_target = std::max<int64_t>(148 * waves - (int64_t)tiles_total * std::min(rgroups, 74), 74);
+                const int target_chunks = (int)std::max<int64_t>(1, blocks_target / tiles_total);
                 const int64_t chunk_rows = MAX_ROWS_PER_FLUSH;  // upper bound; integer counts: 2^18 rows * 1024 < 2^32 as well
                 const int max_chunks = (int)(n / chunk_rows + target_chunks + rgroups + 2);
                 const size_t scan_items = (size_t)rgroups * (size_t)rowlist_n_ranges(n) + 1;

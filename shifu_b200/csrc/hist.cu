@@ -171,7 +171,7 @@ __device__ __forceinline__ void flush_hist(const uint32_t* hist, int gcount, int
         if (off < 0) continue;
         const int64_t idx = off + (int64_t)bin * n_stats + stt;
         atomicAdd(reinterpret_cast<unsigned long long*>(raw_lo + idx), (unsigned long long)(v & 0xffffffffLL));
-        atomicAdd(reinterpret_cast<unsigned long long*>(raw_hi + idx), (unsigned long long)(v >> 32));
+        if ((v >> 32) != 0) atomicAdd(reinterpret_cast<unsigned long long*>(raw_hi + idx), (unsigned long long)(v >> 32));
     }
 }
 
