@@ -504,7 +504,9 @@ __device__ __forceinline__ void rows_consume(const HistRowsArgs& a, const RowOps
 #pragma unroll
             for (int j = 0; j < BATCH; ++j) {  // phase 1: operands, addresses, low-word atomics
                 const uint4 v0 = *reinterpret_cast<const uint4*>(&v[jb + j]);       // row, cnt_hi, slot, cnt_lo
-                const uint4 v1 = *reinterpret_cast<const uint4*>(&v[jb + j].q[0]);  // sum / sq words
+                uint4 v1;  // sum / sq words (VARIANCE) or the class byte offset (CLASS)
+                if (KIND == STAT_VARIANCE) v1 = *reinterpret_cast<const uint4*>(&v[jb + j].q[0]);
+                else v1 = make_uint4(v[jb + j].q[0], 0u, 0u, 0u);
                 const uint32_t slot = v0.z;
                 const bool rowok = (wr0 + jb + j < rows) && slot < (uint32_t)gcount;
                 uint32_t base = lane_base + slot * slot_stride;
@@ -516,14 +518,27 @@ __device__ __forceinline__ void rows_consume(const HistRowsArgs& a, const RowOps
                 const uint32_t rbase = rowok ? base : dummy_addr;
                 const uint32_t bmul = rowok ? bin_stride : 0u;
                 const uint32_t bwj = bw_cur[jb + j];
-                const uint32_t fm_row = (slot & (R_MAX_GS - 1)) * FPL;
+                // feature masks of the row's slot: the FPL words sit side by side, one vector load
+                uint32_t fmw[FPL];
+                if (!ALLF) {
+                    const uint32_t* fmp = fm_tab + (slot & (R_MAX_GS - 1)) * FPL;
+                    if (FPL == 4) {
+                        const uint4 t = *reinterpret_cast<const uint4*>(fmp);
+                        fmw[0] = t.x; fmw[1] = t.y; fmw[2] = t.z; fmw[3] = t.w;
+                    } else if (FPL == 2) {
+                        const uint2 t = *reinterpret_cast<const uint2*>(fmp);
+                        fmw[0] = t.x; fmw[1] = t.y;
+                    } else {
+                        fmw[0] = fmp[0];
+                    }
+                }
                 static_for(KS, [&](auto kc) {
                     constexpr int k = decltype(kc)::value;
                     constexpr uint32_t KO = 128u * k;
                     const uint32_t bin = (k == 3) ? (bwj >> 24) : ((bwj >> (8 * k)) & 0xffu);
                     uint32_t adr;
                     if (ALLF) adr = rbase + bin * bmul;
-                    else adr = (rowok && (fm_tab[fm_row + k] & lane_bit) != 0u) ? base + bin * bin_stride : dummy_addr;
+                    else adr = (rowok && (fmw[k] & lane_bit) != 0u) ? base + bin * bin_stride : dummy_addr;
                     ad[j][k] = adr;
                     if (KIND == STAT_VARIANCE) {
                         if (CNT_INT) {
