@@ -734,7 +734,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 const int64_t blocks_target = std::max<int64_t>(148 * waves - (int64_t)tiles_total * std::min(rgroups, 74), 74);
                 const int target_chunks = (int)std::max<int64_t>(1, blocks_target / tiles_total);
                 const int64_t chunk_rows = MAX_ROWS_PER_FLUSH;  // upper bound; integer counts: 2^18 rows * 1024 < 2^32 as well
-                const int max_chunks = (int)(n / chunk_rows + target_chunks + rgroups + 2);
+                const int max_chunks = (int)(n / chunk_rows + target_chunks + rgroups + 2 + 2 * 148);  // + up to two waves of rounding
                 const size_t scan_items = (size_t)rgroups * (size_t)rowlist_n_ranges(n) + 1;
                 SB_CUDA(h->rl_counts.reserve(2 * scan_items));
                 const size_t temp_bytes = rowlist_scan_temp_bytes((int64_t)scan_items);
@@ -750,7 +750,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 la.slot_of_node = a.slot_of_node; la.slot_table_size = a.slot_table_size; la.gs = rgs; la.n_groups = rgroups;
                 la.stats_size = h->stats_size; la.kind = h->stat_kind; la.cnt_int = cnt_int; la.scales = h->d_scales;
                 la.counts = h->rl_counts.p; la.scanned = h->rl_counts.p + scan_items;
-                la.temp = h->rl_temp.p; la.temp_bytes = temp_bytes; la.chunk_rows = chunk_rows; la.target_chunks = target_chunks;
+                la.temp = h->rl_temp.p; la.temp_bytes = temp_bytes; la.chunk_rows = chunk_rows; la.target_chunks = target_chunks; la.n_tiles = std::max(tiles_total, 1);
                 la.identity = (ns == 1 && lay.nodes[order[s0]].node_id == SB_ROOT_INDEX && partner[order[s0]] < 0) ? 1 : 0;
                 la.route = 0;
                 if (h->pending_route && !la.identity && tree_ranges.size() == 1 && h->cfg.is_gbdt) {

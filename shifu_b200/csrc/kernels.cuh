@@ -74,6 +74,7 @@ struct RowListArgs {
     int64_t chunk_rows;        // upper bound of rows per chunk (accumulator headroom)
     int identity;              // 1: no sort -- the list is all rows in storage order (single todo node that is a tree root)
     int target_chunks;         // the chunk size is chosen on the device so that about this many chunks result
+    int n_tiles;               // feature tiles per chunk (blocks = chunks x tiles)
     int64_t* offsets;          // [n_groups + 1]
     int32_t* chunk_group;      // [max_chunks]
     int64_t* chunk_begin;

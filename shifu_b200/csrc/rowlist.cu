@@ -161,7 +161,7 @@ rowlist_count_kernel(int64_t n, int32_t* __restrict__ node_id, const float* __re
 // the identity list (scanned == nullptr), a single group holding every row; then the chunk table: chunk c covers ops
 // [begin, end) of one group.
 __global__ void rowlist_chunks_kernel(const uint32_t* __restrict__ scanned, int64_t n_ranges, int64_t n, int n_groups,
-                                      int64_t max_chunk_rows, int target_chunks, int64_t* __restrict__ offsets,
+                                      int64_t max_chunk_rows, int target_chunks, int n_tiles, int64_t* __restrict__ offsets,
                                       int32_t* __restrict__ chunk_group, int64_t* __restrict__ chunk_begin,
                                       int64_t* __restrict__ chunk_end, int32_t* __restrict__ n_chunks, int max_chunks) {
     __shared__ int64_t off[257];
@@ -177,7 +177,19 @@ __global__ void rowlist_chunks_kernel(const uint32_t* __restrict__ scanned, int6
         // chunk size from the number of ACTIVE rows of this pass (with subtraction most passes touch a fraction of the
         // rows): about target_chunks chunks, so the grid fills the GPU several times over whatever the list length
         const int64_t total = off[n_groups];
-        int64_t chunk_rows = ((total + target_chunks - 1) / target_chunks + 127) / 128 * 128;
+        // number of chunks: at least what the accumulator headroom asks for (max_chunk_rows), about target_chunks, and
+        // such that chunks x tiles fills whole waves of 148 blocks (one block per SM) with room for the partial chunk
+        // that ends every group -- a launch of 2.6 waves costs 3
+        const int64_t k_min = (total + max_chunk_rows - 1) / max_chunk_rows;
+        int64_t k = k_min > target_chunks ? k_min : target_chunks;
+        if (k_min > target_chunks) {
+            const int64_t spare = n_groups < 74 ? n_groups : 74;
+            int64_t waves = (k * n_tiles + 147) / 148;
+            int64_t kw = (waves * 148) / n_tiles - spare;
+            if (kw < k_min) kw = ((waves + 1) * 148) / n_tiles - spare;
+            if (kw >= k_min) k = kw;
+        }
+        int64_t chunk_rows = ((total + k - 1) / k + 127) / 128 * 128;
         if (chunk_rows < 1024) chunk_rows = 1024;
         if (chunk_rows > max_chunk_rows) chunk_rows = max_chunk_rows;
         int c = 0;
@@ -330,7 +342,7 @@ cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s) {
     cudaError_t e;
     if (a.identity) {
         // no grouping: one group = all rows in storage order
-        rowlist_chunks_kernel<<<1, 256, 0, s>>>(nullptr, 0, n, 1, a.chunk_rows, a.target_chunks, a.offsets, a.chunk_group,
+        rowlist_chunks_kernel<<<1, 256, 0, s>>>(nullptr, 0, n, 1, a.chunk_rows, a.target_chunks, a.n_tiles, a.offsets, a.chunk_group,
                                                 a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
@@ -360,7 +372,7 @@ cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s) {
     size_t temp = a.temp_bytes;
     e = cub::DeviceScan::ExclusiveSum(a.temp, temp, (const uint32_t*)a.counts, a.scanned, items, s);
     if (e != cudaSuccess) return e;
-    rowlist_chunks_kernel<<<1, 256, 0, s>>>(a.scanned, n_ranges, n, a.n_groups, a.chunk_rows, a.target_chunks, a.offsets,
+    rowlist_chunks_kernel<<<1, 256, 0, s>>>(a.scanned, n_ranges, n, a.n_groups, a.chunk_rows, a.target_chunks, a.n_tiles, a.offsets,
                                             a.chunk_group, a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
