@@ -181,8 +181,12 @@ __global__ void rowlist_chunks_kernel(const uint32_t* __restrict__ scanned, int6
         // such that chunks x tiles fills whole waves of 148 blocks (one block per SM) with room for the partial chunk
         // that ends every group -- a launch of 2.6 waves costs 3
         const int64_t k_min = (total + max_chunk_rows - 1) / max_chunk_rows;
-        int64_t k = k_min > target_chunks ? k_min : target_chunks;
-        if (k_min > target_chunks) {
+        // target_chunks is about four waves; a short list takes two, so that zeroing and flushing a block's histogram
+        // stays small next to its rows
+        int64_t want = target_chunks;
+        if (total / want < 16384 && want >= 2) want /= 2;
+        int64_t k = k_min > want ? k_min : want;
+        if (k_min > want) {
             const int64_t spare = n_groups < 74 ? n_groups : 74;
             int64_t waves = (k * n_tiles + 147) / 148;
             int64_t kw = (waves * 148) / n_tiles - spare;
