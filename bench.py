@@ -141,6 +141,20 @@ def grow_tree(worker, master, it, e2e_buffers=None):
     return it, passes, scalars
 
 
+def measured_traffic(a, rows_local):
+    """dram__bytes_read + dram__bytes_write per launch of the histogram kernel, from the committed ncu --set full capture
+    of this very workload (profiles/r01_hist_rows_traffic.json: mean over the 7 passes of a tree at 100M rows on one
+    GPU), scaled to this rank's share of the rows.  None for any other shape."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_hist_rows_traffic.json")
+    try:
+        t = json.load(open(path))
+    except Exception:
+        return None
+    if (a.rows, a.features, a.bins, a.depth) != (t.get("rows"), 200, 64, 8):
+        return None
+    return t["mean_dram_bytes_per_launch"] * rows_local / t["rows"]
+
+
 def run_b200(a):
     import torch
     from shifu_b200.capi import ConfigArrays, NativeMaster, Worker
@@ -264,7 +278,7 @@ def run_b200(a):
         "hist_ms_per_pass": avg_hist_ms,
         "hist_share_of_step": hist_ms / ms,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_kind,
+                     "traffic": measured_traffic(a, rows_local), "peak_source": peak_kind,
                      "algorithmic_bytes_per_launch": algo_bytes,
                      "note": "average over the passes of the timed trees (levels 1..%d); see DESIGN.md for the shared-memory atomic ceiling" % (a.depth - 1)},
         "e2e": {"value": e2e_value, "unit": "rows*features/s",
