@@ -7,3 +7,5 @@ SRC="shifu_b200/csrc/api.cu shifu_b200/csrc/rowlist.cu shifu_b200/csrc/hist.cu s
 $NVCC -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -fmad=false \
     -Xcompiler -fPIC,-fvisibility=hidden -shared -o shifu_b200/libshifu_b200.so $SRC "$@"
 make -s -C oracle
+# a host program on the bare C ABI (no Python): see tools/train_gbt.cpp
+g++ -O2 -std=c++17 -o tools/train_gbt tools/train_gbt.cpp -Lshifu_b200 -lshifu_b200 -Wl,-rpath,'$ORIGIN/../shifu_b200'

@@ -73,3 +73,19 @@ def test_product_never_imports_oracle():
                 low = line.lower()
                 if "oracle" in low:
                     assert not any(k in low for k in ("import", "#include", "cdll", "dlopen", "liboracle")), (f, line)
+
+
+def test_cpp_host_program_on_the_bare_c_abi():
+    """tools/train_gbt.cpp uses only include/shifu_b200.h.  Without a GPU it must stop with the library's own error
+    (no CPU fallback); with one it grows its trees."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "tools", "train_gbt")
+    if not os.path.exists(exe):
+        subprocess.check_call(["bash", os.path.join(root, "build.sh")])
+    p = subprocess.run([exe, "20000", "12", "16", "2", "4"], capture_output=True, text=True, timeout=300)
+    if p.returncode == 0:
+        assert "2 trees grown" in p.stdout
+    else:
+        assert "no CUDA device: shifu_b200 has no CPU fallback" in p.stderr
