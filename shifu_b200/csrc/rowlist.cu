@@ -163,7 +163,8 @@ rowlist_count_kernel(int64_t n, int32_t* __restrict__ node_id, const float* __re
 __global__ void rowlist_chunks_kernel(const uint32_t* __restrict__ scanned, int64_t n_ranges, int64_t n, int n_groups,
                                       int64_t max_chunk_rows, int target_chunks, int n_tiles, int64_t* __restrict__ offsets,
                                       int32_t* __restrict__ chunk_group, int64_t* __restrict__ chunk_begin,
-                                      int64_t* __restrict__ chunk_end, int32_t* __restrict__ n_chunks, int max_chunks) {
+                                      int64_t* __restrict__ chunk_end, int32_t* __restrict__ n_chunks, int max_chunks,
+                                      uint32_t* error_flag) {
     __shared__ int64_t off[257];
     for (int g = threadIdx.x; g <= n_groups; g += blockDim.x) {
         int64_t v;
@@ -198,7 +199,11 @@ __global__ void rowlist_chunks_kernel(const uint32_t* __restrict__ scanned, int6
         if (chunk_rows > max_chunk_rows) chunk_rows = max_chunk_rows;
         int c = 0;
         for (int g = 0; g < n_groups; ++g)
-            for (int64_t b = off[g]; b < off[g + 1] && c < max_chunks; b += chunk_rows) {
+            for (int64_t b = off[g]; b < off[g + 1]; b += chunk_rows) {
+                if (c >= max_chunks) {  // cannot happen with the host's bound; never drop rows silently
+                    atomicOr(error_flag, 8u);
+                    break;
+                }
                 chunk_group[c] = g;
                 chunk_begin[c] = b;
                 chunk_end[c] = min(off[g + 1], b + chunk_rows);
@@ -347,7 +352,7 @@ cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s) {
     if (a.identity) {
         // no grouping: one group = all rows in storage order
         rowlist_chunks_kernel<<<1, 256, 0, s>>>(nullptr, 0, n, 1, a.chunk_rows, a.target_chunks, a.n_tiles, a.offsets, a.chunk_group,
-                                                a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks);
+                                                a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks, a.error_flag);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
         int64_t g = (n + TPB - 1) / TPB;
@@ -377,7 +382,7 @@ cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s) {
     e = cub::DeviceScan::ExclusiveSum(a.temp, temp, (const uint32_t*)a.counts, a.scanned, items, s);
     if (e != cudaSuccess) return e;
     rowlist_chunks_kernel<<<1, 256, 0, s>>>(a.scanned, n_ranges, n, a.n_groups, a.chunk_rows, a.target_chunks, a.n_tiles, a.offsets,
-                                            a.chunk_group, a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks);
+                                            a.chunk_group, a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks, a.error_flag);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
 #define SCATTER(K, C)                                                                                                     \
