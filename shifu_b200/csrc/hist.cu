@@ -142,36 +142,39 @@ template <int KIND, int CNT_INT, int LW>
 __device__ __forceinline__ void flush_hist(const uint32_t* hist, int gcount, int g0, int bins_pad, int nw, int n_stats,
                                            int cnt_shift, const int32_t* tile_feats, const int64_t* pair_off,
                                            int n_features, int64_t* raw_lo, int64_t* raw_hi, int nthreads) {
-    // LW = features (words) per histogram word row: 32*FPL laid out [k][lane], or 8 for the wide-feature kernel
-    const int per_slot = bins_pad * n_stats * LW;    // 64-bit statistics per slot
-    for (int i = threadIdx.x; i < gcount * per_slot; i += nthreads) {
-        const int l = i % LW;                        // k * 32 + lane
-        int t = i / LW;
-        const int stt = t % n_stats;
-        t /= n_stats;
-        const int bin = t % bins_pad;
-        const int sl = t / bins_pad;
-        const uint32_t* pb = hist + ((sl * bins_pad + bin) * nw) * LW + l;
-        long long v;
-        if (KIND == STAT_VARIANCE) {
-            if (CNT_INT) {
-                if (stt == 0) v = (long long)((unsigned long long)pb[0] << cnt_shift);
-                else v = (long long)(((unsigned long long)pb[(2 * stt) * LW] << 32) | pb[(2 * stt - 1) * LW]);
-            } else {
-                v = (long long)(((unsigned long long)pb[(2 * stt + 1) * LW] << 32) | pb[(2 * stt) * LW]);
-            }
-        } else {
-            if (CNT_INT) v = (long long)((unsigned long long)pb[stt * LW] << cnt_shift);
-            else v = (long long)(((unsigned long long)pb[(2 * stt + 1) * LW] << 32) | pb[(2 * stt) * LW]);
-        }
-        if (v == 0) continue;
-        const int f = tile_feats[l];
-        if (f < 0) continue;
+    // LW = features (words) per histogram word row: 32*FPL laid out [k][lane], or 8 for the wide-feature kernel.
+    // A thread owns one column l (one feature) and every (nthreads / LW)-th (bin, statistic) of it, so the feature id
+    // and the block offset are loaded once per slot instead of once per entry: the loop body is shared-memory reads
+    // and fire-and-forget RED.ADD.64, no dependent global load.
+    const int groups = nthreads / LW;
+    const int l = threadIdx.x % LW, q = threadIdx.x / LW;
+    if (q >= groups) return;
+    const int f = tile_feats[l];
+    if (f < 0) return;
+    const int per_slot = bins_pad * n_stats;
+    for (int sl = 0; sl < gcount; ++sl) {
         const int64_t off = pair_off[(size_t)(g0 + sl) * n_features + f];
         if (off < 0) continue;
-        const int64_t idx = off + (int64_t)bin * n_stats + stt;
-        atomicAdd(reinterpret_cast<unsigned long long*>(raw_lo + idx), (unsigned long long)(v & 0xffffffffLL));
-        if ((v >> 32) != 0) atomicAdd(reinterpret_cast<unsigned long long*>(raw_hi + idx), (unsigned long long)(v >> 32));
+        for (int e = q; e < per_slot; e += groups) {
+            const int bin = e / n_stats, stt = e - bin * n_stats;
+            const uint32_t* pb = hist + ((sl * bins_pad + bin) * nw) * LW + l;
+            long long v;
+            if (KIND == STAT_VARIANCE) {
+                if (CNT_INT) {
+                    if (stt == 0) v = (long long)((unsigned long long)pb[0] << cnt_shift);
+                    else v = (long long)(((unsigned long long)pb[(2 * stt) * LW] << 32) | pb[(2 * stt - 1) * LW]);
+                } else {
+                    v = (long long)(((unsigned long long)pb[(2 * stt + 1) * LW] << 32) | pb[(2 * stt) * LW]);
+                }
+            } else {
+                if (CNT_INT) v = (long long)((unsigned long long)pb[stt * LW] << cnt_shift);
+                else v = (long long)(((unsigned long long)pb[(2 * stt + 1) * LW] << 32) | pb[(2 * stt) * LW]);
+            }
+            if (v == 0) continue;
+            const int64_t idx = off + (int64_t)bin * n_stats + stt;
+            atomicAdd(reinterpret_cast<unsigned long long*>(raw_lo + idx), (unsigned long long)(v & 0xffffffffLL));
+            if ((v >> 32) != 0) atomicAdd(reinterpret_cast<unsigned long long*>(raw_hi + idx), (unsigned long long)(v >> 32));
+        }
     }
 }
 
