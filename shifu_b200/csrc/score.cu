@@ -4,8 +4,8 @@
 // One thread scores one row.  The rows of a block are staged in shared memory with coalesced loads (a data row is
 // read by one thread, column after column, as the trees ask for them).  The model is re-laid out at creation: every
 // tree in pre-order (the left child of node i is node i + 1), 16 bytes per node {threshold | leaf value | bitset
-// reference, right child, column, flags}, so a step of the walk is one 16-byte read-only load that hits L1 (100 trees
-// of the reference's fixture = 69 KB; half of the SM's L1/shared array is left to L1 for it).  The walk and the
+// reference, right child, column, flags}, so a step of the walk is one 16-byte load -- from shared memory when the
+// nodes fit there beside the rows (100 trees of the reference's fixture = 69 KB), else through L1.  The walk and the
 // accumulation follow the reference's loop order in fp64 without contraction (-fmad=false), so raw and cut-off
 // scores are bit-identical to the Java loop; the sigmoid converts go through exp().
 #include <algorithm>
@@ -58,10 +58,12 @@ __device__ __forceinline__ bool java_compare_lt(double a, double b) {
 }
 
 // predictNode (dt/IndependentTreeModel.java:516-560); returns the value of the node it stops at
-template <class RowReader>
+template <bool NODES_IN_SMEM, class RowReader>
 __device__ __forceinline__ double predict_node(const ScoreView& m, int node, const RowReader& row, uint32_t* error_flag) {
     while (true) {
-        const int4 raw = __ldg(reinterpret_cast<const int4*>(m.nodes + node));
+        int4 raw;
+        if (NODES_IN_SMEM) raw = *reinterpret_cast<const int4*>(m.nodes + node);  // m.nodes points into shared memory
+        else raw = __ldg(reinterpret_cast<const int4*>(m.nodes + node));
         const double nvalue = __hiloint2double(raw.y, raw.x);
         const uint32_t flags = (uint32_t)raw.w >> 16;
         if (!(flags & PN_WALK)) return nvalue;  // split == null or isRealLeaf()
@@ -97,10 +99,10 @@ __device__ __forceinline__ double convert_score(int convert, double predict) {
     return predict;
 }
 
-template <class RowReader>
+template <bool NODES_IN_SMEM, class RowReader>
 __device__ __forceinline__ void score_row(const ScoreView& m, const RowReader& row, double* out, uint32_t* error_flag) {
     if (m.is_classification) {  // computeClassificationScore (:365-379): every tree's class value
-        for (int t = 0; t < m.n_trees; ++t) out[t] = predict_node(m, m.tree_root[t], row, error_flag);
+        for (int t = 0; t < m.n_trees; ++t) out[t] = predict_node<NODES_IN_SMEM>(m, m.tree_root[t], row, error_flag);
         return;
     }
     double final_predict = 0.0;
@@ -108,12 +110,12 @@ __device__ __forceinline__ void score_row(const ScoreView& m, const RowReader& r
         if (m.is_gbdt) {  // :390-420
             double predict = 0.0;
             for (int t = m.bag_begin[b]; t < m.bag_begin[b + 1]; ++t)
-                predict += predict_node(m, m.tree_root[t], row, error_flag) * m.weights[t];
+                predict += predict_node<NODES_IN_SMEM>(m, m.tree_root[t], row, error_flag) * m.weights[t];
             final_predict += convert_score(m.convert, predict);
         } else {          // :423-441
             double predict_sum = 0.0, weight_sum = 0.0;
             for (int t = m.bag_begin[b]; t < m.bag_begin[b + 1]; ++t) {
-                const double score = predict_node(m, m.tree_root[t], row, error_flag);
+                const double score = predict_node<NODES_IN_SMEM>(m, m.tree_root[t], row, error_flag);
                 const double weight = m.weights[t];
                 weight_sum += weight;
                 predict_sum += score * weight;
@@ -133,28 +135,40 @@ struct GlobalRow {
     __device__ __forceinline__ double operator()(int c) const { return __ldg(p + c); }
 };
 
-// STAGED: the block's SC_ROWS x n_columns doubles are copied to shared memory first (contiguous in global memory:
+// STAGED: the block's rows x n_columns doubles are copied to shared memory first (contiguous in global memory:
 // fully coalesced), each row at an odd stride so that the threads of a warp reading "their" column hit distinct banks.
-template <bool STAGED>
-__global__ void __launch_bounds__(SC_ROWS) score_kernel(ScoreView m, const double* __restrict__ data, int64_t n_rows,
-                                                       double* __restrict__ scores, uint32_t* error_flag) {
-    extern __shared__ double tile[];
-    const int64_t r0 = (int64_t)blockIdx.x * SC_ROWS;
+// NODES_IN_SMEM: the packed nodes are copied to shared memory as well.  The 32 lanes of a warp sit in 32 different nodes,
+// so through L1 a step of the walk is 32 tag lookups (measured 1.1 node visits per cycle and SM); in shared memory it
+// is a few bank conflicts.  Used when nodes + rows fit one block's shared memory.
+template <bool STAGED, bool NODES_IN_SMEM>
+__global__ void score_kernel(ScoreView m, const double* __restrict__ data, int64_t n_rows, double* __restrict__ scores,
+                             uint32_t* error_flag) {
+    extern __shared__ __align__(16) unsigned char score_smem[];
+    const int rows_per_block = blockDim.x;
+    double* tile = reinterpret_cast<double*>(score_smem);
+    if (NODES_IN_SMEM) {
+        int4* dst = reinterpret_cast<int4*>(score_smem);
+        const int4* src = reinterpret_cast<const int4*>(m.nodes);
+        for (int i = threadIdx.x; i < m.n_nodes; i += blockDim.x) dst[i] = __ldg(src + i);
+        m.nodes = reinterpret_cast<const PackedNode*>(score_smem);
+        tile = reinterpret_cast<double*>(score_smem + (size_t)m.n_nodes * sizeof(PackedNode));
+    }
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
     const int64_t r = r0 + threadIdx.x;
     const int out_per_row = m.is_classification ? m.n_trees : 1;
     if (STAGED) {
         const int stride = m.n_columns | 1;
-        const int64_t rows_here = min((int64_t)SC_ROWS, n_rows - r0);
+        const int64_t rows_here = min((int64_t)rows_per_block, n_rows - r0);
         const int64_t total = rows_here * m.n_columns;
         const double* src = data + r0 * m.n_columns;
-        for (int64_t i = threadIdx.x; i < total; i += SC_ROWS) {
+        for (int64_t i = threadIdx.x; i < total; i += rows_per_block) {
             const int rr = (int)(i / m.n_columns), c = (int)(i - (int64_t)rr * m.n_columns);
             tile[rr * stride + c] = src[i];
         }
         __syncthreads();
-        if (r < n_rows) score_row(m, SmemRow{tile + threadIdx.x * stride}, scores + r * out_per_row, error_flag);
+        if (r < n_rows) score_row<NODES_IN_SMEM>(m, SmemRow{tile + threadIdx.x * stride}, scores + r * out_per_row, error_flag);
     } else {
-        if (r < n_rows) score_row(m, GlobalRow{data + r * m.n_columns}, scores + r * out_per_row, error_flag);
+        if (r < n_rows) score_row<false>(m, GlobalRow{data + r * m.n_columns}, scores + r * out_per_row, error_flag);
     }
 }
 
@@ -322,20 +336,31 @@ SB_API int sb_scorer_score(sb_scorer* s, int64_t n_rows, const double* data, int
         s->scores_cap = n_out;
     }
     SB_CUDA(cudaMemsetAsync(s->d_error, 0, 4, 0));
-    const unsigned grid = (unsigned)((n_rows + SC_ROWS - 1) / SC_ROWS);
+    // shared memory per block: rows x (n_columns | 1) doubles, plus the packed nodes when both fit
+    const size_t budget = 220 * 1024;
+    const size_t row_bytes = (size_t)(v.n_columns | 1) * 8;
+    const size_t node_bytes = (size_t)v.n_nodes * sizeof(PackedNode);
+    static bool attr_set = false;
+    if (!attr_set) {
+        SB_CUDA(cudaFuncSetAttribute(score_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        SB_CUDA(cudaFuncSetAttribute(score_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        // nodes read through L1: leave half of the L1/shared array to L1
+        SB_CUDA(cudaFuncSetAttribute(score_kernel<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 50));
+        attr_set = true;
+    }
     SB_CUDA(cudaEventRecord(s->e0, 0));
-    if (v.n_columns <= SC_MAX_SMEM_COLS) {
-        const size_t smem = (size_t)SC_ROWS * (v.n_columns | 1) * 8;
-        static bool attr_set = false;
-        if (!attr_set) {
-            SB_CUDA(cudaFuncSetAttribute(score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-            // leave half of the L1/shared array to L1: the packed model is re-read by every thread
-            SB_CUDA(cudaFuncSetAttribute(score_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 50));
-            attr_set = true;
-        }
-        score_kernel<true><<<grid, SC_ROWS, smem, 0>>>(v, d_in, n_rows, s->d_scores, s->d_error);
+    int rows_per_block = 0;
+    for (int t : {512, 256, 128})
+        if (node_bytes + (size_t)t * row_bytes <= budget) { rows_per_block = t; break; }
+    if (rows_per_block > 0 && node_bytes <= 110 * 1024) {
+        const unsigned grid = (unsigned)((n_rows + rows_per_block - 1) / rows_per_block);
+        score_kernel<true, true><<<grid, rows_per_block, node_bytes + (size_t)rows_per_block * row_bytes, 0>>>(v, d_in, n_rows, s->d_scores, s->d_error);
+    } else if (v.n_columns <= SC_MAX_SMEM_COLS) {
+        const unsigned grid = (unsigned)((n_rows + SC_ROWS - 1) / SC_ROWS);
+        score_kernel<true, false><<<grid, SC_ROWS, (size_t)SC_ROWS * row_bytes, 0>>>(v, d_in, n_rows, s->d_scores, s->d_error);
     } else {
-        score_kernel<false><<<grid, SC_ROWS, 0, 0>>>(v, d_in, n_rows, s->d_scores, s->d_error);
+        const unsigned grid = (unsigned)((n_rows + SC_ROWS - 1) / SC_ROWS);
+        score_kernel<false, false><<<grid, SC_ROWS, 0, 0>>>(v, d_in, n_rows, s->d_scores, s->d_error);
     }
     SB_CUDA(cudaGetLastError());
     SB_CUDA(cudaEventRecord(s->e1, 0));
