@@ -334,6 +334,7 @@ int upload_tree(sb_handle* h, const sb_tree& t, DeviceTree& d) {
 // dt/DTWorker.java:903-929 initTodoNodeStats: sizes and order of the statistics buffer.
 int build_layout(const sb_handle* h, const sb_iter_in* in, TodoLayout& lay) {
     lay.nodes.clear();
+    lay.nodes.reserve((size_t)std::max(in->n_todo, 0));
     int64_t off = 0;
     for (int i = 0; i < in->n_todo; ++i) {
         const sb_todo_node& t = in->todo[i];
@@ -342,6 +343,7 @@ int build_layout(const sb_handle* h, const sb_iter_in* in, TodoLayout& lay) {
         if (t.n_features == 0) nd.features.assign(h->all_features.begin(), h->all_features.end());
         else nd.features.assign(t.features, t.features + t.n_features);
         int64_t l = 0;
+        nd.feat_off.reserve(nd.features.size());
         for (int f : nd.features) {
             if (f < 0 || f >= h->cfg.n_features) return fail(SB_ERR_INVALID, "todo node feature slot out of range");
             nd.feat_off.push_back(l);
@@ -582,16 +584,15 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 rfm[((size_t)s * n_rt + t) * fpl + rel % fpl] |= 1u << (rel / fpl);
             }
         }
+        // allf: every slot takes every feature that lives in a launched tile
+        std::vector<uint32_t> full((size_t)n_rt * fpl, 0u);
+        for (int t = 0; t < n_rt; ++t)
+            for (int f = rt_slot0[t]; f < std::min(F, rt_slot0[t] + tw); ++f) {
+                const int rel = pos_of[f] - rt_slot0[t];
+                full[(size_t)t * fpl + rel % fpl] |= 1u << (rel / fpl);
+            }
         for (int s = 0; s < S && allf; ++s)
-            for (int t = 0; t < n_rt && allf; ++t)
-                for (int k = 0; k < fpl && allf; ++k) {
-                    uint32_t full = 0;  // every feature that lives in this (tile, k)
-                    for (int f = rt_slot0[t]; f < std::min(F, rt_slot0[t] + tw); ++f) {
-                        const int rel = pos_of[f] - rt_slot0[t];
-                        if (rel % fpl == k) full |= 1u << (rel / fpl);
-                    }
-                    if (rfm[((size_t)s * n_rt + t) * fpl + k] != full) allf = 0;
-                }
+            if (memcmp(&rfm[(size_t)s * n_rt * fpl], full.data(), full.size() * 4) != 0) allf = 0;
         SB_CUDA(h->rt_tiles.reserve(rt_feats.size() + 2 * rt_slot0.size()));
         SB_CUDA(h->rt_fmask.reserve(rfm.size()));
         SB_CUDA(cudaMemcpyAsync(h->rt_tiles.p, rt_feats.data(), rt_feats.size() * 4, cudaMemcpyHostToDevice, h->stream));
