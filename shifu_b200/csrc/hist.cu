@@ -472,7 +472,10 @@ __device__ __forceinline__ void rows_consume(const HistRowsArgs& a, const RowOps
 
     // The bins of tile it+1 are requested before the atomics of tile it are issued, so the global-load latency
     // of one tile hides behind the shared-memory work of the previous one.
-    uint32_t bw_cur[RPW], bw_next[RPW];
+    // Class statistics cost one atomic per cell, so a tile is consumed faster than a global load returns: their bins are
+    // requested two tiles ahead (PF2), the variance statistics' one tile ahead.
+    constexpr bool PF2 = KIND != STAT_VARIANCE;
+    uint32_t bw_cur[RPW], bw_next[RPW], bw_next2[PF2 ? RPW : 1];
     auto fetch_bins = [&](int it, uint32_t (&bw)[RPW]) {
         const int s = it % R_NST;
         mbar_wait(&st[s].full, (uint32_t)((it / R_NST) & 1));
@@ -490,9 +493,14 @@ __device__ __forceinline__ void rows_consume(const HistRowsArgs& a, const RowOps
         }
     };
     if (n_iters > 0) fetch_bins(0, bw_cur);
+    if (PF2 && n_iters > 1) fetch_bins(1, bw_next);
     for (int it = 0; it < n_iters; ++it) {
         const int s = it % R_NST;
-        if (it + 1 < n_iters) fetch_bins(it + 1, bw_next);
+        if (PF2) {
+            if (it + 2 < n_iters) fetch_bins(it + 2, reinterpret_cast<uint32_t (&)[RPW]>(bw_next2));
+        } else {
+            if (it + 1 < n_iters) fetch_bins(it + 1, bw_next);
+        }
         const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
         const RowOps* v = ops_s + s * R_TILE + wr0;
 #pragma unroll
@@ -583,7 +591,10 @@ __device__ __forceinline__ void rows_consume(const HistRowsArgs& a, const RowOps
         __syncwarp();
         if (lane == 0) mbar_arrive(&st[s].empty);
 #pragma unroll
-        for (int j = 0; j < RPW; ++j) bw_cur[j] = bw_next[j];
+        for (int j = 0; j < RPW; ++j) {
+            bw_cur[j] = bw_next[j];
+            if (PF2) bw_next[j] = bw_next2[j];
+        }
     }
 }
 
