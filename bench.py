@@ -41,6 +41,7 @@ def parse():
     ap.add_argument("--depth", type=int, default=8)
     ap.add_argument("--cpu-sample-rows", type=int, default=1_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--flags", type=int, default=0, help="sb_config.flags (SB_FLAG_*), for A/B runs")
     return ap.parse_args()
 
 
@@ -174,7 +175,7 @@ def run_b200(a):
 
     n_trees_total = a.warmup + a.steps + a.steps + 2
     cfg = ConfigArrays([a.bins] * a.features, max_depth=a.depth, tree_num=n_trees_total, learning_rate=0.05,
-                       min_instances_per_node=5, device=local_rank)
+                       min_instances_per_node=5, device=local_rank, flags=a.flags)
     worker = Worker(cfg)
     worker.load_synthetic(rows_local, seed=SEED, row0=row0, label_kind=0)
     if dist_ctx is not None:

@@ -237,8 +237,11 @@ SB_API int sb_sample_weights_stratified(sb_handle* h, int32_t w_index, int64_t s
 SB_API int sb_sample_poisson(sb_handle* h, int32_t w_index, uint64_t seed, double rate, int64_t row0);
 /* DTWorker.getBinIndex (dt/DTWorker.java:1001-1034) for a whole numeric column: values (device, n floats; NaN counts as
    0f like DTWorker.getFloatValue :1299-1305) -> bin indices (device, uint8 if out_width == 1 else uint16).
-   bin_boundary is a HOST array of n_bins (<= 4096) doubles.  A value below the first boundary gets the all-ones
-   index (the reference returns -1), which sb_load_rows rejects.  Handle-free; runs on cuda_stream (NULL = default). */
+   bin_boundary is a HOST array of n_bins (<= 4096) doubles; it is copied into a per-call device table allocated and
+   freed in stream order (cudaMallocAsync), so calls on different streams or host threads are independent; pinned host
+   memory must stay valid until the stream reaches the copy.  A value below the first boundary gets the all-ones index
+   (the reference returns -1), which sb_load_rows rejects -- for that reason 256 bins need out_width == 2.
+   Handle-free; runs on cuda_stream (NULL = default). */
 SB_API int sb_bin_values(const float* values, int64_t n, const double* bin_boundary, int32_t n_bins, void* bins_out,
                          int32_t out_width, void* cuda_stream);
 /* Reads back per-row state (any pointer may be NULL): Data.predict, Data.output, current node id of

@@ -92,7 +92,8 @@ struct sb_handle {
     // histogram subtraction: the previous pass's merged accumulators and layout stay around for one pass
     DevBuf<int64_t> raw_prev;
     TodoLayout prev_layout;
-    bool prev_valid = false;
+    bool prev_valid = false;   // raw_prev / prev_layout hold the merged accumulators of the last FINISHED pass
+    bool use_prev = false;     // this pass may derive children from them (prev_valid as seen when the pass began)
     bool enable_subtraction = true;
     std::vector<PairDesc> pairs;
     DevBuf<PairDesc> d_pairs;
@@ -212,6 +213,9 @@ int refresh_cnt_int(sb_handle* h) {
     h->cnt_int = (flag & 1u) == 0;
     h->weights_all_one = (flag & 2u) == 0;  // then the weight arrays need not be read at all (x * 1.0f == x)
     h->weights_version += 1;  // every caller changed (or loaded) sample weights
+    // the previous pass's accumulators were built with the old weights: a child must not be derived from them
+    h->prev_valid = false;
+    h->use_prev = false;
     return SB_OK;
 }
 
@@ -397,7 +401,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     h->pairs.clear();
     h->pair_max_len = 0;
     std::vector<int> pair_parent_prev;            // per pair: index into prev_layout
-    if (h->enable_subtraction && h->prev_valid) {
+    if (h->enable_subtraction && h->use_prev) {
         std::map<std::pair<int, int>, int> cur_idx, prev_idx;
         for (int i = 0; i < S_all; ++i) cur_idx[{lay.nodes[i].tree_id, lay.nodes[i].node_id}] = i;
         for (size_t i = 0; i < h->prev_layout.nodes.size(); ++i)
@@ -479,6 +483,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
 
     const int cnt_int = h->cnt_int ? 1 : 0;
     const int nw = hist_words_per_bin(h->stat_kind, cnt_int, h->stats_size);
+    const int nw_rows = hist_rows_words_per_bin(h->stat_kind, cnt_int, h->stats_size);  // hist_rows_kernel (limb layout)
     const int max_gs = hist_max_slots_per_block(bins_pad, nw);
     if (max_gs < 1) return fail(SB_ERR_UNSUPPORTED, "one node's histogram tile does not fit in shared memory");
 
@@ -529,7 +534,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     const bool rows_enabled = h->enable_row_lists && h->train.n < (int64_t)0xffffffff;
     if (rows_enabled && n_tiles > 0) {
         for (int f : {4, 2, 1}) {
-            rows_max_gs = hist_rows_max_slots_per_block(bins_pad, nw, f);
+            rows_max_gs = hist_rows_max_slots_per_block(bins_pad, nw_rows, f);
             if (rows_max_gs >= 1) { fpl = f; break; }
         }
     }
@@ -794,7 +799,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                     }
                 }
                 L.grid = max_chunks * std::max(n_rt, 1);
-                L.smem = L.has_narrow ? hist_rows_smem_bytes(rgs, bins_pad, nw, fpl) : 0;
+                L.smem = L.has_narrow ? hist_rows_smem_bytes(rgs, bins_pad, nw_rows, fpl) : 0;
                 if (any_wide) {
                     L.has_wide = true;
                     L.wide = ra;
@@ -1297,6 +1302,10 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     SB_CUDA(cudaSetDevice(h->cfg.device));
     h->begun = false;
     h->stats_ready = false;
+    // A pass that does not reach finish_check (an error, or a second begin) must not leave the next one pairing its
+    // children with accumulators of an older pass: the claim is renewed only by a finished pass.
+    h->use_prev = h->prev_valid;
+    h->prev_valid = false;
     int rc = build_layout(h, in, h->layout);
     if (rc != SB_OK) return rc;
     const int64_t total = h->layout.total;
@@ -1421,7 +1430,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
             SB_CUDA(launch_route(tr.d_col, h->d_feat_bins, tr.n, nid, v, h->d_error_flag, h->stream));
             ErrArgs e{};
             e.n = tr.n; e.label = tr.label; e.predict = tr.predict; e.significance = tr.significance;
-            e.weights = tr.weights + (int64_t)tree.tree_id * tr.n;  // [treeId], no modulo (:592)
+            e.weights = tr.weights ? tr.weights + (int64_t)tree.tree_id * tr.n : nullptr;  // [treeId], no modulo (:592); adopted rows without weights: all 1
             e.node_id = nid; e.tree = v; e.from_tree = 1; e.loss = loss; e.is_validation = 0; e.rf_oob = 1;
             SB_CUDA(launch_errors(e, h->d_err_scratch, h->d_acc, h->stream));
             h->launches_count += 2;

@@ -18,6 +18,8 @@
 //     The only word that must start at zero (the finish ticket) is cleared on the stream before each launch; the
 //     per-block partials are fully overwritten before they are read.  Two calls that overlap on the GPU (different
 //     streams, different threads) race on the array and produce garbage: serialise them.
+#include <atomic>
+
 #include "common.cuh"
 
 namespace {
@@ -97,7 +99,9 @@ __global__ void __launch_bounds__(NA_TPB) error_sums_static_kernel(int64_t n, co
 }
 
 constexpr int MAX_DEVICES = 64;
-double* g_scratch_addr[MAX_DEVICES];  // device address of g_static_scratch, per device ordinal (0 = not looked up yet)
+// device address of g_static_scratch, per device ordinal (null = not looked up yet).  Atomic because the first call on a
+// device may come from two host threads at once (a monitor thread beside the trainer); both would store the same address.
+std::atomic<double*> g_scratch_addr[MAX_DEVICES];
 
 }  // namespace
 
@@ -113,14 +117,14 @@ extern "C" SB_API int sb_error_sums_static(const float* label, const float* pred
     int dev = -1;
     SB_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= MAX_DEVICES) return sb::fail(SB_ERR_UNSUPPORTED, "sb_error_sums_static: device ordinal beyond 63");
-    if (!g_scratch_addr[dev]) {
+    if (!g_scratch_addr[dev].load(std::memory_order_relaxed)) {
         // one-time set-up for this device, with this device current (the caller made it current)
         double* p = nullptr;
         SB_CUDA(cudaGetSymbolAddress((void**)&p, g_static_scratch));
         if (!p) return sb::fail(SB_ERR_CUDA, "sb_error_sums_static: cudaGetSymbolAddress returned a null address");
-        g_scratch_addr[dev] = p;
+        g_scratch_addr[dev].store(p, std::memory_order_relaxed);
     }
-    double* scratch = g_scratch_addr[dev];
+    double* scratch = g_scratch_addr[dev].load(std::memory_order_relaxed);
     if (n_rows == 0) {
         SB_CUDA(cudaMemsetAsync(out, 0, 2 * sizeof(double), stream));
         return SB_OK;

@@ -10,10 +10,15 @@
 namespace {
 
 constexpr int MAX_BOUNDARIES = 4096;
-__constant__ double c_boundaries[MAX_BOUNDARIES];
 
 // getBinIndex: NaN is mapped to 0f first, as DTWorker.getFloatValue does for unparsable input (:1299-1305).
-__global__ void bin_values_kernel(const float* __restrict__ values, int64_t n, int n_bins, void* out, int out_width) {
+// The boundaries of the column are staged in shared memory once per block (<= 32 KB): every thread then bisects
+// over on-chip data, and two columns binned at the same time on different streams share nothing.
+__global__ void bin_values_kernel(const float* __restrict__ values, int64_t n, const double* __restrict__ boundaries,
+                                  int n_bins, void* out, int out_width) {
+    extern __shared__ double c_boundaries[];
+    for (int i = threadIdx.x; i < n_bins; i += blockDim.x) c_boundaries[i] = boundaries[i];
+    __syncthreads();
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         float v = values[i];
         if (isnan(v)) v = 0.0f;
@@ -182,12 +187,24 @@ extern "C" SB_API int sb_bin_values(const float* values, int64_t n, const double
     if (n_bins < 1 || n_bins > MAX_BOUNDARIES) return sb::fail(SB_ERR_RANGE, "sb_bin_values: between 1 and 4096 boundaries are supported");
     if (out_width != 1 && out_width != 2) return sb::fail(SB_ERR_INVALID, "sb_bin_values: out_width must be 1 (uint8) or 2 (uint16)");
     if (out_width == 1 && n_bins > 256) return sb::fail(SB_ERR_INVALID, "sb_bin_values: more than 256 bins need uint16 output");
+    // The reference's -1 (value below the first boundary) is stored as the all-ones index so that sb_load_rows can
+    // reject it; with 256 bins in uint8 that index would be the valid bin 255.
+    if (out_width == 1 && n_bins == 256) return sb::fail(SB_ERR_INVALID, "sb_bin_values: 256 bins need uint16 output (index 255 must stay free for values below the first boundary)");
     cudaStream_t stream = (cudaStream_t)cuda_stream;
-    SB_CUDA(cudaMemcpyToSymbolAsync(c_boundaries, bin_boundary, sizeof(double) * n_bins, 0, cudaMemcpyHostToDevice, stream));
     if (n == 0) return SB_OK;
-    int64_t g = (n + 255) / 256;
-    if (g > 148 * 8) g = 148 * 8;
-    bin_values_kernel<<<(int)g, 256, 0, stream>>>(values, n, n_bins, bins_out, out_width);
-    SB_CUDA(cudaGetLastError());
+    // per-call boundary table, allocated and freed in stream order: calls on different streams or from different host
+    // threads do not share it (a single __constant__ table would be overwritten under a running kernel)
+    double* d_bounds = nullptr;
+    SB_CUDA(cudaMallocAsync((void**)&d_bounds, sizeof(double) * n_bins, stream));
+    cudaError_t e = cudaMemcpyAsync(d_bounds, bin_boundary, sizeof(double) * n_bins, cudaMemcpyHostToDevice, stream);
+    if (e == cudaSuccess) {
+        // 4096 doubles = 32 KB of dynamic shared memory: inside the default 48 KB limit
+        int64_t g = (n + 255) / 256;
+        if (g > 148 * 8) g = 148 * 8;
+        bin_values_kernel<<<(int)g, 256, sizeof(double) * n_bins, stream>>>(values, n, d_bounds, n_bins, bins_out, out_width);
+        e = cudaGetLastError();
+    }
+    cudaFreeAsync(d_bounds, stream);
+    SB_CUDA(e);
     return SB_OK;
 }

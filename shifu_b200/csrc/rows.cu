@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(TPB) errors_kernel(const ErrArgs a, double* sc
             ve += (double)(sig * err);
             vc += (double)sig;
         } else if (a.rf_oob) {
-            const float w = a.weights[r];
+            const float w = a.weights ? a.weights[r] : 1.0f;  // rows adopted without a weight array: weight 1, never out-of-bag
             if (__float_as_int(w) == 0) {  // Float.compare(weight, 0f) == 0: out-of-bag row (dt/DTWorker.java:593-597)
                 ve += (double)(sig * err);
                 vc += (double)sig;
@@ -220,6 +220,9 @@ __global__ void make_scales_kernel(const uint32_t* maxbits, int kind, float* sca
     int e = 0;
     if (m > 0.0f && isfinite(m)) {
         e = QBITS - ilogbf(m) - 1;  // m * 2^e < 2^QBITS
+        // the sum statistic is signed: one bit less, so that its high limb fits the headroom of hist_rows_kernel's
+        // limb accumulation (hist.cu) -- |q| < 2^43
+        if (kind == STAT_VARIANCE && k == 1) e -= 1;
         if (e > 100) e = 100;
         if (e < -100) e = -100;
     }

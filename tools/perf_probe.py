@@ -15,9 +15,10 @@ ap.add_argument("--bins", type=int, default=64)
 ap.add_argument("--depth", type=int, default=8)
 ap.add_argument("--trees", type=int, default=2)
 ap.add_argument("--weighted", type=int, default=0)
+ap.add_argument("--flags", type=int, default=0, help="sb_config.flags (SB_FLAG_*)")
 a = ap.parse_args()
 
-cfg = ConfigArrays([a.bins] * a.features, max_depth=a.depth, tree_num=a.trees, learning_rate=0.05, min_instances_per_node=5)
+cfg = ConfigArrays([a.bins] * a.features, max_depth=a.depth, tree_num=a.trees, learning_rate=0.05, min_instances_per_node=5, flags=a.flags)
 w = Worker(cfg)
 t0 = time.time()
 w.load_synthetic(a.rows, seed=1002, weighted=bool(a.weighted))
