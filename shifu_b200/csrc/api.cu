@@ -483,7 +483,6 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
 
     const int cnt_int = h->cnt_int ? 1 : 0;
     const int nw = hist_words_per_bin(h->stat_kind, cnt_int, h->stats_size);
-    const int nw_rows = hist_rows_words_per_bin(h->stat_kind, cnt_int, h->stats_size);  // hist_rows_kernel (limb layout)
     const int max_gs = hist_max_slots_per_block(bins_pad, nw);
     if (max_gs < 1) return fail(SB_ERR_UNSUPPORTED, "one node's histogram tile does not fit in shared memory");
 
@@ -534,7 +533,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     const bool rows_enabled = h->enable_row_lists && h->train.n < (int64_t)0xffffffff;
     if (rows_enabled && n_tiles > 0) {
         for (int f : {4, 2, 1}) {
-            rows_max_gs = hist_rows_max_slots_per_block(bins_pad, nw_rows, f);
+            rows_max_gs = hist_rows_max_slots_per_block(bins_pad, nw, f);
             if (rows_max_gs >= 1) { fpl = f; break; }
         }
     }
@@ -799,7 +798,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                     }
                 }
                 L.grid = max_chunks * std::max(n_rt, 1);
-                L.smem = L.has_narrow ? hist_rows_smem_bytes(rgs, bins_pad, nw_rows, fpl) : 0;
+                L.smem = L.has_narrow ? hist_rows_smem_bytes(rgs, bins_pad, nw, fpl) : 0;
                 if (any_wide) {
                     L.has_wide = true;
                     L.wide = ra;

@@ -29,7 +29,6 @@
 
 #include "common.cuh"
 #include "kernels.cuh"
-#include "limb.h"
 
 namespace sb {
 
@@ -135,82 +134,6 @@ constexpr size_t SMEM_FIXED = (size_t)NST * TILE_BYTES                   // bin 
 __host__ __device__ inline int hist_words(int kind, int cnt_int, int stats_size) {
     if (kind == STAT_VARIANCE) return cnt_int ? 5 : 6;
     return cnt_int ? stats_size : 2 * stats_size;
-}
-
-// ---------------------------------------------------------------------------------------------------------------------
-// Limb accumulation (hist_rows_kernel, variance statistics with integer counts -- the GBT default): limb.h has the
-// word layout, the bounds and the arithmetic; here are the scan of the count words and the final merge.
-__device__ __forceinline__ void emit_global(int64_t* raw_lo, int64_t* raw_hi, int64_t idx, long long v) {
-    if (v == 0) return;
-    // explicit state space: through a by-value struct the compiler no longer knows these are global addresses
-    asm volatile("red.global.add.u64 [%0], %1;" ::"l"(raw_lo + idx), "l"((unsigned long long)(v & 0xffffffffLL)) : "memory");
-    if ((v >> 32) != 0) asm volatile("red.global.add.u64 [%0], %1;" ::"l"(raw_hi + idx), "l"((unsigned long long)(v >> 32)) : "memory");
-}
-
-// one entry -> the global (lo, hi) accumulators of its three statistics
-__device__ __forceinline__ void limb_emit_entry(const uint32_t* p, int stride, int cnt_shift, int64_t* raw_lo, int64_t* raw_hi, int64_t idx) {
-    long long vc, va, vb;
-    limb_values(p, stride, vc, va, vb);
-    emit_global(raw_lo, raw_hi, idx, (long long)((unsigned long long)vc << cnt_shift));
-    emit_global(raw_lo, raw_hi, idx + 1, va);
-    emit_global(raw_lo, raw_hi, idx + 2, vb);
-}
-
-struct LimbOut {  // where a block's entries go (by value: a reference to the kernel parameters would force a local copy)
-    const int32_t* tile_feats;  // of this tile: [32 * FPL]
-    const int64_t* pair_off;    // of this block's first slot: [gcount][n_features]
-    int n_features;
-    const int* cnt_shift;
-    int64_t* raw_lo;
-    int64_t* raw_hi;
-};
-
-template <int FPL, int NCONS>
-__device__ __noinline__ void limb_sweep(uint32_t* hist, int gcount, int bins_pad, const LimbOut a, int ctid) {
-    constexpr int LW = 32 * FPL;
-    constexpr int VPB = LW / 4;  // 128-bit vectors per (slot, bin)
-    asm volatile("bar.sync 1, %0;" ::"n"(NCONS) : "memory");
-    const int total = gcount * bins_pad * VPB;
-    for (int v = ctid; v < total; v += NCONS) {
-        const int sb = v / VPB, j = v - sb * VPB;
-        uint32_t* p4 = hist + (size_t)sb * LIMB_WORDS * LW + 4 * j;
-        const uint4 c = *reinterpret_cast<const uint4*>(p4);
-        if (((c.x | c.y | c.z | c.w) & LIMB_TRIGGER) == 0u) continue;
-        const uint32_t cw[4] = {c.x, c.y, c.z, c.w};
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            if ((cw[i] & LIMB_TRIGGER) == 0u) continue;
-            uint32_t* p = p4 + i;
-            if (limb_normalise(p, LW)) {
-                // a carry field is half full: merge the entry into the global accumulators now
-                const int col = 4 * j + i, slot = sb / bins_pad, bin = sb - slot * bins_pad;
-                const int f = a.tile_feats[col];
-                const int64_t off = f >= 0 ? a.pair_off[(size_t)slot * a.n_features + f] : -1;
-                if (off >= 0) limb_emit_entry(p, LW, *a.cnt_shift, a.raw_lo, a.raw_hi, off + (int64_t)bin * 3);
-                p[0] = 0u; p[LW] = 0u; p[2 * LW] = 0u; p[3 * LW] = 0u; p[4 * LW] = 0u; p[5 * LW] = 0u;
-            }
-        }
-    }
-    asm volatile("bar.sync 1, %0;" ::"n"(NCONS) : "memory");
-}
-
-// end of the chunk: every entry of the block's histogram goes to the global accumulators (same thread mapping as flush_hist)
-template <int LW>
-__device__ __forceinline__ void flush_hist_limb(const uint32_t* hist, int gcount, int g0, int bins_pad, int cnt_shift,
-                                                const int32_t* tile_feats, const int64_t* pair_off, int n_features,
-                                                int64_t* raw_lo, int64_t* raw_hi, int nthreads) {
-    const int groups = nthreads / LW;
-    const int l = threadIdx.x % LW, q = threadIdx.x / LW;
-    if (q >= groups) return;
-    const int f = tile_feats[l];
-    if (f < 0) return;
-    for (int sl = 0; sl < gcount; ++sl) {
-        const int64_t off = pair_off[(size_t)(g0 + sl) * n_features + f];
-        if (off < 0) continue;
-        for (int bin = q; bin < bins_pad; bin += groups) {
-            limb_emit_entry(hist + (size_t)(sl * bins_pad + bin) * LIMB_WORDS * LW + l, LW, cnt_shift, raw_lo, raw_hi, off + (int64_t)bin * 3);
-        }
-    }
 }
 
 // Merge a block's privatised histogram into the global integer accumulators.  (lo, hi) split: the global sum over
@@ -675,105 +598,6 @@ __device__ __forceinline__ void rows_consume(const HistRowsArgs& a, const RowOps
     }
 }
 
-// The consumer loop for the limb accumulation (variance statistics, integer counts): five fire-and-forget atomics per
-// cell, no second phase.  Same tile / lane / dummy-bin conventions as rows_consume.
-template <int FPL, int ALLF, int KACT>
-__device__ __forceinline__ void rows_consume_limb(const HistRowsArgs& a, const RowOps* ops_s, RStage* st, const uint32_t* fm_tab,
-                                                  uint32_t* hist, int cw, int lane, int tile_id, int g0, int gcount,
-                                                  int64_t begin, int64_t end, int n_iters) {
-    constexpr int RPW = RCfg<FPL>::RPW;
-    constexpr int NCONS = RCfg<FPL>::CONS_WARPS * 32;
-    constexpr int LIMB_SWEEP_STAGES = LIMB_SWEEP_ROWS / R_TILE;  // a stage holds at most R_TILE rows
-    static_assert(LIMB_SWEEP_STAGES * R_TILE == LIMB_SWEEP_ROWS, "scan interval in whole stages");
-    constexpr uint32_t WORD = 128u * FPL;                           // bytes between the words of one entry
-    constexpr auto KS = std::make_integer_sequence<int, KACT>{};
-    const uint32_t lane_bit = 1u << lane;
-    const uint32_t lane_base = smem_u32(hist) + (uint32_t)lane * 4u;
-    constexpr uint32_t bin_stride = (uint32_t)LIMB_WORDS * WORD;     // bytes between bins
-    const uint32_t slot_stride = (uint32_t)a.bins_pad * bin_stride;  // bytes between slots
-    const uint8_t* my_bins = a.rm_bins + a.tile_slot0[tile_id] + lane * FPL;
-    bool lane_loads = !ALLF;
-#pragma unroll
-    for (int k = 0; k < FPL; ++k)
-        if (a.tile_feats[tile_id * 32 * FPL + k * 32 + lane] >= 0) lane_loads = true;
-    const int wr0 = cw * RPW;
-    const uint32_t dummy_addr = lane_base + (uint32_t)gcount * slot_stride;
-    const LimbOut lo{a.tile_feats + tile_id * 32 * FPL, a.pair_off + (size_t)g0 * a.n_features, a.n_features, a.cnt_shift, a.raw_lo, a.raw_hi};
-
-    uint32_t bw_cur[RPW], bw_next[RPW];
-    auto fetch_bins = [&](int it, uint32_t (&bw)[RPW]) {
-        const int s = it % R_NST;
-        mbar_wait(&st[s].full, (uint32_t)((it / R_NST) & 1));
-        const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
-        const RowOps* v = ops_s + s * R_TILE + wr0;
-#pragma unroll
-        for (int j = 0; j < RPW; ++j) {
-            bw[j] = 0;
-            if (wr0 + j < rows && lane_loads) {
-                const uint8_t* src = my_bins + (size_t)v[j].row * a.fpad;
-                if (FPL == 4) bw[j] = __ldg(reinterpret_cast<const uint32_t*>(src));
-                else if (FPL == 2) bw[j] = __ldg(reinterpret_cast<const unsigned short*>(src));
-                else bw[j] = __ldg(src);
-            }
-        }
-    };
-    if (n_iters > 0) fetch_bins(0, bw_cur);
-    for (int it = 0; it < n_iters; ++it) {
-        const int s = it % R_NST;
-        if (it + 1 < n_iters) fetch_bins(it + 1, bw_next);
-        const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
-        const RowOps* v = ops_s + s * R_TILE + wr0;
-#pragma unroll
-        for (int j = 0; j < RPW; ++j) {
-            if (wr0 + j >= rows) break;  // warp-uniform
-            const uint2 v0 = *reinterpret_cast<const uint2*>(&v[j].slot);   // slot, integer sig*w
-            const uint4 v1 = *reinterpret_cast<const uint4*>(&v[j].q[0]);   // sum, sum of squares: 64-bit fixed point
-            const uint32_t slot = v0.x;
-            const bool rowok = slot < (uint32_t)gcount;
-            const uint32_t base = lane_base + slot * slot_stride;
-            const uint32_t c0 = v0.y + LIMB_MARK;
-            const uint32_t alo = v1.x & LIMB_MASK, ahi = __funnelshift_r(v1.x, v1.y, LIMB_BITS);
-            const uint32_t blo = v1.z & LIMB_MASK, bhi = __funnelshift_r(v1.z, v1.w, LIMB_BITS);
-            const uint32_t rbase = rowok ? base : dummy_addr;
-            const uint32_t bmul = rowok ? bin_stride : 0u;
-            const uint32_t bwj = bw_cur[j];
-            uint32_t fmw[FPL];
-            if (!ALLF) {
-                const uint32_t* fmp = fm_tab + (slot & (R_MAX_GS - 1)) * FPL;
-                if (FPL == 4) {
-                    const uint4 t = *reinterpret_cast<const uint4*>(fmp);
-                    fmw[0] = t.x; fmw[1] = t.y; fmw[2] = t.z; fmw[3] = t.w;
-                } else if (FPL == 2) {
-                    const uint2 t = *reinterpret_cast<const uint2*>(fmp);
-                    fmw[0] = t.x; fmw[1] = t.y;
-                } else {
-                    fmw[0] = fmp[0];
-                }
-            }
-            static_for(KS, [&](auto kc) {
-                constexpr int k = decltype(kc)::value;
-                constexpr uint32_t KO = 128u * k;
-                const uint32_t bin = (k == 3) ? (bwj >> 24) : ((bwj >> (8 * k)) & 0xffu);
-                uint32_t adr;
-                if (ALLF) adr = rbase + bin * bmul;
-                else adr = (rowok && (fmw[k] & lane_bit) != 0u) ? base + bin * bin_stride : dummy_addr;
-                sred_add<KO>(adr, c0);
-                sred_add<KO + WORD>(adr, alo);
-                sred_add<KO + 2 * WORD>(adr, ahi);
-                sred_add<KO + 3 * WORD>(adr, blo);
-                sred_add<KO + 4 * WORD>(adr, bhi);
-            });
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&st[s].empty);
-        // every 512 rows: normalise the entries that may not take another 512 contributions
-        if ((it % LIMB_SWEEP_STAGES) == LIMB_SWEEP_STAGES - 1 && it + 1 < n_iters)
-            limb_sweep<FPL, NCONS>(hist, gcount, a.bins_pad, lo, cw * 32 + lane);
-#pragma unroll
-        for (int j = 0; j < RPW; ++j) bw_cur[j] = bw_next[j];
-    }
-}
-
 template <int KIND, int CNT_INT, int FPL, int ALLF>
 __global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const HistRowsArgs a) {
     constexpr int CONS_WARPS = RCfg<FPL>::CONS_WARPS;
@@ -786,8 +610,7 @@ __global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const
     const int tile_id = blockIdx.x / n_chunks;
     const int ci = blockIdx.x - tile_id * n_chunks;
     if (tile_id >= a.n_tiles) return;  // the grid is an upper bound; uniform for the block
-    constexpr bool LIMB = KIND == STAT_VARIANCE && CNT_INT == 1;
-    const int nw = LIMB ? LIMB_WORDS : hist_words(KIND, CNT_INT, a.stats_size);
+    const int nw = hist_words(KIND, CNT_INT, a.stats_size);
     RowOps* ops_s = reinterpret_cast<RowOps*>(smem);
     RStage* st = reinterpret_cast<RStage*>(smem + (size_t)R_NST * R_TILE * sizeof(RowOps));
     uint32_t* fm_tab = reinterpret_cast<uint32_t*>(smem + (size_t)R_NST * R_TILE * sizeof(RowOps) + 128);
@@ -831,11 +654,7 @@ __global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const
         const int cw = warp - 1;
         const int kact = a.tile_kact[tile_id];  // a partly filled tile spreads its features over the lanes first
         const uint32_t hb = smem_u32(hist);
-#define SB_CONSUME(K)                                                                                                      \
-    do {                                                                                                               \
-        if constexpr (LIMB) rows_consume_limb<FPL, ALLF, K>(a, ops_s, st, fm_tab, hist, cw, lane, tile_id, g0, gcount, begin, end, n_iters); \
-        else rows_consume<KIND, CNT_INT, FPL, ALLF, K>(a, ops_s, st, fm_tab, hb, cw, lane, tile_id, gcount, begin, end, n_iters, nw); \
-    } while (0)
+#define SB_CONSUME(K) rows_consume<KIND, CNT_INT, FPL, ALLF, K>(a, ops_s, st, fm_tab, hb, cw, lane, tile_id, gcount, begin, end, n_iters, nw)
         if (kact >= FPL) SB_CONSUME(FPL);
         else if constexpr (FPL == 4) {
             if (kact == 3) SB_CONSUME(3);
@@ -845,18 +664,10 @@ __global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const
 #undef SB_CONSUME
     }
     __syncthreads();
-    if constexpr (LIMB)
-        flush_hist_limb<32 * FPL>(hist, gcount, g0, bins_pad, *a.cnt_shift, a.tile_feats + tile_id * 32 * FPL, a.pair_off,
-                                  a.n_features, a.raw_lo, a.raw_hi, NTHR);
-    else
-        flush_hist<KIND, CNT_INT, 32 * FPL>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0,
-                                            a.tile_feats + tile_id * 32 * FPL, a.pair_off, a.n_features, a.raw_lo, a.raw_hi, NTHR);
+    flush_hist<KIND, CNT_INT, 32 * FPL>(hist, gcount, g0, bins_pad, nw, a.stats_size, CNT_INT ? *a.cnt_shift : 0,
+                                   a.tile_feats + tile_id * 32 * FPL, a.pair_off, a.n_features, a.raw_lo, a.raw_hi, NTHR);
 }
 
-// words per bin of hist_rows_kernel's histogram: the limb layout where it applies, else as hist_words
-int hist_rows_words_per_bin(int kind, int cnt_int, int stats_size) {
-    return (kind == STAT_VARIANCE && cnt_int == 1) ? LIMB_WORDS : hist_words(kind, cnt_int, stats_size);
-}
 size_t hist_rows_smem_bytes(int gs, int bins_pad, int nw, int fpl) {
     return R_SMEM_FIXED + (size_t)gs * bins_pad * nw * 32 * fpl * 4 + (size_t)nw * 32 * fpl * 4 /* dummy bin */;
 }

@@ -119,7 +119,6 @@ cudaError_t hist_rows_launch(int kind, int cnt_int, int fpl, int allf, const His
 cudaError_t hist_rows_wide_launch(int kind, int cnt_int, const HistRowsArgs& a, int grid, size_t smem, cudaStream_t stream);
 size_t hist_rows_wide_smem_bytes(int gs, int bins_pad, int nw);
 int hist_rows_wide_max_slots_per_block(int bins_pad, int nw);
-int hist_rows_words_per_bin(int kind, int cnt_int, int stats_size);
 size_t hist_rows_smem_bytes(int gs, int bins_pad, int nw, int fpl);
 int hist_rows_max_slots_per_block(int bins_pad, int nw, int fpl);
 

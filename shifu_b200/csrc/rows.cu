@@ -220,9 +220,6 @@ __global__ void make_scales_kernel(const uint32_t* maxbits, int kind, float* sca
     int e = 0;
     if (m > 0.0f && isfinite(m)) {
         e = QBITS - ilogbf(m) - 1;  // m * 2^e < 2^QBITS
-        // the sum statistic is signed: one bit less, so that its high limb fits the headroom of hist_rows_kernel's
-        // limb accumulation (hist.cu) -- |q| < 2^43
-        if (kind == STAT_VARIANCE && k == 1) e -= 1;
         if (e > 100) e = 100;
         if (e < -100) e = -100;
     }

@@ -16,7 +16,11 @@ ap.add_argument("--depth", type=int, default=8)
 ap.add_argument("--trees", type=int, default=2)
 ap.add_argument("--weighted", type=int, default=0)
 ap.add_argument("--flags", type=int, default=0, help="sb_config.flags (SB_FLAG_*)")
+ap.add_argument("--lib", default=None, help="alternative libshifu_b200.so (kernel experiments)")
 a = ap.parse_args()
+if a.lib:
+    from shifu_b200 import capi
+    capi.LIB_PATH = os.path.abspath(a.lib)
 
 cfg = ConfigArrays([a.bins] * a.features, max_depth=a.depth, tree_num=a.trees, learning_rate=0.05, min_instances_per_node=5, flags=a.flags)
 w = Worker(cfg)
