@@ -423,7 +423,13 @@ cudaError_t hist_launch(int kind, int cnt_int, const HistArgs& a, const void* te
 // (8 words) as the atomics of 32 cells do; with FPL = 4 that cost is shared by 128 cells.  The histogram is laid out
 // [slot][bin][word][k][lane] (feature = FPL*lane + k), so for every k a warp's atomics still hit 32 distinct banks.
 namespace {
-constexpr int R_NST = 4;
+#ifndef SB_R_NST
+#define SB_R_NST 4  // stages of the RowOps ring
+#endif
+#ifndef SB_ROWS_PF
+#define SB_ROWS_PF 2  // tiles whose bins are in flight ahead of the one being accumulated
+#endif
+constexpr int R_NST = SB_R_NST;
 constexpr int R_TILE = 128;  // rows per stage
 constexpr size_t R_SMEM_FIXED = (size_t)R_NST * R_TILE * sizeof(RowOps) + 128 /* barriers */ + 256 /* fmask table */;
 struct RStage { uint64_t full, empty; };
@@ -470,37 +476,34 @@ __device__ __forceinline__ void rows_consume(const HistRowsArgs& a, const RowOps
     // per-lane dummy bin right behind the block's histogram (one bin's worth of words)
     const uint32_t dummy_addr = lane_base + (uint32_t)gcount * slot_stride;
 
-    // The bins of tile it+1 are requested before the atomics of tile it are issued, so the global-load latency
-    // of one tile hides behind the shared-memory work of the previous one.
-    // Class statistics cost one atomic per cell, so a tile is consumed faster than a global load returns: their bins are
-    // requested two tiles ahead (PF2), the variance statistics' one tile ahead.
-    constexpr bool PF2 = KIND != STAT_VARIANCE;
-    uint32_t bw_cur[RPW], bw_next[RPW], bw_next2[PF2 ? RPW : 1];
-    auto fetch_bins = [&](int it, uint32_t (&bw)[RPW]) {
+    // The bins of the next PF tiles are requested before the atomics of tile `it` are issued, so the global-load latency
+    // hides behind the shared-memory work of the tiles in between (one tile ahead left the consumer warps waiting on
+    // the loads for a quarter of their time: ncu, long_scoreboard at the first use of a tile's bins).
+    constexpr int PF = SB_ROWS_PF;
+    static_assert(PF >= 1 && PF < R_NST, "the RowOps ring must hold the tiles whose bins are in flight");
+    uint32_t bw[PF + 1][RPW];
+    auto fetch_bins = [&](int it, uint32_t (&b)[RPW]) {
         const int s = it % R_NST;
         mbar_wait(&st[s].full, (uint32_t)((it / R_NST) & 1));
         const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
         const RowOps* v = ops_s + s * R_TILE + wr0;
 #pragma unroll
         for (int j = 0; j < RPW; ++j) {
-            bw[j] = 0;
+            b[j] = 0;
             if (wr0 + j < rows && lane_loads) {
                 const uint8_t* src = my_bins + (size_t)v[j].row * a.fpad;
-                if (FPL == 4) bw[j] = __ldg(reinterpret_cast<const uint32_t*>(src));
-                else if (FPL == 2) bw[j] = __ldg(reinterpret_cast<const unsigned short*>(src));
-                else bw[j] = __ldg(src);
+                if (FPL == 4) b[j] = __ldg(reinterpret_cast<const uint32_t*>(src));
+                else if (FPL == 2) b[j] = __ldg(reinterpret_cast<const unsigned short*>(src));
+                else b[j] = __ldg(src);
             }
         }
     };
-    if (n_iters > 0) fetch_bins(0, bw_cur);
-    if (PF2 && n_iters > 1) fetch_bins(1, bw_next);
+#pragma unroll
+    for (int d = 0; d < PF; ++d)
+        if (d < n_iters) fetch_bins(d, bw[d]);
     for (int it = 0; it < n_iters; ++it) {
         const int s = it % R_NST;
-        if (PF2) {
-            if (it + 2 < n_iters) fetch_bins(it + 2, reinterpret_cast<uint32_t (&)[RPW]>(bw_next2));
-        } else {
-            if (it + 1 < n_iters) fetch_bins(it + 1, bw_next);
-        }
+        if (it + PF < n_iters) fetch_bins(it + PF, bw[PF]);
         const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
         const RowOps* v = ops_s + s * R_TILE + wr0;
 #pragma unroll
@@ -528,7 +531,7 @@ __device__ __forceinline__ void rows_consume(const HistRowsArgs& a, const RowOps
                 // ALLF: one select per row; a bad row lands in the dummy bin whatever its bins are
                 const uint32_t rbase = rowok ? base : dummy_addr;
                 const uint32_t bmul = rowok ? bin_stride : 0u;
-                const uint32_t bwj = bw_cur[jb + j];
+                const uint32_t bwj = bw[0][jb + j];
                 // feature masks of the row's slot: the FPL words sit side by side, one vector load
                 uint32_t fmw[FPL];
                 if (!ALLF) {
@@ -591,10 +594,9 @@ __device__ __forceinline__ void rows_consume(const HistRowsArgs& a, const RowOps
         __syncwarp();
         if (lane == 0) mbar_arrive(&st[s].empty);
 #pragma unroll
-        for (int j = 0; j < RPW; ++j) {
-            bw_cur[j] = bw_next[j];
-            if (PF2) bw_next[j] = bw_next2[j];
-        }
+        for (int d = 0; d < PF; ++d)
+#pragma unroll
+            for (int j = 0; j < RPW; ++j) bw[d][j] = bw[d + 1][j];
     }
 }
 
