@@ -70,15 +70,32 @@ def assert_gain_equal(gd, go, bits_d=None, bits_o=None, idx=0):
         assert np.array_equal(a, b)
 
 
+def assert_stats_close_per_bin(dev, orc):
+    """The strict reading of the bar: every statistic of every bin within 1e-9 of the ORACLE'S OWN value for that bin,
+    with no allowance tied to the size of the whole data set.  The signed sum may cancel inside a bin, so its yardstick
+    is the bin's sum of |contributions|, bounded from the bin's other two statistics by Cauchy-Schwarz:
+    sum |y s| <= sqrt(sum s * sum y^2 s)."""
+    d, o = dev.reshape(-1, 3), orc.reshape(-1, 3)
+    assert np.all(np.abs(d[:, 0] - o[:, 0]) <= 1e-9 * np.abs(o[:, 0]))
+    assert np.all(np.abs(d[:, 2] - o[:, 2]) <= 1e-9 * np.abs(o[:, 2]))
+    yard = np.maximum(np.abs(o[:, 1]), np.sqrt(np.abs(o[:, 0] * o[:, 2])))
+    assert np.all(np.abs(d[:, 1] - o[:, 1]) <= 1e-9 * yard)
+
+
 def run_gbt(n, n_bins, seed, n_trees=2, max_depth=4, weighted=False, loss=capi.SB_LOSS_SQUARED, label="binary",
             is_categorical=None, feature_subsets=False, with_validation=True, bagging=False, min_inst=1,
-            oracle_threads=3, flags=0):
+            oracle_threads=3, flags=0, impurity=capi.SB_IMPURITY_VARIANCE, min_info_gain=0.0, dropout_rate=0.0,
+            sig_log2_range=0, per_bin_strict=False, learning_rate=0.1, on_pass=None):
     from oracle.pyoracle import OracleWorker
     cfg = ConfigArrays(n_bins, is_categorical=is_categorical, loss=loss, is_gbdt=True, tree_num=n_trees,
-                       max_depth=max_depth, min_instances_per_node=min_inst, learning_rate=0.1,
-                       column_num=np.arange(len(n_bins)) + 3, flags=flags)
+                       max_depth=max_depth, min_instances_per_node=min_inst, learning_rate=learning_rate,
+                       column_num=np.arange(len(n_bins)) + 3, flags=flags, impurity=impurity,
+                       min_info_gain=min_info_gain)
     cols, y, sig, _ = make_data(n, n_bins, seed, label=label, weighted=weighted)
     rng = np.random.default_rng(seed + 1)
+    if sig_log2_range:  # significance spread log-uniformly over 2^-r .. 2^r
+        sig = np.exp2(rng.uniform(-sig_log2_range, sig_log2_range, n)).astype(np.float32)
+        weighted = True
     w0 = (rng.random(n) < 0.7).astype(np.float32)[None, :] if bagging else None
     dev, orc = Worker(cfg), OracleWorker(cfg)
     dev.load_rows(cols, y, sig, w0)
@@ -108,8 +125,11 @@ def run_gbt(n, n_bins, seed, n_trees=2, max_depth=4, weighted=False, loss=capi.S
             new_w = (rng.random(n) < 0.7).astype(np.float32) if (bagging and switch and t >= 1) else None
             # isFirstTree as the master sets it: trees.size() == 1, evaluated before a new root is added
             # (dt/DTMaster.java:418,475)
-            it = IterIn(cfg, sent, todo, switch_to_next_tree=switch, is_first_tree=(t == 0) or (switch and t == 1),
-                        new_weights=new_w)
+            first = (t == 0) or (switch and t == 1)
+            # the reference draws dropOutRandom.nextDouble() < dropOutRate per row at a tree switch after the first tree
+            # (dt/DTWorker.java:634-638); the draws are injected as a mask so both sides drop the same rows
+            drop = (rng.random(n) < dropout_rate).astype(np.uint8) if (dropout_rate > 0 and switch and not first) else None
+            it = IterIn(cfg, sent, todo, switch_to_next_tree=switch, is_first_tree=first, new_weights=new_w, dropout=drop)
             d = dev.compute(it)
             o = orc.compute(it, n_threads=oracle_threads)
             n_iter += 1
@@ -128,7 +148,11 @@ def run_gbt(n, n_bins, seed, n_trees=2, max_depth=4, weighted=False, loss=capi.S
             scale = (np.sum(np.abs(sv * wv)), np.sum(np.abs(dout * sv * wv)), np.sum(np.abs(dout * dout * sv * wv)))
             exact_counts = not weighted
             assert_stats_close(cfg, it, d[4], o[4], scale, exact_counts)
+            if per_bin_strict:
+                assert_stats_close_per_bin(d[4], o[4])
             gd, bits_d = dev.best_splits(len(todo), with_cat=has_cat)
+            if on_pass is not None:
+                on_pass(it, d, o, gd)
             go, bits_o = orc.best_splits(it, d[4], with_cat=has_cat)   # oracle scan of the device's statistics
             go2, _ = orc.best_splits(it, o[4], with_cat=has_cat)      # oracle scan of its own statistics
             next_nodes = []

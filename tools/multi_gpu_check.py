@@ -111,5 +111,37 @@ if rank == 0:
     assert passes == passes_full and trees_sharded == trees_full, "native tree loop: sharded trees differ from the single-GPU trees"
     print("in-library NCCL merge ok: %d iterations bit-identical; native tree loop: %d trees, %d passes, identical to single GPU"
           % (n_iter, len(trees_full), passes))
+
+# ---- a shard without a single active row (all its sample weights are 0): its row lists are empty, its kernels must do
+# nothing, and the merged result must still equal the single-GPU run over the concatenated rows
+ids = [dist_unique_id() if rank == 0 else None]
+dist.broadcast_object_list(ids, src=0)
+w4 = Worker(cfg)
+w4.load_synthetic(per, seed=5, row0=rank * per, weighted=False)
+w4.dist_init(ids[0], rank, world)
+if rank == world - 1:
+    w4.set_weights(0, np.zeros(per, np.float32))
+full4 = None
+if rank == 0:
+    full4 = Worker(cfg)
+    full4.load_synthetic(per * world, seed=5, row0=0, weighted=False)
+    wz = np.ones(per * world, np.float32)
+    wz[(world - 1) * per:] = 0.0
+    full4.set_weights(0, wz)
+m4 = DTMaster(cfg, tree_num=1, max_depth=5, worker_number=world)
+it = m4.build_initial_master_params()
+n_iter4 = 0
+while it is not None:
+    sc = w4.compute(it)
+    gains, bits = w4.best_splits(it.n_todo)
+    if full4 is not None:
+        ref = full4.compute(it)
+        assert np.array_equal(ref[4], sc[4]), "empty shard: merged statistics differ from the single-GPU run"
+    it = m4.do_compute(gains, bits)
+    n_iter4 += 1
+w4.close()
+if full4 is not None:
+    full4.close()
+    print("empty-shard check ok: %d iterations bit-identical" % n_iter4)
 dist.barrier()
 dist.destroy_process_group()
