@@ -52,9 +52,16 @@ def load():
     lib.orc_score_rows.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
     lib.orc_java_random_doubles.restype = None
     lib.orc_index_to_level.argtypes = [C.c_int]
-    lib.orc_sample_features.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.c_void_p]
-    lib.orc_java_random_init.argtypes = [C.c_int64]
-    lib.orc_java_random_init.restype = C.c_uint64
+    from shifu_b200.capi import SbhParams
+    lib.orc_master_create.argtypes = [C.POINTER(SbConfig), C.POINTER(SbhParams), C.POINTER(V)]
+    lib.orc_master_destroy.argtypes = [V]
+    lib.orc_master_destroy.restype = None
+    lib.orc_master_initial.argtypes = [V]
+    lib.orc_master_initial.restype = C.POINTER(SbIterIn)
+    lib.orc_master_do_compute.argtypes = [V, C.POINTER(SbGain), C.c_void_p]
+    lib.orc_master_do_compute.restype = C.POINTER(SbIterIn)
+    lib.orc_master_tree_count.argtypes = [V]
+    lib.orc_master_dump_tree.argtypes = [V, C.c_int, C.c_void_p, C.c_int]
     _lib = lib
     return lib
 
@@ -138,3 +145,52 @@ def score_rows(model, data):
     if rc != 0:
         raise RuntimeError("NullPointerException in predictNode: a split node is missing a child")
     return out if model.is_classification else out[:, 0]
+
+
+class OracleMaster:
+    """DTMaster's growth rules restated on the CPU (oracle_master.cpp); same constructor and calls as
+    shifu_b200.capi.NativeMaster, so a test can drive both with one stream of gain records."""
+
+    def __init__(self, cfg, tree_num, max_depth, is_gbdt=True, learning_rate=0.05, feature_subset_strategy="ALL",
+                 feature_subset_rate=1.0, feature_sampling_seed=0, max_leaves=-1, max_batch_split_size=32,
+                 max_stats_memory=256 << 20, worker_number=1):
+        from shifu_b200.capi import SBH_FSS, NativeMessage, SbhParams
+        self._message = NativeMessage
+        self.lib = load()
+        self.cfg = cfg
+        p = SbhParams()
+        p.tree_num, p.max_depth, p.is_gbdt = tree_num, max_depth, int(bool(is_gbdt))
+        p.feature_subset_strategy = SBH_FSS[feature_subset_strategy]
+        p.feature_subset_rate, p.learning_rate = feature_subset_rate, learning_rate
+        p.feature_sampling_seed, p.max_leaves = feature_sampling_seed, max_leaves
+        p.max_batch_split_size, p.max_stats_memory, p.worker_number = max_batch_split_size, max_stats_memory, worker_number
+        self.h = C.c_void_p()
+        rc = self.lib.orc_master_create(C.byref(cfg.struct), C.byref(p), C.byref(self.h))
+        if rc != 0:
+            raise RuntimeError("orc_master_create failed: %d" % rc)
+
+    def close(self):
+        if self.h:
+            self.lib.orc_master_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def build_initial_master_params(self):
+        return self._message(self.lib.orc_master_initial(self.h))
+
+    def do_compute(self, gains, cat_bits=None):
+        if isinstance(gains, list):
+            gains = (SbGain * max(len(gains), 1))(*gains)
+        ptr = self.lib.orc_master_do_compute(self.h, gains, None if cat_bits is None else cat_bits.ctypes.data)
+        return self._message(ptr) if ptr else None
+
+    @property
+    def n_trees(self):
+        return self.lib.orc_master_tree_count(self.h)
+
+    def dump_tree(self, index):
+        """[n_nodes, 13] in pre-order: id, isLeaf, hasSplit, feature, gain, impurity, leftImpurity, rightImpurity,
+        leftPredict, rightPredict, wgtCnt, wgtCntRatio, predict."""
+        n = self.lib.orc_master_dump_tree(self.h, index, None, 0)
+        out = np.zeros((max(n, 1), 13), dtype=np.float64)
+        self.lib.orc_master_dump_tree(self.h, index, out.ctypes.data, n)
+        return out[:n]

@@ -924,21 +924,4 @@ SB_API void orc_java_random_doubles(int64_t seed, int n, double* out) {
 }
 SB_API int orc_index_to_level(int id) { return indexToLevel(id); }
 
-/*
- * sampleFeaturesForNodeStats (dt/DTMaster.java:880-893): reservoir sample of `sample` features, driven by
- * a java.util.Random whose state is carried in *rng_state (scrambled seed as JavaRandom keeps it).
- */
-SB_API int orc_sample_features(const int32_t* all, int n_all, int sample, uint64_t* rng_state, int32_t* out) {
-    JavaRandom r(0);
-    r.seed = *rng_state;
-    for (int i = 0; i < sample; ++i) out[i] = all[i];
-    for (int i = sample; i < n_all; ++i) {
-        int replacementIndex = (int)(r.nextDouble() * i);
-        if (replacementIndex >= 0 && replacementIndex < sample) out[replacementIndex] = all[i];
-    }
-    *rng_state = r.seed;
-    return 0;
-}
-SB_API uint64_t orc_java_random_init(int64_t seed) { return JavaRandom(seed).seed; }
-
 }  // extern "C"

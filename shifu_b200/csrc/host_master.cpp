@@ -66,6 +66,53 @@ inline int index_to_level(int id) {  // dt/Node.java:459-461
 }
 inline bool is_pos_zero(double x) { return x == 0.0 && !std::signbit(x); }  // Double.compare(x, 0d) == 0
 
+// Double.compare as a total order: -0.0 below 0.0, NaN above everything
+inline int double_compare(double a, double b) {
+    if (a < b) return -1;
+    if (a > b) return 1;
+    const bool an = std::isnan(a), bn = std::isnan(b);
+    if (an || bn) return an == bn ? 0 : (an ? 1 : -1);
+    const bool as = std::signbit(a), bs = std::signbit(b);
+    return as == bs ? 0 : (as ? -1 : 1);
+}
+
+// The leaf-wise split queue is a java.util.PriorityQueue (dt/DTMaster.java:1064-1070): a binary heap, so the order in
+// which entries of EQUAL priority leave it is a property of the heap operations, not of the values -- and every tree
+// root has priority 0 (Node.wgtCntRatio is never set for a root, :721-726).  Same sift-up / sift-down here.
+struct SplitQueue {
+    struct Item { double prio; int tree_id; Node* node; };
+    std::vector<Item> heap;
+    static bool before(const Item& a, const Item& b) { return double_compare(b.prio, a.prio) < 0; }  // larger first
+    bool empty() const { return heap.empty(); }
+    void offer(Item e) {
+        size_t k = heap.size();
+        heap.push_back(e);
+        while (k > 0) {
+            const size_t parent = (k - 1) / 2;
+            if (!before(e, heap[parent])) break;
+            heap[k] = heap[parent];
+            k = parent;
+        }
+        heap[k] = e;
+    }
+    Item poll() {
+        const Item top = heap.front();
+        const Item last = heap.back();
+        heap.pop_back();
+        const size_t n = heap.size();
+        size_t k = 0;
+        while (2 * k + 1 < n) {
+            size_t c = 2 * k + 1;
+            if (c + 1 < n && before(heap[c + 1], heap[c])) c = c + 1;
+            if (!before(heap[c], last)) break;
+            heap[k] = heap[c];
+            k = c;
+        }
+        if (n > 0) heap[k] = last;
+        return top;
+    }
+};
+
 }  // namespace
 
 struct sbh_master {
@@ -292,8 +339,7 @@ struct sbh_master {
 
     // ---- dt/DTMaster.java:316-537 with the merged statistics already reduced to gain records on the device
     const sb_iter_in* do_compute(const sb_gain* gains, const uint8_t* cat_bits) {
-        struct SplitItem { double prio; size_t seq; int tree_id; Node* node; };
-        std::vector<SplitItem> to_split;
+        SplitQueue to_split;
         for (size_t idx = 0; idx < todo_nodes.size(); ++idx) {
             const sb_gain& g = gains[idx];
             const int tree_id = todo_nodes[idx].tree_id;
@@ -301,10 +347,7 @@ struct sbh_master {
             if (!g.found) { done->is_leaf = true; continue; }  // :335-339
             populate_gain_info_to_node(tree_id, done, g, cat_bits, idx);
             if (is_leaf_wise) {
-                if (!(g.gain <= 0.0)) {
-                    const double ratio = done->id == 1 ? 1.0 : g.wgt_cnt / trees[(size_t)tree_id]->root_wgt_cnt;
-                    to_split.push_back({ratio * g.gain, to_split.size(), tree_id, done});  // priority :1064-1070
-                }
+                if (!(g.gain <= 0.0)) to_split.offer({done->wgt_cnt_ratio * g.gain, tree_id, done});  // priority :1064-1070
             } else {
                 const bool is_leaf = g.gain <= 0.0 || index_to_level(done->id) == p.max_depth;
                 done->is_leaf = is_leaf;
@@ -312,8 +355,10 @@ struct sbh_master {
             }
         }
         if (is_leaf_wise) {  // the reference never increments currSplitIndex (:359-363): the whole queue is split
-            std::stable_sort(to_split.begin(), to_split.end(), [](const SplitItem& a, const SplitItem& b) { return a.prio > b.prio; });
-            for (auto& it : to_split) split_node_for_leaf_wised_tree(it.tree_id, it.node);
+            while (!to_split.empty()) {
+                const SplitQueue::Item it = to_split.poll();
+                split_node_for_leaf_wised_tree(it.tree_id, it.node);
+            }
         }
         todo_nodes.clear();
         if (to_do_queue.empty()) {

@@ -490,7 +490,7 @@ def test_device_binning_matches_get_bin_index(oracle_lib):
 
 def test_device_bagging_mask_is_java_random():
     """f4: subsampleWeights drawn on the device are `new java.util.Random(seed).nextDouble() <= rate`, row by row."""
-    from shifu_b200.dt_master import JavaRandom
+    from java_random import JavaRandom
     n = 70001
     cfg = ConfigArrays([8] * 3)
     w = Worker(cfg)
@@ -509,7 +509,7 @@ def test_device_bagging_mask_is_java_random():
 def test_device_stratified_mask_is_one_java_random_per_class():
     """f4, isStratifiedSampling: one Random(seed) per class value, so a row gets the k-th nextDouble(), k = earlier rows
     of its class (dt/DTWorker.java:1526-1532)."""
-    from shifu_b200.dt_master import JavaRandom
+    from java_random import JavaRandom
     n, n_bins = 50021, [8] * 3
     rng = np.random.default_rng(17)
     cols = [rng.integers(0, 8, size=n).astype(np.uint8) for _ in n_bins]

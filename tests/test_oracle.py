@@ -31,7 +31,7 @@ def test_java_random_known_answers(orc):
     assert out[0] == 0.7275636800328681  # new java.util.Random(42).nextDouble()
     lib.orc_java_random_doubles(0, 1, out.ctypes.data)
     assert out[0] == 0.730967787376657   # new java.util.Random(0).nextDouble()
-    from shifu_b200.dt_master import JavaRandom
+    from java_random import JavaRandom
     r = JavaRandom(42)
     lib.orc_java_random_doubles(42, 3, out.ctypes.data)
     assert [r.next_double() for _ in range(3)] == list(out)

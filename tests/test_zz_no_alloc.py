@@ -41,7 +41,7 @@ def static_sums(lib, torch, label, predict, sig, loss):
 
 
 @pytest.mark.parametrize("loss", [capi.SB_LOSS_SQUARED, capi.SB_LOSS_LOG])
-def test_static_error_sums_match_sb_compute_twice_in_a_row(loss):
+def test_static_error_sums_match_sb_compute_twice_in_a_row(loss, oracle_lib):
     import torch
     lib = capi.load_library()
     n, nv, n_bins = 70001, 9001, [32] * 12
@@ -74,6 +74,14 @@ def test_static_error_sums_match_sb_compute_twice_in_a_row(loss):
     # and again the first one: same input, same bits, whatever the previous call left behind
     c3, e3 = static_sums(lib, torch, y, predict, sig, loss)
     assert (c3, e3) == (c1, e1)
+    # an answer that does not come from this library: the oracle's Loss.computeError (dt/Loss.java) row by row, the
+    # float product sig * error widened and summed in double as dt/DTWorker.java:681-682 does
+    for (lab, pred, sg, got_c, got_e) in ((y, predict, sig, c1, e1), (vy, vpredict, vsig, c2, e2)):
+        errs = np.array([oracle_lib.orc_loss_error(loss, C.c_float(float(p)), C.c_float(float(t))) for p, t in zip(pred, lab)],
+                        dtype=np.float32)
+        want_e = float(np.sum((sg * errs).astype(np.float64)))
+        want_c = float(np.sum(sg.astype(np.float64)))
+        assert abs(got_c - want_c) <= 1e-9 * want_c and abs(got_e - want_e) <= 1e-9 * want_e, (got_c, want_c, got_e, want_e)
     w.close()
 
 

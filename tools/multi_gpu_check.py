@@ -10,7 +10,7 @@ import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from bench import DevView  # noqa: E402
 from shifu_b200.capi import ConfigArrays, Worker  # noqa: E402
-from shifu_b200.dt_master import DTMaster  # noqa: E402
+from shifu_b200.capi import NativeMaster as DTMaster  # noqa: E402  (the C++ DTMaster mirror)
 
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
@@ -52,7 +52,7 @@ while it is not None:
     it = m.do_compute(gains, bits)
     n_iter += 1
 if rank == 0:
-    print("multi-gpu check ok: %d iterations, %d trees, bit-identical to the single-GPU run" % (n_iter, len(m.trees)))
+    print("multi-gpu check ok: %d iterations, %d trees, bit-identical to the single-GPU run" % (n_iter, m.n_trees))
 
 # ---- the same through the library's own NCCL communicator (sb_dist_init) and the native tree loop (sbh_grow_tree)
 from shifu_b200.capi import NativeMaster, dist_unique_id  # noqa: E402
