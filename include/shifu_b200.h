@@ -209,7 +209,10 @@ SB_API const char* sb_version(void);
  * (Data.subsampleWeights transposed); NULL => all 1f.  significance NULL => all 1f.
  * output = predict = label initially (dt/DTWorker.java:1264-1273).
  * Host pointers; the call copies to the device and returns when the copy is complete.
- * One call per set (the Java side batches DTWorker.load lines into direct buffers and loads in postLoad).
+ * Limits: ONE load call per set and handle (a second sb_load_rows* / sb_load_synthetic of the same set returns
+ * SB_ERR_UNSUPPORTED -- the Java side batches DTWorker.load lines into direct buffers and loads in postLoad);
+ * fewer than 2^32 - 1 rows per handle (row indices are 32-bit on the device: SB_ERR_UNSUPPORTED beyond; shard
+ * larger sets over several GPUs); at most 16 classes for Entropy / Gini (sb_create rejects more).
  */
 SB_API int sb_load_rows(sb_handle* h, int32_t is_validation, int64_t n_rows, const void* const* bins,
                         const float* label, const float* significance, const float* weights);
@@ -413,6 +416,49 @@ SB_API int sbh_master_halted(sbh_master* m);
    (gain, impurity, leftImpurity, rightImpurity, leftPredict, rightPredict, wgtCnt).  Call with nodes == NULL to size. */
 SB_API int sbh_master_export_tree(sbh_master* m, int index, sb_node* nodes, int node_cap, uint8_t* pool, int pool_cap,
                                   double* extras, int* n_nodes, int* pool_bytes);
+
+/* ------------------------------------------------------------------ categorical binning at load (host side)
+ *
+ * The value -> bin-index map DTWorker.init builds from ColumnConfig.binCategory (dt/DTWorker.java:362-376): entry i
+ * of bin_category may be a group "a@^b@^c" (CommonUtils.flattenCatValGrp, util/CommonUtils.java:1767; delimiter
+ * Constants.CATEGORICAL_GROUP_VAL_DELIMITER) whose members all map to i; a value listed twice keeps the LAST index
+ * (HashMap.put).  sb_category_map_lookup is the per-value rule of DTWorker.load (dt/DTWorker.java:1152-1169): the
+ * empty string (or NULL) and any value that is in no group get bin n_categories, the missing-value bin.  Host strings
+ * in, host bin indices out (uint8 if out_width == 1 else uint16) -- ready for sb_load_rows.
+ */
+typedef struct sb_category_map sb_category_map;
+SB_API int sb_category_map_create(const char* const* bin_category, int32_t n_categories, sb_category_map** out);
+SB_API int sb_category_map_lookup(const sb_category_map* m, const char* const* values, int64_t n, void* bins_out,
+                                  int32_t out_width);
+SB_API void sb_category_map_destroy(sb_category_map* m);
+
+/* ------------------------------------------------------------------ wire format of sb_iter_in
+ *
+ * DTMasterParams (dt/DTMasterParams.java:148-173 write / readFields) as ONE position-independent buffer: what a JVM
+ * hands over in a direct ByteBuffer (jni/DTMessageFlattener.java writes it, jni/shifu_b200_jni.c unpacks it).
+ * Little endian, every section starts on a multiple of 8 bytes:
+ *
+ *   offset  0  u32 magic 0x314D4253 ("SBM1")      4  u32 total bytes of the message
+ *           8  i32 n_trees                        12  i32 n_todo
+ *          16  i32 switch_to_next_tree            20  i32 is_first_tree
+ *          24  i32 continuous_running_start       28  u32 bit 0: new_weights present, bit 1: dropout present
+ *          32  i64 n_rows (length of new_weights / dropout)
+ *          40  per tree:  i32 tree_id, i32 n_nodes, i32 mask_pool_bytes, i32 0,
+ *                         n_nodes x sb_node (64 bytes each, fields in declaration order),
+ *                         mask_pool_bytes bytes, zero-padded to a multiple of 8
+ *              per todo:  i32 key, i32 tree_id, i32 node_id, i32 n_features,
+ *                         n_features x i32 feature slots, zero-padded to a multiple of 8
+ *              new_weights: n_rows x f32, padded to 8 (if present);  dropout: n_rows x u8, padded to 8 (if present)
+ *
+ * sb_msg_unpack validates sizes, child indices and mask offsets and returns a view whose sb_iter_in points INTO the
+ * buffer (nodes, pools, feature lists and per-row arrays are not copied): the buffer must be 8-byte aligned and
+ * outlive the view.  sb_msg_pack writes the same layout from an sb_iter_in (buf == NULL: returns the size needed).
+ */
+typedef struct sb_msg sb_msg;
+SB_API int64_t sb_msg_pack(const sb_iter_in* in, int64_t n_rows, void* buf, int64_t cap);
+SB_API int sb_msg_unpack(const void* buf, int64_t len, sb_msg** out);
+SB_API const sb_iter_in* sb_msg_iter_in(const sb_msg* m);
+SB_API void sb_msg_free(sb_msg* m);
 
 /*
  * No counterpart in the reference.  Weighted error sums of a row set -- out[0] = sum(significance),

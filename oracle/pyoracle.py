@@ -52,6 +52,8 @@ def load():
     lib.orc_score_rows.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
     lib.orc_java_random_doubles.restype = None
     lib.orc_index_to_level.argtypes = [C.c_int]
+    lib.orc_flatten_cat_val_grp.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
+    lib.orc_category_index.argtypes = [C.POINTER(C.c_char_p), C.c_int, C.c_char_p]
     from shifu_b200.capi import SbhParams
     lib.orc_master_create.argtypes = [C.POINTER(SbConfig), C.POINTER(SbhParams), C.POINTER(V)]
     lib.orc_master_destroy.argtypes = [V]

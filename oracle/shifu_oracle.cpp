@@ -924,4 +924,54 @@ SB_API void orc_java_random_doubles(int64_t seed, int n, double* out) {
 }
 SB_API int orc_index_to_level(int id) { return indexToLevel(id); }
 
+/*
+ * Categorical binning at load, restated (f1):
+ *   CommonUtils.flattenCatValGrp (util/CommonUtils.java:1767-1775): isNotBlank(group) ? Splitter.on("@^").split(group) : [];
+ *   DTWorker.init (dt/DTWorker.java:362-376): tmpMap.put(cval, i) for every member of binCategory.get(i), in order;
+ *   DTWorker.load (dt/DTWorker.java:1152-1169): "" -> binCategory.size(); not in the map -> binCategory.size().
+ * The map is not built: the groups are scanned in order and the LAST one holding the value wins, which is what a
+ * sequence of HashMap.put calls leaves behind.
+ */
+static bool javaIsBlank(const std::string& s) {
+    for (unsigned char c : s)
+        if (!(c == ' ' || (c >= 0x09 && c <= 0x0d) || (c >= 0x1c && c <= 0x1f))) return false;
+    return true;
+}
+static std::vector<std::string> flattenCatValGrp(const std::string& categoricalValGrp) {
+    std::vector<std::string> catVals;
+    if (!javaIsBlank(categoricalValGrp)) {
+        size_t start = 0;
+        while (true) {
+            const size_t hit = categoricalValGrp.find("@^", start);
+            if (hit == std::string::npos) {
+                catVals.push_back(categoricalValGrp.substr(start));
+                break;
+            }
+            catVals.push_back(categoricalValGrp.substr(start, hit - start));
+            start = hit + 2;
+        }
+    }
+    return catVals;
+}
+/* pieces of one group, '\n'-joined into out (cap bytes); returns the number of pieces */
+SB_API int orc_flatten_cat_val_grp(const char* group, char* out, int cap) {
+    const std::vector<std::string> v = flattenCatValGrp(group);
+    std::string joined;
+    for (size_t i = 0; i < v.size(); ++i) joined += (i ? "\n" : "") + v[i];
+    if ((int)joined.size() + 1 > cap) return -1;
+    std::memcpy(out, joined.c_str(), joined.size() + 1);
+    return (int)v.size();
+}
+SB_API int orc_category_index(const char* const* bin_category, int n_categories, const char* input) {
+    short shortValue = (short)n_categories;
+    if (input == nullptr || input[0] == '\0') return shortValue;
+    int categoricalIndex = -1;  // null
+    for (int i = 0; i < n_categories; ++i)
+        for (const std::string& cval : flattenCatValGrp(bin_category[i]))
+            if (cval == input) categoricalIndex = i;
+    shortValue = categoricalIndex < 0 ? (short)-1 : (short)categoricalIndex;
+    if (shortValue == -1) shortValue = (short)n_categories;
+    return shortValue;
+}
+
 }  // extern "C"

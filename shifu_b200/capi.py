@@ -270,6 +270,8 @@ EXPORTS = [
     "sb_sample_weights_stratified", "sb_sample_poisson", "sb_scorer_create", "sb_scorer_destroy", "sb_scorer_score", "sb_scorer_last_kernel_ms",
     "sbh_master_create", "sbh_master_destroy", "sbh_master_initial", "sbh_master_do_compute", "sbh_master_tree_count",
     "sbh_master_halted", "sbh_master_export_tree",
+    "sb_msg_pack", "sb_msg_unpack", "sb_msg_iter_in", "sb_msg_free",
+    "sb_category_map_create", "sb_category_map_lookup", "sb_category_map_destroy",
 ]
 
 _lib = None
@@ -340,6 +342,17 @@ def load_library(path=None):
     lib.sbh_master_halted.argtypes = [H]
     lib.sbh_master_export_tree.argtypes = [H, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.sb_error_sums_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]
+    lib.sb_msg_pack.argtypes = [C.POINTER(SbIterIn), C.c_int64, C.c_void_p, C.c_int64]
+    lib.sb_msg_pack.restype = C.c_int64
+    lib.sb_msg_unpack.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]
+    lib.sb_msg_iter_in.argtypes = [C.c_void_p]
+    lib.sb_msg_iter_in.restype = C.POINTER(SbIterIn)
+    lib.sb_msg_free.argtypes = [C.c_void_p]
+    lib.sb_msg_free.restype = None
+    lib.sb_category_map_create.argtypes = [C.POINTER(C.c_char_p), C.c_int32, C.POINTER(C.c_void_p)]
+    lib.sb_category_map_lookup.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.c_int64, C.c_void_p, C.c_int32]
+    lib.sb_category_map_destroy.argtypes = [C.c_void_p]
+    lib.sb_category_map_destroy.restype = None
     if path is None:
         _lib = lib
     return lib
@@ -654,3 +667,28 @@ class NativeMaster:
         check(self.lib, self.lib.sbh_master_export_tree(self.h, index, nodes, nn.value, pool.ctypes.data, pb.value,
                                                         extras.ctypes.data, C.byref(nn), C.byref(pb)))
         return list(nodes)[:nn.value], pool[:pb.value], extras[:nn.value]
+
+
+class CategoryMap:
+    """ColumnConfig.binCategory -> bin indices (sb_category_map_*): groups "a@^b" share an index, empty and unknown
+    values get the missing-value bin len(bin_category)."""
+
+    def __init__(self, bin_category):
+        self.lib = load_library()
+        self.n = len(bin_category)
+        arr = (C.c_char_p * max(self.n, 1))(*[c.encode("utf-8") for c in bin_category])
+        self.h = C.c_void_p()
+        check(self.lib, self.lib.sb_category_map_create(arr, self.n, C.byref(self.h)))
+
+    def lookup(self, values):
+        n = len(values)
+        width = 2 if self.n + 1 > 256 else 1
+        out = np.zeros(n, dtype=np.uint16 if width == 2 else np.uint8)
+        arr = (C.c_char_p * max(n, 1))(*[None if v is None else v.encode("utf-8") for v in values])
+        check(self.lib, self.lib.sb_category_map_lookup(self.h, arr, n, out.ctypes.data, width))
+        return out
+
+    def close(self):
+        if self.h:
+            self.lib.sb_category_map_destroy(self.h)
+            self.h = C.c_void_p()

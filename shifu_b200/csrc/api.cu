@@ -1085,6 +1085,7 @@ SB_API int sb_load_rows(sb_handle* h, int32_t is_validation, int64_t n_rows, con
     SB_CUDA(cudaSetDevice(h->cfg.device));
     RowSet& r = is_validation ? h->valid : h->train;
     if (r.loaded) return fail(SB_ERR_UNSUPPORTED, "rows of this set were already loaded (one load call per set)");
+    if (n_rows >= (int64_t)0xffffffff) return fail(SB_ERR_UNSUPPORTED, "2^32 - 1 rows or more in one handle (row indices are 32-bit on the device): shard the rows over several GPUs");
     const int F = h->cfg.n_features, W = h->cfg.weights_per_row;
     r.n = n_rows;
     r.n_features = F;
@@ -1127,6 +1128,7 @@ SB_API int sb_load_rows_device(sb_handle* h, int32_t is_validation, int64_t n_ro
     SB_CUDA(cudaSetDevice(h->cfg.device));
     RowSet& r = is_validation ? h->valid : h->train;
     if (r.loaded) return fail(SB_ERR_UNSUPPORTED, "rows of this set were already loaded (one load call per set)");
+    if (n_rows >= (int64_t)0xffffffff) return fail(SB_ERR_UNSUPPORTED, "2^32 - 1 rows or more in one handle (row indices are 32-bit on the device): shard the rows over several GPUs");
     const int F = h->cfg.n_features;
     r.n = n_rows;
     r.n_features = F;
@@ -1146,6 +1148,7 @@ SB_API int sb_load_synthetic(sb_handle* h, int32_t is_validation, int64_t row0, 
     SB_CUDA(cudaSetDevice(h->cfg.device));
     RowSet& r = is_validation ? h->valid : h->train;
     if (r.loaded) return fail(SB_ERR_UNSUPPORTED, "rows of this set were already loaded (one load call per set)");
+    if (n_rows >= (int64_t)0xffffffff) return fail(SB_ERR_UNSUPPORTED, "2^32 - 1 rows or more in one handle (row indices are 32-bit on the device): shard the rows over several GPUs");
     const int F = h->cfg.n_features, W = h->cfg.weights_per_row;
     r.n = n_rows;
     r.n_features = F;
@@ -1254,7 +1257,6 @@ SB_API int sb_sample_weights_stratified(sb_handle* h, int32_t w_index, int64_t s
     if (!r.loaded || !r.weights) return fail(SB_ERR_STATE, "training rows not loaded (or adopted without a weight array)");
     if (w_index < 0 || w_index >= h->cfg.weights_per_row) return fail(SB_ERR_INVALID, "weight index out of range");
     if (n_classes < 1 || n_classes > 64) return fail(SB_ERR_INVALID, "n_classes must be in [1, 64]");
-    if (r.n >= (int64_t)0xffffffff) return fail(SB_ERR_UNSUPPORTED, "more than 2^32 - 1 rows per handle");
     SB_CUDA(cudaSetDevice(h->cfg.device));
     const size_t n = (size_t)std::max<int64_t>(r.n, 1);
     const size_t temp_bytes = stratified_temp_bytes(r.n);
