@@ -489,6 +489,10 @@ SB_API int sb_set_profiling(sb_handle* h, int32_t on);
 SB_API int sb_hist_time(sb_handle* h, float* ms_total, int32_t* n_passes, int32_t* n_launches);
 /* Counters since creation: kernels launched by this library, bytes copied H2D / D2H. */
 SB_API int sb_counters(sb_handle* h, int64_t* launches, int64_t* h2d_bytes, int64_t* d2h_bytes);
+/* Rows the statistics kernels actually read since creation (or since the last call with reset != 0): with histogram
+   subtraction a pass below the root reads only the rows of the smaller child of every sibling pair.  For reporting a
+   bandwidth that counts streamed bytes, not the bytes a pass over every row would move.  Synchronises the stream. */
+SB_API int sb_rows_streamed(sb_handle* h, int64_t* rows, int32_t reset);
 /* Fills device memory with the synthetic data set of SURVEY.md 8(d) (counter-based splitmix64) and loads it:
    n_rows rows starting at global row `row0`, all features uint8 with n_bins[f] uniform bins.
    label_kind 0: binary label from a 5-feature logistic with 10% flips (C2); 1: threshold rule (C1). */

@@ -270,7 +270,7 @@ EXPORTS = [
     "sb_sample_weights_stratified", "sb_sample_poisson", "sb_scorer_create", "sb_scorer_destroy", "sb_scorer_score", "sb_scorer_last_kernel_ms",
     "sbh_master_create", "sbh_master_destroy", "sbh_master_initial", "sbh_master_do_compute", "sbh_master_tree_count",
     "sbh_master_halted", "sbh_master_export_tree",
-    "sb_msg_pack", "sb_msg_unpack", "sb_msg_iter_in", "sb_msg_free",
+    "sb_rows_streamed", "sb_msg_pack", "sb_msg_unpack", "sb_msg_iter_in", "sb_msg_free",
     "sb_category_map_create", "sb_category_map_lookup", "sb_category_map_destroy",
 ]
 
@@ -342,6 +342,7 @@ def load_library(path=None):
     lib.sbh_master_halted.argtypes = [H]
     lib.sbh_master_export_tree.argtypes = [H, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.sb_error_sums_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]
+    lib.sb_rows_streamed.argtypes = [H, C.POINTER(C.c_int64), C.c_int32]
     lib.sb_msg_pack.argtypes = [C.POINTER(SbIterIn), C.c_int64, C.c_void_p, C.c_int64]
     lib.sb_msg_pack.restype = C.c_int64
     lib.sb_msg_unpack.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]
@@ -571,6 +572,12 @@ class Worker:
         a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
         check(self.lib, self.lib.sb_counters(self.h, C.byref(a), C.byref(b), C.byref(c)))
         return a.value, b.value, c.value
+
+    def rows_streamed(self, reset=False):
+        """Rows the statistics kernels read since creation / the last reset."""
+        r = C.c_int64()
+        check(self.lib, self.lib.sb_rows_streamed(self.h, C.byref(r), int(reset)))
+        return r.value
 
     def set_profiling(self, on=True):
         check(self.lib, self.lib.sb_set_profiling(self.h, int(on)))

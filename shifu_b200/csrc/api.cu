@@ -5,6 +5,7 @@
 #include <nccl.h>  // types and enums only: the library is opened at run time (sb_dist_init)
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -125,6 +126,8 @@ struct sb_handle {
     float* d_scales = nullptr;        // 3
     double* d_inv_scales = nullptr;   // 3
     uint32_t* d_error_flag = nullptr;
+    unsigned long long* d_rows_streamed = nullptr;  // active rows the statistics kernels read (row-list passes)
+    int64_t rows_streamed_host = 0;                 // the same for passes without row lists (every row, once)
     int* d_cnt_shift = nullptr;
     // row-list path buffers
     DevBuf<uint32_t> rl_counts;   // [2][n_groups * n_ranges + 1]: counts, then their exclusive scan
@@ -155,6 +158,10 @@ struct sb_handle {
 
     int64_t launches_count = 0, h2d_bytes = 0, d2h_bytes = 0;
 
+    // SB_TRACE=1 in the environment: host / device timeline of every pass, printed by sb_destroy (developer aid)
+    struct PassTrace { double t0, t_begin, t_stats, t_enq, t_sync; cudaEvent_t e0, e1; int n_todo; double sub[6]; };
+    bool trace = false;
+    std::vector<PassTrace> passes_trace;
     // optional per-pass timing of the histogram kernel (CUDA events on the launching stream)
     bool profiling = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
@@ -162,6 +169,29 @@ struct sb_handle {
 };
 
 namespace {
+
+double now_ms() {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+void dump_trace(sb_handle* h) {
+    double last_sync = 0;
+    fprintf(stderr, "SB_TRACE rank %d: pass todo | host gap before, begin, stats enqueue, finish enqueue, sync wait | wall, gpu busy (ms)\n", h->rank);
+    for (size_t i = 0; i < h->passes_trace.size(); ++i) {
+        auto& p = h->passes_trace[i];
+        float gpu = 0;
+        cudaEventElapsedTime(&gpu, p.e0, p.e1);
+        fprintf(stderr, "SB_TRACE %4zu %4d | %7.3f %7.3f %7.3f %7.3f %7.3f | %7.3f %7.3f\n", i, p.n_todo,
+                last_sync > 0 ? p.t0 - last_sync : 0.0, p.t_begin - p.t0, p.t_stats - p.t_begin, p.t_enq - p.t_stats,
+                p.t_sync - p.t_enq, p.t_sync - p.t0, (double)gpu);
+        fprintf(stderr, "SB_TRACE      begin parts: layout+memset %.3f  trees+switch kernels %.3f  scales %.3f  plan_hist %.3f  plan_split %.3f\n",
+                p.sub[0], p.sub[1], p.sub[2], p.sub[3], p.sub[4]);
+        last_sync = p.t_sync;
+        cudaEventDestroy(p.e0);
+        cudaEventDestroy(p.e1);
+    }
+    h->passes_trace.clear();
+}
 
 bool is_variance(int imp) { return imp == SB_IMPURITY_VARIANCE || imp == SB_IMPURITY_FRIEDMANMSE; }
 
@@ -768,7 +798,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 }
                 la.offsets = h->rl_tables.p; la.chunk_begin = h->rl_tables.p + 257; la.chunk_end = h->rl_tables.p + 257 + max_chunks;
                 la.chunk_group = h->rl_chunk_group.p; la.n_chunks = h->rl_chunk_group.p + max_chunks; la.max_chunks = max_chunks;
-                la.ops = h->rl_ops.p; la.error_flag = h->d_error_flag;
+                la.ops = h->rl_ops.p; la.error_flag = h->d_error_flag; la.rows_streamed = h->d_rows_streamed;
                 HistRowsArgs& ra = L.rows;
                 ra.rm_bins = tr.bins_rm; ra.fpad = tr.fpad; ra.ops = la.ops; ra.chunk_group = la.chunk_group;
                 ra.chunk_begin = la.chunk_begin; ra.chunk_end = la.chunk_end; ra.n_chunks = la.n_chunks;
@@ -978,6 +1008,7 @@ int run_histograms(sb_handle* h) {
         } else {
             SB_CUDA(hist_launch(L.kind, L.cnt_int, L.args, h->train.tensor_map, L.grid, L.smem, h->stream));
             h->launches_count += 1;
+            h->rows_streamed_host += h->train.n * L.args.n_groups;
         }
     }
     return SB_OK;
@@ -1027,6 +1058,7 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
         if (h->n_bins[f] > 256) h->wide_index[f] = h->n_wide++;
     if (cfg->bin_boundary) h->bin_boundary.assign(cfg->bin_boundary, cfg->bin_boundary + nb);
     h->cfg.n_bins = nullptr; h->cfg.is_categorical = nullptr; h->cfg.column_num = nullptr; h->cfg.bin_boundary = nullptr;
+    h->trace = getenv("SB_TRACE") != nullptr;
     h->enable_row_lists = (cfg->flags & SB_FLAG_NO_ROW_LISTS) == 0;
     h->enable_subtraction = (cfg->flags & SB_FLAG_NO_SUBTRACTION) == 0;
     h->enable_root_cache = (cfg->flags & SB_FLAG_NO_ROOT_COUNT_CACHE) == 0;
@@ -1041,6 +1073,8 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
     SB_CUDA(cudaMalloc(&h->d_scales, 16));
     SB_CUDA(cudaMalloc(&h->d_inv_scales, 32));
     SB_CUDA(cudaMalloc(&h->d_error_flag, 4));
+    SB_CUDA(cudaMalloc(&h->d_rows_streamed, 8));
+    SB_CUDA(cudaMemset(h->d_rows_streamed, 0, 8));
     SB_CUDA(cudaMemset(h->d_error_flag, 0, 4));
     SB_CUDA(cudaMalloc(&h->d_cnt_shift, 8));
     SB_CUDA(cudaMemset(h->d_cnt_shift, 0, 8));
@@ -1052,6 +1086,7 @@ SB_API void sb_destroy(sb_handle* h) {
     if (!h) return;
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
+    if (h->trace) dump_trace(h);
     free_rowset(h->train);
     free_rowset(h->valid);
     for (auto& kv : h->trees) free_tree(kv.second);
@@ -1069,6 +1104,7 @@ SB_API void sb_destroy(sb_handle* h) {
     if (h->d_scales) cudaFree(h->d_scales);
     if (h->d_inv_scales) cudaFree(h->d_inv_scales);
     if (h->d_error_flag) cudaFree(h->d_error_flag);
+    if (h->d_rows_streamed) cudaFree(h->d_rows_streamed);
     if (h->d_cnt_shift) cudaFree(h->d_cnt_shift);
     delete h;
 }
@@ -1301,6 +1337,15 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     if (in->continuous_running_start) return fail(SB_ERR_UNSUPPORTED, "continuous training is handled on the Java side");
     if (in->n_trees < 1 || !in->trees) return fail(SB_ERR_INVALID, "no trees");
     SB_CUDA(cudaSetDevice(h->cfg.device));
+    if (h->trace) {
+        sb_handle::PassTrace p{};
+        p.t0 = now_ms();
+        p.n_todo = in->n_todo;
+        cudaEventCreate(&p.e0);
+        cudaEventCreate(&p.e1);
+        cudaEventRecord(p.e0, h->stream);
+        h->passes_trace.push_back(p);
+    }
     h->begun = false;
     h->stats_ready = false;
     // A pass that does not reach finish_check (an error, or a second begin) must not leave the next one pairing its
@@ -1323,6 +1368,8 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     RowSet& tr = h->train;
     RowSet& va = h->valid;
     const int loss = h->cfg.loss;
+    double tt0 = h->trace ? now_ms() : 0;
+    if (h->trace) h->passes_trace.back().sub[0] = tt0 - h->passes_trace.back().t0;
 
     if (h->cfg.is_gbdt) {
         const int curr = in->n_trees - 1;  // currTreeIndex (dt/DTWorker.java:620)
@@ -1446,6 +1493,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
         }
     }
 
+    if (h->trace) { const double t = now_ms(); h->passes_trace.back().sub[1] = t - tt0; tt0 = t; }
     // Fixed-point scales: maxima of the per-row contributions.  They change only when Data.output or the sample
     // weights change, i.e. at a GBT tree switch (RF: never after load), so they are computed once per tree and
     // the accumulators of all levels of a tree share one scale.
@@ -1471,8 +1519,10 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
         }
         h->scales_valid = true;
     }
+    if (h->trace) { const double t = now_ms(); h->passes_trace.back().sub[2] = t - tt0; tt0 = t; }
     rc = plan_histograms(h, in);
     if (rc != SB_OK) return rc;
+    if (h->trace) { const double t = now_ms(); h->passes_trace.back().sub[3] = t - tt0; tt0 = t; }
     if (h->pending_route) {  // no row list took the walk along: do it on its own
         SB_CUDA(launch_route(tr.d_col, h->d_feat_bins, tr.n, tr.node_id, h->pending_tree, h->d_error_flag, h->stream));
         h->launches_count += 1;
@@ -1481,6 +1531,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     rc = plan_split_tasks(h);
     if (rc != SB_OK) return rc;
     h->begun = true;
+    if (h->trace) { h->passes_trace.back().t_begin = now_ms(); h->passes_trace.back().sub[4] = h->passes_trace.back().t_begin - tt0; }
     return SB_OK;
 }
 
@@ -1529,6 +1580,7 @@ SB_API int sb_compute_stats(sb_handle* h) {
             SB_NCCL(nccl_api().AllReduce(h->raw.p, h->raw.p, (size_t)(2 * h->layout.total), ncclInt64, ncclSum, h->comm, h->stream));
         if (h->acc_fresh) SB_NCCL(nccl_api().AllReduce(h->d_acc, h->d_acc, 4, ncclFloat64, ncclSum, h->comm, h->stream));
     }
+    if (h->trace && !h->passes_trace.empty()) h->passes_trace.back().t_stats = now_ms();
     return SB_OK;
 }
 
@@ -1705,7 +1757,9 @@ SB_API int sb_compute_finish(sb_handle* h, sb_iter_out* out) {
     if (rc != SB_OK) return rc;
     rc = finish_enqueue(h, out);
     if (rc != SB_OK) return rc;
+    if (h->trace && !h->passes_trace.empty()) { cudaEventRecord(h->passes_trace.back().e1, h->stream); h->passes_trace.back().t_enq = now_ms(); }
     SB_CUDA(cudaStreamSynchronize(h->stream));
+    if (h->trace && !h->passes_trace.empty()) h->passes_trace.back().t_sync = now_ms();
     return finish_check(h, out);
 }
 
@@ -1719,7 +1773,9 @@ SB_API int sb_compute_finish_split(sb_handle* h, sb_iter_out* out, sb_gain* gain
     if (rc != SB_OK) return rc;
     rc = best_enqueue(h, cat_bits != nullptr);
     if (rc != SB_OK) return rc;
+    if (h->trace && !h->passes_trace.empty()) { cudaEventRecord(h->passes_trace.back().e1, h->stream); h->passes_trace.back().t_enq = now_ms(); }
     SB_CUDA(cudaStreamSynchronize(h->stream));
+    if (h->trace && !h->passes_trace.empty()) h->passes_trace.back().t_sync = now_ms();
     rc = finish_check(h, out);
     if (rc != SB_OK) return rc;
     best_deliver(h, gains, cat_bits);
@@ -1772,6 +1828,20 @@ SB_API int sb_time_stats_pass(sb_handle* h, int32_t n_repeat, float* ms_hist_ker
     cudaEventDestroy(e1);
     if (ms_hist_kernel) *ms_hist_kernel = (float)(sum_ms / n_repeat);
     if (ms_total) *ms_total = (float)(sum_ms / n_repeat);
+    return SB_OK;
+}
+
+SB_API int sb_rows_streamed(sb_handle* h, int64_t* rows, int32_t reset) {
+    if (!h || !rows) return fail(SB_ERR_INVALID, "null argument");
+    SB_CUDA(cudaSetDevice(h->cfg.device));
+    unsigned long long dev = 0;
+    SB_CUDA(cudaMemcpyAsync(&dev, h->d_rows_streamed, 8, cudaMemcpyDeviceToHost, h->stream));
+    SB_CUDA(cudaStreamSynchronize(h->stream));
+    *rows = (int64_t)dev + h->rows_streamed_host;
+    if (reset) {
+        SB_CUDA(cudaMemsetAsync(h->d_rows_streamed, 0, 8, h->stream));
+        h->rows_streamed_host = 0;
+    }
     return SB_OK;
 }
 

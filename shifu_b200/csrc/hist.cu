@@ -517,17 +517,25 @@ __device__ __forceinline__ void rows_consume(const HistRowsArgs& a, const RowOps
             uint32_t lo0[BATCH], lo1[BATCH], lo2[BATCH], hi0[BATCH], hi1[BATCH], hi2[BATCH];
 #pragma unroll
             for (int j = 0; j < BATCH; ++j) {  // phase 1: operands, addresses, low-word atomics
-                const uint4 v0 = *reinterpret_cast<const uint4*>(&v[jb + j]);       // row, cnt_hi, slot, cnt_lo
                 uint4 v1;  // sum / sq words (VARIANCE) or the class byte offset (CLASS)
                 if (KIND == STAT_VARIANCE) v1 = *reinterpret_cast<const uint4*>(&v[jb + j].q[0]);
                 else v1 = make_uint4(v[jb + j].q[0], 0u, 0u, 0u);
-                const uint32_t slot = v0.z;
+                uint32_t slot;
+                lo1[j] = hi1[j] = lo2[j] = hi2[j] = 0;
+                if (KIND == STAT_VARIANCE && CNT_INT) {
+                    // packed operands: one 128-bit broadcast load carries slot, count and both statistics
+                    slot = rowops_upper(v1.w);
+                    lo0[j] = rowops_upper(v1.y); hi0[j] = 0;
+                    lo1[j] = v1.x; hi1[j] = rowops_hi_signed(v1.y); lo2[j] = v1.z; hi2[j] = rowops_hi_unsigned(v1.w);
+                } else {
+                    const uint4 v0 = *reinterpret_cast<const uint4*>(&v[jb + j]);  // row, cnt_hi, slot, cnt_lo
+                    slot = v0.z;
+                    lo0[j] = v0.w; hi0[j] = v0.y;
+                    if (KIND == STAT_VARIANCE) { lo1[j] = v1.x; hi1[j] = v1.y; lo2[j] = v1.z; hi2[j] = v1.w; }
+                }
                 const bool rowok = (wr0 + jb + j < rows) && slot < (uint32_t)gcount;
                 uint32_t base = lane_base + slot * slot_stride;
-                lo0[j] = v0.w; hi0[j] = v0.y;
-                lo1[j] = hi1[j] = lo2[j] = hi2[j] = 0;
-                if (KIND == STAT_VARIANCE) { lo1[j] = v1.x; hi1[j] = v1.y; lo2[j] = v1.z; hi2[j] = v1.w; }
-                else base += v1.x * FPL;  // class words
+                if (KIND != STAT_VARIANCE) base += v1.x * FPL;  // class words
                 // ALLF: one select per row; a bad row lands in the dummy bin whatever its bins are
                 const uint32_t rbase = rowok ? base : dummy_addr;
                 const uint32_t bmul = rowok ? bin_stride : 0u;
@@ -804,8 +812,13 @@ __global__ void __launch_bounds__(W_NTHREADS, 1) hist_rows_wide_kernel(const His
                 for (int hs = 0; hs < 2; ++hs) {
                     const int r = min(wr0 + hs * 4 + q, R_TILE - 1);
                     const RowOps* v = ops_s + s * R_TILE + r;
-                    const uint4 v0 = *reinterpret_cast<const uint4*>(v);          // row, cnt_hi, slot, cnt_lo
-                    const uint4 v1 = *reinterpret_cast<const uint4*>(&v->q[0]);   // sum / sq words
+                    uint4 v0 = *reinterpret_cast<const uint4*>(v);                // row, cnt_hi, slot, cnt_lo
+                    uint4 v1 = *reinterpret_cast<const uint4*>(&v->q[0]);         // sum / sq words
+                    if (KIND == STAT_VARIANCE && CNT_INT) {  // packed high words (rowops_pack): same lists as the narrow tiles
+                        v0.w = rowops_upper(v1.y); v0.y = 0u; v0.z = rowops_upper(v1.w);
+                        if (v0.z == 0xffffu) v0.z = 0xffffffffu;
+                        v1.y = rowops_hi_signed(v1.y); v1.w = rowops_hi_unsigned(v1.w);
+                    }
                     const uint32_t slot = v0.z;
                     const bool ok = (wr0 + hs * 4 + q < rows) && slot < (uint32_t)gcount && feat_ok &&
                                     (fm_tab[slot & (R_MAX_GS - 1)] & feat_bit) != 0u && bw_cur[hs] < (uint32_t)bins_pad;

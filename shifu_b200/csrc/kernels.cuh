@@ -42,6 +42,16 @@ struct __align__(16) RowOps {   // one active row of the pass, in slot-group ord
     uint32_t cnt_lo;
     uint32_t q[4];              // VARIANCE: (sum_lo, sum_hi, sq_lo, sq_hi); CLASS: (class byte offset, -, -, -)
 };
+// Variance statistics with integer counts (the GBT default): the high words of the two fixed-point operands need 13
+// bits (|q| < 2^44), so their upper halves carry what a consumer would otherwise fetch with a second shared-memory
+// load -- q[1] = (count << 16) | (sum_hi & 0xffff), q[3] = (slot << 16) | (sq_hi & 0xffff): ONE 128-bit broadcast load per
+// row and tile gives a consumer warp everything (the shared-memory wavefronts of these loads are a fifth of the
+// kernel's LSU work).  A row that must be skipped has slot 0xffff.
+__host__ __device__ inline uint32_t rowops_pack(uint32_t hi_word, uint32_t upper) { return (hi_word & 0xffffu) | (upper << 16); }
+__host__ __device__ inline uint32_t rowops_hi_signed(uint32_t packed) { return (uint32_t)((int32_t)(packed << 16) >> 16); }
+__host__ __device__ inline uint32_t rowops_hi_unsigned(uint32_t packed) { return packed & 0xffffu; }
+__host__ __device__ inline uint32_t rowops_upper(uint32_t packed) { return packed >> 16; }
+
 struct TreeView {  // DeviceTree as kernels see it
     const int32_t* feat;
     const int32_t* mask_off;
@@ -83,6 +93,7 @@ struct RowListArgs {
     int max_chunks;
     RowOps* ops;               // [n]
     uint32_t* error_flag;
+    unsigned long long* rows_streamed;  // device counter: += active rows of this list (what the statistics kernels read)
 };
 cudaError_t launch_transpose_bins(const uint8_t* cm, int64_t pitch, int n_features, const int32_t* feat_of_pos, int64_t n, uint8_t* rm, int fpad,
                                   cudaStream_t s);

@@ -164,7 +164,7 @@ __global__ void rowlist_chunks_kernel(const uint32_t* __restrict__ scanned, int6
                                       int64_t max_chunk_rows, int target_chunks, int n_tiles, int64_t* __restrict__ offsets,
                                       int32_t* __restrict__ chunk_group, int64_t* __restrict__ chunk_begin,
                                       int64_t* __restrict__ chunk_end, int32_t* __restrict__ n_chunks, int max_chunks,
-                                      uint32_t* error_flag) {
+                                      uint32_t* error_flag, unsigned long long* rows_streamed) {
     __shared__ int64_t off[257];
     for (int g = threadIdx.x; g <= n_groups; g += blockDim.x) {
         int64_t v;
@@ -178,6 +178,7 @@ __global__ void rowlist_chunks_kernel(const uint32_t* __restrict__ scanned, int6
         // chunk size from the number of ACTIVE rows of this pass (with subtraction most passes touch a fraction of the
         // rows): about target_chunks chunks, so the grid fills the GPU several times over whatever the list length
         const int64_t total = off[n_groups];
+        if (rows_streamed) atomicAdd(rows_streamed, (unsigned long long)total);
         // number of chunks: at least what the accumulator headroom asks for (max_chunk_rows), about target_chunks, and
         // such that chunks x tiles fills whole waves of 148 blocks (one block per SM) with room for the partial chunk
         // that ends every group -- a launch of 2.6 waves costs 3
@@ -232,6 +233,10 @@ __device__ __forceinline__ RowOps make_row_ops(uint32_t r, int s, int gs, float 
         const long long qq = __float2ll_rn(__fmul_rn(qw, sc2));
         o.q[0] = (uint32_t)qs; o.q[1] = (uint32_t)(qs >> 32);
         o.q[2] = (uint32_t)qq; o.q[3] = (uint32_t)(qq >> 32);
+        if (CNT_INT) {  // packed high words, see rowops_pack in kernels.cuh
+            o.q[1] = rowops_pack(o.q[1], (uint32_t)qc);
+            o.q[3] = rowops_pack(o.q[3], o.slot);
+        }
     } else {
         const int cls = (int)(__fadd_rn(y, 0.000001f));
         if (cls < 0 || cls >= stats_size) { atomicOr(error_flag, 1u); o.slot = 0xffffffffu; o.q[0] = 0; }
@@ -303,6 +308,7 @@ __global__ void rowlist_ops_kernel(int64_t total, const int32_t* __restrict__ no
             skip.cnt_lo = skip.cnt_hi = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) skip.q[k] = 0;
+            if (KIND == STAT_VARIANCE && CNT_INT) skip.q[3] = rowops_pack(0u, 0xffffu);
             ops[i] = skip;
             continue;
         }
@@ -352,7 +358,7 @@ cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s) {
     if (a.identity) {
         // no grouping: one group = all rows in storage order
         rowlist_chunks_kernel<<<1, 256, 0, s>>>(nullptr, 0, n, 1, a.chunk_rows, a.target_chunks, a.n_tiles, a.offsets, a.chunk_group,
-                                                a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks, a.error_flag);
+                                                a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks, a.error_flag, a.rows_streamed);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
         int64_t g = (n + TPB - 1) / TPB;
@@ -382,7 +388,7 @@ cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s) {
     e = cub::DeviceScan::ExclusiveSum(a.temp, temp, (const uint32_t*)a.counts, a.scanned, items, s);
     if (e != cudaSuccess) return e;
     rowlist_chunks_kernel<<<1, 256, 0, s>>>(a.scanned, n_ranges, n, a.n_groups, a.chunk_rows, a.target_chunks, a.n_tiles, a.offsets,
-                                            a.chunk_group, a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks, a.error_flag);
+                                            a.chunk_group, a.chunk_begin, a.chunk_end, a.n_chunks, a.max_chunks, a.error_flag, a.rows_streamed);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
 #define SCATTER(K, C)                                                                                                     \

@@ -54,7 +54,13 @@ def labels(seed, cols, n_bins, row0, n_rows, label_kind=0, weighted=False):
 
 def make(seed, n_bins, row0, n_rows, label_kind=0, weighted=False):
     F = len(n_bins)
-    cols = [bins_column(seed, f, F, int(n_bins[f]), row0, n_rows) for f in range(F)]
+    if n_rows * F >= 50_000_000:  # numpy releases the GIL inside the hash arithmetic: one column per thread
+        import os
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=min(32, os.cpu_count() or 1)) as ex:
+            cols = list(ex.map(lambda f: bins_column(seed, f, F, int(n_bins[f]), row0, n_rows), range(F)))
+    else:
+        cols = [bins_column(seed, f, F, int(n_bins[f]), row0, n_rows) for f in range(F)]
     y, sig = labels(seed, cols, n_bins, row0, n_rows, label_kind, weighted)
     return cols, y, sig
 
