@@ -25,22 +25,104 @@ int fail(int code, const std::string& msg) {
 }
 
 template <typename T>
-struct DevBuf {  // grow-only device buffer
+struct DevBuf {  // grow-only device buffer; or an alias of a piece of the per-pass staging arena (not owned)
     T* p = nullptr;
     size_t cap = 0;
-    cudaError_t reserve(size_t n) {
-        if (n <= cap) return cudaSuccess;
-        if (p) cudaFree(p);
+    bool owned = true;
+    // Growth is stream-ordered (cudaMallocAsync / cudaFreeAsync): cudaFree would wait for everything queued on the
+    // device, and the buffers of a pass grow while the kernels of its first half are still running.
+    cudaError_t reserve(cudaStream_t stream, size_t n) {
+        if (owned && n <= cap) return cudaSuccess;
+        if (p && owned) cudaFreeAsync(p, stream);
         p = nullptr;
         cap = 0;
-        size_t want = std::max<size_t>(n, 16);
-        cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+        owned = true;
+        // 4x: the statistics of a level-wise tree double with every level, and a pool that has to map new memory
+        // costs about 10 us per MB
+        size_t want = std::max<size_t>(cap ? 4 * n : n, 16);
+        cudaError_t e = cudaMallocAsync((void**)&p, want * sizeof(T), stream);
         if (e == cudaSuccess) cap = want;
         return e;
     }
+    void alias(T* q) {
+        if (p && owned) cudaFreeAsync(p, 0);
+        p = q;
+        cap = 0;
+        owned = false;
+    }
     void release() {
-        if (p) cudaFree(p);
+        if (p && owned) cudaFreeAsync(p, 0);
         p = nullptr;
+        cap = 0;
+        owned = true;
+    }
+};
+
+// The small tables of a pass (tree arrays, tile / slot / offset tables, sibling pairs, split tasks) are written into ONE
+// pinned host arena and reach the device with one asynchronous copy per flush, instead of a dozen separate copies
+// from pageable memory -- those are staged by the driver and, above 64 KB, wait for the work already queued on the
+// stream.  The arena is recycled at the start of every pass: a pass ends with a stream synchronisation, so by then
+// both the copies and the kernels that read the device side are done.
+struct Stager {
+    uint8_t* host = nullptr;  // pinned
+    uint8_t* dev = nullptr;
+    size_t cap = 0, off = 0, flushed = 0;
+    std::vector<std::pair<uint8_t*, uint8_t*>> retired;  // arenas that were too small; alive until the next reset
+    cudaError_t grow(size_t need, cudaStream_t stream) {
+        cudaError_t e = flush(stream);  // what was handed out from the old arena must still arrive
+        if (e != cudaSuccess) return e;
+        if (host) retired.push_back({host, dev});
+        host = dev = nullptr;
+        const size_t want = std::max<size_t>(std::max<size_t>(2 * cap, need + need / 2), 1 << 20);
+        e = cudaMallocHost((void**)&host, want);
+        if (e != cudaSuccess) return e;
+        e = cudaMalloc((void**)&dev, want);
+        if (e != cudaSuccess) return e;
+        cap = want;
+        off = flushed = 0;
+        return cudaSuccess;
+    }
+    // room for n elements: *hp = where to write them now, *d = where they will be on the device after the next flush
+    template <typename T>
+    cudaError_t take(size_t n, T** hp, T** d, cudaStream_t stream) {
+        const size_t bytes = n * sizeof(T);
+        size_t at = (off + 255) & ~(size_t)255;
+        if (at + bytes > cap) {
+            cudaError_t e = grow(bytes + 256, stream);
+            if (e != cudaSuccess) return e;
+            at = 0;
+        }
+        *hp = reinterpret_cast<T*>(host + at);
+        *d = reinterpret_cast<T*>(dev + at);
+        off = at + bytes;
+        return cudaSuccess;
+    }
+    template <typename T>
+    cudaError_t put(const T* src, size_t n, T** d, cudaStream_t stream) {
+        T* hp = nullptr;
+        cudaError_t e = take(n, &hp, d, stream);
+        if (e == cudaSuccess && n) memcpy(hp, src, n * sizeof(T));
+        return e;
+    }
+    cudaError_t flush(cudaStream_t stream) {
+        if (off == flushed) return cudaSuccess;
+        cudaError_t e = cudaMemcpyAsync(dev + flushed, host + flushed, off - flushed, cudaMemcpyHostToDevice, stream);
+        flushed = off;
+        return e;
+    }
+    void reset() {  // only after a stream synchronisation
+        for (auto& r : retired) {
+            cudaFreeHost(r.first);
+            cudaFree(r.second);
+        }
+        retired.clear();
+        off = flushed = 0;
+    }
+    void release() {
+        reset();
+        if (host) cudaFreeHost(host);
+        if (dev) cudaFree(dev);
+        host = dev = nullptr;
         cap = 0;
     }
 };
@@ -81,6 +163,7 @@ struct sb_handle {
     cudaStream_t stream = nullptr;
 
     RowSet train, valid;
+    Stager stage;
     int32_t* d_feat_bins = nullptr;
     std::map<int, DeviceTree> trees;  // by tree id
     int tracked_tree = -1;            // GBT: tree id whose node ids train.node_id currently holds
@@ -193,6 +276,18 @@ void dump_trace(sb_handle* h) {
     h->passes_trace.clear();
 }
 
+// stage `n` elements and let `buf` point at their place in the device arena
+template <typename T>
+cudaError_t stage_into(sb_handle* h, DevBuf<T>& buf, const T* src, size_t n) {
+    T* d = nullptr;
+    cudaError_t e = h->stage.put(src, n, &d, h->stream);
+    if (e == cudaSuccess) {
+        buf.alias(d);
+        h->h2d_bytes += (int64_t)(n * sizeof(T));
+    }
+    return e;
+}
+
 bool is_variance(int imp) { return imp == SB_IMPURITY_VARIANCE || imp == SB_IMPURITY_FRIEDMANMSE; }
 
 void free_rowset(RowSet& r) {
@@ -212,14 +307,7 @@ void free_rowset(RowSet& r) {
     r = RowSet();
 }
 
-void free_tree(DeviceTree& t) {
-    if (t.feat) cudaFree(t.feat);
-    if (t.mask_off) cudaFree(t.mask_off);
-    if (t.predict) cudaFree(t.predict);
-    if (t.has_predict) cudaFree(t.has_predict);
-    if (t.masks) cudaFree(t.masks);
-    t = DeviceTree();
-}
+void free_tree(DeviceTree& t) { t = DeviceTree(); }  // the arrays live in the per-pass staging arena
 
 TreeView view_of(const DeviceTree& t) { return TreeView{t.feat, t.mask_off, t.predict, t.has_predict, t.masks, t.capacity}; }
 
@@ -316,31 +404,18 @@ int upload_tree(sb_handle* h, const sb_tree& t, DeviceTree& d) {
     }
     if (max_id >= (1 << 24)) return fail(SB_ERR_UNSUPPORTED, "node id beyond 2^24 (MaxDepth <= 20 in the reference)");
     const int cap = max_id + 1;
-    if (cap > d.capacity) {
-        const int mask_cap = d.mask_capacity;
-        uint8_t* masks = d.masks;
-        d.masks = nullptr;
-        free_tree(d);
-        d.masks = masks;
-        d.mask_capacity = mask_cap;
-        int newcap = 256;
-        while (newcap < cap) newcap *= 2;
-        SB_CUDA(cudaMalloc(&d.feat, sizeof(int32_t) * newcap));
-        SB_CUDA(cudaMalloc(&d.mask_off, sizeof(int32_t) * newcap));
-        SB_CUDA(cudaMalloc(&d.predict, sizeof(double) * newcap));
-        SB_CUDA(cudaMalloc(&d.has_predict, newcap));
-        d.capacity = newcap;
-    }
-    if (t.mask_pool_bytes > d.mask_capacity) {
-        if (d.masks) cudaFree(d.masks);
-        int newcap = 4096;
-        while (newcap < t.mask_pool_bytes) newcap *= 2;
-        SB_CUDA(cudaMalloc(&d.masks, newcap));
-        d.mask_capacity = newcap;
-    }
-    std::vector<int32_t> feat((size_t)d.capacity, -1), moff((size_t)d.capacity, 0);
-    std::vector<double> pred((size_t)d.capacity, 0.0);
-    std::vector<uint8_t> hasp((size_t)d.capacity, 0);
+    // the arrays of a tree are rebuilt from the message every pass: they live in the staging arena of the pass
+    int32_t *feat = nullptr, *moff = nullptr;
+    double* pred = nullptr;
+    uint8_t *hasp = nullptr, *masks = nullptr;
+    SB_CUDA(h->stage.take((size_t)cap, &feat, &d.feat, h->stream));
+    SB_CUDA(h->stage.take((size_t)cap, &moff, &d.mask_off, h->stream));
+    SB_CUDA(h->stage.take((size_t)cap, &pred, &d.predict, h->stream));
+    SB_CUDA(h->stage.take((size_t)cap, &hasp, &d.has_predict, h->stream));
+    SB_CUDA(h->stage.take((size_t)std::max(t.mask_pool_bytes, 1), &masks, &d.masks, h->stream));
+    d.capacity = cap;
+    d.mask_capacity = t.mask_pool_bytes;
+    for (int i = 0; i < cap; ++i) { feat[i] = -1; moff[i] = 0; pred[i] = 0.0; hasp[i] = 0; }
     for (int i = 0; i < t.n_nodes; ++i) {
         const sb_node& nd = t.nodes[i];
         const bool routes = nd.feature >= 0 && (nd.left >= 0 || nd.right >= 0);  // dt/DTWorker.java:1041
@@ -355,13 +430,8 @@ int upload_tree(sb_handle* h, const sb_tree& t, DeviceTree& d) {
         pred[nd.id] = nd.predict;
         hasp[nd.id] = nd.has_predict ? 1 : 0;
     }
-    SB_CUDA(cudaMemcpyAsync(d.feat, feat.data(), sizeof(int32_t) * d.capacity, cudaMemcpyHostToDevice, h->stream));
-    SB_CUDA(cudaMemcpyAsync(d.mask_off, moff.data(), sizeof(int32_t) * d.capacity, cudaMemcpyHostToDevice, h->stream));
-    SB_CUDA(cudaMemcpyAsync(d.predict, pred.data(), sizeof(double) * d.capacity, cudaMemcpyHostToDevice, h->stream));
-    SB_CUDA(cudaMemcpyAsync(d.has_predict, hasp.data(), d.capacity, cudaMemcpyHostToDevice, h->stream));
-    if (t.mask_pool_bytes > 0)
-        SB_CUDA(cudaMemcpyAsync(d.masks, t.mask_pool, t.mask_pool_bytes, cudaMemcpyHostToDevice, h->stream));
-    h->h2d_bytes += (int64_t)d.capacity * 17 + t.mask_pool_bytes;
+    if (t.mask_pool_bytes > 0) memcpy(masks, t.mask_pool, (size_t)t.mask_pool_bytes);
+    h->h2d_bytes += (int64_t)cap * 17 + t.mask_pool_bytes;
     return SB_OK;
 }
 
@@ -397,16 +467,18 @@ std::vector<int> hashmap_visit_rank(const std::vector<int>& column_nums) {
     const int n = (int)column_nums.size();
     int cap = 1;
     while (cap < n) cap <<= 1;
-    std::vector<int> pos((size_t)n);
-    for (int i = 0; i < n; ++i) pos[i] = i;
     auto bucket = [cap](int k) {
         uint32_t x = (uint32_t)k;
         x ^= x >> 16;
         return (int)(x & (uint32_t)(cap - 1));
     };
-    std::stable_sort(pos.begin(), pos.end(), [&](int a, int b) { return bucket(column_nums[a]) < bucket(column_nums[b]); });
+    // a stable counting sort by bucket: first position of every bucket, then list order inside it
+    static thread_local std::vector<int> first;
+    first.assign((size_t)cap + 1, 0);
+    for (int i = 0; i < n; ++i) first[(size_t)bucket(column_nums[i]) + 1] += 1;
+    for (int b = 0; b < cap; ++b) first[(size_t)b + 1] += first[(size_t)b];
     std::vector<int> rank((size_t)n);
-    for (int i = 0; i < n; ++i) rank[pos[i]] = i;
+    for (int i = 0; i < n; ++i) rank[(size_t)i] = first[(size_t)bucket(column_nums[i])]++;
     return rank;
 }
 
@@ -502,14 +574,14 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
             pair_off[(size_t)s * F + f] = nd.offset + nd.feat_off[k];
         }
     }
-    SB_CUDA(h->tile_feats.reserve(tile_feats.size() + tile_slot0.size()));
-    SB_CUDA(h->slot_fmask.reserve(fmask.size()));
-    SB_CUDA(h->pair_off.reserve(pair_off.size()));
-    SB_CUDA(cudaMemcpyAsync(h->tile_feats.p, tile_feats.data(), tile_feats.size() * 4, cudaMemcpyHostToDevice, h->stream));
-    SB_CUDA(cudaMemcpyAsync(h->tile_feats.p + tile_feats.size(), tile_slot0.data(), tile_slot0.size() * 4, cudaMemcpyHostToDevice, h->stream));
-    SB_CUDA(cudaMemcpyAsync(h->slot_fmask.p, fmask.data(), fmask.size() * 4, cudaMemcpyHostToDevice, h->stream));
-    SB_CUDA(cudaMemcpyAsync(h->pair_off.p, pair_off.data(), pair_off.size() * 8, cudaMemcpyHostToDevice, h->stream));
-    h->h2d_bytes += tile_feats.size() * 4 + fmask.size() * 4 + pair_off.size() * 8;
+    {
+        const size_t n_tf = tile_feats.size();
+        tile_feats.insert(tile_feats.end(), tile_slot0.begin(), tile_slot0.end());  // one table: feats, then slot0
+        SB_CUDA(stage_into(h, h->tile_feats, tile_feats.data(), tile_feats.size()));
+        tile_feats.resize(n_tf);
+    }
+    SB_CUDA(stage_into(h, h->slot_fmask, fmask.data(), fmask.size()));
+    SB_CUDA(stage_into(h, h->pair_off, pair_off.data(), pair_off.size()));
 
     const int cnt_int = h->cnt_int ? 1 : 0;
     const int nw = hist_words_per_bin(h->stat_kind, cnt_int, h->stats_size);
@@ -550,12 +622,12 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 if (wt_of[f] >= 0) wfm[(size_t)s * n_wt + wt_of[f]] |= 1u << wj_of[f];
         wide_max_gs = hist_rows_wide_max_slots_per_block(bins_pad_w, nw);
         if (wide_max_gs < 1) return fail(SB_ERR_UNSUPPORTED, "a tile of 8 wide features does not fit in shared memory");
-        SB_CUDA(h->wt_tiles.reserve(wt_feats.size() + wt_slot0.size()));
-        SB_CUDA(h->wt_fmask.reserve(wfm.size()));
-        SB_CUDA(cudaMemcpyAsync(h->wt_tiles.p, wt_feats.data(), wt_feats.size() * 4, cudaMemcpyHostToDevice, h->stream));
-        SB_CUDA(cudaMemcpyAsync(h->wt_tiles.p + wt_feats.size(), wt_slot0.data(), wt_slot0.size() * 4, cudaMemcpyHostToDevice, h->stream));
-        SB_CUDA(cudaMemcpyAsync(h->wt_fmask.p, wfm.data(), wfm.size() * 4, cudaMemcpyHostToDevice, h->stream));
-        h->h2d_bytes += (wt_feats.size() + wt_slot0.size() + wfm.size()) * 4;
+        {
+            std::vector<int32_t> both(wt_feats);
+            both.insert(both.end(), wt_slot0.begin(), wt_slot0.end());
+            SB_CUDA(stage_into(h, h->wt_tiles, both.data(), both.size()));
+        }
+        SB_CUDA(stage_into(h, h->wt_fmask, wfm.data(), wfm.size()));
     }
 
     // ---- row-list path tables: tiles of 32*fpl consecutive feature slots, fpl = features per lane
@@ -627,13 +699,13 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
             }
         for (int s = 0; s < S && allf; ++s)
             if (memcmp(&rfm[(size_t)s * n_rt * fpl], full.data(), full.size() * 4) != 0) allf = 0;
-        SB_CUDA(h->rt_tiles.reserve(rt_feats.size() + 2 * rt_slot0.size()));
-        SB_CUDA(h->rt_fmask.reserve(rfm.size()));
-        SB_CUDA(cudaMemcpyAsync(h->rt_tiles.p, rt_feats.data(), rt_feats.size() * 4, cudaMemcpyHostToDevice, h->stream));
-        SB_CUDA(cudaMemcpyAsync(h->rt_tiles.p + rt_feats.size(), rt_slot0.data(), rt_slot0.size() * 4, cudaMemcpyHostToDevice, h->stream));
-        SB_CUDA(cudaMemcpyAsync(h->rt_tiles.p + rt_feats.size() + rt_slot0.size(), rt_kact.data(), rt_kact.size() * 4, cudaMemcpyHostToDevice, h->stream));
-        SB_CUDA(cudaMemcpyAsync(h->rt_fmask.p, rfm.data(), rfm.size() * 4, cudaMemcpyHostToDevice, h->stream));
-        h->h2d_bytes += (rt_feats.size() + 2 * rt_slot0.size() + rfm.size()) * 4;
+        {
+            std::vector<int32_t> all3(rt_feats);  // one table: feats, then slot0, then kact
+            all3.insert(all3.end(), rt_slot0.begin(), rt_slot0.end());
+            all3.insert(all3.end(), rt_kact.begin(), rt_kact.end());
+            SB_CUDA(stage_into(h, h->rt_tiles, all3.data(), all3.size()));
+        }
+        SB_CUDA(stage_into(h, h->rt_fmask, rfm.data(), rfm.size()));
     }
 
     // per tree: slot table + launch
@@ -653,8 +725,14 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         table_size[t] = max_id + 1;
         table_total += (size_t)table_size[t];
     }
-    std::vector<int16_t> tables(table_total, (int16_t)-1);
-    SB_CUDA(h->slot_of_node.reserve(table_total));
+    int16_t* tables = nullptr;  // written in place in the staging arena
+    {
+        int16_t* d_tables = nullptr;
+        SB_CUDA(h->stage.take(std::max<size_t>(table_total, 1), &tables, &d_tables, h->stream));
+        h->slot_of_node.alias(d_tables);
+        for (size_t i = 0; i < table_total; ++i) tables[i] = (int16_t)-1;
+        h->h2d_bytes += (int64_t)table_total * 2;
+    }
     size_t toff = 0;
     const int64_t n = h->train.n;
     const int W = h->cfg.weights_per_row;
@@ -756,7 +834,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                     tr.rm_fpl = fpl;
                     std::vector<int32_t> feat_of_pos((size_t)twin_pad, -1);
                     for (int f = 0; f < F; ++f) feat_of_pos[pos_of[f]] = f;
-                    SB_CUDA(h->twin_map.reserve((size_t)twin_pad));
+                    SB_CUDA(h->twin_map.reserve(h->stream, (size_t)twin_pad));
                     SB_CUDA(cudaMemcpyAsync(h->twin_map.p, feat_of_pos.data(), (size_t)twin_pad * 4, cudaMemcpyHostToDevice, h->stream));
                     SB_CUDA(cudaStreamSynchronize(h->stream));  // feat_of_pos is a local
                     SB_CUDA(cudaMalloc(&tr.bins_rm, (size_t)std::max<int64_t>(n, 1) * tr.fpad + 256));
@@ -771,12 +849,12 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 const int64_t chunk_rows = MAX_ROWS_PER_FLUSH;  // upper bound; integer counts: 2^18 rows * 1024 < 2^32 as well
                 const int max_chunks = (int)(n / chunk_rows + target_chunks + rgroups + 2 + 2 * 148);  // + up to two waves of rounding
                 const size_t scan_items = (size_t)rgroups * (size_t)rowlist_n_ranges(n) + 1;
-                SB_CUDA(h->rl_counts.reserve(2 * scan_items));
+                SB_CUDA(h->rl_counts.reserve(h->stream, 2 * scan_items));
                 const size_t temp_bytes = rowlist_scan_temp_bytes((int64_t)scan_items);
-                SB_CUDA(h->rl_temp.reserve(temp_bytes + 16));
-                SB_CUDA(h->rl_tables.reserve((size_t)257 + 2 * (size_t)max_chunks));
-                SB_CUDA(h->rl_chunk_group.reserve((size_t)max_chunks + 1));
-                SB_CUDA(h->rl_ops.reserve((size_t)n));
+                SB_CUDA(h->rl_temp.reserve(h->stream, temp_bytes + 16));
+                SB_CUDA(h->rl_tables.reserve(h->stream, (size_t)257 + 2 * (size_t)max_chunks));
+                SB_CUDA(h->rl_chunk_group.reserve(h->stream, (size_t)max_chunks + 1));
+                SB_CUDA(h->rl_ops.reserve(h->stream, (size_t)n));
                 L.use_rows = true;
                 L.fpl = fpl;
                 L.allf = allf;
@@ -818,7 +896,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                         h->root_cnt_total == lay.total && h->root_cnt_feats == feats) {
                         L.root_counts = 2;
                     } else {
-                        SB_CUDA(h->root_cnt.reserve((size_t)(2 * L.root_bins)));
+                        SB_CUDA(h->root_cnt.reserve(h->stream, (size_t)(2 * L.root_bins)));
                         L.root_counts = 1;
                         h->root_cnt_valid = true;
                         h->root_cnt_version = h->weights_version;
@@ -867,13 +945,12 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         h->launches.push_back(L);
         toff += (size_t)table_size[t];
     }
-    SB_CUDA(cudaMemcpyAsync(h->slot_of_node.p, tables.data(), tables.size() * 2, cudaMemcpyHostToDevice, h->stream));
-    h->h2d_bytes += tables.size() * 2;
     if (!h->pairs.empty()) {
-        SB_CUDA(h->d_pairs.reserve(h->pairs.size()));
-        SB_CUDA(h->d_small_is_b.reserve(h->pairs.size()));
-        SB_CUDA(cudaMemcpyAsync(h->d_pairs.p, h->pairs.data(), h->pairs.size() * sizeof(PairDesc), cudaMemcpyHostToDevice, h->stream));
-        h->h2d_bytes += h->pairs.size() * sizeof(PairDesc);
+        SB_CUDA(stage_into(h, h->d_pairs, h->pairs.data(), h->pairs.size()));
+        SB_CUDA(h->d_small_is_b.reserve(h->stream, h->pairs.size()));
+    }
+    SB_CUDA(h->stage.flush(h->stream));  // every table of the pass so far, in one copy
+    if (!h->pairs.empty()) {
         SB_CUDA(launch_pair_decide(h->d_pairs.p, (int)h->pairs.size(), h->raw_prev.p, h->raw_prev.p + h->prev_layout.total,
                                    h->stats_size, h->stat_kind, F, h->slot_of_node.p, h->pair_off.p, h->d_small_is_b.p, h->stream));
         h->launches_count += 1;
@@ -888,10 +965,11 @@ int plan_split_tasks(sb_handle* h) {
     int max_cat_bins = 0;
     bool same_lists = N > 0;
     for (size_t n = 1; n < N && same_lists; ++n) same_lists = lay.nodes[n].features == lay.nodes[0].features;
-    // tasks of one node: (feature, block offset relative to the node, bins, kind, HashMap visit rank)
-    auto node_tasks = [&](size_t n, int64_t base, std::vector<SplitTask>& out) {
+    // tasks of one node: (feature, block offset relative to the node, bins, kind, HashMap visit rank), written at `out`
+    std::vector<int> cols;
+    auto node_tasks = [&](size_t n, int64_t base, SplitTask* out) {
         const auto& nd = lay.nodes[n];
-        std::vector<int> cols;
+        cols.clear();
         for (int f : nd.features) cols.push_back(h->column_num[f]);
         const std::vector<int> rank = hashmap_visit_rank(cols);
         for (size_t k = 0; k < nd.features.size(); ++k) {
@@ -905,51 +983,54 @@ int plan_split_tasks(sb_handle* h) {
             t.visit_rank = rank[k];
             t.pad = 0;
             if (t.categorical) { h->has_cat_tasks = true; max_cat_bins = std::max(max_cat_bins, t.n_bins); }
-            out.push_back(t);
+            out[k] = t;
         }
     };
     size_t n_tasks = 0;
     for (const auto& nd : lay.nodes) n_tasks += nd.features.size();
     h->n_tasks = (int)n_tasks;
-    SB_CUDA(h->tasks.reserve(n_tasks + (N ? lay.nodes[0].features.size() : 0) + 1));
-    SB_CUDA(h->node_task_begin.reserve(N + 1));
-    SB_CUDA(h->cand.reserve(n_tasks));
-    SB_CUDA(h->gain_out.reserve(N));
+    SB_CUDA(h->cand.reserve(h->stream, n_tasks));
+    SB_CUDA(h->gain_out.reserve(h->stream, N));
     if (same_lists && N > 1) {
         // one template row + the node offsets; expanded on the device
-        std::vector<SplitTask> tmpl;
+        const size_t fk = lay.nodes[0].features.size();
+        SplitTask *tmpl = nullptr, *d_tmpl = nullptr;
+        int64_t *node_off = nullptr, *d_node_off = nullptr;
+        SB_CUDA(h->stage.take(std::max<size_t>(fk, 1), &tmpl, &d_tmpl, h->stream));
+        SB_CUDA(h->stage.take(N, &node_off, &d_node_off, h->stream));
         node_tasks(0, 0, tmpl);
-        const int fk = (int)tmpl.size();
-        std::vector<int64_t> node_off(N);
         for (size_t n = 0; n < N; ++n) node_off[n] = lay.nodes[n].offset;
-        SB_CUDA(h->task_node_off.reserve(N));
-        SplitTask* d_tmpl = h->tasks.p + n_tasks;  // parked behind the expanded table
-        if (fk > 0) SB_CUDA(cudaMemcpyAsync(d_tmpl, tmpl.data(), tmpl.size() * sizeof(SplitTask), cudaMemcpyHostToDevice, h->stream));
-        SB_CUDA(cudaMemcpyAsync(h->task_node_off.p, node_off.data(), N * 8, cudaMemcpyHostToDevice, h->stream));
-        SB_CUDA(launch_expand_tasks(d_tmpl, fk, h->task_node_off.p, (int)N, h->tasks.p, h->node_task_begin.p, h->stream));
+        SB_CUDA(h->stage.flush(h->stream));
+        SB_CUDA(h->tasks.reserve(h->stream, n_tasks + 1));
+        SB_CUDA(h->node_task_begin.reserve(h->stream, N + 1));
+        SB_CUDA(launch_expand_tasks(d_tmpl, (int)fk, d_node_off, (int)N, h->tasks.p, h->node_task_begin.p, h->stream));
         h->launches_count += 1;
-        h->h2d_bytes += tmpl.size() * sizeof(SplitTask) + N * 8;
+        h->h2d_bytes += fk * sizeof(SplitTask) + N * 8;
     } else {
-        std::vector<SplitTask> tasks;
-        std::vector<int32_t> begin;
-        tasks.reserve(n_tasks);
+        // written in place in the staging arena
+        SplitTask *tasks = nullptr, *d_tasks = nullptr;
+        int32_t *begin = nullptr, *d_begin = nullptr;
+        SB_CUDA(h->stage.take(std::max<size_t>(n_tasks, 1), &tasks, &d_tasks, h->stream));
+        SB_CUDA(h->stage.take(N + 1, &begin, &d_begin, h->stream));
+        size_t at = 0;
         for (size_t n = 0; n < N; ++n) {
-            begin.push_back((int32_t)tasks.size());
-            node_tasks(n, lay.nodes[n].offset, tasks);
+            begin[n] = (int32_t)at;
+            node_tasks(n, lay.nodes[n].offset, tasks + at);
+            at += lay.nodes[n].features.size();
         }
-        begin.push_back((int32_t)tasks.size());
-        if (!tasks.empty())
-            SB_CUDA(cudaMemcpyAsync(h->tasks.p, tasks.data(), tasks.size() * sizeof(SplitTask), cudaMemcpyHostToDevice, h->stream));
-        SB_CUDA(cudaMemcpyAsync(h->node_task_begin.p, begin.data(), begin.size() * 4, cudaMemcpyHostToDevice, h->stream));
-        h->h2d_bytes += tasks.size() * sizeof(SplitTask) + begin.size() * 4;
+        begin[N] = (int32_t)at;
+        h->tasks.alias(d_tasks);
+        h->node_task_begin.alias(d_begin);
+        SB_CUDA(h->stage.flush(h->stream));
+        h->h2d_bytes += n_tasks * sizeof(SplitTask) + (N + 1) * 4;
     }
     if (h->has_cat_tasks) {
-        SB_CUDA(h->cand_bits.reserve(n_tasks * SB_MAX_CAT_BYTES));
-        SB_CUDA(h->out_bits.reserve(N * SB_MAX_CAT_BYTES));
-        SB_CUDA(h->sort_keys.reserve(n_tasks * max_cat_bins));
-        SB_CUDA(h->sort_idx.reserve(n_tasks * max_cat_bins));
-        SB_CUDA(h->sort_tmp.reserve(n_tasks * max_cat_bins));
-        SB_CUDA(h->sort_flags.reserve(n_tasks * max_cat_bins));
+        SB_CUDA(h->cand_bits.reserve(h->stream, n_tasks * SB_MAX_CAT_BYTES));
+        SB_CUDA(h->out_bits.reserve(h->stream, N * SB_MAX_CAT_BYTES));
+        SB_CUDA(h->sort_keys.reserve(h->stream, n_tasks * max_cat_bins));
+        SB_CUDA(h->sort_idx.reserve(h->stream, n_tasks * max_cat_bins));
+        SB_CUDA(h->sort_tmp.reserve(h->stream, n_tasks * max_cat_bins));
+        SB_CUDA(h->sort_flags.reserve(h->stream, n_tasks * max_cat_bins));
     }
     h->max_bins = max_cat_bins;
     return SB_OK;
@@ -1039,6 +1120,15 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
     }
     if (cfg->device < 0 || cfg->device >= ndev) return fail(SB_ERR_INVALID, "device ordinal out of range");
     SB_CUDA(cudaSetDevice(cfg->device));
+    {   // keep what cudaFreeAsync returns inside the pool: the work buffers of a pass are re-sized level after level
+        cudaMemPool_t pool = nullptr;
+        if (cudaDeviceGetDefaultMemPool(&pool, cfg->device) == cudaSuccess && pool) {
+            uint64_t keep = UINT64_MAX;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        } else {
+            cudaGetLastError();
+        }
+    }
     std::unique_ptr<sb_handle> h(new sb_handle());
     h->cfg = *cfg;
     h->n_bins.assign(cfg->n_bins, cfg->n_bins + cfg->n_features);
@@ -1087,6 +1177,7 @@ SB_API void sb_destroy(sb_handle* h) {
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
     if (h->trace) dump_trace(h);
+    h->stage.release();
     free_rowset(h->train);
     free_rowset(h->valid);
     for (auto& kv : h->trees) free_tree(kv.second);
@@ -1296,8 +1387,8 @@ SB_API int sb_sample_weights_stratified(sb_handle* h, int32_t w_index, int64_t s
     SB_CUDA(cudaSetDevice(h->cfg.device));
     const size_t n = (size_t)std::max<int64_t>(r.n, 1);
     const size_t temp_bytes = stratified_temp_bytes(r.n);
-    SB_CUDA(h->rl_counts.reserve(2 * n));
-    SB_CUDA(h->rl_temp.reserve(temp_bytes + 16));
+    SB_CUDA(h->rl_counts.reserve(h->stream, 2 * n));
+    SB_CUDA(h->rl_temp.reserve(h->stream, temp_bytes + 16));
     SB_CUDA(cudaMemsetAsync(h->d_error_flag, 0, 4, h->stream));
     SB_CUDA(launch_stratified_mask(r.weights + (int64_t)w_index * r.n, r.label, r.n, n_classes, seed, rate, h->rl_counts.p,
                                    h->rl_counts.p + n, h->rl_temp.p, temp_bytes, h->d_error_flag, h->stream));
@@ -1352,11 +1443,12 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     // children with accumulators of an older pass: the claim is renewed only by a finished pass.
     h->use_prev = h->prev_valid;
     h->prev_valid = false;
+    h->stage.reset();  // the previous pass ended with a stream synchronisation: its tables are no longer in use
     int rc = build_layout(h, in, h->layout);
     if (rc != SB_OK) return rc;
     const int64_t total = h->layout.total;
-    SB_CUDA(h->raw.reserve((size_t)std::max<int64_t>(2 * total, 1)));
-    SB_CUDA(h->stats.reserve((size_t)std::max<int64_t>(total, 1)));
+    SB_CUDA(h->raw.reserve(h->stream, (size_t)std::max<int64_t>(2 * total, 1)));
+    SB_CUDA(h->stats.reserve(h->stream, (size_t)std::max<int64_t>(total, 1)));
     SB_CUDA(cudaMemsetAsync(h->raw.p, 0, (size_t)(2 * total) * 8, h->stream));
     // GBT error sums are sums over Data.predict, which only changes at a tree switch (dt/DTWorker.java:627-640, 681):
     // inside a tree (after the first one) the four scalars of the previous pass are still the answer.
@@ -1381,6 +1473,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
                 DeviceTree& dprev = h->trees[prev.tree_id];
                 rc = upload_tree(h, prev, dprev);
                 if (rc != SB_OK) return rc;
+                SB_CUDA(h->stage.flush(h->stream));
                 if (h->tracked_tree != prev.tree_id) {  // first time we see it: walk from the root
                     SB_CUDA(launch_fill_i32(tr.node_id, tr.n, SB_ROOT_INDEX, h->stream));
                     if (va.loaded) SB_CUDA(launch_fill_i32(va.node_id, va.n, SB_ROOT_INDEX, h->stream));
@@ -1389,7 +1482,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
                 SB_CUDA(launch_route(tr.d_col, h->d_feat_bins, tr.n, tr.node_id, pv, h->d_error_flag, h->stream));
                 const uint8_t* d_drop = nullptr;
                 if (in->dropout && !in->is_first_tree) {
-                    SB_CUDA(h->new_dropout.reserve((size_t)tr.n));
+                    SB_CUDA(h->new_dropout.reserve(h->stream, (size_t)tr.n));
                     SB_CUDA(cudaMemcpyAsync(h->new_dropout.p, in->dropout, (size_t)tr.n, cudaMemcpyHostToDevice, h->stream));
                     h->h2d_bytes += tr.n;
                     d_drop = h->new_dropout.p;
@@ -1423,6 +1516,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
         DeviceTree& dcur = h->trees[cur_tree.tree_id];
         rc = upload_tree(h, cur_tree, dcur);
         if (rc != SB_OK) return rc;
+        SB_CUDA(h->stage.flush(h->stream));
         h->tracked_tree = cur_tree.tree_id;
         // keep the device copies of the current and the previous tree only
         const int keep_prev = curr >= 1 ? in->trees[curr - 1].tree_id : cur_tree.tree_id;
@@ -1465,15 +1559,19 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
         }
     } else {
         // RF (dt/DTWorker.java:583-605, 691-705): every real tree is walked for the error sums
-        for (int t = 0; t < in->n_trees; ++t) {
+        for (int t = 0; t < in->n_trees; ++t) {  // all trees reach the device with one copy
             const sb_tree& tree = in->trees[t];
             if (tree.n_nodes < 1) continue;  // INVALID_INDEX placeholder
             if (tree.tree_id < 0 || tree.tree_id >= tr.n_node_arrays) return fail(SB_ERR_INVALID, "tree id out of range");
             if (tree.tree_id >= h->cfg.weights_per_row) return fail(SB_ERR_INVALID, "RF needs one weight per tree");
-            DeviceTree& d = h->trees[tree.tree_id];
-            rc = upload_tree(h, tree, d);
+            rc = upload_tree(h, tree, h->trees[tree.tree_id]);
             if (rc != SB_OK) return rc;
-            const TreeView v = view_of(d);
+        }
+        SB_CUDA(h->stage.flush(h->stream));
+        for (int t = 0; t < in->n_trees; ++t) {
+            const sb_tree& tree = in->trees[t];
+            if (tree.n_nodes < 1) continue;
+            const TreeView v = view_of(h->trees[tree.tree_id]);
             int32_t* nid = tr.node_id + (int64_t)tree.tree_id * tr.n;
             SB_CUDA(launch_route(tr.d_col, h->d_feat_bins, tr.n, nid, v, h->d_error_flag, h->stream));
             ErrArgs e{};
@@ -1530,6 +1628,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     }
     rc = plan_split_tasks(h);
     if (rc != SB_OK) return rc;
+    SB_CUDA(h->stage.flush(h->stream));
     h->begun = true;
     if (h->trace) { h->passes_trace.back().t_begin = now_ms(); h->passes_trace.back().sub[4] = h->passes_trace.back().t_begin - tt0; }
     return SB_OK;
@@ -1721,6 +1820,10 @@ static int finish_check(sb_handle* h, sb_iter_out* out) {
 static int best_enqueue(sb_handle* h, bool want_bits) {
     const int n_nodes = (int)h->layout.nodes.size();
     if (n_nodes == 0) return SB_OK;
+    // stream-ordered allocations are not zero-filled: bytes the kernels leave alone (category bits past cat_bytes, the
+    // record of a node without any candidate) must not carry an earlier pass's data to the caller
+    SB_CUDA(cudaMemsetAsync(h->gain_out.p, 0, sizeof(sb_gain) * (size_t)n_nodes, h->stream));
+    if (h->has_cat_tasks) SB_CUDA(cudaMemsetAsync(h->out_bits.p, 0, (size_t)n_nodes * SB_MAX_CAT_BYTES, h->stream));
     SplitScratch sc;
     sc.keys = h->sort_keys.p; sc.idx = h->sort_idx.p; sc.tmp = h->sort_tmp.p; sc.flags = h->sort_flags.p; sc.max_bins = h->max_bins;
     SB_CUDA(launch_best_splits(h->stats.p, h->tasks.p, h->n_tasks, n_nodes, h->cfg.impurity, h->stats_size,
