@@ -1463,6 +1463,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     double tt0 = h->trace ? now_ms() : 0;
     if (h->trace) h->passes_trace.back().sub[0] = tt0 - h->passes_trace.back().t0;
 
+    bool fused_switch = false;  // the GBT tree switch already produced the error sums and the scale maxima of this pass
     if (h->cfg.is_gbdt) {
         const int curr = in->n_trees - 1;  // currTreeIndex (dt/DTWorker.java:620)
         const sb_tree& cur_tree = in->trees[curr];
@@ -1479,23 +1480,6 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
                     if (va.loaded) SB_CUDA(launch_fill_i32(va.node_id, va.n, SB_ROOT_INDEX, h->stream));
                 }
                 const TreeView pv = view_of(dprev);
-                SB_CUDA(launch_route(tr.d_col, h->d_feat_bins, tr.n, tr.node_id, pv, h->d_error_flag, h->stream));
-                const uint8_t* d_drop = nullptr;
-                if (in->dropout && !in->is_first_tree) {
-                    SB_CUDA(h->new_dropout.reserve(h->stream, (size_t)tr.n));
-                    SB_CUDA(cudaMemcpyAsync(h->new_dropout.p, in->dropout, (size_t)tr.n, cudaMemcpyHostToDevice, h->stream));
-                    h->h2d_bytes += tr.n;
-                    d_drop = h->new_dropout.p;
-                }
-                SB_CUDA(launch_gbt_update(tr.n, tr.node_id, pv, in->is_first_tree, h->cfg.learning_rate, loss, tr.label,
-                                          tr.predict, tr.output, d_drop, h->stream));
-                h->launches_count += 2;
-                if (va.loaded) {
-                    SB_CUDA(launch_route(va.d_col, h->d_feat_bins, va.n, va.node_id, pv, h->d_error_flag, h->stream));
-                    SB_CUDA(launch_gbt_update(va.n, va.node_id, pv, in->is_first_tree, h->cfg.learning_rate, loss, va.label,
-                                              va.predict, va.output, nullptr, h->stream));
-                    h->launches_count += 2;
-                }
                 if (in->new_weights) {  // redraw of subsampleWeights[currTreeIndex % len] (dt/DTWorker.java:643-668), injected
                     const int W = h->cfg.weights_per_row;
                     SB_CUDA(cudaMemcpyAsync(tr.weights + (int64_t)(curr % W) * tr.n, in->new_weights, (size_t)tr.n * 4,
@@ -1504,10 +1488,39 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
                     rc = refresh_cnt_int(h);
                     if (rc != SB_OK) return rc;
                 }
+                const uint8_t* d_drop = nullptr;
+                if (in->dropout && !in->is_first_tree) {
+                    SB_CUDA(h->new_dropout.reserve(h->stream, (size_t)tr.n));
+                    SB_CUDA(cudaMemcpyAsync(h->new_dropout.p, in->dropout, (size_t)tr.n, cudaMemcpyHostToDevice, h->stream));
+                    h->h2d_bytes += tr.n;
+                    d_drop = h->new_dropout.p;
+                }
+                // one pass over the rows: walk the finished tree, update predict / output, back to the root, error
+                // sums over the new predict, maxima for the next tree's fixed-point scales (gbt_switch_kernel)
+                SB_CUDA(cudaMemsetAsync(h->d_maxbits, 0, 16, h->stream));
+                SwitchArgs sa{};
+                sa.n = tr.n; sa.cols = tr.d_col; sa.feat_bins = h->d_feat_bins; sa.node_id = tr.node_id; sa.prev = pv;
+                sa.is_first_tree = in->is_first_tree; sa.learning_rate = h->cfg.learning_rate; sa.loss = loss;
+                sa.label = tr.label; sa.predict = tr.predict; sa.output = tr.output; sa.significance = tr.significance;
+                const int wcol = cur_tree.tree_id % (tr.weights ? h->cfg.weights_per_row : 1);
+                sa.weights = (tr.weights && !h->weights_all_one) ? tr.weights + (int64_t)wcol * tr.n : nullptr;
+                sa.dropout = d_drop; sa.is_validation = 0; sa.maxbits = h->d_maxbits; sa.error_flag = h->d_error_flag;
+                SB_CUDA(launch_gbt_switch(sa, h->d_err_scratch, h->d_acc, h->stream));
+                h->launches_count += 1;
+                if (va.loaded) {
+                    sa.n = va.n; sa.cols = va.d_col; sa.node_id = va.node_id; sa.label = va.label; sa.predict = va.predict;
+                    sa.output = va.output; sa.significance = va.significance; sa.weights = nullptr; sa.dropout = nullptr;
+                    sa.is_validation = 1; sa.maxbits = nullptr;
+                    SB_CUDA(launch_gbt_switch(sa, h->d_err_scratch, h->d_acc, h->stream));
+                    h->launches_count += 1;
+                }
+                fused_switch = true;
             }
-            SB_CUDA(launch_fill_i32(tr.node_id, tr.n, SB_ROOT_INDEX, h->stream));
-            if (va.loaded) SB_CUDA(launch_fill_i32(va.node_id, va.n, SB_ROOT_INDEX, h->stream));
-            h->launches_count += 1 + (va.loaded ? 1 : 0);
+            if (!fused_switch) {  // the very first tree: nothing to walk, every row starts at the root
+                SB_CUDA(launch_fill_i32(tr.node_id, tr.n, SB_ROOT_INDEX, h->stream));
+                if (va.loaded) SB_CUDA(launch_fill_i32(va.node_id, va.n, SB_ROOT_INDEX, h->stream));
+                h->launches_count += 1 + (va.loaded ? 1 : 0);
+            }
         } else if (h->tracked_tree != cur_tree.tree_id) {
             SB_CUDA(launch_fill_i32(tr.node_id, tr.n, SB_ROOT_INDEX, h->stream));
             if (va.loaded) SB_CUDA(launch_fill_i32(va.node_id, va.n, SB_ROOT_INDEX, h->stream));
@@ -1546,7 +1559,9 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
         ErrArgs e{};
         e.n = tr.n; e.label = tr.label; e.predict = tr.predict; e.significance = tr.significance; e.weights = nullptr;
         e.node_id = tr.node_id; e.tree = cv; e.from_tree = from_tree ? 1 : 0; e.loss = loss; e.is_validation = 0; e.rf_oob = 0;
-        if (need_errors) {
+        if (need_errors && fused_switch) {
+            h->acc_valid = true;  // sums over Data.predict: they hold until the next tree switch
+        } else if (need_errors) {
             SB_CUDA(launch_errors(e, h->d_err_scratch, h->d_acc, h->stream));
             h->launches_count += 1;
             if (va.loaded) {
@@ -1596,7 +1611,10 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     // weights change, i.e. at a GBT tree switch (RF: never after load), so they are computed once per tree and
     // the accumulators of all levels of a tree share one scale.
     h->scales_fresh = false;
-    if (!h->scales_valid || (h->cfg.is_gbdt && in->switch_to_next_tree)) {
+    if (fused_switch) {
+        h->scales_fresh = true;
+        h->scales_valid = true;
+    } else if (!h->scales_valid || (h->cfg.is_gbdt && in->switch_to_next_tree)) {
         h->scales_fresh = true;
         SB_CUDA(cudaMemsetAsync(h->d_maxbits, 0, 16, h->stream));
         const int W = tr.weights ? h->cfg.weights_per_row : 1;

@@ -169,7 +169,29 @@ struct ErrArgs {
     int is_validation;         // validation rows: everything goes to (validation_count, validation_error)
     int rf_oob;                // RF training rows: weight == 0 -> out-of-bag "validation" sums
 };
-constexpr int ERR_BLOCKS = 592;  // 4 per SM
+// GBT tree switch, fused (gbt_switch_kernel): route through the finished tree, update predict / output, reset the node id,
+// error sums over the new predict, and (training rows) the maxima behind the next tree's fixed-point scales.
+struct SwitchArgs {
+    int64_t n;
+    const void* const* cols;
+    const int32_t* feat_bins;
+    int32_t* node_id;
+    TreeView prev;             // the finished tree
+    int is_first_tree;
+    double learning_rate;
+    int loss;
+    const float* label;
+    float* predict;
+    float* output;
+    const float* significance;
+    const float* weights;      // training rows: the next tree's sample-weight column, nullptr = all 1f
+    const uint8_t* dropout;    // training rows, may be nullptr
+    int is_validation;
+    uint32_t* maxbits;         // [3], training rows only
+    uint32_t* error_flag;
+};
+cudaError_t launch_gbt_switch(const SwitchArgs& a, double* scratch /*[ERR_SCRATCH_DOUBLES]*/, double* acc /*[4], += */, cudaStream_t s);
+constexpr int ERR_BLOCKS = 1184;  // 8 per SM
 constexpr int ERR_SCRATCH_DOUBLES = ERR_BLOCKS * 4 + 1;  // per-block partials + the finish ticket (zeroed once at allocation)
 cudaError_t launch_errors(const ErrArgs& a, double* scratch /*[ERR_SCRATCH_DOUBLES]*/, double* acc /*[4], += */, cudaStream_t s);
 // max |sig*w|, |y*sig*w|, |y*y*sig*w| over rows (as fp32 bit patterns, atomicMax) -> out[3]

@@ -108,38 +108,9 @@ __global__ void gbt_update_kernel(int64_t n, const int32_t* __restrict__ node_id
     }
 }
 
-// Per-block partial sums in a fixed order -> scratch; the last block to finish folds the partials, again in a
-// fixed order, into acc.  Same input => same bits, whatever the scheduling.
-__global__ void __launch_bounds__(TPB) errors_kernel(const ErrArgs a, double* scratch, double* acc) {
-    double tc = 0, vc = 0, te = 0, ve = 0;
-    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < a.n; r += (int64_t)gridDim.x * blockDim.x) {
-        float p;
-        if (a.from_tree) {
-            const int id = a.node_id[r];
-            if (id <= 0 || id >= a.tree.capacity || !a.tree.has_predict[id]) continue;
-            p = (float)a.tree.predict[id];
-        } else {
-            p = a.predict[r];
-        }
-        const float sig = a.significance[r];
-        const float err = loss_error(a.loss, p, a.label[r]);
-        if (a.is_validation) {
-            ve += (double)(sig * err);
-            vc += (double)sig;
-        } else if (a.rf_oob) {
-            const float w = a.weights ? a.weights[r] : 1.0f;  // rows adopted without a weight array: weight 1, never out-of-bag
-            if (__float_as_int(w) == 0) {  // Float.compare(weight, 0f) == 0: out-of-bag row (dt/DTWorker.java:593-597)
-                ve += (double)(sig * err);
-                vc += (double)sig;
-            } else {
-                te += (double)((w * sig) * err);
-                tc += (double)(w * sig);
-            }
-        } else {
-            te += (double)(sig * err);
-            tc += (double)sig;
-        }
-    }
+// Per-block partial sums in a fixed order -> scratch; the last block to finish folds the partials, again in a fixed
+// order, into acc.  Same input => same bits, whatever the scheduling.  Shared by errors_kernel and gbt_switch_kernel.
+__device__ __forceinline__ void fold_error_sums(double tc, double vc, double te, double ve, double* scratch, double* acc) {
     __shared__ double sh[4][TPB / 32];
     double v[4] = {tc, vc, te, ve};
 #pragma unroll
@@ -171,6 +142,132 @@ __global__ void __launch_bounds__(TPB) errors_kernel(const ErrArgs a, double* sc
         acc[threadIdx.x] += s;
         if (threadIdx.x == 0) *reinterpret_cast<unsigned int*>(scratch + ERR_BLOCKS * 4) = 0u;
     }
+}
+
+
+// Error sums (dt/DTWorker.java:672-683, 737-748 GBT; 583-605, 691-705 RF).
+__global__ void __launch_bounds__(TPB) errors_kernel(const ErrArgs a, double* scratch, double* acc) {
+    double tc = 0, vc = 0, te = 0, ve = 0;
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < a.n; r += (int64_t)gridDim.x * blockDim.x) {
+        float p;
+        if (a.from_tree) {
+            const int id = a.node_id[r];
+            if (id <= 0 || id >= a.tree.capacity || !a.tree.has_predict[id]) continue;
+            p = (float)a.tree.predict[id];
+        } else {
+            p = a.predict[r];
+        }
+        const float sig = a.significance[r];
+        const float err = loss_error(a.loss, p, a.label[r]);
+        if (a.is_validation) {
+            ve += (double)(sig * err);
+            vc += (double)sig;
+        } else if (a.rf_oob) {
+            const float w = a.weights ? a.weights[r] : 1.0f;  // rows adopted without a weight array: weight 1, never out-of-bag
+            if (__float_as_int(w) == 0) {  // Float.compare(weight, 0f) == 0: out-of-bag row (dt/DTWorker.java:593-597)
+                ve += (double)(sig * err);
+                vc += (double)sig;
+            } else {
+                te += (double)((w * sig) * err);
+                tc += (double)(w * sig);
+            }
+        } else {
+            te += (double)(sig * err);
+            tc += (double)sig;
+        }
+    }
+    fold_error_sums(tc, vc, te, ve, scratch, acc);
+}
+
+// GBT tree switch in ONE pass over the rows (dt/DTWorker.java:620-641, 672-683 training; :721-748 validation): walk the
+// finished tree from the row's node to its leaf (predictNodeIndex), update Data.predict / Data.output from the leaf,
+// put the row back at the root for the next tree, add the row to the error sums over the new predict and -- training
+// rows -- to the maxima behind the fixed-point scales of the next tree.  Replaces route + gbt_update + fill + errors +
+// absmax (five passes over 20 bytes per row and one gathered bin per level walked).
+__global__ void __launch_bounds__(TPB)
+gbt_switch_kernel(const SwitchArgs a, double* scratch, double* acc) {
+    double tc = 0, vc = 0, te = 0, ve = 0;
+    float m0 = 0.f, m1 = 0.f, m2 = 0.f;
+    // U rows per thread and step, their dependent loads (node id -> split feature -> bin -> mask) issued side by side:
+    // one row at a time the kernel waits on four global-load latencies per row
+    constexpr int U = 4;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t r0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r0 < a.n; r0 += U * stride) {
+        int id[U], f[U], bin[U];
+        float pr[U], out[U], lab[U], sig[U], w[U];
+        uint8_t drop[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t r = r0 + u * stride;
+            id[u] = r < a.n ? a.node_id[r] : 0;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t r = r0 + u * stride;
+            f[u] = (id[u] > 0 && id[u] < a.prev.capacity) ? a.prev.feat[id[u]] : -1;
+            if (r < a.n) {
+                pr[u] = a.predict[r]; out[u] = a.output[r]; lab[u] = a.label[r]; sig[u] = a.significance[r];
+                w[u] = (a.weights && !a.is_validation) ? a.weights[r] : 1.0f;
+                drop[u] = a.dropout ? a.dropout[r] : (uint8_t)0;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) bin[u] = f[u] >= 0 ? load_bin(a.cols, a.feat_bins, f[u], r0 + u * stride) : 0;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t r = r0 + u * stride;
+            if (r >= a.n) continue;
+            int nid = id[u];
+            if (f[u] >= 0) {
+                const uint8_t m = a.prev.masks[a.prev.mask_off[nid] + (bin[u] >> 3)];
+                nid = 2 * nid + (((m >> (bin[u] & 7)) & 1) ? 0 : 1);
+                while (nid > 0 && nid < a.prev.capacity) {  // a tree seen for the first time: the rest of the way down
+                    const int ff = a.prev.feat[nid];
+                    if (ff < 0) break;
+                    const int bb = load_bin(a.cols, a.feat_bins, ff, r);
+                    const uint8_t mm = a.prev.masks[a.prev.mask_off[nid] + (bb >> 3)];
+                    nid = 2 * nid + (((mm >> (bb & 7)) & 1) ? 0 : 1);
+                }
+            }
+            if (nid >= a.prev.capacity) atomicOr(a.error_flag, 4u);
+            if (nid > 0 && nid < a.prev.capacity && a.prev.has_predict[nid]) {
+                const double p = a.prev.predict[nid];
+                if (a.is_first_tree) pr[u] = (float)p;
+                else if (!drop[u]) pr[u] = pr[u] + (float)(a.learning_rate * p);
+                out[u] = -1.0f * loss_gradient(a.loss, pr[u], lab[u]);
+                a.predict[r] = pr[u];
+                a.output[r] = out[u];
+            }
+            a.node_id[r] = SB_ROOT_INDEX;
+            const float err = loss_error(a.loss, pr[u], lab[u]);
+            if (a.is_validation) {
+                ve += (double)(sig[u] * err);
+                vc += (double)sig[u];
+            } else {
+                te += (double)(sig[u] * err);
+                tc += (double)sig[u];
+                m0 = fmaxf(m0, fabsf(sig[u] * w[u]));
+                m1 = fmaxf(m1, fabsf((out[u] * sig[u]) * w[u]));
+                m2 = fmaxf(m2, fabsf(((out[u] * out[u]) * sig[u]) * w[u]));
+                if (!isfinite(sig[u] * w[u]) || !isfinite((out[u] * sig[u]) * w[u]) || !isfinite(((out[u] * out[u]) * sig[u]) * w[u]))
+                    m0 = __int_as_float(0x7f800000);
+            }
+        }
+    }
+    if (!a.is_validation) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            m0 = fmaxf(m0, __shfl_down_sync(0xffffffffu, m0, o));
+            m1 = fmaxf(m1, __shfl_down_sync(0xffffffffu, m1, o));
+            m2 = fmaxf(m2, __shfl_down_sync(0xffffffffu, m2, o));
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicMax(&a.maxbits[0], __float_as_uint(m0));
+            atomicMax(&a.maxbits[1], __float_as_uint(m1));
+            atomicMax(&a.maxbits[2], __float_as_uint(m2));
+        }
+    }
+    fold_error_sums(tc, vc, te, ve, scratch, acc);
 }
 
 __global__ void __launch_bounds__(TPB) absmax_kernel(int64_t n, const float* __restrict__ output,
@@ -348,6 +445,11 @@ cudaError_t launch_gbt_update(int64_t n, const int32_t* node_id, TreeView prev, 
 cudaError_t launch_errors(const ErrArgs& a, double* scratch, double* acc, cudaStream_t s) {
     if (a.n <= 0) return cudaSuccess;
     errors_kernel<<<grid_for(a.n, TPB, ERR_BLOCKS), TPB, 0, s>>>(a, scratch, acc);
+    return cudaGetLastError();
+}
+cudaError_t launch_gbt_switch(const SwitchArgs& a, double* scratch, double* acc, cudaStream_t s) {
+    if (a.n <= 0) return cudaSuccess;
+    gbt_switch_kernel<<<grid_for(a.n, TPB, ERR_BLOCKS), TPB, 0, s>>>(a, scratch, acc);
     return cudaGetLastError();
 }
 cudaError_t launch_absmax(int64_t n, const float* output, const float* significance, const float* weights,
