@@ -155,6 +155,9 @@ struct sb_handle {
     std::vector<uint8_t> is_cat;
     std::vector<double> bin_boundary;
     std::vector<int> all_features;  // getAllValidFeatures (dt/DTWorker.java:965-990)
+    std::vector<int> all_feature_pos;   // feature slot -> its position in all_features, or -1
+    std::vector<int64_t> all_feat_off;  // offset of each of them inside a node block that takes all of them
+    int64_t all_feat_total = 0;
     std::vector<int> wide_index;    // per feature slot: index among the wide (> 256 bins, uint16) features, or -1
     int n_wide = 0;
     int stats_size = 3;
@@ -224,6 +227,8 @@ struct sb_handle {
     DevBuf<int32_t> wt_tiles;     // wide tiles: tile_feats [n_wt][8] then first wide index [n_wt]
     DevBuf<uint32_t> wt_fmask;    // [n_slots][n_wt]
     bool enable_row_lists = true;
+    size_t scan_temp_bytes = 0;
+    bool split_planned = false;
     bool acc_valid = false;     // d_acc holds the error sums of the current Data.predict (GBT, inside a tree)
     bool acc_fresh = false, scales_fresh = false;  // recomputed by the last sb_compute_begin (=> need an all-reduce)
     bool scales_valid = false;  // d_maxbits holds the maxima of the current tree's contributions
@@ -242,7 +247,7 @@ struct sb_handle {
     int64_t launches_count = 0, h2d_bytes = 0, d2h_bytes = 0;
 
     // SB_TRACE=1 in the environment: host / device timeline of every pass, printed by sb_destroy (developer aid)
-    struct PassTrace { double t0, t_begin, t_stats, t_enq, t_sync; cudaEvent_t e0, e1; int n_todo; double sub[6]; };
+    struct PassTrace { double t0, t_begin, t_stats, t_enq, t_sync; cudaEvent_t e0, e1, c0, c1; int n_todo; double sub[6]; };
     bool trace = false;
     std::vector<PassTrace> passes_trace;
     // optional per-pass timing of the histogram kernel (CUDA events on the launching stream)
@@ -262,11 +267,13 @@ void dump_trace(sb_handle* h) {
     fprintf(stderr, "SB_TRACE rank %d: pass todo | host gap before, begin, stats enqueue, finish enqueue, sync wait | wall, gpu busy (ms)\n", h->rank);
     for (size_t i = 0; i < h->passes_trace.size(); ++i) {
         auto& p = h->passes_trace[i];
-        float gpu = 0;
+        float gpu = 0, coll = 0;
         cudaEventElapsedTime(&gpu, p.e0, p.e1);
+        if (cudaEventElapsedTime(&coll, p.c0, p.c1) != cudaSuccess) { coll = -1; cudaGetLastError(); }
         fprintf(stderr, "SB_TRACE %4zu %4d | %7.3f %7.3f %7.3f %7.3f %7.3f | %7.3f %7.3f\n", i, p.n_todo,
                 last_sync > 0 ? p.t0 - last_sync : 0.0, p.t_begin - p.t0, p.t_stats - p.t_begin, p.t_enq - p.t_stats,
                 p.t_sync - p.t_enq, p.t_sync - p.t0, (double)gpu);
+        fprintf(stderr, "SB_TRACE      all-reduce (wait for the slowest rank + transfer) %.3f ms\n", (double)coll);
         fprintf(stderr, "SB_TRACE      begin parts: layout+memset %.3f  trees+switch kernels %.3f  scales %.3f  plan_hist %.3f  plan_split %.3f\n",
                 p.sub[0], p.sub[1], p.sub[2], p.sub[3], p.sub[4]);
         last_sync = p.t_sync;
@@ -437,24 +444,28 @@ int upload_tree(sb_handle* h, const sb_tree& t, DeviceTree& d) {
 
 // dt/DTWorker.java:903-929 initTodoNodeStats: sizes and order of the statistics buffer.
 int build_layout(const sb_handle* h, const sb_iter_in* in, TodoLayout& lay) {
-    lay.nodes.clear();
-    lay.nodes.reserve((size_t)std::max(in->n_todo, 0));
+    // `lay` is recycled from an earlier pass: resize + assign keep the capacity of the inner vectors
+    lay.nodes.resize((size_t)std::max(in->n_todo, 0));
     int64_t off = 0;
     for (int i = 0; i < in->n_todo; ++i) {
         const sb_todo_node& t = in->todo[i];
-        TodoLayout::Node nd;
+        TodoLayout::Node& nd = lay.nodes[(size_t)i];
         nd.key = t.key; nd.tree_id = t.tree_id; nd.node_id = t.node_id; nd.offset = off;
-        if (t.n_features == 0) nd.features.assign(h->all_features.begin(), h->all_features.end());
-        else nd.features.assign(t.features, t.features + t.n_features);
+        if (t.n_features == 0) {  // every valid feature: sizes and offsets are the same for all such nodes
+            nd.features = h->all_features;
+            nd.feat_off = h->all_feat_off;
+            off += h->all_feat_total;
+            continue;
+        }
+        nd.features.assign(t.features, t.features + t.n_features);
         int64_t l = 0;
-        nd.feat_off.reserve(nd.features.size());
+        nd.feat_off.clear();
         for (int f : nd.features) {
             if (f < 0 || f >= h->cfg.n_features) return fail(SB_ERR_INVALID, "todo node feature slot out of range");
             nd.feat_off.push_back(l);
             l += (int64_t)h->n_bins[f] * h->stats_size;
         }
         off += l;
-        lay.nodes.push_back(std::move(nd));
     }
     lay.total = off;
     return SB_OK;
@@ -503,8 +514,13 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     h->pairs.clear();
     h->pair_max_len = 0;
     std::vector<int> pair_parent_prev;            // per pair: index into prev_layout
+    std::map<std::pair<int, int>, int> prev_by_key;  // (tree id, heap id) -> index into prev_layout
+    std::vector<int> msg_index;                      // heap id -> index into the message's node array, for one tree
+    int msg_index_tree = -1;
+    const sb_tree* tr_msg = nullptr;
     if (h->enable_subtraction && h->use_prev) {
-        std::map<std::pair<int, int>, int> cur_idx, prev_idx;
+        std::map<std::pair<int, int>, int> cur_idx;
+        std::map<std::pair<int, int>, int>& prev_idx = prev_by_key;
         for (int i = 0; i < S_all; ++i) cur_idx[{lay.nodes[i].tree_id, lay.nodes[i].node_id}] = i;
         for (size_t i = 0; i < h->prev_layout.nodes.size(); ++i)
             prev_idx[{h->prev_layout.nodes[i].tree_id, h->prev_layout.nodes[i].node_id}] = (int)i;
@@ -533,11 +549,18 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     // `used`: narrow (uint8) features some todo node asks for; wide (uint16) ones go to their own 8-feature tiles
     std::vector<uint8_t> used((size_t)F, 0), used_wide((size_t)F, 0);
     bool any_wide = false;
-    for (const auto& nd : lay.nodes)
-        for (int f : nd.features) {
+    // common case (GBT with FeatureSubsetStrategy ALL): every todo node takes every valid feature -- one list to look at
+    bool all_feats_nodes = true;
+    for (int i = 0; i < in->n_todo && all_feats_nodes; ++i) all_feats_nodes = in->todo[i].n_features == 0;
+    auto mark_used = [&](const std::vector<int>& feats) {
+        for (int f : feats) {
             if (h->wide_index[f] >= 0) { used_wide[f] = 1; any_wide = true; }
             else used[f] = 1;
         }
+    };
+    if (all_feats_nodes) mark_used(h->all_features);
+    else
+        for (const auto& nd : lay.nodes) mark_used(nd.features);
     std::vector<int32_t> tile_feats, tile_slot0;
     std::vector<int> tile_of((size_t)F, -1), lane_of((size_t)F, -1);
     int bins_pad = 1;
@@ -568,6 +591,16 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     std::vector<int64_t> pair_off((size_t)S * F, -1);
     for (int s = 0; s < S; ++s) {
         const auto& nd = lay.nodes[order[s]];
+        if (all_feats_nodes && s > 0) {  // same features as slot 0: its mask row, its offsets shifted to this node's block
+            const auto& n0 = lay.nodes[order[0]];
+            for (int t = 0; t < n_tiles; ++t) fmask[(size_t)s * n_tiles + t] = fmask[(size_t)t];
+            const int64_t shift = nd.offset - n0.offset;
+            for (int f = 0; f < F; ++f) {
+                const int64_t o = pair_off[(size_t)f];
+                pair_off[(size_t)s * F + f] = o < 0 ? -1 : o + shift;
+            }
+            continue;
+        }
         for (size_t k = 0; k < nd.features.size(); ++k) {
             const int f = nd.features[k];
             if (tile_of[f] >= 0) fmask[(size_t)s * n_tiles + tile_of[f]] |= 1u << lane_of[f];
@@ -683,6 +716,10 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
         std::vector<uint32_t> rfm((size_t)S * n_rt * fpl, 0u);
         for (int s = 0; s < S; ++s) {
             const auto& nd = lay.nodes[order[s]];
+            if (all_feats_nodes && s > 0) {
+                memcpy(&rfm[(size_t)s * n_rt * fpl], rfm.data(), (size_t)n_rt * fpl * 4);
+                continue;
+            }
             for (int f : nd.features) {
                 const int t = rt_of[f];
                 if (t < 0) continue;  // wide feature
@@ -751,17 +788,33 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 const auto& nb = lay.nodes[partner[order[s]]];
                 tables[toff + nb.node_id] = (int16_t)(s - s0);
                 // the parent: its split feature, left mask and node block in the previous pass
-                const sb_tree* tr_msg = find_tree(in, na.tree_id);
-                const sb_node* pn = nullptr;
-                for (int q = 0; q < tr_msg->n_nodes; ++q)
-                    if (tr_msg->nodes[q].id == nid / 2) pn = &tr_msg->nodes[q];
+                // the parent in the message (by heap id, indexed once per tree) and in the previous pass's layout
+                if (msg_index_tree != na.tree_id) {
+                    msg_index_tree = na.tree_id;
+                    tr_msg = find_tree(in, na.tree_id);
+                    msg_index.clear();
+                    for (int q = 0; q < tr_msg->n_nodes; ++q) {
+                        const int id = tr_msg->nodes[q].id;
+                        if (id >= (int)msg_index.size()) msg_index.resize((size_t)id + 1, -1);
+                        msg_index[(size_t)id] = q;
+                    }
+                }
+                const sb_node* pn = (nid / 2 < (int)msg_index.size() && msg_index[(size_t)(nid / 2)] >= 0)
+                                        ? &tr_msg->nodes[msg_index[(size_t)(nid / 2)]] : nullptr;
                 const TodoLayout::Node* par = nullptr;
-                for (const auto& pv : h->prev_layout.nodes)
-                    if (pv.tree_id == na.tree_id && pv.node_id == nid / 2) par = &pv;
+                {
+                    auto ip = prev_by_key.find({na.tree_id, nid / 2});
+                    if (ip != prev_by_key.end()) par = &h->prev_layout.nodes[(size_t)ip->second];
+                }
                 int kf = -1;
-                if (pn && par)
-                    for (size_t k = 0; k < par->features.size(); ++k)
-                        if (par->features[k] == pn->feature) kf = (int)k;
+                if (pn && par) {
+                    if (par->features.size() == h->all_features.size() && pn->feature >= 0 && pn->feature < F &&
+                        h->all_feature_pos[(size_t)pn->feature] >= 0 && par->features[(size_t)h->all_feature_pos[(size_t)pn->feature]] == pn->feature)
+                        kf = h->all_feature_pos[(size_t)pn->feature];  // the list is "every valid feature": position known
+                    else
+                        for (size_t k = 0; k < par->features.size(); ++k)
+                            if (par->features[k] == pn->feature) kf = (int)k;
+                }
                 if (!pn || !par || kf < 0 || pn->feature < 0) return fail(SB_ERR_STATE, "histogram subtraction: parent split not found");
                 PairDesc d{};
                 d.parent_split_block = par->offset + par->feat_off[(size_t)kf];
@@ -842,7 +895,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                     h->launches_count += 1;
                 }
                 const int tiles_total = n_rt + n_wt;
-                constexpr int waves = 4;  // measured on C2 / C3: 54.4 ms per tree against 56.0 (1), 56.6 (2), 55.1 (3), 54.7 (8)
+                static const int waves = getenv("SB_WAVES") ? atoi(getenv("SB_WAVES")) : 4;  // measured on C2 / C3: 54.4 ms per tree against 56.0 (1), 56.6 (2), 55.1 (3), 54.7 (8)
                 // every group ends with a partial chunk: leave room for those, or the launch spills into one more wave
                 const int64_t blocks_target = std::max<int64_t>(148 * waves - (int64_t)tiles_total * std::min(rgroups, 74), 74);
                 const int target_chunks = (int)std::max<int64_t>(1, blocks_target / tiles_total);
@@ -850,7 +903,9 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 const int max_chunks = (int)(n / chunk_rows + target_chunks + rgroups + 2 + 2 * 148);  // + up to two waves of rounding
                 const size_t scan_items = (size_t)rgroups * (size_t)rowlist_n_ranges(n) + 1;
                 SB_CUDA(h->rl_counts.reserve(h->stream, 2 * scan_items));
-                const size_t temp_bytes = rowlist_scan_temp_bytes((int64_t)scan_items);
+                // cub's size query asks the driver about the device every time: one query for the largest scan of this handle
+                if (h->scan_temp_bytes == 0) h->scan_temp_bytes = rowlist_scan_temp_bytes((int64_t)254 * rowlist_n_ranges(n) + 1);
+                const size_t temp_bytes = h->scan_temp_bytes;
                 SB_CUDA(h->rl_temp.reserve(h->stream, temp_bytes + 16));
                 SB_CUDA(h->rl_tables.reserve(h->stream, (size_t)257 + 2 * (size_t)max_chunks));
                 SB_CUDA(h->rl_chunk_group.reserve(h->stream, (size_t)max_chunks + 1));
@@ -1154,6 +1209,12 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
     h->enable_root_cache = (cfg->flags & SB_FLAG_NO_ROOT_COUNT_CACHE) == 0;
     h->stats_size = is_variance(cfg->impurity) ? 3 : cfg->num_classes;
     h->stat_kind = is_variance(cfg->impurity) ? STAT_VARIANCE : STAT_CLASS;
+    h->all_feature_pos.assign((size_t)cfg->n_features, -1);
+    for (size_t k = 0; k < h->all_features.size(); ++k) h->all_feature_pos[(size_t)h->all_features[k]] = (int)k;
+    for (int f : h->all_features) {
+        h->all_feat_off.push_back(h->all_feat_total);
+        h->all_feat_total += (int64_t)h->n_bins[f] * h->stats_size;
+    }
     SB_CUDA(cudaMalloc(&h->d_feat_bins, sizeof(int32_t) * cfg->n_features));
     SB_CUDA(cudaMemcpy(h->d_feat_bins, h->n_bins.data(), sizeof(int32_t) * cfg->n_features, cudaMemcpyHostToDevice));
     SB_CUDA(cudaMalloc(&h->d_acc, sizeof(double) * 4));
@@ -1434,6 +1495,8 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
         p.n_todo = in->n_todo;
         cudaEventCreate(&p.e0);
         cudaEventCreate(&p.e1);
+        cudaEventCreate(&p.c0);
+        cudaEventCreate(&p.c1);
         cudaEventRecord(p.e0, h->stream);
         h->passes_trace.push_back(p);
     }
@@ -1444,6 +1507,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     h->use_prev = h->prev_valid;
     h->prev_valid = false;
     h->stage.reset();  // the previous pass ended with a stream synchronisation: its tables are no longer in use
+    std::swap(h->layout, h->prev_layout);  // the last pass's layout goes with raw_prev; its storage before that is recycled
     int rc = build_layout(h, in, h->layout);
     if (rc != SB_OK) return rc;
     const int64_t total = h->layout.total;
@@ -1644,8 +1708,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
         h->launches_count += 1;
         h->pending_route = false;
     }
-    rc = plan_split_tasks(h);
-    if (rc != SB_OK) return rc;
+    h->split_planned = false;  // the best-split task table is built while the statistics kernels run (sb_compute_stats)
     SB_CUDA(h->stage.flush(h->stream));
     h->begun = true;
     if (h->trace) { h->passes_trace.back().t_begin = now_ms(); h->passes_trace.back().sub[4] = h->passes_trace.back().t_begin - tt0; }
@@ -1690,6 +1753,13 @@ SB_API int sb_compute_stats(sb_handle* h) {
         h->prof_launches.push_back((int)h->launches.size());
     }
     if (rc != SB_OK) return rc;
+    if (!h->split_planned) {  // host work that only the best-split step needs: done while the GPU is busy
+        rc = plan_split_tasks(h);
+        if (rc != SB_OK) return rc;
+        SB_CUDA(h->stage.flush(h->stream));
+        h->split_planned = true;
+    }
+    if (h->trace && !h->passes_trace.empty()) cudaEventRecord(h->passes_trace.back().c0, h->stream);
     if (h->comm) {
         // the DTMaster merge (dt/DTMaster.java:316-331 adds the workers' statistics node by node): one integer sum
         // over all GPUs, exact and order-independent; plus the four error scalars when this pass recomputed them
@@ -1697,7 +1767,10 @@ SB_API int sb_compute_stats(sb_handle* h) {
             SB_NCCL(nccl_api().AllReduce(h->raw.p, h->raw.p, (size_t)(2 * h->layout.total), ncclInt64, ncclSum, h->comm, h->stream));
         if (h->acc_fresh) SB_NCCL(nccl_api().AllReduce(h->d_acc, h->d_acc, 4, ncclFloat64, ncclSum, h->comm, h->stream));
     }
-    if (h->trace && !h->passes_trace.empty()) h->passes_trace.back().t_stats = now_ms();
+    if (h->trace && !h->passes_trace.empty()) {
+        cudaEventRecord(h->passes_trace.back().c1, h->stream);
+        h->passes_trace.back().t_stats = now_ms();
+    }
     return SB_OK;
 }
 
@@ -1827,8 +1900,7 @@ static int finish_check(sb_handle* h, sb_iter_out* out) {
     out->validation_error = po->acc[3];
     h->stats_ready = true;
     if (h->enable_subtraction) {  // keep this pass's merged accumulators for the children of its nodes
-        std::swap(h->raw, h->raw_prev);
-        h->prev_layout = h->layout;
+        std::swap(h->raw, h->raw_prev);  // (the layouts are swapped by the next sb_compute_begin)
         h->prev_valid = true;
     }
     return SB_OK;
@@ -1838,6 +1910,12 @@ static int finish_check(sb_handle* h, sb_iter_out* out) {
 static int best_enqueue(sb_handle* h, bool want_bits) {
     const int n_nodes = (int)h->layout.nodes.size();
     if (n_nodes == 0) return SB_OK;
+    if (!h->split_planned) {  // a caller that skipped sb_compute_stats
+        int rc = plan_split_tasks(h);
+        if (rc != SB_OK) return rc;
+        SB_CUDA(h->stage.flush(h->stream));
+        h->split_planned = true;
+    }
     // stream-ordered allocations are not zero-filled: bytes the kernels leave alone (category bits past cat_bytes, the
     // record of a node without any candidate) must not carry an earlier pass's data to the caller
     SB_CUDA(cudaMemsetAsync(h->gain_out.p, 0, sizeof(sb_gain) * (size_t)n_nodes, h->stream));
