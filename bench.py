@@ -119,7 +119,8 @@ def grow_tree(worker, master, it, e2e_buffers=None):
 
     Device-resident measurement: the native iteration loop (sbh_grow_tree).  End-to-end measurement: the call a
     user of the reference makes, DTWorker.doCompute with HOST buffers (message in, statistics out: sb_compute), then
-    sb_best_splits and the master step.  With several GPUs the merge is the library's own NCCL all-reduce in both."""
+    sb_best_splits and the master step.  With several GPUs the merge is the library's own NCCL all-reduce in both, and
+    only rank 0 asks for the merged statistics on its host."""
     from shifu_b200 import capi
     if e2e_buffers is None:
         return master.grow_tree(worker, it)
@@ -129,9 +130,10 @@ def grow_tree(worker, master, it, e2e_buffers=None):
     while it is not None:
         n = worker.stats_len(it)
         out = capi.SbIterOut()
-        out.stats = C.cast(e2e_buffers["stats_ptr"], C.POINTER(C.c_double))
-        out.stats_len = e2e_buffers["stats_cap"]
-        assert n <= e2e_buffers["stats_cap"]
+        if e2e_buffers["want_stats"]:
+            out.stats = C.cast(e2e_buffers["stats_ptr"], C.POINTER(C.c_double))
+            out.stats_len = e2e_buffers["stats_cap"]
+            assert n <= e2e_buffers["stats_cap"]
         capi.check(worker.lib, worker.lib.sb_compute(worker.h, C.byref(it.struct), C.byref(out)))
         e2e_buffers["d2h"] += n * 8 + 32
         scalars = (out.train_count, out.validation_count, out.train_error, out.validation_error)
@@ -342,7 +344,10 @@ def run_b200(a):
     # ---- timed region 2: end to end through sb_compute with pinned host buffers
     stats_cap = (1 << (a.depth - 2)) * a.features * a.bins * 3 + 16
     pinned = torch.empty(stats_cap, dtype=torch.float64, pin_memory=True)
-    e2e_buf = {"stats_ptr": pinned.data_ptr(), "stats_cap": stats_cap, "d2h": 0}
+    # After the in-library merge every rank holds the same statistics: ONE copy reaches a host (rank 0, where a Guagua
+    # master would consume it); the other ranks leave theirs on the device (sb_iter_out.stats = NULL) and only read the
+    # four scalars and the gain records.
+    e2e_buf = {"stats_ptr": pinned.data_ptr(), "stats_cap": stats_cap, "d2h": 0, "want_stats": rank == 0}
     _, h2d_a, d2h_a = worker.counters()
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
