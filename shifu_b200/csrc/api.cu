@@ -168,6 +168,10 @@ struct sb_handle {
     RowSet train, valid;
     Stager stage;
     int32_t* d_feat_bins = nullptr;
+    uint8_t* d_is_cat = nullptr;       // [n_features]
+    int32_t* d_column_num = nullptr;   // [n_features]
+    bool any_categorical = false;
+    int max_categorical_bins = 0;
     std::map<int, DeviceTree> trees;  // by tree id
     int tracked_tree = -1;            // GBT: tree id whose node ids train.node_id currently holds
 
@@ -1062,22 +1066,34 @@ int plan_split_tasks(sb_handle* h) {
         h->launches_count += 1;
         h->h2d_bytes += fk * sizeof(SplitTask) + N * 8;
     } else {
-        // written in place in the staging arena
-        SplitTask *tasks = nullptr, *d_tasks = nullptr;
-        int32_t *begin = nullptr, *d_begin = nullptr;
-        SB_CUDA(h->stage.take(std::max<size_t>(n_tasks, 1), &tasks, &d_tasks, h->stream));
+        // every node has its own list: the lists cross PCIe (4 bytes per entry) and build_tasks_kernel turns them into
+        // tasks -- block offsets and HashMap visit ranks -- on the device
+        int32_t *feats = nullptr, *d_feats = nullptr, *begin = nullptr, *d_begin = nullptr;
+        int64_t *node_off = nullptr, *d_node_off = nullptr;
+        SB_CUDA(h->stage.take(std::max<size_t>(n_tasks, 1), &feats, &d_feats, h->stream));
         SB_CUDA(h->stage.take(N + 1, &begin, &d_begin, h->stream));
-        size_t at = 0;
+        SB_CUDA(h->stage.take(std::max<size_t>(N, 1), &node_off, &d_node_off, h->stream));
+        size_t at = 0, max_list = 1;
         for (size_t n = 0; n < N; ++n) {
+            const auto& nd = lay.nodes[n];
             begin[n] = (int32_t)at;
-            node_tasks(n, lay.nodes[n].offset, tasks + at);
-            at += lay.nodes[n].features.size();
+            node_off[n] = nd.offset;
+            if (!nd.features.empty()) memcpy(feats + at, nd.features.data(), nd.features.size() * 4);
+            at += nd.features.size();
+            max_list = std::max(max_list, nd.features.size());
+            if (h->any_categorical)
+                for (int f : nd.features)
+                    if (h->is_cat[(size_t)f]) { h->has_cat_tasks = true; max_cat_bins = std::max(max_cat_bins, h->n_bins[(size_t)f]); }
         }
         begin[N] = (int32_t)at;
-        h->tasks.alias(d_tasks);
+        if (max_list > 8192) return fail(SB_ERR_UNSUPPORTED, "a todo node with more than 8192 features of its own");
         h->node_task_begin.alias(d_begin);
         SB_CUDA(h->stage.flush(h->stream));
-        h->h2d_bytes += n_tasks * sizeof(SplitTask) + (N + 1) * 4;
+        SB_CUDA(h->tasks.reserve(h->stream, n_tasks + 1));
+        SB_CUDA(launch_build_tasks(d_feats, d_begin, d_node_off, (int)N, (int)max_list, h->d_feat_bins, h->d_is_cat, h->d_column_num,
+                                   h->stats_size, h->tasks.p, h->stream));
+        h->launches_count += 1;
+        h->h2d_bytes += n_tasks * 4 + (N + 1) * 4 + N * 8;
     }
     if (h->has_cat_tasks) {
         SB_CUDA(h->cand_bits.reserve(h->stream, n_tasks * SB_MAX_CAT_BYTES));
@@ -1216,6 +1232,12 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
         h->all_feat_total += (int64_t)h->n_bins[f] * h->stats_size;
     }
     SB_CUDA(cudaMalloc(&h->d_feat_bins, sizeof(int32_t) * cfg->n_features));
+    SB_CUDA(cudaMalloc(&h->d_is_cat, (size_t)cfg->n_features));
+    SB_CUDA(cudaMalloc(&h->d_column_num, sizeof(int32_t) * cfg->n_features));
+    SB_CUDA(cudaMemcpy(h->d_is_cat, h->is_cat.data(), (size_t)cfg->n_features, cudaMemcpyHostToDevice));
+    SB_CUDA(cudaMemcpy(h->d_column_num, h->column_num.data(), sizeof(int32_t) * cfg->n_features, cudaMemcpyHostToDevice));
+    for (int f : h->all_features)
+        if (h->is_cat[(size_t)f]) { h->any_categorical = true; h->max_categorical_bins = std::max(h->max_categorical_bins, h->n_bins[(size_t)f]); }
     SB_CUDA(cudaMemcpy(h->d_feat_bins, h->n_bins.data(), sizeof(int32_t) * cfg->n_features, cudaMemcpyHostToDevice));
     SB_CUDA(cudaMalloc(&h->d_acc, sizeof(double) * 4));
     SB_CUDA(cudaMalloc(&h->d_err_scratch, sizeof(double) * ERR_SCRATCH_DOUBLES));
@@ -1248,6 +1270,8 @@ SB_API void sb_destroy(sb_handle* h) {
     h->sort_keys.release(); h->sort_idx.release(); h->sort_tmp.release(); h->sort_flags.release();
     h->rl_counts.release(); h->rl_temp.release(); h->rl_tables.release(); h->rl_chunk_group.release(); h->rl_ops.release(); h->rt_tiles.release(); h->rt_fmask.release(); h->wt_tiles.release(); h->wt_fmask.release();
     if (h->d_feat_bins) cudaFree(h->d_feat_bins);
+    if (h->d_is_cat) cudaFree(h->d_is_cat);
+    if (h->d_column_num) cudaFree(h->d_column_num);
     if (h->d_acc) cudaFree(h->d_acc);
     if (h->pin) cudaFreeHost(h->pin);
     if (h->comm && nccl_api().ok) nccl_api().CommDestroy(h->comm);
@@ -1483,6 +1507,9 @@ SB_API int64_t sb_stats_len(sb_handle* h, const sb_iter_in* in) {
     return lay.total;
 }
 
+static int pinned_reserve(sb_handle* h, size_t bytes);
+static size_t pinned_need(const sb_handle* h);
+
 SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     if (!h || !in) return fail(SB_ERR_INVALID, "null argument");
     if (!h->train.loaded) return fail(SB_ERR_STATE, "sb_compute before sb_load_rows");
@@ -1509,6 +1536,8 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     h->stage.reset();  // the previous pass ended with a stream synchronisation: its tables are no longer in use
     std::swap(h->layout, h->prev_layout);  // the last pass's layout goes with raw_prev; its storage before that is recycled
     int rc = build_layout(h, in, h->layout);
+    if (rc != SB_OK) return rc;
+    rc = pinned_reserve(h, pinned_need(h));  // now, while the GPU is idle: growing the pinned block waits for the device
     if (rc != SB_OK) return rc;
     const int64_t total = h->layout.total;
     SB_CUDA(h->raw.reserve(h->stream, (size_t)std::max<int64_t>(2 * total, 1)));
@@ -1854,7 +1883,7 @@ static int pinned_reserve(sb_handle* h, size_t bytes) {
     if (h->pin) cudaFreeHost(h->pin);
     h->pin = nullptr;
     h->pin_bytes = 0;
-    const size_t cap = std::max<size_t>(bytes * 2, 1 << 16);
+    const size_t cap = std::max<size_t>(bytes * 4, 1 << 16);  // pinned allocations synchronise the device: rarely
     SB_CUDA(cudaMallocHost(&h->pin, cap));
     h->pin_bytes = cap;
     return SB_OK;
@@ -1945,7 +1974,8 @@ static void best_deliver(sb_handle* h, sb_gain* gains, uint8_t* cat_bits) {
 }
 
 static size_t pinned_need(const sb_handle* h) {
-    return 256 + h->layout.nodes.size() * (sizeof(sb_gain) + SB_MAX_CAT_BYTES);
+    // category bits only travel when the handle has a categorical feature at all
+    return 256 + h->layout.nodes.size() * (sizeof(sb_gain) + (h->any_categorical ? SB_MAX_CAT_BYTES : 0));
 }
 
 SB_API int sb_compute_finish(sb_handle* h, sb_iter_out* out) {

@@ -251,6 +251,10 @@ struct SplitTask {       // one (todo node, feature) pair
 };
 cudaError_t launch_expand_tasks(const SplitTask* tmpl, int fk, const int64_t* node_off, int n_nodes, SplitTask* tasks,
                                 int32_t* begin, cudaStream_t s);
+// per-node feature lists -> (node, feature) tasks on the device; max_list = the longest list (<= 8192 features)
+cudaError_t launch_build_tasks(const int32_t* feats, const int32_t* begin, const int64_t* node_off, int n_nodes, int max_list,
+                               const int32_t* feat_bins, const uint8_t* is_cat, const int32_t* column_num, int stats_size,
+                               SplitTask* tasks, cudaStream_t s);
 cudaError_t launch_counts_cache(int64_t* raw_lo, int64_t* raw_hi, int64_t* cache, int64_t n_bins_total, int stats_size, int save,
                                 cudaStream_t s);
 struct SplitScratch {    // categorical features only: per task, max_bins entries each

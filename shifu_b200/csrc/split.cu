@@ -454,6 +454,88 @@ cudaError_t launch_expand_tasks(const SplitTask* tmpl, int fk, const int64_t* no
     return cudaGetLastError();
 }
 
+// Todo nodes with their OWN feature lists (RF, FeatureSubsetStrategy != ALL): the task table of every node is built on
+// the device from the concatenated lists -- block offsets (a running sum of bins * statsSize in list order) and the
+// java.util.HashMap visit rank of every feature of the node (dt/DTMaster.java:324: buckets ascending, insertion order
+// inside a bucket; capacity = the power of two >= the list length, as `new HashMap(n, 1f)` sizes it).  One warp per node;
+// the bucket counters live in shared memory.  The host used to build and copy 32 bytes per (node, feature).
+__global__ void build_tasks_kernel(const int32_t* __restrict__ feats, const int32_t* __restrict__ begin,
+                                   const int64_t* __restrict__ node_off, int n_nodes, const int32_t* __restrict__ feat_bins,
+                                   const uint8_t* __restrict__ is_cat, const int32_t* __restrict__ column_num, int stats_size,
+                                   SplitTask* __restrict__ tasks) {
+    extern __shared__ int bucket_first[];
+    const int n = blockIdx.x, lane = threadIdx.x;
+    if (n >= n_nodes) return;
+    const int b0 = begin[n], k = begin[n + 1] - b0;
+    int cap = 1;
+    while (cap < k) cap <<= 1;
+    for (int i = lane; i < cap; i += 32) bucket_first[i] = 0;
+    __syncwarp();
+    auto bucket = [cap](int key) {
+        uint32_t x = (uint32_t)key;
+        x ^= x >> 16;
+        return (int)(x & (uint32_t)(cap - 1));
+    };
+    for (int i = lane; i < k; i += 32) atomicAdd(&bucket_first[bucket(column_num[feats[b0 + i]])], 1);
+    __syncwarp();
+    int running = 0;  // exclusive scan of the bucket sizes: first visit position of every bucket
+    for (int c0 = 0; c0 < cap; c0 += 32) {
+        const int v = (c0 + lane < cap) ? bucket_first[c0 + lane] : 0;
+        int incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (c0 + lane < cap) bucket_first[c0 + lane] = running + incl - v;
+        running += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    __syncwarp();
+    int64_t carry = 0;  // block offset of the next feature inside the node block
+    const uint32_t lt = (1u << lane) - 1u;
+    for (int c0 = 0; c0 < k; c0 += 32) {
+        const int i = c0 + lane;
+        const bool valid = i < k;
+        const int f = valid ? feats[b0 + i] : 0;
+        const int b = valid ? bucket(column_num[f]) : -1 - lane;
+        const uint32_t same = __match_any_sync(0xffffffffu, b);
+        int rank = 0;
+        if (valid) rank = bucket_first[b] + __popc(same & lt);
+        __syncwarp();
+        if (valid && lane == __ffs(same) - 1) bucket_first[b] += __popc(same);
+        __syncwarp();
+        const int64_t size = valid ? (int64_t)feat_bins[f] * stats_size : 0;
+        int64_t incl = size;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int64_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (valid) {
+            SplitTask t;
+            t.node = n;
+            t.feature = f;
+            t.offset = node_off[n] + carry + incl - size;
+            t.n_bins = feat_bins[f];
+            t.categorical = is_cat[f];
+            t.visit_rank = rank;
+            t.pad = 0;
+            tasks[b0 + i] = t;
+        }
+        carry += __shfl_sync(0xffffffffu, incl, 31);
+    }
+}
+cudaError_t launch_build_tasks(const int32_t* feats, const int32_t* begin, const int64_t* node_off, int n_nodes, int max_list,
+                               const int32_t* feat_bins, const uint8_t* is_cat, const int32_t* column_num, int stats_size,
+                               SplitTask* tasks, cudaStream_t s) {
+    if (n_nodes <= 0) return cudaSuccess;
+    int cap = 1;
+    while (cap < max_list) cap <<= 1;
+    build_tasks_kernel<<<n_nodes, 32, (size_t)cap * sizeof(int), s>>>(feats, begin, node_off, n_nodes, feat_bins, is_cat, column_num,
+                                                                       stats_size, tasks);
+    return cudaGetLastError();
+}
+
 // Count statistic (stat 0) of every bin of a raw block, saved to / restored from a cache of (lo, hi) pairs.
 __global__ void counts_cache_kernel(int64_t* __restrict__ raw_lo, int64_t* __restrict__ raw_hi, int64_t* __restrict__ cache,
                                     int64_t n_bins_total, int stats_size, int save) {
