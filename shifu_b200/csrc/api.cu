@@ -142,6 +142,7 @@ struct HistLaunch {
     RowListArgs list{};
     HistRowsArgs rows{};
     int root_counts = 0;   // 1: save the bin counts of this root pass after the kernel; 2: the kernel skips them, restore
+    int root_wcol = 0;     // sample-weight column the counts belong to
     int64_t root_bins = 0;
 };
 
@@ -957,11 +958,8 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                     } else {
                         SB_CUDA(h->root_cnt.reserve(h->stream, (size_t)(2 * L.root_bins)));
                         L.root_counts = 1;
-                        h->root_cnt_valid = true;
-                        h->root_cnt_version = h->weights_version;
-                        h->root_cnt_wcol = wcol;
-                        h->root_cnt_total = lay.total;
-                        h->root_cnt_feats = feats;
+                        L.root_wcol = wcol;
+                        h->root_cnt_valid = false;  // valid again once the saving kernel of THIS pass is enqueued (run_histograms)
                     }
                 }
                 L.grid = max_chunks * std::max(n_rt, 1);
@@ -1152,6 +1150,13 @@ int run_histograms(sb_handle* h) {
                 SB_CUDA(launch_counts_cache(L.rows.raw_lo, L.rows.raw_hi, h->root_cnt.p, L.root_bins, h->stats_size,
                                             L.root_counts == 1, h->stream));
                 h->launches_count += 1;
+                if (L.root_counts == 1) {  // only now does the cache describe something: a pass that stopped earlier leaves it invalid
+                    h->root_cnt_valid = true;
+                    h->root_cnt_version = h->weights_version;
+                    h->root_cnt_wcol = L.root_wcol;
+                    h->root_cnt_total = h->layout.total;
+                    h->root_cnt_feats = h->layout.nodes.empty() ? std::vector<int>() : h->layout.nodes[0].features;
+                }
             }
             if (L.has_wide) {
                 SB_CUDA(hist_rows_wide_launch(L.kind, L.cnt_int, L.wide, L.wide_grid, L.wide_smem, h->stream));
