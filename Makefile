@@ -3,7 +3,7 @@
 NVCC ?= /usr/local/cuda/bin/nvcc
 NVCCFLAGS = -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -fmad=false -Xcompiler -fPIC,-fvisibility=hidden
 CSRC = shifu_b200/csrc
-SRCS = api.cu rowlist.cu hist.cu rows.cu split.cu noalloc.cu prep.cu score.cu host_master.cpp wire.cpp
+SRCS = api.cu rowlist.cu hist.cu rows.cu split.cu noalloc.cu prep.cu score.cu p2p.cu host_master.cpp wire.cpp
 OBJS = $(addprefix build/,$(addsuffix .o,$(basename $(SRCS))))
 HDRS = $(CSRC)/common.cuh $(CSRC)/kernels.cuh include/shifu_b200.h
 

@@ -29,10 +29,13 @@ struct DevBuf {  // grow-only device buffer; or an alias of a piece of the per-p
     T* p = nullptr;
     size_t cap = 0;
     bool owned = true;
+    size_t fixed = 0;  // capacity of an aliased buffer that may be kept as long as it is large enough
     // Growth is stream-ordered (cudaMallocAsync / cudaFreeAsync): cudaFree would wait for everything queued on the
     // device, and the buffers of a pass grow while the kernels of its first half are still running.
     cudaError_t reserve(cudaStream_t stream, size_t n) {
         if (owned && n <= cap) return cudaSuccess;
+        if (!owned && n <= fixed) return cudaSuccess;
+        fixed = 0;
         if (p && owned) cudaFreeAsync(p, stream);
         p = nullptr;
         cap = 0;
@@ -44,11 +47,12 @@ struct DevBuf {  // grow-only device buffer; or an alias of a piece of the per-p
         if (e == cudaSuccess) cap = want;
         return e;
     }
-    void alias(T* q) {
+    void alias(T* q, size_t fixed_capacity = 0) {
         if (p && owned) cudaFreeAsync(p, 0);
         p = q;
         cap = 0;
         owned = false;
+        fixed = fixed_capacity;
     }
     void release() {
         if (p && owned) cudaFreeAsync(p, 0);
@@ -209,6 +213,15 @@ struct sb_handle {
     bool has_cat_tasks = false;
     double* d_acc = nullptr;          // 4 doubles
     ncclComm_t comm = nullptr;        // set by sb_dist_init: the pass merges itself over NCCL
+    struct P2P {  // accumulators in peer-mapped memory: the merge is launch_p2p_allreduce (p2p.cu) instead of ncclAllReduce
+        bool ok = false;
+        P2PView view{};
+        int64_t* buf[2] = {nullptr, nullptr};
+        uint32_t* flags = nullptr;
+        size_t cap_elems = 0;
+        uint32_t epoch = 0;
+        std::vector<void*> opened;  // peer mappings to close
+    } p2p;
     int world = 1, rank = 0;
     void* pin = nullptr;              // pinned host block: PinnedOut, then the sb_gain records (+ category bits)
     size_t pin_bytes = 0;
@@ -260,6 +273,10 @@ struct sb_handle {
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
     std::vector<int> prof_launches;
 };
+
+extern "C" {
+static void p2p_teardown(sb_handle* h);
+}
 
 namespace {
 
@@ -1112,6 +1129,7 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
     bool ok = false;
 };
@@ -1127,6 +1145,7 @@ NcclApi& nccl_api() {
     api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(dlsym(lib, "ncclCommInitRank"));
     api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(dlsym(lib, "ncclCommDestroy"));
     api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(dlsym(lib, "ncclAllReduce"));
+    api.AllGather = reinterpret_cast<decltype(api.AllGather)>(dlsym(lib, "ncclAllGather"));
     api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(dlsym(lib, "ncclGetErrorString"));
     api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllReduce && api.GetErrorString;
     return api;
@@ -1265,6 +1284,7 @@ SB_API void sb_destroy(sb_handle* h) {
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
     if (h->trace) dump_trace(h);
+    if (h->p2p.buf[0] || h->p2p.flags) p2p_teardown(h);
     h->stage.release();
     free_rowset(h->train);
     free_rowset(h->valid);
@@ -1797,8 +1817,15 @@ SB_API int sb_compute_stats(sb_handle* h) {
     if (h->comm) {
         // the DTMaster merge (dt/DTMaster.java:316-331 adds the workers' statistics node by node): one integer sum
         // over all GPUs, exact and order-independent; plus the four error scalars when this pass recomputed them
-        if (h->layout.total > 0)
-            SB_NCCL(nccl_api().AllReduce(h->raw.p, h->raw.p, (size_t)(2 * h->layout.total), ncclInt64, ncclSum, h->comm, h->stream));
+        if (h->layout.total > 0) {
+            const int which = h->raw.p == h->p2p.buf[0] ? 0 : (h->raw.p == h->p2p.buf[1] ? 1 : -1);
+            if (h->p2p.ok && which >= 0) {  // the accumulators sit in peer-mapped memory: merge over NVLink loads (p2p.cu)
+                SB_CUDA(launch_p2p_allreduce(h->p2p.view, which, 2 * h->layout.total, ++h->p2p.epoch, h->d_error_flag, h->stream));
+                h->launches_count += 5;
+            } else {
+                SB_NCCL(nccl_api().AllReduce(h->raw.p, h->raw.p, (size_t)(2 * h->layout.total), ncclInt64, ncclSum, h->comm, h->stream));
+            }
+        }
         if (h->acc_fresh) SB_NCCL(nccl_api().AllReduce(h->d_acc, h->d_acc, 4, ncclFloat64, ncclSum, h->comm, h->stream));
     }
     if (h->trace && !h->passes_trace.empty()) {
@@ -1819,6 +1846,93 @@ SB_API int sb_dist_unique_id(uint8_t* id128) {
     return SB_OK;
 }
 
+// Accumulators in peer-mapped memory (p2p.cu).  Any failure leaves the NCCL merge in place; every rank must reach the
+// same answer, so the ranks vote.  Two buffers: the accumulators of this pass and of the previous one swap every pass.
+static void p2p_teardown(sb_handle* h) {
+    for (void* q : h->p2p.opened) cudaIpcCloseMemHandle(q);
+    h->p2p.opened.clear();
+    for (int k = 0; k < 2; ++k) {
+        if (h->raw.p == h->p2p.buf[k]) h->raw.alias(nullptr);
+        if (h->raw_prev.p == h->p2p.buf[k]) h->raw_prev.alias(nullptr);
+        if (h->p2p.buf[k]) cudaFree(h->p2p.buf[k]);
+        h->p2p.buf[k] = nullptr;
+    }
+    if (h->p2p.flags) cudaFree(h->p2p.flags);
+    h->p2p.flags = nullptr;
+    h->p2p.ok = false;
+    cudaGetLastError();
+}
+
+static int p2p_setup(sb_handle* h) {
+    NcclApi& api = nccl_api();
+    if (h->world < 2 || h->world > P2P_MAX_WORLD || !api.AllGather || getenv("SB_NO_P2P")) return SB_OK;
+    struct Wire { cudaIpcMemHandle_t mem[3]; int32_t ok; int32_t pad; };
+    static_assert(sizeof(Wire) % 8 == 0, "all-gathered as bytes");
+    const size_t mb = getenv("SB_P2P_MB") ? (size_t)atol(getenv("SB_P2P_MB")) : 96;  // per buffer; C2 needs 39 MB
+    const size_t cap_bytes = mb << 20;
+    Wire mine{};
+    mine.ok = 1;
+    bool local_ok = cudaMalloc((void**)&h->p2p.buf[0], cap_bytes) == cudaSuccess && cudaMalloc((void**)&h->p2p.buf[1], cap_bytes) == cudaSuccess &&
+                    cudaMalloc((void**)&h->p2p.flags, 3 * P2P_MAX_WORLD * sizeof(uint32_t)) == cudaSuccess;
+    if (local_ok) {
+        cudaMemset(h->p2p.flags, 0, 3 * P2P_MAX_WORLD * sizeof(uint32_t));
+        local_ok = cudaIpcGetMemHandle(&mine.mem[0], h->p2p.buf[0]) == cudaSuccess && cudaIpcGetMemHandle(&mine.mem[1], h->p2p.buf[1]) == cudaSuccess &&
+                   cudaIpcGetMemHandle(&mine.mem[2], h->p2p.flags) == cudaSuccess;
+    }
+    if (!local_ok) { mine.ok = 0; cudaGetLastError(); }
+    // the handles travel in one all-gather
+    Wire *d_send = nullptr, *d_recv = nullptr;
+    SB_CUDA(cudaMalloc((void**)&d_send, sizeof(Wire)));
+    SB_CUDA(cudaMalloc((void**)&d_recv, sizeof(Wire) * (size_t)h->world));
+    SB_CUDA(cudaMemcpyAsync(d_send, &mine, sizeof(Wire), cudaMemcpyHostToDevice, h->stream));
+    SB_NCCL(api.AllGather(d_send, d_recv, sizeof(Wire), ncclChar, h->comm, h->stream));
+    std::vector<Wire> all((size_t)h->world);
+    SB_CUDA(cudaMemcpyAsync(all.data(), d_recv, sizeof(Wire) * (size_t)h->world, cudaMemcpyDeviceToHost, h->stream));
+    SB_CUDA(cudaStreamSynchronize(h->stream));
+    int32_t ok = 1;
+    for (auto& w : all) ok &= w.ok;
+    P2PView v{};
+    v.world = h->world;
+    v.rank = h->rank;
+    for (int p = 0; p < h->world && ok; ++p) {
+        if (p == h->rank) {
+            v.peer_buf[0][p] = h->p2p.buf[0];
+            v.peer_buf[1][p] = h->p2p.buf[1];
+            v.peer_flags[p] = h->p2p.flags;
+            continue;
+        }
+        void* q[3] = {nullptr, nullptr, nullptr};
+        for (int k = 0; k < 3 && ok; ++k) {
+            if (cudaIpcOpenMemHandle(&q[k], all[(size_t)p].mem[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = 0; cudaGetLastError(); }
+            else h->p2p.opened.push_back(q[k]);
+        }
+        v.peer_buf[0][p] = static_cast<int64_t*>(q[0]);
+        v.peer_buf[1][p] = static_cast<int64_t*>(q[1]);
+        v.peer_flags[p] = static_cast<uint32_t*>(q[2]);
+    }
+    // vote: a rank that could not map a peer takes everybody back to NCCL
+    int32_t* d_vote = reinterpret_cast<int32_t*>(d_send);
+    SB_CUDA(cudaMemcpyAsync(d_vote, &ok, 4, cudaMemcpyHostToDevice, h->stream));
+    SB_NCCL(api.AllReduce(d_vote, d_vote, 1, ncclInt32, ncclMin, h->comm, h->stream));
+    SB_CUDA(cudaMemcpyAsync(&ok, d_vote, 4, cudaMemcpyDeviceToHost, h->stream));
+    SB_CUDA(cudaStreamSynchronize(h->stream));
+    cudaFree(d_send);
+    cudaFree(d_recv);
+    if (!ok) {
+        if (h->trace) fprintf(stderr, "SB_TRACE rank %d: peer mapping not available, merging with ncclAllReduce\n", h->rank);
+        p2p_teardown(h);
+        return SB_OK;
+    }
+    h->p2p.view = v;
+    h->p2p.cap_elems = cap_bytes / sizeof(int64_t);
+    h->p2p.ok = true;
+    if (h->trace) fprintf(stderr, "SB_TRACE rank %d: accumulators in peer-mapped memory (%zu MB x 2): merge over NVLink loads\n", h->rank, mb);
+    h->raw.alias(h->p2p.buf[0], h->p2p.cap_elems);
+    h->raw_prev.alias(h->p2p.buf[1], h->p2p.cap_elems);
+    h->prev_valid = false;
+    return SB_OK;
+}
+
 SB_API int sb_dist_init(sb_handle* h, const uint8_t* id128, int32_t rank, int32_t world_size) {
     if (!h || !id128) return fail(SB_ERR_INVALID, "null argument");
     if (world_size < 1 || rank < 0 || rank >= world_size) return fail(SB_ERR_INVALID, "rank / world_size out of range");
@@ -1831,7 +1945,7 @@ SB_API int sb_dist_init(sb_handle* h, const uint8_t* id128, int32_t rank, int32_
     SB_NCCL(api.CommInitRank(&h->comm, world_size, id, rank));
     h->world = world_size;
     h->rank = rank;
-    return SB_OK;
+    return p2p_setup(h);
 }
 
 SB_API int sb_set_profiling(sb_handle* h, int32_t on) {
@@ -1925,6 +2039,7 @@ static int finish_check(sb_handle* h, sb_iter_out* out) {
     if (flags & 2u) return fail(SB_ERR_RANGE, "a bin index is outside [0, n_bins) of its feature");
     if (flags & 4u) return fail(SB_ERR_STATE, "NextNode is null: a split node is missing a child (dt/DTWorker.java:1089-1094)");
     if (flags & 8u) return fail(SB_ERR_STATE, "internal: the chunk table of a row list overflowed");
+    if (flags & 16u) return fail(SB_ERR_CUDA, "multi-GPU merge: a peer did not reach the barrier within two seconds");
     for (int k = 0; k < 3; ++k)
         if ((po->maxbits[k] & 0x7f800000u) == 0x7f800000u) return fail(SB_ERR_RANGE, "non-finite per-row contribution (label, significance or weight)");
     if ((po->maxbits[0] >> 23) >= 127 + 38) return fail(SB_ERR_RANGE, "significance * weight beyond 2^38");

@@ -218,6 +218,15 @@ cudaError_t launch_stratified_mask(float* weights, const float* label, int64_t n
 cudaError_t launch_poisson_bags(float* weights, int64_t n, unsigned long long seed, long long row0, int tree, double rate, double p0,
                                 cudaStream_t s);
 
+// ---- p2p.cu: all-reduce of the integer accumulators over NVLink peer memory (GPUs of one box)
+constexpr int P2P_MAX_WORLD = 8;
+struct P2PView {
+    int world, rank;
+    int64_t* peer_buf[2][P2P_MAX_WORLD];   // the two accumulator buffers (this pass / previous pass) of every rank, as mapped here
+    uint32_t* peer_flags[P2P_MAX_WORLD];   // every rank's barrier words: [3 barriers][P2P_MAX_WORLD arrivals]
+};
+cudaError_t launch_p2p_allreduce(const P2PView& v, int which, int64_t n_elems, uint32_t epoch, uint32_t* error_flag, cudaStream_t s);
+
 // ---- split.cu
 // raw (lo, hi) integer accumulators -> the reference's double statistics (one rounding each).
 cudaError_t launch_finalize(const int64_t* raw_lo, const int64_t* raw_hi, int64_t total, int stats_size, int kind,
