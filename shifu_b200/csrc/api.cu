@@ -2039,7 +2039,7 @@ static int finish_check(sb_handle* h, sb_iter_out* out) {
     if (flags & 2u) return fail(SB_ERR_RANGE, "a bin index is outside [0, n_bins) of its feature");
     if (flags & 4u) return fail(SB_ERR_STATE, "NextNode is null: a split node is missing a child (dt/DTWorker.java:1089-1094)");
     if (flags & 8u) return fail(SB_ERR_STATE, "internal: the chunk table of a row list overflowed");
-    if (flags & 16u) return fail(SB_ERR_CUDA, "multi-GPU merge: a peer did not reach the barrier within two seconds");
+    if (flags & 16u) return fail(SB_ERR_CUDA, "multi-GPU merge: a peer did not reach the barrier within thirty seconds");
     for (int k = 0; k < 3; ++k)
         if ((po->maxbits[k] & 0x7f800000u) == 0x7f800000u) return fail(SB_ERR_RANGE, "non-finite per-row contribution (label, significance or weight)");
     if ((po->maxbits[0] >> 23) >= 127 + 38) return fail(SB_ERR_RANGE, "significance * weight beyond 2^38");
