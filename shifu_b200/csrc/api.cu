@@ -1820,7 +1820,8 @@ SB_API int sb_compute_stats(sb_handle* h) {
         if (h->layout.total > 0) {
             const int which = h->raw.p == h->p2p.buf[0] ? 0 : (h->raw.p == h->p2p.buf[1] ? 1 : -1);
             if (h->p2p.ok && which >= 0) {  // the accumulators sit in peer-mapped memory: merge over NVLink loads (p2p.cu)
-                SB_CUDA(launch_p2p_allreduce(h->p2p.view, which, 2 * h->layout.total, ++h->p2p.epoch, h->d_error_flag, h->stream));
+                SB_CUDA(launch_p2p_allreduce(h->p2p.view, which, 2 * h->layout.total, ++h->p2p.epoch, h->enable_subtraction ? 0 : 1,
+                                             h->d_error_flag, h->stream));
                 h->launches_count += 5;
             } else {
                 SB_NCCL(nccl_api().AllReduce(h->raw.p, h->raw.p, (size_t)(2 * h->layout.total), ncclInt64, ncclSum, h->comm, h->stream));

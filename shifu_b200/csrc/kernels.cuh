@@ -225,7 +225,8 @@ struct P2PView {
     int64_t* peer_buf[2][P2P_MAX_WORLD];   // the two accumulator buffers (this pass / previous pass) of every rank, as mapped here
     uint32_t* peer_flags[P2P_MAX_WORLD];   // every rank's barrier words: [3 barriers][P2P_MAX_WORLD arrivals]
 };
-cudaError_t launch_p2p_allreduce(const P2PView& v, int which, int64_t n_elems, uint32_t epoch, uint32_t* error_flag, cudaStream_t s);
+cudaError_t launch_p2p_allreduce(const P2PView& v, int which, int64_t n_elems, uint32_t epoch, int tail_barrier, uint32_t* error_flag,
+                                 cudaStream_t s);
 
 // ---- split.cu
 // raw (lo, hi) integer accumulators -> the reference's double statistics (one rounding each).

@@ -8,7 +8,7 @@
 //             no multicast), adds the integers in rank order and writes the sum into its own buffer
 //   barrier   every slice is final
 //   gather    rank r copies the other slices from their owners' buffers
-//   barrier   nobody still reads a buffer that the next pass clears
+//   barrier   nobody still reads a buffer that the next pass clears (skipped when the two buffers alternate)
 // Integer addition makes the result independent of the order of the reads, so it equals the NCCL sum bit for bit.  The
 // barriers are flag words in peer memory written with system-scope release stores and polled with acquire loads; a
 // poll gives up after about thirty seconds and raises the handle's error flag instead of hanging the GPU.
@@ -96,7 +96,8 @@ __global__ void __launch_bounds__(256) p2p_gather_kernel(P2PView v, int which, i
 
 }  // namespace
 
-cudaError_t launch_p2p_allreduce(const P2PView& v, int which, int64_t n_elems, uint32_t epoch, uint32_t* error_flag, cudaStream_t s) {
+cudaError_t launch_p2p_allreduce(const P2PView& v, int which, int64_t n_elems, uint32_t epoch, int tail_barrier, uint32_t* error_flag,
+                                 cudaStream_t s) {
     // n_elems int64 values, an even number (lo and hi planes of equal length): 16-byte units
     const int64_t n2 = (n_elems + 1) / 2;
     p2p_barrier_kernel<<<1, 32, 0, s>>>(v, 0, epoch, error_flag);
@@ -110,7 +111,10 @@ cudaError_t launch_p2p_allreduce(const P2PView& v, int which, int64_t n_elems, u
         if (grid < 1) grid = 1;
         p2p_gather_kernel<<<grid, 256, 0, s>>>(v, which, n2);
     }
-    p2p_barrier_kernel<<<1, 32, 0, s>>>(v, 2, epoch, error_flag);
+    // When the two buffers alternate from pass to pass (histogram subtraction keeps the previous pass), a buffer is
+    // cleared again only after its owner passed the first two barriers of the NEXT pass, which every rank reaches after
+    // its gather of this one: the third barrier is then implied.
+    if (tail_barrier) p2p_barrier_kernel<<<1, 32, 0, s>>>(v, 2, epoch, error_flag);
     return cudaGetLastError();
 }
 
