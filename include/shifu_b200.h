@@ -61,6 +61,9 @@ enum { SB_SPLIT_CONTINUOUS = 1, SB_SPLIT_CATEGORICAL = 2 };
                                      sibling pair as parent - smaller child (same numbers either way) */
 #define SB_FLAG_NO_ROOT_COUNT_CACHE 8u /* accumulate the bin counts of a tree root every time instead of reusing those of the
                                           previous root pass while the sample weights are unchanged */
+#define SB_FLAG_NO_FOREST_PASS 16u /* RF: one set of launches per tree and pass instead of one for all trees of the pass
+                                      (same numbers either way; the forest pass needs room for one operand record per
+                                      active (row, tree) pair) */
 #define SB_FLAG_NO_ROW_LISTS 2u  /* never build per-pass row lists / the row-major bin copy: passes with more todo
                                     nodes than one shared-memory slot group then stream the column tiles once per group
                                     (slower, but needs no extra memory) */

@@ -36,13 +36,13 @@ struct DevBuf {  // grow-only device buffer; or an alias of a piece of the per-p
         if (owned && n <= cap) return cudaSuccess;
         if (!owned && n <= fixed) return cudaSuccess;
         fixed = 0;
+        // 4x: the statistics of a level-wise tree double with every level, and a pool that has to map new memory
+        // costs about 10 us per MB
+        const size_t want = std::max<size_t>((owned && cap) ? 4 * n : n, 16);
         if (p && owned) cudaFreeAsync(p, stream);
         p = nullptr;
         cap = 0;
         owned = true;
-        // 4x: the statistics of a level-wise tree double with every level, and a pool that has to map new memory
-        // costs about 10 us per MB
-        size_t want = std::max<size_t>(cap ? 4 * n : n, 16);
         cudaError_t e = cudaMallocAsync((void**)&p, want * sizeof(T), stream);
         if (e == cudaSuccess) cap = want;
         return e;
@@ -240,11 +240,37 @@ struct sb_handle {
     DevBuf<int32_t> rl_chunk_group;  // [max] + n_chunks scalar at the end
     DevBuf<RowOps> rl_ops;        // [n]
     DevBuf<int32_t> twin_map;     // feature held at each byte position of a twin row
+    DevBuf<int32_t> twin_pos;     // feature slot -> byte position in a twin row (-1: a uint16 column)
+    std::vector<int32_t> twin_pos_host;  // the same on the host (empty: no twin yet)
     DevBuf<int32_t> rt_tiles;     // row-list path: tile_feats [n_rt][32*fpl] then tile_slot0 [n_rt]
     DevBuf<uint32_t> rt_fmask;    // [n_slots][n_rt][fpl]
     DevBuf<int32_t> wt_tiles;     // wide tiles: tile_feats [n_wt][8] then first wide index [n_wt]
     DevBuf<uint32_t> wt_fmask;    // [n_slots][n_wt]
     bool enable_row_lists = true;
+    // forest passes (RF): all trees of a pass in one set of launches (plan_forest / run_forest)
+    bool enable_forest = true;
+    int sm_count = 148;
+    bool forest_pass = false;       // this pass's statistics are planned as a forest pass (layout.flat)
+    struct ForestBatch {            // trees whose pair list fits the operand buffer and the key limit
+        ForestListArgs list{};
+        int slim = 0, fpl = 1;
+        HistClassArgs cls{};
+        HistRowsArgs rows{};
+        int grid = 0;
+        size_t smem = 0;
+    };
+    std::vector<ForestBatch> forest_batches;
+    DevBuf<uint8_t> forest_ops;     // ClassOps or RowOps of the active (row, tree) pairs of one batch
+    DevBuf<uint32_t> forest_counts; // [2][n_keys * n_ranges + 1]
+    DevBuf<int64_t> forest_pair_off;
+    size_t forest_scan_items = 0, forest_scan_temp = 0;
+    size_t forest_ops_budget = 0;   // bytes the operand buffer may take (half of the free memory at first use)
+    // the flat feature lists of the pass on the device (shared by the pair_off and the split task kernels)
+    const int32_t *d_flat_feats = nullptr, *d_flat_begin = nullptr;
+    const int64_t* d_flat_node_off = nullptr;
+    int flat_max_list = 0, flat_max_cat_bins = 0;
+    bool flat_has_cat = false;
+    std::vector<uint32_t> col_flags;  // per sample-weight column: bit0 non-integer products, bit1 a weight != 1
     size_t scan_temp_bytes = 0;
     bool split_planned = false;
     bool acc_valid = false;     // d_acc holds the error sums of the current Data.predict (GBT, inside a tree)
@@ -344,19 +370,28 @@ int n_node_arrays(const sb_handle* h) { return h->cfg.is_gbdt ? 1 : std::max(1, 
 
 // Decides whether the count statistic can be accumulated as plain 32-bit integers (see hist.cu).  Synchronises;
 // called at load time and whenever the caller injects new sample weights.
-int refresh_cnt_int(sb_handle* h) {
+int refresh_cnt_int(sb_handle* h, int only_col = -1) {
     RowSet& r = h->train;
     uint32_t* flag_dev = reinterpret_cast<uint32_t*>(h->d_cnt_shift) + 1;  // second word of the same allocation
-    SB_CUDA(cudaMemsetAsync(flag_dev, 0, 4, h->stream));
     const int W = r.weights ? h->cfg.weights_per_row : 1;
-    for (int c = 0; c < W; ++c) {
+    // a column's verdict depends on that column and the significances alone: after a change of one column only that
+    // one is looked at again (an RF draws its 50 bags one call at a time)
+    if ((int)h->col_flags.size() != W || only_col < 0 || only_col >= W) {
+        h->col_flags.assign((size_t)W, 0u);
+        only_col = -1;
+    }
+    uint32_t flag = 0;
+    for (int c = (only_col >= 0 ? only_col : 0); c < (only_col >= 0 ? only_col + 1 : W); ++c) {
+        SB_CUDA(cudaMemsetAsync(flag_dev, 0, 4, h->stream));
         SB_CUDA(launch_check_int_weights(r.n, r.significance, r.weights ? r.weights + (int64_t)c * r.n : nullptr, flag_dev,
                                          h->stream));
         h->launches_count += 1;
+        SB_CUDA(cudaMemcpyAsync(&flag, flag_dev, 4, cudaMemcpyDeviceToHost, h->stream));
+        SB_CUDA(cudaStreamSynchronize(h->stream));
+        h->col_flags[(size_t)c] = flag;
     }
-    uint32_t flag = 0;
-    SB_CUDA(cudaMemcpyAsync(&flag, flag_dev, 4, cudaMemcpyDeviceToHost, h->stream));
-    SB_CUDA(cudaStreamSynchronize(h->stream));
+    flag = 0;
+    for (uint32_t f : h->col_flags) flag |= f;
     h->cnt_int = (flag & 1u) == 0;
     h->weights_all_one = (flag & 2u) == 0;  // then the weight arrays need not be read at all (x * 1.0f == x)
     h->weights_version += 1;  // every caller changed (or loaded) sample weights
@@ -461,14 +496,82 @@ int upload_tree(sb_handle* h, const sb_tree& t, DeviceTree& d) {
     }
     if (t.mask_pool_bytes > 0) memcpy(masks, t.mask_pool, (size_t)t.mask_pool_bytes);
     h->h2d_bytes += (int64_t)cap * 17 + t.mask_pool_bytes;
+    d.walk = nullptr;
+    if (!h->cfg.is_gbdt && h->enable_forest) {  // the same nodes as 32-byte records for forest_walk_kernel
+        WalkNode *wn = nullptr, *d_wn = nullptr;
+        SB_CUDA(h->stage.take((size_t)cap, &wn, &d_wn, h->stream));
+        memset(wn, 0, (size_t)cap * sizeof(WalkNode));
+        for (int i = 0; i < cap; ++i) { wn[i].feat = -1; wn[i].pos = -1; }
+        for (int i = 0; i < t.n_nodes; ++i) {
+            const sb_node& nd = t.nodes[i];
+            WalkNode& w = wn[nd.id];
+            if (feat[nd.id] >= 0) {
+                w.feat = nd.feature;
+                w.pos = h->twin_pos_host.empty() ? -1 : h->twin_pos_host[(size_t)nd.feature];
+                w.mask_off = (uint32_t)nd.left_mask_offset;
+                if (h->n_bins[nd.feature] <= 64) {
+                    uint64_t m = 0;
+                    memcpy(&m, t.mask_pool + nd.left_mask_offset, (size_t)std::min(8, nd.left_mask_bytes));
+                    w.mask64 = m;
+                    w.flags |= 2u;
+                }
+            }
+            w.predict = (float)nd.predict;
+            if (nd.has_predict) w.flags |= 1u;
+        }
+        d.walk = d_wn;
+        h->h2d_bytes += (int64_t)cap * (int64_t)sizeof(WalkNode);
+    }
     return SB_OK;
 }
 
 // dt/DTWorker.java:903-929 initTodoNodeStats: sizes and order of the statistics buffer.
-int build_layout(const sb_handle* h, const sb_iter_in* in, TodoLayout& lay) {
+int build_layout(const sb_handle* h, const sb_iter_in* in, TodoLayout& lay, bool flat = false) {
     // `lay` is recycled from an earlier pass: resize + assign keep the capacity of the inner vectors
     lay.nodes.resize((size_t)std::max(in->n_todo, 0));
+    lay.flat = flat;
+    lay.flat_begin.clear();
+    lay.flat_feats.clear();
     int64_t off = 0;
+    if (flat) {
+        // one flat array for all lists: a pass of an RF at depth 10 has 10^4 todo nodes with their own feature subsets
+        const int F = h->cfg.n_features;
+        const int n_all = (int)h->all_features.size();
+        size_t total_feats = 0;
+        for (int i = 0; i < in->n_todo; ++i) total_feats += (size_t)(in->todo[i].n_features == 0 ? n_all : in->todo[i].n_features);
+        if (total_feats > (size_t)0x7fffffff) return fail(SB_ERR_UNSUPPORTED, "more than 2^31 (todo node, feature) pairs in one pass");
+        lay.flat_feats.resize(total_feats);
+        lay.flat_begin.resize((size_t)in->n_todo + 1);
+        std::vector<int64_t> len_of((size_t)F);
+        for (int f = 0; f < F; ++f) len_of[(size_t)f] = (int64_t)h->n_bins[(size_t)f] * h->stats_size;
+        size_t at = 0;
+        for (int i = 0; i < in->n_todo; ++i) {
+            const sb_todo_node& t = in->todo[i];
+            TodoLayout::Node& nd = lay.nodes[(size_t)i];
+            nd.key = t.key; nd.tree_id = t.tree_id; nd.node_id = t.node_id; nd.offset = off;
+            nd.features.clear();
+            nd.feat_off.clear();
+            lay.flat_begin[(size_t)i] = (int32_t)at;
+            if (t.n_features == 0) {
+                if (n_all) memcpy(&lay.flat_feats[at], h->all_features.data(), (size_t)n_all * 4);
+                at += (size_t)n_all;
+                off += h->all_feat_total;
+                continue;
+            }
+            int64_t l = 0;
+            for (int k = 0; k < t.n_features; ++k) {
+                const int f = t.features[k];
+                if (f < 0 || f >= F) return fail(SB_ERR_INVALID, "todo node feature slot out of range");
+                lay.flat_feats[at + (size_t)k] = f;
+                l += len_of[(size_t)f];
+            }
+            at += (size_t)t.n_features;
+            off += l;
+        }
+        lay.flat_begin[(size_t)in->n_todo] = (int32_t)at;
+        lay.total = off;
+        return SB_OK;
+    }
     for (int i = 0; i < in->n_todo; ++i) {
         const sb_todo_node& t = in->todo[i];
         TodoLayout::Node& nd = lay.nodes[(size_t)i];
@@ -491,6 +594,11 @@ int build_layout(const sb_handle* h, const sb_iter_in* in, TodoLayout& lay) {
     }
     lay.total = off;
     return SB_OK;
+}
+
+// RF passes whose statistics go through one list for all trees (plan_forest): needs the row lists, uint8 bins only
+bool forest_lists(const sb_handle* h) {
+    return !h->cfg.is_gbdt && h->enable_forest && h->enable_row_lists && h->n_wide == 0 && h->train.n < (int64_t)0xffffffff;
 }
 
 // Iteration order of a java.util.HashMap<Integer, double[]> created with (n, 1f) and filled in list order
@@ -519,6 +627,89 @@ const sb_tree* find_tree(const sb_iter_in* in, int tree_id) {
     for (int i = 0; i < in->n_trees; ++i)
         if (in->trees[i].tree_id == tree_id && in->trees[i].n_nodes > 0) return &in->trees[i];
     return nullptr;
+}
+
+// Byte layout of a row of the row-major twin for `fpl` features per lane: full tiles of 32*fpl feature slots hold feature
+// fpl*lane + k in natural order; the last, partly filled tile spreads its r features over the lanes first (kact =
+// ceil(r / 32) features per lane), so the kernels issue kact instead of fpl rounds of atomics per row for it.
+void twin_positions(const sb_handle* h, int fpl, std::vector<int32_t>& pos_of, int& twin_pad) {
+    const int F = h->cfg.n_features;
+    pos_of.assign((size_t)F, -1);
+    const int tw = 32 * fpl;
+    for (int f0 = 0; f0 < F; f0 += tw) {
+        const int r = std::min(tw, F - f0), kact = (r + 31) / 32;
+        for (int j = 0; j < r; ++j) pos_of[f0 + j] = f0 + fpl * (j / kact) + (j % kact);
+    }
+    int max_pos = 0;
+    for (int f = 0; f < F; ++f) max_pos = std::max(max_pos, pos_of[f]);
+    // Row pitch: DRAM is fetched in whole 128-byte lines, so a tile of a row must not straddle lines -- rows
+    // wider than one line are padded to a multiple of 128 bytes (a 224-byte pitch read 450 bytes per row).
+    twin_pad = (max_pos / 32 + 1) * 32;
+    if (twin_pad > 128) twin_pad = (twin_pad + 127) / 128 * 128;
+}
+
+// The row-major twin of the training rows' bin matrix for this layout, built on first use (and again when the
+// statistics layout -- integer <-> real counts -- changes the features per lane).
+int ensure_twin(sb_handle* h, int fpl, const std::vector<int32_t>& pos_of, int twin_pad) {
+    RowSet& tr = h->train;
+    const int F = h->cfg.n_features;
+    const int64_t n = tr.n;
+    if (tr.bins_rm && tr.rm_fpl != fpl) {
+        SB_CUDA(cudaStreamSynchronize(h->stream));
+        cudaFree(tr.bins_rm);
+        tr.bins_rm = nullptr;
+        h->twin_pos_host.clear();
+    }
+    if (tr.bins_rm) return SB_OK;
+    // 32-byte row pitch: a lane group that reaches past F reads into the next row (masked out in
+    // the kernel); the allocation is padded so the last row's over-read stays inside it
+    tr.fpad = twin_pad;
+    tr.rm_fpl = fpl;
+    std::vector<int32_t> feat_of_pos((size_t)twin_pad, -1);
+    for (int f = 0; f < F; ++f) feat_of_pos[pos_of[f]] = f;
+    SB_CUDA(h->twin_map.reserve(h->stream, (size_t)twin_pad));
+    SB_CUDA(cudaMemcpyAsync(h->twin_map.p, feat_of_pos.data(), (size_t)twin_pad * 4, cudaMemcpyHostToDevice, h->stream));
+    // feature slot -> byte position, for kernels that look single bins up in the twin (forest_walk_kernel); uint16 columns are not in it
+    std::vector<int32_t> pos_dev(pos_of);
+    for (int f = 0; f < F; ++f)
+        if (h->wide_index[f] >= 0) pos_dev[f] = -1;
+    SB_CUDA(h->twin_pos.reserve(h->stream, (size_t)F));
+    SB_CUDA(cudaMemcpyAsync(h->twin_pos.p, pos_dev.data(), (size_t)F * 4, cudaMemcpyHostToDevice, h->stream));
+    h->twin_pos_host = pos_dev;
+    SB_CUDA(cudaStreamSynchronize(h->stream));  // the tables are locals
+    SB_CUDA(cudaMalloc(&tr.bins_rm, (size_t)std::max<int64_t>(n, 1) * tr.fpad + 256));
+    SB_CUDA(cudaMemsetAsync(tr.bins_rm + (size_t)std::max<int64_t>(n, 1) * tr.fpad, 0, 256, h->stream));  // what a lane group reads past the last row
+    SB_CUDA(launch_transpose_bins(static_cast<const uint8_t*>(tr.bins_base), tr.pitch, F, h->twin_map.p, n, tr.bins_rm, tr.fpad, h->stream));
+    h->launches_count += 1;
+    return SB_OK;
+}
+
+// Tiles of 32*fpl consecutive feature slots of the twin that hold a used feature: rt_feats [n_rt][32*fpl] (entry k*32+lane =
+// feature at byte slot0 + fpl*lane + k, or -1), rt_slot0, rt_kact (features per lane actually populated); rt_of[f] = tile
+void build_row_tiles(const sb_handle* h, const std::vector<uint8_t>& used, int fpl, const std::vector<int32_t>& pos_of,
+                     std::vector<int32_t>& rt_feats, std::vector<int32_t>& rt_slot0, std::vector<int32_t>& rt_kact,
+                     std::vector<int>& rt_of) {
+    const int F = h->cfg.n_features, tw = 32 * fpl;
+    rt_feats.clear(); rt_slot0.clear(); rt_kact.clear();
+    rt_of.assign((size_t)F, -1);
+    for (int f0 = 0; f0 < F; f0 += tw) {
+        bool any = false;
+        for (int f = f0; f < std::min(F, f0 + tw); ++f) any |= used[f] != 0;
+        if (!any) continue;
+        const int t = (int)rt_slot0.size();
+        rt_slot0.push_back(f0);
+        const size_t base = rt_feats.size();
+        rt_feats.resize(base + tw, -1);
+        int kact = 1;
+        for (int f = f0; f < std::min(F, f0 + tw); ++f) {
+            if (!used[f]) continue;
+            const int rel = pos_of[f] - f0;
+            rt_feats[base + (size_t)(rel % fpl) * 32 + rel / fpl] = f;
+            rt_of[f] = t;
+            kact = std::max(kact, rel % fpl + 1);
+        }
+        rt_kact.push_back(kact);
+    }
 }
 
 int plan_histograms(sb_handle* h, const sb_iter_in* in) {
@@ -694,46 +885,14 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
             if (rows_max_gs >= 1) { fpl = f; break; }
         }
     }
-    // Byte layout of a row of the row-major twin: full tiles hold features fpl*lane + k in natural order; the last,
-    // partly filled tile spreads its r features over the lanes first (kact = ceil(r / 32) features per lane), so the
-    // kernel issues kact instead of fpl rounds of atomics per row for it.
     std::vector<int32_t> pos_of((size_t)F, -1);
     int twin_pad = 32;
-    if (fpl > 0) {
-        const int tw = 32 * fpl;
-        for (int f0 = 0; f0 < F; f0 += tw) {
-            const int r = std::min(tw, F - f0), kact = (r + 31) / 32;
-            for (int j = 0; j < r; ++j) pos_of[f0 + j] = f0 + fpl * (j / kact) + (j % kact);
-        }
-        int max_pos = 0;
-        for (int f = 0; f < F; ++f) max_pos = std::max(max_pos, pos_of[f]);
-        // Row pitch: DRAM is fetched in whole 128-byte lines, so a tile of a row must not straddle lines -- rows
-        // wider than one line are padded to a multiple of 128 bytes (a 224-byte pitch read 450 bytes per row).
-        twin_pad = (max_pos / 32 + 1) * 32;
-        if (twin_pad > 128) twin_pad = (twin_pad + 127) / 128 * 128;
-    }
+    if (fpl > 0) twin_positions(h, fpl, pos_of, twin_pad);
     if (fpl > 0) {
         const int tw = 32 * fpl;
         std::vector<int32_t> rt_feats, rt_slot0, rt_kact;
-        std::vector<int> rt_of((size_t)F, -1);
-        for (int f0 = 0; f0 < F; f0 += tw) {
-            bool any = false;
-            for (int f = f0; f < std::min(F, f0 + tw); ++f) any |= used[f] != 0;
-            if (!any) continue;
-            const int t = (int)rt_slot0.size();
-            rt_slot0.push_back(f0);
-            const size_t base = rt_feats.size();
-            rt_feats.resize(base + tw, -1);
-            int kact = 1;
-            for (int f = f0; f < std::min(F, f0 + tw); ++f) {
-                if (!used[f]) continue;
-                const int rel = pos_of[f] - f0;
-                rt_feats[base + (size_t)(rel % fpl) * 32 + rel / fpl] = f;
-                rt_of[f] = t;
-                kact = std::max(kact, rel % fpl + 1);
-            }
-            rt_kact.push_back(kact);
-        }
+        std::vector<int> rt_of;
+        build_row_tiles(h, used, fpl, pos_of, rt_feats, rt_slot0, rt_kact, rt_of);
         n_rt = (int)rt_slot0.size();
         std::vector<uint32_t> rfm((size_t)S * n_rt * fpl, 0u);
         for (int s = 0; s < S; ++s) {
@@ -897,24 +1056,9 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                     SB_CUDA(launch_transpose_bins16(tr.bins16, tr.pitch16, h->n_wide, n, tr.bins16_rm, tr.wpad, h->stream));
                     h->launches_count += 1;
                 }
-                if (fpl > 0 && tr.bins_rm && tr.rm_fpl != fpl) {  // the statistics layout changed (integer <-> real counts)
-                    SB_CUDA(cudaStreamSynchronize(h->stream));
-                    cudaFree(tr.bins_rm);
-                    tr.bins_rm = nullptr;
-                }
-                if (fpl > 0 && !tr.bins_rm) {  // row-major twin of the bin matrix, built once
-                    // 32-byte row pitch: a lane group that reaches past F reads into the next row (masked out in
-                    // the kernel); the allocation is padded so the last row's over-read stays inside it
-                    tr.fpad = twin_pad;
-                    tr.rm_fpl = fpl;
-                    std::vector<int32_t> feat_of_pos((size_t)twin_pad, -1);
-                    for (int f = 0; f < F; ++f) feat_of_pos[pos_of[f]] = f;
-                    SB_CUDA(h->twin_map.reserve(h->stream, (size_t)twin_pad));
-                    SB_CUDA(cudaMemcpyAsync(h->twin_map.p, feat_of_pos.data(), (size_t)twin_pad * 4, cudaMemcpyHostToDevice, h->stream));
-                    SB_CUDA(cudaStreamSynchronize(h->stream));  // feat_of_pos is a local
-                    SB_CUDA(cudaMalloc(&tr.bins_rm, (size_t)std::max<int64_t>(n, 1) * tr.fpad + 256));
-                    SB_CUDA(launch_transpose_bins(static_cast<const uint8_t*>(tr.bins_base), tr.pitch, F, h->twin_map.p, n, tr.bins_rm, tr.fpad, h->stream));
-                    h->launches_count += 1;
+                if (fpl > 0) {
+                    const int trc = ensure_twin(h, fpl, pos_of, twin_pad);
+                    if (trc != SB_OK) return trc;
                 }
                 const int tiles_total = n_rt + n_wt;
                 static const int waves = getenv("SB_WAVES") ? atoi(getenv("SB_WAVES")) : 4;  // measured on C2 / C3: 54.4 ms per tree against 56.0 (1), 56.6 (2), 55.1 (3), 54.7 (8)
@@ -1032,12 +1176,257 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     return SB_OK;
 }
 
+// RF: the statistics of ALL trees of the pass from one list (dt/DTWorker.java:810-826 visits every tree of a row in one
+// pass over the rows).  Slots are numbered over the trees of the pass (todo nodes ordered by tree), slot groups are
+// ranges of that numbering -- a group may span trees -- and every active (row, tree) pair becomes one operand record
+// in its group's part of the list (rowlist.cu, forest_*).  One counting pass, one scan, one scatter and ONE statistics
+// launch per batch of trees; a batch is as many trees as the operand buffer and the key limit take (all 50 trees of a
+// 10M-row forest).  Host work per pass is linear in the flat feature lists: no per-node vectors, no per-slot masks
+// (every slot accumulates every feature of a launched tile; columns outside a node's list are never flushed), and the
+// (slot, feature) offset table is filled on the device from the lists.
+int plan_forest(sb_handle* h, const sb_iter_in* in) {
+    (void)in;
+    h->forest_batches.clear();
+    h->launches.clear();
+    const TodoLayout& lay = h->layout;
+    const int F = h->cfg.n_features;
+    const int N = (int)lay.nodes.size();
+    RowSet& tr = h->train;
+    const int64_t n = tr.n;
+    h->d_flat_feats = h->d_flat_begin = nullptr;
+    h->d_flat_node_off = nullptr;
+    h->flat_max_list = 0;
+    h->flat_has_cat = false;
+    h->flat_max_cat_bins = 0;
+    if (N == 0) return SB_OK;
+
+    // ---- the lists on the device + what the split step wants to know about them
+    std::vector<uint8_t> used((size_t)F, 0);
+    for (int32_t f : lay.flat_feats) used[(size_t)f] = 1;
+    for (int i = 0; i < N; ++i) h->flat_max_list = std::max(h->flat_max_list, lay.flat_begin[(size_t)i + 1] - lay.flat_begin[(size_t)i]);
+    for (int f = 0; f < F; ++f)
+        if (used[(size_t)f] && h->is_cat[(size_t)f]) { h->flat_has_cat = true; h->flat_max_cat_bins = std::max(h->flat_max_cat_bins, h->n_bins[(size_t)f]); }
+    {
+        int32_t *hf = nullptr, *df = nullptr, *hb = nullptr, *db = nullptr;
+        int64_t *ho = nullptr, *dof = nullptr;
+        SB_CUDA(h->stage.take(std::max<size_t>(lay.flat_feats.size(), 1), &hf, &df, h->stream));
+        SB_CUDA(h->stage.take((size_t)N + 1, &hb, &db, h->stream));
+        SB_CUDA(h->stage.take((size_t)N, &ho, &dof, h->stream));
+        if (!lay.flat_feats.empty()) memcpy(hf, lay.flat_feats.data(), lay.flat_feats.size() * 4);
+        memcpy(hb, lay.flat_begin.data(), ((size_t)N + 1) * 4);
+        for (int i = 0; i < N; ++i) ho[i] = lay.nodes[(size_t)i].offset;
+        h->d_flat_feats = df; h->d_flat_begin = db; h->d_flat_node_off = dof;
+        h->h2d_bytes += (int64_t)lay.flat_feats.size() * 4 + ((int64_t)N + 1) * 4 + (int64_t)N * 8;
+    }
+    if (n == 0) return SB_OK;  // a shard without rows still takes part in the merge
+
+    // ---- slots: todo nodes ordered by tree (stable counting sort), one slot each
+    const int T_arr = tr.n_node_arrays;
+    std::vector<int> first((size_t)T_arr + 1, 0);
+    for (int i = 0; i < N; ++i) {
+        const int t = lay.nodes[(size_t)i].tree_id;
+        if (t < 0 || t >= T_arr) return fail(SB_ERR_INVALID, "todo node tree id out of range");
+        if (lay.nodes[(size_t)i].node_id <= 0) return fail(SB_ERR_INVALID, "todo node with non-positive id");
+        first[(size_t)t + 1] += 1;
+    }
+    for (int t = 0; t < T_arr; ++t) first[(size_t)t + 1] += first[(size_t)t];
+    const int S = N;
+    int32_t *slot_node = nullptr, *d_slot_node = nullptr;
+    SB_CUDA(h->stage.take((size_t)S, &slot_node, &d_slot_node, h->stream));
+    {
+        std::vector<int> at(first.begin(), first.end() - 1);
+        for (int i = 0; i < N; ++i) {
+            slot_node[at[(size_t)lay.nodes[(size_t)i].tree_id]++] = i;
+        }
+    }
+    // slot tables: heap id -> global slot, one table per tree with todo nodes
+    struct TreeSlots { int tree_id, s0, s1, table_off, table_size; };
+    std::vector<TreeSlots> tl;
+    size_t table_total = 0;
+    for (int t = 0; t < T_arr; ++t) {
+        if (first[(size_t)t + 1] == first[(size_t)t]) continue;
+        int max_id = 1;
+        for (int sl = first[(size_t)t]; sl < first[(size_t)t + 1]; ++sl) max_id = std::max(max_id, lay.nodes[(size_t)slot_node[sl]].node_id);
+        tl.push_back({t, first[(size_t)t], first[(size_t)t + 1], (int)table_total, max_id + 1});
+        table_total += (size_t)max_id + 1;
+    }
+    int32_t *tables = nullptr, *d_tables = nullptr;
+    SB_CUDA(h->stage.take(table_total, &tables, &d_tables, h->stream));
+    for (size_t i = 0; i < table_total; ++i) tables[i] = -1;
+    for (const TreeSlots& ts : tl)
+        for (int sl = ts.s0; sl < ts.s1; ++sl) tables[(size_t)ts.table_off + (size_t)lay.nodes[(size_t)slot_node[sl]].node_id] = sl;
+    ListTree *lts = nullptr, *d_lts = nullptr;
+    SB_CUDA(h->stage.take(tl.size(), &lts, &d_lts, h->stream));
+    const int W = h->cfg.weights_per_row;
+    for (size_t i = 0; i < tl.size(); ++i) {
+        ListTree& lt = lts[i];
+        lt.node_id = tr.node_id + (int64_t)tl[i].tree_id * n;
+        lt.weights = (tr.weights && !h->weights_all_one) ? tr.weights + (int64_t)(tl[i].tree_id % W) * n : nullptr;  // [treeId % len], :847
+        lt.slot_of_node = d_tables + tl[i].table_off;
+        lt.slot_table_size = tl[i].table_size;
+        lt.pad = 0;
+    }
+    h->h2d_bytes += (int64_t)S * 4 + (int64_t)table_total * 4 + (int64_t)tl.size() * (int64_t)sizeof(ListTree);
+
+    // ---- feature tiles of the twin.  The tile geometry depends on the widest histogram, taken over ALL uint8 features so
+    // that it (and with it the twin's byte layout) does not change from pass to pass with the sampled subsets.
+    int bins_pad = 1;
+    for (int f = 0; f < F; ++f)
+        if (h->wide_index[(size_t)f] < 0) bins_pad = std::max(bins_pad, h->n_bins[(size_t)f]);
+    const int cnt_int = h->cnt_int ? 1 : 0;
+    const int slim = (h->stat_kind == STAT_CLASS && cnt_int) ? 1 : 0;
+    const int nw = hist_words_per_bin(h->stat_kind, cnt_int, h->stats_size);
+    int fpl = 0, gs = 0;
+    for (int f : {4, 2, 1}) {
+        gs = slim ? hist_rows_class_max_slots_per_block(bins_pad, h->stats_size, f) : hist_rows_max_slots_per_block(bins_pad, nw, f);
+        if (gs >= 1) { fpl = f; break; }
+    }
+    if (fpl == 0) return fail(SB_ERR_UNSUPPORTED, "one node's histogram tile does not fit in shared memory");
+    std::vector<int32_t> pos_of;
+    int twin_pad = 32;
+    twin_positions(h, fpl, pos_of, twin_pad);
+    std::vector<int32_t> rt_feats, rt_slot0, rt_kact;
+    std::vector<int> rt_of;
+    build_row_tiles(h, used, fpl, pos_of, rt_feats, rt_slot0, rt_kact, rt_of);
+    const int n_rt = (int)rt_slot0.size();
+    if (n_rt == 0) return SB_OK;
+    {
+        std::vector<int32_t> all3(rt_feats);  // one table: feats, then slot0, then kact
+        all3.insert(all3.end(), rt_slot0.begin(), rt_slot0.end());
+        all3.insert(all3.end(), rt_kact.begin(), rt_kact.end());
+        SB_CUDA(stage_into(h, h->rt_tiles, all3.data(), all3.size()));
+    }
+    int rc = ensure_twin(h, fpl, pos_of, twin_pad);
+    if (rc != SB_OK) return rc;
+    // more slots per block than the pass has: smaller histograms to clear and merge
+    gs = std::min(gs, S);
+
+    // ---- (slot, feature) -> offset in the statistics, on the device
+    SB_CUDA(h->forest_pair_off.reserve(h->stream, (size_t)S * F));
+    SB_CUDA(h->stage.flush(h->stream));
+    SB_CUDA(launch_build_pair_off(d_slot_node, S, h->d_flat_feats, h->d_flat_begin, h->d_flat_node_off, h->d_feat_bins,
+                                  h->stats_size, F, h->forest_pair_off.p, h->stream));
+    h->launches_count += 1;
+
+    // ---- batches of trees
+    const size_t ops_bytes = slim ? sizeof(ClassOps) : sizeof(RowOps);
+    if (h->forest_ops_budget == 0) {
+        size_t free_b = 0, total_b = 0;
+        SB_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        h->forest_ops_budget = std::max<size_t>(free_b / 2, (size_t)std::max<int64_t>(n, 1) * ops_bytes);
+        if (const char* e = getenv("SB_FOREST_OPS_MB")) h->forest_ops_budget = std::max<size_t>((size_t)atoll(e) << 20, (size_t)n * ops_bytes);
+    }
+    const int64_t n_ranges = forest_n_ranges(n);
+    const int64_t max_pairs = std::min<int64_t>((int64_t)0xfffffff0, (int64_t)(h->forest_ops_budget / ops_bytes));
+    const int trees_cap = (int)std::max<int64_t>(1, max_pairs / n);
+    const int64_t keys_cap = std::min<int64_t>(FOREST_MAX_KEYS, std::max<int64_t>(1, ((int64_t)1 << 28) / n_ranges));
+    const int64_t chunk_rows = MAX_ROWS_PER_FLUSH;  // integer counts: 2^18 pairs * 1024 < 2^32 as well
+    const int target_chunks = std::max(1, 148 * 8 / n_rt);
+    static const int64_t slab_bytes = (getenv("SB_FOREST_SLAB_MB") ? std::max<int64_t>(1, atoll(getenv("SB_FOREST_SLAB_MB"))) : (int64_t)1 << 20) << 20;  // default: no slabs beyond what fills the GPU
+    const int64_t j_l2 = ((int64_t)n * tr.fpad + slab_bytes - 1) / slab_bytes;
+    size_t need_ops = 0, need_counts = 0, need_scan_items = 0;
+    int need_chunks = 0;
+    for (size_t i0 = 0; i0 < tl.size();) {
+        size_t i1 = i0;
+        int slots = 0;
+        while (i1 < tl.size() && (int)(i1 - i0) < trees_cap) {
+            const int more = tl[i1].s1 - tl[i1].s0;
+            if (i1 > i0 && ((int64_t)slots + more + gs - 1) / gs > keys_cap) break;
+            slots += more;
+            ++i1;
+        }
+        const int n_keys = (slots + gs - 1) / gs;
+        if (n_keys > keys_cap) return fail(SB_ERR_UNSUPPORTED, "one tree has more todo nodes than a forest pass can group");
+        sb_handle::ForestBatch b{};
+        b.slim = slim;
+        b.fpl = fpl;
+        const int batch_trees = (int)(i1 - i0);
+        const int64_t pairs_max = n * batch_trees;
+        const int64_t j_max = std::max<int64_t>(j_l2, (target_chunks + n_keys - 1) / n_keys) + 1;  // slabs: see forest_chunks_kernel
+        const int64_t max_chunks64 = j_max * n_keys + pairs_max / chunk_rows + 2;
+        if (max_chunks64 * n_rt > 0x7fffffff) return fail(SB_ERR_UNSUPPORTED, "forest pass: chunk table too large");
+        const int max_chunks = (int)max_chunks64;
+        ForestListArgs& la = b.list;
+        la.n = n; la.trees = d_lts + i0; la.n_trees = batch_trees; la.slot_base = tl[i0].s0; la.gs = gs; la.n_keys = n_keys;
+        la.n_ranges = n_ranges; la.output = tr.output; la.significance = tr.significance; la.scales = h->d_scales;
+        la.stats_size = h->stats_size; la.kind = h->stat_kind; la.cnt_int = cnt_int; la.slim = slim;
+        la.class_stride = 128u * (uint32_t)fpl;  // one 32-bit word per class and (k, lane)
+        la.slot_stride = (uint32_t)bins_pad * (uint32_t)h->stats_size * 128u * (uint32_t)fpl;
+        la.chunk_rows = chunk_rows; la.target_chunks = target_chunks; la.max_chunks = max_chunks;
+        la.row_bytes = tr.fpad; la.slab_bytes = slab_bytes; la.stats_bytes = lay.total * 16;
+        la.error_flag = h->d_error_flag; la.rows_streamed = h->d_rows_streamed;
+        need_ops = std::max(need_ops, (size_t)pairs_max * ops_bytes + 16);  // a bulk copy may take one record past the last pair
+        need_scan_items = std::max(need_scan_items, (size_t)n_keys * (size_t)n_ranges + 1);
+        need_counts = std::max(need_counts, 2 * ((size_t)n_keys * (size_t)n_ranges + 1));
+        need_chunks = std::max(need_chunks, max_chunks);
+        if (slim) {
+            HistClassArgs& ca = b.cls;
+            ca.rm_bins = tr.bins_rm; ca.fpad = (uint32_t)tr.fpad;
+            ca.tile_feats = h->rt_tiles.p; ca.tile_slot0 = h->rt_tiles.p + (size_t)n_rt * 32 * fpl; ca.tile_kact = ca.tile_slot0 + n_rt;
+            ca.pair_off = h->forest_pair_off.p + (size_t)la.slot_base * F;
+            ca.n_tiles = n_rt; ca.gs = gs; ca.n_slots = slots; ca.bins_pad = bins_pad; ca.n_features = F; ca.stats_size = h->stats_size;
+            ca.cnt_shift = h->d_cnt_shift; ca.raw_lo = h->raw.p; ca.raw_hi = h->raw.p + lay.total;
+            b.smem = hist_rows_class_smem_bytes(gs, bins_pad, h->stats_size, fpl);
+        } else {
+            HistRowsArgs& ra = b.rows;
+            ra.rm_bins = tr.bins_rm; ra.fpad = tr.fpad;
+            ra.tile_feats = h->rt_tiles.p; ra.tile_slot0 = h->rt_tiles.p + (size_t)n_rt * 32 * fpl; ra.tile_kact = ra.tile_slot0 + n_rt;
+            ra.slot_fmask = nullptr;  // every slot takes every feature of a launched tile
+            ra.pair_off = h->forest_pair_off.p + (size_t)la.slot_base * F;
+            ra.n_tiles = n_rt; ra.gs = gs; ra.n_slots = slots; ra.bins_pad = bins_pad; ra.n_features = F; ra.stats_size = h->stats_size;
+            ra.cnt_shift = h->d_cnt_shift; ra.raw_lo = h->raw.p; ra.raw_hi = h->raw.p + lay.total;
+            b.smem = hist_rows_smem_bytes(gs, bins_pad, nw, fpl);
+        }
+        b.grid = slim ? h->sm_count : max_chunks * n_rt;  // the class kernel is persistent: one block per SM
+        h->forest_batches.push_back(b);
+        i0 = i1;
+    }
+    // buffers shared by the batches (they run one after the other on the stream)
+    SB_CUDA(h->forest_ops.reserve(h->stream, need_ops));
+    SB_CUDA(h->forest_counts.reserve(h->stream, need_counts));
+    if (need_scan_items > h->forest_scan_items) {
+        h->forest_scan_items = need_scan_items * 2;
+        h->forest_scan_temp = rowlist_scan_temp_bytes((int64_t)h->forest_scan_items);
+    }
+    SB_CUDA(h->rl_temp.reserve(h->stream, h->forest_scan_temp + 16));
+    SB_CUDA(h->rl_tables.reserve(h->stream, 2 * (size_t)need_chunks));
+    SB_CUDA(h->rl_chunk_group.reserve(h->stream, (size_t)need_chunks + 2));
+    for (auto& b : h->forest_batches) {
+        ForestListArgs& la = b.list;
+        const size_t items = (size_t)la.n_keys * (size_t)n_ranges + 1;
+        la.counts = h->forest_counts.p; la.scanned = h->forest_counts.p + items;
+        la.temp = h->rl_temp.p; la.temp_bytes = h->forest_scan_temp;
+        la.ops = h->forest_ops.p;
+        la.chunk_begin = h->rl_tables.p; la.chunk_end = h->rl_tables.p + need_chunks;
+        la.chunk_group = h->rl_chunk_group.p; la.n_chunks = h->rl_chunk_group.p + need_chunks;
+        if (b.slim) {
+            b.cls.ops = reinterpret_cast<const ClassOps*>(la.ops);
+            b.cls.chunk_group = la.chunk_group; b.cls.chunk_begin = la.chunk_begin; b.cls.chunk_end = la.chunk_end; b.cls.n_chunks = la.n_chunks;
+        } else {
+            b.rows.ops = reinterpret_cast<const RowOps*>(la.ops);
+            b.rows.chunk_group = la.chunk_group; b.rows.chunk_begin = la.chunk_begin; b.rows.chunk_end = la.chunk_end; b.rows.n_chunks = la.n_chunks;
+        }
+    }
+    return SB_OK;
+}
+
+int run_forest(sb_handle* h) {
+    for (const auto& b : h->forest_batches) {
+        SB_CUDA(launch_forest_lists(b.list, h->stream));
+        h->launches_count += 5;  // count, scan (2 kernels), chunk table, scatter
+        if (b.slim) SB_CUDA(hist_rows_class_launch(b.fpl, b.cls, b.grid, b.smem, h->stream));
+        else SB_CUDA(hist_rows_launch(b.list.kind, b.list.cnt_int, b.fpl, 1, b.rows, b.grid, b.smem, h->stream));
+        h->launches_count += 1;
+    }
+    return SB_OK;
+}
+
 int plan_split_tasks(sb_handle* h) {
     const TodoLayout& lay = h->layout;
     const size_t N = lay.nodes.size();
     h->has_cat_tasks = false;
     int max_cat_bins = 0;
-    bool same_lists = N > 0;
+    bool same_lists = N > 0 && !lay.flat;
     for (size_t n = 1; n < N && same_lists; ++n) same_lists = lay.nodes[n].features == lay.nodes[0].features;
     // tasks of one node: (feature, block offset relative to the node, bins, kind, HashMap visit rank), written at `out`
     std::vector<int> cols;
@@ -1061,11 +1450,23 @@ int plan_split_tasks(sb_handle* h) {
         }
     };
     size_t n_tasks = 0;
-    for (const auto& nd : lay.nodes) n_tasks += nd.features.size();
+    if (lay.flat) n_tasks = lay.flat_feats.size();
+    else
+        for (const auto& nd : lay.nodes) n_tasks += nd.features.size();
     h->n_tasks = (int)n_tasks;
     SB_CUDA(h->cand.reserve(h->stream, n_tasks));
     SB_CUDA(h->gain_out.reserve(h->stream, N));
-    if (same_lists && N > 1) {
+    if (lay.flat && N > 0) {
+        // forest pass: the lists are on the device already (plan_forest); build_tasks_kernel turns them into tasks
+        if (h->flat_max_list > 8192) return fail(SB_ERR_UNSUPPORTED, "a todo node with more than 8192 features of its own");
+        h->has_cat_tasks = h->flat_has_cat;
+        max_cat_bins = h->flat_max_cat_bins;
+        h->node_task_begin.alias(const_cast<int32_t*>(h->d_flat_begin));
+        SB_CUDA(h->tasks.reserve(h->stream, n_tasks + 1));
+        SB_CUDA(launch_build_tasks(h->d_flat_feats, h->d_flat_begin, h->d_flat_node_off, (int)N, std::max(h->flat_max_list, 1), h->d_feat_bins,
+                                   h->d_is_cat, h->d_column_num, h->stats_size, h->tasks.p, h->stream));
+        h->launches_count += 1;
+    } else if (same_lists && N > 1) {
         // one template row + the node offsets; expanded on the device
         const size_t fk = lay.nodes[0].features.size();
         SplitTask *tmpl = nullptr, *d_tmpl = nullptr;
@@ -1157,6 +1558,7 @@ NcclApi& nccl_api() {
     } while (0)
 
 int run_histograms(sb_handle* h) {
+    if (h->forest_pass) return run_forest(h);
     for (const HistLaunch& L : h->launches) {
         if (L.use_rows) {
             SB_CUDA(launch_rowlist_build(L.list, h->stream));
@@ -1247,6 +1649,8 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
     h->enable_row_lists = (cfg->flags & SB_FLAG_NO_ROW_LISTS) == 0;
     h->enable_subtraction = (cfg->flags & SB_FLAG_NO_SUBTRACTION) == 0;
     h->enable_root_cache = (cfg->flags & SB_FLAG_NO_ROOT_COUNT_CACHE) == 0;
+    h->enable_forest = (cfg->flags & SB_FLAG_NO_FOREST_PASS) == 0;
+    if (cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, cfg->device) != cudaSuccess || h->sm_count < 1) h->sm_count = 148;
     h->stats_size = is_variance(cfg->impurity) ? 3 : cfg->num_classes;
     h->stat_kind = is_variance(cfg->impurity) ? STAT_VARIANCE : STAT_CLASS;
     h->all_feature_pos.assign((size_t)cfg->n_features, -1);
@@ -1472,7 +1876,7 @@ SB_API int sb_set_weights(sb_handle* h, int32_t w_index, const float* weights) {
     SB_CUDA(cudaMemcpyAsync(r.weights + (int64_t)w_index * r.n, weights, (size_t)r.n * 4, cudaMemcpyHostToDevice, h->stream));
     h->h2d_bytes += r.n * 4;
     h->scales_valid = false;
-    return refresh_cnt_int(h);
+    return refresh_cnt_int(h, w_index);
 }
 
 SB_API int sb_sample_weights(sb_handle* h, int32_t w_index, int64_t seed, double rate, int64_t first_draw) {
@@ -1485,7 +1889,7 @@ SB_API int sb_sample_weights(sb_handle* h, int32_t w_index, int64_t seed, double
     SB_CUDA(launch_java_bagging_mask(r.weights + (int64_t)w_index * r.n, r.n, seed, rate, first_draw, h->stream));
     h->launches_count += 1;
     h->scales_valid = false;
-    return refresh_cnt_int(h);
+    return refresh_cnt_int(h, w_index);
 }
 
 SB_API int sb_sample_weights_stratified(sb_handle* h, int32_t w_index, int64_t seed, double rate, int32_t n_classes) {
@@ -1508,7 +1912,7 @@ SB_API int sb_sample_weights_stratified(sb_handle* h, int32_t w_index, int64_t s
     SB_CUDA(cudaStreamSynchronize(h->stream));
     if (flag & 1u) return fail(SB_ERR_RANGE, "class (int)(label + 0.01f) outside [0, n_classes)");
     h->scales_valid = false;
-    return refresh_cnt_int(h);
+    return refresh_cnt_int(h, w_index);
 }
 
 SB_API int sb_sample_poisson(sb_handle* h, int32_t w_index, uint64_t seed, double rate, int64_t row0) {
@@ -1521,15 +1925,23 @@ SB_API int sb_sample_poisson(sb_handle* h, int32_t w_index, uint64_t seed, doubl
     SB_CUDA(launch_poisson_bags(r.weights + (int64_t)w_index * r.n, r.n, seed, row0, w_index, rate, std::exp(-rate), h->stream));
     h->launches_count += 1;
     h->scales_valid = false;
-    return refresh_cnt_int(h);
+    return refresh_cnt_int(h, w_index);
 }
 
 SB_API int64_t sb_stats_len(sb_handle* h, const sb_iter_in* in) {
     if (!h || !in) return fail(SB_ERR_INVALID, "null argument");
-    TodoLayout lay;
-    int rc = build_layout(h, in, lay);
-    if (rc != SB_OK) return rc;
-    return lay.total;
+    // the sum build_layout forms, without building the layout (callers ask before every pass)
+    int64_t total = 0;
+    for (int i = 0; i < in->n_todo; ++i) {
+        const sb_todo_node& t = in->todo[i];
+        if (t.n_features == 0) { total += h->all_feat_total; continue; }
+        for (int k = 0; k < t.n_features; ++k) {
+            const int f = t.features[k];
+            if (f < 0 || f >= h->cfg.n_features) return fail(SB_ERR_INVALID, "todo node feature slot out of range");
+            total += (int64_t)h->n_bins[(size_t)f] * h->stats_size;
+        }
+    }
+    return total;
 }
 
 static int pinned_reserve(sb_handle* h, size_t bytes);
@@ -1560,7 +1972,8 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     h->prev_valid = false;
     h->stage.reset();  // the previous pass ended with a stream synchronisation: its tables are no longer in use
     std::swap(h->layout, h->prev_layout);  // the last pass's layout goes with raw_prev; its storage before that is recycled
-    int rc = build_layout(h, in, h->layout);
+    h->forest_pass = forest_lists(h);
+    int rc = build_layout(h, in, h->layout, h->forest_pass);
     if (rc != SB_OK) return rc;
     rc = pinned_reserve(h, pinned_need(h));  // now, while the GPU is idle: growing the pinned block waits for the device
     if (rc != SB_OK) return rc;
@@ -1603,7 +2016,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
                     SB_CUDA(cudaMemcpyAsync(tr.weights + (int64_t)(curr % W) * tr.n, in->new_weights, (size_t)tr.n * 4,
                                             cudaMemcpyHostToDevice, h->stream));
                     h->h2d_bytes += tr.n * 4;
-                    rc = refresh_cnt_int(h);
+                    rc = refresh_cnt_int(h, curr % W);
                     if (rc != SB_OK) return rc;
                 }
                 const uint8_t* d_drop = nullptr;
@@ -1700,6 +2113,46 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
             rc = upload_tree(h, tree, h->trees[tree.tree_id]);
             if (rc != SB_OK) return rc;
         }
+        if (h->enable_forest) {
+            // one launch walks every tree and takes the error sums of the pass (forest_walk_kernel)
+            int n_real = 0;
+            for (int t = 0; t < in->n_trees; ++t) n_real += in->trees[t].n_nodes >= 1 ? 1 : 0;
+            WalkTree *wt = nullptr, *d_wt = nullptr, *wv = nullptr, *d_wv = nullptr;
+            SB_CUDA(h->stage.take((size_t)std::max(n_real, 1), &wt, &d_wt, h->stream));
+            if (va.loaded) SB_CUDA(h->stage.take((size_t)std::max(n_real, 1), &wv, &d_wv, h->stream));
+            int k = 0;
+            for (int t = 0; t < in->n_trees; ++t) {
+                const sb_tree& tree = in->trees[t];
+                if (tree.n_nodes < 1) continue;
+                const DeviceTree& dt = h->trees[tree.tree_id];
+                wt[k].nodes = static_cast<const WalkNode*>(dt.walk);
+                wt[k].masks = dt.masks;
+                wt[k].capacity = dt.capacity;
+                wt[k].pad = 0;
+                wt[k].node_id = tr.node_id + (int64_t)tree.tree_id * tr.n;
+                wt[k].weights = tr.weights ? tr.weights + (int64_t)tree.tree_id * tr.n : nullptr;  // [treeId], no modulo (:592); adopted rows without weights: all 1
+                if (va.loaded) {
+                    wv[k] = wt[k];
+                    wv[k].node_id = va.node_id + (int64_t)tree.tree_id * va.n;
+                    wv[k].weights = nullptr;
+                }
+                ++k;
+            }
+            h->h2d_bytes += (int64_t)n_real * (int64_t)sizeof(WalkTree) * (va.loaded ? 2 : 1);
+            SB_CUDA(h->stage.flush(h->stream));
+            ForestWalkArgs wa{};
+            wa.n = tr.n; wa.trees = d_wt; wa.n_trees = n_real; wa.cols = tr.d_col; wa.feat_bins = h->d_feat_bins;
+            wa.rm_bins = (tr.bins_rm && !h->twin_pos_host.empty()) ? tr.bins_rm : nullptr; wa.fpad = (uint32_t)tr.fpad;
+            wa.label = tr.label; wa.significance = tr.significance; wa.loss = loss; wa.is_validation = 0; wa.error_flag = h->d_error_flag;
+            SB_CUDA(launch_forest_walk(wa, h->d_err_scratch, h->d_acc, h->stream));
+            h->launches_count += 1;
+            if (va.loaded) {
+                wa.n = va.n; wa.trees = d_wv; wa.cols = va.d_col; wa.rm_bins = nullptr; wa.fpad = 0;
+                wa.label = va.label; wa.significance = va.significance; wa.is_validation = 1;
+                SB_CUDA(launch_forest_walk(wa, h->d_err_scratch, h->d_acc, h->stream));
+                h->launches_count += 1;
+            }
+        } else {
         SB_CUDA(h->stage.flush(h->stream));
         for (int t = 0; t < in->n_trees; ++t) {
             const sb_tree& tree = in->trees[t];
@@ -1721,6 +2174,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
                 SB_CUDA(launch_errors(e, h->d_err_scratch, h->d_acc, h->stream));
                 h->launches_count += 2;
             }
+        }
         }
     }
 
@@ -1754,7 +2208,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
         h->scales_valid = true;
     }
     if (h->trace) { const double t = now_ms(); h->passes_trace.back().sub[2] = t - tt0; tt0 = t; }
-    rc = plan_histograms(h, in);
+    rc = h->forest_pass ? plan_forest(h, in) : plan_histograms(h, in);
     if (rc != SB_OK) return rc;
     if (h->trace) { const double t = now_ms(); h->passes_trace.back().sub[3] = t - tt0; tt0 = t; }
     if (h->pending_route) {  // no row list took the walk along: do it on its own

@@ -70,6 +70,7 @@ struct DeviceTree {
     uint8_t* has_predict = nullptr;
     uint8_t* masks = nullptr;
     int mask_capacity = 0;
+    void* walk = nullptr;    // WalkNode[capacity] (RF passes), or nullptr
 };
 
 struct TodoLayout {  // host description of the statistics buffer of one iteration
@@ -81,6 +82,11 @@ struct TodoLayout {  // host description of the statistics buffer of one iterati
     };
     std::vector<Node> nodes;
     int64_t total = 0;  // doubles
+    // Forest passes (RF with thousands of todo nodes): the feature lists as one flat array instead of a vector per node;
+    // nodes[i].features / feat_off stay empty then.
+    bool flat = false;
+    std::vector<int32_t> flat_begin;  // [n + 1]
+    std::vector<int32_t> flat_feats;  // lists in todo order; a node that takes every valid feature has them spelled out
 };
 
 }  // namespace sb

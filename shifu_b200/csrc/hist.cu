@@ -636,7 +636,7 @@ __global__ void __launch_bounds__(RCfg<FPL>::NTHREADS, 1) hist_rows_kernel(const
 
     // the dummy bin behind the histogram is zeroed too: it only ever absorbs additions
     for (int i = threadIdx.x; i < (gcount * bins_pad + 1) * nw * 32 * FPL; i += NTHR) hist[i] = 0u;
-    if (threadIdx.x < R_MAX_GS * FPL) {
+    if (!ALLF && threadIdx.x < R_MAX_GS * FPL) {  // ALLF: no masks (slot_fmask may be null)
         const int sl = threadIdx.x / FPL, k = threadIdx.x % FPL;
         fm_tab[threadIdx.x] = sl < gcount ? a.slot_fmask[((size_t)(g0 + sl) * a.n_tiles + tile_id) * FPL + k] : 0u;
     }
@@ -717,6 +717,204 @@ cudaError_t hist_rows_launch(int kind, int cnt_int, int fpl, int allf, const His
     if (kind == STAT_VARIANCE)
         return cnt_int ? launch_rows_kc<STAT_VARIANCE, 1>(fpl, allf, a, grid, smem, stream) : launch_rows_kc<STAT_VARIANCE, 0>(fpl, allf, a, grid, smem, stream);
     return cnt_int ? launch_rows_kc<STAT_CLASS, 1>(fpl, allf, a, grid, smem, stream) : launch_rows_kc<STAT_CLASS, 0>(fpl, allf, a, grid, smem, stream);
+}
+
+
+// =====================================================================================================================
+// hist_rows_class_kernel: class counts (Gini / Entropy) with integer weights over a forest list (rowlist.cu, forest_*).
+// A cell costs ONE shared-memory word update here, so the instruction stream around the atomics decides the speed
+// (the general kernel spent 61 instructions per row and tile on this case and ran at 61 % issue utilisation, ncu): the
+// operands of a pair are 8 bytes (row; byte offset of its (slot, class) words and count in one word), fetched with one
+// broadcast load per row when the tile's bins are requested and kept in registers until the atomics are issued -- the ring
+// slot is free again right after the fetch -- and a row and k cost one byte extract, one multiply-add and the atomic.
+// Every slot takes every feature of the tile: features outside a node's list accumulate into columns that are never
+// flushed (pair_off < 0), which costs nothing extra next to redirecting them.  The bins of two tiles are in flight
+// while a third is accumulated (three register buffers of RPW rows).
+// The kernel is persistent: one block per SM takes chunks off a work counter in table order, which is slab-major
+// (forest_chunks_kernel), so the blocks sweep the rows together and share the twin's lines through L2.
+namespace {
+constexpr int C_NST = 8;                   // 1 KB stages: the operand ring runs well ahead of the bins
+constexpr int C_WARPS = 15;                // consumer warps; with the producer warp 512 threads, which leaves 128 registers a thread
+constexpr int C_RPW = 8;                   // rows of a tile per consumer warp
+constexpr int C_TILE = C_WARPS * C_RPW;    // pairs per stage (120)
+constexpr int C_NTHR = (1 + C_WARPS) * 32;
+constexpr int C_STAGE = C_TILE + 2;               // a bulk copy starts and ends on 16 bytes: up to one record of the neighbours on either side
+struct CStage { uint64_t full, empty; };
+constexpr size_t C_SMEM_FIXED = (size_t)C_NST * C_STAGE * sizeof(ClassOps) + 128 + 16;  // ring, barriers, work item
+
+template <int FPL, int KACT>
+__device__ __noinline__ void class_consume(const HistClassArgs& a, const ClassOps* ops_s, CStage* st, uint32_t hist_base,
+                                              int cw, int lane, int tile_id, int64_t begin, int64_t end, int n_iters,
+                                              uint32_t it_base, uint32_t bin_stride) {
+    constexpr int RPW = C_RPW;
+    constexpr auto KS = std::make_integer_sequence<int, KACT>{};
+    const uint32_t lane_base = hist_base + (uint32_t)lane * 4u;
+    // Every lane loads, whatever its features: a byte that belongs to no used feature is a bin of an unused feature or
+    // padding (zero) -- never more than bins_pad, which spans all uint8 features -- and lands in a column that is
+    // not flushed.  The base is made opaque so that the address of a row is one 32 x 32 + 64 multiply-add.
+    const uint8_t* my_bins = a.rm_bins + a.tile_slot0[tile_id] + lane * FPL;
+    asm volatile("" : "+l"(my_bins));
+    const int wr0 = cw * RPW;
+    const uint32_t fpad = a.fpad;
+    const int skew = (int)(begin & 1);  // records are 8 bytes, bulk copies start on 16: every stage begins one record early then
+
+    struct Buf { uint32_t bw[RPW], where[RPW]; };
+    Buf b0, b1, b2;
+    auto load_bins = [&](uint32_t row) -> uint32_t {
+        const uint8_t* src = my_bins + (uint64_t)row * fpad;
+        if (FPL == 4) return __ldg(reinterpret_cast<const uint32_t*>(src));
+        if (FPL == 2) return __ldg(reinterpret_cast<const unsigned short*>(src));
+        return __ldg(src);
+    };
+    // operands of tile `it` into registers + its bins requested; rows past the end of the chunk add zero to slot 0
+    auto fetch = [&](int it, Buf& b) {
+        const uint32_t g = it_base + (uint32_t)it;
+        const int s = (int)(g % C_NST);
+        mbar_wait(&st[s].full, (g / C_NST) & 1u);
+        const int rows = (int)min((int64_t)C_TILE, end - (begin + (int64_t)it * C_TILE));
+        const ClassOps* v = ops_s + s * C_STAGE + skew + wr0;
+        // one path for full and partial tiles: a record past the end of the chunk is whatever the ring slot held before
+        // (an older pair, or the zeros the ring starts with) -- a valid row to load bins from -- and counts zero
+        const int mine = rows - wr0;
+#pragma unroll
+        for (int j = 0; j < RPW; ++j) {
+            const uint2 o = *reinterpret_cast<const uint2*>(&v[j]);
+            b.where[j] = o.y;
+            b.bw[j] = load_bins(o.x);
+        }
+        if (mine < RPW) {  // warp-uniform, the last tile of a chunk only
+#pragma unroll
+            for (int j = 0; j < RPW; ++j)
+                if (j >= mine) b.where[j] = 0u;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&st[s].empty);  // the operands are in registers: the ring slot may be refilled
+    };
+    auto accumulate = [&](const Buf& b) {
+#pragma unroll
+        for (int j = 0; j < RPW; ++j) {
+            const uint32_t base = lane_base + (b.where[j] & ((1u << CLASSOPS_OFF_BITS) - 1u));
+            const uint32_t cnt = b.where[j] >> CLASSOPS_OFF_BITS;
+            static_for(KS, [&](auto kc) {
+                constexpr int k = decltype(kc)::value;
+                const uint32_t bin = __byte_perm(b.bw[j], 0u, 0x4440u + (uint32_t)k);
+                sred_add<128 * k>(base + bin * bin_stride, cnt);
+            });
+        }
+    };
+    if (n_iters > 0) fetch(0, b0);
+    if (n_iters > 1) fetch(1, b1);
+#pragma unroll 1
+    for (int it = 0; it < n_iters; ++it) {
+        if (it + 2 < n_iters) fetch(it + 2, b2);
+        accumulate(b0);
+        b0 = b1;  // register moves: three statically rotating copies of the loop body did not fit the register file
+        b1 = b2;  // (spills in the loop: 22 ms per pass on C1 against 15 with the moves)
+    }
+}
+}  // namespace
+
+template <int FPL>
+__global__ void __launch_bounds__(C_NTHR, 1) hist_rows_class_kernel(const HistClassArgs a) {
+    constexpr int CONS_WARPS = C_WARPS;
+    constexpr int NTHR = C_NTHR;
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int n_chunks = a.n_chunks[0];
+    const int n_items = n_chunks * a.n_tiles;  // tile-major: item = tile * n_chunks + chunk
+    const int nw = a.stats_size;               // one 32-bit word per class
+    ClassOps* ops_s = reinterpret_cast<ClassOps*>(smem);
+    CStage* st = reinterpret_cast<CStage*>(smem + (size_t)C_NST * C_STAGE * sizeof(ClassOps));
+    int* s_item = reinterpret_cast<int*>(smem + (size_t)C_NST * C_STAGE * sizeof(ClassOps) + 128);
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem + C_SMEM_FIXED);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int bins_pad = a.bins_pad;
+    const uint32_t hb = smem_u32(hist);
+    const uint32_t bin_stride = (uint32_t)nw * 128u * FPL;
+
+    for (int i = threadIdx.x; i < C_NST * C_STAGE * 2; i += NTHR) reinterpret_cast<uint32_t*>(ops_s)[i] = 0u;  // see class_consume
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < C_NST; ++s) {
+            mbar_init(&st[s].full, 1);
+            mbar_init(&st[s].empty, CONS_WARPS);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    uint32_t it_base = 0;  // tiles that went through the ring so far: the barriers' phases run on across chunks
+    for (;;) {
+        __syncthreads();  // the previous item is flushed; s_item may be overwritten
+        if (threadIdx.x == 0) *s_item = atomicAdd(&a.n_chunks[1], 1);
+        __syncthreads();
+        const int item = *s_item;
+        if (item >= n_items) break;
+        const int tile_id = item / n_chunks;
+        const int ci = item - tile_id * n_chunks;
+        const int group = a.chunk_group[ci];
+        const int64_t begin = a.chunk_begin[ci], end = a.chunk_end[ci];
+        if (end <= begin) continue;
+        const int g0 = group * a.gs;
+        const int gcount = min(a.gs, a.n_slots - g0);
+        const int n_iters = (int)((end - begin + C_TILE - 1) / C_TILE);
+
+        for (int i = threadIdx.x; i < gcount * bins_pad * nw * 32 * FPL; i += NTHR) hist[i] = 0u;
+        __syncthreads();
+
+        if (warp == 0) {
+            if (lane == 0) {
+                for (int it = 0; it < n_iters; ++it) {
+                    const uint32_t g = it_base + (uint32_t)it;
+                    const int s = (int)(g % C_NST);
+                    if (g >= (uint32_t)C_NST) mbar_wait(&st[s].empty, ((g / C_NST) - 1u) & 1u);
+                    const int64_t r0 = begin + (int64_t)it * C_TILE;
+                    const int64_t e0 = r0 & ~(int64_t)1;  // first record copied (16-byte aligned), e1: one past the last, even
+                    const int64_t e1 = (min(r0 + C_TILE, end) + 1) & ~(int64_t)1;
+                    const uint32_t bytes = (uint32_t)((e1 - e0) * (int64_t)sizeof(ClassOps));
+                    mbar_expect_tx(&st[s].full, bytes);
+                    tma_load_1d(ops_s + s * C_STAGE, a.ops + e0, bytes, &st[s].full);
+                }
+            }
+        } else {
+            const int cw = warp - 1;
+            const int kact = a.tile_kact[tile_id];
+#define SB_CCONSUME(K) class_consume<FPL, K>(a, ops_s, st, hb, cw, lane, tile_id, begin, end, n_iters, it_base, bin_stride)
+            if (kact >= FPL) SB_CCONSUME(FPL);
+            else if constexpr (FPL == 4) {
+                if (kact == 3) SB_CCONSUME(3);
+                else if (kact == 2) SB_CCONSUME(2);
+                else SB_CCONSUME(1);
+            } else if constexpr (FPL == 2) SB_CCONSUME(1);
+#undef SB_CCONSUME
+        }
+        it_base += (uint32_t)n_iters;
+        __syncthreads();
+        flush_hist<STAT_CLASS, 1, 32 * FPL>(hist, gcount, g0, bins_pad, nw, a.stats_size, *a.cnt_shift, a.tile_feats + tile_id * 32 * FPL,
+                                            a.pair_off, a.n_features, a.raw_lo, a.raw_hi, NTHR);
+    }
+}
+
+size_t hist_rows_class_smem_bytes(int gs, int bins_pad, int n_classes, int fpl) {
+    return C_SMEM_FIXED + (size_t)gs * bins_pad * n_classes * 32 * fpl * 4;
+}
+int hist_rows_class_max_slots_per_block(int bins_pad, int n_classes, int fpl) {
+    const size_t budget = 227 * 1024 - C_SMEM_FIXED;
+    const int gs = (int)(budget / ((size_t)bins_pad * n_classes * 32 * fpl * 4));
+    return gs > 4096 ? 4096 : gs;
+}
+
+template <int FPL>
+static cudaError_t launch_class_one(const HistClassArgs& a, int grid, size_t smem, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(hist_rows_class_kernel<FPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    hist_rows_class_kernel<FPL><<<grid, C_NTHR, smem, stream>>>(a);
+    return cudaGetLastError();
+}
+cudaError_t hist_rows_class_launch(int fpl, const HistClassArgs& a, int grid, size_t smem, cudaStream_t stream) {
+    if (fpl == 4) return launch_class_one<4>(a, grid, smem, stream);
+    if (fpl == 2) return launch_class_one<2>(a, grid, smem, stream);
+    return launch_class_one<1>(a, grid, smem, stream);
 }
 
 

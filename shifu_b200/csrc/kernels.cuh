@@ -140,6 +140,99 @@ int hist_words_per_bin(int kind, int cnt_int, int stats_size);
 cudaError_t hist_launch(int kind, int cnt_int, const HistArgs& a, const void* tensor_map, int grid, size_t smem,
                         cudaStream_t stream);
 
+// ---- forest passes (RF): the todo nodes of ALL trees of a pass in one set of launches -- one list keyed by global slot
+// group (slots numbered over the trees of the pass), one statistics launch (dt/DTWorker.java:810-826 walks every tree per
+// row in one pass over the rows).  rowlist.cu: forest_* kernels; hist.cu: hist_rows_class_kernel.
+struct __align__(32) WalkNode {   // everything the walk wants to know about a node, in one 32-byte sector
+    int32_t feat;                 // split feature slot if the node routes further, else -1
+    int32_t pos;                  // byte position of that feature in a row of the twin, -1: read the column
+    uint32_t mask_off;            // left_mask in the tree's mask pool (used when the feature has more than 64 bins)
+    float predict;                // (float) Node.predict
+    uint32_t flags;               // bit 0: the node has a predict; bit 1: mask64 holds the left_mask
+    uint32_t pad;
+    uint64_t mask64;              // bit b: bin b goes left
+};
+struct WalkTree {                 // a real tree of the message, for the walk + error sums (rows.cu: forest_walk_kernel)
+    const WalkNode* nodes;        // [capacity], by heap id
+    const uint8_t* masks;
+    int32_t* node_id;             // [n] node of every row in this tree
+    const float* weights;         // [n] subsampleWeights[treeId] of every row, nullptr: all 1f (adopted rows, validation rows)
+    int32_t capacity;
+    int32_t pad;
+};
+struct ListTree {                 // a tree with todo nodes in this pass
+    const int32_t* node_id;
+    const float* weights;
+    const int32_t* slot_of_node;  // [slot_table_size] heap id -> GLOBAL slot of the pass, -1: not a todo node
+    int32_t slot_table_size;
+    int32_t pad;
+};
+struct __align__(8) ClassOps {    // an active (row, tree) pair of an integer-count class pass (Gini / Entropy)
+    uint32_t row;
+    uint32_t where;               // low 18 bits: byte offset of the (slot inside its group, class) words in the block's
+                                  // histogram; upper 14 bits: significance * weight, an integer in [0, 1024]
+};
+constexpr uint32_t CLASSOPS_OFF_BITS = 18;  // 227 KB of shared memory < 2^18 bytes
+constexpr int FOREST_RANGE = 4096;   // consecutive rows counted / scattered by one block
+constexpr int FOREST_MAX_KEYS = 24576;  // slot groups of one batch of trees (counters in shared memory, 96 KB)
+struct ForestListArgs {
+    int64_t n;
+    const ListTree* trees;
+    int n_trees;
+    int slot_base;                // first global slot of this batch of trees
+    int gs, n_keys;               // slots per group, groups of the batch: key = (slot - slot_base) / gs
+    int64_t n_ranges;
+    uint32_t* counts;             // [n_keys * n_ranges + 1], key-major
+    uint32_t* scanned;
+    void* temp;
+    size_t temp_bytes;
+    const float* output;
+    const float* significance;
+    const float* scales;
+    int stats_size, kind, cnt_int;
+    int slim;                     // 1: ops are ClassOps (kind == STAT_CLASS with integer counts), 0: RowOps
+    uint32_t slot_stride, class_stride;  // slim: bytes between slots / classes in the block's histogram
+    void* ops;
+    int64_t chunk_rows;           // upper bound (accumulator headroom)
+    int target_chunks;
+    int64_t row_bytes;            // bytes of a twin row (what a pair reads)
+    int64_t slab_bytes;           // bytes of the twin a slab of rows may span (a fraction of L2)
+    int64_t stats_bytes;          // bytes of the pass's global accumulators (what the chunks of one slab merge into)
+    int32_t* chunk_group;
+    int64_t* chunk_begin;
+    int64_t* chunk_end;
+    int32_t* n_chunks;            // [2]: number of chunks; work counter of the persistent statistics kernel
+    int max_chunks;
+    uint32_t* error_flag;
+    unsigned long long* rows_streamed;
+};
+int64_t forest_n_ranges(int64_t n);
+cudaError_t launch_forest_lists(const ForestListArgs& a, cudaStream_t s);
+// pair_off[s][f] for every slot from the per-node feature lists (CSR in todo order): one warp per slot
+cudaError_t launch_build_pair_off(const int32_t* slot_node, int n_slots, const int32_t* feats, const int32_t* begin,
+                                  const int64_t* node_off, const int32_t* feat_bins, int stats_size, int n_features,
+                                  int64_t* pair_off, cudaStream_t s);
+struct HistClassArgs {
+    const uint8_t* rm_bins;
+    uint32_t fpad;
+    const ClassOps* ops;
+    const int32_t* chunk_group;
+    const int64_t* chunk_begin;
+    const int64_t* chunk_end;
+    int32_t* n_chunks;            // [2]: number of chunks, work counter (zeroed by forest_chunks_kernel)
+    const int32_t* tile_feats;
+    const int32_t* tile_slot0;
+    const int32_t* tile_kact;
+    const int64_t* pair_off;      // [n_slots][F], first row = the batch's first slot
+    int n_tiles, gs, n_slots, bins_pad, n_features, stats_size;
+    const int* cnt_shift;
+    int64_t* raw_lo;
+    int64_t* raw_hi;
+};
+cudaError_t hist_rows_class_launch(int fpl, const HistClassArgs& a, int grid, size_t smem, cudaStream_t stream);
+size_t hist_rows_class_smem_bytes(int gs, int bins_pad, int n_classes, int fpl);
+int hist_rows_class_max_slots_per_block(int bins_pad, int n_classes, int fpl);
+
 // ---- rows.cu
 
 cudaError_t launch_fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t s);
@@ -194,6 +287,24 @@ cudaError_t launch_gbt_switch(const SwitchArgs& a, double* scratch /*[ERR_SCRATC
 constexpr int ERR_BLOCKS = 1184;  // 8 per SM
 constexpr int ERR_SCRATCH_DOUBLES = ERR_BLOCKS * 4 + 1;  // per-block partials + the finish ticket (zeroed once at allocation)
 cudaError_t launch_errors(const ErrArgs& a, double* scratch /*[ERR_SCRATCH_DOUBLES]*/, double* acc /*[4], += */, cudaStream_t s);
+// RF: predictNodeIndex continued from every row's node in every tree + the error sums of the pass, one launch
+// (dt/DTWorker.java:583-605 training rows, 691-705 validation rows).  rm_bins / pos_of: the row-major twin of the bin
+// matrix and feature -> byte position in a twin row, or nullptr (then the column-major columns are read).
+struct ForestWalkArgs {
+    int64_t n;
+    const WalkTree* trees;
+    int n_trees;
+    const void* const* cols;
+    const int32_t* feat_bins;
+    const uint8_t* rm_bins;       // row-major twin (the positions are in the nodes), or nullptr
+    uint32_t fpad;
+    const float* label;
+    const float* significance;
+    int loss;
+    int is_validation;
+    uint32_t* error_flag;
+};
+cudaError_t launch_forest_walk(const ForestWalkArgs& a, double* scratch, double* acc, cudaStream_t s);
 // max |sig*w|, |y*sig*w|, |y*y*sig*w| over rows (as fp32 bit patterns, atomicMax) -> out[3]
 cudaError_t launch_absmax(int64_t n, const float* output, const float* significance, const float* weights,
                           uint32_t* out, cudaStream_t s);

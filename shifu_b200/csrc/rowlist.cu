@@ -316,6 +316,228 @@ __global__ void rowlist_ops_kernel(int64_t total, const int32_t* __restrict__ no
     }
 }
 
+
+// ---- forest passes: one list for the todo nodes of all trees of a pass, keyed by GLOBAL slot group ----------------------
+// Same three steps as above -- count per (key, range), exclusive scan, scatter -- with two differences: a block (not a
+// warp) owns a range of FOREST_RANGE rows and walks it once per tree, and the counters of all keys of the batch sit in
+// shared memory (a pass of 50 trees at depth 10 has thousands of slot groups).  Positions inside a (key, range) cell are
+// handed out by shared-memory atomics, so the order of the pairs inside a cell is not fixed; the integer sums
+// the statistics kernels form do not depend on it.
+
+// key of (row, tree): slot group inside the batch, or -1.  *slot_out = slot inside the batch.
+__device__ __forceinline__ int forest_key(const ListTree& lt, int64_t r, int slot_base, int gs, int n_keys, int* slot_out,
+                                          float* w_out) {
+    const int nid = lt.node_id[r];
+    const int s = (nid >= 0 && nid < lt.slot_table_size) ? lt.slot_of_node[nid] - slot_base : -1;
+    const float w = lt.weights ? lt.weights[r] : 1.0f;
+    *slot_out = s;
+    *w_out = w;
+    if (s < 0 || w == 0.0f) return -1;
+    const int key = s / gs;
+    return key < n_keys ? key : -1;  // a slot of a later batch
+}
+
+__global__ void __launch_bounds__(256) forest_count_kernel(const ForestListArgs a) {
+    extern __shared__ uint32_t fcnt[];
+    const int64_t range = blockIdx.x;
+    if (blockIdx.x == 0 && threadIdx.x == 0) a.counts[(int64_t)a.n_keys * a.n_ranges] = 0u;
+    for (int k = threadIdx.x; k < a.n_keys; k += 256) fcnt[k] = 0u;
+    __syncthreads();
+    const int64_t r0 = range * FOREST_RANGE;
+    const int lane = threadIdx.x & 31;
+    for (int t = 0; t < a.n_trees; ++t) {
+        const ListTree lt = a.trees[t];
+        constexpr int U = 4;
+        for (int step = 0; step < FOREST_RANGE / 256; step += U) {
+            int key[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t r = r0 + (int64_t)(step + u) * 256 + threadIdx.x;
+                int sl;
+                float w;
+                key[u] = r < a.n ? forest_key(lt, r, a.slot_base, a.gs, a.n_keys, &sl, &w) : -1;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const uint32_t mask = __match_any_sync(0xffffffffu, key[u]);
+                if (key[u] >= 0 && lane == __ffs(mask) - 1) atomicAdd(&fcnt[key[u]], (uint32_t)__popc(mask));
+            }
+        }
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < a.n_keys; k += 256) a.counts[(int64_t)k * a.n_ranges + range] = fcnt[k];
+}
+
+// Chunk table of a forest list, slab-major.  The rows are cut into J slabs of whole ranges, the same for every key; cell
+// (j, k) = the pairs of key k whose rows lie in slab j -- a contiguous piece of the key's list, read off the scanned
+// counts -- and a cell becomes one chunk (more when it exceeds the accumulator headroom, chunk_rows).  Chunks are numbered
+// slab by slab: blocks that run at the same time work on the same slab of rows for different keys (different trees), so
+// a row's line of the twin is fetched from DRAM once and comes out of L2 for the other trees that hold the row (the
+// twin of 10M rows is ten times the L2; a slab is a fraction of it).  Every chunk merges its block's histogram into the
+// global accumulators, so J is bounded by what that costs: J sweeps over the statistics buffer must stay well below the
+// bytes of bins the pass reads.  One block; the word behind n_chunks is the work counter of the persistent statistics kernel.
+__global__ void __launch_bounds__(1024) forest_chunks_kernel(const ForestListArgs a) {
+    __shared__ int s_J, s_R, s_base;
+    __shared__ int s_warp[32];
+    const int64_t nr = a.n_ranges;
+    if (threadIdx.x == 0) {
+        const int64_t total = (int64_t)a.scanned[(int64_t)a.n_keys * nr];
+        if (a.rows_streamed) atomicAdd(a.rows_streamed, (unsigned long long)total);
+        // the statistics kernel's bulk copies are 16 bytes wide and may take one 8-byte record past the last pair, and
+        // it loads bins for whatever row that record names: make it row 0, count 0 (the scatter writes below `total` only)
+        if (a.slim) {
+            static_cast<ClassOps*>(a.ops)[total] = ClassOps{0u, 0u};
+            static_cast<ClassOps*>(a.ops)[total + 1] = ClassOps{0u, 0u};
+        }
+        int64_t J = (a.n * a.row_bytes + a.slab_bytes - 1) / a.slab_bytes;            // a slab of the twin fits L2
+        const int64_t j_merge = (total * a.row_bytes) / (4 * (a.stats_bytes > 0 ? a.stats_bytes : 1));  // merges stay a quarter of the bins
+        if (J > j_merge) J = j_merge;
+        const int64_t j_par = (a.target_chunks + a.n_keys - 1) / a.n_keys;            // enough chunks to fill the GPU
+        if (J < j_par) J = j_par;
+        if (J < 1) J = 1;
+        if (J > nr) J = nr;
+        const int64_t R = (nr + J - 1) / J;   // ranges per slab
+        J = (nr + R - 1) / R;
+        s_J = (int)J;
+        s_R = (int)R;
+        s_base = 0;
+    }
+    __syncthreads();
+    const int J = s_J, R = s_R;
+    const int64_t cells = (int64_t)J * a.n_keys;
+    const int64_t cr = a.chunk_rows;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t c0 = 0; c0 < cells; c0 += 1024) {
+        const int64_t c = c0 + threadIdx.x;
+        int64_t b = 0, e = 0;
+        int k = 0;
+        if (c < cells) {
+            const int j = (int)(c / a.n_keys);
+            k = (int)(c - (int64_t)j * a.n_keys);
+            const int64_t r_lo = (int64_t)j * R, r_hi = min(nr, r_lo + R);
+            b = (int64_t)a.scanned[(int64_t)k * nr + r_lo];
+            e = (int64_t)a.scanned[(int64_t)k * nr + r_hi];  // r_hi == nr: the first position of key k + 1
+        }
+        const int nc = (int)((e - b + cr - 1) / cr);
+        int incl = nc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            int v = s_warp[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, v, o);
+                if (lane >= o) v += u;
+            }
+            s_warp[lane] = v;  // inclusive over warps
+        }
+        __syncthreads();
+        const int base = s_base + (warp > 0 ? s_warp[warp - 1] : 0) + incl - nc;
+        for (int q = 0; q < nc; ++q) {
+            const int at = base + q;
+            if (at >= a.max_chunks) {  // cannot happen with the host's bound; never drop pairs silently
+                atomicOr(a.error_flag, 8u);
+                break;
+            }
+            a.chunk_group[at] = k;
+            a.chunk_begin[at] = b + (int64_t)q * cr;
+            a.chunk_end[at] = min(e, b + (int64_t)(q + 1) * cr);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) s_base += s_warp[31];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        a.n_chunks[0] = min(s_base, a.max_chunks);
+        a.n_chunks[1] = 0;  // work counter
+    }
+}
+
+template <int KIND, int CNT_INT, int SLIM>
+__global__ void __launch_bounds__(256) forest_scatter_kernel(const ForestListArgs a) {
+    extern __shared__ uint32_t foff[];
+    const int64_t range = blockIdx.x;
+    for (int k = threadIdx.x; k < a.n_keys; k += 256) foff[k] = a.scanned[(int64_t)k * a.n_ranges + range];
+    __syncthreads();
+    const float sc0 = a.scales[0], sc1 = a.scales[1], sc2 = a.scales[2];
+    const int64_t r0 = range * FOREST_RANGE;
+    const int lane = threadIdx.x & 31;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    for (int t = 0; t < a.n_trees; ++t) {
+        const ListTree lt = a.trees[t];
+        constexpr int U = 4;
+        for (int step = 0; step < FOREST_RANGE / 256; step += U) {
+            int key[U], sl[U];
+            float w[U], sig[U], y[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t r = r0 + (int64_t)(step + u) * 256 + threadIdx.x;
+                key[u] = r < a.n ? forest_key(lt, r, a.slot_base, a.gs, a.n_keys, &sl[u], &w[u]) : -1;
+                sig[u] = y[u] = 0.0f;
+                if (key[u] >= 0) { sig[u] = a.significance[r]; y[u] = a.output[r]; }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const uint32_t mask = __match_any_sync(0xffffffffu, key[u]);
+                const int leader = __ffs(mask) - 1;
+                uint32_t first = 0;
+                if (key[u] >= 0 && lane == leader) first = atomicAdd(&foff[key[u]], (uint32_t)__popc(mask));
+                first = __shfl_sync(0xffffffffu, first, leader);
+                if (key[u] < 0) continue;
+                const uint32_t pos = first + (uint32_t)__popc(mask & lt_mask);
+                const uint32_t row = (uint32_t)(r0 + (int64_t)(step + u) * 256 + threadIdx.x);
+                if (SLIM) {
+                    ClassOps o;
+                    o.row = row;
+                    const int cls = (int)(__fadd_rn(y[u], 0.000001f));  // dt/Impurity.java: (int) (label + 0.000001f)
+                    const uint32_t cnt = (uint32_t)__float2int_rn(__fmul_rn(sig[u], w[u]));
+                    if (cls < 0 || cls >= a.stats_size) { atomicOr(a.error_flag, 1u); o.where = 0u; }
+                    else o.where = ((uint32_t)(sl[u] % a.gs) * a.slot_stride + (uint32_t)cls * a.class_stride) | (cnt << CLASSOPS_OFF_BITS);
+                    static_cast<ClassOps*>(a.ops)[pos] = o;
+                } else {
+                    static_cast<RowOps*>(a.ops)[pos] = make_row_ops<KIND, CNT_INT>(row, sl[u], a.gs, w[u], sig[u], y[u], sc0, sc1, sc2,
+                                                                                  a.stats_size, a.error_flag);
+                }
+            }
+        }
+    }
+}
+
+// pair_off[s][f] = offset (in statistics) of feature f's block of the todo node that slot s stands for, -1 if the node
+// does not take f.  One warp per slot; the offsets inside a node block are a running sum over its list.
+__global__ void __launch_bounds__(256) build_pair_off_kernel(const int32_t* __restrict__ slot_node, int n_slots,
+                                                             const int32_t* __restrict__ feats, const int32_t* __restrict__ begin,
+                                                             const int64_t* __restrict__ node_off,
+                                                             const int32_t* __restrict__ feat_bins, int stats_size, int n_features,
+                                                             int64_t* __restrict__ pair_off) {
+    const int s = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (s >= n_slots) return;
+    int64_t* row = pair_off + (int64_t)s * n_features;
+    for (int f = lane; f < n_features; f += 32) row[f] = -1;
+    __syncwarp();
+    const int n = slot_node[s];
+    const int b = begin[n], e = begin[n + 1];
+    int64_t run = node_off[n];
+    for (int k0 = b; k0 < e; k0 += 32) {
+        const int k = k0 + lane;
+        const int f = k < e ? feats[k] : -1;
+        const int64_t len = f >= 0 ? (int64_t)feat_bins[f] * stats_size : 0;
+        int64_t incl = len;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int64_t v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (f >= 0) row[f] = run + incl - len;
+        run += __shfl_sync(0xffffffffu, incl, 31);
+    }
+}
+
 }  // namespace
 
 __global__ void transpose_bins16_kernel(const uint16_t* __restrict__ cm, int64_t pitch16, int n_wide, int64_t n,
@@ -399,6 +621,54 @@ cudaError_t launch_rowlist_build(const RowListArgs& a, cudaStream_t s) {
     if (a.kind == STAT_VARIANCE) { if (a.cnt_int) SCATTER(STAT_VARIANCE, 1); else SCATTER(STAT_VARIANCE, 0); }
     else { if (a.cnt_int) SCATTER(STAT_CLASS, 1); else SCATTER(STAT_CLASS, 0); }
 #undef SCATTER
+    return cudaGetLastError();
+}
+
+int64_t forest_n_ranges(int64_t n) { return (n + FOREST_RANGE - 1) / FOREST_RANGE; }
+
+cudaError_t launch_forest_lists(const ForestListArgs& a, cudaStream_t s) {
+    if (a.n <= 0 || a.n_keys <= 0) return cudaSuccess;
+    static bool attr_set = false;
+    const int max_smem = FOREST_MAX_KEYS * 4;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(forest_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(forest_scatter_kernel<STAT_VARIANCE, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(forest_scatter_kernel<STAT_VARIANCE, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(forest_scatter_kernel<STAT_CLASS, 0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(forest_scatter_kernel<STAT_CLASS, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(forest_scatter_kernel<STAT_CLASS, 1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    if (a.n_keys > FOREST_MAX_KEYS) return cudaErrorInvalidValue;
+    const size_t smem = (size_t)a.n_keys * 4;
+    const unsigned grid = (unsigned)a.n_ranges;
+    forest_count_kernel<<<grid, 256, smem, s>>>(a);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    size_t temp = a.temp_bytes;
+    e = cub::DeviceScan::ExclusiveSum(a.temp, temp, (const uint32_t*)a.counts, a.scanned, (int64_t)a.n_keys * a.n_ranges + 1, s);
+    if (e != cudaSuccess) return e;
+    forest_chunks_kernel<<<1, 1024, 0, s>>>(a);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    if (a.slim) forest_scatter_kernel<STAT_CLASS, 1, 1><<<grid, 256, smem, s>>>(a);
+    else if (a.kind == STAT_VARIANCE) {
+        if (a.cnt_int) forest_scatter_kernel<STAT_VARIANCE, 1, 0><<<grid, 256, smem, s>>>(a);
+        else forest_scatter_kernel<STAT_VARIANCE, 0, 0><<<grid, 256, smem, s>>>(a);
+    } else {
+        if (a.cnt_int) forest_scatter_kernel<STAT_CLASS, 1, 0><<<grid, 256, smem, s>>>(a);
+        else forest_scatter_kernel<STAT_CLASS, 0, 0><<<grid, 256, smem, s>>>(a);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_build_pair_off(const int32_t* slot_node, int n_slots, const int32_t* feats, const int32_t* begin,
+                                  const int64_t* node_off, const int32_t* feat_bins, int stats_size, int n_features,
+                                  int64_t* pair_off, cudaStream_t s) {
+    if (n_slots <= 0) return cudaSuccess;
+    build_pair_off_kernel<<<(n_slots + 7) / 8, 256, 0, s>>>(slot_node, n_slots, feats, begin, node_off, feat_bins, stats_size,
+                                                            n_features, pair_off);
     return cudaGetLastError();
 }
 

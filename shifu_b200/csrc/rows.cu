@@ -179,6 +179,109 @@ __global__ void __launch_bounds__(TPB) errors_kernel(const ErrArgs a, double* sc
     fold_error_sums(tc, vc, te, ve, scratch, acc);
 }
 
+// RF pass, rows side, in ONE launch for all trees (dt/DTWorker.java:583-605, 691-705): every row is walked from its node in
+// every real tree to where the tree now sends it (predictNodeIndex continued), and the pass's error sums are taken
+// over the predicts of those nodes.  A thread owns a row and loops over the trees: label and significance are read once
+// per row, node id and bag weight once per (row, tree) -- coalesced, a tree's arrays are [n] -- and the bins the walks
+// look at come from the row's line of the row-major twin, staged in shared memory by the block (one coalesced read
+// of the 256 rows; row pitch + 4 bytes keeps the threads on different banks).  Without a twin (validation rows, the
+// first pass) or for a uint16 column the column-major arrays are read.
+// The kernel waits on dependent gathers (node id -> node -> bin -> mask -> child -> predict), so (1) a node is one
+// 32-byte record with its left_mask inline (WalkNode): a row that moves one level costs two gathers, and (2) four trees
+// are walked side by side, their loads issued together.
+constexpr int WALK_MAX_FPAD = 256;  // twin rows up to this pitch are staged (256 rows x 260 B = 65 KB)
+__device__ __forceinline__ WalkNode load_walk_node(const WalkNode* p) {
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(p));
+    const uint4 b = __ldg(reinterpret_cast<const uint4*>(p) + 1);
+    WalkNode n;
+    n.feat = (int32_t)a.x; n.pos = (int32_t)a.y; n.mask_off = a.z; n.predict = __uint_as_float(a.w);
+    n.flags = b.x; n.pad = b.y; n.mask64 = ((uint64_t)b.w << 32) | b.z;
+    return n;
+}
+__global__ void __launch_bounds__(TPB) forest_walk_kernel(const ForestWalkArgs a, double* scratch, double* acc) {
+    extern __shared__ __align__(16) unsigned char walk_smem[];
+    double tc = 0, vc = 0, te = 0, ve = 0;
+    const bool staged = a.rm_bins != nullptr && a.fpad <= (uint32_t)WALK_MAX_FPAD;
+    const uint32_t pitch_s = a.fpad + 4u;
+    constexpr int U = 4;
+    for (int64_t r0 = (int64_t)blockIdx.x * TPB; r0 < a.n; r0 += (int64_t)gridDim.x * TPB) {
+        if (staged) {
+            __syncthreads();  // the previous step's readers are done
+            const uint64_t first = (uint64_t)r0 * a.fpad, limit = (uint64_t)a.n * a.fpad;
+            const uint32_t words = TPB * a.fpad / 4u;
+            for (uint32_t w = threadIdx.x; w < words; w += TPB) {
+                const uint64_t o = first + 4ull * w;
+                const uint32_t v = o < limit ? __ldg(reinterpret_cast<const uint32_t*>(a.rm_bins + o)) : 0u;
+                const uint32_t row = (4u * w) / a.fpad, col = (4u * w) - row * a.fpad;
+                *reinterpret_cast<uint32_t*>(walk_smem + row * pitch_s + col) = v;
+            }
+            __syncthreads();
+        }
+        const int64_t r = r0 + threadIdx.x;
+        if (r >= a.n) continue;
+        const unsigned char* my_row = walk_smem + threadIdx.x * pitch_s;
+        const float sig = a.significance[r], label = a.label[r];
+        auto bin_of = [&](const WalkNode& nd) -> int {
+            if (nd.pos >= 0 && a.rm_bins) return staged ? (int)my_row[nd.pos] : (int)a.rm_bins[(uint64_t)r * a.fpad + nd.pos];
+            return load_bin(a.cols, a.feat_bins, nd.feat, r);
+        };
+        for (int t0 = 0; t0 < a.n_trees; t0 += U) {
+            int id[U], id0[U];
+            float w[U];
+            WalkNode nd[U];
+            bool live[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                live[u] = t0 + u < a.n_trees;
+                id[u] = live[u] ? a.trees[t0 + u].node_id[r] : 0;
+                id0[u] = id[u];
+                w[u] = 1.0f;
+                if (live[u] && !a.is_validation && a.trees[t0 + u].weights) w[u] = a.trees[t0 + u].weights[r];
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                nd[u].feat = -1; nd[u].flags = 0; nd[u].predict = 0.f;
+                if (live[u] && id[u] > 0 && id[u] < a.trees[t0 + u].capacity) nd[u] = load_walk_node(a.trees[t0 + u].nodes + id[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {  // first step of every walk; a row that goes further (a tree seen for the first time) loops
+                if (!live[u]) continue;
+                const WalkTree& wt = a.trees[t0 + u];
+                while (nd[u].feat >= 0) {
+                    const int bin = bin_of(nd[u]);
+                    bool left;
+                    if (nd[u].flags & 2u) left = (nd[u].mask64 >> bin) & 1ull;
+                    else left = (wt.masks[nd[u].mask_off + (bin >> 3)] >> (bin & 7)) & 1;
+                    id[u] = 2 * id[u] + (left ? 0 : 1);
+                    if (id[u] >= wt.capacity) {  // child missing: the reference throws IllegalStateException (:1091)
+                        atomicOr(a.error_flag, 4u);
+                        nd[u].feat = -1; nd[u].flags = 0;
+                        break;
+                    }
+                    nd[u] = load_walk_node(wt.nodes + id[u]);
+                }
+                if (id[u] != id0[u]) wt.node_id[r] = id[u];
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (!live[u] || id[u] <= 0 || !(nd[u].flags & 1u)) continue;
+                const float err = loss_error(a.loss, nd[u].predict, label);
+                if (a.is_validation) {
+                    ve += (double)(sig * err);
+                    vc += (double)sig;
+                } else if (__float_as_int(w[u]) == 0) {  // Float.compare(weight, 0f) == 0: out-of-bag row (dt/DTWorker.java:593-597)
+                    ve += (double)(sig * err);
+                    vc += (double)sig;
+                } else {
+                    te += (double)((w[u] * sig) * err);
+                    tc += (double)(w[u] * sig);
+                }
+            }
+        }
+    }
+    fold_error_sums(tc, vc, te, ve, scratch, acc);
+}
+
 // GBT tree switch in ONE pass over the rows (dt/DTWorker.java:620-641, 672-683 training; :721-748 validation): walk the
 // finished tree from the row's node to its leaf (predictNodeIndex), update Data.predict / Data.output from the leaf,
 // put the row back at the root for the next tree, add the row to the error sums over the new predict and -- training
@@ -445,6 +548,19 @@ cudaError_t launch_gbt_update(int64_t n, const int32_t* node_id, TreeView prev, 
 cudaError_t launch_errors(const ErrArgs& a, double* scratch, double* acc, cudaStream_t s) {
     if (a.n <= 0) return cudaSuccess;
     errors_kernel<<<grid_for(a.n, TPB, ERR_BLOCKS), TPB, 0, s>>>(a, scratch, acc);
+    return cudaGetLastError();
+}
+cudaError_t launch_forest_walk(const ForestWalkArgs& a, double* scratch, double* acc, cudaStream_t s) {
+    if (a.n <= 0 || a.n_trees <= 0) return cudaSuccess;
+    const bool staged = a.rm_bins != nullptr && a.fpad <= (uint32_t)WALK_MAX_FPAD;
+    const size_t smem = staged ? (size_t)TPB * (a.fpad + 4u) : 0;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(forest_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TPB * (WALK_MAX_FPAD + 4));
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    forest_walk_kernel<<<grid_for(a.n, TPB, ERR_BLOCKS), TPB, smem, s>>>(a, scratch, acc);
     return cudaGetLastError();
 }
 cudaError_t launch_gbt_switch(const SwitchArgs& a, double* scratch, double* acc, cudaStream_t s) {

@@ -1,0 +1,96 @@
+"""RF passes as ONE list for all trees (plan_forest / forest_* kernels / hist_rows_class_kernel) against the oracle and
+against the per-tree launch sequence they replace (SB_FLAG_NO_FOREST_PASS): integer sums, so bit for bit."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from shifu_b200 import capi  # noqa: E402
+from shifu_b200.capi import ConfigArrays, Worker  # noqa: E402
+from shifu_b200.messages import IterIn, Node  # noqa: E402
+
+from helpers import apply_gain, make_data  # noqa: E402
+from test_gpu_parity import index_to_level, is_pos_zero, run_rf  # noqa: E402
+
+NO_FOREST = 16  # SB_FLAG_NO_FOREST_PASS
+
+
+def test_forest_many_slot_groups_gini():
+    """6 trees to depth 8: up to 6 x 128 todo nodes in a pass -> more than a hundred slot groups, groups that span trees."""
+    assert run_rf(30000, [32] * 40, seed=61, n_trees=6, max_depth=8) >= 7
+
+
+def test_forest_partly_filled_tile_and_two_tiles():
+    run_rf(9000, [16] * 37, seed=62, n_trees=3, max_depth=5)          # one tile, 2 features per lane populated
+    run_rf(9000, [8] * 150, seed=63, n_trees=3, max_depth=4)          # two tiles of 128, the second partly filled
+    run_rf(5000, [200] * 12, seed=64, n_trees=3, max_depth=4)         # wide histograms: fewer features per lane
+
+
+def test_forest_general_operands():
+    """Non-integer weights (no ClassOps), more than two classes, and a regression forest (variance statistics)."""
+    run_rf(9000, [16] * 20 + [8] * 5, seed=65, n_trees=4, max_depth=6, impurity=capi.SB_IMPURITY_ENTROPY, num_classes=3, weighted=True)
+    run_rf(9000, [32] * 24, seed=66, n_trees=4, max_depth=5, impurity=capi.SB_IMPURITY_GINI, num_classes=5)
+    run_rf(9000, [32] * 24, seed=67, n_trees=4, max_depth=5, impurity=capi.SB_IMPURITY_VARIANCE)
+    run_rf(9000, [32] * 24, seed=68, n_trees=3, max_depth=5, impurity=capi.SB_IMPURITY_VARIANCE, weighted=True)
+
+
+def test_forest_in_batches_of_trees(monkeypatch):
+    """An operand buffer that holds the pairs of 4 trees only: the 7 trees of the pass go through in two batches."""
+    monkeypatch.setenv("SB_FOREST_OPS_MB", "1")  # 2^20 bytes / 8 per pair = 131072 pairs = 4 trees of 30000 rows
+    assert run_rf(30000, [32] * 20, seed=69, n_trees=7, max_depth=6) >= 5
+
+
+def test_per_tree_launches_still_match_the_oracle():
+    run_rf(12000, [32] * 40, seed=21, n_trees=4, max_depth=5, flags=NO_FOREST)
+    run_rf(9000, [16] * 20 + [8] * 5, seed=22, n_trees=3, max_depth=4, impurity=capi.SB_IMPURITY_ENTROPY, num_classes=3,
+           weighted=True, flags=NO_FOREST)
+
+
+def _grow_both(n, n_bins, seed, n_trees, max_depth, impurity, weighted):
+    cfgs = [ConfigArrays(n_bins, impurity=impurity, num_classes=2, loss=capi.SB_LOSS_SQUARED, is_gbdt=False, tree_num=n_trees,
+                         weights_per_row=n_trees, max_depth=max_depth, min_instances_per_node=1, flags=f) for f in (0, NO_FOREST)]
+    cols, y, sig, w = make_data(n, n_bins, seed, weighted=weighted, wpr=n_trees, poisson=True)
+    vcols, vy, vsig, _ = make_data(n // 3, n_bins, seed + 5, weighted=weighted)
+    workers = [Worker(c) for c in cfgs]
+    for wk in workers:
+        wk.load_rows(cols, y, sig, w)
+        wk.load_rows(vcols, vy, vsig, None, is_validation=True)
+    rng = np.random.default_rng(seed + 1)
+    F = len(n_bins)
+    roots = [Node(1) for _ in range(n_trees)]
+    todo_nodes = [(t, roots[t]) for t in range(n_trees)]
+    passes = 0
+    while todo_nodes:
+        todo = [(k, t, nd.id, rng.choice(F, size=max(1, (2 * F) // 3), replace=False).tolist()) for k, (t, nd) in enumerate(todo_nodes)]
+        it = IterIn(cfgs[0], [(t, roots[t]) for t in range(n_trees)], todo)
+        a, b = workers[0].compute(it), workers[1].compute(it)
+        assert np.array_equal(a[4], b[4]), "forest pass and per-tree passes must give the same statistics, bit for bit"
+        for x, z in zip(a[:4], b[:4]):  # fp64 sums taken in a different order
+            assert abs(x - z) <= 1e-12 * abs(z) + 1e-300
+        ga, _ = workers[0].best_splits(len(todo))
+        gb, _ = workers[1].best_splits(len(todo))
+        assert all(p.found == q.found and p.feature == q.feature and p.gain == q.gain for p, q in zip(ga, gb))
+        passes += 1
+        nxt = []
+        for k, (t, nd) in enumerate(todo_nodes):
+            g = ga[k]
+            if not g.found:
+                continue
+            level = index_to_level(nd.id)
+            nd.predict = g.predict
+            if g.gain <= 0 or level == max_depth:
+                continue
+            left, right = apply_gain(cfgs[0], nd, g, None, k)
+            if not (level + 1 == max_depth or is_pos_zero(g.left_impurity)):
+                nxt.append((t, left))
+            if not (level + 1 == max_depth or is_pos_zero(g.right_impurity)):
+                nxt.append((t, right))
+        todo_nodes = nxt
+    for wk in workers:
+        wk.close()
+    return passes
+
+
+def test_forest_pass_equals_per_tree_passes_bit_for_bit():
+    assert _grow_both(40000, [32] * 30, 71, n_trees=5, max_depth=7, impurity=capi.SB_IMPURITY_GINI, weighted=False) >= 6
+    assert _grow_both(20000, [32] * 30, 72, n_trees=4, max_depth=6, impurity=capi.SB_IMPURITY_VARIANCE, weighted=True) >= 5

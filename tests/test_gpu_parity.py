@@ -336,12 +336,12 @@ def test_bin_out_of_range_is_rejected():
 
 
 def run_rf(n, n_bins, seed, n_trees=4, max_depth=4, impurity=capi.SB_IMPURITY_GINI, num_classes=2, weighted=False,
-           is_categorical=None, feature_subsets=True, oracle_threads=3):
+           is_categorical=None, feature_subsets=True, oracle_threads=3, flags=0):
     """RF: all trees advance together, Poisson bag counts per (row, tree), per-node feature subsets, OOB error."""
     from oracle.pyoracle import OracleWorker
     cfg = ConfigArrays(n_bins, is_categorical=is_categorical, impurity=impurity, num_classes=num_classes,
                        loss=capi.SB_LOSS_SQUARED, is_gbdt=False, tree_num=n_trees, weights_per_row=n_trees,
-                       max_depth=max_depth, min_instances_per_node=1)
+                       max_depth=max_depth, min_instances_per_node=1, flags=flags)
     cols, y, sig, w = make_data(n, n_bins, seed, weighted=weighted, wpr=n_trees, poisson=True)
     if num_classes > 2:
         rng0 = np.random.default_rng(seed + 3)
