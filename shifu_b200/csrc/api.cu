@@ -36,9 +36,9 @@ struct DevBuf {  // grow-only device buffer; or an alias of a piece of the per-p
         if (owned && n <= cap) return cudaSuccess;
         if (!owned && n <= fixed) return cudaSuccess;
         fixed = 0;
-        // 4x: the statistics of a level-wise tree double with every level, and a pool that has to map new memory
-        // costs about 10 us per MB
-        const size_t want = std::max<size_t>((owned && cap) ? 4 * n : n, 16);
+        // 2x: the statistics of a level-wise tree double with every level (a buffer then serves two levels), and a
+        // pool that has to map new memory costs about 10 us per MB (prewarm_pool reserves the usual working set)
+        const size_t want = std::max<size_t>((owned && cap) ? 2 * n : n, 16);
         if (p && owned) cudaFreeAsync(p, stream);
         p = nullptr;
         cap = 0;
@@ -427,6 +427,29 @@ int make_tensor_map(sb_handle* h, RowSet& r) {
     return SB_OK;
 }
 
+// The work buffers of a pass come from the stream-ordered pool and grow level after level; a pool that has to map new
+// memory does so at about 10 us per MB, in the middle of a pass.  Reserve the working set once, when the rows are
+// loaded: allocate and free it, the pool keeps what it is given back (release threshold, sb_create).
+int prewarm_pool(sb_handle* h) {
+    const long long def_mb = h->cfg.is_gbdt ? 512 : 8192;  // an RF pass at depth 10 holds 10^4 node histograms
+    const long long want_mb = getenv("SB_POOL_RESERVE_MB") ? atoll(getenv("SB_POOL_RESERVE_MB")) : def_mb;
+    if (want_mb <= 0) return SB_OK;
+    cudaMemPool_t pool = nullptr;
+    if (cudaDeviceGetDefaultMemPool(&pool, h->cfg.device) != cudaSuccess || !pool) { cudaGetLastError(); return SB_OK; }
+    uint64_t reserved = 0;
+    if (cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &reserved) != cudaSuccess) { cudaGetLastError(); return SB_OK; }
+    size_t free_b = 0, total_b = 0;
+    SB_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    const uint64_t want = (uint64_t)want_mb << 20;
+    if (reserved >= want) return SB_OK;
+    const size_t add = (size_t)std::min<uint64_t>(want - reserved, free_b / 4);
+    if (add < ((size_t)1 << 20)) return SB_OK;
+    void* p = nullptr;
+    if (cudaMallocAsync(&p, add, h->stream) == cudaSuccess) cudaFreeAsync(p, h->stream);
+    else cudaGetLastError();  // not enough room: the buffers grow on demand as before
+    return SB_OK;
+}
+
 // Allocates the derived per-row state and finishes a load (shared by the host and device loaders).
 int finish_load(sb_handle* h, RowSet& r) {
     const int64_t n = r.n;
@@ -456,7 +479,11 @@ int finish_load(sb_handle* h, RowSet& r) {
     SB_CUDA(cudaStreamSynchronize(h->stream));
     if (flag & 2u) return fail(SB_ERR_RANGE, "a bin index is outside [0, n_bins) of its feature");
     r.loaded = true;
-    if (&r == &h->train) return refresh_cnt_int(h);
+    if (&r == &h->train) {
+        const int prc = prewarm_pool(h);
+        if (prc != SB_OK) return prc;
+        return refresh_cnt_int(h);
+    }
     return SB_OK;
 }
 
@@ -1650,6 +1677,8 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
     h->enable_subtraction = (cfg->flags & SB_FLAG_NO_SUBTRACTION) == 0;
     h->enable_root_cache = (cfg->flags & SB_FLAG_NO_ROOT_COUNT_CACHE) == 0;
     h->enable_forest = (cfg->flags & SB_FLAG_NO_FOREST_PASS) == 0;
+    // an RF pass stages the feature lists of thousands of todo nodes: start with an arena that does not have to grow level by level
+    if (!cfg->is_gbdt) SB_CUDA(h->stage.grow((size_t)32 << 20, h->stream));
     if (cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, cfg->device) != cudaSuccess || h->sm_count < 1) h->sm_count = 148;
     h->stats_size = is_variance(cfg->impurity) ? 3 : cfg->num_classes;
     h->stat_kind = is_variance(cfg->impurity) ? STAT_VARIANCE : STAT_CLASS;

@@ -724,17 +724,16 @@ cudaError_t hist_rows_launch(int kind, int cnt_int, int fpl, int allf, const His
 // hist_rows_class_kernel: class counts (Gini / Entropy) with integer weights over a forest list (rowlist.cu, forest_*).
 // A cell costs ONE shared-memory word update here, so the instruction stream around the atomics decides the speed
 // (the general kernel spent 61 instructions per row and tile on this case and ran at 61 % issue utilisation, ncu): the
-// operands of a pair are 8 bytes (row; byte offset of its (slot, class) words and count in one word), fetched with one
-// broadcast load per row when the tile's bins are requested and kept in registers until the atomics are issued -- the ring
-// slot is free again right after the fetch -- and a row and k cost one byte extract, one multiply-add and the atomic.
+// operands of a pair are 8 bytes (row; byte offset of its (slot, class) words and count in one word), read from the
+// ring with broadcast loads, and a row and k cost one byte extract, one multiply-add and the atomic.
 // Every slot takes every feature of the tile: features outside a node's list accumulate into columns that are never
 // flushed (pair_off < 0), which costs nothing extra next to redirecting them.  The bins of two tiles are in flight
-// while a third is accumulated (three register buffers of RPW rows).
+// while a third is accumulated.
 // The kernel is persistent: one block per SM takes chunks off a work counter in table order, which is slab-major
 // (forest_chunks_kernel), so the blocks sweep the rows together and share the twin's lines through L2.
 namespace {
 constexpr int C_NST = 8;                   // 1 KB stages: the operand ring runs well ahead of the bins
-constexpr int C_WARPS = 15;                // consumer warps; with the producer warp 512 threads, which leaves 128 registers a thread
+constexpr int C_WARPS = 15;                // consumer warps; with the producer warp 512 threads at 128 registers (30 warps of 4 rows at 64 registers: 15.4 ms against 14.3 on C1)
 constexpr int C_RPW = 8;                   // rows of a tile per consumer warp
 constexpr int C_TILE = C_WARPS * C_RPW;    // pairs per stage (120)
 constexpr int C_NTHR = (1 + C_WARPS) * 32;
@@ -758,7 +757,11 @@ __device__ __noinline__ void class_consume(const HistClassArgs& a, const ClassOp
     const uint32_t fpad = a.fpad;
     const int skew = (int)(begin & 1);  // records are 8 bytes, bulk copies start on 16: every stage begins one record early then
 
-    struct Buf { uint32_t bw[RPW], where[RPW]; };
+    // Only the bins travel through registers: three buffers of RPW words rotate statically (the loop is unrolled by
+    // three; copying a buffer whose loads are still in flight would wait for them, and so would spilling it).  The
+    // (offset, count) word of a row is read from the ring when its atomics are issued, so a ring slot is released
+    // after the accumulation; the ring is deep enough (C_NST stages) for the producer to stay ahead.
+    struct Buf { uint32_t bw[RPW]; };
     Buf b0, b1, b2;
     auto load_bins = [&](uint32_t row) -> uint32_t {
         const uint8_t* src = my_bins + (uint64_t)row * fpad;
@@ -766,50 +769,54 @@ __device__ __noinline__ void class_consume(const HistClassArgs& a, const ClassOp
         if (FPL == 2) return __ldg(reinterpret_cast<const unsigned short*>(src));
         return __ldg(src);
     };
-    // operands of tile `it` into registers + its bins requested; rows past the end of the chunk add zero to slot 0
+    // bins of tile `it` requested.  A record past the end of the chunk is whatever the ring slot held before (an older
+    // pair, or the zeros the ring starts with): a valid row to load bins from; accumulate() gives it count zero.
     auto fetch = [&](int it, Buf& b) {
         const uint32_t g = it_base + (uint32_t)it;
         const int s = (int)(g % C_NST);
         mbar_wait(&st[s].full, (g / C_NST) & 1u);
-        const int rows = (int)min((int64_t)C_TILE, end - (begin + (int64_t)it * C_TILE));
         const ClassOps* v = ops_s + s * C_STAGE + skew + wr0;
-        // one path for full and partial tiles: a record past the end of the chunk is whatever the ring slot held before
-        // (an older pair, or the zeros the ring starts with) -- a valid row to load bins from -- and counts zero
-        const int mine = rows - wr0;
 #pragma unroll
-        for (int j = 0; j < RPW; ++j) {
-            const uint2 o = *reinterpret_cast<const uint2*>(&v[j]);
-            b.where[j] = o.y;
-            b.bw[j] = load_bins(o.x);
-        }
+        for (int j = 0; j < RPW; ++j) b.bw[j] = load_bins(v[j].row);
+    };
+    auto accumulate = [&](int it, const Buf& b) {
+        const uint32_t g = it_base + (uint32_t)it;
+        const int s = (int)(g % C_NST);
+        const int mine = (int)min((int64_t)C_TILE, end - (begin + (int64_t)it * C_TILE)) - wr0;
+        const ClassOps* v = ops_s + s * C_STAGE + skew + wr0;
+        uint32_t where[RPW];
+#pragma unroll
+        for (int j = 0; j < RPW; ++j) where[j] = v[j].where;
         if (mine < RPW) {  // warp-uniform, the last tile of a chunk only
 #pragma unroll
             for (int j = 0; j < RPW; ++j)
-                if (j >= mine) b.where[j] = 0u;
+                if (j >= mine) where[j] = 0u;
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&st[s].empty);  // the operands are in registers: the ring slot may be refilled
-    };
-    auto accumulate = [&](const Buf& b) {
 #pragma unroll
         for (int j = 0; j < RPW; ++j) {
-            const uint32_t base = lane_base + (b.where[j] & ((1u << CLASSOPS_OFF_BITS) - 1u));
-            const uint32_t cnt = b.where[j] >> CLASSOPS_OFF_BITS;
+            const uint32_t base = lane_base + (where[j] & ((1u << CLASSOPS_OFF_BITS) - 1u));
+            const uint32_t cnt = where[j] >> CLASSOPS_OFF_BITS;
             static_for(KS, [&](auto kc) {
                 constexpr int k = decltype(kc)::value;
                 const uint32_t bin = __byte_perm(b.bw[j], 0u, 0x4440u + (uint32_t)k);
                 sred_add<128 * k>(base + bin * bin_stride, cnt);
             });
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&st[s].empty);
     };
     if (n_iters > 0) fetch(0, b0);
     if (n_iters > 1) fetch(1, b1);
 #pragma unroll 1
-    for (int it = 0; it < n_iters; ++it) {
+    for (int it = 0; it < n_iters; it += 3) {
         if (it + 2 < n_iters) fetch(it + 2, b2);
-        accumulate(b0);
-        b0 = b1;  // register moves: three statically rotating copies of the loop body did not fit the register file
-        b1 = b2;  // (spills in the loop: 22 ms per pass on C1 against 15 with the moves)
+        accumulate(it, b0);
+        if (it + 1 >= n_iters) break;
+        if (it + 3 < n_iters) fetch(it + 3, b0);
+        accumulate(it + 1, b1);
+        if (it + 2 >= n_iters) break;
+        if (it + 4 < n_iters) fetch(it + 4, b1);
+        accumulate(it + 2, b2);
     }
 }
 }  // namespace

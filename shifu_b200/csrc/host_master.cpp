@@ -446,6 +446,8 @@ SB_API int sbh_grow_tree(sbh_master* m, sb_handle* worker, const sb_iter_in* fir
     const sb_iter_in* it = first;
     std::vector<sb_gain> gains;
     std::vector<uint8_t> bits;
+    bool any_cat = false;
+    for (uint8_t c : m->is_cat) any_cat |= c != 0;
     int passes = 0;
     sb_iter_out out{};
     while (it) {
@@ -455,12 +457,15 @@ SB_API int sbh_grow_tree(sbh_master* m, sb_handle* worker, const sb_iter_in* fir
         if (rc != SB_OK) return rc;
         const size_t n = (size_t)std::max(it->n_todo, 1);
         gains.resize(n);
-        bits.resize(n * SB_MAX_CAT_BYTES);
+        // category bits travel only when a categorical feature exists (4 KB per todo node: 52 MB for a forest level of
+        // 12800 nodes, zero-filled by resize)
+        if (any_cat) bits.resize(n * SB_MAX_CAT_BYTES);
+        uint8_t* bits_p = any_cat ? bits.data() : nullptr;
         out = sb_iter_out{};
-        rc = sb_compute_finish_split(worker, &out, gains.data(), bits.data());
+        rc = sb_compute_finish_split(worker, &out, gains.data(), bits_p);
         if (rc != SB_OK) return rc;
         ++passes;
-        it = m->do_compute(gains.data(), bits.data());
+        it = m->do_compute(gains.data(), bits_p);
         if (m->trees.size() != tree0) break;
     }
     *next = it;
