@@ -184,6 +184,10 @@ OTHER_CONFIGS = {
                trees=3, depth=8, impurity="variance", loss="log", fss="ALL", rate=1.0, bag=None, label_kind=0, seed=1003, gpus=(1, 8),
                what="synthetic 50M rows x 150 features (120 numeric x 64 bins + 30 categorical with 10/50/200/1000 categories), GBT log loss depth 8 "
                     "(variance impurity: the reference rejects GBT + entropy, ModelInspector.java:898-904)"),
+    # not a BASELINE.json config: C3's columns as a random forest (the probe VERDICT.md round 1 used); run by tools/run_other.py only
+    "C3RF": dict(rows=50_000_000, n_bins=[64] * 120 + [CAT_BINS[i % 4] for i in range(30)], is_cat=[0] * 120 + [1] * 30, gbdt=False,
+                 trees=20, depth=8, impurity="entropy", loss="squared", fss="TWOTHIRDS", rate=1.0, bag=None, label_kind=0, seed=1003, gpus=(),
+                 what="C3's 50M rows x 150 features as RF 20 trees depth 8, Entropy, Poisson(1) bags, TWOTHIRDS features per node"),
     "C4": dict(rows=1_000_000_000, n_bins=[64] * 100, is_cat=None, gbdt=True, trees=3, depth=8, impurity="variance", loss="squared",
                fss=None, rate=0.5, bag=0.5, label_kind=0, seed=1004, gpus=(8,),
                what="synthetic 1B rows x 100 features x 64 bins, GBT depth 8, 0.5 row bagging per tree, 0.5 features per node"),
@@ -198,7 +202,7 @@ def measure_config(name, world, rank, local_rank, dist_ctx, barrier):
     from shifu_b200.capi import ConfigArrays, NativeMaster, Worker, dist_unique_id
     from shifu_b200.sharding import shard_rows
     c = OTHER_CONFIGS[name]
-    imp = {"gini": capi.SB_IMPURITY_GINI, "variance": capi.SB_IMPURITY_VARIANCE}[c["impurity"]]
+    imp = {"gini": capi.SB_IMPURITY_GINI, "entropy": capi.SB_IMPURITY_ENTROPY, "variance": capi.SB_IMPURITY_VARIANCE}[c["impurity"]]
     loss = {"squared": capi.SB_LOSS_SQUARED, "log": capi.SB_LOSS_LOG}[c["loss"]]
     F, T, gbdt = len(c["n_bins"]), c["trees"], c["gbdt"]
     row0, n_local = shard_rows(c["rows"], world, rank)

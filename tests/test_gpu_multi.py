@@ -1,6 +1,7 @@
 """Multi-GPU identity as a test: tools/multi_gpu_check.py under torchrun on 2 GPUs of this box (skipped with fewer).
-It asserts that the sharded run -- caller-side all-reduce, the library's own NCCL merge, the native tree loop, and a
-shard without any active row -- gives statistics and trees bit-identical to one GPU over the concatenated rows."""
+It asserts that the sharded run -- caller-side all-reduce, the library's own NCCL merge, the native tree loop, a
+shard without any active row, and a random forest (forest passes on every shard) -- gives statistics and trees
+bit-identical to one GPU over the concatenated rows."""
 import os
 import subprocess
 import sys
@@ -20,3 +21,4 @@ def test_two_gpus_bit_identical_to_one():
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert "multi-gpu check ok" in out.stdout and "in-library NCCL merge ok" in out.stdout and "empty-shard check ok" in out.stdout
+    assert "forest check ok" in out.stdout

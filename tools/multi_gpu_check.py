@@ -143,5 +143,48 @@ w4.close()
 if full4 is not None:
     full4.close()
     print("empty-shard check ok: %d iterations bit-identical" % n_iter4)
+
+# ---- a random forest: all trees advance together, every pass is one forest pass (one list for all trees) on every shard
+from shifu_b200 import capi  # noqa: E402
+
+T_RF = 5
+cfg_rf = ConfigArrays([32] * 40, impurity=capi.SB_IMPURITY_GINI, num_classes=2, loss=capi.SB_LOSS_SQUARED, is_gbdt=False,
+                      tree_num=T_RF, weights_per_row=T_RF, max_depth=6, min_instances_per_node=5,
+                      device=int(os.environ["LOCAL_RANK"]))
+
+
+def grow_forest(worker, n_workers):
+    nm = NativeMaster(cfg_rf, tree_num=T_RF, max_depth=6, is_gbdt=False, feature_subset_strategy="TWOTHIRDS",
+                      feature_sampling_seed=11, max_stats_memory=(1 << 40), worker_number=n_workers)
+    msg, total = nm.build_initial_master_params(), 0
+    while msg is not None:
+        msg, passes, _ = nm.grow_tree(worker, msg)
+        total += passes
+    out = []
+    for t in range(nm.n_trees):
+        nodes, pool, extras = nm.export_tree(t)
+        out.append((bytes(b"".join(bytes(x) for x in nodes)), pool.tobytes(), extras.tobytes()))
+    nm.close()
+    return out, total
+
+
+ids = [dist_unique_id() if rank == 0 else None]
+dist.broadcast_object_list(ids, src=0)
+w5 = Worker(cfg_rf)
+w5.load_synthetic(per, seed=9, row0=rank * per, label_kind=1)
+for t in range(T_RF):
+    w5.sample_poisson(t, 9, 1.0, row0=rank * per)
+w5.dist_init(ids[0], rank, world)
+forest_sharded, passes_rf = grow_forest(w5, world)
+w5.close()
+if rank == 0:
+    full5 = Worker(cfg_rf)
+    full5.load_synthetic(per * world, seed=9, row0=0, label_kind=1)
+    for t in range(T_RF):
+        full5.sample_poisson(t, 9, 1.0, row0=0)
+    forest_full, passes_rf_full = grow_forest(full5, 1)
+    full5.close()
+    assert passes_rf == passes_rf_full and forest_sharded == forest_full, "random forest: sharded trees differ from the single-GPU trees"
+    print("forest check ok: %d trees, %d passes, identical to single GPU" % (len(forest_full), passes_rf))
 dist.barrier()
 dist.destroy_process_group()
