@@ -255,9 +255,11 @@ struct sb_handle {
         ForestListArgs list{};
         int slim = 0, fpl = 1;
         HistClassArgs cls{};
+        HistClassArgs cls_wide{};    // tiles of 8 uint16 features over the same list
         HistRowsArgs rows{};
+        bool has_narrow = false, has_wide = false;
         int grid = 0;
-        size_t smem = 0;
+        size_t smem = 0, smem_wide = 0;
     };
     std::vector<ForestBatch> forest_batches;
     DevBuf<uint8_t> forest_ops;     // ClassOps or RowOps of the active (row, tree) pairs of one batch
@@ -623,9 +625,11 @@ int build_layout(const sb_handle* h, const sb_iter_in* in, TodoLayout& lay, bool
     return SB_OK;
 }
 
-// RF passes whose statistics go through one list for all trees (plan_forest): needs the row lists, uint8 bins only
+// RF passes whose statistics go through one list for all trees (plan_forest)
 bool forest_lists(const sb_handle* h) {
-    return !h->cfg.is_gbdt && h->enable_forest && h->enable_row_lists && h->n_wide == 0 && h->train.n < (int64_t)0xffffffff;
+    // uint16 columns: only the class kernels over 8-byte operands have a wide-tile variant
+    const bool wide_ok = h->n_wide == 0 || (h->stat_kind == STAT_CLASS && h->cnt_int);
+    return !h->cfg.is_gbdt && h->enable_forest && h->enable_row_lists && wide_ok && h->train.n < (int64_t)0xffffffff;
 }
 
 // Iteration order of a java.util.HashMap<Integer, double[]> created with (n, 1f) and filled in list order
@@ -693,7 +697,8 @@ int ensure_twin(sb_handle* h, int fpl, const std::vector<int32_t>& pos_of, int t
     tr.fpad = twin_pad;
     tr.rm_fpl = fpl;
     std::vector<int32_t> feat_of_pos((size_t)twin_pad, -1);
-    for (int f = 0; f < F; ++f) feat_of_pos[pos_of[f]] = f;
+    for (int f = 0; f < F; ++f)
+        if (h->wide_index[f] < 0) feat_of_pos[pos_of[f]] = f;  // a uint16 column has no bytes to show: its position stays zero
     SB_CUDA(h->twin_map.reserve(h->stream, (size_t)twin_pad));
     SB_CUDA(cudaMemcpyAsync(h->twin_map.p, feat_of_pos.data(), (size_t)twin_pad * 4, cudaMemcpyHostToDevice, h->stream));
     // feature slot -> byte position, for kernels that look single bins up in the twin (forest_walk_kernel); uint16 columns are not in it
@@ -707,6 +712,17 @@ int ensure_twin(sb_handle* h, int fpl, const std::vector<int32_t>& pos_of, int t
     SB_CUDA(cudaMalloc(&tr.bins_rm, (size_t)std::max<int64_t>(n, 1) * tr.fpad + 256));
     SB_CUDA(cudaMemsetAsync(tr.bins_rm + (size_t)std::max<int64_t>(n, 1) * tr.fpad, 0, 256, h->stream));  // what a lane group reads past the last row
     SB_CUDA(launch_transpose_bins(static_cast<const uint8_t*>(tr.bins_base), tr.pitch, F, h->twin_map.p, n, tr.bins_rm, tr.fpad, h->stream));
+    h->launches_count += 1;
+    return SB_OK;
+}
+
+// row-major twin of the uint16 columns [n][wpad], built on first use
+int ensure_twin16(sb_handle* h) {
+    RowSet& tr = h->train;
+    if (tr.bins16_rm || h->n_wide == 0) return SB_OK;
+    tr.wpad = ((h->n_wide + 7) / 8) * 8;
+    SB_CUDA(cudaMalloc(&tr.bins16_rm, ((size_t)std::max<int64_t>(tr.n, 1) * tr.wpad + 64) * 2));
+    SB_CUDA(launch_transpose_bins16(tr.bins16, tr.pitch16, h->n_wide, tr.n, tr.bins16_rm, tr.wpad, h->stream));
     h->launches_count += 1;
     return SB_OK;
 }
@@ -1077,11 +1093,9 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
             if (rgroups > 254 && any_wide) return fail(SB_ERR_UNSUPPORTED, "more than 254 slot groups with wide features");
             if (rgroups <= 254) {
                 RowSet& tr = h->train;
-                if (any_wide && !tr.bins16_rm) {
-                    tr.wpad = ((h->n_wide + 7) / 8) * 8;
-                    SB_CUDA(cudaMalloc(&tr.bins16_rm, ((size_t)std::max<int64_t>(n, 1) * tr.wpad + 64) * 2));
-                    SB_CUDA(launch_transpose_bins16(tr.bins16, tr.pitch16, h->n_wide, n, tr.bins16_rm, tr.wpad, h->stream));
-                    h->launches_count += 1;
+                if (any_wide) {
+                    const int wrc = ensure_twin16(h);
+                    if (wrc != SB_OK) return wrc;
                 }
                 if (fpl > 0) {
                     const int trc = ensure_twin(h, fpl, pos_of, twin_pad);
@@ -1228,11 +1242,17 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
     if (N == 0) return SB_OK;
 
     // ---- the lists on the device + what the split step wants to know about them
-    std::vector<uint8_t> used((size_t)F, 0);
-    for (int32_t f : lay.flat_feats) used[(size_t)f] = 1;
+    std::vector<uint8_t> used_any((size_t)F, 0), used((size_t)F, 0), used_wide((size_t)F, 0);
+    for (int32_t f : lay.flat_feats) used_any[(size_t)f] = 1;
+    bool any_wide = false;
+    for (int f = 0; f < F; ++f) {
+        if (!used_any[(size_t)f]) continue;
+        if (h->wide_index[(size_t)f] >= 0) { used_wide[(size_t)f] = 1; any_wide = true; }
+        else used[(size_t)f] = 1;
+    }
     for (int i = 0; i < N; ++i) h->flat_max_list = std::max(h->flat_max_list, lay.flat_begin[(size_t)i + 1] - lay.flat_begin[(size_t)i]);
     for (int f = 0; f < F; ++f)
-        if (used[(size_t)f] && h->is_cat[(size_t)f]) { h->flat_has_cat = true; h->flat_max_cat_bins = std::max(h->flat_max_cat_bins, h->n_bins[(size_t)f]); }
+        if (used_any[(size_t)f] && h->is_cat[(size_t)f]) { h->flat_has_cat = true; h->flat_max_cat_bins = std::max(h->flat_max_cat_bins, h->n_bins[(size_t)f]); }
     {
         int32_t *hf = nullptr, *df = nullptr, *hb = nullptr, *db = nullptr;
         int64_t *ho = nullptr, *dof = nullptr;
@@ -1297,11 +1317,14 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
 
     // ---- feature tiles of the twin.  The tile geometry depends on the widest histogram, taken over ALL uint8 features so
     // that it (and with it the twin's byte layout) does not change from pass to pass with the sampled subsets.
-    int bins_pad = 1;
-    for (int f = 0; f < F; ++f)
+    int bins_pad = 1, bins_pad_w = 1;
+    for (int f = 0; f < F; ++f) {
         if (h->wide_index[(size_t)f] < 0) bins_pad = std::max(bins_pad, h->n_bins[(size_t)f]);
+        else bins_pad_w = std::max(bins_pad_w, h->n_bins[(size_t)f]);
+    }
     const int cnt_int = h->cnt_int ? 1 : 0;
     const int slim = (h->stat_kind == STAT_CLASS && cnt_int) ? 1 : 0;
+    if (any_wide && !slim) return fail(SB_ERR_STATE, "internal: forest pass with uint16 columns needs integer class counts");
     const int nw = hist_words_per_bin(h->stat_kind, cnt_int, h->stats_size);
     int fpl = 0, gs = 0;
     for (int f : {4, 2, 1}) {
@@ -1316,17 +1339,54 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
     std::vector<int> rt_of;
     build_row_tiles(h, used, fpl, pos_of, rt_feats, rt_slot0, rt_kact, rt_of);
     const int n_rt = (int)rt_slot0.size();
-    if (n_rt == 0) return SB_OK;
-    {
+    // tiles of 8 uint16 features (hist_rows_class_wide_kernel)
+    int n_wt = 0;
+    if (any_wide) {
+        std::vector<int> feat_of_wide((size_t)h->n_wide, -1);
+        for (int f = 0; f < F; ++f)
+            if (h->wide_index[(size_t)f] >= 0) feat_of_wide[(size_t)h->wide_index[(size_t)f]] = f;
+        std::vector<int32_t> wt;  // [n_wt][8] features, then [n_wt] first wide index
+        std::vector<int32_t> wt_slot0;
+        for (int w0 = 0; w0 < h->n_wide; w0 += 8) {
+            bool any = false;
+            for (int w = w0; w < std::min(h->n_wide, w0 + 8); ++w) any |= used_wide[(size_t)feat_of_wide[(size_t)w]] != 0;
+            if (!any) continue;
+            wt_slot0.push_back(w0);
+            for (int j = 0; j < 8; ++j) {
+                const int w = w0 + j;
+                const int f = w < h->n_wide ? feat_of_wide[(size_t)w] : -1;
+                wt.push_back((f >= 0 && used_wide[(size_t)f]) ? f : -1);
+            }
+        }
+        n_wt = (int)wt_slot0.size();
+        wt.insert(wt.end(), wt_slot0.begin(), wt_slot0.end());
+        SB_CUDA(stage_into(h, h->wt_tiles, wt.data(), wt.size()));
+        const int gs_w = hist_rows_class_wide_max_slots_per_block(bins_pad_w, h->stats_size);
+        if (gs_w < 1) return fail(SB_ERR_UNSUPPORTED, "a tile of 8 wide features does not fit in shared memory");
+        gs = n_rt > 0 ? std::min(gs, gs_w) : gs_w;
+        const int wrc = ensure_twin16(h);
+        if (wrc != SB_OK) return wrc;
+    }
+    if (n_rt == 0 && n_wt == 0) return SB_OK;
+    if (n_rt > 0) {
         std::vector<int32_t> all3(rt_feats);  // one table: feats, then slot0, then kact
         all3.insert(all3.end(), rt_slot0.begin(), rt_slot0.end());
         all3.insert(all3.end(), rt_kact.begin(), rt_kact.end());
         SB_CUDA(stage_into(h, h->rt_tiles, all3.data(), all3.size()));
+        const int rc2 = ensure_twin(h, fpl, pos_of, twin_pad);
+        if (rc2 != SB_OK) return rc2;
     }
-    int rc = ensure_twin(h, fpl, pos_of, twin_pad);
-    if (rc != SB_OK) return rc;
+    int rc = SB_OK;
     // more slots per block than the pass has: smaller histograms to clear and merge
     gs = std::min(gs, S);
+    // A pair's operand word carries the byte offset of its (slot, class) words in the narrow tiles' histogram,
+    // (slot * enc_slot_words + class) << enc_shift; a pass without narrow tiles encodes with the smallest geometry
+    const int enc_fpl = n_rt > 0 ? fpl : 1;
+    const uint32_t enc_shift = 7u + (enc_fpl == 4 ? 2u : (enc_fpl == 2 ? 1u : 0u));
+    const uint32_t enc_slot_words = (uint32_t)(n_rt > 0 ? bins_pad : 1) * (uint32_t)h->stats_size;
+    if (slim && ((uint64_t)gs * enc_slot_words << enc_shift) > ((uint64_t)1 << CLASSOPS_OFF_BITS))
+        return fail(SB_ERR_STATE, "internal: forest pass operand offset out of range");
+    const int n_tiles_all = n_rt + n_wt;
 
     // ---- (slot, feature) -> offset in the statistics, on the device
     SB_CUDA(h->forest_pair_off.reserve(h->stream, (size_t)S * F));
@@ -1348,7 +1408,7 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
     const int trees_cap = (int)std::max<int64_t>(1, max_pairs / n);
     const int64_t keys_cap = std::min<int64_t>(FOREST_MAX_KEYS, std::max<int64_t>(1, ((int64_t)1 << 28) / n_ranges));
     const int64_t chunk_rows = MAX_ROWS_PER_FLUSH;  // integer counts: 2^18 pairs * 1024 < 2^32 as well
-    const int target_chunks = std::max(1, 148 * 8 / n_rt);
+    const int target_chunks = std::max(1, 148 * 8 / std::max(n_rt, 1));
     static const int64_t slab_bytes = (getenv("SB_FOREST_SLAB_MB") ? std::max<int64_t>(1, atoll(getenv("SB_FOREST_SLAB_MB"))) : (int64_t)1 << 20) << 20;  // default: no slabs beyond what fills the GPU
     const int64_t j_l2 = ((int64_t)n * tr.fpad + slab_bytes - 1) / slab_bytes;
     size_t need_ops = 0, need_counts = 0, need_scan_items = 0;
@@ -1371,14 +1431,14 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
         const int64_t pairs_max = n * batch_trees;
         const int64_t j_max = std::max<int64_t>(j_l2, (target_chunks + n_keys - 1) / n_keys) + 1;  // slabs: see forest_chunks_kernel
         const int64_t max_chunks64 = j_max * n_keys + pairs_max / chunk_rows + 2;
-        if (max_chunks64 * n_rt > 0x7fffffff) return fail(SB_ERR_UNSUPPORTED, "forest pass: chunk table too large");
+        if (max_chunks64 * std::max(n_tiles_all, 1) > 0x7fffffff) return fail(SB_ERR_UNSUPPORTED, "forest pass: chunk table too large");
         const int max_chunks = (int)max_chunks64;
         ForestListArgs& la = b.list;
         la.n = n; la.trees = d_lts + i0; la.n_trees = batch_trees; la.slot_base = tl[i0].s0; la.gs = gs; la.n_keys = n_keys;
         la.n_ranges = n_ranges; la.output = tr.output; la.significance = tr.significance; la.scales = h->d_scales;
         la.stats_size = h->stats_size; la.kind = h->stat_kind; la.cnt_int = cnt_int; la.slim = slim;
-        la.class_stride = 128u * (uint32_t)fpl;  // one 32-bit word per class and (k, lane)
-        la.slot_stride = (uint32_t)bins_pad * (uint32_t)h->stats_size * 128u * (uint32_t)fpl;
+        la.class_stride = 1u << enc_shift;  // one 32-bit word per class and (k, lane)
+        la.slot_stride = enc_slot_words << enc_shift;
         la.chunk_rows = chunk_rows; la.target_chunks = target_chunks; la.max_chunks = max_chunks;
         la.row_bytes = tr.fpad; la.slab_bytes = slab_bytes; la.stats_bytes = lay.total * 16;
         la.error_flag = h->d_error_flag; la.rows_streamed = h->d_rows_streamed;
@@ -1386,6 +1446,8 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
         need_scan_items = std::max(need_scan_items, (size_t)n_keys * (size_t)n_ranges + 1);
         need_counts = std::max(need_counts, 2 * ((size_t)n_keys * (size_t)n_ranges + 1));
         need_chunks = std::max(need_chunks, max_chunks);
+        b.has_narrow = n_rt > 0;
+        b.has_wide = n_wt > 0;
         if (slim) {
             HistClassArgs& ca = b.cls;
             ca.rm_bins = tr.bins_rm; ca.fpad = (uint32_t)tr.fpad;
@@ -1393,7 +1455,16 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
             ca.pair_off = h->forest_pair_off.p + (size_t)la.slot_base * F;
             ca.n_tiles = n_rt; ca.gs = gs; ca.n_slots = slots; ca.bins_pad = bins_pad; ca.n_features = F; ca.stats_size = h->stats_size;
             ca.cnt_shift = h->d_cnt_shift; ca.raw_lo = h->raw.p; ca.raw_hi = h->raw.p + lay.total;
+            ca.word_shift = enc_shift; ca.slot_words = enc_slot_words; ca.counter = 1;
             b.smem = hist_rows_class_smem_bytes(gs, bins_pad, h->stats_size, fpl);
+            if (b.has_wide) {
+                HistClassArgs& cw = b.cls_wide;
+                cw = ca;
+                cw.rm_bins = reinterpret_cast<const uint8_t*>(tr.bins16_rm); cw.fpad = (uint32_t)tr.wpad;
+                cw.tile_feats = h->wt_tiles.p; cw.tile_slot0 = h->wt_tiles.p + (size_t)n_wt * 8; cw.tile_kact = nullptr;
+                cw.n_tiles = n_wt; cw.bins_pad = bins_pad_w; cw.counter = 2;
+                b.smem_wide = hist_rows_class_wide_smem_bytes(gs, bins_pad_w, h->stats_size);
+            }
         } else {
             HistRowsArgs& ra = b.rows;
             ra.rm_bins = tr.bins_rm; ra.fpad = tr.fpad;
@@ -1417,7 +1488,7 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
     }
     SB_CUDA(h->rl_temp.reserve(h->stream, h->forest_scan_temp + 16));
     SB_CUDA(h->rl_tables.reserve(h->stream, 2 * (size_t)need_chunks));
-    SB_CUDA(h->rl_chunk_group.reserve(h->stream, (size_t)need_chunks + 2));
+    SB_CUDA(h->rl_chunk_group.reserve(h->stream, (size_t)need_chunks + 3));
     for (auto& b : h->forest_batches) {
         ForestListArgs& la = b.list;
         const size_t items = (size_t)la.n_keys * (size_t)n_ranges + 1;
@@ -1427,8 +1498,10 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
         la.chunk_begin = h->rl_tables.p; la.chunk_end = h->rl_tables.p + need_chunks;
         la.chunk_group = h->rl_chunk_group.p; la.n_chunks = h->rl_chunk_group.p + need_chunks;
         if (b.slim) {
-            b.cls.ops = reinterpret_cast<const ClassOps*>(la.ops);
-            b.cls.chunk_group = la.chunk_group; b.cls.chunk_begin = la.chunk_begin; b.cls.chunk_end = la.chunk_end; b.cls.n_chunks = la.n_chunks;
+            for (HistClassArgs* ca : {&b.cls, &b.cls_wide}) {
+                ca->ops = reinterpret_cast<const ClassOps*>(la.ops);
+                ca->chunk_group = la.chunk_group; ca->chunk_begin = la.chunk_begin; ca->chunk_end = la.chunk_end; ca->n_chunks = la.n_chunks;
+            }
         } else {
             b.rows.ops = reinterpret_cast<const RowOps*>(la.ops);
             b.rows.chunk_group = la.chunk_group; b.rows.chunk_begin = la.chunk_begin; b.rows.chunk_end = la.chunk_end; b.rows.n_chunks = la.n_chunks;
@@ -1441,9 +1514,19 @@ int run_forest(sb_handle* h) {
     for (const auto& b : h->forest_batches) {
         SB_CUDA(launch_forest_lists(b.list, h->stream));
         h->launches_count += 5;  // count, scan (2 kernels), chunk table, scatter
-        if (b.slim) SB_CUDA(hist_rows_class_launch(b.fpl, b.cls, b.grid, b.smem, h->stream));
-        else SB_CUDA(hist_rows_launch(b.list.kind, b.list.cnt_int, b.fpl, 1, b.rows, b.grid, b.smem, h->stream));
-        h->launches_count += 1;
+        if (b.slim) {
+            if (b.has_narrow) {
+                SB_CUDA(hist_rows_class_launch(b.fpl, b.cls, b.grid, b.smem, h->stream));
+                h->launches_count += 1;
+            }
+            if (b.has_wide) {
+                SB_CUDA(hist_rows_class_wide_launch(b.cls_wide, b.grid, b.smem_wide, h->stream));
+                h->launches_count += 1;
+            }
+        } else {
+            SB_CUDA(hist_rows_launch(b.list.kind, b.list.cnt_int, b.fpl, 1, b.rows, b.grid, b.smem, h->stream));
+            h->launches_count += 1;
+        }
     }
     return SB_OK;
 }

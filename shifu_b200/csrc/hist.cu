@@ -849,7 +849,7 @@ __global__ void __launch_bounds__(C_NTHR, 1) hist_rows_class_kernel(const HistCl
     uint32_t it_base = 0;  // tiles that went through the ring so far: the barriers' phases run on across chunks
     for (;;) {
         __syncthreads();  // the previous item is flushed; s_item may be overwritten
-        if (threadIdx.x == 0) *s_item = atomicAdd(&a.n_chunks[1], 1);
+        if (threadIdx.x == 0) *s_item = atomicAdd(&a.n_chunks[a.counter], 1);
         __syncthreads();
         const int item = *s_item;
         if (item >= n_items) break;
@@ -896,6 +896,142 @@ __global__ void __launch_bounds__(C_NTHR, 1) hist_rows_class_kernel(const HistCl
         flush_hist<STAT_CLASS, 1, 32 * FPL>(hist, gcount, g0, bins_pad, nw, a.stats_size, *a.cnt_shift, a.tile_feats + tile_id * 32 * FPL,
                                             a.pair_off, a.n_features, a.raw_lo, a.raw_hi, NTHR);
     }
+}
+
+// hist_rows_class_wide_kernel: the same pairs for the features with more than 256 bins (uint16 columns).  Tiles of 8
+// features, a warp instruction covers 4 rows x 8 features (lane = (row q = lane >> 3, feature j = lane & 7)), histogram
+// [slot][bin][class][8]; persistent blocks and work counter as above.  A pair's ClassOps word holds the byte offset of
+// its (slot, class) in the NARROW tiles' histogram: slot and class are recovered from it (one division per row).
+namespace {
+constexpr int CW_RPW = 8;                     // rows of a tile per consumer warp = 2 steps of 4 rows
+constexpr int CW_TILE = C_WARPS * CW_RPW;     // 120, as for the narrow tiles
+}  // namespace
+
+__global__ void __launch_bounds__(C_NTHR, 1) hist_rows_class_wide_kernel(const HistClassArgs a) {
+    constexpr int NTHR = C_NTHR;
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int n_chunks = a.n_chunks[0];
+    const int n_items = n_chunks * a.n_tiles;
+    const int nw = a.stats_size;
+    ClassOps* ops_s = reinterpret_cast<ClassOps*>(smem);
+    CStage* st = reinterpret_cast<CStage*>(smem + (size_t)C_NST * C_STAGE * sizeof(ClassOps));
+    int* s_item = reinterpret_cast<int*>(smem + (size_t)C_NST * C_STAGE * sizeof(ClassOps) + 128);
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem + C_SMEM_FIXED);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int bins_pad = a.bins_pad;
+    constexpr uint32_t WORD = 32u;  // bytes between the class words of one bin
+    const uint32_t bin_stride = (uint32_t)nw * WORD;
+    const uint32_t slot_stride = (uint32_t)bins_pad * bin_stride;
+
+    for (int i = threadIdx.x; i < C_NST * C_STAGE * 2; i += NTHR) reinterpret_cast<uint32_t*>(ops_s)[i] = 0u;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < C_NST; ++s) {
+            mbar_init(&st[s].full, 1);
+            mbar_init(&st[s].empty, C_WARPS);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    uint32_t it_base = 0;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) *s_item = atomicAdd(&a.n_chunks[a.counter], 1);
+        __syncthreads();
+        const int item = *s_item;
+        if (item >= n_items) break;
+        const int tile_id = item / n_chunks;
+        const int ci = item - tile_id * n_chunks;
+        const int group = a.chunk_group[ci];
+        const int64_t begin = a.chunk_begin[ci], end = a.chunk_end[ci];
+        if (end <= begin) continue;
+        const int g0 = group * a.gs;
+        const int gcount = min(a.gs, a.n_slots - g0);
+        const int n_iters = (int)((end - begin + CW_TILE - 1) / CW_TILE);
+        // one spare bin behind the histogram takes what must not count (a row past the chunk, a bin out of range)
+        for (int i = threadIdx.x; i < (gcount * bins_pad + 1) * nw * 8; i += NTHR) hist[i] = 0u;
+        __syncthreads();
+
+        if (warp == 0) {
+            if (lane == 0) {
+                for (int it = 0; it < n_iters; ++it) {
+                    const uint32_t g = it_base + (uint32_t)it;
+                    const int s = (int)(g % C_NST);
+                    if (g >= (uint32_t)C_NST) mbar_wait(&st[s].empty, ((g / C_NST) - 1u) & 1u);
+                    const int64_t r0 = begin + (int64_t)it * CW_TILE;
+                    const int64_t e0 = r0 & ~(int64_t)1;
+                    const int64_t e1 = (min(r0 + CW_TILE, end) + 1) & ~(int64_t)1;
+                    const uint32_t bytes = (uint32_t)((e1 - e0) * (int64_t)sizeof(ClassOps));
+                    mbar_expect_tx(&st[s].full, bytes);
+                    tma_load_1d(ops_s + s * C_STAGE, a.ops + e0, bytes, &st[s].full);
+                }
+            }
+        } else {
+            const int cw = warp - 1;
+            const int q = lane >> 3, j = lane & 7;
+            const bool feat_ok = a.tile_feats[tile_id * 8 + j] >= 0;
+            const uint32_t lane_base = smem_u32(hist) + (uint32_t)j * 4u;
+            const uint32_t dummy_addr = lane_base + (uint32_t)gcount * slot_stride;
+            const uint16_t* my_bins = reinterpret_cast<const uint16_t*>(a.rm_bins) + a.tile_slot0[tile_id] + j;
+            const int wr0 = cw * CW_RPW;
+            const int skew = (int)(begin & 1);
+            uint32_t bw_cur[2], bw_next[2];
+            auto fetch_bins = [&](int it, uint32_t (&bw)[2]) {
+                const uint32_t g = it_base + (uint32_t)it;
+                const int s = (int)(g % C_NST);
+                mbar_wait(&st[s].full, (g / C_NST) & 1u);
+                const int rows = (int)min((int64_t)CW_TILE, end - (begin + (int64_t)it * CW_TILE));
+#pragma unroll
+                for (int hs = 0; hs < 2; ++hs) {
+                    const int r = wr0 + hs * 4 + q;
+                    bw[hs] = 0;
+                    if (r < rows) bw[hs] = __ldg(my_bins + (size_t)ops_s[s * C_STAGE + skew + r].row * a.fpad);
+                }
+            };
+            if (n_iters > 0) fetch_bins(0, bw_cur);
+            for (int it = 0; it < n_iters; ++it) {
+                const uint32_t g = it_base + (uint32_t)it;
+                const int s = (int)(g % C_NST);
+                if (it + 1 < n_iters) fetch_bins(it + 1, bw_next);
+                const int rows = (int)min((int64_t)CW_TILE, end - (begin + (int64_t)it * CW_TILE));
+#pragma unroll
+                for (int hs = 0; hs < 2; ++hs) {
+                    const int r = wr0 + hs * 4 + q;
+                    const uint32_t where = ops_s[s * C_STAGE + skew + min(r, CW_TILE - 1)].where;
+                    const uint32_t words = (where & ((1u << CLASSOPS_OFF_BITS) - 1u)) >> a.word_shift;  // slot * slot_words + class
+                    const uint32_t slot = words / a.slot_words, cls = words - slot * a.slot_words;
+                    const bool ok = r < rows && feat_ok && bw_cur[hs] < (uint32_t)bins_pad;
+                    const uint32_t adr = ok ? lane_base + slot * slot_stride + bw_cur[hs] * bin_stride + cls * WORD : dummy_addr;
+                    sred_add<0>(adr, where >> CLASSOPS_OFF_BITS);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&st[s].empty);
+                bw_cur[0] = bw_next[0];
+                bw_cur[1] = bw_next[1];
+            }
+        }
+        it_base += (uint32_t)n_iters;
+        __syncthreads();
+        flush_hist<STAT_CLASS, 1, 8>(hist, gcount, g0, bins_pad, nw, a.stats_size, *a.cnt_shift, a.tile_feats + tile_id * 8, a.pair_off,
+                                     a.n_features, a.raw_lo, a.raw_hi, NTHR);
+    }
+}
+
+size_t hist_rows_class_wide_smem_bytes(int gs, int bins_pad, int n_classes) {
+    return C_SMEM_FIXED + ((size_t)gs * bins_pad + 1) * n_classes * 8 * 4;
+}
+int hist_rows_class_wide_max_slots_per_block(int bins_pad, int n_classes) {
+    const size_t budget = 227 * 1024 - C_SMEM_FIXED - (size_t)n_classes * 8 * 4;
+    const int gs = (int)(budget / ((size_t)bins_pad * n_classes * 8 * 4));
+    return gs > 4096 ? 4096 : gs;
+}
+cudaError_t hist_rows_class_wide_launch(const HistClassArgs& a, int grid, size_t smem, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(hist_rows_class_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    hist_rows_class_wide_kernel<<<grid, C_NTHR, smem, stream>>>(a);
+    return cudaGetLastError();
 }
 
 size_t hist_rows_class_smem_bytes(int gs, int bins_pad, int n_classes, int fpl) {

@@ -201,7 +201,7 @@ struct ForestListArgs {
     int32_t* chunk_group;
     int64_t* chunk_begin;
     int64_t* chunk_end;
-    int32_t* n_chunks;            // [2]: number of chunks; work counter of the persistent statistics kernel
+    int32_t* n_chunks;            // [3]: number of chunks; work counters of the persistent statistics kernels
     int max_chunks;
     uint32_t* error_flag;
     unsigned long long* rows_streamed;
@@ -219,7 +219,7 @@ struct HistClassArgs {
     const int32_t* chunk_group;
     const int64_t* chunk_begin;
     const int64_t* chunk_end;
-    int32_t* n_chunks;            // [2]: number of chunks, work counter (zeroed by forest_chunks_kernel)
+    int32_t* n_chunks;            // [3]: number of chunks, work counters of the narrow and the wide launch (zeroed by forest_chunks_kernel)
     const int32_t* tile_feats;
     const int32_t* tile_slot0;
     const int32_t* tile_kact;
@@ -228,8 +228,16 @@ struct HistClassArgs {
     const int* cnt_shift;
     int64_t* raw_lo;
     int64_t* raw_hi;
+    // wide tiles only (hist_rows_class_wide_kernel): how to take a ClassOps offset apart -- it was built for the narrow
+    // tiles' histogram, (slot * slot_words + class) << word_shift bytes
+    uint32_t word_shift, slot_words;
+    int counter;                  // which word of n_chunks is this launch's work counter (1: narrow tiles, 2: wide tiles)
 };
 cudaError_t hist_rows_class_launch(int fpl, const HistClassArgs& a, int grid, size_t smem, cudaStream_t stream);
+// tiles of 8 uint16 features over the same ClassOps list; rm_bins = the uint16 twin, fpad = its pitch in elements
+cudaError_t hist_rows_class_wide_launch(const HistClassArgs& a, int grid, size_t smem, cudaStream_t stream);
+size_t hist_rows_class_wide_smem_bytes(int gs, int bins_pad, int n_classes);
+int hist_rows_class_wide_max_slots_per_block(int bins_pad, int n_classes);
 size_t hist_rows_class_smem_bytes(int gs, int bins_pad, int n_classes, int fpl);
 int hist_rows_class_max_slots_per_block(int bins_pad, int n_classes, int fpl);
 

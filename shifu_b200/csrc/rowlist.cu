@@ -454,7 +454,8 @@ __global__ void __launch_bounds__(1024) forest_chunks_kernel(const ForestListArg
     }
     if (threadIdx.x == 0) {
         a.n_chunks[0] = min(s_base, a.max_chunks);
-        a.n_chunks[1] = 0;  // work counter
+        a.n_chunks[1] = 0;  // work counters
+        a.n_chunks[2] = 0;
     }
 }
 

@@ -34,6 +34,16 @@ def test_forest_general_operands():
     run_rf(9000, [32] * 24, seed=68, n_trees=3, max_depth=5, impurity=capi.SB_IMPURITY_VARIANCE, weighted=True)
 
 
+def test_forest_wide_features():
+    """Features with more than 256 bins (uint16 columns): tiles of 8 in hist_rows_class_wide_kernel over the same pair list."""
+    run_rf(12000, [32] * 6 + [501, 300, 11, 1001], seed=73, n_trees=4, max_depth=5, is_categorical=[0] * 6 + [1, 1, 1, 1])
+    run_rf(8000, [64] * 3 + [257] * 9 + [201], seed=74, n_trees=3, max_depth=5, impurity=capi.SB_IMPURITY_ENTROPY,
+           is_categorical=[0] * 3 + [1] * 9 + [1])                                   # two wide tiles, one of them partly filled
+    run_rf(6000, [400, 1001, 300], seed=75, n_trees=3, max_depth=4, is_categorical=[0, 1, 1])   # uint16 columns only
+    # non-integer weights: no 8-byte operands, the pass falls back to one launch sequence per tree
+    run_rf(6000, [32] * 4 + [300, 600], seed=76, n_trees=3, max_depth=4, is_categorical=[0] * 4 + [1, 1], weighted=True)
+
+
 def test_forest_in_batches_of_trees(monkeypatch):
     """An operand buffer that holds the pairs of 4 trees only: the 7 trees of the pass go through in two batches."""
     monkeypatch.setenv("SB_FOREST_OPS_MB", "1")  # 2^20 bytes / 8 per pair = 131072 pairs = 4 trees of 30000 rows
