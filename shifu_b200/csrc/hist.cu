@@ -922,6 +922,8 @@ __global__ void __launch_bounds__(C_NTHR, 1) hist_rows_class_wide_kernel(const H
     constexpr uint32_t WORD = 32u;  // bytes between the class words of one bin
     const uint32_t bin_stride = (uint32_t)nw * WORD;
     const uint32_t slot_stride = (uint32_t)bins_pad * bin_stride;
+    // words / slot_words as a multiply: exact while words * slot_words < 2^32, and words < 2^18
+    const uint32_t slot_magic = (uint32_t)((((uint64_t)1 << 32) + a.slot_words - 1) / a.slot_words);
 
     for (int i = threadIdx.x; i < C_NST * C_STAGE * 2; i += NTHR) reinterpret_cast<uint32_t*>(ops_s)[i] = 0u;
     if (threadIdx.x == 0) {
@@ -997,7 +999,7 @@ __global__ void __launch_bounds__(C_NTHR, 1) hist_rows_class_wide_kernel(const H
                     const int r = wr0 + hs * 4 + q;
                     const uint32_t where = ops_s[s * C_STAGE + skew + min(r, CW_TILE - 1)].where;
                     const uint32_t words = (where & ((1u << CLASSOPS_OFF_BITS) - 1u)) >> a.word_shift;  // slot * slot_words + class
-                    const uint32_t slot = words / a.slot_words, cls = words - slot * a.slot_words;
+                    const uint32_t slot = a.slot_words > 1u ? __umulhi(words, slot_magic) : words, cls = words - slot * a.slot_words;
                     const bool ok = r < rows && feat_ok && bw_cur[hs] < (uint32_t)bins_pad;
                     const uint32_t adr = ok ? lane_base + slot * slot_stride + bw_cur[hs] * bin_stride + cls * WORD : dummy_addr;
                     sred_add<0>(adr, where >> CLASSOPS_OFF_BITS);

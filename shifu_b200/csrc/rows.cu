@@ -190,6 +190,7 @@ __global__ void __launch_bounds__(TPB) errors_kernel(const ErrArgs a, double* sc
 // 32-byte record with its left_mask inline (WalkNode): a row that moves one level costs two gathers, and (2) four trees
 // are walked side by side, their loads issued together.
 constexpr int WALK_MAX_FPAD = 256;  // twin rows up to this pitch are staged (256 rows x 260 B = 65 KB)
+constexpr int WALK_TREES_SMEM = 128;
 __device__ __forceinline__ WalkNode load_walk_node(const WalkNode* p) {
     const uint4 a = __ldg(reinterpret_cast<const uint4*>(p));
     const uint4 b = __ldg(reinterpret_cast<const uint4*>(p) + 1);
@@ -200,6 +201,13 @@ __device__ __forceinline__ WalkNode load_walk_node(const WalkNode* p) {
 }
 __global__ void __launch_bounds__(TPB) forest_walk_kernel(const ForestWalkArgs a, double* scratch, double* acc) {
     extern __shared__ __align__(16) unsigned char walk_smem[];
+    // the tree table is read by every thread for every tree: a copy in shared memory (the first WALK_TREES_SMEM trees;
+    // a forest with more reads the rest from global memory)
+    __shared__ WalkTree s_trees[WALK_TREES_SMEM];
+    for (int i = threadIdx.x; i < min(a.n_trees, WALK_TREES_SMEM) * (int)(sizeof(WalkTree) / 8); i += TPB)
+        reinterpret_cast<uint64_t*>(s_trees)[i] = reinterpret_cast<const uint64_t*>(a.trees)[i];
+    __syncthreads();
+    auto tree_of = [&](int t) -> const WalkTree& { return t < WALK_TREES_SMEM ? s_trees[t] : a.trees[t]; };
     double tc = 0, vc = 0, te = 0, ve = 0;
     const bool staged = a.rm_bins != nullptr && a.fpad <= (uint32_t)WALK_MAX_FPAD;
     const uint32_t pitch_s = a.fpad + 4u;
@@ -230,23 +238,25 @@ __global__ void __launch_bounds__(TPB) forest_walk_kernel(const ForestWalkArgs a
             float w[U];
             WalkNode nd[U];
             bool live[U];
+            // (requesting the node ids of the NEXT four trees here, ahead of the walk, made the kernel slower: 3.6 ms
+            // against 3.0 per launch on C1 -- more registers, fewer resident blocks)
 #pragma unroll
             for (int u = 0; u < U; ++u) {
                 live[u] = t0 + u < a.n_trees;
-                id[u] = live[u] ? a.trees[t0 + u].node_id[r] : 0;
+                id[u] = live[u] ? tree_of(t0 + u).node_id[r] : 0;
                 id0[u] = id[u];
                 w[u] = 1.0f;
-                if (live[u] && !a.is_validation && a.trees[t0 + u].weights) w[u] = a.trees[t0 + u].weights[r];
+                if (live[u] && !a.is_validation && tree_of(t0 + u).weights) w[u] = tree_of(t0 + u).weights[r];
             }
 #pragma unroll
             for (int u = 0; u < U; ++u) {
                 nd[u].feat = -1; nd[u].flags = 0; nd[u].predict = 0.f;
-                if (live[u] && id[u] > 0 && id[u] < a.trees[t0 + u].capacity) nd[u] = load_walk_node(a.trees[t0 + u].nodes + id[u]);
+                if (live[u] && id[u] > 0 && id[u] < tree_of(t0 + u).capacity) nd[u] = load_walk_node(tree_of(t0 + u).nodes + id[u]);
             }
 #pragma unroll
             for (int u = 0; u < U; ++u) {  // first step of every walk; a row that goes further (a tree seen for the first time) loops
                 if (!live[u]) continue;
-                const WalkTree& wt = a.trees[t0 + u];
+                const WalkTree& wt = tree_of(t0 + u);
                 while (nd[u].feat >= 0) {
                     const int bin = bin_of(nd[u]);
                     bool left;
