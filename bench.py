@@ -148,9 +148,9 @@ def grow_tree(worker, master, it, e2e_buffers=None):
 def measured_traffic(a, rows_local):
     """dram__bytes_read + dram__bytes_write per launch of the histogram kernel.  NOT measured in this run: it is the
     mean over the 7 passes of a tree in the committed ncu --set full capture of this very workload at 100M rows on one
-    GPU (profiles/r01_hist_rows_traffic.json), scaled to this rank's share of the rows; the bench line says so in
+    GPU (profiles/r02_hist_rows_traffic.json), scaled to this rank's share of the rows; the bench line says so in
     roofline.traffic_source.  None for any other shape."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_hist_rows_traffic.json")
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r02_hist_rows_traffic.json")
     try:
         t = json.load(open(path))
     except Exception:
@@ -435,7 +435,7 @@ def run_b200(a):
                      "achieved_effective": achieved_effective,
                      "rows_streamed_per_pass": float(rows_streamed) / max(hist_passes, 1),
                      "traffic": measured_traffic(a, rows_local),
-                     "traffic_source": "committed ncu capture (profiles/r01_hist_rows_traffic.json), not measured in this run",
+                     "traffic_source": "committed ncu capture (profiles/r02_hist_rows_traffic.json), not measured in this run",
                      "peak_source": peak_kind,
                      "algorithmic_bytes_per_row": bytes_per_row, "algorithmic_bytes_per_launch": algo_bytes,
                      "second_bound": {"bound": "smem_atomics", "achieved": atom_achieved, "peak": atom_peak,
