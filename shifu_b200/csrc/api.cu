@@ -433,7 +433,9 @@ int make_tensor_map(sb_handle* h, RowSet& r) {
 // memory does so at about 10 us per MB, in the middle of a pass.  Reserve the working set once, when the rows are
 // loaded: allocate and free it, the pool keeps what it is given back (release threshold, sb_create).
 int prewarm_pool(sb_handle* h) {
-    const long long def_mb = h->cfg.is_gbdt ? 512 : 8192;  // an RF pass at depth 10 holds 10^4 node histograms
+    // GBT: the statistics of one tree level.  RF: 10^4 node histograms at depth 10 (4 GB) + the operand list of a forest
+    // pass, 8 bytes per (row, tree) pair
+    const long long def_mb = h->cfg.is_gbdt ? 512 : 4096 + (long long)(((double)h->train.n * std::max(h->cfg.tree_num, 1) * 8.0) / (1 << 20));
     const long long want_mb = getenv("SB_POOL_RESERVE_MB") ? atoll(getenv("SB_POOL_RESERVE_MB")) : def_mb;
     if (want_mb <= 0) return SB_OK;
     cudaMemPool_t pool = nullptr;
@@ -444,7 +446,7 @@ int prewarm_pool(sb_handle* h) {
     SB_CUDA(cudaMemGetInfo(&free_b, &total_b));
     const uint64_t want = (uint64_t)want_mb << 20;
     if (reserved >= want) return SB_OK;
-    const size_t add = (size_t)std::min<uint64_t>(want - reserved, free_b / 4);
+    const size_t add = (size_t)std::min<uint64_t>(want - reserved, free_b / 2);
     if (add < ((size_t)1 << 20)) return SB_OK;
     void* p = nullptr;
     if (cudaMallocAsync(&p, add, h->stream) == cudaSuccess) cudaFreeAsync(p, h->stream);

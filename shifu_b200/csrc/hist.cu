@@ -988,11 +988,11 @@ __global__ void __launch_bounds__(C_NTHR, 1) hist_rows_class_wide_kernel(const H
                     if (r < rows) bw[hs] = __ldg(my_bins + (size_t)ops_s[s * C_STAGE + skew + r].row * a.fpad);
                 }
             };
-            if (n_iters > 0) fetch_bins(0, bw_cur);
-            for (int it = 0; it < n_iters; ++it) {
+            // two register buffers, used alternately (the loop is unrolled by two): moving a buffer whose loads are still
+            // in flight would wait for them and undo the prefetch
+            auto accumulate = [&](int it, const uint32_t (&bw)[2]) {
                 const uint32_t g = it_base + (uint32_t)it;
                 const int s = (int)(g % C_NST);
-                if (it + 1 < n_iters) fetch_bins(it + 1, bw_next);
                 const int rows = (int)min((int64_t)CW_TILE, end - (begin + (int64_t)it * CW_TILE));
 #pragma unroll
                 for (int hs = 0; hs < 2; ++hs) {
@@ -1000,14 +1000,21 @@ __global__ void __launch_bounds__(C_NTHR, 1) hist_rows_class_wide_kernel(const H
                     const uint32_t where = ops_s[s * C_STAGE + skew + min(r, CW_TILE - 1)].where;
                     const uint32_t words = (where & ((1u << CLASSOPS_OFF_BITS) - 1u)) >> a.word_shift;  // slot * slot_words + class
                     const uint32_t slot = a.slot_words > 1u ? __umulhi(words, slot_magic) : words, cls = words - slot * a.slot_words;
-                    const bool ok = r < rows && feat_ok && bw_cur[hs] < (uint32_t)bins_pad;
-                    const uint32_t adr = ok ? lane_base + slot * slot_stride + bw_cur[hs] * bin_stride + cls * WORD : dummy_addr;
+                    const bool ok = r < rows && feat_ok && bw[hs] < (uint32_t)bins_pad;
+                    const uint32_t adr = ok ? lane_base + slot * slot_stride + bw[hs] * bin_stride + cls * WORD : dummy_addr;
                     sred_add<0>(adr, where >> CLASSOPS_OFF_BITS);
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&st[s].empty);
-                bw_cur[0] = bw_next[0];
-                bw_cur[1] = bw_next[1];
+            };
+            if (n_iters > 0) fetch_bins(0, bw_cur);
+#pragma unroll 1
+            for (int it = 0; it < n_iters; it += 2) {
+                if (it + 1 < n_iters) fetch_bins(it + 1, bw_next);
+                accumulate(it, bw_cur);
+                if (it + 1 >= n_iters) break;
+                if (it + 2 < n_iters) fetch_bins(it + 2, bw_cur);
+                accumulate(it + 1, bw_next);
             }
         }
         it_base += (uint32_t)n_iters;
@@ -1144,10 +1151,10 @@ __global__ void __launch_bounds__(W_NTHREADS, 1) hist_rows_wide_kernel(const His
                 if (r < rows) bw[hs] = __ldg(my_bins + (size_t)ops_s[s * R_TILE + r].row * a.fpad);
             }
         };
-        if (n_iters > 0) fetch_bins(0, bw_cur);
-        for (int it = 0; it < n_iters; ++it) {
+        // two register buffers, used alternately (the loop is unrolled by two): moving a buffer whose loads are still in
+        // flight would wait for them and undo the prefetch
+        auto accumulate = [&](int it, const uint32_t (&bw)[2]) {
             const int s = it % R_NST;
-            if (it + 1 < n_iters) fetch_bins(it + 1, bw_next);
             const int rows = (int)min((int64_t)R_TILE, end - (begin + (int64_t)it * R_TILE));
             if (wr0 < rows) {
                 uint32_t ad[2], o0[2], o1[2], o2[2], lo0[2], lo1[2], lo2[2], hi0[2], hi1[2], hi2[2];
@@ -1164,8 +1171,8 @@ __global__ void __launch_bounds__(W_NTHREADS, 1) hist_rows_wide_kernel(const His
                     }
                     const uint32_t slot = v0.z;
                     const bool ok = (wr0 + hs * 4 + q < rows) && slot < (uint32_t)gcount && feat_ok &&
-                                    (fm_tab[slot & (R_MAX_GS - 1)] & feat_bit) != 0u && bw_cur[hs] < (uint32_t)bins_pad;
-                    uint32_t base = lane_base + slot * slot_stride + bw_cur[hs] * bin_stride;
+                                    (fm_tab[slot & (R_MAX_GS - 1)] & feat_bit) != 0u && bw[hs] < (uint32_t)bins_pad;
+                    uint32_t base = lane_base + slot * slot_stride + bw[hs] * bin_stride;
                     lo0[hs] = v0.w; hi0[hs] = v0.y;
                     lo1[hs] = hi1[hs] = lo2[hs] = hi2[hs] = 0;
                     if (KIND == STAT_VARIANCE) { lo1[hs] = v1.x; hi1[hs] = v1.y; lo2[hs] = v1.z; hi2[hs] = v1.w; }
@@ -1205,8 +1212,15 @@ __global__ void __launch_bounds__(W_NTHREADS, 1) hist_rows_wide_kernel(const His
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&st[s].empty);
-            bw_cur[0] = bw_next[0];
-            bw_cur[1] = bw_next[1];
+        };
+        if (n_iters > 0) fetch_bins(0, bw_cur);
+#pragma unroll 1
+        for (int it = 0; it < n_iters; it += 2) {
+            if (it + 1 < n_iters) fetch_bins(it + 1, bw_next);
+            accumulate(it, bw_cur);
+            if (it + 1 >= n_iters) break;
+            if (it + 2 < n_iters) fetch_bins(it + 2, bw_cur);
+            accumulate(it + 1, bw_next);
         }
     }
     __syncthreads();
