@@ -1764,6 +1764,11 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
     h->enable_forest = (cfg->flags & SB_FLAG_NO_FOREST_PASS) == 0;
     // an RF pass stages the feature lists of thousands of todo nodes: start with an arena that does not have to grow level by level
     if (!cfg->is_gbdt) SB_CUDA(h->stage.grow((size_t)32 << 20, h->stream));
+    // ... and a pinned result block for 10^4 todo nodes (growing it synchronises the device and takes milliseconds)
+    if (!cfg->is_gbdt) {
+        SB_CUDA(cudaMallocHost(&h->pin, (size_t)4 << 20));
+        h->pin_bytes = (size_t)4 << 20;
+    }
     if (cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, cfg->device) != cudaSuccess || h->sm_count < 1) h->sm_count = 148;
     h->stats_size = is_variance(cfg->impurity) ? 3 : cfg->num_classes;
     h->stat_kind = is_variance(cfg->impurity) ? STAT_VARIANCE : STAT_CLASS;
@@ -2388,7 +2393,9 @@ SB_API int sb_compute_stats(sb_handle* h) {
         if (h->layout.total > 0) {
             const int which = h->raw.p == h->p2p.buf[0] ? 0 : (h->raw.p == h->p2p.buf[1] ? 1 : -1);
             if (h->p2p.ok && which >= 0) {  // the accumulators sit in peer-mapped memory: merge over NVLink loads (p2p.cu)
-                SB_CUDA(launch_p2p_allreduce(h->p2p.view, which, 2 * h->layout.total, ++h->p2p.epoch, h->enable_subtraction ? 0 : 1,
+                // the tail barrier is implied only when the two buffers alternate from pass to pass (finish_check)
+                const int alternate = (h->enable_subtraction && !h->forest_pass) ? 1 : 0;
+                SB_CUDA(launch_p2p_allreduce(h->p2p.view, which, 2 * h->layout.total, ++h->p2p.epoch, alternate ? 0 : 1,
                                              h->d_error_flag, h->stream));
                 h->launches_count += 5;
             } else {
@@ -2617,7 +2624,7 @@ static int finish_check(sb_handle* h, sb_iter_out* out) {
     out->train_error = po->acc[2];
     out->validation_error = po->acc[3];
     h->stats_ready = true;
-    if (h->enable_subtraction) {  // keep this pass's merged accumulators for the children of its nodes
+    if (h->enable_subtraction && !h->forest_pass) {  // keep this pass's merged accumulators for the children of its nodes (forest passes never pair)
         std::swap(h->raw, h->raw_prev);  // (the layouts are swapped by the next sb_compute_begin)
         h->prev_valid = true;
     }
