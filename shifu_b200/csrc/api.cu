@@ -922,7 +922,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     }
 
     // ---- row-list path tables: tiles of 32*fpl consecutive feature slots, fpl = features per lane
-    int fpl = 0, rows_max_gs = 0, n_rt = 0, allf = 1;
+    int fpl = 0, rows_max_gs = 0, n_rt = 0, allf = 1, allf_kernel = 1;
     const bool rows_enabled = h->enable_row_lists && h->train.n < (int64_t)0xffffffff;
     if (rows_enabled && n_tiles > 0) {
         for (int f : {4, 2, 1}) {
@@ -962,6 +962,19 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
             }
         for (int s = 0; s < S && allf; ++s)
             if (memcmp(&rfm[(size_t)s * n_rt * fpl], full.data(), full.size() * 4) != 0) allf = 0;
+        // Nodes with feature lists of their own: the kernel's masked mode issues the atomics of an unlisted cell all the
+        // same (redirected to a spare bin) and pays a mask lookup per row on top, so the all-features mode is the
+        // cheaper one whenever it is safe: unlisted cells then land in columns of the block's histogram that are never
+        // flushed (pair_off < 0).  Safe = no feature of a launched tile has more bins than the histogram was sized for.
+        allf_kernel = allf;
+        if (!allf) {
+            static const bool force = getenv("SB_NO_ALLF_FORCE") == nullptr;
+            int bins_in_tiles = 1;
+            for (int t = 0; t < n_rt; ++t)
+                for (int f = rt_slot0[t]; f < std::min(F, rt_slot0[t] + tw); ++f)
+                    if (h->wide_index[(size_t)f] < 0) bins_in_tiles = std::max(bins_in_tiles, h->n_bins[(size_t)f]);
+            if (force && bins_in_tiles <= bins_pad) allf_kernel = 1;
+        }
         {
             std::vector<int32_t> all3(rt_feats);  // one table: feats, then slot0, then kact
             all3.insert(all3.end(), rt_slot0.begin(), rt_slot0.end());
@@ -1121,7 +1134,7 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
                 SB_CUDA(h->rl_ops.reserve(h->stream, (size_t)n));
                 L.use_rows = true;
                 L.fpl = fpl;
-                L.allf = allf;
+                L.allf = allf_kernel;
                 RowListArgs& la = L.list;
                 la.n = n; la.node_id = a.node_id; la.output = a.output; la.significance = a.significance; la.weights = a.weights;
                 la.slot_of_node = a.slot_of_node; la.slot_table_size = a.slot_table_size; la.gs = rgs; la.n_groups = rgroups;

@@ -16,6 +16,7 @@ ap.add_argument("--depth", type=int, default=8)
 ap.add_argument("--trees", type=int, default=2)
 ap.add_argument("--weighted", type=int, default=0)
 ap.add_argument("--flags", type=int, default=0, help="sb_config.flags (SB_FLAG_*)")
+ap.add_argument("--feature-rate", type=float, default=1.0, help="featureSubsetRate per node (C4: 0.5)")
 ap.add_argument("--lib", default=None, help="alternative libshifu_b200.so (kernel experiments)")
 a = ap.parse_args()
 if a.lib:
@@ -28,7 +29,8 @@ t0 = time.time()
 w.load_synthetic(a.rows, seed=1002, weighted=bool(a.weighted))
 print("load_synthetic %.2fs" % (time.time() - t0))
 w.set_profiling(True)
-m = NativeMaster(cfg, tree_num=a.trees, max_depth=a.depth, learning_rate=0.05)
+m = NativeMaster(cfg, tree_num=a.trees, max_depth=a.depth, learning_rate=0.05,
+                 feature_subset_strategy=(None if a.feature_rate < 1.0 else "ALL"), feature_subset_rate=a.feature_rate, feature_sampling_seed=7)
 it = m.build_initial_master_params()
 algo_bytes = a.rows * (a.features + 16)
 tm = time.time()
