@@ -25,8 +25,6 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# stdout carries ONE JSON line: whatever NCCL has to say (its version banner, NCCL_DEBUG output) goes to stderr
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 SEED = 1002
 
@@ -462,7 +460,7 @@ def run_b200(a):
         line["cpu_baseline"] = cpu_baseline(a, a.cpu_sample_rows, steps=5, warmup=1)  # about 10 s with all cores + one tree with 4 threads
     if dist_ctx is not None:
         dist_ctx.destroy_process_group()
-    print(json.dumps(line))
+    OUT.emit(line) if OUT is not None else print(json.dumps(line))
 
 
 def oracle_tree(orc, cfg, max_depth, tree_index, prev_root, threads):
@@ -572,12 +570,38 @@ def run_reference(a):
         "e2e": {"value": base["value"], "unit": "rows*features/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    OUT.emit(line) if OUT is not None else print(json.dumps(line))
 
+
+class OneLineStdout:
+    """stdout carries ONE JSON line.  Libraries write there too (NCCL prints its version banner with printf when a
+    communicator is created), so file descriptor 1 points at stderr until the line is ready."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def emit(self, line):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        print(json.dumps(line), flush=True)
+        os.dup2(2, 1)
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+        return False
+
+
+OUT = None
 
 if __name__ == "__main__":
     args = parse()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_b200(args)
+    with OneLineStdout() as OUT:
+        if args.impl == "reference":
+            run_reference(args)
+        else:
+            run_b200(args)
