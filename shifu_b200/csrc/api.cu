@@ -1420,7 +1420,7 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
     }
     const int64_t n_ranges = forest_n_ranges(n);
     const int64_t max_pairs = std::min<int64_t>((int64_t)0xfffffff0, (int64_t)(h->forest_ops_budget / ops_bytes));
-    const int trees_cap = (int)std::max<int64_t>(1, max_pairs / n);
+    const int trees_cap = (int)std::min<int64_t>(std::max<int64_t>(1, max_pairs / n), 1 << 20);
     const int64_t keys_cap = std::min<int64_t>(FOREST_MAX_KEYS, std::max<int64_t>(1, ((int64_t)1 << 28) / n_ranges));
     const int64_t chunk_rows = MAX_ROWS_PER_FLUSH;  // integer counts: 2^18 pairs * 1024 < 2^32 as well
     const int target_chunks = std::max(1, 148 * 8 / std::max(n_rt, 1));

@@ -104,3 +104,58 @@ def _grow_both(n, n_bins, seed, n_trees, max_depth, impurity, weighted):
 def test_forest_pass_equals_per_tree_passes_bit_for_bit():
     assert _grow_both(40000, [32] * 30, 71, n_trees=5, max_depth=7, impurity=capi.SB_IMPURITY_GINI, weighted=False) >= 6
     assert _grow_both(20000, [32] * 30, 72, n_trees=4, max_depth=6, impurity=capi.SB_IMPURITY_VARIANCE, weighted=True) >= 5
+
+
+def _one_pass(cfg, cols, y, sig, w, todo, roots, vcols=None, vy=None):
+    from oracle.pyoracle import OracleWorker
+    dev, orc = Worker(cfg), OracleWorker(cfg)
+    for wk in (dev, orc):
+        wk.load_rows(cols, y, sig, w)
+        if vcols is not None:
+            wk.load_rows(vcols, vy, None, None, is_validation=True)
+    it = IterIn(cfg, roots, todo)
+    d, o = dev.compute(it), orc.compute(it, n_threads=2)
+    dev.close()
+    orc.close()
+    return d, o
+
+
+def test_forest_ragged_and_empty_inputs():
+    """Rows 0, 1, 119, 120, 121, 4095, 4096, 4097 (tile of 120 pairs, range of 4096 rows), a tree none of whose rows is in
+    its bag, and a pass whose only active tree is the last one."""
+    T, n_bins = 3, [32] * 9 + [7]
+    cfg = ConfigArrays(n_bins, impurity=capi.SB_IMPURITY_GINI, num_classes=2, loss=capi.SB_LOSS_SQUARED, is_gbdt=False, tree_num=T,
+                       weights_per_row=T, max_depth=3, min_instances_per_node=1)
+    roots = [(t, Node(1)) for t in range(T)]
+    todo = [(t, t, 1, []) for t in range(T)]
+    for n in (0, 1, 119, 120, 121, 4095, 4096, 4097):
+        cols, y, sig, w = make_data(n, n_bins, 300 + n, weighted=False, wpr=T, poisson=True)
+        d, o = _one_pass(cfg, cols, y, sig, w, todo, roots)
+        assert np.array_equal(d[4], o[4]), n
+        for a, b in zip(d[:4], o[:4]):
+            assert abs(a - b) <= 1e-9 * abs(b) + 1e-12, (n, d[:4], o[:4])
+    cols, y, sig, w = make_data(5000, n_bins, 77, weighted=False, wpr=T, poisson=True)
+    w[1, :] = 0.0                      # tree 1: every row out of bag
+    d, o = _one_pass(cfg, cols, y, sig, w, todo, roots)
+    assert np.array_equal(d[4], o[4]) and np.all(d[4].reshape(T, -1)[1] == 0)
+    w[0, :] = 0.0                      # only the last tree has pairs
+    d, o = _one_pass(cfg, cols, y, sig, w, todo, roots)
+    assert np.array_equal(d[4], o[4])
+    w[2, :] = 0.0                      # no pair at all: the kernels must do nothing
+    d, o = _one_pass(cfg, cols, y, sig, w, todo, roots)
+    assert np.array_equal(d[4], o[4]) and not d[4].any()
+
+
+def test_forest_only_some_trees_have_todo_nodes():
+    """Trees 0 and 3 of five are in the pass, each with a node list of its own; the others are walked for the error sums only."""
+    T, n_bins = 5, [16] * 20
+    cfg = ConfigArrays(n_bins, impurity=capi.SB_IMPURITY_ENTROPY, num_classes=2, loss=capi.SB_LOSS_SQUARED, is_gbdt=False, tree_num=T,
+                       weights_per_row=T, max_depth=3, min_instances_per_node=1)
+    cols, y, sig, w = make_data(7000, n_bins, 81, weighted=False, wpr=T, poisson=True)
+    vcols, vy, _, _ = make_data(900, n_bins, 82, weighted=False)
+    roots = [(t, Node(1)) for t in range(T)]
+    todo = [(0, 0, 1, [0, 3, 5, 19]), (1, 3, 1, list(range(2, 17)))]
+    d, o = _one_pass(cfg, cols, y, sig, w, todo, roots, vcols, vy)
+    assert np.array_equal(d[4], o[4])
+    for a, b in zip(d[:4], o[:4]):
+        assert abs(a - b) <= 1e-9 * abs(b) + 1e-12, (d[:4], o[:4])
