@@ -375,7 +375,9 @@ __global__ void __launch_bounds__(256) forest_count_kernel(const ForestListArgs 
 // a row's line of the twin is fetched from DRAM once and comes out of L2 for the other trees that hold the row (the
 // twin of 10M rows is ten times the L2; a slab is a fraction of it).  Every chunk merges its block's histogram into the
 // global accumulators, so J is bounded by what that costs: J sweeps over the statistics buffer must stay well below the
-// bytes of bins the pass reads.  One block; the word behind n_chunks is the work counter of the persistent statistics kernel.
+// bytes of bins the pass reads.  By default the slab size is unbounded and J only provides enough chunks to fill the GPU:
+// slabs sized for L2 (SB_FOREST_SLAB_MB) were measured slower on C1 at every size, because the class kernel is not bound by
+// HBM.  One block; the words behind n_chunks are the work counters of the persistent statistics kernels.
 __global__ void __launch_bounds__(1024) forest_chunks_kernel(const ForestListArgs a) {
     __shared__ int s_J, s_R, s_base;
     __shared__ int s_warp[32];
