@@ -272,6 +272,8 @@ struct sb_handle {
     const int64_t* d_flat_node_off = nullptr;
     int flat_max_list = 0, flat_max_cat_bins = 0;
     bool flat_has_cat = false;
+    std::vector<uint8_t> flat_used;  // feature slot appears in some caller list of the pass
+    int64_t* d_int_feat_off = nullptr;  // [F] offset of a feature's block inside a node block that holds every valid feature, -1
     std::vector<uint32_t> col_flags;  // per sample-weight column: bit0 non-integer products, bit1 a weight != 1
     size_t scan_temp_bytes = 0;
     bool split_planned = false;
@@ -557,32 +559,43 @@ int upload_tree(sb_handle* h, const sb_tree& t, DeviceTree& d) {
 }
 
 // dt/DTWorker.java:903-929 initTodoNodeStats: sizes and order of the statistics buffer.
-int build_layout(const sb_handle* h, const sb_iter_in* in, TodoLayout& lay, bool flat = false) {
+int build_layout(const sb_handle* h, const sb_iter_in* in, TodoLayout& lay, bool flat = false, bool full = false, bool keep_lists = true) {
     // `lay` is recycled from an earlier pass: resize + assign keep the capacity of the inner vectors
-    lay.nodes.resize((size_t)std::max(in->n_todo, 0));
+    const int N = std::max(in->n_todo, 0);
+    lay.nodes.resize((size_t)N);
     lay.flat = flat;
+    lay.full = full;
     lay.flat_begin.clear();
     lay.flat_feats.clear();
+    lay.caller_off.resize((size_t)N);
     int64_t off = 0;
     if (flat) {
-        // one flat array for all lists: a pass of an RF at depth 10 has 10^4 todo nodes with their own feature subsets
+        // the caller's lists as one flat array: a pass of an RF at depth 10 has 10^4 todo nodes with their own subsets
         const int F = h->cfg.n_features;
         const int n_all = (int)h->all_features.size();
         size_t total_feats = 0;
-        for (int i = 0; i < in->n_todo; ++i) total_feats += (size_t)(in->todo[i].n_features == 0 ? n_all : in->todo[i].n_features);
+        for (int i = 0; i < N; ++i) total_feats += (size_t)(in->todo[i].n_features == 0 ? n_all : in->todo[i].n_features);
         if (total_feats > (size_t)0x7fffffff) return fail(SB_ERR_UNSUPPORTED, "more than 2^31 (todo node, feature) pairs in one pass");
         lay.flat_feats.resize(total_feats);
-        lay.flat_begin.resize((size_t)in->n_todo + 1);
+        lay.flat_begin.resize((size_t)N + 1);
         std::vector<int64_t> len_of((size_t)F);
         for (int f = 0; f < F; ++f) len_of[(size_t)f] = (int64_t)h->n_bins[(size_t)f] * h->stats_size;
         size_t at = 0;
-        for (int i = 0; i < in->n_todo; ++i) {
+        for (int i = 0; i < N; ++i) {
             const sb_todo_node& t = in->todo[i];
             TodoLayout::Node& nd = lay.nodes[(size_t)i];
-            nd.key = t.key; nd.tree_id = t.tree_id; nd.node_id = t.node_id; nd.offset = off;
-            nd.features.clear();
-            nd.feat_off.clear();
+            nd.key = t.key; nd.tree_id = t.tree_id; nd.node_id = t.node_id;
+            lay.caller_off[(size_t)i] = off;
             lay.flat_begin[(size_t)i] = (int32_t)at;
+            if (full) {  // internal layout: every valid feature, the same block size for every node
+                nd.offset = (int64_t)i * h->all_feat_total;
+                if (keep_lists) { nd.features = h->all_features; nd.feat_off = h->all_feat_off; }
+                else { nd.features.clear(); nd.feat_off.clear(); }
+            } else {
+                nd.offset = off;
+                nd.features.clear();
+                nd.feat_off.clear();
+            }
             if (t.n_features == 0) {
                 if (n_all) memcpy(&lay.flat_feats[at], h->all_features.data(), (size_t)n_all * 4);
                 at += (size_t)n_all;
@@ -593,20 +606,23 @@ int build_layout(const sb_handle* h, const sb_iter_in* in, TodoLayout& lay, bool
             for (int k = 0; k < t.n_features; ++k) {
                 const int f = t.features[k];
                 if (f < 0 || f >= F) return fail(SB_ERR_INVALID, "todo node feature slot out of range");
+                if (full && h->all_feature_pos[(size_t)f] < 0) return fail(SB_ERR_INVALID, "todo node lists a feature without bins to split");
                 lay.flat_feats[at + (size_t)k] = f;
                 l += len_of[(size_t)f];
             }
             at += (size_t)t.n_features;
             off += l;
         }
-        lay.flat_begin[(size_t)in->n_todo] = (int32_t)at;
-        lay.total = off;
+        lay.flat_begin[(size_t)N] = (int32_t)at;
+        lay.caller_total = off;
+        lay.total = full ? (int64_t)N * h->all_feat_total : off;
         return SB_OK;
     }
-    for (int i = 0; i < in->n_todo; ++i) {
+    for (int i = 0; i < N; ++i) {
         const sb_todo_node& t = in->todo[i];
         TodoLayout::Node& nd = lay.nodes[(size_t)i];
         nd.key = t.key; nd.tree_id = t.tree_id; nd.node_id = t.node_id; nd.offset = off;
+        lay.caller_off[(size_t)i] = off;
         if (t.n_features == 0) {  // every valid feature: sizes and offsets are the same for all such nodes
             nd.features = h->all_features;
             nd.feat_off = h->all_feat_off;
@@ -624,6 +640,37 @@ int build_layout(const sb_handle* h, const sb_iter_in* in, TodoLayout& lay, bool
         off += l;
     }
     lay.total = off;
+    lay.caller_total = off;
+    return SB_OK;
+}
+
+// The caller's flat feature lists of the pass on the device (shared by the (slot, feature) offset kernel of a forest
+// pass, the split task kernel and the gather of a full pass), and what the split step wants to know about them.
+int stage_flat_lists(sb_handle* h) {
+    const TodoLayout& lay = h->layout;
+    const int N = (int)lay.nodes.size();
+    const int F = h->cfg.n_features;
+    h->d_flat_feats = h->d_flat_begin = nullptr;
+    h->d_flat_node_off = nullptr;
+    h->flat_max_list = 0;
+    h->flat_has_cat = false;
+    h->flat_max_cat_bins = 0;
+    if (N == 0) return SB_OK;
+    h->flat_used.assign((size_t)F, 0);
+    for (int32_t f : lay.flat_feats) h->flat_used[(size_t)f] = 1;
+    for (int i = 0; i < N; ++i) h->flat_max_list = std::max(h->flat_max_list, lay.flat_begin[(size_t)i + 1] - lay.flat_begin[(size_t)i]);
+    for (int f = 0; f < F; ++f)
+        if (h->flat_used[(size_t)f] && h->is_cat[(size_t)f]) { h->flat_has_cat = true; h->flat_max_cat_bins = std::max(h->flat_max_cat_bins, h->n_bins[(size_t)f]); }
+    int32_t *hf = nullptr, *df = nullptr, *hb = nullptr, *db = nullptr;
+    int64_t *ho = nullptr, *dof = nullptr;
+    SB_CUDA(h->stage.take(std::max<size_t>(lay.flat_feats.size(), 1), &hf, &df, h->stream));
+    SB_CUDA(h->stage.take((size_t)N + 1, &hb, &db, h->stream));
+    SB_CUDA(h->stage.take((size_t)N, &ho, &dof, h->stream));
+    if (!lay.flat_feats.empty()) memcpy(hf, lay.flat_feats.data(), lay.flat_feats.size() * 4);
+    memcpy(hb, lay.flat_begin.data(), ((size_t)N + 1) * 4);
+    memcpy(ho, lay.caller_off.data(), (size_t)N * 8);
+    h->d_flat_feats = df; h->d_flat_begin = db; h->d_flat_node_off = dof;
+    h->h2d_bytes += (int64_t)lay.flat_feats.size() * 4 + ((int64_t)N + 1) * 4 + (int64_t)N * 8;
     return SB_OK;
 }
 
@@ -808,8 +855,8 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
     std::vector<uint8_t> used((size_t)F, 0), used_wide((size_t)F, 0);
     bool any_wide = false;
     // common case (GBT with FeatureSubsetStrategy ALL): every todo node takes every valid feature -- one list to look at
-    bool all_feats_nodes = true;
-    for (int i = 0; i < in->n_todo && all_feats_nodes; ++i) all_feats_nodes = in->todo[i].n_features == 0;
+    bool all_feats_nodes = true;  // (a full pass lays every node out with every valid feature, whatever its own list)
+    for (int i = 0; i < in->n_todo && all_feats_nodes && !lay.full; ++i) all_feats_nodes = in->todo[i].n_features == 0;
     auto mark_used = [&](const std::vector<int>& feats) {
         for (int f : feats) {
             if (h->wide_index[f] >= 0) { used_wide[f] = 1; any_wide = true; }
@@ -1249,36 +1296,16 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
     const int N = (int)lay.nodes.size();
     RowSet& tr = h->train;
     const int64_t n = tr.n;
-    h->d_flat_feats = h->d_flat_begin = nullptr;
-    h->d_flat_node_off = nullptr;
-    h->flat_max_list = 0;
-    h->flat_has_cat = false;
-    h->flat_max_cat_bins = 0;
     if (N == 0) return SB_OK;
 
-    // ---- the lists on the device + what the split step wants to know about them
-    std::vector<uint8_t> used_any((size_t)F, 0), used((size_t)F, 0), used_wide((size_t)F, 0);
-    for (int32_t f : lay.flat_feats) used_any[(size_t)f] = 1;
+    // ---- features in use (the caller's lists are on the device already: stage_flat_lists)
+    const std::vector<uint8_t>& used_any = h->flat_used;
+    std::vector<uint8_t> used((size_t)F, 0), used_wide((size_t)F, 0);
     bool any_wide = false;
     for (int f = 0; f < F; ++f) {
         if (!used_any[(size_t)f]) continue;
         if (h->wide_index[(size_t)f] >= 0) { used_wide[(size_t)f] = 1; any_wide = true; }
         else used[(size_t)f] = 1;
-    }
-    for (int i = 0; i < N; ++i) h->flat_max_list = std::max(h->flat_max_list, lay.flat_begin[(size_t)i + 1] - lay.flat_begin[(size_t)i]);
-    for (int f = 0; f < F; ++f)
-        if (used_any[(size_t)f] && h->is_cat[(size_t)f]) { h->flat_has_cat = true; h->flat_max_cat_bins = std::max(h->flat_max_cat_bins, h->n_bins[(size_t)f]); }
-    {
-        int32_t *hf = nullptr, *df = nullptr, *hb = nullptr, *db = nullptr;
-        int64_t *ho = nullptr, *dof = nullptr;
-        SB_CUDA(h->stage.take(std::max<size_t>(lay.flat_feats.size(), 1), &hf, &df, h->stream));
-        SB_CUDA(h->stage.take((size_t)N + 1, &hb, &db, h->stream));
-        SB_CUDA(h->stage.take((size_t)N, &ho, &dof, h->stream));
-        if (!lay.flat_feats.empty()) memcpy(hf, lay.flat_feats.data(), lay.flat_feats.size() * 4);
-        memcpy(hb, lay.flat_begin.data(), ((size_t)N + 1) * 4);
-        for (int i = 0; i < N; ++i) ho[i] = lay.nodes[(size_t)i].offset;
-        h->d_flat_feats = df; h->d_flat_begin = db; h->d_flat_node_off = dof;
-        h->h2d_bytes += (int64_t)lay.flat_feats.size() * 4 + ((int64_t)N + 1) * 4 + (int64_t)N * 8;
     }
     if (n == 0) return SB_OK;  // a shard without rows still takes part in the merge
 
@@ -1792,6 +1819,12 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
         h->all_feat_total += (int64_t)h->n_bins[f] * h->stats_size;
     }
     SB_CUDA(cudaMalloc(&h->d_feat_bins, sizeof(int32_t) * cfg->n_features));
+    {
+        std::vector<int64_t> int_off((size_t)cfg->n_features, -1);
+        for (size_t k = 0; k < h->all_features.size(); ++k) int_off[(size_t)h->all_features[k]] = h->all_feat_off[k];
+        SB_CUDA(cudaMalloc(&h->d_int_feat_off, sizeof(int64_t) * cfg->n_features));
+        SB_CUDA(cudaMemcpy(h->d_int_feat_off, int_off.data(), sizeof(int64_t) * cfg->n_features, cudaMemcpyHostToDevice));
+    }
     SB_CUDA(cudaMalloc(&h->d_is_cat, (size_t)cfg->n_features));
     SB_CUDA(cudaMalloc(&h->d_column_num, sizeof(int32_t) * cfg->n_features));
     SB_CUDA(cudaMemcpy(h->d_is_cat, h->is_cat.data(), (size_t)cfg->n_features, cudaMemcpyHostToDevice));
@@ -1841,6 +1874,7 @@ SB_API void sb_destroy(sb_handle* h) {
     if (h->d_scales) cudaFree(h->d_scales);
     if (h->d_inv_scales) cudaFree(h->d_inv_scales);
     if (h->d_error_flag) cudaFree(h->d_error_flag);
+    if (h->d_int_feat_off) cudaFree(h->d_int_feat_off);
     if (h->d_rows_streamed) cudaFree(h->d_rows_streamed);
     if (h->d_cnt_shift) cudaFree(h->d_cnt_shift);
     delete h;
@@ -2105,13 +2139,36 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     h->stage.reset();  // the previous pass ended with a stream synchronisation: its tables are no longer in use
     std::swap(h->layout, h->prev_layout);  // the last pass's layout goes with raw_prev; its storage before that is recycled
     h->forest_pass = forest_lists(h);
-    int rc = build_layout(h, in, h->layout, h->forest_pass);
+    // Nodes with feature lists of their own (FeatureSubsetStrategy): when the lists cover a fair share of the features,
+    // accumulate EVERY valid feature for every node (the kernels do that in shared memory anyway, see plan_histograms) and
+    // keep it, so that histogram subtraction and the root count cache work as they do without lists; the caller's
+    // statistics are gathered from that internal layout (finish_enqueue).
+    bool full = false;
+    if (h->enable_subtraction && !h->forest_pass && in->n_todo > 0 && !h->all_features.empty()) {
+        int64_t listed = 0;
+        bool own = false;
+        bool listable = true;  // every listed feature has a block in the all-features layout
+        for (int i = 0; i < in->n_todo; ++i) {
+            const sb_todo_node& t = in->todo[i];
+            own |= t.n_features != 0;
+            listed += t.n_features == 0 ? (int64_t)h->all_features.size() : t.n_features;
+            for (int k = 0; k < t.n_features && listable; ++k)
+                listable = t.features[k] >= 0 && t.features[k] < h->cfg.n_features && h->all_feature_pos[(size_t)t.features[k]] >= 0;
+        }
+        static const bool off = getenv("SB_NO_FULL_PASS") != nullptr;
+        full = own && listable && !off && 4 * listed >= (int64_t)in->n_todo * (int64_t)h->all_features.size();
+    }
+    int rc = build_layout(h, in, h->layout, h->forest_pass || full, full, !h->forest_pass);
     if (rc != SB_OK) return rc;
+    if (h->layout.flat) {
+        rc = stage_flat_lists(h);
+        if (rc != SB_OK) return rc;
+    }
     rc = pinned_reserve(h, pinned_need(h));  // now, while the GPU is idle: growing the pinned block waits for the device
     if (rc != SB_OK) return rc;
     const int64_t total = h->layout.total;
     SB_CUDA(h->raw.reserve(h->stream, (size_t)std::max<int64_t>(2 * total, 1)));
-    SB_CUDA(h->stats.reserve(h->stream, (size_t)std::max<int64_t>(total, 1)));
+    SB_CUDA(h->stats.reserve(h->stream, (size_t)std::max<int64_t>(h->layout.caller_total, 1)));
     SB_CUDA(cudaMemsetAsync(h->raw.p, 0, (size_t)(2 * total) * 8, h->stream));
     // GBT error sums are sums over Data.predict, which only changes at a tree switch (dt/DTWorker.java:627-640, 681):
     // inside a tree (after the first one) the four scalars of the previous pass are still the answer.
@@ -2598,23 +2655,30 @@ static int pinned_reserve(sb_handle* h, size_t bytes) {
 }
 
 static int finish_enqueue(sb_handle* h, sb_iter_out* out) {
-    const int64_t total = h->layout.total;
-    if (out->stats && out->stats_len < total) return fail(SB_ERR_INVALID, "stats buffer too small");
+    const int64_t total = h->layout.total, caller_total = h->layout.caller_total;
+    if (out->stats && out->stats_len < caller_total) return fail(SB_ERR_INVALID, "stats buffer too small");
     if (!h->pairs.empty()) {  // the larger child of every sibling pair = parent - smaller child (after the merge)
         SB_CUDA(launch_pair_fixup(h->d_pairs.p, (int)h->pairs.size(), h->pair_max_len, h->d_small_is_b.p, h->raw_prev.p,
                                   h->raw_prev.p + h->prev_layout.total, h->raw.p, h->raw.p + total, h->stream));
         h->launches_count += 1;
         h->pairs.clear();
     }
-    SB_CUDA(launch_finalize(h->raw.p, h->raw.p + total, total, h->stats_size, h->stat_kind, h->d_inv_scales, h->stats.p, h->stream));
+    if (h->layout.full) {
+        // the caller's blocks out of the internal all-features layout, one (node, listed feature) task at a time
+        if (!h->split_planned) return fail(SB_ERR_STATE, "sb_compute_finish before sb_compute_stats");
+        SB_CUDA(launch_finalize_tasks(h->raw.p, h->raw.p + total, h->tasks.p, h->n_tasks, h->all_feat_total, h->d_int_feat_off, h->stats_size,
+                                      h->stat_kind, h->d_inv_scales, h->stats.p, h->stream));
+    } else {
+        SB_CUDA(launch_finalize(h->raw.p, h->raw.p + total, total, h->stats_size, h->stat_kind, h->d_inv_scales, h->stats.p, h->stream));
+    }
     h->launches_count += 1;
     PinnedOut* po = static_cast<PinnedOut*>(h->pin);
     SB_CUDA(cudaMemcpyAsync(po->acc, h->d_acc, 32, cudaMemcpyDeviceToHost, h->stream));
     SB_CUDA(cudaMemcpyAsync(po->flags, h->d_error_flag, 4, cudaMemcpyDeviceToHost, h->stream));
     SB_CUDA(cudaMemcpyAsync(po->maxbits, h->d_maxbits, 12, cudaMemcpyDeviceToHost, h->stream));
-    if (out->stats && total > 0) {
-        SB_CUDA(cudaMemcpyAsync(out->stats, h->stats.p, (size_t)total * 8, cudaMemcpyDeviceToHost, h->stream));
-        h->d2h_bytes += total * 8;
+    if (out->stats && caller_total > 0) {
+        SB_CUDA(cudaMemcpyAsync(out->stats, h->stats.p, (size_t)caller_total * 8, cudaMemcpyDeviceToHost, h->stream));
+        h->d2h_bytes += caller_total * 8;
     }
     h->d2h_bytes += 48;
     return SB_OK;

@@ -82,11 +82,18 @@ struct TodoLayout {  // host description of the statistics buffer of one iterati
     };
     std::vector<Node> nodes;
     int64_t total = 0;  // doubles
-    // Forest passes (RF with thousands of todo nodes): the feature lists as one flat array instead of a vector per node;
-    // nodes[i].features / feat_off stay empty then.
+    // flat: the CALLER's feature lists are kept as one flat array (forest passes of an RF with thousands of todo nodes,
+    // where nodes[i].features / feat_off stay empty; and full passes).
     bool flat = false;
     std::vector<int32_t> flat_begin;  // [n + 1]
     std::vector<int32_t> flat_feats;  // lists in todo order; a node that takes every valid feature has them spelled out
+    // full: todo nodes have feature lists of their own, but the accumulators are laid out (and filled) for EVERY valid
+    // feature of every node -- nodes[i] describes that internal layout, `total` is its size -- so that a child can be
+    // derived from its parent and sibling whatever the lists are.  The caller still gets its own layout: caller_off[i] =
+    // offset of node i's block there, caller_total its size (== total and nodes[i].offset when not full).
+    bool full = false;
+    std::vector<int64_t> caller_off;
+    int64_t caller_total = 0;
 };
 
 }  // namespace sb

@@ -364,6 +364,12 @@ struct PairDesc {
     int32_t table_off;           // offset of the tree's slot table inside the slot-table buffer
     int32_t pad;
 };
+// the same for a full pass: task t's block is read at tasks[t].node * node_stride + feat_off[tasks[t].feature] of the
+// internal (every valid feature) layout and written at tasks[t].offset of the caller's
+struct SplitTask;
+cudaError_t launch_finalize_tasks(const int64_t* raw_lo, const int64_t* raw_hi, const SplitTask* tasks, int n_tasks, int64_t node_stride,
+                                  const int64_t* feat_off, int stats_size, int kind, const double* inv_scales, double* stats,
+                                  cudaStream_t s);
 cudaError_t launch_pair_decide(const PairDesc* pairs, int n_pairs, const int64_t* prev_lo, const int64_t* prev_hi,
                                int stats_size, int kind, int n_features, int16_t* slot_tables, int64_t* pair_off,
                                int32_t* small_is_b, cudaStream_t s);

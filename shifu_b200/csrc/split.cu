@@ -45,6 +45,21 @@ __global__ void finalize_stats_kernel(const int64_t* __restrict__ raw_lo, const 
     (void)stats_size;
 }
 
+__global__ void finalize_tasks_kernel(const int64_t* __restrict__ raw_lo, const int64_t* __restrict__ raw_hi,
+                                      const SplitTask* __restrict__ tasks, int n_tasks, int64_t node_stride,
+                                      const int64_t* __restrict__ feat_off, int stats_size, int kind,
+                                      const double* __restrict__ inv_scales, double* __restrict__ stats) {
+    const int t = (int)((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+    if (t >= n_tasks) return;
+    const SplitTask tk = tasks[t];
+    const int64_t src = (int64_t)tk.node * node_stride + feat_off[tk.feature];
+    const int n = tk.n_bins * stats_size;
+    for (int i = lane; i < n; i += 32) {
+        const int st = (kind == STAT_VARIANCE) ? i % 3 : 0;
+        stats[tk.offset + i] = int96_to_double(raw_lo[src + i], raw_hi[src + i]) * inv_scales[st];
+    }
+}
+
 constexpr double JAVA_DOUBLE_MIN_VALUE = 4.9406564584124654e-324;
 
 // Double.compareTo ordering: numeric, -0.0 < +0.0, NaN greatest.
@@ -605,6 +620,15 @@ cudaError_t launch_finalize(const int64_t* raw_lo, const int64_t* raw_hi, int64_
     int64_t g = (total + 255) / 256;
     if (g > 148 * 8) g = 148 * 8;
     finalize_stats_kernel<<<(int)g, 256, 0, s>>>(raw_lo, raw_hi, total, stats_size, kind, inv_scales, stats);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_finalize_tasks(const int64_t* raw_lo, const int64_t* raw_hi, const SplitTask* tasks, int n_tasks, int64_t node_stride,
+                                  const int64_t* feat_off, int stats_size, int kind, const double* inv_scales, double* stats,
+                                  cudaStream_t s) {
+    if (n_tasks <= 0) return cudaSuccess;
+    finalize_tasks_kernel<<<(unsigned)(((int64_t)n_tasks * 32 + 255) / 256), 256, 0, s>>>(raw_lo, raw_hi, tasks, n_tasks, node_stride, feat_off,
+                                                                                          stats_size, kind, inv_scales, stats);
     return cudaGetLastError();
 }
 
