@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <unordered_map>
 #include <memory>
 
 #include "common.cuh"
@@ -1299,7 +1300,10 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
     if (N == 0) return SB_OK;
 
     // ---- features in use (the caller's lists are on the device already: stage_flat_lists)
-    const std::vector<uint8_t>& used_any = h->flat_used;
+    // (a full pass accumulates and keeps every valid feature, whatever the lists say)
+    std::vector<uint8_t> used_any(h->flat_used);
+    if (lay.full)
+        for (int f : h->all_features) used_any[(size_t)f] = 1;
     std::vector<uint8_t> used((size_t)F, 0), used_wide((size_t)F, 0);
     bool any_wide = false;
     for (int f = 0; f < F; ++f) {
@@ -1309,7 +1313,9 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
     }
     if (n == 0) return SB_OK;  // a shard without rows still takes part in the merge
 
-    // ---- slots: todo nodes ordered by tree (stable counting sort), one slot each
+    // ---- slots: todo nodes ordered by tree (stable counting sort), one slot each -- or, on a full pass, one slot per
+    // SIBLING PAIR whose parent's merged accumulators are still on the device (the previous pass was full as well): only
+    // the smaller child is accumulated, the other one is parent - child (pair_decide / pair_fixup, exact in the integers)
     const int T_arr = tr.n_node_arrays;
     std::vector<int> first((size_t)T_arr + 1, 0);
     for (int i = 0; i < N; ++i) {
@@ -1319,31 +1325,114 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
         first[(size_t)t + 1] += 1;
     }
     for (int t = 0; t < T_arr; ++t) first[(size_t)t + 1] += first[(size_t)t];
-    const int S = N;
-    int32_t *slot_node = nullptr, *d_slot_node = nullptr;
-    SB_CUDA(h->stage.take((size_t)S, &slot_node, &d_slot_node, h->stream));
+    std::vector<int> by_tree((size_t)N);  // todo indices ordered by tree, todo order inside a tree
     {
         std::vector<int> at(first.begin(), first.end() - 1);
-        for (int i = 0; i < N; ++i) {
-            slot_node[at[(size_t)lay.nodes[(size_t)i].tree_id]++] = i;
+        for (int i = 0; i < N; ++i) by_tree[(size_t)at[(size_t)lay.nodes[(size_t)i].tree_id]++] = i;
+    }
+    h->pairs.clear();
+    h->pair_max_len = 0;
+    std::vector<int> partner((size_t)N, -1);     // todo index of child B for child A of a pair; -2 for child B
+    std::vector<int> pair_parent_prev;           // per pair (in the order of their child A in by_tree): index into prev_layout
+    if (lay.full && h->enable_subtraction && h->use_prev && h->prev_layout.full) {
+        auto key_of = [](int tree, int node) { return ((uint64_t)(uint32_t)tree << 32) | (uint32_t)node; };
+        std::unordered_map<uint64_t, int> cur_idx, prev_idx;
+        cur_idx.reserve((size_t)N * 2);
+        prev_idx.reserve(h->prev_layout.nodes.size() * 2);
+        for (int i = 0; i < N; ++i) cur_idx[key_of(lay.nodes[(size_t)i].tree_id, lay.nodes[(size_t)i].node_id)] = i;
+        for (size_t i = 0; i < h->prev_layout.nodes.size(); ++i)
+            prev_idx[key_of(h->prev_layout.nodes[i].tree_id, h->prev_layout.nodes[i].node_id)] = (int)i;
+        for (int q = 0; q < N; ++q) {
+            const int i = by_tree[(size_t)q];
+            const auto& a = lay.nodes[(size_t)i];
+            if (a.node_id < 2 || (a.node_id & 1)) continue;
+            auto ib = cur_idx.find(key_of(a.tree_id, a.node_id + 1));
+            auto ip = prev_idx.find(key_of(a.tree_id, a.node_id / 2));
+            if (ib == cur_idx.end() || ip == prev_idx.end()) continue;
+            if (find_tree(in, a.tree_id) == nullptr) continue;
+            partner[(size_t)i] = ib->second;
+            partner[(size_t)ib->second] = -2;
+            pair_parent_prev.push_back(ip->second);
         }
     }
+    std::vector<int> slot_of_todo((size_t)N, -1);
+    int S = 0;
+    for (int q = 0; q < N; ++q)
+        if (partner[(size_t)by_tree[(size_t)q]] != -2) slot_of_todo[(size_t)by_tree[(size_t)q]] = S++;
+    for (int i = 0; i < N; ++i)
+        if (partner[(size_t)i] >= 0) slot_of_todo[(size_t)partner[(size_t)i]] = slot_of_todo[(size_t)i];
+    int32_t *slot_node = nullptr, *d_slot_node = nullptr;   // the todo node a slot stands for (child A of a pair)
+    SB_CUDA(h->stage.take((size_t)S, &slot_node, &d_slot_node, h->stream));
+    for (int i = 0; i < N; ++i)
+        if (partner[(size_t)i] != -2) slot_node[slot_of_todo[(size_t)i]] = i;
     // slot tables: heap id -> global slot, one table per tree with todo nodes
     struct TreeSlots { int tree_id, s0, s1, table_off, table_size; };
     std::vector<TreeSlots> tl;
     size_t table_total = 0;
     for (int t = 0; t < T_arr; ++t) {
         if (first[(size_t)t + 1] == first[(size_t)t]) continue;
-        int max_id = 1;
-        for (int sl = first[(size_t)t]; sl < first[(size_t)t + 1]; ++sl) max_id = std::max(max_id, lay.nodes[(size_t)slot_node[sl]].node_id);
-        tl.push_back({t, first[(size_t)t], first[(size_t)t + 1], (int)table_total, max_id + 1});
+        int max_id = 1, s0 = S, s1 = 0;
+        for (int q = first[(size_t)t]; q < first[(size_t)t + 1]; ++q) {
+            const int i = by_tree[(size_t)q];
+            max_id = std::max(max_id, lay.nodes[(size_t)i].node_id);
+            s0 = std::min(s0, slot_of_todo[(size_t)i]);
+            s1 = std::max(s1, slot_of_todo[(size_t)i] + 1);
+        }
+        tl.push_back({t, s0, s1, (int)table_total, max_id + 1});
         table_total += (size_t)max_id + 1;
     }
     int32_t *tables = nullptr, *d_tables = nullptr;
     SB_CUDA(h->stage.take(table_total, &tables, &d_tables, h->stream));
     for (size_t i = 0; i < table_total; ++i) tables[i] = -1;
+    // both children of a pair map to the pair's slot for now; pair_decide_kernel removes the larger one
     for (const TreeSlots& ts : tl)
-        for (int sl = ts.s0; sl < ts.s1; ++sl) tables[(size_t)ts.table_off + (size_t)lay.nodes[(size_t)slot_node[sl]].node_id] = sl;
+        for (int q = first[(size_t)ts.tree_id]; q < first[(size_t)ts.tree_id + 1]; ++q) {
+            const int i = by_tree[(size_t)q];
+            tables[(size_t)ts.table_off + (size_t)lay.nodes[(size_t)i].node_id] = slot_of_todo[(size_t)i];
+        }
+    // the pairs: parent's split block and node block in the previous pass, the children's blocks in this one
+    if (!pair_parent_prev.empty()) {
+        std::vector<int> msg_index;
+        int msg_index_tree = -1;
+        const sb_tree* tr_msg = nullptr;
+        size_t pi = 0;
+        for (int q = 0; q < N; ++q) {
+            const int i = by_tree[(size_t)q];
+            if (partner[(size_t)i] < 0) continue;
+            const auto& na = lay.nodes[(size_t)i];
+            const auto& nb = lay.nodes[(size_t)partner[(size_t)i]];
+            const auto& par = h->prev_layout.nodes[(size_t)pair_parent_prev[pi++]];
+            if (msg_index_tree != na.tree_id) {
+                msg_index_tree = na.tree_id;
+                tr_msg = find_tree(in, na.tree_id);
+                msg_index.clear();
+                for (int k = 0; k < tr_msg->n_nodes; ++k) {
+                    const int id = tr_msg->nodes[k].id;
+                    if (id >= (int)msg_index.size()) msg_index.resize((size_t)id + 1, -1);
+                    msg_index[(size_t)id] = k;
+                }
+            }
+            const int pid = na.node_id / 2;
+            const sb_node* pn = (pid < (int)msg_index.size() && msg_index[(size_t)pid] >= 0) ? &tr_msg->nodes[msg_index[(size_t)pid]] : nullptr;
+            if (!pn || pn->feature < 0 || pn->feature >= F || h->all_feature_pos[(size_t)pn->feature] < 0)
+                return fail(SB_ERR_STATE, "histogram subtraction: parent split not found");
+            const int li = [&] { for (size_t k = 0; k < tl.size(); ++k) if (tl[k].tree_id == na.tree_id) return (int)k; return -1; }();
+            PairDesc d{};
+            d.parent_split_block = par.offset + h->all_feat_off[(size_t)h->all_feature_pos[(size_t)pn->feature]];
+            d.parent_off = par.offset;
+            d.off_a = na.offset;
+            d.off_b = nb.offset;
+            d.len = h->all_feat_total;
+            d.left_mask = h->trees[na.tree_id].masks + pn->left_mask_offset;
+            d.n_bins = h->n_bins[(size_t)pn->feature];
+            d.node_a = na.node_id;
+            d.node_b = nb.node_id;
+            d.slot = slot_of_todo[(size_t)i];
+            d.table_off = tl[(size_t)li].table_off;
+            h->pairs.push_back(d);
+        }
+        h->pair_max_len = h->all_feat_total;
+    }
     ListTree *lts = nullptr, *d_lts = nullptr;
     SB_CUDA(h->stage.take(tl.size(), &lts, &d_lts, h->stream));
     const int W = h->cfg.weights_per_row;
@@ -1433,9 +1522,22 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
     // ---- (slot, feature) -> offset in the statistics, on the device
     SB_CUDA(h->forest_pair_off.reserve(h->stream, (size_t)S * F));
     SB_CUDA(h->stage.flush(h->stream));
-    SB_CUDA(launch_build_pair_off(d_slot_node, S, h->d_flat_feats, h->d_flat_begin, h->d_flat_node_off, h->d_feat_bins,
-                                  h->stats_size, F, h->forest_pair_off.p, h->stream));
-    h->launches_count += 1;
+    if (lay.full) {
+        SB_CUDA(launch_fill_pair_off_full(d_slot_node, S, h->all_feat_total, h->d_int_feat_off, F, h->forest_pair_off.p, h->stream));
+        h->launches_count += 1;
+        if (!h->pairs.empty()) {
+            SB_CUDA(stage_into(h, h->d_pairs, h->pairs.data(), h->pairs.size()));
+            SB_CUDA(h->d_small_is_b.reserve(h->stream, h->pairs.size()));
+            SB_CUDA(h->stage.flush(h->stream));
+            SB_CUDA(launch_pair_decide32(h->d_pairs.p, (int)h->pairs.size(), h->raw_prev.p, h->raw_prev.p + h->prev_layout.total,
+                                         h->stats_size, h->stat_kind, F, d_tables, h->forest_pair_off.p, h->d_small_is_b.p, h->stream));
+            h->launches_count += 1;
+        }
+    } else {
+        SB_CUDA(launch_build_pair_off(d_slot_node, S, h->d_flat_feats, h->d_flat_begin, h->d_flat_node_off, h->d_feat_bins,
+                                      h->stats_size, F, h->forest_pair_off.p, h->stream));
+        h->launches_count += 1;
+    }
 
     // ---- batches of trees
     const size_t ops_bytes = slim ? sizeof(ClassOps) : sizeof(RowOps);
@@ -2144,7 +2246,7 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     // keep it, so that histogram subtraction and the root count cache work as they do without lists; the caller's
     // statistics are gathered from that internal layout (finish_enqueue).
     bool full = false;
-    if (h->enable_subtraction && !h->forest_pass && in->n_todo > 0 && !h->all_features.empty()) {
+    if (h->enable_subtraction && in->n_todo > 0 && !h->all_features.empty()) {
         int64_t listed = 0;
         bool own = false;
         bool listable = true;  // every listed feature has a block in the all-features layout
@@ -2464,7 +2566,7 @@ SB_API int sb_compute_stats(sb_handle* h) {
             const int which = h->raw.p == h->p2p.buf[0] ? 0 : (h->raw.p == h->p2p.buf[1] ? 1 : -1);
             if (h->p2p.ok && which >= 0) {  // the accumulators sit in peer-mapped memory: merge over NVLink loads (p2p.cu)
                 // the tail barrier is implied only when the two buffers alternate from pass to pass (finish_check)
-                const int alternate = (h->enable_subtraction && !h->forest_pass) ? 1 : 0;
+                const int alternate = (h->enable_subtraction && (!h->forest_pass || h->layout.full)) ? 1 : 0;
                 SB_CUDA(launch_p2p_allreduce(h->p2p.view, which, 2 * h->layout.total, ++h->p2p.epoch, alternate ? 0 : 1,
                                              h->d_error_flag, h->stream));
                 h->launches_count += 5;
@@ -2701,7 +2803,7 @@ static int finish_check(sb_handle* h, sb_iter_out* out) {
     out->train_error = po->acc[2];
     out->validation_error = po->acc[3];
     h->stats_ready = true;
-    if (h->enable_subtraction && !h->forest_pass) {  // keep this pass's merged accumulators for the children of its nodes (forest passes never pair)
+    if (h->enable_subtraction && (!h->forest_pass || h->layout.full)) {  // keep this pass's merged accumulators for the children of its nodes (a forest pass pairs only when it is full)
         std::swap(h->raw, h->raw_prev);  // (the layouts are swapped by the next sb_compute_begin)
         h->prev_valid = true;
     }

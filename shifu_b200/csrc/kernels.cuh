@@ -212,6 +212,9 @@ cudaError_t launch_forest_lists(const ForestListArgs& a, cudaStream_t s);
 cudaError_t launch_build_pair_off(const int32_t* slot_node, int n_slots, const int32_t* feats, const int32_t* begin,
                                   const int64_t* node_off, const int32_t* feat_bins, int stats_size, int n_features,
                                   int64_t* pair_off, cudaStream_t s);
+// full passes: pair_off[s][f] = slot_node[s] * node_stride + feat_off[f] (every valid feature of every node), -1 where feat_off is
+cudaError_t launch_fill_pair_off_full(const int32_t* slot_node, int n_slots, int64_t node_stride, const int64_t* feat_off, int n_features,
+                                      int64_t* pair_off, cudaStream_t s);
 struct HistClassArgs {
     const uint8_t* rm_bins;
     uint32_t fpad;
@@ -373,6 +376,10 @@ cudaError_t launch_finalize_tasks(const int64_t* raw_lo, const int64_t* raw_hi, 
 cudaError_t launch_pair_decide(const PairDesc* pairs, int n_pairs, const int64_t* prev_lo, const int64_t* prev_hi,
                                int stats_size, int kind, int n_features, int16_t* slot_tables, int64_t* pair_off,
                                int32_t* small_is_b, cudaStream_t s);
+// the same over 32-bit slot tables (forest passes)
+cudaError_t launch_pair_decide32(const PairDesc* pairs, int n_pairs, const int64_t* prev_lo, const int64_t* prev_hi,
+                                 int stats_size, int kind, int n_features, int32_t* slot_tables, int64_t* pair_off,
+                                 int32_t* small_is_b, cudaStream_t s);
 cudaError_t launch_pair_fixup(const PairDesc* pairs, int n_pairs, int64_t max_len, const int32_t* small_is_b,
                               const int64_t* prev_lo, const int64_t* prev_hi, int64_t* lo, int64_t* hi, cudaStream_t s);
 struct SplitTask {       // one (todo node, feature) pair

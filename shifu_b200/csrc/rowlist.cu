@@ -666,6 +666,24 @@ cudaError_t launch_forest_lists(const ForestListArgs& a, cudaStream_t s) {
     return cudaGetLastError();
 }
 
+__global__ void fill_pair_off_full_kernel(const int32_t* __restrict__ slot_node, int n_slots, int64_t node_stride,
+                                          const int64_t* __restrict__ feat_off, int n_features, int64_t* __restrict__ pair_off) {
+    const int64_t total = (int64_t)n_slots * n_features;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int s = (int)(i / n_features), f = (int)(i - (int64_t)s * n_features);
+        const int64_t o = feat_off[f];
+        pair_off[i] = o < 0 ? -1 : (int64_t)slot_node[s] * node_stride + o;
+    }
+}
+cudaError_t launch_fill_pair_off_full(const int32_t* slot_node, int n_slots, int64_t node_stride, const int64_t* feat_off, int n_features,
+                                      int64_t* pair_off, cudaStream_t s) {
+    if (n_slots <= 0 || n_features <= 0) return cudaSuccess;
+    const int64_t total = (int64_t)n_slots * n_features;
+    fill_pair_off_full_kernel<<<(unsigned)std::min<int64_t>((total + 255) / 256, 148 * 8), 256, 0, s>>>(slot_node, n_slots, node_stride, feat_off,
+                                                                                                    n_features, pair_off);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_build_pair_off(const int32_t* slot_node, int n_slots, const int32_t* feats, const int32_t* begin,
                                   const int64_t* node_off, const int32_t* feat_bins, int stats_size, int n_features,
                                   int64_t* pair_off, cudaStream_t s) {

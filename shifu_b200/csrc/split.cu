@@ -422,9 +422,10 @@ __global__ void node_best_kernel(const sb_gain* __restrict__ cand, const uint8_t
 // One warp per sibling pair: which child holds less (weighted) count under the parent's split?  Only that child is
 // accumulated directly; the other one is derived after the merge.  The decision is made from the parent's merged
 // (all-reduced) accumulators, so every GPU takes the same one.  Integer sums: the lane order does not matter.
+template <typename SlotT>
 __global__ void pair_decide_kernel(const PairDesc* __restrict__ pairs, int n_pairs, const int64_t* __restrict__ prev_lo,
                                    const int64_t* __restrict__ prev_hi, int stats_size, int kind, int n_features,
-                                   int16_t* __restrict__ slot_tables, int64_t* __restrict__ pair_off, int32_t* __restrict__ small_is_b) {
+                                   SlotT* __restrict__ slot_tables, int64_t* __restrict__ pair_off, int32_t* __restrict__ small_is_b) {
     const int p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (p >= n_pairs) return;
@@ -452,8 +453,8 @@ __global__ void pair_decide_kernel(const PairDesc* __restrict__ pairs, int n_pai
     const int b_small = (2 * left > total) ? 1 : 0;  // left = child A (even id); ties -> A
     if (lane == 0) {
         small_is_b[p] = b_small;
-        int16_t* table = slot_tables + d.table_off;
-        table[b_small ? d.node_a : d.node_b] = (int16_t)-1;  // the larger child is not accumulated
+        SlotT* table = slot_tables + d.table_off;
+        table[b_small ? d.node_a : d.node_b] = (SlotT)-1;  // the larger child is not accumulated
     }
     if (b_small) {
         int64_t* row = pair_off + (size_t)d.slot * n_features;
@@ -599,8 +600,17 @@ cudaError_t launch_pair_decide(const PairDesc* pairs, int n_pairs, const int64_t
                                int stats_size, int kind, int n_features, int16_t* slot_tables, int64_t* pair_off,
                                int32_t* small_is_b, cudaStream_t s) {
     if (n_pairs <= 0) return cudaSuccess;
-    pair_decide_kernel<<<(n_pairs * 32 + 127) / 128, 128, 0, s>>>(pairs, n_pairs, prev_lo, prev_hi, stats_size, kind, n_features,
-                                                          slot_tables, pair_off, small_is_b);
+    pair_decide_kernel<int16_t><<<(n_pairs * 32 + 127) / 128, 128, 0, s>>>(pairs, n_pairs, prev_lo, prev_hi, stats_size, kind, n_features,
+                                                                   slot_tables, pair_off, small_is_b);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pair_decide32(const PairDesc* pairs, int n_pairs, const int64_t* prev_lo, const int64_t* prev_hi,
+                                 int stats_size, int kind, int n_features, int32_t* slot_tables, int64_t* pair_off,
+                                 int32_t* small_is_b, cudaStream_t s) {
+    if (n_pairs <= 0) return cudaSuccess;
+    pair_decide_kernel<int32_t><<<(n_pairs * 32 + 127) / 128, 128, 0, s>>>(pairs, n_pairs, prev_lo, prev_hi, stats_size, kind, n_features,
+                                                                   slot_tables, pair_off, small_is_b);
     return cudaGetLastError();
 }
 
