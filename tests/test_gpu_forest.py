@@ -57,8 +57,10 @@ def test_per_tree_launches_still_match_the_oracle():
 
 
 def _grow_both(n, n_bins, seed, n_trees, max_depth, impurity, weighted):
+    # 0: forest passes, full (every valid feature accumulated, siblings paired); 16: one launch sequence per tree (full as
+    # well); 4: SB_FLAG_NO_SUBTRACTION -- forest passes that accumulate every listed (node, feature) directly
     cfgs = [ConfigArrays(n_bins, impurity=impurity, num_classes=2, loss=capi.SB_LOSS_SQUARED, is_gbdt=False, tree_num=n_trees,
-                         weights_per_row=n_trees, max_depth=max_depth, min_instances_per_node=1, flags=f) for f in (0, NO_FOREST)]
+                         weights_per_row=n_trees, max_depth=max_depth, min_instances_per_node=1, flags=f) for f in (0, NO_FOREST, 4)]
     cols, y, sig, w = make_data(n, n_bins, seed, weighted=weighted, wpr=n_trees, poisson=True)
     vcols, vy, vsig, _ = make_data(n // 3, n_bins, seed + 5, weighted=weighted)
     workers = [Worker(c) for c in cfgs]
@@ -73,12 +75,14 @@ def _grow_both(n, n_bins, seed, n_trees, max_depth, impurity, weighted):
     while todo_nodes:
         todo = [(k, t, nd.id, rng.choice(F, size=max(1, (2 * F) // 3), replace=False).tolist()) for k, (t, nd) in enumerate(todo_nodes)]
         it = IterIn(cfgs[0], [(t, roots[t]) for t in range(n_trees)], todo)
-        a, b = workers[0].compute(it), workers[1].compute(it)
+        a, b, c = workers[0].compute(it), workers[1].compute(it), workers[2].compute(it)
         assert np.array_equal(a[4], b[4]), "forest pass and per-tree passes must give the same statistics, bit for bit"
+        assert np.array_equal(a[4], c[4]), "paired (parent - sibling) and directly accumulated statistics must be the same, bit for bit"
         for x, z in zip(a[:4], b[:4]):  # fp64 sums taken in a different order
             assert abs(x - z) <= 1e-12 * abs(z) + 1e-300
         ga, _ = workers[0].best_splits(len(todo))
         gb, _ = workers[1].best_splits(len(todo))
+        workers[2].best_splits(len(todo))
         assert all(p.found == q.found and p.feature == q.feature and p.gain == q.gain for p, q in zip(ga, gb))
         passes += 1
         nxt = []
@@ -159,3 +163,47 @@ def test_forest_only_some_trees_have_todo_nodes():
     assert np.array_equal(d[4], o[4])
     for a, b in zip(d[:4], o[:4]):
         assert abs(a - b) <= 1e-9 * abs(b) + 1e-12, (d[:4], o[:4])
+
+
+def test_gbt_feature_lists_full_passes_equal_direct_accumulation():
+    """GBT nodes with feature lists of their own (FeatureSubsetStrategy): the full pass (internal all-features layout,
+    sibling subtraction, root count cache, gather into the caller's layout) against SB_FLAG_NO_SUBTRACTION, which
+    accumulates exactly the listed (node, feature) blocks -- bit for bit, over two trees, with lists that differ between
+    siblings and a root that takes every feature."""
+    n, n_bins = 30000, [64] * 20 + [16] * 5 + [300]
+    is_cat = [0] * 25 + [1]
+    cols, y, sig, _ = make_data(n, n_bins, seed=91, weighted=True, is_categorical=is_cat)
+    F = len(n_bins)
+    runs = []
+    for flags in (0, 4):
+        cfg = ConfigArrays(n_bins, is_categorical=is_cat, max_depth=5, tree_num=2, min_instances_per_node=1, flags=flags)
+        w = Worker(cfg)
+        w.load_rows(cols, y, sig, None)
+        rng = np.random.default_rng(7)
+        stats_all, roots = [], []
+        for t in range(2):
+            root = Node(1)
+            roots.append(root)
+            todo_nodes, switch = [root], True
+            while todo_nodes:
+                todo = [(k, t, nd.id, [] if nd.id == 1 else sorted(rng.choice(F, size=F // 2, replace=False).tolist()))
+                        for k, nd in enumerate(todo_nodes)]
+                it = IterIn(cfg, [(i, r) for i, r in enumerate(roots)], todo, switch_to_next_tree=switch, is_first_tree=(t == 0))
+                res = w.compute(it)
+                stats_all.append(res[4].copy())
+                gains, bits = w.best_splits(len(todo), with_cat=True)
+                nxt = []
+                for k, nd in enumerate(todo_nodes):
+                    g = gains[k]
+                    nd.predict = g.predict if g.found else nd.predict
+                    if not g.found or g.gain <= 0 or index_to_level(nd.id) == 5:
+                        continue
+                    left, right = apply_gain(cfg, nd, g, bits, k)
+                    if index_to_level(nd.id) + 1 < 5:
+                        nxt += [left, right]
+                todo_nodes, switch = nxt, False
+        runs.append(stats_all)
+        w.close()
+    assert len(runs[0]) == len(runs[1]) >= 8
+    for a, b in zip(runs[0], runs[1]):
+        assert np.array_equal(a, b)
