@@ -10,7 +10,6 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
-#include <unordered_map>
 #include <memory>
 
 #include "common.cuh"
@@ -438,7 +437,7 @@ int make_tensor_map(sb_handle* h, RowSet& r) {
 int prewarm_pool(sb_handle* h) {
     // GBT: the statistics of one tree level.  RF: 10^4 node histograms at depth 10 (4 GB) + the operand list of a forest
     // pass, 8 bytes per (row, tree) pair
-    const long long def_mb = h->cfg.is_gbdt ? 512 : 4096 + (long long)(((double)h->train.n * std::max(h->cfg.tree_num, 1) * 8.0) / (1 << 20));
+    const long long def_mb = h->cfg.is_gbdt ? 512 : 8192 + (long long)(((double)h->train.n * std::max(h->cfg.tree_num, 1) * 8.0) / (1 << 20));
     const long long want_mb = getenv("SB_POOL_RESERVE_MB") ? atoll(getenv("SB_POOL_RESERVE_MB")) : def_mb;
     if (want_mb <= 0) return SB_OK;
     cudaMemPool_t pool = nullptr;
@@ -1335,24 +1334,32 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
     std::vector<int> partner((size_t)N, -1);     // todo index of child B for child A of a pair; -2 for child B
     std::vector<int> pair_parent_prev;           // per pair (in the order of their child A in by_tree): index into prev_layout
     if (lay.full && h->enable_subtraction && h->use_prev && h->prev_layout.full) {
-        auto key_of = [](int tree, int node) { return ((uint64_t)(uint32_t)tree << 32) | (uint32_t)node; };
-        std::unordered_map<uint64_t, int> cur_idx, prev_idx;
-        cur_idx.reserve((size_t)N * 2);
-        prev_idx.reserve(h->prev_layout.nodes.size() * 2);
-        for (int i = 0; i < N; ++i) cur_idx[key_of(lay.nodes[(size_t)i].tree_id, lay.nodes[(size_t)i].node_id)] = i;
-        for (size_t i = 0; i < h->prev_layout.nodes.size(); ++i)
-            prev_idx[key_of(h->prev_layout.nodes[i].tree_id, h->prev_layout.nodes[i].node_id)] = (int)i;
-        for (int q = 0; q < N; ++q) {
-            const int i = by_tree[(size_t)q];
-            const auto& a = lay.nodes[(size_t)i];
-            if (a.node_id < 2 || (a.node_id & 1)) continue;
-            auto ib = cur_idx.find(key_of(a.tree_id, a.node_id + 1));
-            auto ip = prev_idx.find(key_of(a.tree_id, a.node_id / 2));
-            if (ib == cur_idx.end() || ip == prev_idx.end()) continue;
-            if (find_tree(in, a.tree_id) == nullptr) continue;
-            partner[(size_t)i] = ib->second;
-            partner[(size_t)ib->second] = -2;
-            pair_parent_prev.push_back(ip->second);
+        // (tree, heap id) -> index, for this pass's nodes and the previous pass's: flat tables, one row per tree
+        int stride = 2;
+        for (int i = 0; i < N; ++i) stride = std::max(stride, lay.nodes[(size_t)i].node_id + 2);
+        for (const auto& pn : h->prev_layout.nodes) stride = std::max(stride, pn.node_id + 2);
+        if ((int64_t)stride * T_arr <= ((int64_t)1 << 26)) {
+            std::vector<int> cur_idx((size_t)stride * T_arr, -1), prev_idx((size_t)stride * T_arr, -1);
+            for (int i = 0; i < N; ++i) cur_idx[(size_t)lay.nodes[(size_t)i].tree_id * stride + lay.nodes[(size_t)i].node_id] = i;
+            for (size_t i = 0; i < h->prev_layout.nodes.size(); ++i) {
+                const auto& pn = h->prev_layout.nodes[i];
+                if (pn.tree_id >= 0 && pn.tree_id < T_arr && pn.node_id >= 0) prev_idx[(size_t)pn.tree_id * stride + pn.node_id] = (int)i;
+            }
+            int have_tree = -1;
+            bool tree_ok = false;
+            for (int q = 0; q < N; ++q) {
+                const int i = by_tree[(size_t)q];
+                const auto& a = lay.nodes[(size_t)i];
+                if (a.node_id < 2 || (a.node_id & 1)) continue;
+                const int ib = cur_idx[(size_t)a.tree_id * stride + a.node_id + 1];
+                const int ip = prev_idx[(size_t)a.tree_id * stride + a.node_id / 2];
+                if (ib < 0 || ip < 0) continue;
+                if (have_tree != a.tree_id) { have_tree = a.tree_id; tree_ok = find_tree(in, a.tree_id) != nullptr; }
+                if (!tree_ok) continue;
+                partner[(size_t)i] = ib;
+                partner[(size_t)ib] = -2;
+                pair_parent_prev.push_back(ip);
+            }
         }
     }
     std::vector<int> slot_of_todo((size_t)N, -1);
@@ -1393,7 +1400,7 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
     // the pairs: parent's split block and node block in the previous pass, the children's blocks in this one
     if (!pair_parent_prev.empty()) {
         std::vector<int> msg_index;
-        int msg_index_tree = -1;
+        int msg_index_tree = -1, li = -1;
         const sb_tree* tr_msg = nullptr;
         size_t pi = 0;
         for (int q = 0; q < N; ++q) {
@@ -1404,6 +1411,7 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
             const auto& par = h->prev_layout.nodes[(size_t)pair_parent_prev[pi++]];
             if (msg_index_tree != na.tree_id) {
                 msg_index_tree = na.tree_id;
+                for (li = 0; li < (int)tl.size() && tl[(size_t)li].tree_id != na.tree_id; ++li) {}
                 tr_msg = find_tree(in, na.tree_id);
                 msg_index.clear();
                 for (int k = 0; k < tr_msg->n_nodes; ++k) {
@@ -1416,7 +1424,6 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
             const sb_node* pn = (pid < (int)msg_index.size() && msg_index[(size_t)pid] >= 0) ? &tr_msg->nodes[msg_index[(size_t)pid]] : nullptr;
             if (!pn || pn->feature < 0 || pn->feature >= F || h->all_feature_pos[(size_t)pn->feature] < 0)
                 return fail(SB_ERR_STATE, "histogram subtraction: parent split not found");
-            const int li = [&] { for (size_t k = 0; k < tl.size(); ++k) if (tl[k].tree_id == na.tree_id) return (int)k; return -1; }();
             PairDesc d{};
             d.parent_split_block = par.offset + h->all_feat_off[(size_t)h->all_feature_pos[(size_t)pn->feature]];
             d.parent_off = par.offset;
