@@ -355,6 +355,8 @@ SB_API int sb_scorer_last_kernel_ms(sb_scorer* s, float* ms);
  * the 128 bytes to every process (any side channel); each process then calls sb_dist_init once on its handle.
  * Afterwards every rank's sb_compute returns the merged statistics and sb_best_splits the same splits.
  * NCCL is opened with dlopen("libnccl.so.2") at the first call; single-GPU use needs no NCCL.
+ * Every rank must hold at least one training row (a rank without rows is refused: it would not take part in the
+ * sibling subtraction the other ranks plan).
  * No counterpart call in the reference: there the merge is the Guagua master's message loop.
  */
 SB_API int sb_dist_unique_id(uint8_t* id128);

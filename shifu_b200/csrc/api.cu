@@ -1291,6 +1291,8 @@ int plan_forest(sb_handle* h, const sb_iter_in* in) {
     (void)in;
     h->forest_batches.clear();
     h->launches.clear();
+    h->pairs.clear();
+    h->pair_max_len = 0;
     const TodoLayout& lay = h->layout;
     const int F = h->cfg.n_features;
     const int N = (int)lay.nodes.size();
@@ -2227,6 +2229,9 @@ SB_API int sb_compute_begin(sb_handle* h, const sb_iter_in* in) {
     if (!h->train.loaded) return fail(SB_ERR_STATE, "sb_compute before sb_load_rows");
     if (in->continuous_running_start) return fail(SB_ERR_UNSUPPORTED, "continuous training is handled on the Java side");
     if (in->n_trees < 1 || !in->trees) return fail(SB_ERR_INVALID, "no trees");
+    // A rank without a single training row plans no sibling pairs, so after the merge it would not derive the larger
+    // children the other ranks derive: its statistics, and the trees its master grows from them, would differ.
+    if (h->comm && h->train.n == 0) return fail(SB_ERR_UNSUPPORTED, "multi-GPU merge: every rank must hold at least one training row");
     SB_CUDA(cudaSetDevice(h->cfg.device));
     if (h->trace) {
         sb_handle::PassTrace p{};
