@@ -273,6 +273,7 @@ struct sb_handle {
     int flat_max_list = 0, flat_max_cat_bins = 0;
     bool flat_has_cat = false;
     std::vector<uint8_t> flat_used;  // feature slot appears in some caller list of the pass
+    size_t flat_n_cat = 0;           // categorical entries over all caller lists
     int64_t* d_int_feat_off = nullptr;  // [F] offset of a feature's block inside a node block that holds every valid feature, -1
     std::vector<uint32_t> col_flags;  // per sample-weight column: bit0 non-integer products, bit1 a weight != 1
     size_t scan_temp_bytes = 0;
@@ -657,7 +658,11 @@ int stage_flat_lists(sb_handle* h) {
     h->flat_max_cat_bins = 0;
     if (N == 0) return SB_OK;
     h->flat_used.assign((size_t)F, 0);
-    for (int32_t f : lay.flat_feats) h->flat_used[(size_t)f] = 1;
+    h->flat_n_cat = 0;
+    for (int32_t f : lay.flat_feats) {
+        h->flat_used[(size_t)f] = 1;
+        h->flat_n_cat += h->is_cat[(size_t)f] ? 1 : 0;
+    }
     for (int i = 0; i < N; ++i) h->flat_max_list = std::max(h->flat_max_list, lay.flat_begin[(size_t)i + 1] - lay.flat_begin[(size_t)i]);
     for (int f = 0; f < F; ++f)
         if (h->flat_used[(size_t)f] && h->is_cat[(size_t)f]) { h->flat_has_cat = true; h->flat_max_cat_bins = std::max(h->flat_max_cat_bins, h->n_bins[(size_t)f]); }
@@ -1689,6 +1694,7 @@ int plan_split_tasks(sb_handle* h) {
     const size_t N = lay.nodes.size();
     h->has_cat_tasks = false;
     int max_cat_bins = 0;
+    size_t n_cat = 0, n_cat_tmpl = 0;  // categorical tasks of the pass / of the one list all nodes share
     bool same_lists = N > 0 && !lay.flat;
     for (size_t n = 1; n < N && same_lists; ++n) same_lists = lay.nodes[n].features == lay.nodes[0].features;
     // tasks of one node: (feature, block offset relative to the node, bins, kind, HashMap visit rank), written at `out`
@@ -1708,7 +1714,7 @@ int plan_split_tasks(sb_handle* h) {
             t.categorical = h->is_cat[f];
             t.visit_rank = rank[k];
             t.pad = 0;
-            if (t.categorical) { h->has_cat_tasks = true; max_cat_bins = std::max(max_cat_bins, t.n_bins); }
+            if (t.categorical) { h->has_cat_tasks = true; max_cat_bins = std::max(max_cat_bins, t.n_bins); n_cat_tmpl += 1; }
             out[k] = t;
         }
     };
@@ -1724,6 +1730,7 @@ int plan_split_tasks(sb_handle* h) {
         if (h->flat_max_list > 8192) return fail(SB_ERR_UNSUPPORTED, "a todo node with more than 8192 features of its own");
         h->has_cat_tasks = h->flat_has_cat;
         max_cat_bins = h->flat_max_cat_bins;
+        n_cat = h->flat_n_cat;
         h->node_task_begin.alias(const_cast<int32_t*>(h->d_flat_begin));
         SB_CUDA(h->tasks.reserve(h->stream, n_tasks + 1));
         SB_CUDA(launch_build_tasks(h->d_flat_feats, h->d_flat_begin, h->d_flat_node_off, (int)N, std::max(h->flat_max_list, 1), h->d_feat_bins,
@@ -1737,6 +1744,7 @@ int plan_split_tasks(sb_handle* h) {
         SB_CUDA(h->stage.take(std::max<size_t>(fk, 1), &tmpl, &d_tmpl, h->stream));
         SB_CUDA(h->stage.take(N, &node_off, &d_node_off, h->stream));
         node_tasks(0, 0, tmpl);
+        n_cat = n_cat_tmpl * N;
         for (size_t n = 0; n < N; ++n) node_off[n] = lay.nodes[n].offset;
         SB_CUDA(h->stage.flush(h->stream));
         SB_CUDA(h->tasks.reserve(h->stream, n_tasks + 1));
@@ -1762,7 +1770,7 @@ int plan_split_tasks(sb_handle* h) {
             max_list = std::max(max_list, nd.features.size());
             if (h->any_categorical)
                 for (int f : nd.features)
-                    if (h->is_cat[(size_t)f]) { h->has_cat_tasks = true; max_cat_bins = std::max(max_cat_bins, h->n_bins[(size_t)f]); }
+                    if (h->is_cat[(size_t)f]) { h->has_cat_tasks = true; max_cat_bins = std::max(max_cat_bins, h->n_bins[(size_t)f]); n_cat += 1; }
         }
         begin[N] = (int32_t)at;
         if (max_list > 8192) return fail(SB_ERR_UNSUPPORTED, "a todo node with more than 8192 features of its own");
@@ -1777,10 +1785,11 @@ int plan_split_tasks(sb_handle* h) {
     if (h->has_cat_tasks) {
         SB_CUDA(h->cand_bits.reserve(h->stream, n_tasks * SB_MAX_CAT_BYTES));
         SB_CUDA(h->out_bits.reserve(h->stream, N * SB_MAX_CAT_BYTES));
-        SB_CUDA(h->sort_keys.reserve(h->stream, n_tasks * max_cat_bins));
-        SB_CUDA(h->sort_idx.reserve(h->stream, n_tasks * max_cat_bins));
-        SB_CUDA(h->sort_tmp.reserve(h->stream, n_tasks * max_cat_bins));
-        SB_CUDA(h->sort_flags.reserve(h->stream, n_tasks * max_cat_bins));
+        const size_t scratch = std::max<size_t>(n_cat, 1) * (size_t)max_cat_bins;  // per categorical task
+        SB_CUDA(h->sort_keys.reserve(h->stream, scratch));
+        SB_CUDA(h->sort_idx.reserve(h->stream, scratch));
+        SB_CUDA(h->sort_tmp.reserve(h->stream, scratch));
+        SB_CUDA(h->sort_flags.reserve(h->stream, scratch));
     }
     h->max_bins = max_cat_bins;
     return SB_OK;
@@ -1953,8 +1962,8 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
     SB_CUDA(cudaMalloc(&h->d_rows_streamed, 8));
     SB_CUDA(cudaMemset(h->d_rows_streamed, 0, 8));
     SB_CUDA(cudaMemset(h->d_error_flag, 0, 4));
-    SB_CUDA(cudaMalloc(&h->d_cnt_shift, 8));
-    SB_CUDA(cudaMemset(h->d_cnt_shift, 0, 8));
+    SB_CUDA(cudaMalloc(&h->d_cnt_shift, 16));  // count shift, integer-weights flag, scratch slot counter of the best-split kernel
+    SB_CUDA(cudaMemset(h->d_cnt_shift, 0, 16));
     *out = h.release();
     return SB_OK;
 }
@@ -2838,6 +2847,8 @@ static int best_enqueue(sb_handle* h, bool want_bits) {
     if (h->has_cat_tasks) SB_CUDA(cudaMemsetAsync(h->out_bits.p, 0, (size_t)n_nodes * SB_MAX_CAT_BYTES, h->stream));
     SplitScratch sc;
     sc.keys = h->sort_keys.p; sc.idx = h->sort_idx.p; sc.tmp = h->sort_tmp.p; sc.flags = h->sort_flags.p; sc.max_bins = h->max_bins;
+    sc.next = h->d_cnt_shift + 2;  // third word of the same small allocation
+    if (h->has_cat_tasks) SB_CUDA(cudaMemsetAsync(sc.next, 0, 4, h->stream));
     SB_CUDA(launch_best_splits(h->stats.p, h->tasks.p, h->n_tasks, n_nodes, h->cfg.impurity, h->stats_size,
                                h->cfg.min_instances_per_node, h->cfg.min_info_gain, h->cand.p,
                                h->has_cat_tasks ? h->cand_bits.p : nullptr, h->gain_out.p,

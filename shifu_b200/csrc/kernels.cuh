@@ -399,12 +399,13 @@ cudaError_t launch_build_tasks(const int32_t* feats, const int32_t* begin, const
                                SplitTask* tasks, cudaStream_t s);
 cudaError_t launch_counts_cache(int64_t* raw_lo, int64_t* raw_hi, int64_t* cache, int64_t n_bins_total, int stats_size, int save,
                                 cudaStream_t s);
-struct SplitScratch {    // categorical features only: per task, max_bins entries each
+struct SplitScratch {    // categorical features only: max_bins entries per CATEGORICAL task; a task claims its piece from `next`
     double* keys = nullptr;
     int* idx = nullptr;
     int* tmp = nullptr;
     uint8_t* flags = nullptr;
     int max_bins = 0;
+    int* next = nullptr;     // device counter, zero before the launch
 };
 cudaError_t launch_best_splits(const double* stats, const SplitTask* tasks, int n_tasks, int n_nodes, int impurity,
                                int stats_size, int min_instances, double min_info_gain, sb_gain* cand /*[n_tasks]*/,

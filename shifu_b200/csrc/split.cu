@@ -260,7 +260,7 @@ constexpr int RANK_SORT_MAX = 128;   // categories up to which the warp sorts by
 __global__ void __launch_bounds__(SPLIT_WARPS * 32)
 feature_split_kernel(const double* __restrict__ stats, const SplitTask* __restrict__ tasks, int n_tasks,
                      int impurity_kind, int c, int min_inst, double min_gain, sb_gain* cand, uint8_t* cand_bits,
-                     double* sort_keys, int* sort_idx, int* sort_tmp, uint8_t* pass_flags, int max_bins) {
+                     double* sort_keys, int* sort_idx, int* sort_tmp, uint8_t* pass_flags, int max_bins, int* next_slot) {
     __shared__ double stage[SPLIT_WARPS][SPLIT_STAGE];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int t = blockIdx.x * SPLIT_WARPS + warp;
@@ -277,10 +277,15 @@ feature_split_kernel(const double* __restrict__ stats, const SplitTask* __restri
     int* order = nullptr;
     uint8_t* flags = nullptr;
     if (tk.categorical) {
-        double* key = sort_keys + (size_t)t * max_bins;
-        order = sort_idx + (size_t)t * max_bins;
-        int* tmp = sort_tmp + (size_t)t * max_bins;
-        flags = pass_flags + (size_t)t * max_bins;
+        // scratch exists for the categorical tasks only (a forest level has 10^5 tasks, a fifth of them categorical, with
+        // up to 1001 entries each): the task claims the next piece; which one it gets does not matter
+        int slot = 0;
+        if (lane == 0) slot = atomicAdd(next_slot, 1);
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        double* key = sort_keys + (size_t)slot * max_bins;
+        order = sort_idx + (size_t)slot * max_bins;
+        int* tmp = sort_tmp + (size_t)slot * max_bins;
+        flags = pass_flags + (size_t)slot * max_bins;
         for (int i = lane; i < tk.n_bins; i += 32) {
             double k;
             if (variance) {  // dt/Impurity.java:213-231: empty bins sort first with key Double.MIN_VALUE
@@ -649,7 +654,7 @@ cudaError_t launch_best_splits(const double* stats, const SplitTask* tasks, int 
     if (n_tasks <= 0 || n_nodes <= 0) return cudaSuccess;
     feature_split_kernel<<<(n_tasks + SPLIT_WARPS - 1) / SPLIT_WARPS, SPLIT_WARPS * 32, 0, s>>>(stats, tasks, n_tasks, impurity, stats_size, min_instances,
                                                             min_info_gain, cand, cand_bits, sc.keys, sc.idx, sc.tmp,
-                                                            sc.flags, sc.max_bins);
+                                                            sc.flags, sc.max_bins, sc.next);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     node_best_kernel<<<(n_nodes * 32 + 127) / 128, 128, 0, s>>>(cand, cand_bits, tasks, node_task_begin, n_nodes, out, out_bits);
