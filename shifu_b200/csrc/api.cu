@@ -1924,11 +1924,6 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
     h->enable_forest = (cfg->flags & SB_FLAG_NO_FOREST_PASS) == 0;
     // an RF pass stages the feature lists of thousands of todo nodes: start with an arena that does not have to grow level by level
     if (!cfg->is_gbdt) SB_CUDA(h->stage.grow((size_t)32 << 20, h->stream));
-    // ... and a pinned result block for 10^4 todo nodes (growing it synchronises the device and takes milliseconds)
-    if (!cfg->is_gbdt) {
-        SB_CUDA(cudaMallocHost(&h->pin, (size_t)4 << 20));
-        h->pin_bytes = (size_t)4 << 20;
-    }
     if (cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, cfg->device) != cudaSuccess || h->sm_count < 1) h->sm_count = 148;
     h->stats_size = is_variance(cfg->impurity) ? 3 : cfg->num_classes;
     h->stat_kind = is_variance(cfg->impurity) ? STAT_VARIANCE : STAT_CLASS;
@@ -1952,6 +1947,13 @@ SB_API int sb_create(const sb_config* cfg, sb_handle** out) {
     for (int f : h->all_features)
         if (h->is_cat[(size_t)f]) { h->any_categorical = true; h->max_categorical_bins = std::max(h->max_categorical_bins, h->n_bins[(size_t)f]); }
     SB_CUDA(cudaMemcpy(h->d_feat_bins, h->n_bins.data(), sizeof(int32_t) * cfg->n_features, cudaMemcpyHostToDevice));
+    if (!cfg->is_gbdt) {
+        // RF: a pinned result block for 10^4 todo nodes up front (growing it synchronises the device and takes tens of
+        // milliseconds); with categorical features a node also returns up to 4 KB of category bits
+        const size_t pin0 = h->any_categorical ? (size_t)64 << 20 : (size_t)4 << 20;
+        SB_CUDA(cudaMallocHost(&h->pin, pin0));
+        h->pin_bytes = pin0;
+    }
     SB_CUDA(cudaMalloc(&h->d_acc, sizeof(double) * 4));
     SB_CUDA(cudaMalloc(&h->d_err_scratch, sizeof(double) * ERR_SCRATCH_DOUBLES));
     SB_CUDA(cudaMemset(h->d_err_scratch, 0, sizeof(double) * ERR_SCRATCH_DOUBLES));
