@@ -441,18 +441,23 @@ int prewarm_pool(sb_handle* h) {
     const long long def_mb = h->cfg.is_gbdt ? 512 : 8192 + (long long)(((double)h->train.n * std::max(h->cfg.tree_num, 1) * 8.0) / (1 << 20));
     const long long want_mb = getenv("SB_POOL_RESERVE_MB") ? atoll(getenv("SB_POOL_RESERVE_MB")) : def_mb;
     if (want_mb <= 0) return SB_OK;
-    cudaMemPool_t pool = nullptr;
-    if (cudaDeviceGetDefaultMemPool(&pool, h->cfg.device) != cudaSuccess || !pool) { cudaGetLastError(); return SB_OK; }
-    uint64_t reserved = 0;
-    if (cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &reserved) != cudaSuccess) { cudaGetLastError(); return SB_OK; }
+    // One block of the wanted size, allocated and freed: if the pool already holds such a block (an earlier handle of
+    // this process reserved it) this costs nothing; a pool that is large but fragmented by what earlier handles
+    // left behind grows here, once, and not level by level inside the passes.
     size_t free_b = 0, total_b = 0;
     SB_CUDA(cudaMemGetInfo(&free_b, &total_b));
-    const uint64_t want = (uint64_t)want_mb << 20;
-    if (reserved >= want) return SB_OK;
-    const size_t add = (size_t)std::min<uint64_t>(want - reserved, free_b / 2);
-    if (add < ((size_t)1 << 20)) return SB_OK;
+    cudaMemPool_t pool = nullptr;
+    uint64_t reserved = 0, used = 0;
+    if (cudaDeviceGetDefaultMemPool(&pool, h->cfg.device) == cudaSuccess && pool) {
+        if (cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &reserved) != cudaSuccess) reserved = 0;
+        if (cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used) != cudaSuccess) used = 0;
+    }
+    cudaGetLastError();
+    const uint64_t idle = reserved > used ? reserved - used : 0;  // what the pool holds without anyone using it
+    const size_t want = (size_t)std::min<uint64_t>((uint64_t)want_mb << 20, (uint64_t)free_b / 2 + idle);
+    if (want < ((size_t)1 << 20)) return SB_OK;
     void* p = nullptr;
-    if (cudaMallocAsync(&p, add, h->stream) == cudaSuccess) cudaFreeAsync(p, h->stream);
+    if (cudaMallocAsync(&p, want, h->stream) == cudaSuccess) cudaFreeAsync(p, h->stream);
     else cudaGetLastError();  // not enough room: the buffers grow on demand as before
     return SB_OK;
 }
