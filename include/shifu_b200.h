@@ -58,7 +58,8 @@ enum { SB_SPLIT_CONTINUOUS = 1, SB_SPLIT_CATEGORICAL = 2 };
 /* sb_config.flags */
 #define SB_FLAG_DETERMINISTIC 1u /* reserved: the histogram path is order-independent by construction */
 #define SB_FLAG_NO_SUBTRACTION 4u /* accumulate every todo node directly instead of deriving the larger child of a
-                                     sibling pair as parent - smaller child (same numbers either way) */
+                                     sibling pair as parent - smaller child (same numbers either way); nodes with
+                                     feature lists of their own are then accumulated for the listed features only */
 #define SB_FLAG_NO_ROOT_COUNT_CACHE 8u /* accumulate the bin counts of a tree root every time instead of reusing those of the
                                           previous root pass while the sample weights are unchanged */
 #define SB_FLAG_NO_FOREST_PASS 16u /* RF: one set of launches per tree and pass instead of one for all trees of the pass

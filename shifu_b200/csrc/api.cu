@@ -1298,7 +1298,6 @@ int plan_histograms(sb_handle* h, const sb_iter_in* in) {
 // (every slot accumulates every feature of a launched tile; columns outside a node's list are never flushed), and the
 // (slot, feature) offset table is filled on the device from the lists.
 int plan_forest(sb_handle* h, const sb_iter_in* in) {
-    (void)in;
     h->forest_batches.clear();
     h->launches.clear();
     h->pairs.clear();
